@@ -1,0 +1,278 @@
+/*
+ * minpy_cuda.h -- C ABI of libminpy_cuda.so, the sm_100a compute library behind the
+ * `cuda` array variant of MinPy (minpy/array_variants/cuda).
+ *
+ * The reference (dmlc/minpy @2e44927) has no native code of its own: its GPU variant
+ * calls into MXNet's NDArray library (minpy/array_variants/mxnet/mxnet_core.py:100-170).
+ * Every entry point below therefore replaces one *Python-level* call site of the
+ * reference; the file:line each one stands in for is cited beside it.  A maintainer
+ * binds these with ctypes; no C++ or torch types cross the ABI.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; mc_last_error() gives
+ *     the message of the last failure on the calling thread;
+ *   - all array pointers are DEVICE pointers owned by the caller, dense row-major,
+ *     float32 unless the parameter name says otherwise (i32 / i64 / u8 / f64);
+ *   - work is enqueued on the library's current stream (mc_set_stream); nothing
+ *     synchronises unless the name says so (mc_sync, mc_memcpy_d2h);
+ *   - `n`, `rows`, `cols`, `outer`, `red`, `inner` are element counts (int64_t).
+ */
+#ifndef MINPY_CUDA_H_
+#define MINPY_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ runtime --- */
+/* Device selection: replaces minpy/context.py:55-56 (mxnet.Context construction). */
+int mc_init(int device);
+int mc_device_count(int* count);
+int mc_set_device(int device);
+int mc_get_device(int* device);
+int mc_sm_count(int* count);
+/* Stream used by every later call; NULL selects the legacy default stream. */
+int mc_set_stream(void* cuda_stream);
+int mc_get_stream(void** cuda_stream);
+/* Blocks until the current stream drains: replaces NDArray.wait_to_read (minpy/array.py:480-487). */
+int mc_sync(void);
+const char* mc_last_error(void);
+/* Number of kernels this library has launched since load (bench.py's gpu_launches). */
+int mc_launch_count(uint64_t* count);
+
+/* Stream-ordered device allocator (cudaMallocAsync pool): replaces NDArray allocation
+ * inside mxnet.ndarray.array / mx.nd.* results (minpy/array.py:388-389). */
+int mc_alloc(void** ptr, size_t nbytes);
+int mc_free(void* ptr);
+int mc_host_alloc(void** ptr, size_t nbytes);   /* pinned host memory */
+int mc_host_free(void* ptr);
+int mc_mem_info(size_t* free_bytes, size_t* total_bytes);
+/* Copies: replace Array._synchronize_data (minpy/array.py:375-390). d2h synchronises. */
+int mc_memcpy_h2d(void* dst_dev, const void* src_host, size_t nbytes);
+int mc_memcpy_d2h(void* dst_host, const void* src_dev, size_t nbytes);
+int mc_memcpy_d2h_async(void* dst_host, const void* src_dev, size_t nbytes);
+int mc_memcpy_d2d(void* dst_dev, const void* src_dev, size_t nbytes);
+int mc_memset(void* dst_dev, int byte, size_t nbytes);
+/* CUDA events on the current stream (bench timing). */
+int mc_event_create(void** ev);
+int mc_event_record(void* ev);
+int mc_event_sync(void* ev);
+int mc_event_elapsed_ms(void* start, void* stop, float* ms);
+int mc_event_destroy(void* ev);
+/* CUDA-graph capture of a step on the current stream (must be a non-default stream). */
+int mc_graph_begin(void);
+int mc_graph_end(void** graph_exec);
+int mc_graph_launch(void* graph_exec);
+int mc_graph_destroy(void* graph_exec);
+
+/* ------------------------------------------------------------- elementwise --- */
+/* Unary ufuncs: numpy_core.py:228-230,267-276,303 / mxnet_core.py:116-118,150-159. */
+enum mc_unary_op {
+  MC_NEG = 0, MC_ABS, MC_SIGN, MC_ROUND, MC_CEIL, MC_FLOOR, MC_SQRT, MC_EXP, MC_LOG,
+  MC_SIN, MC_COS, MC_TANH, MC_SIGMOID, MC_SQUARE, MC_RECIP, MC_RELU, MC_COPY, MC_COSH,
+  MC_LOGICAL_NOT, MC_UNARY_COUNT
+};
+int mc_unary(int op, const float* x, float* y, int64_t n);
+
+/* Binary ufuncs and comparisons (0/1 float results, as the MXNet variant gave):
+ * numpy_core.py:240-291; comparisons minpy/array.py:73-89. */
+enum mc_binary_op {
+  MC_ADD = 0, MC_SUB, MC_MUL, MC_DIV, MC_POW, MC_MAX, MC_MIN, MC_MOD,
+  MC_EQ, MC_NE, MC_LT, MC_GT, MC_LE, MC_GE, MC_BINARY_COUNT
+};
+int mc_binary(int op, const float* a, const float* b, float* out, int64_t n);
+/* scalar_left != 0 computes op(s, a[i]) instead of op(a[i], s). */
+int mc_binary_scalar(int op, const float* a, float s, int scalar_left, float* out, int64_t n);
+/* out(rows, cols) = op(a(rows, cols), v) with v a row vector (cols,) [vec_is_col == 0] or a
+ * column vector (rows,) [vec_is_col != 0]; vec_left puts v on the left of op.
+ * The (N,D) o (D,) bias / batchnorm-scale pattern of nn/layers.py:27,107. */
+int mc_binary_vec(int op, const float* a, const float* v, int vec_is_col, int vec_left,
+                  float* out, int64_t rows, int64_t cols);
+/* General NumPy broadcasting, up to MC_MAX_DIMS dims; strides in elements, 0 on a
+ * broadcast axis. */
+#define MC_MAX_DIMS 6
+int mc_binary_bcast(int op, const float* a, const float* b, float* out, int ndim,
+                    const int64_t* out_shape, const int64_t* a_strides, const int64_t* b_strides);
+int mc_fill(float* dst, float value, int64_t n);
+int mc_arange(float* dst, float start, float step, int64_t n);
+/* dtype casts; codes: 0 f32, 1 i32, 2 i64, 3 f64, 4 u8. */
+enum mc_dtype { MC_F32 = 0, MC_I32, MC_I64, MC_F64, MC_U8 };
+int mc_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n);
+
+/* Fused chain of elementwise VJPs -- the rewrite of the per-record loop of
+ * minpy/tape.py:223-234: out[i] = (acc ? acc[i] : 0) + g[i] * prod_k f_k(a_k, b_k, s_k).
+ * Each step multiplies the running gradient by one primitive's local derivative. */
+enum mc_vjp_op {
+  MC_VJP_MUL_A = 0,     /* g * a                    multiply, exp (a = ans)            */
+  MC_VJP_MUL_S,         /* g * s                    scalar multiply                    */
+  MC_VJP_NEG,           /* -g                       negative / subtract rhs            */
+  MC_VJP_DIV_A,         /* g / a                    divide lhs, log (a = x)            */
+  MC_VJP_DIV_S,         /* g / s                                                        */
+  MC_VJP_TANH_ANS,      /* g * (1 - a^2)            tanh (a = ans)                     */
+  MC_VJP_SQRT_ANS,      /* g * 0.5 / a              sqrt (a = ans)                     */
+  MC_VJP_SIN_X,         /* g * cos(a)                                                   */
+  MC_VJP_COS_X,         /* -g * sin(a)                                                  */
+  MC_VJP_ABS_X,         /* g * sign(a)                                                  */
+  MC_VJP_SIGMOID_ANS,   /* g * a * (1 - a)                                              */
+  MC_VJP_EQ_AB,         /* g * (a == b)             maximum / minimum / relu           */
+  MC_VJP_EQ_AS,         /* g * (a == s)                                                 */
+  MC_VJP_DIV_Y,         /* -g * a / (b * b)         divide rhs (a = x, b = y)          */
+  MC_VJP_S_DIV_Y,       /* -g * s / (a * a)         scalar / array rhs (a = y)         */
+  MC_VJP_POW_XS,        /* g * s * a^(s-1)          power, scalar exponent (a = x)     */
+  MC_VJP_POW_SY,        /* g * log(s) * a           power, scalar base (a = ans)       */
+  MC_VJP_POW_X,         /* g * b * a^(b-1)          power lhs (a = x, b = y)           */
+  MC_VJP_POW_Y,         /* g * log(a) * b           power rhs (a = x, b = ans)         */
+  MC_VJP_RECIP_ANS,     /* -g * a * a               1/x (a = ans)                      */
+  MC_VJP_GT0_A,         /* g * (a > 0)                                                  */
+  MC_VJP_COUNT
+};
+/* Operand addressing inside a step: how element i of the output maps to a / b. */
+enum mc_vjp_mode { MC_OPD_FULL = 0, MC_OPD_ROW = 1 /* a[i % inner] */, MC_OPD_COL = 2 /* a[i / inner] */,
+                   MC_OPD_ONE = 3 /* a[0] */ };
+typedef struct mc_vjp_step {
+  int32_t op;        /* mc_vjp_op */
+  int32_t a_mode;    /* mc_vjp_mode */
+  int32_t b_mode;
+  float scalar;
+  const float* a;
+  const float* b;
+  int64_t inner;     /* for ROW / COL modes */
+} mc_vjp_step;
+#define MC_VJP_MAX_STEPS 12
+/* g may be NULL (then g_scalar is the incoming gradient); g_mode addresses g like an operand. */
+int mc_vjp_chain(const float* g, int g_mode, int64_t g_inner, float g_scalar, const float* acc,
+                 const mc_vjp_step* steps, int nsteps, float* out, int64_t n);
+
+/* -------------------------------------------------------------- reductions --- */
+/* x viewed as (outer, red, inner); the middle axis is reduced: out is (outer, inner).
+ * np.sum/max/min with axis/keepdims: numpy_core.py:233-237, mxnet_core.py:120-122;
+ * `_unbroadcast` sums: numpy_core.py:119-146. */
+enum mc_reduce_op { MC_RED_SUM = 0, MC_RED_MAX, MC_RED_MIN, MC_RED_COUNT };
+int mc_reduce(int op, const float* x, float* out, int64_t outer, int64_t red, int64_t inner);
+/* np.argmax (first maximal index, int64, bit-exact): NumPy-only in the reference
+ * (docs/feature/op_stat.rst:113-119); used by nn/solver.py:231. */
+int mc_argmax(const float* x, int64_t* out_i64, int64_t outer, int64_t red, int64_t inner);
+/* out(outer, red, inner) = g(outer, inner) broadcast over red: VJP of sum
+ * (numpy_core.py:150-162 `_sum_grad`). scale multiplies. */
+int mc_bcast_mid(const float* g, float* out, float scale, int64_t outer, int64_t red, int64_t inner);
+/* VJP of max/min: out = g_b * (x == ans_b), ties all receive g
+ * (numpy_core.py:66-70 `_chooser_grad`; tests/unittest/test_autograd.py:107-130). */
+int mc_select_grad(const float* x, const float* ans, const float* g, float* out,
+                   int64_t outer, int64_t red, int64_t inner);
+
+/* ----------------------------------------------------- softmax / losses ------ */
+/* Row softmax: `_softmax_output` numpy_core.py:164-168 (4 NDArray ops in mxnet_core.py:85-90). */
+int mc_softmax_rows(const float* x, float* out, int64_t rows, int64_t cols);
+int mc_logsumexp_rows(const float* x, float* out, int64_t rows, int64_t cols);
+/* One-hot in place: `_onehot_encode` numpy_core.py:47-63 (out[i, idx[i]] = 1). */
+int mc_onehot(const int32_t* idx_i32, float* out, int64_t rows, int64_t cols);
+/* Fused softmax_loss of nn/layers.py:176-198: probs = softmax(x);
+ * loss[0] = -sum_i log(probs[i, y_i]) / rows (labels) or -sum(log(p) * onehot)/rows.
+ * Exactly one of labels_i32 / onehot is non-NULL. */
+int mc_softmax_ce_fwd(const float* x, const int32_t* labels_i32, const float* onehot,
+                      float* probs, float* loss, int64_t rows, int64_t cols);
+/* dx = (probs - y) / rows: `_softmax_output_grad` numpy_core.py:170-175 (ignores upstream g). */
+int mc_softmax_ce_bwd(const float* probs, const int32_t* labels_i32, const float* onehot,
+                      float* dx, int64_t rows, int64_t cols);
+
+/* ---------------------------------------------------------------- indexing --- */
+/* dst (dense, shape[]) = src[offset + sum_k idx_k * strides[k]]: basic slices, strided
+ * slices and axis permutations of `_minpy_getitem` / np.transpose
+ * (numpy_core.py:19-21; minpy/array.py:432-443). */
+int mc_strided_copy(const float* src, float* dst, int ndim, const int64_t* shape,
+                    const int64_t* src_strides, int64_t src_offset);
+/* dst[offset + sum idx*strides] += src (dense): VJP of a basic slice
+ * (`_minpy_getitem_grad`, numpy_core.py:24-28, np.add.at semantics). */
+int mc_strided_add(float* dst, const float* src, int ndim, const int64_t* shape,
+                   const int64_t* dst_strides, int64_t dst_offset);
+/* out[i] = x[i, idx[i]]  (probs[np.arange(N), y], nn/layers.py:478) and its scatter-add VJP. */
+int mc_pick_cols(const float* x, const int32_t* idx_i32, float* out, int64_t rows, int64_t cols);
+int mc_pick_cols_grad(const float* g, const int32_t* idx_i32, float* dx_zeroed, int64_t rows, int64_t cols);
+/* out[i, :] = x[idx[i], :] integer-array gather on axis 0, and np.add.at scatter VJP
+ * (duplicates accumulate). */
+int mc_take_rows(const float* x, const int32_t* idx_i32, float* out, int64_t nidx, int64_t row_elems);
+int mc_take_rows_grad(const float* g, const int32_t* idx_i32, float* dx_zeroed, int64_t nidx, int64_t row_elems);
+/* concatenation along the middle axis of (outer, na + nb, inner): np.append / concatenate
+ * (numpy_core.py:296-302). */
+int mc_concat_mid(const float* a, const float* b, float* out, int64_t outer, int64_t na, int64_t nb, int64_t inner);
+
+/* -------------------------------------------------------------------- GEMM --- */
+/* C(M,N) = op(A) . op(B) [+ bias(N,)] [relu] [+ C if accumulate]; row-major, leading
+ * dimensions in elements.  np.dot and its two VJPs: numpy_core.py:224-225,
+ * mxnet_core.py:112-114; bias/relu epilogue = nn/layers.py:27,41.
+ * precision: 0 = FP32 CUDA-core (exact-accumulate cross-check), 1 = TF32 tcgen05/TMEM
+ * fed by TMA (FP32 accumulate). Falls back from 1 to 0 only for shapes TMA cannot
+ * describe (row pitch not a multiple of 16 bytes). */
+enum mc_gemm_precision { MC_GEMM_FP32 = 0, MC_GEMM_TF32 = 1 };
+int mc_gemm(int trans_a, int trans_b, int64_t M, int64_t N, int64_t K,
+            const float* A, int64_t lda, const float* B, int64_t ldb,
+            float* C, int64_t ldc, const float* bias, int relu, int accumulate, int precision);
+/* Which path the last mc_gemm call on this thread took (0 fp32, 1 tf32 tcgen05). */
+int mc_gemm_last_path(int* path);
+
+/* ------------------------------------------------------------ nn.layers ------ */
+/* layers.batchnorm train mode, nn/layers.py:93-110: biased variance, returns updated
+ * running stats (momentum*r + (1-momentum)*stat). save_mean/save_invstd feed the VJP. */
+int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta,
+                           const float* running_mean, const float* running_var,
+                           float* out, float* new_running_mean, float* new_running_var,
+                           float* save_mean, float* save_invstd,
+                           int64_t N, int64_t D, float eps, float momentum);
+int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma,
+                           const float* save_mean, const float* save_invstd,
+                           float* dx, float* dgamma, float* dbeta, int64_t N, int64_t D);
+/* test mode, nn/layers.py:111-113. */
+int mc_batchnorm_test_fwd(const float* x, const float* gamma, const float* beta,
+                          const float* running_mean, const float* running_var,
+                          float* out, int64_t N, int64_t D, float eps);
+/* layers.dropout train mode, nn/layers.py:141-144: keep where u > p, NOT rescaled.
+ * The Philox stream is keyed by (seed, offset); the same pair regenerates the mask in bwd. */
+int mc_dropout(const float* x, float* out, int64_t n, float p, uint64_t seed, uint64_t offset);
+/* lstm_step of nn/layers.py:353-380 after the two GEMMs: a is (N, 4H) pre-activations. */
+int mc_lstm_cell_fwd(const float* a, const float* prev_c, float* next_h, float* next_c,
+                     float* gates /* (N,4H) saved i,f,o,g */, int64_t N, int64_t H);
+int mc_lstm_cell_bwd(const float* gates, const float* prev_c, const float* next_c,
+                     const float* dnext_h, const float* dnext_c /* may be NULL */,
+                     float* da /* (N,4H) */, float* dprev_c, int64_t N, int64_t H);
+
+/* --------------------------------------------------------------- nn.optim ---- */
+/* Update rules of nn/optim.py:33-141; outputs may alias inputs. */
+int mc_sgd(const float* w, const float* dw, float* w_out, float lr, int64_t n);
+int mc_sgd_momentum(const float* w, const float* dw, const float* v, float* w_out, float* v_out,
+                    float lr, float momentum, int64_t n);
+int mc_rmsprop(const float* w, const float* dw, const float* cache, float* w_out, float* cache_out,
+               float lr, float decay, float eps, int64_t n);
+int mc_adam(const float* w, const float* dw, const float* m, const float* v,
+            float* w_out, float* m_out, float* v_out,
+            float lr, float beta1, float beta2, float eps, int64_t t, int64_t n);
+
+/* -------------------------------------------------------------------- RNG ---- */
+/* Philox4x32-10 counter RNG: replaces numpy.random.rand/randn (array_variants/numpy/random.py)
+ * and mx.random.uniform/normal (array_variants/mxnet/random.py:11-16). */
+int mc_rand_uniform(float* out, int64_t n, uint64_t seed, uint64_t offset);
+int mc_rand_normal(float* out, int64_t n, uint64_t seed, uint64_t offset);
+
+/* ---------------------------------------------------- convolution / pooling -- */
+/* NCHW cross-correlation, the MXNet `Convolution` / `Pooling(max)` / `Activation(relu)`
+ * symbols reached through core.Function (minpy/core.py:148-190; examples/nn/cnn.py:32-40). */
+int mc_conv2d_fwd(const float* x, const float* w, const float* bias, float* y,
+                  int64_t N, int64_t C, int64_t H, int64_t W, int64_t F, int64_t KH, int64_t KW,
+                  int64_t stride, int64_t pad, int relu, int precision);
+int mc_conv2d_dgrad(const float* dy, const float* w, float* dx,
+                    int64_t N, int64_t C, int64_t H, int64_t W, int64_t F, int64_t KH, int64_t KW,
+                    int64_t stride, int64_t pad, int precision);
+int mc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* dbias,
+                    int64_t N, int64_t C, int64_t H, int64_t W, int64_t F, int64_t KH, int64_t KW,
+                    int64_t stride, int64_t pad, int precision);
+int mc_maxpool2d_fwd(const float* x, float* y, int32_t* argmax_i32, int64_t NC, int64_t H, int64_t W,
+                     int64_t KH, int64_t KW, int64_t stride);
+int mc_maxpool2d_bwd(const float* dy, const int32_t* argmax_i32, float* dx_zeroed, int64_t NC,
+                     int64_t H, int64_t W, int64_t OH, int64_t OW);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* MINPY_CUDA_H_ */

@@ -1,0 +1,112 @@
+// Shared helpers for libminpy_cuda.so (sm_100a).  Internal -- the public surface is
+// include/minpy_cuda.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/minpy_cuda.h"
+
+namespace mc {
+
+// ---- per-thread error string + library-wide stream / counters (runtime.cu) ----------
+void set_error(const char* fmt, ...);
+cudaStream_t stream();
+int sm_count();
+void count_launch(int n = 1);
+
+#define MC_CHECK(expr)                                                              \
+  do {                                                                              \
+    cudaError_t _e = (expr);                                                        \
+    if (_e != cudaSuccess) {                                                        \
+      mc::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return 1;                                                                     \
+    }                                                                               \
+  } while (0)
+
+#define MC_REQUIRE(cond, msg)                                                       \
+  do {                                                                              \
+    if (!(cond)) {                                                                  \
+      mc::set_error("%s: requirement failed: %s", __func__, msg);                   \
+      return 2;                                                                     \
+    }                                                                               \
+  } while (0)
+
+// After a kernel launch: catch launch-configuration errors, count the launch.
+#define MC_LAUNCHED()                                                               \
+  do {                                                                              \
+    cudaError_t _e = cudaGetLastError();                                            \
+    if (_e != cudaSuccess) {                                                        \
+      mc::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return 1;                                                                     \
+    }                                                                               \
+    mc::count_launch();                                                             \
+  } while (0)
+
+// Grid sizing for bandwidth-bound grid-stride kernels: enough CTAs to fill every SM
+// `waves` times over, never more than the work needs.
+inline int grid_for(int64_t work_items, int per_block, int ctas_per_sm = 8) {
+  int64_t need = (work_items + per_block - 1) / per_block;
+  int64_t cap = (int64_t)sm_count() * ctas_per_sm;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---- device helpers ------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// NaN-propagating max/min (NumPy's np.max / np.maximum propagate NaN; fmaxf does not).
+__device__ __forceinline__ float nanmax(float a, float b) {
+  return (a != a) ? a : ((b != b) ? b : fmaxf(a, b));
+}
+__device__ __forceinline__ float nanmin(float a, float b) {
+  return (a != a) ? a : ((b != b) ? b : fminf(a, b));
+}
+
+// Block-wide reduction through shared memory; `Op` is a functor with ::identity() and
+// operator()(a,b).  Result valid in every thread.  Requires blockDim.x % 32 == 0, <= 1024.
+template <class Op>
+__device__ __forceinline__ float block_reduce(float v, Op op, float* smem32) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = op(v, __shfl_xor_sync(0xffffffffu, v, o));
+  if (lane == 0) smem32[warp] = v;
+  __syncthreads();
+  const int nwarps = (blockDim.x + 31) >> 5;
+  float r = (lane < nwarps) ? smem32[lane] : Op::identity();
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) r = op(r, __shfl_xor_sync(0xffffffffu, r, o));
+  __syncthreads();
+  return r;
+}
+
+struct SumOp {
+  __device__ static float identity() { return 0.f; }
+  __device__ float operator()(float a, float b) const { return a + b; }
+};
+struct MaxOp {
+  __device__ static float identity() { return -INFINITY; }
+  __device__ float operator()(float a, float b) const { return nanmax(a, b); }
+};
+struct MinOp {
+  __device__ static float identity() { return INFINITY; }
+  __device__ float operator()(float a, float b) const { return nanmin(a, b); }
+};
+
+}  // namespace mc

@@ -1,0 +1,559 @@
+// Dense contractions: np.dot and its two VJPs (numpy_core.py:224-225).
+//
+// Two paths behind one entry point (mc_gemm):
+//   * TF32 tensor-core path (sm_100a): tcgen05.mma kind::tf32 issued by one thread,
+//     operands staged in shared memory by TMA (SWIZZLE_128B), FP32 accumulator in TMEM,
+//     read back with tcgen05.ld for a fused bias / relu / accumulate epilogue.  The FP32
+//     operands are consumed in place -- no conversion pass over HBM.  All four
+//     transpose combinations are expressed through the UMMA "major" bits and the TMA
+//     box shape (K-major vs MN-major operand tiles), never through a transposed copy.
+//     Skinny problems are split along K across CTAs (workspace + deterministic reduce)
+//     so that every SM streams operand bytes: these GEMMs sit below the B200 ridge
+//      and are bound by how many SMs pull from HBM/L2.
+//   * FP32 CUDA-core path: exact FP32 FMA accumulation; serves shapes TMA cannot
+//     describe (row pitch not a multiple of 16 B, e.g. the 10-class output layer) and is
+//     the FP32-accumulate cross-check the parity tests compare the TF32 path with.
+#include <cuda.h>
+#include "common.cuh"
+
+namespace mc {
+
+// =====================================================================================
+//                                FP32 CUDA-core GEMM
+// =====================================================================================
+constexpr int SG_BM = 64, SG_BN = 64, SG_BK = 16, SG_THREADS = 256;
+
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(SG_THREADS) sgemm_kernel(int M, int N, int K, const float* __restrict__ A, int64_t lda,
+                                                           const float* __restrict__ B, int64_t ldb,
+                                                           float* __restrict__ C, int64_t ldc,
+                                                           const float* __restrict__ bias, int relu, int accumulate,
+                                                           int k_per_split, float* __restrict__ ws) {
+  __shared__ float As[SG_BK][SG_BM + 4];
+  __shared__ float Bs[SG_BK][SG_BN + 4];
+  const int t = threadIdx.x;
+  const int tx = t & 15, ty = t >> 4;
+  const int m0 = blockIdx.y * SG_BM, n0 = blockIdx.x * SG_BN;
+  const int kbeg = blockIdx.z * k_per_split;
+  const int kend = min(K, kbeg + k_per_split);
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = kbeg; k0 < kend; k0 += SG_BK) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int m, k;
+      if (TA) { m = t & 63; k = (t >> 6) + 4 * j; }
+      else { k = t & 15; m = (t >> 4) + 16 * j; }
+      const int gm = m0 + m, gk = k0 + k;
+      float v = 0.f;
+      if (gm < M && gk < kend) v = TA ? A[(int64_t)gk * lda + gm] : A[(int64_t)gm * lda + gk];
+      As[k][m] = v;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int n, k;
+      if (TB) { k = t & 15; n = (t >> 4) + 16 * j; }
+      else { n = t & 63; k = (t >> 6) + 4 * j; }
+      const int gn = n0 + n, gk = k0 + k;
+      float v = 0.f;
+      if (gn < N && gk < kend) v = TB ? B[(int64_t)gn * ldb + gk] : B[(int64_t)gk * ldb + gn];
+      Bs[k][n] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < SG_BK; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gm = m0 + ty * 4 + i;
+    if (gm >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int gn = n0 + tx * 4 + j;
+      if (gn >= N) continue;
+      float v = acc[i][j];
+      if (ws) {
+        ws[((int64_t)blockIdx.z * M + gm) * N + gn] = v;
+      } else {
+        if (bias) v += bias[gn];
+        if (accumulate) v += C[(int64_t)gm * ldc + gn];
+        if (relu) v = (v != v) ? v : fmaxf(v, 0.f);
+        C[(int64_t)gm * ldc + gn] = v;
+      }
+    }
+  }
+}
+
+// Deterministic split-K combine with the fused epilogue.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ ws, int splits, int64_t M, int64_t N,
+                                                            float* __restrict__ C, int64_t ldc,
+                                                            const float* __restrict__ bias, int relu, int accumulate) {
+  const int64_t total = M * N;
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  if ((N & 3) == 0 && (ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(C) & 15u) == 0)) {
+    const int64_t total4 = total >> 2;
+    for (int64_t i4 = (int64_t)blockIdx.x * 256 + threadIdx.x; i4 < total4; i4 += stride) {
+      const int64_t i = i4 << 2;
+      float4 s = *reinterpret_cast<const float4*>(ws + i);
+      for (int z = 1; z < splits; ++z) {
+        const float4 p = *reinterpret_cast<const float4*>(ws + (int64_t)z * total + i);
+        s.x += p.x; s.y += p.y; s.z += p.z; s.w += p.w;
+      }
+      const int64_t m = i / N, n = i % N;
+      if (bias) { s.x += bias[n]; s.y += bias[n + 1]; s.z += bias[n + 2]; s.w += bias[n + 3]; }
+      float4* dst = reinterpret_cast<float4*>(C + m * ldc + n);
+      if (accumulate) { const float4 c = *dst; s.x += c.x; s.y += c.y; s.z += c.z; s.w += c.w; }
+      if (relu) {
+        s.x = (s.x != s.x) ? s.x : fmaxf(s.x, 0.f); s.y = (s.y != s.y) ? s.y : fmaxf(s.y, 0.f);
+        s.z = (s.z != s.z) ? s.z : fmaxf(s.z, 0.f); s.w = (s.w != s.w) ? s.w : fmaxf(s.w, 0.f);
+      }
+      *dst = s;
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += stride) {
+      float s = ws[i];
+      for (int z = 1; z < splits; ++z) s += ws[(int64_t)z * total + i];
+      const int64_t m = i / N, n = i % N;
+      if (bias) s += bias[n];
+      if (accumulate) s += C[m * ldc + n];
+      if (relu) s = (s != s) ? s : fmaxf(s, 0.f);
+      C[m * ldc + n] = s;
+    }
+  }
+}
+
+// =====================================================================================
+//                         TF32 tcgen05 / TMEM / TMA GEMM (sm_100a)
+// =====================================================================================
+namespace tc {
+
+constexpr int BM = 128;         // UMMA M (cta_group::1): accumulator row i <-> TMEM lane i
+constexpr int BK = 32;          // fp32 per stage along K = 128 B = one SWIZZLE_128B row
+constexpr int UMMA_K = 8;       // kind::tf32: 32 B of K per instruction
+constexpr int THREADS = 128;    // warp 0: TMA producer, warp 1: MMA issuer; all 4: epilogue
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Bounded wait: a pipeline bug must surface as a trap (reported by the next CUDA call),
+// never as a hung GPU.  ~2 s at 2 GHz is far beyond any legitimate wait in these kernels.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  const long long t0 = clock64();
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (!done && clock64() - t0 > 4000000000LL) __trap();
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
+                                            int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// 64-bit shared-memory matrix descriptor (cute/arch/mma_sm100_desc.hpp SmemDescriptor):
+// [0,14) addr>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout=2 (SWIZZLE_128B)
+// `layout`: 2 = SWIZZLE_128B (16 B atoms; K-major tiles), 1 = SWIZZLE_128B_BASE32B (32 B atoms) --
+// the only layout tcgen05 accepts for MN-major 32-bit (tf32) operands.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+  return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46) | ((uint64_t)layout << 61);
+}
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct GemmParams {
+  float* C;
+  int64_t ldc;
+  const float* bias;
+  float* ws;           // split-K workspace [splits][M][N] or nullptr
+  int M, N, K;
+  int relu, accumulate;
+  int a_mn, b_mn;      // operand tile is MN-major (1) or K-major (0)
+  int kb_per_split;    // k-blocks (of BK) per grid.z slice
+};
+
+// Stage layout (each operand tile is a stack of SWIZZLE_128B atoms: 8 rows x 128 B):
+//   K-major  tile (R rows of MN, BK of K): R rows x 128 B; 8-row groups 1024 B apart (SBO).
+//            MMA k (K = 8k..8k+7) starts 32k bytes into the swizzled row.
+//   MN-major tile: R/32 blocks of [BK k-rows x 128 B] (4096 B each, LBO), written by TMA with
+//            SWIZZLE_128B_ATOM_32B (pattern repeats every 4 k-rows = 512 B, SBO); one MMA
+//            (K = 8) covers two such groups: start + 1024k.
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                               const __grid_constant__ CUtensorMap tmB,
+                                                               const GemmParams p) {
+  constexpr uint32_t A_BYTES = BM * BK * 4;
+  constexpr uint32_t B_BYTES = BN * BK * 4;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;  // full[STAGES], empty[STAGES], tmem_full
+  const uint32_t tmem_slot = bar_base + (2 * STAGES + 1) * 8;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int num_kb_total = (p.K + BK - 1) / BK;
+  const int kb_begin = blockIdx.z * p.kb_per_split;
+  const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
+  const int num_kb = kb_end - kb_begin;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)BN)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------ TMA producer ------------------------------------
+    for (int i = 0; i < num_kb; ++i) {
+      const int s = i % STAGES;
+      const uint32_t ph = (i / STAGES) & 1;
+      mbar_wait(empty_bar(s), ph ^ 1u);
+      mbar_expect_tx(full_bar(s), STAGE_BYTES);
+      const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
+      const int k0 = (kb_begin + i) * BK;
+      if (!p.a_mn) {
+        tma_load_2d(sa, &tmA, full_bar(s), k0, m0);
+      } else {
+#pragma unroll
+        for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, full_bar(s), m0 + 32 * j, k0);
+      }
+      if (!p.b_mn) {
+        tma_load_2d(sb, &tmB, full_bar(s), k0, n0);
+      } else {
+#pragma unroll
+        for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, full_bar(s), n0 + 32 * j, k0);
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ------------------------------ MMA issuer --------------------------------------
+    // Instruction descriptor (cute UMMA::InstrDescriptor): c_format F32 (1<<4), a/b TF32
+    // (2<<7, 2<<10), a_major bit 15, b_major bit 16, N>>3 at [17,23), M>>4 at [24,29).
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
+                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    for (int i = 0; i < num_kb; ++i) {
+      const int s = i % STAGES;
+      const uint32_t ph = (i / STAGES) & 1;
+      mbar_wait(full_bar(s), ph);
+      tcgen05_fence_after();
+      const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
+#pragma unroll
+      for (int k = 0; k < BK / UMMA_K; ++k) {
+        const uint64_t adesc = p.a_mn ? make_desc(sa + k * 1024, 4096, 512, 1) : make_desc(sa + k * 32, 16, 1024, 2);
+        const uint64_t bdesc = p.b_mn ? make_desc(sb + k * 1024, 4096, 512, 1) : make_desc(sb + k * 32, 16, 1024, 2);
+        umma_tf32(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+      }
+      umma_commit(empty_bar(s));  // frees the smem stage once these MMAs have read it
+    }
+    umma_commit(tmem_full_bar);   // accumulator complete
+  }
+  __syncwarp();
+
+  // ---------------------------------- epilogue ----------------------------------------
+  mbar_wait(tmem_full_bar, 0);
+  tcgen05_fence_after();
+  __syncwarp();
+  const int row = m0 + warp * 32 + lane;
+  const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += 32) {
+    float v[32];
+    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+    if (row < p.M && num_kb > 0) {
+      const int col0 = n0 + c0;
+      if (p.ws) {
+        float* dst = p.ws + ((int64_t)blockIdx.z * p.M + row) * p.N + col0;
+        if ((p.N & 3) == 0 && col0 + 32 <= p.N) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (col0 + j < p.N) dst[j] = v[j];
+        }
+      } else {
+        float* dst = p.C + (int64_t)row * p.ldc + col0;
+        if (vec_ok && col0 + 32 <= p.N) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            if (p.bias) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+              o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+            }
+            if (p.accumulate) {
+              const float4 c = *reinterpret_cast<const float4*>(dst + j);
+              o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
+            }
+            if (p.relu) {
+              o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
+              o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
+            }
+            *reinterpret_cast<float4*>(dst + j) = o;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            if (col0 + j < p.N) {
+              float o = v[j];
+              if (p.bias) o += __ldg(p.bias + col0 + j);
+              if (p.accumulate) o += dst[j];
+              if (p.relu) o = (o != o) ? o : fmaxf(o, 0.f);
+              dst[j] = o;
+            }
+          }
+        }
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
+  }
+}
+
+// ------------------------------- host side --------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+static int load_encode() {
+  if (g_encode) return 0;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+    set_error("cuTensorMapEncodeTiled unavailable (%s)", cudaGetErrorString(e));
+    return 1;
+  }
+  g_encode = (EncodeTiledFn)fn;
+  return 0;
+}
+
+// 2-D fp32 matrix, `inner` contiguous elements per row, `outer` rows of pitch ld elements.
+int make_tmap_2d(CUtensorMap* map, const float* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner,
+                 int box_outer, bool mn_major) {
+  if (load_encode()) return 1;
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (inner=%lld outer=%lld ld=%lld box=%dx%d)", (int)r,
+              (long long)inner, (long long)outer, (long long)ld, box_inner, box_outer);
+    return 1;
+  }
+  return 0;
+}
+
+template <int BN, int STAGES>
+static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits) {
+  constexpr size_t SMEM = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) + (2 * STAGES + 1) * 8 + 16 + 1024;
+  static bool configured = false;
+  if (!configured) {
+    MC_CHECK(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    configured = true;
+  }
+  dim3 grid((unsigned)((p.N + BN - 1) / BN), (unsigned)((p.M + BM - 1) / BM), (unsigned)splits);
+  gemm_tf32_kernel<BN, STAGES><<<grid, THREADS, SMEM, stream()>>>(tmA, tmB, p);
+  MC_LAUNCHED();
+  return 0;
+}
+
+}  // namespace tc
+
+static thread_local int g_last_path = -1;
+
+static int gemm_fp32(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
+                     int64_t ldb, float* C, int64_t ldc, const float* bias, int relu, int accumulate) {
+  const int64_t tiles = ((M + SG_BM - 1) / SG_BM) * ((N + SG_BN - 1) / SG_BN);
+  int splits = 1;
+  if (tiles < sm_count() && K >= 512) {
+    splits = (int)((2 * sm_count()) / tiles);
+    const int maxs = (int)(K / 128);
+    if (splits > maxs) splits = maxs;
+    if (splits > 64) splits = 64;
+    if (splits < 1) splits = 1;
+  }
+  int k_per = (int)((K + splits - 1) / splits);
+  k_per = (k_per + SG_BK - 1) / SG_BK * SG_BK;
+  splits = (int)((K + k_per - 1) / k_per);
+  float* ws = nullptr;
+  if (splits > 1) MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * splits * M * N, stream()));
+  dim3 grid((unsigned)((N + SG_BN - 1) / SG_BN), (unsigned)((M + SG_BM - 1) / SG_BM), (unsigned)splits);
+#define SG_LAUNCH(TA, TB)                                                                                          \
+  sgemm_kernel<TA, TB><<<grid, SG_THREADS, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu, \
+                                                          accumulate, k_per, ws)
+  if (ta && tb) SG_LAUNCH(true, true);
+  else if (ta) SG_LAUNCH(true, false);
+  else if (tb) SG_LAUNCH(false, true);
+  else SG_LAUNCH(false, false);
+#undef SG_LAUNCH
+  MC_LAUNCHED();
+  if (splits > 1) {
+    splitk_reduce_kernel<<<grid_for(M * N / 4 + 1, 256), 256, 0, stream()>>>(ws, splits, M, N, C, ldc, bias, relu, accumulate);
+    MC_LAUNCHED();
+    MC_CHECK(cudaFreeAsync(ws, stream()));
+  }
+  return 0;
+}
+
+static bool tma_ok(const float* p, int64_t ld) { return aligned16(p) && (ld % 4 == 0); }
+
+static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
+                     int64_t ldb, float* C, int64_t ldc, const float* bias, int relu, int accumulate) {
+  using namespace tc;
+  const int BN = (N > 64) ? 128 : 64;
+  CUtensorMap tmA, tmB;
+  // A operand: op(A) is (M, K).  Stored (M,K) row-major -> K-major tile {BK x BM};
+  // stored (K,M) (trans_a) -> MN-major: boxes of {32 (M) x BK (K)}.
+  if (!ta) { if (make_tmap_2d(&tmA, A, K, M, lda, BK, BM, false)) return 1; }
+  else     { if (make_tmap_2d(&tmA, A, M, K, lda, 32, BK, true)) return 1; }
+  // B operand: op(B) is (K, N).  Stored (K,N) row-major -> MN-major; stored (N,K) (trans_b) -> K-major.
+  if (!tb) { if (make_tmap_2d(&tmB, B, N, K, ldb, 32, BK, true)) return 1; }
+  else     { if (make_tmap_2d(&tmB, B, K, N, ldb, BK, BN, false)) return 1; }
+
+  const int64_t tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int num_kb = (int)((K + BK - 1) / BK);
+  int splits = 1;
+  if (tiles < sm_count() && num_kb >= 16) {
+    splits = (int)(sm_count() / tiles);
+    const int maxs = num_kb / 8;  // at least 8 k-blocks (K = 256) per slice
+    if (splits > maxs) splits = maxs;
+    if (splits < 1) splits = 1;
+  }
+  int kb_per = (num_kb + splits - 1) / splits;
+  splits = (num_kb + kb_per - 1) / kb_per;
+
+  GemmParams p;
+  p.C = C; p.ldc = ldc; p.bias = bias; p.ws = nullptr;
+  p.M = (int)M; p.N = (int)N; p.K = (int)K;
+  p.relu = relu; p.accumulate = accumulate;
+  p.a_mn = ta ? 1 : 0;
+  p.b_mn = tb ? 0 : 1;
+  p.kb_per_split = kb_per;
+  if (splits > 1) MC_CHECK(cudaMallocAsync((void**)&p.ws, sizeof(float) * splits * M * N, stream()));
+  int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
+  if (rc == 0 && splits > 1) {
+    splitk_reduce_kernel<<<grid_for(M * N / 4 + 1, 256), 256, 0, stream()>>>(p.ws, splits, M, N, C, ldc, bias, relu, accumulate);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("splitk reduce launch failed: %s", cudaGetErrorString(e)); rc = 1; }
+    else count_launch();
+  }
+  if (p.ws) MC_CHECK(cudaFreeAsync(p.ws, stream()));
+  return rc;
+}
+
+}  // namespace mc
+
+using namespace mc;
+
+extern "C" {
+
+int mc_gemm(int trans_a, int trans_b, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
+            int64_t ldb, float* C, int64_t ldc, const float* bias, int relu, int accumulate, int precision) {
+  MC_REQUIRE(M >= 0 && N >= 0 && K >= 0, "negative extent");
+  MC_REQUIRE(M < 2147483647LL && N < 2147483647LL && K < 2147483647LL, "extent exceeds int32");
+  if (M == 0 || N == 0) return 0;
+  if (K == 0) {
+    // empty contraction: C = bias (+C), NumPy gives zeros
+    if (!accumulate) {
+      for (int64_t m = 0; m < M; ++m) if (mc_fill(C + m * ldc, 0.f, N)) return 1;
+    }
+    if (bias) return mc_binary_vec(MC_ADD, C, bias, 0, 0, C, M, N);
+    return 0;
+  }
+  const bool tma = tma_ok(A, lda) && tma_ok(B, ldb) && (M >= 32 || N >= 32);
+  if (precision == MC_GEMM_TF32 && tma) {
+    g_last_path = 1;
+    return gemm_tf32(trans_a, trans_b, M, N, K, A, lda, B, ldb, C, ldc, bias, relu, accumulate);
+  }
+  g_last_path = 0;
+  return gemm_fp32(trans_a, trans_b, M, N, K, A, lda, B, ldb, C, ldc, bias, relu, accumulate);
+}
+
+int mc_gemm_last_path(int* path) {
+  *path = g_last_path;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,515 @@
+// Fused nn.layers / nn.optim kernels and the Philox RNG.
+//
+// Everything here is HBM-bound.  BatchNorm (nn/layers.py:93-110: 22 primitive dispatches
+// forward, 23 VJP records backward in the reference) becomes two kernels per direction:
+// a column "partial statistics" pass and a normalise / input-gradient pass that both
+// use the same (128 columns x row-chunk) tiling, float4 loads along the contiguous
+// feature axis, and a deterministic workspace combine instead of atomics.
+#include "common.cuh"
+
+namespace mc {
+
+constexpr int L_THREADS = 256;
+
+// ===================================== Philox4x32-10 ==================================
+struct Philox {
+  uint32_t k0, k1;
+  __device__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
+  __device__ __forceinline__ uint4 operator()(uint64_t ctr) const {
+    uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32), c2 = 0x243F6A88u, c3 = 0x85A308D3u;
+    uint32_t a = k0, b = k1;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+      const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+      const uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
+      c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+      a += 0x9E3779B9u; b += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+  }
+};
+__device__ __forceinline__ float u01(uint32_t r) { return (float)(r >> 8) * (1.0f / 16777216.0f); }  // [0,1)
+
+__global__ void __launch_bounds__(L_THREADS) rand_uniform_kernel(float* __restrict__ out, int64_t n, uint64_t seed,
+                                                                 uint64_t offset) {
+  const Philox rng(seed);
+  const int64_t n4 = (n + 3) >> 2;
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t i4 = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i4 < n4; i4 += stride) {
+    const uint4 r = rng(offset + (uint64_t)i4);
+    const float v[4] = {u01(r.x), u01(r.y), u01(r.z), u01(r.w)};
+    const int64_t i = i4 << 2;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) if (i + k < n) out[i + k] = v[k];
+  }
+}
+
+__global__ void __launch_bounds__(L_THREADS) rand_normal_kernel(float* __restrict__ out, int64_t n, uint64_t seed,
+                                                                uint64_t offset) {
+  const Philox rng(seed);
+  const int64_t n4 = (n + 3) >> 2;
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t i4 = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i4 < n4; i4 += stride) {
+    const uint4 r = rng(offset + (uint64_t)i4);
+    // Box-Muller on (0,1] x [0,1)
+    const float u1 = 1.0f - u01(r.x), u2 = u01(r.y), u3 = 1.0f - u01(r.z), u4 = u01(r.w);
+    const float ra = sqrtf(-2.0f * logf(u1)), rb = sqrtf(-2.0f * logf(u3));
+    float s1, c1, s2, c2;
+    sincospif(2.0f * u2, &s1, &c1);
+    sincospif(2.0f * u4, &s2, &c2);
+    const float v[4] = {ra * c1, ra * s1, rb * c2, rb * s2};
+    const int64_t i = i4 << 2;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) if (i + k < n) out[i + k] = v[k];
+  }
+}
+
+// out = x * (u > p); the (seed, offset) pair regenerates the identical mask for the VJP.
+__global__ void __launch_bounds__(L_THREADS) dropout_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n,
+                                                            float p, uint64_t seed, uint64_t offset, int vec_ok) {
+  const Philox rng(seed);
+  const int64_t n4 = (n + 3) >> 2;
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t i4 = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i4 < n4; i4 += stride) {
+    const uint4 r = rng(offset + (uint64_t)i4);
+    const int64_t i = i4 << 2;
+    if (vec_ok && i + 3 < n) {
+      float4 v = *reinterpret_cast<const float4*>(x + i);
+      v.x = (u01(r.x) > p) ? v.x : 0.f;
+      v.y = (u01(r.y) > p) ? v.y : 0.f;
+      v.z = (u01(r.z) > p) ? v.z : 0.f;
+      v.w = (u01(r.w) > p) ? v.w : 0.f;
+      *reinterpret_cast<float4*>(out + i) = v;
+    } else {
+      const float u[4] = {u01(r.x), u01(r.y), u01(r.z), u01(r.w)};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) if (i + k < n) out[i + k] = (u[k] > p) ? x[i + k] : 0.f;
+    }
+  }
+}
+
+// ===================================== BatchNorm ======================================
+// Tile: 32 threads x VEC columns wide, 8 row lanes; grid = (col_tiles, row_chunks).
+// Partial layout: part[(chunk * 2 + which) * D + col].
+template <int VEC>
+struct ColVec {
+  float v[VEC];
+};
+template <int VEC>
+__device__ __forceinline__ ColVec<VEC> ld_cols(const float* __restrict__ p) {
+  ColVec<VEC> r;
+  if (VEC == 4) {
+    const float4 t = *reinterpret_cast<const float4*>(p);
+    r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) r.v[k] = p[k];
+  }
+  return r;
+}
+template <int VEC>
+__device__ __forceinline__ void st_cols(float* __restrict__ p, const ColVec<VEC>& r) {
+  if (VEC == 4) *reinterpret_cast<float4*>(p) = make_float4(r.v[0], r.v[1], r.v[2], r.v[3]);
+  else {
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) p[k] = r.v[k];
+  }
+}
+
+// BWD == false: s1 = sum(x - x[0,:]), s2 = sum((x - x[0,:])^2)   (shifted sums: no cancellation blow-up)
+// BWD == true : s1 = sum(dy),         s2 = sum(dy * xhat)
+template <int VEC, bool BWD>
+__global__ void __launch_bounds__(L_THREADS) bn_partial_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                               const float* __restrict__ mean,
+                                                               const float* __restrict__ invstd, float* __restrict__ part,
+                                                               int64_t N, int64_t D, int64_t rows_per_chunk) {
+  __shared__ float sm1[8][32 * VEC + 1];
+  __shared__ float sm2[8][32 * VEC + 1];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * VEC;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
+  const int64_t r1 = min(N, r0 + rows_per_chunk);
+  float a1[VEC], a2[VEC];
+#pragma unroll
+  for (int k = 0; k < VEC; ++k) a1[k] = a2[k] = 0.f;
+  if (col < D) {
+    ColVec<VEC> c0, c1;
+    if (BWD) { c0 = ld_cols<VEC>(mean + col); c1 = ld_cols<VEC>(invstd + col); }
+    else { c0 = ld_cols<VEC>(x + col); }
+    for (int64_t r = r0 + ty; r < r1; r += 8) {
+      const ColVec<VEC> xv = ld_cols<VEC>(x + r * D + col);
+      if (BWD) {
+        const ColVec<VEC> gv = ld_cols<VEC>(dy + r * D + col);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) { a1[k] += gv.v[k]; a2[k] += gv.v[k] * ((xv.v[k] - c0.v[k]) * c1.v[k]); }
+      } else {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) { const float d = xv.v[k] - c0.v[k]; a1[k] += d; a2[k] += d * d; }
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < VEC; ++k) { sm1[ty][tx * VEC + k] = a1[k]; sm2[ty][tx * VEC + k] = a2[k]; }
+  __syncthreads();
+  if (ty == 0 && col < D) {
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s1 += sm1[j][tx * VEC + k]; s2 += sm2[j][tx * VEC + k]; }
+      part[((int64_t)blockIdx.y * 2 + 0) * D + col + k] = s1;
+      part[((int64_t)blockIdx.y * 2 + 1) * D + col + k] = s2;
+    }
+  }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(L_THREADS) bn_fwd_apply_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                                 const float* __restrict__ beta,
+                                                                 const float* __restrict__ rmean,
+                                                                 const float* __restrict__ rvar, const float* __restrict__ part,
+                                                                 int chunks, float* __restrict__ out,
+                                                                 float* __restrict__ new_rmean, float* __restrict__ new_rvar,
+                                                                 float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                                                                 int64_t N, int64_t D, int64_t rows_per_chunk, float eps,
+                                                                 float momentum) {
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * VEC;
+  if (col >= D) return;
+  float mean[VEC], inv[VEC], sc[VEC], sh[VEC];
+  const ColVec<VEC> x0 = ld_cols<VEC>(x + col);
+  const ColVec<VEC> g = ld_cols<VEC>(gamma + col), b = ld_cols<VEC>(beta + col);
+#pragma unroll
+  for (int k = 0; k < VEC; ++k) {
+    float s1 = 0.f, s2 = 0.f;
+    for (int c = 0; c < chunks; ++c) {
+      s1 += part[((int64_t)c * 2 + 0) * D + col + k];
+      s2 += part[((int64_t)c * 2 + 1) * D + col + k];
+    }
+    const float dm = s1 / (float)N;                 // mean - x0
+    float var = s2 / (float)N - dm * dm;            // biased variance (layers.py:103)
+    var = fmaxf(var, 0.f);
+    mean[k] = x0.v[k] + dm;
+    inv[k] = 1.0f / sqrtf(var + eps);
+    sc[k] = g.v[k] * inv[k];
+    sh[k] = b.v[k] - mean[k] * sc[k];
+    if (blockIdx.y == 0 && ty == 0) {
+      save_mean[col + k] = mean[k];
+      save_invstd[col + k] = inv[k];
+      new_rmean[col + k] = momentum * rmean[col + k] + (1.0f - momentum) * mean[k];
+      new_rvar[col + k] = momentum * rvar[col + k] + (1.0f - momentum) * var;
+    }
+  }
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
+  const int64_t r1 = min(N, r0 + rows_per_chunk);
+  for (int64_t r = r0 + ty; r < r1; r += 8) {
+    ColVec<VEC> xv = ld_cols<VEC>(x + r * D + col);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) xv.v[k] = fmaf(xv.v[k], sc[k], sh[k]);
+    st_cols<VEC>(out + r * D + col, xv);
+  }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(L_THREADS) bn_bwd_apply_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                                 const float* __restrict__ gamma,
+                                                                 const float* __restrict__ mean,
+                                                                 const float* __restrict__ invstd,
+                                                                 const float* __restrict__ part, int chunks,
+                                                                 float* __restrict__ dx, float* __restrict__ dgamma,
+                                                                 float* __restrict__ dbeta, int64_t N, int64_t D,
+                                                                 int64_t rows_per_chunk) {
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * VEC;
+  if (col >= D) return;
+  const ColVec<VEC> g = ld_cols<VEC>(gamma + col), mu = ld_cols<VEC>(mean + col), iv = ld_cols<VEC>(invstd + col);
+  float k1[VEC], k2[VEC], k3[VEC];  // dx = k1 * (dy - k2 - xhat * k3)
+#pragma unroll
+  for (int k = 0; k < VEC; ++k) {
+    float s1 = 0.f, s2 = 0.f;
+    for (int c = 0; c < chunks; ++c) {
+      s1 += part[((int64_t)c * 2 + 0) * D + col + k];
+      s2 += part[((int64_t)c * 2 + 1) * D + col + k];
+    }
+    if (blockIdx.y == 0 && ty == 0) { dbeta[col + k] = s1; dgamma[col + k] = s2; }
+    k1[k] = g.v[k] * iv.v[k];
+    k2[k] = s1 / (float)N;
+    k3[k] = s2 / (float)N;
+  }
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
+  const int64_t r1 = min(N, r0 + rows_per_chunk);
+  for (int64_t r = r0 + ty; r < r1; r += 8) {
+    const ColVec<VEC> xv = ld_cols<VEC>(x + r * D + col);
+    ColVec<VEC> gv = ld_cols<VEC>(dy + r * D + col);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      const float xhat = (xv.v[k] - mu.v[k]) * iv.v[k];
+      gv.v[k] = k1[k] * (gv.v[k] - k2[k] - xhat * k3[k]);
+    }
+    st_cols<VEC>(dx + r * D + col, gv);
+  }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(L_THREADS) bn_test_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, const float* __restrict__ rmean,
+                                                            const float* __restrict__ rvar, float* __restrict__ out, int64_t N,
+                                                            int64_t D, int64_t rows_per_chunk, float eps) {
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * VEC;
+  if (col >= D) return;
+  const ColVec<VEC> g = ld_cols<VEC>(gamma + col), b = ld_cols<VEC>(beta + col);
+  const ColVec<VEC> m = ld_cols<VEC>(rmean + col), v = ld_cols<VEC>(rvar + col);
+  float sc[VEC], sh[VEC];
+#pragma unroll
+  for (int k = 0; k < VEC; ++k) { sc[k] = g.v[k] / sqrtf(v.v[k] + eps); sh[k] = b.v[k] - m.v[k] * sc[k]; }
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
+  const int64_t r1 = min(N, r0 + rows_per_chunk);
+  for (int64_t r = r0 + ty; r < r1; r += 8) {
+    ColVec<VEC> xv = ld_cols<VEC>(x + r * D + col);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) xv.v[k] = fmaf(xv.v[k], sc[k], sh[k]);
+    st_cols<VEC>(out + r * D + col, xv);
+  }
+}
+
+struct BnTiling {
+  int vec;
+  int64_t col_tiles, chunks, rows_per_chunk;
+};
+static BnTiling bn_tiling(bool ptrs_aligned, int64_t N, int64_t D) {
+  BnTiling t;
+  t.vec = ((D % 4 == 0) && ptrs_aligned) ? 4 : 1;
+  t.col_tiles = (D + 32 * t.vec - 1) / (32 * t.vec);
+  int64_t want = (2 * (int64_t)sm_count() + t.col_tiles - 1) / t.col_tiles;  // ~2 CTAs per SM
+  int64_t maxc = (N + 31) / 32;                                             // >= 32 rows per chunk
+  t.chunks = want < maxc ? want : maxc;
+  if (t.chunks < 1) t.chunks = 1;
+  if (t.chunks > 4096) t.chunks = 4096;
+  t.rows_per_chunk = (N + t.chunks - 1) / t.chunks;
+  t.chunks = (N + t.rows_per_chunk - 1) / t.rows_per_chunk;
+  return t;
+}
+
+// ===================================== LSTM cell ======================================
+__device__ __forceinline__ float sigmoid_ref(float x) { return 1.0f / (1.0f + expf(-x)); }  // layers.py:243
+
+__global__ void __launch_bounds__(L_THREADS) lstm_fwd_kernel(const float* __restrict__ a, const float* __restrict__ prev_c,
+                                                             float* __restrict__ next_h, float* __restrict__ next_c,
+                                                             float* __restrict__ gates, int64_t N, int64_t H) {
+  const int64_t n = N * H;
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t t = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; t < n; t += stride) {
+    const int64_t r = t / H, j = t % H;
+    const float* __restrict__ ar = a + r * 4 * H;
+    const float i = sigmoid_ref(ar[j]), f = sigmoid_ref(ar[H + j]), o = sigmoid_ref(ar[2 * H + j]);
+    const float g = tanhf(ar[3 * H + j]);
+    const float c = f * prev_c[t] + i * g;
+    next_c[t] = c;
+    next_h[t] = o * tanhf(c);
+    float* __restrict__ gr = gates + r * 4 * H;
+    gr[j] = i; gr[H + j] = f; gr[2 * H + j] = o; gr[3 * H + j] = g;
+  }
+}
+
+__global__ void __launch_bounds__(L_THREADS) lstm_bwd_kernel(const float* __restrict__ gates, const float* __restrict__ prev_c,
+                                                             const float* __restrict__ next_c,
+                                                             const float* __restrict__ dnext_h,
+                                                             const float* __restrict__ dnext_c, float* __restrict__ da,
+                                                             float* __restrict__ dprev_c, int64_t N, int64_t H) {
+  const int64_t n = N * H;
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t t = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; t < n; t += stride) {
+    const int64_t r = t / H, j = t % H;
+    const float* __restrict__ gr = gates + r * 4 * H;
+    const float i = gr[j], f = gr[H + j], o = gr[2 * H + j], g = gr[3 * H + j];
+    const float tc = tanhf(next_c[t]);
+    const float dh = dnext_h ? dnext_h[t] : 0.f;
+    float dc = dh * o * (1.f - tc * tc);
+    if (dnext_c) dc += dnext_c[t];
+    float* __restrict__ dr = da + r * 4 * H;
+    dr[j] = dc * g * i * (1.f - i);
+    dr[H + j] = dc * prev_c[t] * f * (1.f - f);
+    dr[2 * H + j] = dh * tc * o * (1.f - o);
+    dr[3 * H + j] = dc * i * (1.f - g * g);
+    dprev_c[t] = dc * f;
+  }
+}
+
+// ===================================== optimizers =====================================
+__global__ void __launch_bounds__(L_THREADS) sgd_kernel(const float* __restrict__ w, const float* __restrict__ dw,
+                                                        float* __restrict__ wo, float lr, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t i = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i < n; i += stride) wo[i] = w[i] - lr * dw[i];
+}
+__global__ void __launch_bounds__(L_THREADS) sgd_momentum_kernel(const float* __restrict__ w, const float* __restrict__ dw,
+                                                                 const float* __restrict__ v, float* __restrict__ wo,
+                                                                 float* __restrict__ vo, float lr, float mu, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t i = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i < n; i += stride) {
+    const float nv = (v ? v[i] : 0.f) * mu - dw[i] * lr;  // optim.py:64
+    vo[i] = nv;
+    wo[i] = w[i] + nv;
+  }
+}
+__global__ void __launch_bounds__(L_THREADS) rmsprop_kernel(const float* __restrict__ w, const float* __restrict__ dw,
+                                                            const float* __restrict__ cache, float* __restrict__ wo,
+                                                            float* __restrict__ co, float lr, float decay, float eps,
+                                                            int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t i = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i < n; i += stride) {
+    const float g = dw[i];
+    const float c = (cache ? cache[i] : 0.f) * decay + g * g * (1.f - decay);  // optim.py:93
+    co[i] = c;
+    wo[i] = w[i] - lr * g / (sqrtf(c) + eps);
+  }
+}
+__global__ void __launch_bounds__(L_THREADS) adam_kernel(const float* __restrict__ w, const float* __restrict__ dw,
+                                                         const float* __restrict__ m, const float* __restrict__ v,
+                                                         float* __restrict__ wo, float* __restrict__ mo, float* __restrict__ vo,
+                                                         float lr, float b1, float b2, float eps, float bc1, float bc2,
+                                                         int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * L_THREADS;
+  for (int64_t i = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i < n; i += stride) {
+    const float g = dw[i];
+    const float nm = b1 * (m ? m[i] : 0.f) + (1.f - b1) * g;        // optim.py:128-129
+    const float nv = b2 * (v ? v[i] : 0.f) + (1.f - b2) * (g * g);
+    mo[i] = nm;
+    vo[i] = nv;
+    wo[i] = w[i] - lr * (nm / bc1) / (sqrtf(nv / bc2) + eps);      // optim.py:130-134
+  }
+}
+
+}  // namespace mc
+
+using namespace mc;
+
+extern "C" {
+
+int mc_rand_uniform(float* out, int64_t n, uint64_t seed, uint64_t offset) {
+  if (n <= 0) return 0;
+  rand_uniform_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(out, n, seed, offset);
+  MC_LAUNCHED();
+  return 0;
+}
+int mc_rand_normal(float* out, int64_t n, uint64_t seed, uint64_t offset) {
+  if (n <= 0) return 0;
+  rand_normal_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(out, n, seed, offset);
+  MC_LAUNCHED();
+  return 0;
+}
+int mc_dropout(const float* x, float* out, int64_t n, float p, uint64_t seed, uint64_t offset) {
+  if (n <= 0) return 0;
+  const int vec_ok = aligned16(x) && aligned16(out);
+  dropout_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(x, out, n, p, seed, offset, vec_ok);
+  MC_LAUNCHED();
+  return 0;
+}
+
+int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta, const float* running_mean,
+                           const float* running_var, float* out, float* new_running_mean, float* new_running_var,
+                           float* save_mean, float* save_invstd, int64_t N, int64_t D, float eps, float momentum) {
+  MC_REQUIRE(N > 0 && D > 0, "empty batch");
+  const BnTiling t = bn_tiling(aligned16(x) && aligned16(out) && aligned16(gamma) && aligned16(beta), N, D);
+  float* part = nullptr;
+  MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * t.chunks * 2 * D, stream()));
+  dim3 grid((unsigned)t.col_tiles, (unsigned)t.chunks);
+  if (t.vec == 4) {
+    bn_partial_kernel<4, false><<<grid, L_THREADS, 0, stream()>>>(x, nullptr, nullptr, nullptr, part, N, D, t.rows_per_chunk);
+    MC_LAUNCHED();
+    bn_fwd_apply_kernel<4><<<grid, L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, part, (int)t.chunks,
+                                                            out, new_running_mean, new_running_var, save_mean, save_invstd,
+                                                            N, D, t.rows_per_chunk, eps, momentum);
+  } else {
+    bn_partial_kernel<1, false><<<grid, L_THREADS, 0, stream()>>>(x, nullptr, nullptr, nullptr, part, N, D, t.rows_per_chunk);
+    MC_LAUNCHED();
+    bn_fwd_apply_kernel<1><<<grid, L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, part, (int)t.chunks,
+                                                            out, new_running_mean, new_running_var, save_mean, save_invstd,
+                                                            N, D, t.rows_per_chunk, eps, momentum);
+  }
+  MC_LAUNCHED();
+  MC_CHECK(cudaFreeAsync(part, stream()));
+  return 0;
+}
+
+int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma, const float* save_mean,
+                           const float* save_invstd, float* dx, float* dgamma, float* dbeta, int64_t N, int64_t D) {
+  MC_REQUIRE(N > 0 && D > 0, "empty batch");
+  const BnTiling t = bn_tiling(aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(gamma), N, D);
+  float* part = nullptr;
+  MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * t.chunks * 2 * D, stream()));
+  dim3 grid((unsigned)t.col_tiles, (unsigned)t.chunks);
+  if (t.vec == 4) {
+    bn_partial_kernel<4, true><<<grid, L_THREADS, 0, stream()>>>(x, dy, save_mean, save_invstd, part, N, D, t.rows_per_chunk);
+    MC_LAUNCHED();
+    bn_bwd_apply_kernel<4><<<grid, L_THREADS, 0, stream()>>>(x, dy, gamma, save_mean, save_invstd, part, (int)t.chunks, dx,
+                                                            dgamma, dbeta, N, D, t.rows_per_chunk);
+  } else {
+    bn_partial_kernel<1, true><<<grid, L_THREADS, 0, stream()>>>(x, dy, save_mean, save_invstd, part, N, D, t.rows_per_chunk);
+    MC_LAUNCHED();
+    bn_bwd_apply_kernel<1><<<grid, L_THREADS, 0, stream()>>>(x, dy, gamma, save_mean, save_invstd, part, (int)t.chunks, dx,
+                                                            dgamma, dbeta, N, D, t.rows_per_chunk);
+  }
+  MC_LAUNCHED();
+  MC_CHECK(cudaFreeAsync(part, stream()));
+  return 0;
+}
+
+int mc_batchnorm_test_fwd(const float* x, const float* gamma, const float* beta, const float* running_mean,
+                          const float* running_var, float* out, int64_t N, int64_t D, float eps) {
+  MC_REQUIRE(N > 0 && D > 0, "empty batch");
+  const BnTiling t = bn_tiling(aligned16(x) && aligned16(out) && aligned16(gamma) && aligned16(beta), N, D);
+  dim3 grid((unsigned)t.col_tiles, (unsigned)t.chunks);
+  if (t.vec == 4) bn_test_kernel<4><<<grid, L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, out, N, D, t.rows_per_chunk, eps);
+  else bn_test_kernel<1><<<grid, L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, out, N, D, t.rows_per_chunk, eps);
+  MC_LAUNCHED();
+  return 0;
+}
+
+int mc_lstm_cell_fwd(const float* a, const float* prev_c, float* next_h, float* next_c, float* gates, int64_t N, int64_t H) {
+  if (N * H <= 0) return 0;
+  lstm_fwd_kernel<<<grid_for(N * H, L_THREADS), L_THREADS, 0, stream()>>>(a, prev_c, next_h, next_c, gates, N, H);
+  MC_LAUNCHED();
+  return 0;
+}
+int mc_lstm_cell_bwd(const float* gates, const float* prev_c, const float* next_c, const float* dnext_h,
+                     const float* dnext_c, float* da, float* dprev_c, int64_t N, int64_t H) {
+  if (N * H <= 0) return 0;
+  lstm_bwd_kernel<<<grid_for(N * H, L_THREADS), L_THREADS, 0, stream()>>>(gates, prev_c, next_c, dnext_h, dnext_c, da, dprev_c, N, H);
+  MC_LAUNCHED();
+  return 0;
+}
+
+int mc_sgd(const float* w, const float* dw, float* w_out, float lr, int64_t n) {
+  if (n <= 0) return 0;
+  sgd_kernel<<<grid_for(n, L_THREADS), L_THREADS, 0, stream()>>>(w, dw, w_out, lr, n);
+  MC_LAUNCHED();
+  return 0;
+}
+int mc_sgd_momentum(const float* w, const float* dw, const float* v, float* w_out, float* v_out, float lr, float momentum,
+                    int64_t n) {
+  if (n <= 0) return 0;
+  sgd_momentum_kernel<<<grid_for(n, L_THREADS), L_THREADS, 0, stream()>>>(w, dw, v, w_out, v_out, lr, momentum, n);
+  MC_LAUNCHED();
+  return 0;
+}
+int mc_rmsprop(const float* w, const float* dw, const float* cache, float* w_out, float* cache_out, float lr, float decay,
+               float eps, int64_t n) {
+  if (n <= 0) return 0;
+  rmsprop_kernel<<<grid_for(n, L_THREADS), L_THREADS, 0, stream()>>>(w, dw, cache, w_out, cache_out, lr, decay, eps, n);
+  MC_LAUNCHED();
+  return 0;
+}
+int mc_adam(const float* w, const float* dw, const float* m, const float* v, float* w_out, float* m_out, float* v_out,
+            float lr, float beta1, float beta2, float eps, int64_t t, int64_t n) {
+  if (n <= 0) return 0;
+  const float bc1 = (float)(1.0 - pow((double)beta1, (double)t));
+  const float bc2 = (float)(1.0 - pow((double)beta2, (double)t));
+  adam_kernel<<<grid_for(n, L_THREADS), L_THREADS, 0, stream()>>>(w, dw, m, v, w_out, m_out, v_out, lr, beta1, beta2, eps, bc1,
+                                                                bc2, n);
+  MC_LAUNCHED();
+  return 0;
+}
+
+}  // extern "C"

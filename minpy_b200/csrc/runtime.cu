@@ -1,0 +1,174 @@
+// Runtime plumbing of libminpy_cuda.so: device / stream selection, the stream-ordered
+// caching allocator, copies, events, CUDA-graph capture and the launch counter.
+#include <atomic>
+#include <stdarg.h>
+#include "common.cuh"
+
+namespace mc {
+
+static thread_local char g_err[512] = "";
+static cudaStream_t g_stream = nullptr;
+static int g_device = -1;
+static int g_sm_count = 148;
+static std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+cudaStream_t stream() { return g_stream; }
+int sm_count() { return g_sm_count; }
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+static int configure_device(int device) {
+  MC_CHECK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  MC_CHECK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("libminpy_cuda is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
+    return 3;
+  }
+  g_sm_count = prop.multiProcessorCount;
+  g_device = device;
+  // Keep freed blocks cached in the default mempool instead of returning them to the
+  // driver at every synchronisation: training steps reuse the same sizes every step.
+  cudaMemPool_t pool;
+  MC_CHECK(cudaDeviceGetDefaultMemPool(&pool, device));
+  uint64_t threshold = UINT64_MAX;
+  MC_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+  return 0;
+}
+
+}  // namespace mc
+
+using namespace mc;
+
+extern "C" {
+
+const char* mc_last_error(void) { return g_err; }
+
+int mc_device_count(int* count) {
+  MC_CHECK(cudaGetDeviceCount(count));
+  return 0;
+}
+int mc_init(int device) { return configure_device(device); }
+int mc_set_device(int device) { return configure_device(device); }
+int mc_get_device(int* device) {
+  *device = g_device;
+  return 0;
+}
+int mc_sm_count(int* count) {
+  *count = g_sm_count;
+  return 0;
+}
+int mc_set_stream(void* s) {
+  g_stream = (cudaStream_t)s;
+  return 0;
+}
+int mc_get_stream(void** s) {
+  *s = (void*)g_stream;
+  return 0;
+}
+int mc_sync(void) {
+  MC_CHECK(cudaStreamSynchronize(g_stream));
+  return 0;
+}
+int mc_launch_count(uint64_t* count) {
+  *count = g_launches.load();
+  return 0;
+}
+
+int mc_alloc(void** ptr, size_t nbytes) {
+  if (nbytes == 0) nbytes = 16;
+  MC_CHECK(cudaMallocAsync(ptr, nbytes, g_stream));
+  return 0;
+}
+int mc_free(void* ptr) {
+  if (!ptr) return 0;
+  MC_CHECK(cudaFreeAsync(ptr, g_stream));
+  return 0;
+}
+int mc_host_alloc(void** ptr, size_t nbytes) {
+  MC_CHECK(cudaMallocHost(ptr, nbytes ? nbytes : 16));
+  return 0;
+}
+int mc_host_free(void* ptr) {
+  MC_CHECK(cudaFreeHost(ptr));
+  return 0;
+}
+int mc_mem_info(size_t* free_bytes, size_t* total_bytes) {
+  MC_CHECK(cudaMemGetInfo(free_bytes, total_bytes));
+  return 0;
+}
+int mc_memcpy_h2d(void* dst, const void* src, size_t n) {
+  if (n == 0) return 0;
+  MC_CHECK(cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, g_stream));
+  return 0;
+}
+int mc_memcpy_d2h(void* dst, const void* src, size_t n) {
+  if (n) MC_CHECK(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, g_stream));
+  MC_CHECK(cudaStreamSynchronize(g_stream));
+  return 0;
+}
+int mc_memcpy_d2h_async(void* dst, const void* src, size_t n) {
+  if (n) MC_CHECK(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, g_stream));
+  return 0;
+}
+int mc_memcpy_d2d(void* dst, const void* src, size_t n) {
+  if (n) MC_CHECK(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToDevice, g_stream));
+  return 0;
+}
+int mc_memset(void* dst, int byte, size_t n) {
+  if (n) MC_CHECK(cudaMemsetAsync(dst, byte, n, g_stream));
+  return 0;
+}
+
+int mc_event_create(void** ev) {
+  cudaEvent_t e;
+  MC_CHECK(cudaEventCreate(&e));
+  *ev = (void*)e;
+  return 0;
+}
+int mc_event_record(void* ev) {
+  MC_CHECK(cudaEventRecord((cudaEvent_t)ev, g_stream));
+  return 0;
+}
+int mc_event_sync(void* ev) {
+  MC_CHECK(cudaEventSynchronize((cudaEvent_t)ev));
+  return 0;
+}
+int mc_event_elapsed_ms(void* start, void* stop, float* ms) {
+  MC_CHECK(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop));
+  return 0;
+}
+int mc_event_destroy(void* ev) {
+  MC_CHECK(cudaEventDestroy((cudaEvent_t)ev));
+  return 0;
+}
+
+int mc_graph_begin(void) {
+  MC_REQUIRE(g_stream != nullptr, "graph capture needs a non-default stream (mc_set_stream)");
+  MC_CHECK(cudaStreamBeginCapture(g_stream, cudaStreamCaptureModeThreadLocal));
+  return 0;
+}
+int mc_graph_end(void** graph_exec) {
+  cudaGraph_t graph;
+  MC_CHECK(cudaStreamEndCapture(g_stream, &graph));
+  cudaGraphExec_t exec;
+  MC_CHECK(cudaGraphInstantiate(&exec, graph, 0));
+  MC_CHECK(cudaGraphDestroy(graph));
+  *graph_exec = (void*)exec;
+  return 0;
+}
+int mc_graph_launch(void* graph_exec) {
+  MC_CHECK(cudaGraphLaunch((cudaGraphExec_t)graph_exec, g_stream));
+  return 0;
+}
+int mc_graph_destroy(void* graph_exec) {
+  MC_CHECK(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec));
+  return 0;
+}
+
+}  // extern "C"

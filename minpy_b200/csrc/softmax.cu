@@ -1,0 +1,270 @@
+// Row softmax, log-sum-exp and the fused softmax cross-entropy forward / backward.
+//
+// HBM-bound: softmax 8*rows*cols bytes (read once, write once).  One warp owns one row
+// and keeps it in registers (cols <= 1024: 8 float4 per lane), so max / exp / sum / scale
+// need a single pass over HBM; wider rows use one CTA per row with the row staged in
+// shared memory (<= 48 KB) or, beyond that, three streaming passes.
+#include "common.cuh"
+
+namespace mc {
+
+int reduce_sum_internal(const float* x, float* out, int64_t outer, int64_t red, int64_t inner);
+
+constexpr int SM_THREADS = 256;
+constexpr int ROW_REGS = 32;  // floats cached per lane -> cols <= 1024
+
+enum { MODE_SOFTMAX = 0, MODE_LSE = 1, MODE_CE = 2 };
+
+// One warp per row, whole row in registers.
+// MODE_SOFTMAX: out = softmax(x).  MODE_LSE: out[row] = logsumexp.  MODE_CE: out = probs and
+// rowloss[row] = -log p[label] (labels) or -sum_j onehot[j] * log p[j].
+template <int MODE>
+__global__ void __launch_bounds__(SM_THREADS) softmax_warp_kernel(const float* __restrict__ x, float* __restrict__ out,
+                                                                  const int32_t* __restrict__ labels,
+                                                                  const float* __restrict__ onehot,
+                                                                  float* __restrict__ rowloss, int64_t rows,
+                                                                  int64_t cols) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps_per_grid = (int64_t)gridDim.x * (SM_THREADS / 32);
+  const bool vec = ((cols & 3) == 0) && ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
+  for (int64_t row = (int64_t)blockIdx.x * (SM_THREADS / 32) + (threadIdx.x >> 5); row < rows; row += warps_per_grid) {
+    const float* __restrict__ p = x + row * cols;
+    float v[ROW_REGS];
+    float m = -INFINITY;
+    if (vec) {
+      const float4* __restrict__ p4 = reinterpret_cast<const float4*>(p);
+      const int64_t c4 = cols >> 2;
+#pragma unroll
+      for (int j = 0; j < ROW_REGS / 4; ++j) {
+        int64_t i = lane + 32 * j;
+        if (i < c4) {
+          float4 t = p4[i];
+          v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+          m = nanmax(m, nanmax(nanmax(t.x, t.y), nanmax(t.z, t.w)));
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < ROW_REGS; ++j) {
+        int64_t i = lane + 32 * j;
+        if (i < cols) { v[j] = p[i]; m = nanmax(m, v[j]); }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = nanmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float s = 0.f;
+    if (vec) {
+      const int64_t c4 = cols >> 2;
+#pragma unroll
+      for (int j = 0; j < ROW_REGS / 4; ++j) {
+        if (lane + 32 * j < c4) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) { v[4 * j + k] = expf(v[4 * j + k] - m); s += v[4 * j + k]; }
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < ROW_REGS; ++j)
+        if (lane + 32 * j < cols) { v[j] = expf(v[j] - m); s += v[j]; }
+    }
+    s = warp_sum(s);
+    if (MODE == MODE_LSE) {
+      if (lane == 0) out[row] = m + logf(s);
+      continue;
+    }
+    const float inv = 1.f / s;
+    float* __restrict__ q = out + row * cols;
+    float loss = 0.f;
+    const float logs = logf(s);
+    if (vec) {
+      float4* __restrict__ q4 = reinterpret_cast<float4*>(q);
+      const int64_t c4 = cols >> 2;
+#pragma unroll
+      for (int j = 0; j < ROW_REGS / 4; ++j) {
+        int64_t i = lane + 32 * j;
+        if (i < c4) {
+          float4 t = make_float4(v[4 * j] * inv, v[4 * j + 1] * inv, v[4 * j + 2] * inv, v[4 * j + 3] * inv);
+          q4[i] = t;
+          if (MODE == MODE_CE && onehot) {
+            float4 y = __ldg(reinterpret_cast<const float4*>(onehot + row * cols) + i);
+            // log p = log(e) - log(s), with e = exp(x - m) kept in v
+            if (y.x != 0.f) loss -= y.x * (logf(v[4 * j]) - logs);
+            if (y.y != 0.f) loss -= y.y * (logf(v[4 * j + 1]) - logs);
+            if (y.z != 0.f) loss -= y.z * (logf(v[4 * j + 2]) - logs);
+            if (y.w != 0.f) loss -= y.w * (logf(v[4 * j + 3]) - logs);
+          }
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < ROW_REGS; ++j) {
+        int64_t i = lane + 32 * j;
+        if (i < cols) {
+          q[i] = v[j] * inv;
+          if (MODE == MODE_CE && onehot) {
+            float y = __ldg(onehot + row * cols + i);
+            if (y != 0.f) loss -= y * (logf(v[j]) - logs);
+          }
+        }
+      }
+    }
+    if (MODE == MODE_CE) {
+      if (labels) {
+        // -log p[label] = log(s) - (x[label] - m)
+        if (lane == 0) {
+          int32_t y = labels[row];
+          rowloss[row] = (y >= 0 && y < cols) ? (logs - (p[y] - m)) : 0.f;
+        }
+      } else {
+        loss = warp_sum(loss);
+        if (lane == 0) rowloss[row] = loss;
+      }
+    }
+  }
+}
+
+// One CTA per row for wide rows: three passes over the row (max, sum-exp, write); the
+// row is re-read from L2, not HBM, for any width that matters here.
+template <int MODE>
+__global__ void __launch_bounds__(SM_THREADS) softmax_block_kernel(const float* __restrict__ x, float* __restrict__ out,
+                                                                   const int32_t* __restrict__ labels,
+                                                                   const float* __restrict__ onehot,
+                                                                   float* __restrict__ rowloss, int64_t cols) {
+  __shared__ float smem[32];
+  const int64_t row = blockIdx.x;
+  const float* __restrict__ p = x + row * cols;
+  float m = -INFINITY;
+  for (int64_t i = threadIdx.x; i < cols; i += SM_THREADS) m = nanmax(m, p[i]);
+  m = block_reduce(m, MaxOp(), smem);
+  float s = 0.f;
+  for (int64_t i = threadIdx.x; i < cols; i += SM_THREADS) s += expf(p[i] - m);
+  s = block_reduce(s, SumOp(), smem);
+  if (MODE == MODE_LSE) {
+    if (threadIdx.x == 0) out[row] = m + logf(s);
+    return;
+  }
+  const float inv = 1.f / s, logs = logf(s);
+  float* __restrict__ q = out + row * cols;
+  float loss = 0.f;
+  for (int64_t i = threadIdx.x; i < cols; i += SM_THREADS) {
+    float d = p[i] - m;
+    q[i] = expf(d) * inv;
+    if (MODE == MODE_CE && onehot) {
+      float y = __ldg(onehot + row * cols + i);
+      if (y != 0.f) loss -= y * (d - logs);
+    }
+  }
+  if (MODE == MODE_CE) {
+    if (labels) {
+      if (threadIdx.x == 0) {
+        int32_t y = labels[row];
+        rowloss[row] = (y >= 0 && y < cols) ? (logs - (p[y] - m)) : 0.f;
+      }
+    } else {
+      loss = block_reduce(loss, SumOp(), smem);
+      if (threadIdx.x == 0) rowloss[row] = loss;
+    }
+  }
+}
+
+template <int MODE>
+static int launch_softmax(const float* x, float* out, const int32_t* labels, const float* onehot, float* rowloss,
+                          int64_t rows, int64_t cols) {
+  if (cols <= 32 * ROW_REGS) {
+    int grid = grid_for(rows, SM_THREADS / 32);
+    softmax_warp_kernel<MODE><<<grid, SM_THREADS, 0, stream()>>>(x, out, labels, onehot, rowloss, rows, cols);
+  } else {
+    MC_REQUIRE(rows < (int64_t)2147483647, "too many rows");
+    softmax_block_kernel<MODE><<<(unsigned)rows, SM_THREADS, 0, stream()>>>(x, out, labels, onehot, rowloss, cols);
+  }
+  MC_LAUNCHED();
+  return 0;
+}
+
+__global__ void __launch_bounds__(SM_THREADS) scale_scalar_kernel(float* __restrict__ v, float s) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) v[0] *= s;
+}
+
+__global__ void __launch_bounds__(SM_THREADS) onehot_kernel(const int32_t* __restrict__ idx, float* __restrict__ out,
+                                                            int64_t rows, int64_t cols) {
+  const int64_t stride = (int64_t)gridDim.x * SM_THREADS;
+  for (int64_t r = (int64_t)blockIdx.x * SM_THREADS + threadIdx.x; r < rows; r += stride) {
+    int32_t c = idx[r];
+    if (c < 0) c += (int32_t)cols;  // NumPy negative indexing
+    if (c >= 0 && c < cols) out[r * cols + c] = 1.f;
+  }
+}
+
+__global__ void __launch_bounds__(SM_THREADS) softmax_ce_bwd_kernel(const float* __restrict__ probs,
+                                                                    const int32_t* __restrict__ labels,
+                                                                    const float* __restrict__ onehot,
+                                                                    float* __restrict__ dx, int64_t rows, int64_t cols,
+                                                                    float inv_rows) {
+  const int64_t n = rows * cols;
+  const int64_t stride = (int64_t)gridDim.x * SM_THREADS;
+  for (int64_t t = (int64_t)blockIdx.x * SM_THREADS + threadIdx.x; t < n; t += stride) {
+    float y;
+    if (labels) {
+      const int64_t r = t / cols, c = t % cols;
+      y = (labels[r] == (int32_t)c) ? 1.f : 0.f;
+    } else {
+      y = onehot[t];
+    }
+    dx[t] = (probs[t] - y) * inv_rows;
+  }
+}
+
+}  // namespace mc
+
+using namespace mc;
+
+extern "C" {
+
+int mc_softmax_rows(const float* x, float* out, int64_t rows, int64_t cols) {
+  if (rows * cols <= 0) return 0;
+  return launch_softmax<MODE_SOFTMAX>(x, out, nullptr, nullptr, nullptr, rows, cols);
+}
+
+int mc_logsumexp_rows(const float* x, float* out, int64_t rows, int64_t cols) {
+  if (rows <= 0) return 0;
+  MC_REQUIRE(cols > 0, "logsumexp of empty rows");
+  return launch_softmax<MODE_LSE>(x, out, nullptr, nullptr, nullptr, rows, cols);
+}
+
+int mc_onehot(const int32_t* idx, float* out, int64_t rows, int64_t cols) {
+  if (rows <= 0) return 0;
+  onehot_kernel<<<grid_for(rows, SM_THREADS), SM_THREADS, 0, stream()>>>(idx, out, rows, cols);
+  MC_LAUNCHED();
+  return 0;
+}
+
+int mc_softmax_ce_fwd(const float* x, const int32_t* labels, const float* onehot, float* probs, float* loss,
+                      int64_t rows, int64_t cols) {
+  MC_REQUIRE((labels != nullptr) != (onehot != nullptr), "exactly one of labels / onehot");
+  MC_REQUIRE(rows > 0 && cols > 0, "empty input");
+  float* rowloss = nullptr;
+  MC_CHECK(cudaMallocAsync((void**)&rowloss, sizeof(float) * rows, stream()));
+  int rc = launch_softmax<MODE_CE>(x, probs, labels, onehot, rowloss, rows, cols);
+  if (rc == 0) rc = reduce_sum_internal(rowloss, loss, 1, rows, 1);
+  if (rc == 0) {
+    scale_scalar_kernel<<<1, 32, 0, stream()>>>(loss, 1.f / (float)rows);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { mc::set_error("scale launch failed: %s", cudaGetErrorString(e)); rc = 1; }
+    else mc::count_launch();
+  }
+  MC_CHECK(cudaFreeAsync(rowloss, stream()));
+  return rc;
+}
+
+int mc_softmax_ce_bwd(const float* probs, const int32_t* labels, const float* onehot, float* dx, int64_t rows,
+                      int64_t cols) {
+  MC_REQUIRE((labels != nullptr) != (onehot != nullptr), "exactly one of labels / onehot");
+  if (rows * cols <= 0) return 0;
+  softmax_ce_bwd_kernel<<<grid_for(rows * cols, SM_THREADS), SM_THREADS, 0, stream()>>>(probs, labels, onehot, dx, rows,
+                                                                                       cols, 1.f / (float)rows);
+  MC_LAUNCHED();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,173 @@
+"""CudaArray: the raw array type of the `cuda` array variant.
+
+Plays the role `mxnet.ndarray.NDArray` plays for the reference's MXNet variant
+(minpy/array_variants/mxnet/__init__.py:10): a dense, row-major device buffer with a
+shape and a dtype, plus the duck-typed surface MinPy's core calls on a raw array
+(`.shape .dtype .size .asnumpy() .wait_to_read() .reshape() .copyto()`,
+SURVEY.md 8b).  Storage comes from the library's stream-ordered pool; it is released
+when the last view dies.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from ._lib import get_lib
+
+_F32 = np.dtype('float32')
+_I32 = np.dtype('int32')
+_I64 = np.dtype('int64')
+_DTYPE_CODE = {_F32: 0, _I32: 1, _I64: 2, np.dtype('float64'): 3, np.dtype('uint8'): 4, np.dtype('bool'): 4}
+
+_state = {'device': None}
+
+
+def ensure_device(device: int = None):
+    """Initialise the library on `device` (default: LOCAL_RANK or 0) once per process."""
+    if _state['device'] is None or (device is not None and device != _state['device']):
+        import os
+        dev = device if device is not None else int(os.environ.get('LOCAL_RANK', '0'))
+        get_lib().mc_init(dev)
+        _state['device'] = dev
+    return _state['device']
+
+
+class _Buffer(object):
+    """Owns one device allocation."""
+    __slots__ = ('ptr', 'nbytes', '_free')
+
+    def __init__(self, nbytes):
+        lib = get_lib()
+        p = ctypes.c_void_p()
+        lib.mc_alloc(ctypes.byref(p), nbytes)
+        self.ptr = p.value
+        self.nbytes = nbytes
+        self._free = lib.cdll.mc_free
+
+    def __del__(self):
+        try:
+            self._free(self.ptr)
+        except Exception:  # interpreter shutdown
+            pass
+
+
+def _prod(shape):
+    n = 1
+    for s in shape:
+        n *= s
+    return n
+
+
+class CudaArray(object):
+    """Dense row-major device array (float32 / int32 / int64)."""
+    __slots__ = ('buf', 'ptr', 'shape', 'size', 'dtype', '__weakref__')
+    __array_priority__ = 200.0
+
+    def __init__(self, buf, ptr, shape, dtype=_F32):
+        self.buf = buf
+        self.ptr = ptr
+        self.shape = shape
+        self.size = _prod(shape)
+        self.dtype = dtype
+
+    # ---- construction -------------------------------------------------------------
+    @staticmethod
+    def empty(shape, dtype=_F32):
+        if _state['device'] is None:
+            ensure_device()
+        shape = tuple(int(s) for s in shape)
+        buf = _Buffer(_prod(shape) * dtype.itemsize)
+        return CudaArray(buf, buf.ptr, shape, dtype)
+
+    @staticmethod
+    def from_numpy(arr):
+        """Host -> device. float64/float16 become float32 (the MXNet variant did the same,
+        minpy/array.py:388-389); integer and bool arrays become int32/int64-preserving."""
+        arr = np.asarray(arr)
+        if arr.dtype.kind == 'f':
+            dt = _F32
+        elif arr.dtype.kind == 'b':
+            dt = _F32
+        elif arr.dtype == _I64:
+            dt = _I64
+        elif arr.dtype.kind in 'iu':
+            dt = _I32
+        else:
+            raise TypeError('unsupported dtype for the cuda variant: %s' % arr.dtype)
+        host = np.ascontiguousarray(arr, dtype=dt)
+        out = CudaArray.empty(host.shape, dt)
+        if host.size:
+            get_lib().mc_memcpy_h2d(out.ptr, host.ctypes.data, host.nbytes)
+            # pageable source: the copy is staged before the call returns, `host` may die
+        return out
+
+    # ---- duck-typed surface ---------------------------------------------------------
+    @property
+    def ndim(self):
+        return len(self.shape)
+
+    @property
+    def nbytes(self):
+        return self.size * self.dtype.itemsize
+
+    @property
+    def context(self):
+        return ('gpu', _state['device'])
+
+    def asnumpy(self):
+        out = np.empty(self.shape, dtype=self.dtype)
+        get_lib().mc_memcpy_d2h(out.ctypes.data, self.ptr, self.nbytes)
+        return out
+
+    def asscalar(self):
+        return self.asnumpy().reshape(-1)[0].item()
+
+    def wait_to_read(self):
+        get_lib().mc_sync()
+
+    def reshape(self, *shape):
+        if len(shape) == 1 and not isinstance(shape[0], (int, np.integer)):
+            shape = tuple(shape[0])
+        shape = [int(s) for s in shape]
+        if -1 in shape:
+            known = -_prod(shape)
+            shape[shape.index(-1)] = self.size // known if known else 0
+        shape = tuple(shape)
+        if _prod(shape) != self.size:
+            raise ValueError('cannot reshape array of size %d into shape %s' % (self.size, shape))
+        return CudaArray(self.buf, self.ptr, shape, self.dtype)
+
+    def copy(self):
+        out = CudaArray.empty(self.shape, self.dtype)
+        get_lib().mc_memcpy_d2d(out.ptr, self.ptr, self.nbytes)
+        return out
+
+    def copyto(self, dst):
+        if dst.shape != self.shape or dst.dtype != self.dtype:
+            raise ValueError('copyto: shape/dtype mismatch')
+        get_lib().mc_memcpy_d2d(dst.ptr, self.ptr, self.nbytes)
+        return dst
+
+    def astype(self, dtype):
+        dtype = np.dtype(dtype)
+        if dtype == np.dtype('float64'):
+            dtype = _F32
+        if dtype == self.dtype:
+            return self
+        out = CudaArray.empty(self.shape, dtype)
+        get_lib().mc_cast(self.ptr, _DTYPE_CODE[self.dtype], out.ptr, _DTYPE_CODE[dtype], self.size)
+        return out
+
+    def __len__(self):
+        if not self.shape:
+            raise TypeError('len() of unsized object')
+        return self.shape[0]
+
+    def __repr__(self):
+        return 'CudaArray(shape=%s, dtype=%s)' % (self.shape, self.dtype)
+
+    def __float__(self):
+        return float(self.asnumpy().reshape(-1)[0])
+
+    # operators are provided by minpy_b200.ops (installed there to avoid an import cycle)

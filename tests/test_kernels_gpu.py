@@ -1,0 +1,415 @@
+"""GPU parity tests of the C-ABI kernels (through minpy_b200.ops -> ctypes -> libminpy_cuda.so)
+against NumPy float64 / the oracle on identical seeded inputs.
+
+Tolerances (BASELINE.json north_star): FP32 elementwise and reductions <= 1e-5 relative;
+argmax / indexing bit-exact; TF32 tensor-core GEMM <= 1e-2 relative with an FP32-accumulate
+cross-check (the CUDA-core path, <= 1e-5)."""
+import numpy as np
+import pytest
+
+from oracle import minpy_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    if a.shape != b.shape:
+        return np.inf
+    if a.size == 0:
+        return 0.0
+    return float(np.max(np.abs(a - b)) / max(1e-30, np.max(np.abs(b))))
+
+
+def up(cuda, a):
+    from minpy_b200.cuda_array import CudaArray
+    return CudaArray.from_numpy(a)
+
+
+UNARY = {
+    'MC_NEG': np.negative, 'MC_ABS': np.abs, 'MC_SIGN': np.sign, 'MC_ROUND': np.round, 'MC_CEIL': np.ceil,
+    'MC_FLOOR': np.floor, 'MC_SQRT': lambda x: np.sqrt(np.abs(x)), 'MC_EXP': np.exp, 'MC_LOG': lambda x: np.log(np.abs(x) + 0.1),
+    'MC_SIN': np.sin, 'MC_COS': np.cos, 'MC_TANH': np.tanh, 'MC_SIGMOID': orc._sigmoid_fwd,
+    'MC_SQUARE': np.square, 'MC_RECIP': lambda x: 1.0 / (np.abs(x) + 0.5), 'MC_RELU': lambda x: np.maximum(0, x),
+    'MC_COPY': lambda x: x, 'MC_COSH': np.cosh, 'MC_LOGICAL_NOT': lambda x: (x == 0).astype(np.float64),
+}
+
+
+@pytest.mark.parametrize('n', [0, 1, 3, 5, 1000, 4099, 1 << 20])
+def test_unary(cuda, n):
+    rng = np.random.RandomState(n)
+    x = (rng.randn(n) * 3).astype(np.float32)
+    for name, f in UNARY.items():
+        xin = x
+        if name == 'MC_SQRT':
+            xin = np.abs(x)
+        elif name == 'MC_LOG':
+            xin = (np.abs(x) + 0.1).astype(np.float32)
+        elif name == 'MC_RECIP':
+            xin = (np.abs(x) + 0.5).astype(np.float32)
+        ref = {'MC_SQRT': np.sqrt, 'MC_LOG': np.log, 'MC_RECIP': lambda v: 1.0 / v}.get(name, f)(xin.astype(np.float64))
+        got = cuda.unary(cuda.L().enums[name], up(cuda, xin)).asnumpy()
+        assert rel(got, ref) <= 1e-5, name
+
+
+BINARY = {
+    'MC_ADD': np.add, 'MC_SUB': np.subtract, 'MC_MUL': np.multiply, 'MC_DIV': np.divide,
+    'MC_MAX': np.maximum, 'MC_MIN': np.minimum, 'MC_MOD': np.mod,
+    'MC_EQ': np.equal, 'MC_NE': np.not_equal, 'MC_LT': np.less, 'MC_GT': np.greater, 'MC_LE': np.less_equal,
+    'MC_GE': np.greater_equal,
+}
+
+
+@pytest.mark.parametrize('shapes', [((1000,), (1000,)), ((37, 53), (37, 53)), ((64, 128), (128,)), ((64, 128), (64, 1)),
+                                    ((5, 7), (7,)), ((5, 7), (5, 1)), ((3, 1, 5), (4, 1)), ((2, 3, 4, 5), (3, 1, 5)),
+                                    ((128,), (64, 128)), ((64, 1), (64, 128)), ((1, 128), (64, 128)), ((6, 1, 8), (1, 7, 1)),
+                                    ((0, 4), (4,))])
+def test_binary_broadcast(cuda, shapes):
+    rng = np.random.RandomState(7)
+    a = rng.randint(-3, 4, size=shapes[0]).astype(np.float32) + 0.5 * rng.randint(0, 2, size=shapes[0])
+    b = rng.randint(1, 4, size=shapes[1]).astype(np.float32)
+    for name, f in BINARY.items():
+        ref = f(a.astype(np.float64), b.astype(np.float64)).astype(np.float64)
+        got = cuda.binary(cuda.L().enums[name], up(cuda, a), up(cuda, b)).asnumpy()
+        assert got.shape == ref.shape, name
+        assert rel(got, ref) <= 1e-6, name
+    # power on positive bases
+    ref = np.power(np.abs(a.astype(np.float64)) + 1, b.astype(np.float64))
+    got = cuda.binary(cuda.L().MC_POW, up(cuda, (np.abs(a) + 1).astype(np.float32)), up(cuda, b)).asnumpy()
+    assert rel(got, ref) <= 1e-5
+
+
+def test_binary_scalar(cuda):
+    rng = np.random.RandomState(3)
+    a = (rng.randn(1237) + 3).astype(np.float32)
+    for name, f in BINARY.items():
+        for s in (2.0, -1.5):
+            assert rel(cuda.binary(cuda.L().enums[name], up(cuda, a), s).asnumpy(), f(a.astype(np.float64), s)) <= 1e-6, name
+            assert rel(cuda.binary(cuda.L().enums[name], s, up(cuda, a)).asnumpy(), f(s, a.astype(np.float64))) <= 1e-6, name
+
+
+@pytest.mark.parametrize('shape,axis', [((1000,), None), ((1 << 20,), None), ((333, 77), 0), ((333, 77), 1), ((333, 77), None),
+                                        ((4096, 512), 0), ((4096, 512), 1), ((8, 4096), 0), ((100000, 8), 0), ((2, 200000), 1),
+                                        ((3, 4, 5), 1), ((3, 4, 5), (0, 2)), ((3, 4, 5), (1, 2)), ((7, 1), 0), ((1, 9), 1),
+                                        ((64, 10), 1), ((70, 1000), 1)])
+@pytest.mark.parametrize('keepdims', [False, True])
+def test_reduce(cuda, shape, axis, keepdims):
+    rng = np.random.RandomState(11)
+    x = rng.rand(*shape).astype(np.float32)
+    xd = up(cuda, x)
+    lib = cuda.L()
+    for op, f in ((lib.MC_RED_SUM, np.sum), (lib.MC_RED_MAX, np.max), (lib.MC_RED_MIN, np.min)):
+        ref = f(x.astype(np.float64), axis=axis, keepdims=keepdims)
+        got = cuda.reduce(op, xd, axis, keepdims).asnumpy()
+        assert got.shape == np.shape(ref)
+        if f is np.sum:
+            assert rel(got, ref) <= 1e-5
+        else:
+            assert np.array_equal(got.astype(np.float64), ref)  # selection: exact
+
+
+@pytest.mark.parametrize('shape,axis', [((64, 10), 1), ((1000, 10), 1), ((33, 1000), 1), ((33, 1000), 0), ((5000,), None),
+                                        ((4, 5, 6), 1), ((4, 5, 6), None)])
+def test_argmax_bit_exact(cuda, shape, axis):
+    rng = np.random.RandomState(5)
+    x = rng.randint(0, 50, size=shape).astype(np.float32)  # many ties -> first index must win
+    got = cuda.argmax(up(cuda, x), axis).asnumpy()
+    ref = np.argmax(x, axis=axis)
+    assert got.dtype == np.int64
+    assert np.array_equal(got, ref)
+
+
+@pytest.mark.parametrize('rows,cols', [(1, 1), (7, 10), (256, 10), (1000, 128), (513, 1000), (64, 1024), (9, 1030), (5, 5000)])
+def test_softmax_and_ce(cuda, rows, cols):
+    from minpy_b200.cuda_array import CudaArray
+    rng = np.random.RandomState(rows * 31 + cols)
+    x = (rng.randn(rows, cols) * 4).astype(np.float32)
+    y = rng.randint(0, cols, size=rows)
+    ref = orc._softmax_output_fwd(x.astype(np.float64), None)
+    got = cuda.softmax_rows(up(cuda, x)).asnumpy()
+    assert rel(got, ref) <= 1e-5
+    lse = cuda.logsumexp_rows(up(cuda, x)).asnumpy()
+    m = x.astype(np.float64).max(axis=1)
+    assert rel(lse, m + np.log(np.exp(x.astype(np.float64) - m[:, None]).sum(axis=1))) <= 1e-5
+    lib = cuda.L()
+    for use_labels in (True, False):
+        probs = CudaArray.empty((rows, cols))
+        loss = CudaArray.empty(())
+        onehot = np.zeros((rows, cols), dtype=np.float32)
+        onehot[np.arange(rows), y] = 1
+        lab = up(cuda, y.astype(np.int32)) if use_labels else None
+        oh = None if use_labels else up(cuda, onehot)
+        lib.mc_softmax_ce_fwd(up(cuda, x).ptr, lab.ptr if lab else None, oh.ptr if oh else None, probs.ptr, loss.ptr, rows, cols)
+        ref_loss = -np.sum(np.log(ref[np.arange(rows), y])) / rows
+        assert rel(probs.asnumpy(), ref) <= 1e-5
+        assert rel(loss.asnumpy(), ref_loss) <= 1e-5
+        dx = CudaArray.empty((rows, cols))
+        lib.mc_softmax_ce_bwd(probs.ptr, lab.ptr if lab else None, oh.ptr if oh else None, dx.ptr, rows, cols)
+        assert rel(dx.asnumpy(), (ref - onehot) / rows) <= 1e-5
+
+
+GEMM_SHAPES = [(256, 512, 3072), (128, 128, 32), (128, 64, 64), (100, 36, 50), (256, 10, 512), (512, 10, 256), (256, 512, 10),
+               (1, 7, 5), (300, 200, 100), (128, 128, 8), (130, 260, 72), (1024, 512, 512), (3072, 512, 256), (32, 4096, 1024)]
+
+
+@pytest.mark.parametrize('M,N,K', GEMM_SHAPES)
+@pytest.mark.parametrize('ta,tb', [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm(cuda, M, N, K, ta, tb):
+    rng = np.random.RandomState(M + N + K)
+    a = rng.randn(*((K, M) if ta else (M, K))).astype(np.float32)
+    b = rng.randn(*((N, K) if tb else (K, N))).astype(np.float32)
+    bias = rng.randn(N).astype(np.float32)
+    A = a.T if ta else a
+    B = b.T if tb else b
+    ref = A.astype(np.float64) @ B.astype(np.float64)
+    scale = np.sqrt(K)
+    ad, bd, biasd = up(cuda, a), up(cuda, b), up(cuda, bias)
+    import ctypes
+    path = ctypes.c_int(-1)
+    for mode, tol in (('fp32', 1e-5), ('tf32', 1e-2)):
+        cuda.set_gemm_precision(mode)
+        got = cuda.gemm(ad, bd, ta, tb).asnumpy()
+        cuda.L().mc_gemm_last_path(ctypes.byref(path))
+        err = float(np.max(np.abs(got - ref)) / (scale * 3))
+        assert got.shape == ref.shape
+        assert err <= tol, (mode, path.value, err)
+        got2 = cuda.gemm(ad, bd, ta, tb, bias=biasd, relu=True).asnumpy()
+        ref2 = np.maximum(ref + bias, 0)
+        assert float(np.max(np.abs(got2 - ref2)) / (scale * 3)) <= tol, (mode, 'epilogue')
+        acc = cuda.gemm(ad, bd, ta, tb, out=up(cuda, ref.astype(np.float32)), accumulate=True).asnumpy()
+        assert float(np.max(np.abs(acc - 2 * ref)) / (scale * 3)) <= tol, (mode, 'accumulate')
+    cuda.set_gemm_precision('tf32')
+
+
+def test_gemm_tf32_path_taken(cuda):
+    """The tensor-core path must actually run for TMA-describable shapes (no silent fallback)."""
+    import ctypes
+    rng = np.random.RandomState(0)
+    a, b = rng.randn(256, 3072).astype(np.float32), rng.randn(3072, 512).astype(np.float32)
+    cuda.set_gemm_precision('tf32')
+    cuda.gemm(up(cuda, a), up(cuda, b))
+    path = ctypes.c_int(-1)
+    cuda.L().mc_gemm_last_path(ctypes.byref(path))
+    assert path.value == 1
+
+
+@pytest.mark.parametrize('N,D', [(1024, 512), (256, 10), (100, 37), (33, 4), (4096, 64), (5, 1000)])
+def test_batchnorm(cuda, N, D):
+    from minpy_b200.cuda_array import CudaArray
+    rng = np.random.RandomState(N + D)
+    x = (rng.randn(N, D) * 2 + 3).astype(np.float32)
+    gamma, beta = rng.rand(D).astype(np.float32) + 0.5, rng.randn(D).astype(np.float32)
+    rm, rv = rng.randn(D).astype(np.float32), rng.rand(D).astype(np.float32)
+    dy = rng.randn(N, D).astype(np.float32)
+    f64 = lambda a: a.astype(np.float64)
+
+    def loss(xv, g, b):
+        out, nrm, nrv = orc.batchnorm(xv, g, b, 'train', 1e-5, 0.9, f64(rm), f64(rv))
+        return orc.sum(out * f64(dy)), out, nrm, nrv
+    (gx, gg, gb), _ = orc.grad_and_loss(lambda a, b, c: loss(a, b, c)[0], (0, 1, 2))(f64(x), f64(gamma), f64(beta))
+    _, out_ref, nrm_ref, nrv_ref = loss(orc.Var(f64(x)), orc.Var(f64(gamma)), orc.Var(f64(beta)))
+    lib = cuda.L()
+    xd, gd, bd, rmd, rvd, dyd = [up(cuda, v) for v in (x, gamma, beta, rm, rv, dy)]
+    out, nrm, nrv, sm, si = [CudaArray.empty(s) for s in ((N, D), (D,), (D,), (D,), (D,))]
+    lib.mc_batchnorm_train_fwd(xd.ptr, gd.ptr, bd.ptr, rmd.ptr, rvd.ptr, out.ptr, nrm.ptr, nrv.ptr, sm.ptr, si.ptr, N, D, 1e-5, 0.9)
+    assert rel(out.asnumpy(), out_ref.value) <= 2e-5
+    assert rel(nrm.asnumpy(), orc.raw(nrm_ref)) <= 1e-5
+    assert rel(nrv.asnumpy(), orc.raw(nrv_ref)) <= 1e-5
+    dx, dg, db = [CudaArray.empty(s) for s in ((N, D), (D,), (D,))]
+    lib.mc_batchnorm_train_bwd(xd.ptr, dyd.ptr, gd.ptr, sm.ptr, si.ptr, dx.ptr, dg.ptr, db.ptr, N, D)
+    assert rel(dx.asnumpy(), gx) <= 1e-4
+    assert rel(dg.asnumpy(), gg) <= 1e-4
+    assert rel(db.asnumpy(), gb) <= 1e-5
+    test_ref, _, _ = orc.batchnorm(orc.Var(f64(x)), f64(gamma), f64(beta), 'test', 1e-5, 0.9, f64(rm), f64(rv))
+    lib.mc_batchnorm_test_fwd(xd.ptr, gd.ptr, bd.ptr, rmd.ptr, rvd.ptr, out.ptr, N, D, 1e-5)
+    assert rel(out.asnumpy(), test_ref.value) <= 1e-5
+
+
+def test_dropout_and_rng(cuda):
+    from minpy_b200.cuda_array import CudaArray
+    lib = cuda.L()
+    n = 1 << 20
+    x = up(cuda, np.ones(n, dtype=np.float32))
+    o1, o2 = CudaArray.empty((n,)), CudaArray.empty((n,))
+    lib.mc_dropout(x.ptr, o1.ptr, n, 0.3, 1234, 10)
+    lib.mc_dropout(x.ptr, o2.ptr, n, 0.3, 1234, 10)
+    a, b = o1.asnumpy(), o2.asnumpy()
+    assert np.array_equal(a, b)                       # same (seed, offset) -> same mask (VJP regeneration)
+    assert set(np.unique(a)) <= {0.0, 1.0}            # not rescaled (layers.py:143-144)
+    assert abs(a.mean() - 0.7) < 5e-3
+    lib.mc_dropout(x.ptr, o2.ptr, n, 0.3, 1234, 10 + n)
+    assert not np.array_equal(a, o2.asnumpy())
+    u, g = CudaArray.empty((n,)), CudaArray.empty((n + 3,))
+    lib.mc_rand_uniform(u.ptr, n, 7, 0)
+    lib.mc_rand_normal(g.ptr, n + 3, 7, 0)
+    uu, gg = u.asnumpy(), g.asnumpy()
+    assert uu.min() >= 0.0 and uu.max() < 1.0 and abs(uu.mean() - 0.5) < 3e-3 and abs(uu.var() - 1 / 12.) < 3e-3
+    assert abs(gg.mean()) < 5e-3 and abs(gg.std() - 1.0) < 5e-3 and np.isfinite(gg).all()
+
+
+def test_lstm_cell(cuda):
+    from minpy_b200.cuda_array import CudaArray
+    rng = np.random.RandomState(2)
+    N, H = 17, 24
+    a, pc = rng.randn(N, 4 * H).astype(np.float32), rng.randn(N, H).astype(np.float32)
+    dh, dc = rng.randn(N, H).astype(np.float32), rng.randn(N, H).astype(np.float32)
+    f64 = lambda v: v.astype(np.float64)
+
+    def cell(av, cv):
+        i, f = orc.sigmoid(av[:, 0:H]), orc.sigmoid(av[:, H:2 * H])
+        o, g = orc.sigmoid(av[:, 2 * H:3 * H]), orc.tanh(av[:, 3 * H:4 * H])
+        nc = f * cv + i * g
+        return o * orc.tanh(nc), nc
+    nh_ref, nc_ref = cell(orc.Var(f64(a)), orc.Var(f64(pc)))
+    (ga, gc), _ = orc.grad_and_loss(lambda av, cv: orc.sum(cell(av, cv)[0] * f64(dh)) + orc.sum(cell(av, cv)[1] * f64(dc)), (0, 1))(f64(a), f64(pc))
+    lib = cuda.L()
+    ad, pcd, dhd, dcd = [up(cuda, v) for v in (a, pc, dh, dc)]
+    nh, nc, gates, da, dpc = [CudaArray.empty(s) for s in ((N, H), (N, H), (N, 4 * H), (N, 4 * H), (N, H))]
+    lib.mc_lstm_cell_fwd(ad.ptr, pcd.ptr, nh.ptr, nc.ptr, gates.ptr, N, H)
+    assert rel(nh.asnumpy(), nh_ref.value) <= 1e-5 and rel(nc.asnumpy(), nc_ref.value) <= 1e-5
+    lib.mc_lstm_cell_bwd(gates.ptr, pcd.ptr, nc.ptr, dhd.ptr, dcd.ptr, da.ptr, dpc.ptr, N, H)
+    assert rel(da.asnumpy(), ga) <= 1e-5 and rel(dpc.asnumpy(), gc) <= 1e-5
+
+
+def test_optimizers(cuda):
+    from minpy_b200.cuda_array import CudaArray
+    rng = np.random.RandomState(9)
+    n = 10007
+    w, dw = rng.randn(n).astype(np.float32), rng.randn(n).astype(np.float32)
+    f64 = lambda v: v.astype(np.float64)
+    lib = cuda.L()
+    wd, dwd = up(cuda, w), up(cuda, dw)
+    wo = CudaArray.empty((n,))
+    lib.mc_sgd(wd.ptr, dwd.ptr, wo.ptr, 0.1, n)
+    assert rel(wo.asnumpy(), orc.sgd(f64(w), f64(dw), {'learning_rate': 0.1})[0]) <= 1e-6
+    cfg, wr = {'learning_rate': 0.1, 'momentum': 0.9}, f64(w)
+    v = None
+    wcur = wd
+    for _ in range(3):
+        wr, cfg = orc.sgd_momentum(wr, f64(dw), cfg)
+        wn, vn = CudaArray.empty((n,)), CudaArray.empty((n,))
+        lib.mc_sgd_momentum(wcur.ptr, dwd.ptr, v.ptr if v else None, wn.ptr, vn.ptr, 0.1, 0.9, n)
+        wcur, v = wn, vn
+    assert rel(wcur.asnumpy(), wr) <= 1e-5
+    cfg, wr = {'learning_rate': 0.01}, f64(w)
+    wcur, c = wd, None
+    for _ in range(3):
+        wr, cfg = orc.rmsprop(wr, f64(dw), cfg)
+        wn, cn = CudaArray.empty((n,)), CudaArray.empty((n,))
+        lib.mc_rmsprop(wcur.ptr, dwd.ptr, c.ptr if c else None, wn.ptr, cn.ptr, 0.01, 0.99, 1e-8, n)
+        wcur, c = wn, cn
+    assert rel(wcur.asnumpy(), wr) <= 1e-5
+    cfg, wr = {'learning_rate': 0.001}, f64(w)
+    wcur, m, v = wd, None, None
+    for t in range(1, 4):
+        wr, cfg = orc.adam(wr, f64(dw), cfg)
+        wn, mn, vn = CudaArray.empty((n,)), CudaArray.empty((n,)), CudaArray.empty((n,))
+        lib.mc_adam(wcur.ptr, dwd.ptr, m.ptr if m else None, v.ptr if v else None, wn.ptr, mn.ptr, vn.ptr, 0.001, 0.9, 0.999, 1e-8, t, n)
+        wcur, m, v = wn, mn, vn
+    assert rel(wcur.asnumpy(), wr) <= 1e-5
+
+
+@pytest.mark.parametrize('index', [np.s_[2:5], np.s_[:, 1:3], np.s_[::2], np.s_[:, ::2], np.s_[1], np.s_[:, 3], np.s_[1:6:2, 4:0:-1],
+                                   np.s_[..., 2], np.s_[-1], np.s_[:, -3:]])
+def test_getitem_basic_bit_exact(cuda, index):
+    rng = np.random.RandomState(4)
+    x = rng.randn(7, 9).astype(np.float32)
+    got = cuda.getitem(up(cuda, x), index).asnumpy()
+    assert np.array_equal(got, x[index])
+    g = rng.randn(*np.shape(x[index])).astype(np.float32)
+    ref = np.zeros_like(x)
+    np.add.at(ref, index, g)
+    assert np.array_equal(cuda.getitem_grad(up(cuda, x), index, up(cuda, g)).asnumpy(), ref)
+
+
+def test_getitem_fancy_bit_exact(cuda):
+    rng = np.random.RandomState(6)
+    x = rng.randn(50, 13).astype(np.float32)
+    y = rng.randint(0, 13, size=50)
+    got = cuda.getitem(up(cuda, x), (np.arange(50), y)).asnumpy()
+    assert np.array_equal(got, x[np.arange(50), y])
+    g = rng.randn(50).astype(np.float32)
+    ref = np.zeros_like(x)
+    np.add.at(ref, (np.arange(50), y), g)
+    assert np.array_equal(cuda.getitem_grad(up(cuda, x), (np.arange(50), y), up(cuda, g)).asnumpy(), ref)
+    rows = np.array([3, 3, 0, 49, -1, 7])
+    assert np.array_equal(cuda.getitem(up(cuda, x), rows).asnumpy(), x[rows])
+    g = rng.randint(-4, 5, size=(6, 13)).astype(np.float32)   # integers: accumulation order cannot matter
+    ref = np.zeros_like(x)
+    np.add.at(ref, rows, g)
+    assert np.array_equal(cuda.getitem_grad(up(cuda, x), rows, up(cuda, g)).asnumpy(), ref)
+
+
+@pytest.mark.parametrize('shape,axes', [((5, 7), None), ((64, 96), None), ((33, 65), (1, 0)), ((2, 3, 4), (2, 0, 1)),
+                                        ((4, 32, 48), (0, 2, 1)), ((2, 3, 4, 5), (3, 1, 0, 2))])
+def test_transpose_bit_exact(cuda, shape, axes):
+    x = np.random.RandomState(8).randn(*shape).astype(np.float32)
+    assert np.array_equal(cuda.transpose(up(cuda, x), axes).asnumpy(), np.transpose(x, axes))
+
+
+def test_concat_onehot_misc(cuda):
+    rng = np.random.RandomState(12)
+    a, b = rng.randn(4, 3, 5).astype(np.float32), rng.randn(4, 2, 5).astype(np.float32)
+    assert np.array_equal(cuda.concat2(up(cuda, a), up(cuda, b), 1).asnumpy(), np.append(a, b, axis=1))
+    y = rng.randint(0, 10, size=64)
+    out = cuda.zeros((64, 10))
+    cuda.onehot_encode(up(cuda, y), out)
+    ref = np.zeros((64, 10), dtype=np.float32)
+    ref[np.arange(64), y] = 1
+    assert np.array_equal(out.asnumpy(), ref)
+    assert np.array_equal(cuda.arange(10).asnumpy(), np.arange(10))
+    assert np.array_equal(cuda.full((3, 4), 2.5).asnumpy(), np.full((3, 4), 2.5, dtype=np.float32))
+
+
+@pytest.mark.parametrize('N,C,H,W,F,K,stride,pad', [(2, 3, 8, 8, 4, 3, 1, 1), (3, 3, 32, 32, 8, 3, 1, 1), (2, 3, 12, 12, 5, 7, 1, 0),
+                                                    (2, 4, 9, 9, 3, 3, 2, 1), (1, 8, 16, 16, 16, 3, 1, 1)])
+def test_conv_pool(cuda, N, C, H, W, F, K, stride, pad):
+    from minpy_b200.cuda_array import CudaArray
+    rng = np.random.RandomState(N * C + K)
+    x, w, b = rng.randn(N, C, H, W).astype(np.float32), rng.randn(F, C, K, K).astype(np.float32), rng.randn(F).astype(np.float32)
+    f64 = lambda v: v.astype(np.float64)
+    yref = orc.conv2d_fwd(f64(x), f64(w), f64(b), stride, pad)
+    OH, OW = yref.shape[2:]
+    lib = cuda.L()
+    xd, wd, bd = up(cuda, x), up(cuda, w), up(cuda, b)
+    y = CudaArray.empty((N, F, OH, OW))
+    lib.mc_conv2d_fwd(xd.ptr, wd.ptr, bd.ptr, y.ptr, N, C, H, W, F, K, K, stride, pad, 0, 0)
+    assert rel(y.asnumpy(), yref) <= 1e-5
+    dy = rng.randn(N, F, OH, OW).astype(np.float32)
+    dxr, dwr, dbr = orc.conv2d_bwd(f64(x), f64(w), f64(dy), stride, pad)
+    dyd = up(cuda, dy)
+    dx, dw, db = CudaArray.empty(x.shape), CudaArray.empty(w.shape), CudaArray.empty((F,))
+    lib.mc_conv2d_dgrad(dyd.ptr, wd.ptr, dx.ptr, N, C, H, W, F, K, K, stride, pad, 0)
+    lib.mc_conv2d_wgrad(xd.ptr, dyd.ptr, dw.ptr, db.ptr, N, C, H, W, F, K, K, stride, pad, 0)
+    assert rel(dx.asnumpy(), dxr) <= 1e-5 and rel(dw.asnumpy(), dwr) <= 1e-5 and rel(db.asnumpy(), dbr) <= 1e-5
+    pref, aref = orc.maxpool2d_fwd(f64(yref).astype(np.float32), 2, 2)
+    PH, PW = pref.shape[2:]
+    p, am = CudaArray.empty((N, F, PH, PW)), CudaArray.empty((N, F, PH, PW), np.dtype('int32'))
+    yd = up(cuda, yref.astype(np.float32))
+    lib.mc_maxpool2d_fwd(yd.ptr, p.ptr, am.ptr, N * F, OH, OW, 2, 2, 2)
+    assert np.array_equal(p.asnumpy(), pref) and np.array_equal(am.asnumpy(), aref)
+    dp = rng.randn(N, F, PH, PW).astype(np.float32)
+    dpool = cuda.zeros((N, F, OH, OW))
+    lib.mc_maxpool2d_bwd(up(cuda, dp).ptr, am.ptr, dpool.ptr, N * F, OH, OW, PH, PW)
+    assert np.array_equal(dpool.asnumpy(), orc.maxpool2d_bwd(dp, aref, (N, F, OH, OW)))
+
+
+def test_vjp_chain(cuda):
+    lib = cuda.L()
+    rng = np.random.RandomState(13)
+    n, d = 64, 48
+    g, a, b = rng.randn(n, d).astype(np.float32), (rng.rand(n, d) + 0.5).astype(np.float32), rng.randn(d).astype(np.float32)
+    acc = rng.randn(n, d).astype(np.float32)
+    gd, ad, bd, accd = up(cuda, g), up(cuda, a), up(cuda, b), up(cuda, acc)
+    E = lib.enums
+    steps = [(E['MC_VJP_MUL_A'], ad, 0, None, 0, 0.0, 1),            # g * a
+             (E['MC_VJP_MUL_A'], bd, 1, None, 0, 0.0, d),            # * row vector b
+             (E['MC_VJP_TANH_ANS'], ad, 0, None, 0, 0.0, 1),         # * (1 - a^2)
+             (E['MC_VJP_DIV_S'], None, 0, None, 0, 4.0, 1),          # / 4
+             (E['MC_VJP_NEG'], None, 0, None, 0, 0.0, 1)]
+    got = cuda.run_chain(gd, 1.0, steps, (n, d), acc=accd).asnumpy()
+    f = np.float64
+    ref = acc.astype(f) - g.astype(f) * a * b[None, :] * (1 - a.astype(f) ** 2) / 4
+    assert rel(got, ref) <= 1e-5
+    got = cuda.run_chain(None, 2.0, steps[:1], (n, d)).asnumpy()
+    assert rel(got, 2.0 * a) <= 1e-6
