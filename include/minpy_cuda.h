@@ -127,6 +127,7 @@ enum mc_vjp_op {
   MC_VJP_POW_Y,         /* g * log(a) * b           power rhs (a = x, b = ans)         */
   MC_VJP_RECIP_ANS,     /* -g * a * a               1/x (a = ans)                      */
   MC_VJP_GT0_A,         /* g * (a > 0)                                                  */
+  MC_VJP_GE0_A,         /* g * (a >= 0)             layers.relu: maximum(0,x) passes g at x == 0 */
   MC_VJP_COUNT
 };
 /* Operand addressing inside a step: how element i of the output maps to a / b. */

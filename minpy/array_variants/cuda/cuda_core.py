@@ -1,0 +1,722 @@
+"""Primitives and VJPs of the CUDA array variant.
+
+Plugs into the reference's variant interface (`register_primitives(reg, prim_wrapper)`,
+`def_grads(prims)`: minpy/array_variants/mxnet/mxnet_core.py:100-170 is the template) with
+functions that enqueue kernels of libminpy_cuda.so through `minpy_b200.ops`.
+
+Two things go beyond the template:
+
+* VJPs of elementwise primitives do not launch kernels.  They append a step to a lazy
+  `ChainGrad` recipe; the rewritten tape evaluates a whole run of them with one
+  `mc_vjp_chain` launch (minpy/tape.py, minpy_b200/lazy.py).
+* `fused_*` primitives (affine, relu, batchnorm, dropout, softmax loss, LSTM step,
+  optimizer updates) are whole-layer kernels that `minpy.nn.layers` / `minpy.nn.optim`
+  pick when they are bound in the namespace; their arithmetic restates the primitive
+  compositions of the reference's nn/layers.py and nn/optim.py (cited per function).
+"""
+from __future__ import absolute_import
+from __future__ import division
+
+import numpy as np
+
+from minpy_b200 import ops
+from minpy_b200._lib import parse_enums
+from minpy_b200.cuda_array import CudaArray
+from minpy_b200.lazy import ChainGrad, as_chain, concrete, FULL, ROW, COL, ONE
+
+E = parse_enums()
+_prod = ops._prod  # pylint: disable=protected-access
+
+
+def _is_arr(x):
+    return isinstance(x, CudaArray)
+
+
+def _shape(x):
+    return x.shape if _is_arr(x) else np.shape(x)
+
+
+# ======================================================================================
+#  operand addressing and un-broadcasting for chain steps
+# ======================================================================================
+def _opd(v, shape):
+    """How array `v` (broadcastable to `shape`) is addressed inside a chain over `shape`:
+    returns (array, mode, inner)."""
+    if v.dtype != ops._F32:  # pylint: disable=protected-access
+        v = v.astype(ops._F32)  # pylint: disable=protected-access
+    if v.shape == shape or v.size == _prod(shape):
+        return v, FULL, 1
+    if v.size == 1:
+        return v, ONE, 1
+    vs = (1,) * (len(shape) - v.ndim) + v.shape
+    k = len(shape)
+    while k > 0 and vs[k - 1] == shape[k - 1]:
+        k -= 1
+    if all(d == 1 for d in vs[:k]):                       # trailing block matches: row vector
+        return v, ROW, _prod(shape[k:])
+    k = 0
+    while k < len(shape) and vs[k] == shape[k]:
+        k += 1
+    if all(d == 1 for d in vs[k:]):                       # leading block matches: column vector
+        return v, COL, _prod(shape[k:])
+    return ops.broadcast_to(v, shape), FULL, 1
+
+
+def _fold(chain, operand):
+    """Gradient recipe in the broadcast shape -> gradient of `operand` (its own shape)."""
+    if _is_arr(operand):
+        if operand.shape == chain.shape:
+            return chain
+        return ops.unbroadcast(chain.materialize(), operand.shape)
+    return ops.reduce(E['MC_RED_SUM'], chain.materialize())    # scalar operand: sum everything
+
+
+def _step1(chain, op_arr, op_scalar, v, shape):
+    """Append `op_arr` with operand v (array) or `op_scalar` with scalar v."""
+    if _is_arr(v):
+        a, mode, inner = _opd(v, shape)
+        return chain.then(E[op_arr], a, mode, inner=inner)
+    return chain.then(E[op_scalar], scalar=float(v))
+
+
+def _step2(chain, op, a, b, shape, scalar=0.0):
+    a, am, ai = _opd(a, shape)
+    b, bm, bi = _opd(b, shape)
+    if am in (ROW, COL) and bm in (ROW, COL) and ai != bi:
+        b, bm, bi = ops.broadcast_to(b, shape), FULL, 1
+    inner = ai if am in (ROW, COL) else bi
+    return chain.then(E[op], a, am, b, bm, scalar, inner)
+
+
+def _binary_vjps(name):
+    """(d/dx maker, d/dy maker) for a broadcasting binary ufunc."""
+    def dx(ans, x, y):
+        shape = ans.shape
+
+        def vjp(g):
+            c = as_chain(g, shape)
+            if name in ('add', 'subtract', 'mod'):
+                pass
+            elif name == 'multiply':
+                c = _step1(c, 'MC_VJP_MUL_A', 'MC_VJP_MUL_S', y, shape)
+            elif name in ('divide', 'true_divide'):
+                c = _step1(c, 'MC_VJP_DIV_A', 'MC_VJP_DIV_S', y, shape)
+            elif name == 'power':
+                # g * y * x^(y-1): the MXNet variant's form (mxnet_core.py:160-162), finite at
+                # x == 0 where the NumPy variant's g*y*ans/x is NaN
+                if _is_arr(y):
+                    c = _step2(c, 'MC_VJP_POW_X', x, y, shape)
+                else:
+                    a, mode, inner = _opd(x, shape)
+                    c = c.then(E['MC_VJP_POW_XS'], a, mode, scalar=float(y), inner=inner)
+            elif name in ('maximum', 'minimum'):
+                c = _step2(c, 'MC_VJP_EQ_AB', x, ans, shape)
+            return _fold(c, x)
+        return vjp
+
+    def dy(ans, x, y):
+        shape = ans.shape
+
+        def vjp(g):
+            c = as_chain(g, shape)
+            if name == 'add':
+                pass
+            elif name == 'subtract':
+                c = c.then(E['MC_VJP_NEG'])
+            elif name == 'multiply':
+                c = _step1(c, 'MC_VJP_MUL_A', 'MC_VJP_MUL_S', x, shape)
+            elif name in ('divide', 'true_divide'):
+                if _is_arr(x):
+                    c = _step2(c, 'MC_VJP_DIV_Y', x, y, shape)
+                else:
+                    a, mode, inner = _opd(y, shape)
+                    c = c.then(E['MC_VJP_S_DIV_Y'], a, mode, scalar=float(x), inner=inner)
+            elif name == 'mod':
+                q = ops.unary(E['MC_FLOOR'], ops.binary(E['MC_DIV'], x, y))
+                c = c.then(E['MC_VJP_MUL_A'], *_opd(q, shape)[:2]).then(E['MC_VJP_NEG'])
+            elif name == 'power':
+                if _is_arr(x):
+                    c = _step2(c, 'MC_VJP_POW_Y', x, ans, shape)
+                else:
+                    c = c.then(E['MC_VJP_POW_SY'], ans, FULL, scalar=float(x))
+            elif name in ('maximum', 'minimum'):
+                c = _step2(c, 'MC_VJP_EQ_AB', y, ans, shape)
+            return _fold(c, y)
+        return vjp
+    return dx, dy
+
+
+# unary: name -> (forward opcode, VJP step opcode or None for zero gradient, operand: 'x'|'ans'|None)
+_UNARY = {
+    'negative': ('MC_NEG', 'MC_VJP_NEG', None),
+    'abs': ('MC_ABS', 'MC_VJP_ABS_X', 'x'),
+    'absolute': ('MC_ABS', 'MC_VJP_ABS_X', 'x'),
+    'sign': ('MC_SIGN', None, None),
+    'round': ('MC_ROUND', None, None),
+    'ceil': ('MC_CEIL', None, None),
+    'floor': ('MC_FLOOR', None, None),
+    'sqrt': ('MC_SQRT', 'MC_VJP_SQRT_ANS', 'ans'),
+    'exp': ('MC_EXP', 'MC_VJP_MUL_A', 'ans'),
+    'log': ('MC_LOG', 'MC_VJP_DIV_A', 'x'),
+    'sin': ('MC_SIN', 'MC_VJP_SIN_X', 'x'),
+    'cos': ('MC_COS', 'MC_VJP_COS_X', 'x'),
+    'tanh': ('MC_TANH', 'MC_VJP_TANH_ANS', 'ans'),
+    'sigmoid': ('MC_SIGMOID', 'MC_VJP_SIGMOID_ANS', 'ans'),
+    'reciprocal': ('MC_RECIP', 'MC_VJP_RECIP_ANS', 'ans'),
+    'cosh': ('MC_COSH', None, None),
+    'logical_not': ('MC_LOGICAL_NOT', None, None),
+}
+
+_BINARY = {
+    'add': 'MC_ADD', 'subtract': 'MC_SUB', 'multiply': 'MC_MUL', 'divide': 'MC_DIV',
+    'true_divide': 'MC_DIV', 'power': 'MC_POW', 'maximum': 'MC_MAX', 'minimum': 'MC_MIN', 'mod': 'MC_MOD',
+}
+_COMPARE = {
+    'equal': 'MC_EQ', 'not_equal': 'MC_NE', 'less': 'MC_LT', 'greater': 'MC_GT',
+    'less_equal': 'MC_LE', 'greater_equal': 'MC_GE',
+}
+
+
+def _named(fn, name):
+    fn.__name__ = name
+    return fn
+
+
+def _make_unary(name, opcode):
+    def fwd(x):
+        if not _is_arr(x):
+            return getattr(np, name if name != 'sigmoid' else 'tanh')(x) if name != 'sigmoid' else 1.0 / (1.0 + np.exp(-x))
+        return ops.unary(E[opcode], x)
+    return _named(fwd, name)
+
+
+def _make_binary(name, opcode):
+    def fwd(x, y):
+        if not _is_arr(x) and not _is_arr(y):
+            return getattr(np, name)(x, y)               # scalar op scalar stays a host scalar
+        return ops.binary(E[opcode], x, y)
+    return _named(fwd, name)
+
+
+def square(x):
+    return ops.unary(E['MC_SQUARE'], x)
+
+
+# ======================================================================================
+#  reductions
+# ======================================================================================
+def _reduce_fn(name, opcode):
+    def fwd(x, axis=None, out=None, keepdims=False):
+        if out is not None:
+            raise ValueError('Out option is not supported.')
+        if not _is_arr(x):
+            return getattr(np, name)(x, axis=axis, keepdims=keepdims)
+        return ops.reduce(E[opcode], x, axis, keepdims)
+    return _named(fwd, name)
+
+
+def _single_run(shape, axis):
+    """(outer, red, inner) when the reduced axes are adjacent, else None."""
+    axes = ops._norm_axes(axis, len(shape))  # pylint: disable=protected-access
+    if not axes or list(axes) != list(range(axes[0], axes[-1] + 1)):
+        return None
+    return _prod(shape[:axes[0]]), _prod(shape[axes[0]:axes[-1] + 1]), _prod(shape[axes[-1] + 1:])
+
+
+def _sum_vjp(ans, x, axis=None, out=None, keepdims=False):  # pylint: disable=unused-argument
+    """Broadcast g back over the reduced axes (numpy_core.py:150-162) -- as an addressing mode
+    of the chain kernel when the layout allows, so it costs no pass of its own."""
+    xshape = x.shape
+
+    def vjp(g):
+        if isinstance(g, ChainGrad):
+            g = g.materialize()
+        if not _is_arr(g):
+            return ChainGrad(xshape, None, float(g))
+        if g.size == 1:
+            return ChainGrad(xshape, g, g_mode=ONE)
+        run = _single_run(xshape, axis)
+        if run is not None:
+            outer, red, inner = run
+            if outer == 1:
+                return ChainGrad(xshape, g, g_mode=ROW, g_inner=inner)
+            if inner == 1:
+                return ChainGrad(xshape, g, g_mode=COL, g_inner=red)
+        return ops.expand_reduced(g, xshape, axis, keepdims)
+    return vjp
+
+
+def _extremum_vjp(ans, x, axis=None, out=None, keepdims=False):  # pylint: disable=unused-argument
+    """g at every position equal to the extremum, ties included (numpy_core.py:66-70)."""
+    def vjp(g):
+        g = concrete(g, ans.shape)
+        return ops.select_grad(x, ans, g, axis, keepdims)
+    return vjp
+
+
+def argmax(x, axis=None, out=None):
+    if out is not None:
+        raise ValueError('Out option is not supported.')
+    return ops.argmax(x, axis)
+
+
+def mean(x, axis=None, keepdims=False):
+    s = ops.reduce(E['MC_RED_SUM'], x, axis, keepdims)
+    count = x.size // max(1, s.size)
+    return ops.binary(E['MC_MUL'], s, 1.0 / count)
+
+
+def count_nonzero(x, axis=None):
+    nz = ops.binary(E['MC_NE'], x, 0.0)
+    return ops.reduce(E['MC_RED_SUM'], nz, axis)
+
+
+# ======================================================================================
+#  shape ops, indexing, creation
+# ======================================================================================
+def reshape(x, shape, order='C'):
+    if order != 'C':
+        raise NotImplementedError('Orders other than C are not currently supported.')
+    if isinstance(shape, (int, np.integer)):
+        shape = (int(shape),)
+    return ops.as_cuda(x).reshape(tuple(shape))
+
+
+def _reshape_back(ans, x, *args, **kwargs):  # pylint: disable=unused-argument
+    xshape = x.shape
+
+    def vjp(g):
+        if isinstance(g, ChainGrad):
+            return g.reshaped(xshape)
+        if _is_arr(g):
+            return g.reshape(xshape)
+        return g
+    return vjp
+
+
+def transpose(x, axes=None):
+    return ops.transpose(x, axes)
+
+
+def _transpose_vjp(ans, x, axes=None):  # pylint: disable=unused-argument
+    inverse = None if axes is None else tuple(int(i) for i in np.argsort(axes))
+    return lambda g: ops.transpose(concrete(g, ans.shape), inverse)
+
+
+def expand_dims(x, axis):
+    return ops.expand_dims(x, axis)
+
+
+def squeeze(x, axis=None):
+    if axis is None:
+        shape = tuple(s for s in x.shape if s != 1)
+    else:
+        axes = ops._norm_axes(axis, x.ndim)  # pylint: disable=protected-access
+        shape = tuple(s for i, s in enumerate(x.shape) if i not in axes)
+    return x.reshape(shape)
+
+
+def ravel(x):
+    return x.reshape((x.size,))
+
+
+def broadcast_to(x, shape):
+    return ops.broadcast_to(x, shape)
+
+
+def append(arr, values, axis=None):
+    arr, values = ops.as_f32(arr), ops.as_f32(values)
+    if axis is None:
+        return ops.concat2(arr.reshape((arr.size,)), values.reshape((values.size,)), 0)
+    return ops.concat2(arr, values, axis)
+
+
+def _append_vjp(pos):
+    def maker(ans, arr, values, axis=None):
+        def vjp(g):
+            g = concrete(g, ans.shape)
+            if axis is None:
+                n = arr.size
+                piece = ops.getitem(g, slice(0, n) if pos == 0 else slice(n, None))
+                return piece.reshape((arr, values)[pos].shape)
+            ax = axis + ans.ndim if axis < 0 else axis
+            n = arr.shape[ax]
+            index = (slice(None),) * ax + ((slice(0, n) if pos == 0 else slice(n, None)),)
+            return ops.getitem(g, index)
+        return vjp
+    return maker
+
+
+def concatenate(arrays, axis=0):
+    arrays = [ops.as_f32(a) for a in arrays]
+    out = arrays[0]
+    for nxt in arrays[1:]:
+        out = ops.concat2(out, nxt, axis)
+    return out
+
+
+def stack(arrays, axis=0):
+    arrays = [ops.expand_dims(ops.as_f32(a), axis) for a in arrays]
+    return concatenate(arrays, axis)
+
+
+def _minpy_getitem(arr, index):
+    return ops.getitem(arr, index)
+
+
+def _getitem_vjp(ans, x, index):
+    return lambda g: ops.getitem_grad(x, index, concrete(g, ans.shape))
+
+
+def _shape_arg(shape, rest=()):
+    if isinstance(shape, (int, np.integer)):
+        return (int(shape),) + tuple(int(r) for r in rest)
+    return tuple(int(s) for s in shape)
+
+
+def zeros(shape, dtype=None, order='C'):  # pylint: disable=unused-argument
+    return ops.zeros(_shape_arg(shape))
+
+
+def ones(shape, dtype=None, order='C'):  # pylint: disable=unused-argument
+    return ops.full(_shape_arg(shape), 1.0)
+
+
+def empty(shape, dtype=None, order='C'):  # pylint: disable=unused-argument
+    return ops.empty(_shape_arg(shape))
+
+
+def full(shape, fill_value, dtype=None):  # pylint: disable=unused-argument
+    return ops.full(_shape_arg(shape), float(fill_value))
+
+
+def zeros_like(a, dtype=None):  # pylint: disable=unused-argument
+    return ops.zeros(_shape(a))
+
+
+def ones_like(a, dtype=None):  # pylint: disable=unused-argument
+    return ops.full(_shape(a), 1.0)
+
+
+def array(obj, dtype=None, copy=True):  # pylint: disable=unused-argument,redefined-outer-name
+    if _is_arr(obj):
+        return obj.copy()
+    return CudaArray.from_numpy(np.asarray(obj))
+
+
+def arange(*args, **kwargs):
+    return ops.arange(*args, **kwargs)
+
+
+def eye(n, m=None, k=0, dtype=None):  # pylint: disable=unused-argument
+    return CudaArray.from_numpy(np.eye(n, m, k, dtype=np.float32))
+
+
+# ======================================================================================
+#  dot, softmax_output, onehot_encode
+# ======================================================================================
+def dot(a, b):
+    return ops.dot(a, b)
+
+
+def _as2d(v, lead_is_row):
+    """1-D operands of dot as matrices: a (K,) -> (1,K); b (K,) -> (K,1)."""
+    if v.ndim == 1:
+        return v.reshape((1, v.shape[0]) if lead_is_row else (v.shape[0], 1))
+    if v.ndim > 2:
+        return v.reshape((_prod(v.shape[:-1]), v.shape[-1]))
+    return v
+
+
+def _dot_vjp_a(ans, a, b):
+    """dA = g . B^T (numpy_core.py:224)."""
+    def vjp(g):
+        if not _is_arr(b):
+            return _fold(as_chain(g, ans.shape).then(E['MC_VJP_MUL_S'], scalar=float(b)), a)
+        if not _is_arr(a):
+            return ops.reduce(E['MC_RED_SUM'], ops.binary(E['MC_MUL'], concrete(g, ans.shape), b))
+        gm = concrete(g, ans.shape)
+        a2, b2 = _as2d(a, True), _as2d(b, False)
+        g2 = gm.reshape((a2.shape[0], b2.shape[1]))
+        return ops.gemm(g2, b2, trans_b=True).reshape(a.shape)
+    return vjp
+
+
+def _dot_vjp_b(ans, a, b):
+    """dB = A^T . g (numpy_core.py:225)."""
+    def vjp(g):
+        if not _is_arr(a):
+            return _fold(as_chain(g, ans.shape).then(E['MC_VJP_MUL_S'], scalar=float(a)), b)
+        if not _is_arr(b):
+            return ops.reduce(E['MC_RED_SUM'], ops.binary(E['MC_MUL'], concrete(g, ans.shape), a))
+        gm = concrete(g, ans.shape)
+        a2, b2 = _as2d(a, True), _as2d(b, False)
+        g2 = gm.reshape((a2.shape[0], b2.shape[1]))
+        return ops.gemm(a2, g2, trans_a=True).reshape(b.shape)
+    return vjp
+
+
+def softmax_output(x, _label):
+    return ops.softmax_rows(x)
+
+
+def _softmax_output_vjp(ans, x, y):
+    """(p - y) / N; the upstream gradient is ignored, exactly as numpy_core.py:170-175."""
+    def vjp(_g):
+        out = CudaArray.empty(ans.shape)
+        if _is_arr(y) and y.ndim == 1:
+            ops.L().mc_softmax_ce_bwd(ans.ptr, ops.as_i32(y).ptr, None, out.ptr, ans.shape[0], ans.shape[1])
+        else:
+            ops.L().mc_softmax_ce_bwd(ans.ptr, None, ops.as_f32(y).ptr, out.ptr, ans.shape[0], ans.shape[1])
+        return out
+    return vjp
+
+
+def onehot_encode(indices, out):
+    return ops.onehot_encode(indices, out)
+
+
+# ======================================================================================
+#  fused layers (picked by minpy.nn.layers when bound)
+# ======================================================================================
+def fused_affine(x, w, b):
+    """dot(x, w) + b in one GEMM with a bias epilogue (nn/layers.py:27)."""
+    return ops.gemm(ops.as_f32(x), w, bias=b.reshape((b.size,)))
+
+
+def _affine_vjps():
+    def dx(ans, x, w, b):  # pylint: disable=unused-argument
+        return lambda g: ops.gemm(concrete(g, ans.shape), w, trans_b=True)
+
+    def dw(ans, x, w, b):  # pylint: disable=unused-argument
+        return lambda g: ops.gemm(ops.as_f32(x), concrete(g, ans.shape), trans_a=True)
+
+    def db(ans, x, w, b):  # pylint: disable=unused-argument
+        return lambda g: ops.reduce(E['MC_RED_SUM'], concrete(g, ans.shape), 0).reshape(b.shape)
+    return dx, dw, db
+
+
+def fused_relu(x):
+    """maximum(0, x) (nn/layers.py:41)."""
+    return ops.unary(E['MC_RELU'], x)
+
+
+def _relu_vjp(ans, x):
+    # g * (x == ans): passes g where x >= 0, including x == 0 (numpy_core.py:284-286)
+    return lambda g: as_chain(g, ans.shape).then(E['MC_VJP_GE0_A'], x, FULL)
+
+
+def fused_batchnorm(x, gamma, beta, running_mean, running_var, eps, momentum):
+    """Train-mode batchnorm of nn/layers.py:93-110 in two kernels: returns
+    (out, new_running_mean, new_running_var)."""
+    lib = ops.L()
+    N, D = x.shape
+    out = CudaArray.empty((N, D))
+    new_rm, new_rv = CudaArray.empty(running_mean.shape), CudaArray.empty(running_var.shape)
+    save_mean, save_invstd = CudaArray.empty((D,)), CudaArray.empty((D,))
+    lib.mc_batchnorm_train_fwd(x.ptr, gamma.ptr, beta.ptr, running_mean.ptr, running_var.ptr, out.ptr,
+                               new_rm.ptr, new_rv.ptr, save_mean.ptr, save_invstd.ptr, N, D, float(eps),
+                               float(momentum))
+    out._saved = (save_mean, save_invstd)  # pylint: disable=protected-access
+    return out, new_rm, new_rv
+
+
+def _batchnorm_vjp(ans, x, gamma, beta, running_mean, running_var, eps, momentum):  # pylint: disable=unused-argument
+    out = ans[0]
+    save_mean, save_invstd = out._saved  # pylint: disable=protected-access
+
+    def vjp(gs):
+        g = gs[0] if isinstance(gs, tuple) else gs
+        if g is None:
+            return [0.0, 0.0, 0.0]
+        g = concrete(g, out.shape)
+        N, D = x.shape
+        dx, dgamma, dbeta = CudaArray.empty((N, D)), CudaArray.empty(gamma.shape), CudaArray.empty(beta.shape)
+        ops.L().mc_batchnorm_train_bwd(x.ptr, g.ptr, gamma.ptr, save_mean.ptr, save_invstd.ptr, dx.ptr,
+                                       dgamma.ptr, dbeta.ptr, N, D)
+        return [dx, dgamma, dbeta]
+    return vjp
+
+
+def fused_batchnorm_test(x, gamma, beta, running_mean, running_var, eps):
+    """Test-mode batchnorm of nn/layers.py:111-113."""
+    N, D = x.shape
+    out = CudaArray.empty((N, D))
+    ops.L().mc_batchnorm_test_fwd(x.ptr, gamma.ptr, beta.ptr, running_mean.ptr, running_var.ptr, out.ptr, N, D,
+                                  float(eps))
+    return out
+
+
+def fused_dropout(x, prob, seed, offset):
+    """x * (u > prob), not rescaled (nn/layers.py:141-144); u from Philox(seed, offset)."""
+    out = CudaArray.empty(x.shape)
+    if x.size:
+        ops.L().mc_dropout(x.ptr, out.ptr, x.size, float(prob), int(seed), int(offset))
+    return out
+
+
+def _dropout_vjp(ans, x, prob, seed, offset):  # pylint: disable=unused-argument
+    def vjp(g):
+        g = concrete(g, ans.shape)
+        return fused_dropout(g, prob, seed, offset)      # same (seed, offset) => same mask
+    return vjp
+
+
+def fused_softmax_loss(x, label):
+    """softmax_loss of nn/layers.py:201-221 in one kernel: mean cross-entropy of row softmax;
+    `label` is (N,) class indices or (N, C) one-hot / soft targets."""
+    lib = ops.L()
+    rows, cols = x.shape
+    probs = CudaArray.empty((rows, cols))
+    loss = CudaArray.empty(())
+    if label.ndim == 1:
+        lab = ops.as_i32(label)
+        lib.mc_softmax_ce_fwd(x.ptr, lab.ptr, None, probs.ptr, loss.ptr, rows, cols)
+    else:
+        lab = ops.as_f32(label)
+        lib.mc_softmax_ce_fwd(x.ptr, None, lab.ptr, probs.ptr, loss.ptr, rows, cols)
+    loss._saved = (probs, lab)  # pylint: disable=protected-access
+    return loss
+
+
+def _softmax_loss_vjp(ans, x, label):  # pylint: disable=unused-argument
+    probs, lab = ans._saved  # pylint: disable=protected-access
+
+    def vjp(_g):
+        # (p - y) / N whatever the upstream gradient: the reference's softmax_output VJP
+        # discards it (numpy_core.py:170-175)
+        dx = CudaArray.empty(probs.shape)
+        if lab.ndim == 1:
+            ops.L().mc_softmax_ce_bwd(probs.ptr, lab.ptr, None, dx.ptr, probs.shape[0], probs.shape[1])
+        else:
+            ops.L().mc_softmax_ce_bwd(probs.ptr, None, lab.ptr, dx.ptr, probs.shape[0], probs.shape[1])
+        return dx
+    return vjp
+
+
+def fused_lstm_step(x, prev_h, prev_c, Wx, Wh, b):
+    """lstm_step of nn/layers.py:353-380: two GEMMs accumulated into one (N, 4H) buffer
+    (bias in the first epilogue) and one gate kernel."""
+    lib = ops.L()
+    N, H = prev_c.shape
+    a = ops.gemm(ops.as_f32(x), Wx, bias=b)
+    ops.gemm(prev_h, Wh, out=a, accumulate=True)
+    next_h, next_c, gates = CudaArray.empty((N, H)), CudaArray.empty((N, H)), CudaArray.empty((N, 4 * H))
+    lib.mc_lstm_cell_fwd(a.ptr, prev_c.ptr, next_h.ptr, next_c.ptr, gates.ptr, N, H)
+    next_h._saved = gates  # pylint: disable=protected-access
+    return next_h, next_c
+
+
+def _lstm_step_vjp(ans, x, prev_h, prev_c, Wx, Wh, b):
+    next_h, next_c = ans
+    gates = next_h._saved  # pylint: disable=protected-access
+
+    def vjp(gs):
+        dh, dc = gs
+        N, H = prev_c.shape
+        dh = concrete(dh, (N, H)) if dh is not None else ops.zeros((N, H))
+        dc = concrete(dc, (N, H)) if dc is not None else None
+        da, dprev_c = CudaArray.empty((N, 4 * H)), CudaArray.empty((N, H))
+        ops.L().mc_lstm_cell_bwd(gates.ptr, prev_c.ptr, next_c.ptr, dh.ptr, dc.ptr if dc is not None else None,
+                                 da.ptr, dprev_c.ptr, N, H)
+        xf = ops.as_f32(x)
+        return [ops.gemm(da, Wx, trans_b=True), ops.gemm(da, Wh, trans_b=True), dprev_c,
+                ops.gemm(xf, da, trans_a=True), ops.gemm(prev_h, da, trans_a=True),
+                ops.reduce(E['MC_RED_SUM'], da, 0).reshape(b.shape)]
+    return vjp
+
+
+# ---- optimizer updates (nn/optim.py:33-141), one kernel per parameter tensor ------------
+def fused_sgd(w, dw, lr):
+    out = CudaArray.empty(w.shape)
+    ops.L().mc_sgd(w.ptr, ops.as_f32(dw).ptr, out.ptr, float(lr), w.size)
+    return out
+
+
+def fused_sgd_momentum(w, dw, v, lr, momentum):
+    w_out, v_out = CudaArray.empty(w.shape), CudaArray.empty(w.shape)
+    ops.L().mc_sgd_momentum(w.ptr, ops.as_f32(dw).ptr, v.ptr, w_out.ptr, v_out.ptr, float(lr), float(momentum), w.size)
+    return w_out, v_out
+
+
+def fused_rmsprop(w, dw, cache, lr, decay, eps):
+    w_out, c_out = CudaArray.empty(w.shape), CudaArray.empty(w.shape)
+    ops.L().mc_rmsprop(w.ptr, ops.as_f32(dw).ptr, cache.ptr, w_out.ptr, c_out.ptr, float(lr), float(decay), float(eps),
+                       w.size)
+    return w_out, c_out
+
+
+def fused_adam(w, dw, m, v, lr, beta1, beta2, eps, t):
+    w_out, m_out, v_out = CudaArray.empty(w.shape), CudaArray.empty(w.shape), CudaArray.empty(w.shape)
+    ops.L().mc_adam(w.ptr, ops.as_f32(dw).ptr, m.ptr, v.ptr, w_out.ptr, m_out.ptr, v_out.ptr, float(lr), float(beta1),
+                    float(beta2), float(eps), int(t), w.size)
+    return w_out, m_out, v_out
+
+
+# ======================================================================================
+#  registration
+# ======================================================================================
+def register_primitives(reg, prim_wrapper):
+    for name, (opcode, _, _) in _UNARY.items():
+        reg.register(name, prim_wrapper(_make_unary(name, opcode)))
+    for name, opcode in list(_BINARY.items()) + list(_COMPARE.items()):
+        reg.register(name, prim_wrapper(_make_binary(name, opcode)))
+    reg.register('square', prim_wrapper(square))
+    for name, opcode in (('sum', 'MC_RED_SUM'), ('max', 'MC_RED_MAX'), ('amax', 'MC_RED_MAX'),
+                         ('min', 'MC_RED_MIN'), ('amin', 'MC_RED_MIN')):
+        reg.register(name, prim_wrapper(_reduce_fn(name, opcode)))
+    for fn in (argmax, mean, count_nonzero, reshape, transpose, expand_dims, squeeze, ravel, broadcast_to,
+               append, concatenate, stack, _minpy_getitem, zeros, ones, empty, full, zeros_like, ones_like,
+               array, arange, eye, dot, softmax_output, onehot_encode,
+               fused_affine, fused_relu, fused_batchnorm, fused_batchnorm_test, fused_dropout,
+               fused_softmax_loss, fused_lstm_step, fused_sgd, fused_sgd_momentum, fused_rmsprop, fused_adam):
+        reg.register(fn.__name__, prim_wrapper(fn))
+
+
+def def_grads(prims):
+    for name, (_, vjp_op, operand) in _UNARY.items():
+        if vjp_op is None:
+            if name in ('sign', 'round', 'ceil', 'floor'):
+                prims(name).def_grad_zero()
+            continue
+
+        def maker(ans, x, _op=vjp_op, _operand=operand):
+            src = {'x': x, 'ans': ans, None: None}[_operand]
+            return lambda g: as_chain(g, ans.shape).then(E[_op], src, FULL)
+        prims(name).def_grad(maker)
+    prims('square').def_grad(
+        lambda ans, x: lambda g: as_chain(g, ans.shape).then(E['MC_VJP_MUL_A'], x, FULL).then(
+            E['MC_VJP_MUL_S'], scalar=2.0))
+    for name in _BINARY:
+        dx, dy = _binary_vjps(name)
+        prims(name).def_grad(dx)
+        prims(name).def_grad(dy, argnum=1)
+
+    prims('sum').def_grad(_sum_vjp)
+    for name in ('max', 'amax', 'min', 'amin'):
+        prims(name).def_grad(_extremum_vjp)
+    prims('mean').def_grad(lambda ans, x, axis=None, keepdims=False: (
+        lambda g: as_chain(_sum_vjp(ans, x, axis, None, keepdims)(g), x.shape).then(
+            E['MC_VJP_MUL_S'], scalar=float(max(1, ans.size)) / max(1, x.size))))
+
+    for name in ('reshape', 'expand_dims', 'squeeze', 'ravel'):
+        prims(name).def_grad(_reshape_back)
+    prims('transpose').def_grad(_transpose_vjp)
+    prims('broadcast_to').def_grad(
+        lambda ans, x, shape: lambda g: ops.unbroadcast(concrete(g, ans.shape), x.shape))
+    prims('append').def_grad(_append_vjp(0))
+    prims('append').def_grad(_append_vjp(1), argnum=1)
+    prims('_minpy_getitem').def_grad(_getitem_vjp)
+
+    prims('dot').def_grad(_dot_vjp_a)
+    prims('dot').def_grad(_dot_vjp_b, argnum=1)
+    prims('softmax_output').def_grad(_softmax_output_vjp)
+
+    dx, dw, db = _affine_vjps()
+    prims('fused_affine').def_grad(dx).def_grad(dw, argnum=1).def_grad(db, argnum=2)
+    prims('fused_relu').def_grad(_relu_vjp)
+    prims('fused_batchnorm').def_multiple_grad(_batchnorm_vjp, (0, 1, 2))
+    prims('fused_batchnorm').def_grad_zero(3).def_grad_zero(4)
+    prims('fused_dropout').def_grad(_dropout_vjp)
+    prims('fused_softmax_loss').def_grad(_softmax_loss_vjp)
+    prims('fused_lstm_step').def_multiple_grad(_lstm_step_vjp, (0, 1, 2, 3, 4, 5))

@@ -1,0 +1,173 @@
+"""`Solver`: the training loop (reference: minpy/nn/solver.py:12-307, after cs231n).
+
+One `_step` = forward + tape backward over every parameter (`core.grad_and_loss`) + one update
+rule call per parameter.  New here: when a data-parallel process group is initialised
+(`minpy_b200.parallel`), the tape-produced gradients are averaged across ranks with one NCCL
+all-reduce over a flat buffer between the backward pass and the updates -- the place the
+reference leaves open between solver.py:184 and :190.
+"""
+from __future__ import division
+from __future__ import absolute_import
+from __future__ import print_function
+
+import time
+
+import minpy.numpy as np
+from minpy import core
+from minpy.nn import optim, init
+
+# pylint: disable=no-member, too-many-instance-attributes
+
+
+class Solver(object):
+    """Trains a `ModelBase` with mini-batch gradient descent.
+
+    Solver(model, train_dataiter, test_dataiter, task_type='classification', init_rule='xavier',
+           init_config={}, update_rule='sgd', optim_config={}, lr_decay=1.0, num_epochs=10,
+           train_acc_num_samples=1000, print_every=10, verbose=True)
+
+    After `init()` and `train()`, `model.params` holds the parameters with the best validation
+    score; `loss_history`, `train_acc_history`, `val_acc_history` hold the curves.
+    """
+
+    _DEFAULTS = (('task_type', 'classification'), ('init_rule', 'xavier'), ('init_config', {}),
+                 ('update_rule', 'sgd'), ('optim_config', {}), ('lr_decay', 1.0), ('num_epochs', 10),
+                 ('train_acc_num_samples', 1000), ('print_every', 10), ('verbose', True))
+
+    def __init__(self, model, train_dataiter, test_dataiter, **kwargs):
+        self.model = model
+        self.train_dataiter = train_dataiter
+        self.test_dataiter = test_dataiter
+        for key, default in self._DEFAULTS:
+            value = kwargs.pop(key, default)
+            setattr(self, key, dict(value) if isinstance(default, dict) else value)
+        if kwargs:
+            raise ValueError('Unrecognized arguments %s' % ', '.join('"%s"' % k for k in kwargs))
+        if not hasattr(optim, self.update_rule):
+            raise ValueError('Invalid update_rule "%s"' % self.update_rule)
+        self.update_rule = getattr(optim, self.update_rule)
+        self._reset()
+
+    def _reset(self):
+        """Clear histories and give every parameter its own optimizer / initializer config."""
+        self.epoch = 0
+        self.best_val_acc = 0
+        self.best_params = {}
+        self.loss_history = []
+        self.train_acc_history = []
+        self.val_acc_history = []
+        self._reset_data_iterators()
+        self.optim_configs = dict((p, dict(self.optim_config)) for p in self.model.param_configs)
+        self.init_rules = {}
+        self.init_configs = {}
+        for p, pconfig in self.model.param_configs.items():
+            if 'init_rule' in pconfig:
+                rule, config = pconfig['init_rule'], pconfig.get('init_config', {})
+            else:
+                rule, config = self.init_rule, dict(self.init_config)
+            if not hasattr(init, rule):
+                raise ValueError('Invalid init_rule "%s"' % rule)
+            self.init_rules[p] = getattr(init, rule)
+            self.init_configs[p] = config
+
+    def _reset_data_iterators(self):
+        if self.train_dataiter:
+            self.train_dataiter.reset()
+        if self.test_dataiter:
+            self.test_dataiter.reset()
+
+    def init(self):
+        """Create the parameters from their init rules (and copy the auxiliary ones)."""
+        for name, config in self.model.param_configs.items():
+            self.model.params[name] = self.init_rules[name](config['shape'], self.init_configs[name])
+        for name, value in self.model.aux_param_configs.items():
+            self.model.aux_params[name] = value
+        self._sync_initial_params()
+
+    def _sync_initial_params(self):
+        """Data parallel: every rank starts from rank 0's parameters."""
+        from minpy_b200 import parallel
+        if parallel.world_size() > 1:
+            parallel.broadcast_params(self.model.params)
+
+    def _step(self, batch):
+        """One gradient update on `batch`."""
+        def loss_func(*_params):
+            # the parameters are read from self.model.params by the model; passing them as
+            # arguments is what puts them on the tape
+            predict = self.model.forward_batch(batch, mode='train')
+            return self.model.loss_batch(batch, predict)
+
+        names = list(self.model.params.keys())
+        values = [self.model.params[k] for k in names]
+        grads, loss = core.grad_and_loss(loss_func, argnum=range(len(values)))(*values)
+        if len(values) == 1:
+            grads = [grads]
+
+        from minpy_b200 import parallel
+        if parallel.world_size() > 1:
+            grads = parallel.allreduce_mean(grads)
+
+        self.loss_history.append(loss.asnumpy() if hasattr(loss, 'asnumpy') else loss)
+        for name, dw in zip(names, grads):
+            next_w, next_config = self.update_rule(self.model.params[name], dw, self.optim_configs[name])
+            self.model.params[name] = next_w
+            self.optim_configs[name] = next_config
+
+    def check_accuracy(self, dataiter, num_samples=None):
+        """Classification: fraction of correct arg-max predictions; regression: mean loss.
+        With `num_samples`, a random sub-iterator of that many rows is scored instead."""
+        check = dataiter
+        if num_samples is not None and dataiter.num_data > num_samples:
+            check = dataiter.getsubiter(num_samples)
+        else:
+            check.reset()
+        if self.task_type == 'classification':
+            correct, seen = 0, 0
+            for batch in check:
+                predict = self.model.forward_batch(batch, mode='test')
+                correct = correct + np.sum(np.argmax(predict, axis=1) == batch.label[0])
+                seen += check.batch_size      # padded rows are counted too, as in the reference (:232)
+            correct = correct.asnumpy() if hasattr(correct, 'asnumpy') else correct
+            return float(correct) / seen
+        if self.task_type == 'regression':
+            total, batches = 0, 0
+            for batch in check:
+                predict = self.model.forward_batch(batch, mode='test')
+                total = total + self.model.loss(predict, batch.label[0])
+                batches += 1
+            total = total.asnumpy() if hasattr(total, 'asnumpy') else total
+            return float(total) / batches
+        raise ValueError('Task type is either classification or regression.')
+
+    def train(self):
+        """Run `num_epochs` epochs; score on (a sample of) the training set and on the test set
+        after each; decay the learning rate; keep the best parameters."""
+        num_iterations = self.train_dataiter.getnumiterations() * self.num_epochs
+        t = 0
+        for epoch in range(self.num_epochs):
+            start = time.time()
+            self.epoch = epoch + 1
+            for batch in self.train_dataiter:
+                self._step(batch)
+                if self.verbose and t % self.print_every == 0:
+                    print('(Iteration %d / %d) loss: %f' % (t + 1, num_iterations, self.loss_history[-1]))
+                t += 1
+            train_acc = self.check_accuracy(self.train_dataiter, num_samples=self.train_acc_num_samples)
+            val_acc = self.check_accuracy(self.test_dataiter)
+            self.train_acc_history.append(train_acc)
+            self.val_acc_history.append(val_acc)
+            self._reset_data_iterators()
+            if self.verbose:
+                if self.task_type not in ('classification', 'regression'):
+                    raise ValueError('task_type is not supported.')
+                what = 'acc' if self.task_type == 'classification' else 'loss'
+                print('(Epoch {} / {}) train {}: {}, val {}: {}, time: {}.'.format(
+                    self.epoch, self.num_epochs, what, train_acc, what, val_acc, time.time() - start))
+            if val_acc > self.best_val_acc:
+                self.best_val_acc = val_acc
+                # references, not copies: updates rebind parameters, they never write in place
+                self.best_params = dict(self.model.params)
+            for config in self.optim_configs.values():
+                config['learning_rate'] *= self.lr_decay
+        self.model.params = self.best_params

@@ -374,6 +374,7 @@ __device__ __forceinline__ float vjp_factor(int op, float g, float a, float b, f
     case MC_VJP_POW_Y: return g * logf(a) * b;
     case MC_VJP_RECIP_ANS: return -g * a * a;
     case MC_VJP_GT0_A: return (a > 0.f) ? g : g * 0.f;
+    case MC_VJP_GE0_A: return (a >= 0.f) ? g : g * 0.f;
     default: return g;
   }
 }

@@ -61,7 +61,7 @@ def _prod(shape):
 
 class CudaArray(object):
     """Dense row-major device array (float32 / int32 / int64)."""
-    __slots__ = ('buf', 'ptr', 'shape', 'size', 'dtype', '__weakref__')
+    __slots__ = ('buf', 'ptr', 'shape', 'size', 'dtype', '_saved', '_tag', '__weakref__')
     __array_priority__ = 200.0
 
     def __init__(self, buf, ptr, shape, dtype=_F32):
@@ -70,6 +70,8 @@ class CudaArray(object):
         self.shape = shape
         self.size = _prod(shape)
         self.dtype = dtype
+        self._saved = None    # forward state a fused primitive keeps for its VJP
+        self._tag = None      # ('arange', n) for index vectors known to be 0..n-1
 
     # ---- construction -------------------------------------------------------------
     @staticmethod

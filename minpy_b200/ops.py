@@ -94,7 +94,9 @@ def arange(start, stop=None, step=1, dtype=None):
     if n:
         L().mc_arange(out.ptr, float(start), float(step), n)
     if integral and dtype is None or (dtype is not None and np.dtype(dtype).kind in 'iu'):
-        return out.astype(_I32)
+        out = out.astype(_I32)
+    if start == 0 and step == 1:
+        out._tag = ('arange', n)
     return out
 
 
@@ -481,6 +483,8 @@ def _is_arange(a, n):
     if isinstance(a, CudaArray):
         if a.shape != (n,):
             return False
+        if a._tag is not None:
+            return a._tag == ('arange', n)
         a = a.asnumpy()
     a = np.asarray(a)
     return a.shape == (n,) and a.dtype.kind in 'iuf' and np.array_equal(a, np.arange(n))
@@ -615,34 +619,33 @@ def onehot_encode(indices, out):
 
 
 # ------------------------------------------------------------------ VJP chain ------
-def run_chain(g, g_scalar, steps, shape, acc=None):
-    """out = (acc or 0) + g * prod_k f_k, elementwise over `shape`, in ONE kernel.
+def run_chain(g, g_scalar, steps, shape, acc=None, g_mode=None, g_inner=1):
+    """out = (acc or 0) + g * g_scalar * prod_k f_k, elementwise over `shape`, in ONE kernel
+    (one per 12 steps for longer recipes).
 
-    `g` is a CudaArray (same shape, or () / broadcastable row/col handled by the caller) or
-    None (then `g_scalar` seeds the chain); `steps` is a list of tuples
-    (op, a, a_mode, b, b_mode, scalar, inner)."""
+    `g` is a CudaArray addressed by `g_mode` (FULL / ROW / COL / ONE; default FULL, or ONE
+    when g has a single element) or None (then `g_scalar` alone seeds the chain); `steps` is
+    a list of tuples (op, a, a_mode, b, b_mode, scalar, inner)."""
     lib = L()
     out = CudaArray.empty(shape)
     n = out.size
     if n == 0:
         return out
-    for start in range(0, max(1, len(steps)), 12):
-        chunk = steps[start:start + 12]
+    if g is not None and g_mode is None:
+        g_mode = 0 if g.size == n else 3
+    nchunks = max(1, (len(steps) + 11) // 12)
+    for c in range(nchunks):
+        chunk = steps[c * 12:(c + 1) * 12]
         arr = (VjpStep * max(1, len(chunk)))()
         for i, (op, a, am, b, bm, s, inner) in enumerate(chunk):
             arr[i].op, arr[i].a_mode, arr[i].b_mode, arr[i].scalar = op, am, bm, s
             arr[i].a = a.ptr if a is not None else None
             arr[i].b = b.ptr if b is not None else None
             arr[i].inner = inner
-        last = start + 12 >= len(steps)
-        if g is None:
-            gptr, gmode = None, 0
-        else:
-            gptr = g.ptr
-            gmode = 0 if g.size == n else 3  # FULL or ONE (0-d / size-1 gradient)
-        lib.mc_vjp_chain(gptr, gmode, 1, float(g_scalar), acc.ptr if (acc is not None and last) else None,
-                         arr, len(chunk), out.ptr, n)
-        g, g_scalar = out, 1.0
+        last = c == nchunks - 1
+        lib.mc_vjp_chain(g.ptr if g is not None else None, g_mode or 0, g_inner, float(g_scalar),
+                         acc.ptr if (acc is not None and last) else None, arr, len(chunk), out.ptr, n)
         if not last:
+            g, g_scalar, g_mode, g_inner = out, 1.0, 0, 1
             out = CudaArray.empty(shape)
     return out
