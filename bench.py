@@ -1,0 +1,606 @@
+#!/usr/bin/env python
+"""bench.py -- training samples/sec of the MinPy hot path on the B200 `cuda` array variant.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload mlp_c3|mlp_c1|lstm_c5]
+                    [--impl b200|reference] [--no-ufunc] [--no-cpu-baseline]
+
+One "step" is one `Solver._step` (forward + tape backward + gradient all-reduce when N > 1 +
+one update rule call per parameter) over one minibatch of synthetic CIFAR-shaped data.  Rank 0
+prints ONE JSON line (contract: see DESIGN.md "Measurement").
+
+* `value`  : samples/s with the batches already resident in HBM, CUDA events on the library's
+             stream, barrier + synchronize on both sides, max over ranks.
+* `e2e`    : the same loop fed from PINNED HOST memory through `NDArrayIter` (one H2D copy of
+             the batch per step) and reading the loss back every step (D2H).
+* `roofline`: the dominant kernel family of the step, timed with CUDA events around every
+             launch in a second, instrumented pass of the same steps.
+* `ufunc`  : GB/s of the elementwise / broadcast / reduction kernels (BASELINE config 2).
+* `cpu_baseline`: the NumPy oracle port of the reference's path, timed on this box's cores.
+
+`--impl reference` times the reference's CPU path (the oracle port, float64 as the
+reference's NumPy variant computes) on the same workload and prints the same line shape.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = 'training samples/sec'
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------ clocks ----
+class ClockSampler(object):
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+
+    FIELDS = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, device):
+        self.device = device
+        self.samples = []
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.device), '--query-gpu=' + self.FIELDS, '--format=csv,noheader,nounits',
+                 '-lms', '100'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(',')]
+            if len(parts) >= 6:
+                self.samples.append(parts)
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:  # pylint: disable=broad-except
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for parts in self.samples:
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for name, flag in zip(names, parts[2:6]):
+                if flag.lower().startswith('active'):
+                    reasons.add(name)
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+# --------------------------------------------------------------------- per-call timing ----
+class CallTimer(object):
+    """CUDA-event pair around every library call (installed on the ctypes binding) so that the
+    kernel families of one step can be ranked and the dominant one put on the roofline."""
+
+    def __init__(self, lib):
+        self.lib = lib
+        self.records = []          # (name, start_event, stop_event, work) ; work = (flops, bytes)
+        self.pool = []
+
+    def _event(self):
+        if self.pool:
+            return self.pool.pop()
+        ev = ctypes.c_void_p()
+        self.lib.mc_event_create(ctypes.byref(ev))
+        return ev
+
+    def install(self):
+        lib = self.lib
+        self.saved = {}
+        skip = ('mc_event', 'mc_alloc', 'mc_free', 'mc_sync', 'mc_launch_count', 'mc_last_error', 'mc_get', 'mc_set',
+                'mc_init', 'mc_host', 'mc_mem_info', 'mc_device_count', 'mc_sm_count', 'mc_graph', 'mc_gemm_last_path')
+        for name in lib.decls:
+            if name.startswith(skip):
+                continue
+            fn = getattr(lib, name)
+            self.saved[name] = fn
+            setattr(lib, name, self._wrap(name, fn))
+
+    def _wrap(self, name, fn):
+        def call(*args):
+            e0, e1 = self._event(), self._event()
+            self.lib.mc_event_record(e0)
+            fn(*args)
+            self.lib.mc_event_record(e1)
+            self.records.append((name, e0, e1, _work_of(name, args)))
+        return call
+
+    def uninstall(self):
+        for name, fn in self.saved.items():
+            setattr(self.lib, name, fn)
+
+    def summary(self):
+        self.lib.mc_sync()
+        fam = {}
+        ms = ctypes.c_float()
+        for name, e0, e1, work in self.records:
+            self.lib.mc_event_elapsed_ms(e0, e1, ctypes.byref(ms))
+            key = name if name != 'mc_gemm' else 'mc_gemm'
+            f = fam.setdefault(key, {'calls': 0, 'ms': 0.0, 'flops': 0.0, 'bytes': 0.0})
+            f['calls'] += 1
+            f['ms'] += ms.value
+            f['flops'] += work[0]
+            f['bytes'] += work[1]
+            self.pool.extend((e0, e1))
+        self.records = []
+        return fam
+
+
+def _i(v):
+    return int(v.value) if hasattr(v, 'value') else int(v)
+
+
+def _work_of(name, a):
+    """(algorithmic flops, algorithmic bytes) of one library call: compulsory traffic, every
+    input read once and every output written once."""
+    try:
+        if name == 'mc_gemm':
+            M, N, K = _i(a[2]), _i(a[3]), _i(a[4])
+            return 2.0 * M * N * K, 4.0 * (M * K + K * N + M * N)
+        if name == 'mc_unary':
+            return 0.0, 8.0 * _i(a[3])
+        if name == 'mc_binary':
+            return 0.0, 12.0 * _i(a[4])
+        if name == 'mc_binary_scalar':
+            return 0.0, 8.0 * _i(a[5])
+        if name == 'mc_binary_vec':
+            return 0.0, 8.0 * _i(a[6]) * _i(a[7])
+        if name == 'mc_reduce':
+            return 0.0, 4.0 * (_i(a[3]) * _i(a[4]) * _i(a[5]) + _i(a[3]) * _i(a[5]))
+        if name == 'mc_batchnorm_train_fwd':
+            N, D = _i(a[10]), _i(a[11])
+            return 0.0, 4.0 * (2 * N * D + 6 * D)
+        if name == 'mc_batchnorm_train_bwd':
+            N, D = _i(a[8]), _i(a[9])
+            return 0.0, 4.0 * (3 * N * D + 4 * D)
+        if name == 'mc_dropout':
+            return 0.0, 8.0 * _i(a[2])
+        if name == 'mc_vjp_chain':
+            return 0.0, 8.0 * _i(a[8])
+        if name in ('mc_softmax_ce_fwd', 'mc_softmax_ce_bwd', 'mc_softmax_rows'):
+            r, c = _i(a[-2]), _i(a[-1])
+            return 0.0, 8.0 * r * c
+        if name == 'mc_sgd_momentum':
+            return 0.0, 20.0 * _i(a[7])
+        if name == 'mc_adam':
+            return 0.0, 28.0 * _i(a[12])
+        if name in ('mc_memcpy_d2d', 'mc_memset'):
+            return 0.0, (2.0 if name == 'mc_memcpy_d2d' else 1.0) * _i(a[2])
+        if name == 'mc_lstm_cell_fwd':
+            N, H = _i(a[5]), _i(a[6])
+            return 0.0, 4.0 * N * H * (4 + 1 + 2 + 4)
+        if name == 'mc_lstm_cell_bwd':
+            N, H = _i(a[7]), _i(a[8])
+            return 0.0, 4.0 * N * H * (4 + 2 + 2 + 4 + 1)
+    except Exception:  # pylint: disable=broad-except
+        pass
+    return 0.0, 0.0
+
+
+# ---------------------------------------------------------------------------- peaks -------
+def measured_peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {'hbm_gbs': p['hbm_gbs'], 'bf16_tflops': p['bf16_tflops'],
+                'bf16_tflops_sustained': p.get('bf16_tflops_sustained', p['bf16_tflops']), 'source': 'measured'}
+    return {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0, 'source': 'fallback'}
+
+
+# ---------------------------------------------------------------- the b200 training arm ----
+def pinned_array(lib, shape, dtype):
+    """NumPy array over pinned host memory from the library (kept alive by the returned base)."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape))
+    p = ctypes.c_void_p()
+    lib.mc_host_alloc(ctypes.byref(p), n * dtype.itemsize)
+    buf = (ctypes.c_char * (n * dtype.itemsize)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+    return arr
+
+
+def build_solver(workload, train_iter):
+    from minpy.nn.solver import Solver
+    from minpy_b200 import workloads
+    factory, _, rule, optim_config, _, _ = workloads.WORKLOADS[workload]
+    model = factory()
+    solver = Solver(model, train_iter, train_iter, update_rule=rule, optim_config=dict(optim_config),
+                    init_rule='gaussian', init_config={'stdvar': 0.01}, verbose=False)
+    solver.init()
+    return model, solver
+
+
+def run_b200(args):
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    import minpy.numpy as mnp
+    from minpy import array as marray
+    from minpy.nn.io import NDArrayIter, DataBatch
+    from minpy_b200 import parallel, workloads
+    from minpy_b200._lib import get_lib
+    from minpy_b200.cuda_array import ensure_device, CudaArray
+
+    world = parallel.init()
+    rank = parallel.rank()
+    if world != args.gpus:
+        log('note: --gpus %d but WORLD_SIZE=%d; using WORLD_SIZE' % (args.gpus, world))
+    device = ensure_device()
+    lib = get_lib()
+    _, batch, _, _, make_data, desc = workloads.WORKLOADS[args.workload]
+
+    # distinct batches per rank: more bytes than the 126 MB L2 so that no step re-reads its
+    # inputs from cache (weights stay L2-resident, as they do in real training)
+    nbatch = args.pool
+    X, Y = make_data(batch * nbatch, seed=100 + rank)
+    in_bytes = X[:batch].nbytes + Y[:batch].nbytes
+    Xp = pinned_array(lib, X.shape, X.dtype)
+    Yp = pinned_array(lib, Y.shape, Y.dtype)
+    Xp[...] = X
+    Yp[...] = Y
+    host_iter = NDArrayIter(Xp, Yp, batch_size=batch, shuffle=False, num_parts=1, part_index=0)
+    model, solver = build_solver(args.workload, host_iter)
+
+    # device-resident batches for the kernel-only leg
+    dev_batches = []
+    for i in range(nbatch):
+        xb = marray.wrap(CudaArray.from_numpy(X[i * batch:(i + 1) * batch]))
+        yb = marray.wrap(CudaArray.from_numpy(Y[i * batch:(i + 1) * batch]))
+        dev_batches.append(DataBatch([xb], [yb], pad=0, index=i))
+    lib.mc_sync()
+
+    def host_batches():
+        while True:
+            host_iter.reset()
+            for b in host_iter:
+                yield b
+    hb = host_batches()
+
+    def step_device(i):
+        solver._step(dev_batches[i % nbatch])  # pylint: disable=protected-access
+
+    def step_e2e(_i):
+        solver._step(next(hb))  # pylint: disable=protected-access
+        return float(solver.loss_history[-1])          # D2H read of the step's result
+
+    def timed(step_fn, steps, warmup):
+        for i in range(warmup):
+            step_fn(i)
+        solver.loss_history = []
+        lib.mc_sync()
+        parallel.barrier()
+        lib.mc_sync()
+        e0, e1 = ctypes.c_void_p(), ctypes.c_void_p()
+        lib.mc_event_create(ctypes.byref(e0))
+        lib.mc_event_create(ctypes.byref(e1))
+        n0, n1 = ctypes.c_uint64(), ctypes.c_uint64()
+        lib.mc_launch_count(ctypes.byref(n0))
+        t0 = time.perf_counter()
+        lib.mc_event_record(e0)
+        for i in range(steps):
+            step_fn(warmup + i)
+        lib.mc_event_record(e1)
+        lib.mc_sync()
+        parallel.barrier()
+        wall = time.perf_counter() - t0
+        lib.mc_launch_count(ctypes.byref(n1))
+        ms = ctypes.c_float()
+        lib.mc_event_elapsed_ms(e0, e1, ctypes.byref(ms))
+        return parallel.max_over_ranks(ms.value), n1.value - n0.value, parallel.max_over_ranks(wall * 1e3)
+
+    sampler = ClockSampler(device)
+    if rank == 0:
+        sampler.start()
+    dev_ms, launches, dev_wall = timed(step_device, args.steps, args.warmup)
+    e2e_ms, _, e2e_wall = timed(step_e2e, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    last_loss = float(solver.loss_history[-1])
+
+    # instrumented pass: event pair around every library call of the same steps
+    timer = CallTimer(lib)
+    timer.install()
+    try:
+        for i in range(min(args.steps, 20)):
+            step_device(i)
+        fam = timer.summary()
+    finally:
+        timer.uninstall()
+    inst_steps = min(args.steps, 20)
+
+    total_samples = batch * world * args.steps
+    value = total_samples / (dev_ms * 1e-3)
+    e2e_value = total_samples / (e2e_ms * 1e-3)
+    peaks = measured_peaks()
+
+    out = None
+    if rank == 0:
+        tot = sum(f['ms'] for f in fam.values()) or 1.0
+        ranked = sorted(fam.items(), key=lambda kv: -kv[1]['ms'])
+        log('kernel families over %d instrumented steps (event time, share of summed kernel time):' % inst_steps)
+        for name, f in ranked[:14]:
+            log('  %-26s calls/step %6.1f  us/call %8.2f  share %5.1f%%  %8.1f GB/s  %8.2f TFLOP/s' % (
+                name, f['calls'] / inst_steps, 1e3 * f['ms'] / f['calls'], 100 * f['ms'] / tot,
+                f['bytes'] / (f['ms'] * 1e-3) / 1e9 if f['ms'] else 0, f['flops'] / (f['ms'] * 1e-3) / 1e12 if f['ms'] else 0))
+        top_name, top = ranked[0]
+        if top['flops'] > 0:
+            # TF32 runs at half the bf16 tensor rate; the denominator is still the measured bf16
+            # cuBLAS figure (sustained: the kernel is timed inside a long step) as the recipe asks
+            ai = top['flops'] / max(1.0, top['bytes'])
+            achieved = top['flops'] / (top['ms'] * 1e-3) / 1e12
+            peak = peaks['bf16_tflops_sustained']
+            roofline = {'kernel': top_name + ' (tcgen05 kind::tf32)', 'bound': 'tensor', 'achieved': round(achieved, 2),
+                        'peak': peak, 'unit': 'TFLOP/s', 'frac': round(achieved / peak, 4), 'traffic': None,
+                        'peak_source': peaks['source'] + ' bf16 cuBLAS sustained; tf32 nominal rate is half of bf16',
+                        'avg_us_per_launch': round(1e3 * top['ms'] / top['calls'], 2),
+                        'share_of_kernel_time': round(top['ms'] / tot, 3),
+                        'arith_intensity_flop_per_byte': round(ai, 1),
+                        'hbm_bound_equiv_gbs': round(top['bytes'] / (top['ms'] * 1e-3) / 1e9, 1)}
+        else:
+            achieved = top['bytes'] / (top['ms'] * 1e-3) / 1e9
+            roofline = {'kernel': top_name, 'bound': 'hbm', 'achieved': round(achieved, 1), 'peak': peaks['hbm_gbs'],
+                        'unit': 'GB/s', 'frac': round(achieved / peaks['hbm_gbs'], 4), 'traffic': None,
+                        'peak_source': peaks['source'],
+                        'avg_us_per_launch': round(1e3 * top['ms'] / top['calls'], 2),
+                        'share_of_kernel_time': round(top['ms'] / tot, 3)}
+        roofline['how'] = ('CUDA-event pair around every library call in a second pass of %d steps; '
+                           'summed kernel time %.3f ms/step vs %.3f ms/step wall' % (inst_steps, tot / inst_steps,
+                                                                                     dev_ms / args.steps))
+        out = {
+            'metric': METRIC, 'value': round(value, 1), 'unit': 'samples/s', 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': round(dev_ms / args.steps, 4), 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32 (tf32 tensor-core GEMM, fp32 accumulate)',
+            'data': 'synthetic',
+            'config': {'workload': args.workload, 'description': desc, 'per_gpu_batch': batch,
+                       'global_batch': batch * world, 'parallelism': 'dp%d' % world,
+                       'l2': '%d distinct batches/rank (%.0f MB) cycled, larger than the 126 MB L2' % (
+                           nbatch, nbatch * in_bytes / 1e6)},
+            'e2e': {'value': round(e2e_value, 1), 'unit': 'samples/s', 'h2d_bytes_per_step': int(in_bytes),
+                    'd2h_bytes_per_step': 4, 'ms_per_step': round(e2e_ms / args.steps, 4)},
+            'gpu_launches': int(launches), 'launches_per_step': round(launches / args.steps, 1),
+            'wall_ms_per_step': round(dev_wall / args.steps, 4), 'final_loss': last_loss,
+            'clocks': clocks, 'roofline': roofline,
+            'kernel_families': dict((k, {'calls_per_step': round(v['calls'] / inst_steps, 1),
+                                         'us_per_call': round(1e3 * v['ms'] / v['calls'], 2),
+                                         'share': round(v['ms'] / tot, 3)}) for k, v in ranked[:8]),
+        }
+    return out, rank, world
+
+
+# ------------------------------------------------------------------ ufunc sweep (config 2) --
+def run_ufunc_sweep(sizes=(10 ** 4, 10 ** 5, 10 ** 6, 10 ** 7, 10 ** 8, 10 ** 9 // 4)):
+    """GB/s of add / multiply / exp / maximum(0,x) / (n/1024,1024)+(1024,) / sum axis 0, 1 / max
+    axis 1 / full sum / softmax rows through `minpy.numpy` on one GPU.  Operands of the large
+    sizes exceed the L2; small sizes are launch-latency numbers and are reported as such."""
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    import minpy.numpy as mnp
+    import minpy.numpy.random as mrandom
+    from minpy_b200._lib import get_lib
+    lib = get_lib()
+    peaks = measured_peaks()
+    res = {}
+    e0, e1 = ctypes.c_void_p(), ctypes.c_void_p()
+    lib.mc_event_create(ctypes.byref(e0))
+    lib.mc_event_create(ctypes.byref(e1))
+
+    def time_op(fn, reps):
+        for _ in range(3):
+            fn()
+        lib.mc_sync()
+        lib.mc_event_record(e0)
+        for _ in range(reps):
+            fn()
+        lib.mc_event_record(e1)
+        lib.mc_sync()
+        ms = ctypes.c_float()
+        lib.mc_event_elapsed_ms(e0, e1, ctypes.byref(ms))
+        return ms.value / reps
+
+    for n in sizes:
+        rows = max(1, n // 1024)
+        n2 = rows * 1024
+        a = mrandom.rand(n2)
+        b = mrandom.rand(n2)
+        m = a.reshape((rows, 1024))
+        v = mrandom.rand(1024)
+        reps = 200 if n <= 10 ** 6 else (50 if n <= 10 ** 7 else 10)
+        ops = {
+            'add': (lambda: mnp.add(a, b), 12.0 * n2),
+            'multiply': (lambda: mnp.multiply(a, b), 12.0 * n2),
+            'exp': (lambda: mnp.exp(a), 8.0 * n2),
+            'relu': (lambda: mnp.maximum(0, a), 8.0 * n2),
+            'bcast_add': (lambda: m + v, 8.0 * n2 + 4096),
+            'sum_axis0': (lambda: mnp.sum(m, axis=0), 4.0 * n2 + 4096),
+            'sum_axis1': (lambda: mnp.sum(m, axis=1), 4.0 * n2 + 4.0 * rows),
+            'max_axis1': (lambda: mnp.max(m, axis=1), 4.0 * n2 + 4.0 * rows),
+            'sum_all': (lambda: mnp.sum(a), 4.0 * n2),
+        }
+        if hasattr(mnp, 'softmax_output'):
+            ops['softmax_rows'] = (lambda: mnp.softmax_output(m, m), 8.0 * n2)
+        entry = {}
+        for name, (fn, nbytes) in ops.items():
+            ms = time_op(fn, reps)
+            gbs = nbytes / (ms * 1e-3) / 1e9
+            entry[name] = {'us': round(ms * 1e3, 2), 'gbs': round(gbs, 1), 'frac_hbm': round(gbs / peaks['hbm_gbs'], 3)}
+        res['n=%.0e' % n2] = entry
+        del a, b, m, v
+    return res
+
+
+# ------------------------------------------------------------- CPU arm (oracle port) -------
+def oracle_step_fn(workload):
+    """One training step of `workload` on the NumPy oracle (float64, as the reference's NumPy
+    variant computes): returns (step(xb, yb) -> loss, batch)."""
+    from oracle import minpy_oracle as orc
+    from minpy_b200 import workloads
+    factory, batch, rule, optim_config, _, _ = workloads.WORKLOADS[workload]
+    model = factory()
+    params = dict((k, v.astype(np.float64)) for k, v in workloads.init_params(model, 3).items())
+    names = list(params.keys())
+    cfgs = dict((k, dict(optim_config)) for k in names)
+    update = getattr(orc, rule)
+    state = {'aux': {}}
+
+    if workload in ('mlp_c1',):
+        def loss_of(xb, yb):
+            def f(*ps):
+                p = dict(zip(names, ps))
+                h = orc.relu(orc.affine(xb, p['w1'], p['b1']))
+                return orc.softmax_loss(orc.affine(h, p['w2'], p['b2']), yb)
+            return f
+    elif workload == 'mlp_c3':
+        depth = model.depth
+        rng = np.random.RandomState(17)
+
+        def loss_of(xb, yb):
+            def f(*ps):
+                p = dict(zip(names, ps))
+                h = xb
+                for i in range(depth):
+                    h = orc.relu(orc.affine(h, p['w%d' % i], p['b%d' % i]))
+                    h, rm, rv = orc.batchnorm(h, p['gamma%d' % i], p['beta%d' % i],
+                                              running_mean=state['aux'].get('rm%d' % i),
+                                              running_var=state['aux'].get('rv%d' % i))
+                    state['aux']['rm%d' % i], state['aux']['rv%d' % i] = orc.raw(rm), orc.raw(rv)
+                    mask = rng.rand(*orc.raw(h).shape) > 0.5
+                    h = orc.dropout(h, 0.5, mask=mask)
+                return orc.softmax_loss(orc.affine(h, p['wo'], p['bo']), yb)
+            return f
+    elif workload == 'lstm_c5':
+        H = model.H
+
+        def loss_of(xb, yb):
+            N, T, _ = xb.shape
+
+            def f(*ps):
+                p = dict(zip(names, ps))
+                ph, pc = np.zeros((N, H)), np.zeros((N, H))
+                hs = orc.zeros((N, 0, H))
+                for t in range(T):
+                    ph, pc = orc.lstm_step(xb[:, t, :], ph, pc, p['Wx'], p['Wh'], p['b'])
+                    hs = orc.append(hs, ph.reshape(N, 1, H), axis=1)
+                return orc.temporal_softmax_loss(orc.temporal_affine(hs, p['Wa'], p['ba']), yb, np.ones((N, T)))
+            return f
+    else:
+        raise ValueError(workload)
+
+    def step(xb, yb):
+        xb = xb.reshape(xb.shape[0], -1).astype(np.float64) if xb.ndim == 4 else xb.astype(np.float64)
+        grads, loss = orc.grad_and_loss(loss_of(xb, yb), argnum=range(len(names)))(*[params[n] for n in names])
+        for n, g in zip(names, grads):
+            params[n], cfgs[n] = update(params[n], g, cfgs[n])
+        return float(loss)
+    return step, batch
+
+
+def time_cpu(workload, budget_s=12.0, max_steps=50, warmup=1):
+    """samples/s of the oracle port on this box's host cores over a bounded number of steps."""
+    from minpy_b200 import workloads
+    step, batch = oracle_step_fn(workload)
+    make_data = workloads.WORKLOADS[workload][4]
+    X, Y = make_data(batch * 4, seed=100)
+    for i in range(warmup):
+        step(X[:batch], Y[:batch])
+    t0 = time.perf_counter()
+    n = 0
+    while n < max_steps:
+        j = n % 4
+        step(X[j * batch:(j + 1) * batch], Y[j * batch:(j + 1) * batch])
+        n += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    try:
+        from threadpoolctl import threadpool_info
+        threads = max([p.get('num_threads', 1) for p in threadpool_info()] or [1])
+    except Exception:  # pylint: disable=broad-except
+        threads = os.cpu_count()
+    return {'value': round(batch * n / dt, 1), 'unit': 'samples/s', 'cores': int(threads), 'kind': 'port',
+            'sample': '%d steps of %s (batch %d) on the NumPy oracle port, float64 as the reference NumPy variant, '
+                      '%.1f s' % (n, workload, batch, dt),
+            'host_cpus': os.cpu_count()}, batch, n, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return None
+    cpu, batch, n, dt = time_cpu(args.workload, budget_s=20.0, max_steps=max(args.steps, 1), warmup=min(args.warmup, 2))
+    from minpy_b200 import workloads
+    desc = workloads.WORKLOADS[args.workload][5]
+    return {
+        'impl': 'reference', 'metric': METRIC, 'value': cpu['value'], 'unit': 'samples/s', 'n_gpus': args.gpus,
+        'steps': n, 'warmup': min(args.warmup, 2), 'ms_per_step': round(1e3 * dt / n, 3), 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': {'workload': args.workload, 'description': desc, 'per_gpu_batch': batch, 'global_batch': batch,
+                   'parallelism': 'cpu'},
+        'cpu_baseline': cpu,
+        'e2e': {'value': cpu['value'], 'unit': 'samples/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=50)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--workload', default='mlp_c3')
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--pool', type=int, default=16, help='distinct batches cycled per rank')
+    ap.add_argument('--no-ufunc', action='store_true')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    if args.impl == 'reference':
+        out = run_reference(args)
+        if out is not None:
+            print(json.dumps(out), flush=True)
+        return
+
+    out, rank, world = run_b200(args)
+    if rank == 0:
+        if world == 1 and not args.no_ufunc:
+            out['ufunc'] = run_ufunc_sweep()
+        if world == 1 and not args.no_cpu_baseline:
+            out['cpu_baseline'] = time_cpu(args.workload)[0]
+        print(json.dumps(out), flush=True)
+    from minpy_b200 import parallel
+    parallel.barrier()
+    parallel.shutdown()
+
+
+if __name__ == '__main__':
+    main()

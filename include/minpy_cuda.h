@@ -101,6 +101,10 @@ int mc_arange(float* dst, float start, float step, int64_t n);
 /* dtype casts; codes: 0 f32, 1 i32, 2 i64, 3 f64, 4 u8. */
 enum mc_dtype { MC_F32 = 0, MC_I32, MC_I64, MC_F64, MC_U8 };
 int mc_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n);
+/* Multi-tensor float32 copy in one launch per 48 tensors: packs the tape's gradients into the
+ * flat all-reduce bucket inserted between nn/solver.py:184 and :190 (srcs/dsts/ns are HOST
+ * arrays of `count` device pointers / element counts). */
+int mc_multi_copy(const void* const* srcs, void* const* dsts, const int64_t* ns, int count);
 
 /* Fused chain of elementwise VJPs -- the rewrite of the per-record loop of
  * minpy/tape.py:223-234: out[i] = (acc ? acc[i] : 0) + g[i] * prod_k f_k(a_k, b_k, s_k).

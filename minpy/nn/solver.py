@@ -108,7 +108,9 @@ class Solver(object):
         if parallel.world_size() > 1:
             grads = parallel.allreduce_mean(grads)
 
-        self.loss_history.append(loss.asnumpy() if hasattr(loss, 'asnumpy') else loss)
+        # the reference fetches the loss here (solver.py:187), a device->host sync every step;
+        # the entry stays a lazy device scalar instead: float(entry) / entry.asnumpy() fetch it
+        self.loss_history.append(loss)
         for name, dw in zip(names, grads):
             next_w, next_config = self.update_rule(self.model.params[name], dw, self.optim_configs[name])
             self.model.params[name] = next_w

@@ -53,6 +53,7 @@ inline int grid_for(int64_t work_items, int per_block, int ctas_per_sm = 8) {
 }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+__device__ __forceinline__ bool aligned16_dev(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // ---- device helpers ------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -435,6 +435,38 @@ __global__ void __launch_bounds__(EW_THREADS) vjp_chain_kernel(const float* __re
   }
 }
 
+
+// ------------------------------------------------------------- multi-tensor copy ----
+// Packs up to MT_MAX tensors into (or out of) a flat buffer with one launch: the gradient
+// bucket handed to the all-reduce.  Block b serves tile (b - first[t]) of tensor t.
+constexpr int MT_MAX = 48;
+constexpr int MT_TILE = EW_THREADS * 4 * 4;   // floats per block
+struct MultiCopyDesc {
+  int count;
+  int first[MT_MAX + 1];        // first block index of each tensor
+  const float* src[MT_MAX];
+  float* dst[MT_MAX];
+  int64_t n[MT_MAX];
+};
+
+__global__ void __launch_bounds__(EW_THREADS) multi_copy_kernel(const __grid_constant__ MultiCopyDesc d) {
+  int t = 0;
+  while (t + 1 < d.count && (int)blockIdx.x >= d.first[t + 1]) ++t;
+  const float* __restrict__ src = d.src[t];
+  float* __restrict__ dst = d.dst[t];
+  const int64_t n = d.n[t];
+  const int64_t lo = (int64_t)(blockIdx.x - d.first[t]) * MT_TILE;
+  const int64_t hi = (lo + MT_TILE < n) ? lo + MT_TILE : n;
+  if (aligned16_dev(src) && aligned16_dev(dst)) {
+    const int64_t hi4 = lo + ((hi - lo) & ~(int64_t)3);
+    for (int64_t i = lo + 4 * (int64_t)threadIdx.x; i < hi4; i += 4 * EW_THREADS)
+      *reinterpret_cast<float4*>(dst + i) = __ldg(reinterpret_cast<const float4*>(src + i));
+    for (int64_t i = hi4 + threadIdx.x; i < hi; i += EW_THREADS) dst[i] = src[i];
+  } else {
+    for (int64_t i = lo + threadIdx.x; i < hi; i += EW_THREADS) dst[i] = src[i];
+  }
+}
+
 // ------------------------------------------------------------ host dispatch ---------
 template <int OP>
 static int launch_unary(const float* x, float* y, int64_t n) {
@@ -626,6 +658,29 @@ int mc_vjp_chain(const float* g, int g_mode, int64_t g_inner, float g_scalar, co
   int grid = grid_for(vec_ok ? (n >> 2) + 1 : n, EW_THREADS);
   vjp_chain_kernel<<<grid, EW_THREADS, 0, stream()>>>(g, acc, out, n, vec_ok, d);
   MC_LAUNCHED();
+  return 0;
+}
+
+int mc_multi_copy(const void* const* srcs, void* const* dsts, const int64_t* ns, int count) {
+  MC_REQUIRE(count >= 0, "negative tensor count");
+  for (int base = 0; base < count; base += MT_MAX) {
+    MultiCopyDesc d;
+    d.count = 0;
+    int blocks = 0;
+    for (int k = base; k < count && d.count < MT_MAX; ++k) {
+      if (ns[k] <= 0) continue;
+      d.first[d.count] = blocks;
+      d.src[d.count] = (const float*)srcs[k];
+      d.dst[d.count] = (float*)dsts[k];
+      d.n[d.count] = ns[k];
+      blocks += (int)((ns[k] + MT_TILE - 1) / MT_TILE);
+      ++d.count;
+    }
+    if (d.count == 0) continue;
+    d.first[d.count] = blocks;
+    multi_copy_kernel<<<blocks, EW_THREADS, 0, stream()>>>(d);
+    MC_LAUNCHED();
+  }
   return 0;
 }
 

@@ -1,0 +1,229 @@
+"""Data parallelism for `Solver._step`: one process per GPU, gradients averaged across ranks.
+
+The reference has no multi-device training loop at all (only manual
+`with gpu(i)` placement, minpy/context.py:92-98).  Minibatch training shards by rows and every
+loss in nn/layers.py is a mean over the batch, so the full-batch gradient is the average of
+the per-shard gradients: ONE exchange step per training step, placed between the tape's
+backward pass and the update rules (minpy/nn/solver.py:184 and :190 in the reference).
+
+Plumbing is `torch.distributed` (NCCL over NVLink on the device, gloo on the host for the
+CPU tests).  The gradients are packed into one persistent flat device buffer with the
+library's multi-tensor pack kernel, all-reduced in place (a 0.5-20 MB message: latency bound,
+so one message, not one per parameter), and handed back as zero-copy views of the flat buffer.
+The library and torch share the legacy default stream, so ordering needs no extra events.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+_state = {'initialised': False, 'world': 1, 'rank': 0, 'backend': None, 'flat': None, 'flat_t': None}
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def init(backend=None):
+    """Join the process group described by RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT
+    (torchrun sets them).  A single process (no WORLD_SIZE, or WORLD_SIZE=1) is a no-op."""
+    if _state['initialised']:
+        return _state['world']
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    if world <= 1:
+        _state.update(initialised=True, world=1, rank=0)
+        return 1
+    import torch
+    dist = _dist()
+    if backend is None:
+        backend = 'nccl' if torch.cuda.is_available() else 'gloo'
+    os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+    os.environ.setdefault('MASTER_PORT', '29500')
+    rank = int(os.environ.get('RANK', '0'))
+    if backend == 'nccl':
+        local = int(os.environ.get('LOCAL_RANK', str(rank)))
+        torch.cuda.set_device(local)
+        from .cuda_array import ensure_device
+        ensure_device(local)
+    if not dist.is_initialized():
+        kwargs = {}
+        if backend == 'nccl':
+            kwargs['device_id'] = torch.device('cuda', int(os.environ.get('LOCAL_RANK', str(rank))))
+        dist.init_process_group(backend=backend, rank=rank, world_size=world, **kwargs)
+    _state.update(initialised=True, world=world, rank=rank, backend=backend)
+    return world
+
+
+def shutdown():
+    if _state['world'] > 1 and _dist().is_initialized():
+        _dist().destroy_process_group()
+    _state.update(initialised=False, world=1, rank=0, backend=None, flat=None, flat_t=None)
+
+
+def world_size():
+    return _state['world']
+
+
+def rank():
+    return _state['rank']
+
+
+def barrier():
+    if _state['world'] > 1:
+        _dist().barrier()
+
+
+class _DevMem(object):
+    """`__cuda_array_interface__` view of a device allocation, so torch can alias it."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {'shape': (n,), 'typestr': '<f4', 'data': (ptr, False), 'version': 2}
+
+
+def torch_view(arr):
+    """torch.Tensor aliasing a float32 CudaArray (no copy)."""
+    import torch
+    from .cuda_array import ensure_device
+    return torch.as_tensor(_DevMem(arr.ptr, max(1, arr.size)), device='cuda:%d' % ensure_device())[:arr.size]
+
+
+_ALIGN = 64   # floats: every segment of the flat buffer starts 256-byte aligned
+
+
+def _segments(sizes):
+    offs, total = [], 0
+    for n in sizes:
+        offs.append(total)
+        total += (n + _ALIGN - 1) // _ALIGN * _ALIGN
+    return offs, total
+
+
+def _flat_buffer(total):
+    from .cuda_array import CudaArray
+    flat = _state['flat']
+    if flat is None or flat.size < total:
+        flat = CudaArray.empty((total,))
+        from .ops import L
+        L().mc_memset(flat.ptr, 0, flat.nbytes)
+        _state['flat'] = flat
+        _state['flat_t'] = torch_view(flat)
+    return flat, _state['flat_t']
+
+
+def allreduce_mean(grads):
+    """Average a list of gradients (MinPy Arrays, raw arrays or the Python scalar 0.0 for
+    parameters the loss does not reach) over all ranks; returns a list of the same form."""
+    world = _state['world']
+    if world <= 1:
+        return grads
+    from minpy import array as marray
+    from minpy.array_variants import ArrayType
+    from .cuda_array import CudaArray
+    dist = _dist()
+    raws = []
+    for g in grads:
+        if isinstance(g, marray.Array):
+            raws.append(g._get_latest_data())  # pylint: disable=protected-access
+        elif isinstance(g, marray.Number):
+            raws.append(float(g.val))
+        else:
+            raws.append(g)
+    if any(isinstance(r, CudaArray) for r in raws):
+        from . import ops
+        lib = ops.L()
+        shapes = [r.shape if isinstance(r, (CudaArray, np.ndarray)) else None for r in raws]
+        offs, total = _segments([ops._prod(s) if s is not None else 0 for s in shapes])  # pylint: disable=protected-access
+        # a fresh flat buffer per step: the views handed back stay valid for as long as the
+        # caller keeps them (the pool recycles the block as soon as they die)
+        flat = CudaArray.empty((total,))
+        srcs, dsts, ns = [], [], []
+        for r, off, shape in zip(raws, offs, shapes):
+            if shape is None:
+                continue
+            if isinstance(r, np.ndarray):
+                r = CudaArray.from_numpy(r)
+            r = ops.as_f32(r)
+            srcs.append(r.ptr)
+            dsts.append(flat.ptr + 4 * off)
+            ns.append(r.size)
+        k = len(srcs)
+        if k:
+            lib.mc_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_void_p * k)(*dsts), (ctypes.c_int64 * k)(*ns), k)
+        t = torch_view(flat)
+        if _state['backend'] == 'nccl':
+            dist.all_reduce(t, op=dist.ReduceOp.AVG)
+        else:   # pragma: no cover  (device arrays with a host backend)
+            raise RuntimeError('device gradients need the nccl backend')
+        out = []
+        for r, off, shape in zip(raws, offs, shapes):
+            if shape is None:
+                out.append(r)
+            else:
+                out.append(marray.wrap(CudaArray(flat.buf, flat.ptr + 4 * off, tuple(shape))))
+        return out
+    # host gradients (NumPy policy): used by the CPU tests of this logic and by the CPU baseline
+    import torch
+    host = [np.asarray(r, dtype=np.float64) for r in raws if isinstance(r, np.ndarray)]
+    if not host:
+        return grads
+    flat = np.concatenate([h.reshape(-1) for h in host])
+    t = torch.from_numpy(flat)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    flat /= world
+    out, pos = [], 0
+    for r in raws:
+        if isinstance(r, np.ndarray):
+            n = r.size
+            out.append(marray.wrap(flat[pos:pos + n].reshape(r.shape).astype(r.dtype, copy=False)))
+            pos += n
+        else:
+            out.append(r)
+    return out
+
+
+def broadcast_params(params, src=0):
+    """Every rank takes rank `src`'s parameter values (dict name -> MinPy Array, in place in
+    the dict).  Called once after `Solver.init`."""
+    if _state['world'] <= 1:
+        return
+    import torch
+    from minpy import array as marray
+    from .cuda_array import CudaArray
+    dist = _dist()
+    for name in sorted(params.keys()):
+        value = params[name]
+        raw = value._get_latest_data() if isinstance(value, marray.Array) else value  # pylint: disable=protected-access
+        if isinstance(raw, CudaArray):
+            dist.broadcast(torch_view(raw), src=src)
+        else:
+            host = np.ascontiguousarray(raw)
+            t = torch.from_numpy(host)
+            dist.broadcast(t, src=src)
+            params[name] = marray.wrap(host)
+
+
+def allreduce_scalar_sum(value):
+    """Sum of a Python number over ranks (accuracy counts, loss for printing)."""
+    if _state['world'] <= 1:
+        return value
+    import torch
+    dist = _dist()
+    dev = 'cuda' if _state['backend'] == 'nccl' else 'cpu'
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def max_over_ranks(value):
+    """Max of a Python number over ranks (bench timing)."""
+    if _state['world'] <= 1:
+        return value
+    import torch
+    dist = _dist()
+    dev = 'cuda' if _state['backend'] == 'nccl' else 'cpu'
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())

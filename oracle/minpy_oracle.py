@@ -333,6 +333,14 @@ def argmax(x, axis=None):
     return np.argmax(raw(x), axis=axis)
 
 
+def arange(*args, **kwargs):
+    return np.arange(*args, **kwargs)
+
+
+def array(obj):
+    return Var(np.array(raw(obj)))
+
+
 # ======================================================================================
 #  nn.layers  (minpy/nn/layers.py)
 # ======================================================================================
