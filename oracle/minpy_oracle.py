@@ -239,6 +239,14 @@ reshape = primitive(np.reshape, {0: lambda ans, x, shape: (lambda g: np.reshape(
 expand_dims = primitive(np.expand_dims, {0: lambda ans, x, axis: (lambda g: np.reshape(g, x.shape))})  # :301-302
 
 
+mod = _binary(np.mod, lambda ans, x, y: _identity,
+              lambda ans, x, y: (lambda g: -g * np.floor(x / y)))                              # :261-266
+_zero_grad = {0: lambda ans, x: (lambda g: 0.0)}
+round = primitive(np.round, _zero_grad)                                                        # :271 (rint-like, zero grad)
+ceil = primitive(np.ceil, _zero_grad)                                                          # :272
+floor = primitive(np.floor, _zero_grad)                                                        # :273
+
+
 def _sum_grad(ans, x, axis=None, keepdims=False):  # numpy_core.py:150-162
     if axis is None:
         return lambda g: np.full(x.shape, g)
@@ -250,13 +258,27 @@ def _sum_grad(ans, x, axis=None, keepdims=False):  # numpy_core.py:150-162
     return lambda g: np.zeros(xshape) + np.reshape(g, expanded)
 
 
-def _chooser_grad(ans, a, axis=None, keepdims=False):  # numpy_core.py:66-116
+def _match_shape(a, axis, keepdims):  # numpy_core.py:71-116
+    """Function repeating a reduction result back to a.shape (int axes may be negative;
+    tuple axes are matched literally, as the reference's `i in axis` does)."""
+    if not isinstance(a, np.ndarray):
+        return _identity
+    shape = a.shape
     if axis is None:
-        rep = lambda g: np.full(a.shape, g)
-    else:
-        axes = [axis] if isinstance(axis, int) else list(axis)
-        expanded = [1 if i in axes else s for i, s in enumerate(a.shape)]
-        rep = lambda g: np.zeros(a.shape) + np.reshape(g, expanded)
+        return lambda g: np.full(shape, g)
+    if isinstance(axis, int):
+        if keepdims:
+            return lambda g: np.repeat(g, shape[axis], axis)
+        return lambda g: np.repeat(np.expand_dims(g, axis), shape[axis], axis)
+    repeats = [shape[i] if i in axis else 1 for i in range(len(shape))]
+    expanded = [shape[i] if i not in axis else 1 for i in range(len(shape))]
+    if keepdims:
+        return lambda g: np.tile(g, repeats)
+    return lambda g: np.tile(np.reshape(g, expanded), repeats)
+
+
+def _chooser_grad(ans, a, axis=None, keepdims=False):  # numpy_core.py:64-68
+    rep = _match_shape(a, axis, keepdims)
     locations = a == rep(ans)
     return lambda g: rep(g) * locations
 
@@ -424,7 +446,7 @@ def svm_loss(x, y):  # layers.py:150-173
     N = x.shape[0]
     yi = np.asarray(raw(y)).astype(int)
     correct = x[np.arange(N), yi]
-    margins = maximum(0, x - expand_dims(correct, 1) + 1.0)
+    margins = maximum(0, x - correct + 1.0)   # (N,C) - (N,): broadcasts only when N == C, as the reference
     return (sum(margins) - sum(margins[np.arange(N), yi])) / N
 
 
@@ -446,6 +468,38 @@ def lstm_step(x, prev_h, prev_c, Wx, Wh, b):  # layers.py:353-380
     next_c = f * prev_c + i * g
     next_h = o * tanh(next_c)
     return next_h, next_c
+
+
+def rnn_temporal(x, h0, Wx, Wh, b):  # layers.py:278-305
+    N, T, _ = x.shape
+    H = h0.shape[1]
+    h = zeros([N, 0, H])
+    for t in range(T):
+        h_step = rnn_step(x[:, t, :], h0 if t == 0 else h[:, t - 1, :], Wx, Wh, b).reshape(N, 1, H)
+        h = append(h, h_step, axis=1)
+    return h
+
+
+def gru_step(x, prev_h, Wx, Wh, b, Wxh, Whh, bh):  # layers.py:308-350
+    H = prev_h.shape[1]
+    a = sigmoid(dot(x, Wx) + dot(prev_h, Wh) + b)
+    r = a[:, 0:H]
+    z = a[:, H:2 * H]
+    h_m = tanh(dot(x, Wxh) + dot(r * prev_h, Whh) + bh)
+    return z * prev_h + (1 - z) * h_m
+
+
+def lstm_temporal(x, h0, Wx, Wh, b):  # layers.py:383-420
+    N, T, _ = x.shape
+    H = h0.shape[1]
+    c = zeros([N, 0, H])
+    h = zeros([N, 0, H])
+    for t in range(T):
+        h_step, c_step = lstm_step(x[:, t, :], h[:, t - 1, :] if t > 0 else h0,
+                                   c[:, t - 1, :] if t > 0 else zeros((N, H)), Wx, Wh, b)
+        h = append(h, h_step.reshape(N, 1, H), axis=1)
+        c = append(c, c_step.reshape(N, 1, H), axis=1)
+    return h
 
 
 def temporal_affine(x, w, b):  # layers.py:423-441
@@ -506,6 +560,23 @@ def adam(x, dx, config):
     v_ = v / (1 - config['beta2'] ** t)
     config['m'], config['v'], config['t'] = m, v, t
     return x - config['learning_rate'] * m_ / (np.sqrt(v_) + config['epsilon']), config
+
+
+# ======================================================================================
+#  nn.init  (minpy/nn/init.py:9-103) -- `z` is the standard-normal draw the rule consumes
+# ======================================================================================
+def xavier(shape, z):  # init.py:27-34: NORMAL draw scaled by sqrt(6 / (shape[0] + prod(shape[1:])))
+    fan_out = shape[0]
+    fan_in = int(np.prod(shape[1:]))
+    return z * np.sqrt(6.0 / (fan_out + fan_in))
+
+
+def gaussian(shape, z, config):  # init.py:60-80: defaults mu 0, stdvar 0.001
+    return z * config.get('stdvar', 0.001) + config.get('mu', 0.0)
+
+
+def constant(shape, config):  # init.py:37-57
+    return np.ones(shape) * config.get('value', 0.0)
 
 
 # ======================================================================================
