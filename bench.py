@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- training samples/sec of the MinPy hot path on the B200 `cuda` array variant.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload mlp_c3|mlp_c1|lstm_c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload mlp_c3|mlp_c1|cnn_c4|cnn_ref|lstm_c5]
                     [--impl b200|reference] [--no-ufunc] [--no-cpu-baseline]
 
 One "step" is one `Solver._step` (forward + tape backward + gradient all-reduce when N > 1 +
@@ -497,6 +497,22 @@ def oracle_step_fn(workload):
                     h = orc.dropout(h, 0.5, mask=mask)
                 return orc.softmax_loss(orc.affine(h, p['wo'], p['bo']), yb)
             return f
+    elif workload in ('cnn_c4', 'cnn_ref'):
+        convs = sorted(k[:-7] for k in names if k.endswith('_weight'))
+        pad = 1 if workload == 'cnn_c4' else 0
+
+        def loss_of(xb, yb):
+            def f(*ps):
+                p = dict(zip(names, ps))
+                h = xb
+                for c in convs:
+                    h = orc.maxpool2d(orc.relu_mx(orc.conv2d(h, p[c + '_weight'], p[c + '_bias'], 1, pad)), 2, 2)
+                h = orc.flatten(h)
+                if workload == 'cnn_ref':
+                    h = orc.relu(orc.affine(h, p['w1'], p['b1']))
+                    return orc.softmax_loss(orc.affine(h, p['w2'], p['b2']), yb)
+                return orc.softmax_loss(orc.affine(h, p['w1'], p['b1']), yb)
+            return f
     elif workload == 'lstm_c5':
         H = model.H
 
@@ -516,7 +532,8 @@ def oracle_step_fn(workload):
         raise ValueError(workload)
 
     def step(xb, yb):
-        xb = xb.reshape(xb.shape[0], -1).astype(np.float64) if xb.ndim == 4 else xb.astype(np.float64)
+        flat = xb.ndim == 4 and not workload.startswith('cnn')
+        xb = xb.reshape(xb.shape[0], -1).astype(np.float64) if flat else xb.astype(np.float64)
         grads, loss = orc.grad_and_loss(loss_of(xb, yb), argnum=range(len(names)))(*[params[n] for n in names])
         for n, g in zip(names, grads):
             params[n], cfgs[n] = update(params[n], g, cfgs[n])

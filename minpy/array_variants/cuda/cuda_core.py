@@ -547,6 +547,22 @@ def fused_batchnorm_test(x, gamma, beta, running_mean, running_var, eps):
     return out
 
 
+def _batchnorm_test_vjp(ans, x, gamma, beta, running_mean, running_var, eps):  # pylint: disable=unused-argument
+    """Test-mode statistics are constants: dx = g * gamma / sqrt(rv + eps), dgamma = sum(g * xhat, 0),
+    dbeta = sum(g, 0).  Not on the training path (only gradient checks reach it): generic ops."""
+    def vjp(g):
+        lib = ops.L()
+        g = concrete(g, ans.shape)
+        inv = ops.unary(lib.MC_RECIP, ops.unary(lib.MC_SQRT, ops.binary(lib.MC_ADD, running_var, float(eps))))
+        scale = ops.binary(lib.MC_MUL, ops.as_f32(gamma).reshape(inv.shape), inv)
+        dx = ops.binary(lib.MC_MUL, g, scale)
+        xhat = ops.binary(lib.MC_MUL, ops.binary(lib.MC_SUB, x, running_mean), inv)
+        dgamma = ops.reduce(lib.MC_RED_SUM, ops.binary(lib.MC_MUL, g, xhat), 0).reshape(gamma.shape)
+        dbeta = ops.reduce(lib.MC_RED_SUM, g, 0).reshape(beta.shape)
+        return [dx, dgamma, dbeta]
+    return vjp
+
+
 def fused_dropout(x, prob, seed, offset):
     """x * (u > prob), not rescaled (nn/layers.py:141-144); u from Philox(seed, offset)."""
     out = CudaArray.empty(x.shape)
@@ -717,6 +733,8 @@ def def_grads(prims):
     prims('fused_relu').def_grad(_relu_vjp)
     prims('fused_batchnorm').def_multiple_grad(_batchnorm_vjp, (0, 1, 2))
     prims('fused_batchnorm').def_grad_zero(3).def_grad_zero(4)
+    prims('fused_batchnorm_test').def_multiple_grad(_batchnorm_test_vjp, (0, 1, 2))
+    prims('fused_batchnorm_test').def_grad_zero(3).def_grad_zero(4)
     prims('fused_dropout').def_grad(_dropout_vjp)
     prims('fused_softmax_loss').def_grad(_softmax_loss_vjp)
     prims('fused_lstm_step').def_multiple_grad(_lstm_step_vjp, (0, 1, 2, 3, 4, 5))

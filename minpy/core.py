@@ -93,7 +93,7 @@ class Function(object):
         self._aux_shapes = dict(zip(self._symbol.list_auxiliary_states(), aux_shapes))
         self._plan = None
 
-    def _create_prim(self, aux_holders):
+    def _create_prim(self, aux_holders, wanted=None):
         """Primitive running the lowered graph; its single multi-gradient VJP returns one
         gradient per argument (and zeros for auxiliary states)."""
         from minpy_b200 import symbol_exec
@@ -105,7 +105,7 @@ class Function(object):
         train = self._is_train
 
         def forward(*raw):
-            run = plan.forward(raw[:len(arg_names)], raw[len(arg_names):], train)
+            run = plan.forward(raw[:len(arg_names)], raw[len(arg_names):], train, data_needs_grad=wanted)
             forward.run = run
             for holder, new in zip(aux_holders, run.new_aux):
                 if holder is not None and new is not None:
@@ -128,7 +128,14 @@ class Function(object):
                                    if k in self._symbol.list_arguments() and hasattr(v, 'shape')))
         args = [kwargs.get(n) for n in self._symbol.list_arguments()]
         aux = [kwargs.get(n) for n in self._symbol.list_auxiliary_states()]
-        return self._create_prim(aux).call(args=args + aux, kwargs={})
+        # arguments the tape is differentiating: the others (the image batch, labels) need no
+        # gradient, so e.g. the first convolution's data-gradient is never computed
+        current = tape.global_tape()
+        wanted = None
+        if current is not None and current.is_recording:
+            wanted = set(n for n, a in zip(self._symbol.list_arguments(), args)
+                         if isinstance(a, array.Value) and a.is_marked_for_bp(current))
+        return self._create_prim(aux, wanted).call(args=args + aux, kwargs={})
 
     def get_params(self):
         return dict((name, {'shape': shape}) for name, shape in self._param_shapes.items())

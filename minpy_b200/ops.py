@@ -649,3 +649,69 @@ def run_chain(g, g_scalar, steps, shape, acc=None, g_mode=None, g_inner=1):
             g, g_scalar, g_mode, g_inner = out, 1.0, 0, 1
             out = CudaArray.empty(shape)
     return out
+
+
+# ------------------------------------------------------------------ convolution / pooling ---
+def conv2d_fwd(x, w, b=None, stride=1, pad=0, relu=False):
+    """NCHW cross-correlation y = conv(x, w) + b [relu]: the `Convolution` (+ `Activation`)
+    symbols of examples/nn/cnn.py:33-36."""
+    lib = L()
+    x, w = as_f32(x), as_f32(w)
+    if x.ndim != 4 or w.ndim != 4 or x.shape[1] != w.shape[1]:
+        raise ValueError('conv2d: x %s and w %s do not match (NCHW / FCHW)' % (x.shape, w.shape))
+    N, C, H, W = x.shape
+    F, _, KH, KW = w.shape
+    OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
+    if OH <= 0 or OW <= 0:
+        raise ValueError('conv2d: kernel larger than padded input')
+    y = CudaArray.empty((N, F, OH, OW))
+    if y.size:
+        lib.mc_conv2d_fwd(x.ptr, w.ptr, as_f32(b).ptr if b is not None else None, y.ptr, N, C, H, W, F, KH, KW,
+                          stride, pad, 1 if relu else 0, _gemm_precision['mode'])
+    return y
+
+
+def conv2d_bwd(x, w, dy, stride=1, pad=0, need_dx=True, need_db=True):
+    """(dx, dw, db) of conv2d_fwd; dx is None when `need_dx` is False (the data input of the
+    first layer is not on the tape)."""
+    lib = L()
+    x, w, dy = as_f32(x), as_f32(w), as_f32(dy)
+    N, C, H, W = x.shape
+    F, _, KH, KW = w.shape
+    dx = None
+    if need_dx:
+        dx = CudaArray.empty(x.shape)
+        if dx.size:
+            lib.mc_conv2d_dgrad(dy.ptr, w.ptr, dx.ptr, N, C, H, W, F, KH, KW, stride, pad, _gemm_precision['mode'])
+    dw = CudaArray.empty(w.shape)
+    db = CudaArray.empty((F,)) if need_db else None
+    lib.mc_conv2d_wgrad(x.ptr, dy.ptr, dw.ptr, db.ptr if db is not None else None, N, C, H, W, F, KH, KW, stride, pad,
+                        _gemm_precision['mode'])
+    return dx, dw, db
+
+
+def maxpool2d_fwd(x, kernel, stride, want_argmax=True):
+    """'valid' max pooling over NCHW; returns (y, argmax int32 or None)."""
+    lib = L()
+    x = as_f32(x)
+    N, C, H, W = x.shape
+    KH, KW = (kernel, kernel) if isinstance(kernel, int) else kernel
+    OH, OW = (H - KH) // stride + 1, (W - KW) // stride + 1
+    if OH <= 0 or OW <= 0:
+        raise ValueError('maxpool2d: kernel larger than input')
+    y = CudaArray.empty((N, C, OH, OW))
+    arg = CudaArray.empty((N, C, OH, OW), _I32) if want_argmax else None
+    if y.size:
+        lib.mc_maxpool2d_fwd(x.ptr, y.ptr, arg.ptr if arg is not None else None, N * C, H, W, KH, KW, stride)
+    return y, arg
+
+
+def maxpool2d_bwd(dy, arg, xshape):
+    """Routes each output gradient to its window's arg-max element (overlapping windows add)."""
+    lib = L()
+    dy = as_f32(dy)
+    N, C, H, W = xshape
+    dx = zeros(xshape)
+    if dy.size:
+        lib.mc_maxpool2d_bwd(dy.ptr, arg.ptr, dx.ptr, N * C, H, W, dy.shape[2], dy.shape[3])
+    return dx

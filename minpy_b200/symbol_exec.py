@@ -1,0 +1,296 @@
+"""Lowering of a `minpy_b200.symbol` graph onto libminpy_cuda.so.
+
+Replaces what `core.Function` obtained from an MXNet executor (minpy/core.py:148-190:
+`simple_bind`, `arg_arrays`, `forward(is_train)`, `outputs`, `backward(out_grads)`,
+`grad_arrays`, `aux_arrays`).  A `Plan` is built once per (symbol, input shapes): it fixes the
+topological order, fuses `Convolution -> Activation(relu)` into the convolution epilogue and
+knows which inputs need gradients.  `Plan.forward` returns a `Run` holding the activations
+the backward pass needs; `Run.backward(out_grad)` returns one gradient per argument.
+
+Operator arithmetic follows MXNet 0.9 (the reference's un-vendored dependency; SURVEY.md 8c
+restates it): NCHW cross-correlation, 'valid' max pooling with the gradient routed to the
+arg-max element, relu gradient `out > 0`, FullyConnected `x.W^T + b`, SoftmaxOutput whose
+backward is `(p - onehot(label)) * grad_scale [/ N if normalization == 'batch']` and ignores
+the incoming gradient (the same quirk as numpy_core.py:170-175).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import ops
+from .cuda_array import CudaArray, _F32, _I32
+from .lazy import concrete
+
+_GT0 = 'MC_VJP_GT0_A'
+
+
+def _sq(pair, what):
+    if pair[0] != pair[1]:
+        raise NotImplementedError('%s must be square, got %s' % (what, pair))
+    return int(pair[0])
+
+
+class Run(object):
+    """State of one forward pass: outputs, updated auxiliary states and the backward closure."""
+
+    def __init__(self, plan, values, saved, new_aux, train):
+        self.plan, self._values, self._saved, self.new_aux, self._train = plan, values, saved, new_aux, train
+        self.outputs = [values[id(plan.head)]]
+
+    def backward(self, out_grad=None):
+        return self.plan._backward(self, out_grad)  # pylint: disable=protected-access
+
+
+class Plan(object):
+    """Execution plan of one symbol for fixed input shapes."""
+
+    def __init__(self, symbol, input_shapes):
+        self.symbol = symbol
+        self.head = symbol._node  # pylint: disable=protected-access
+        self.order = symbol._topo()  # pylint: disable=protected-access
+        self.arg_names = symbol.list_arguments()
+        self.aux_names = symbol.list_auxiliary_states()
+        self.input_names = set(input_shapes or ())
+        consumers = {}
+        for node in self.order:
+            for inp in node.inputs:
+                consumers[id(inp)] = consumers.get(id(inp), 0) + 1
+        # Convolution whose only consumer is a relu Activation: relu runs in the conv epilogue
+        self.fused_relu = {}
+        for node in self.order:
+            if node.op == 'Activation' and node.attrs['act_type'] == 'relu':
+                src = node.inputs[0]
+                if src.op == 'Convolution' and consumers.get(id(src), 0) == 1 and src is not self.head:
+                    self.fused_relu[id(src)] = node
+        # which nodes need a gradient: anything downstream of a non-input argument
+        self.needs_grad = {}
+        for node in self.order:
+            if node.op == 'null':
+                self.needs_grad[id(node)] = True
+            else:
+                self.needs_grad[id(node)] = any(self.needs_grad[id(i)] for i in node.inputs)
+
+    # -------------------------------------------------------------------------- forward -----
+    def forward(self, args, aux, train=True, data_needs_grad=None):
+        """args / aux: raw arrays aligned with list_arguments() / list_auxiliary_states()
+        (None for absent ones).  `data_needs_grad`: names of arguments whose gradient the
+        caller will use (default: all) -- lets the first convolution skip its dgrad."""
+        lib = ops.L()
+        values, saved = {}, {}
+        by_name = dict(zip(self.arg_names, args))
+        aux_by_name = dict(zip(self.aux_names, aux))
+        new_aux = dict((k, None) for k in self.aux_names)
+        skip_relu = set(id(n) for n in self.fused_relu.values())
+        for node in self.order:
+            key = id(node)
+            if node.op == 'null':
+                v = by_name.get(node.name)
+                if v is not None and not isinstance(v, CudaArray):
+                    v = ops.as_cuda(np.asarray(v))
+                if isinstance(v, CudaArray) and v.dtype != _F32 and not node.name.endswith('_label'):
+                    v = v.astype(_F32)
+                values[key] = v
+                continue
+            x = values[id(node.inputs[0])]
+            if x is None:
+                raise ValueError('argument "%s" of the symbol was not supplied' % node.inputs[0].name)
+            a = node.attrs
+            if node.op == 'Convolution':
+                w = values[id(node.inputs[1])]
+                b = values[id(node.inputs[2])] if not a['no_bias'] else None
+                relu = key in self.fused_relu
+                y = ops.conv2d_fwd(x, w, b, _sq(a['stride'], 'stride'), _sq(a['pad'], 'pad'), relu=relu)
+                values[key] = y
+                saved[key] = (x, w)
+            elif node.op == 'Activation':
+                if key in skip_relu:
+                    values[key] = x                     # already applied by the producing convolution
+                else:
+                    op = {'relu': lib.MC_RELU, 'sigmoid': lib.MC_SIGMOID, 'tanh': lib.MC_TANH}[a['act_type']]
+                    values[key] = ops.unary(op, x)
+            elif node.op == 'Pooling':
+                if a['pool_type'] != 'max' or a['global_pool'] or a['pad'] != (0, 0):
+                    raise NotImplementedError('only un-padded max pooling is lowered (avg / global pooling: next)')
+                y, arg = ops.maxpool2d_fwd(x, a['kernel'], _sq(a['stride'], 'stride'), want_argmax=train)
+                values[key] = y
+                saved[key] = (arg, x.shape)
+            elif node.op == 'Flatten':
+                values[key] = x.reshape((x.shape[0], x.size // max(1, x.shape[0])))
+            elif node.op == 'FullyConnected':
+                w = values[id(node.inputs[1])]
+                b = values[id(node.inputs[2])] if not a['no_bias'] else None
+                x2 = x.reshape((x.shape[0], x.size // max(1, x.shape[0])))
+                values[key] = ops.gemm(x2, w, trans_b=True, bias=b)
+                saved[key] = (x2, w)
+            elif node.op == 'SoftmaxOutput':
+                values[key] = ops.softmax_rows(x)
+                saved[key] = values[id(node.inputs[1])]
+            elif node.op == 'BatchNorm':
+                if x.ndim != 2:
+                    raise NotImplementedError('spatial BatchNorm is not lowered yet (SURVEY.md 8f rank 1)')
+                gamma, beta = values[id(node.inputs[1])], values[id(node.inputs[2])]
+                if a['fix_gamma']:
+                    gamma = ops.ones(gamma.shape)
+                rm = aux_by_name.get(node.aux[0])
+                rv = aux_by_name.get(node.aux[1])
+                rm = ops.zeros((x.shape[1],)) if rm is None else ops.as_f32(rm)
+                rv = ops.ones((x.shape[1],)) if rv is None else ops.as_f32(rv)
+                if train and not a['use_global_stats']:
+                    N, D = x.shape
+                    out = CudaArray.empty((N, D))
+                    nrm, nrv = CudaArray.empty((D,)), CudaArray.empty((D,))
+                    sm, si = CudaArray.empty((D,)), CudaArray.empty((D,))
+                    lib.mc_batchnorm_train_fwd(x.ptr, gamma.ptr, beta.ptr, rm.ptr, rv.ptr, out.ptr, nrm.ptr, nrv.ptr,
+                                               sm.ptr, si.ptr, N, D, a['eps'], a['momentum'])
+                    new_aux[node.aux[0]], new_aux[node.aux[1]] = nrm, nrv
+                    saved[key] = (x, gamma, sm, si)
+                    values[key] = out
+                else:
+                    N, D = x.shape
+                    out = CudaArray.empty((N, D))
+                    lib.mc_batchnorm_test_fwd(x.ptr, gamma.ptr, beta.ptr, rm.ptr, rv.ptr, out.ptr, N, D, a['eps'])
+                    saved[key] = None
+                    values[key] = out
+            elif node.op == '_Plus':
+                values[key] = ops.binary(lib.MC_ADD, x, values[id(node.inputs[1])])
+            else:
+                raise NotImplementedError('operator %s is not lowered' % node.op)
+        run = Run(self, values, saved, [new_aux[k] for k in self.aux_names], train)
+        run.data_needs_grad = data_needs_grad
+        return run
+
+    # ------------------------------------------------------------------------- backward -----
+    def _backward(self, run, out_grad):
+        lib = ops.L()
+        values, saved = run._values, run._saved  # pylint: disable=protected-access
+        grads = {}
+        head = self.head
+        if head.op != 'SoftmaxOutput':
+            if out_grad is None:
+                raise ValueError('backward of a symbol without a loss head needs out_grads')
+            if isinstance(out_grad, (tuple, list)):
+                out_grad = out_grad[0]
+            grads[id(head)] = concrete(out_grad, values[id(head)].shape)
+        wanted = run.data_needs_grad
+
+        def want(node):
+            if node.op != 'null':
+                return self.needs_grad[id(node)]
+            return wanted is None or node.name in wanted
+
+        def add(node, g):
+            if g is None or not want(node):
+                return
+            have = grads.get(id(node))
+            grads[id(node)] = g if have is None else ops.binary(lib.MC_ADD, have, g)
+
+        fused_act = dict((id(act), cid) for cid, act in self.fused_relu.items())
+        for node in reversed(self.order):
+            key = id(node)
+            if node.op == 'null':
+                continue
+            a = node.attrs
+            if node.op == 'SoftmaxOutput':
+                p, label = values[key], saved[key]
+                rows, cols = p.shape
+                dx = CudaArray.empty(p.shape)
+                if label is None:
+                    raise ValueError('SoftmaxOutput backward needs the label argument')
+                if label.ndim == 1:
+                    lab = label if label.dtype == _I32 else label.astype(_I32)
+                    lib.mc_softmax_ce_bwd(p.ptr, lab.ptr, None, dx.ptr, rows, cols)
+                else:
+                    lib.mc_softmax_ce_bwd(p.ptr, None, ops.as_f32(label).ptr, dx.ptr, rows, cols)
+                # the kernel yields (p - y) / rows; MXNet's default normalization is 'null'
+                scale = a['grad_scale'] * (1.0 if a['normalization'] in ('batch', 'valid') else float(rows))
+                if scale != 1.0:
+                    dx = ops.binary(lib.MC_MUL, dx, scale)
+                add(node.inputs[0], dx)
+                continue
+            g = grads.pop(key, None)
+            if g is None:
+                continue
+            x_node = node.inputs[0]
+            if node.op == 'Activation':
+                if key in fused_act:
+                    add(x_node, g)            # the convolution applies the relu mask to its own output
+                elif want(x_node):
+                    y = values[key]
+                    op = {'relu': _GT0, 'sigmoid': 'MC_VJP_SIGMOID_ANS', 'tanh': 'MC_VJP_TANH_ANS'}[a['act_type']]
+                    add(x_node, ops.run_chain(g, 1.0, [(lib.enums[op], y, 0, None, 0, 0.0, 1)], y.shape))
+            elif node.op == 'Convolution':
+                x, w = saved[key]
+                if key in self.fused_relu:
+                    y = values[key]
+                    g = ops.run_chain(g, 1.0, [(lib.enums[_GT0], y, 0, None, 0, 0.0, 1)], y.shape)
+                need_dx = want(x_node)
+                dx, dw, db = ops.conv2d_bwd(x, w, g, _sq(a['stride'], 'stride'), _sq(a['pad'], 'pad'),
+                                            need_dx=need_dx, need_db=not a['no_bias'])
+                add(x_node, dx)
+                add(node.inputs[1], dw)
+                if not a['no_bias']:
+                    add(node.inputs[2], db)
+            elif node.op == 'Pooling':
+                if want(x_node):
+                    arg, xshape = saved[key]
+                    add(x_node, ops.maxpool2d_bwd(g, arg, xshape))
+            elif node.op == 'Flatten':
+                add(x_node, g.reshape(values[id(x_node)].shape))
+            elif node.op == 'FullyConnected':
+                x2, w = saved[key]
+                if want(x_node):
+                    add(x_node, ops.gemm(g, w).reshape(values[id(x_node)].shape))          # g . W
+                add(node.inputs[1], ops.gemm(g, x2, trans_a=True))                          # g^T . x
+                if not a['no_bias']:
+                    add(node.inputs[2], ops.reduce(lib.MC_RED_SUM, g, 0))
+            elif node.op == 'BatchNorm':
+                if saved[key] is None:
+                    raise NotImplementedError('backward through inference-mode BatchNorm')
+                x, gamma, sm, si = saved[key]
+                N, D = x.shape
+                dx, dgamma, dbeta = CudaArray.empty((N, D)), CudaArray.empty((D,)), CudaArray.empty((D,))
+                lib.mc_batchnorm_train_bwd(x.ptr, g.ptr, gamma.ptr, sm.ptr, si.ptr, dx.ptr, dgamma.ptr, dbeta.ptr, N, D)
+                add(x_node, dx)
+                add(node.inputs[1], ops.zeros((D,)) if a['fix_gamma'] else dgamma)
+                add(node.inputs[2], dbeta)
+            elif node.op == '_Plus':
+                add(x_node, g)
+                add(node.inputs[1], g)
+        by_name = dict((n.name, grads.get(id(n))) for n in self.order if n.op == 'null')
+        return [by_name[name] if by_name[name] is not None else 0.0 for name in self.arg_names]
+
+
+class Executor(object):
+    """`symbol.simple_bind(...)`: the MXNet executor surface core.Function used (core.py:148-190)."""
+
+    def __init__(self, symbol, shapes, grad_req='write'):
+        self._symbol = symbol
+        self._plan = Plan(symbol, shapes)
+        arg_shapes, _, aux_shapes = symbol.infer_shape(**shapes)
+        self.arg_arrays = [ops.zeros(s) for s in arg_shapes]
+        self.grad_arrays = [None] * len(arg_shapes) if grad_req == 'null' else [ops.zeros(s) for s in arg_shapes]
+        self.aux_arrays = [ops.zeros(s) for s in aux_shapes]
+        self.arg_dict = dict(zip(symbol.list_arguments(), self.arg_arrays))
+        self.aux_dict = dict(zip(symbol.list_auxiliary_states(), self.aux_arrays))
+        self.outputs = []
+        self._run = None
+
+    def forward(self, is_train=False, **kwargs):
+        for k, v in kwargs.items():
+            ops.as_cuda(v).copyto(self.arg_dict[k])
+        self._run = self._plan.forward(self.arg_arrays, self.aux_arrays, train=is_train)
+        for dst, new in zip(self.aux_arrays, self._run.new_aux):
+            if new is not None:
+                new.copyto(dst)
+        self.outputs = list(self._run.outputs)
+        return self.outputs
+
+    def backward(self, out_grads=None):
+        grads = self._run.backward(out_grads)
+        for i, g in enumerate(grads):
+            if self.grad_arrays[i] is None:
+                continue
+            if isinstance(g, CudaArray):
+                g.copyto(self.grad_arrays[i])
+            else:
+                ops.L().mc_memset(self.grad_arrays[i].ptr, 0, self.grad_arrays[i].nbytes)

@@ -90,6 +90,65 @@ class CharLSTM(ModelBase):
         return _layers.temporal_softmax_loss(predict, y, mask)
 
 
+class ConvNet(ModelBase):
+    """Config C4: 3 x (conv3x3 pad 1 -> relu -> maxpool 2/2) with 32/64/128 filters, then
+    affine 2048 -> 10.  Written as examples/nn/cnn.py:26-60 writes its network: the
+    convolutional trunk is an `mx.sym` graph wrapped in `minpy.core.Function`, the classifier
+    is `nn.layers`."""
+
+    def __init__(self, batch=512, filters=(32, 64, 128), classes=10):
+        super(ConvNet, self).__init__()
+        import mxnet as mx
+        from minpy.core import Function
+        net = mx.sym.Variable(name='X')
+        for i, f in enumerate(filters):
+            net = mx.sym.Convolution(data=net, name='conv%d' % i, kernel=(3, 3), pad=(1, 1), num_filter=f)
+            net = mx.sym.Activation(data=net, act_type='relu')
+            net = mx.sym.Pooling(data=net, name='pool%d' % i, pool_type='max', kernel=(2, 2), stride=(2, 2))
+        net = mx.sym.Flatten(data=net)
+        self.conv = Function(net, input_shapes={'X': (batch,) + CIFAR_SHAPE}, name='conv')
+        self.add_params(self.conv.get_params())
+        feat = self.conv.get_one_output_shape()[1]
+        self.add_param(name='w1', shape=(feat, classes)).add_param(name='b1', shape=(classes,))
+
+    def forward(self, X, mode):
+        self.conv.is_train = (mode == 'train')
+        out = self.conv(X=X, **self.params)
+        return _layers.affine(out, self.params['w1'], self.params['b1'])
+
+    def loss(self, predict, y):
+        return _layers.softmax_loss(predict, y)
+
+
+class RefConvNet(ModelBase):
+    """The network of examples/nn/cnn.py:26-60 itself: conv7x7x32 -> relu -> maxpool 2/2 ->
+    affine 5408 -> 512 -> relu -> affine 512 -> 10, batch 128."""
+
+    def __init__(self, batch=128, hidden=512, classes=10):
+        super(RefConvNet, self).__init__()
+        import mxnet as mx
+        from minpy.core import Function
+        net = mx.sym.Variable(name='X')
+        net = mx.sym.Convolution(data=net, name='conv', kernel=(7, 7), num_filter=32)
+        net = mx.sym.Activation(data=net, act_type='relu')
+        net = mx.sym.Pooling(data=net, name='pool', pool_type='max', kernel=(2, 2), stride=(2, 2))
+        net = mx.sym.Flatten(data=net)
+        self.conv = Function(net, input_shapes={'X': (batch,) + CIFAR_SHAPE}, name='conv')
+        self.add_params(self.conv.get_params())
+        feat = self.conv.get_one_output_shape()[1]
+        self.add_param(name='w1', shape=(feat, hidden)).add_param(name='b1', shape=(hidden,)) \
+            .add_param(name='w2', shape=(hidden, classes)).add_param(name='b2', shape=(classes,))
+
+    def forward(self, X, mode):
+        self.conv.is_train = (mode == 'train')
+        out = self.conv(X=X, **self.params)
+        out = _layers.relu(_layers.affine(out, self.params['w1'], self.params['b1']))
+        return _layers.affine(out, self.params['w2'], self.params['b2'])
+
+    def loss(self, predict, y):
+        return _layers.softmax_loss(predict, y)
+
+
 # ------------------------------------------------------------------------ synthetic data --
 def cifar_like(num, seed=0, dtype=np.float32):
     """X ~ N(0,1) of shape (num, 3, 32, 32), y ~ U{0..9}."""
@@ -126,6 +185,10 @@ WORKLOADS = {
                '2-layer MLP 3072-512-10, batch 256, sgd_momentum'),
     'mlp_c3': (DeepMLP, 1024, 'sgd_momentum', {'learning_rate': 1e-3, 'momentum': 0.9}, cifar_like,
                '5-layer MLP 3072-512x4-10 with batchnorm+dropout, batch 1024, sgd_momentum'),
+    'cnn_c4': (ConvNet, 512, 'sgd_momentum', {'learning_rate': 1e-3, 'momentum': 0.9}, cifar_like,
+               'CNN 3x(conv3x3-relu-maxpool) 32/64/128 + affine 2048-10, batch 512, sgd_momentum'),
+    'cnn_ref': (RefConvNet, 128, 'sgd_momentum', {'learning_rate': 1e-3, 'momentum': 0.9}, cifar_like,
+                'examples/nn/cnn.py net: conv7x7x32-relu-maxpool + affine 5408-512-10, batch 128, sgd_momentum'),
     'lstm_c5': (CharLSTM, 128, 'adam', {'learning_rate': 1e-3}, char_like,
                 'char LSTM V=128 H=1024 T=100, batch 128, adam'),
 }

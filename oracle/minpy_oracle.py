@@ -639,3 +639,29 @@ def maxpool2d_bwd(dy, arg, xshape):
     dx = np.zeros((N * C, H * W), dtype=dy.dtype)
     np.add.at(dx, (np.arange(N * C).reshape(-1, 1), arg.reshape(N * C, -1)), dy.reshape(N * C, -1))
     return dx.reshape(xshape)
+
+
+# Tape-level wrappers so that CNN workloads can be differentiated by this oracle's tape the
+# way `core.Function` exposes a symbol graph as one primitive (minpy/core.py:148-190).
+def _conv_prim_fwd(x, w, b, stride=1, pad=0):
+    return conv2d_fwd(x, w, b, stride, pad)
+
+
+conv2d = primitive(_conv_prim_fwd, {
+    0: lambda ans, x, w, b, stride=1, pad=0: (lambda g: conv2d_bwd(x, w, g, stride, pad)[0]),
+    1: lambda ans, x, w, b, stride=1, pad=0: (lambda g: conv2d_bwd(x, w, g, stride, pad)[1]),
+    2: lambda ans, x, w, b, stride=1, pad=0: (lambda g: conv2d_bwd(x, w, g, stride, pad)[2])})
+
+
+def _pool_vjp(ans, x, k=2, stride=2):
+    _, arg = maxpool2d_fwd(x, k, stride)
+    return lambda g: maxpool2d_bwd(g, arg, x.shape)
+
+
+maxpool2d = primitive(lambda x, k=2, stride=2: maxpool2d_fwd(x, k, stride)[0], {0: _pool_vjp})
+# MXNet Activation('relu') backward is out_grad * (out > 0): zero at x == 0, unlike layers.relu
+relu_mx = primitive(lambda x: np.maximum(x, 0), {0: lambda ans, x: (lambda g: g * (ans > 0))})
+
+
+def flatten(x):
+    return x.reshape(x.shape[0], int(np.prod(x.shape[1:])))

@@ -1,0 +1,202 @@
+"""The `mx.sym` façade (minpy_b200/symbol.py) and its lowering (minpy_b200/symbol_exec.py)
+behind `minpy.core.Function` -- the conv path of examples/nn/cnn.py:26-60.
+
+CPU tests: naming / argument order / shape inference restated from MXNet 0.9, and the oracle's
+NumPy convolution / pooling checked by central differences (convolution numerics are "parity
+unpinned": MXNet is an un-vendored dependency, no reference vectors exist -- SURVEY.md 8c).
+GPU tests: forward values and every gradient of Function graphs against the oracle
+(FP32 CUDA-core mode 1e-5; TF32 tensor-core mode 1e-2), and a Solver step of the ref-shaped net.
+"""
+import numpy as np
+import pytest
+
+from oracle import minpy_oracle as orc
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    return float(np.max(np.abs(a - b)) / max(1e-30, np.max(np.abs(b))))
+
+
+def cnn_symbol():
+    import mxnet as mx
+    net = mx.sym.Variable(name='X')
+    net = mx.sym.Convolution(data=net, name='conv', kernel=(7, 7), num_filter=32)
+    net = mx.sym.Activation(data=net, act_type='relu')
+    net = mx.sym.Pooling(data=net, name='pool', pool_type='max', kernel=(2, 2), stride=(2, 2))
+    return mx.sym.Flatten(data=net)
+
+
+def test_facade_names_and_shapes_of_reference_cnn():
+    net = cnn_symbol()
+    assert net.list_arguments() == ['X', 'conv_weight', 'conv_bias']          # examples/nn/cnn.py relies on these names
+    assert net.list_auxiliary_states() == []
+    assert len(net.list_outputs()) == 1 and net.list_outputs()[0].endswith('_output')
+    args, outs, aux = net.infer_shape(X=(128, 3, 32, 32))
+    assert args == [(128, 3, 32, 32), (32, 3, 7, 7), (32,)]
+    assert outs == [(128, 5408)] and aux == []                                # 32 * 13 * 13
+    from minpy.core import Function
+    f = Function(net, input_shapes={'X': (128, 3, 32, 32)}, name='conv')
+    assert f.get_params() == {'conv_weight': {'shape': (32, 3, 7, 7)}, 'conv_bias': {'shape': (32,)}}
+    assert f.get_one_output_shape() == (128, 5408)
+
+
+def test_facade_fullyconnected_batchnorm_softmax_conventions():
+    import mxnet as mx
+    x = mx.sym.Variable('data')
+    fc = mx.sym.FullyConnected(data=x, name='fc1', num_hidden=7)
+    bn = mx.sym.BatchNorm(data=fc, name='bn1')
+    out = mx.sym.SoftmaxOutput(data=bn, name='softmax')
+    assert out.list_arguments() == ['data', 'fc1_weight', 'fc1_bias', 'bn1_gamma', 'bn1_beta', 'softmax_label']
+    assert out.list_auxiliary_states() == ['bn1_moving_mean', 'bn1_moving_var']
+    args, outs, aux = out.infer_shape(data=(5, 11))
+    assert args == [(5, 11), (7, 11), (7,), (7,), (7,), (5,)]                 # FC weight is (out, in)
+    assert outs == [(5, 7)] and aux == [(7,), (7,)]
+    a = mx.sym.Activation(data=x)                                             # auto-naming
+    b = mx.sym.Activation(data=x)
+    assert a.name != b.name and a.name.startswith('activation')
+    with pytest.raises(ValueError):
+        mx.sym.Convolution(data=x, kernel=(9, 9), num_filter=2).infer_shape(data=(1, 1, 4, 4))
+    with pytest.raises(AttributeError):
+        mx.nd  # pylint: disable=pointless-statement
+
+
+def test_function_rejects_non_symbols():
+    from minpy.core import Function, MXNetSymbolError
+    with pytest.raises(MXNetSymbolError):
+        Function(object())
+
+
+def test_oracle_conv_pool_by_central_differences():
+    """The oracle's conv / pool restatement has no reference vectors: pin it numerically."""
+    rng = np.random.RandomState(0)
+    x = rng.randn(2, 3, 6, 6)
+    w = rng.randn(4, 3, 3, 3) * 0.5
+    b = rng.randn(4) * 0.1
+    for stride, pad in ((1, 1), (1, 0), (2, 1)):
+        y = orc.conv2d_fwd(x, w, b, stride, pad)
+        c = rng.randn(*y.shape)
+        dx, dw, db = orc.conv2d_bwd(x, w, c, stride, pad)
+        f = lambda xx, ww, bb: float(np.sum(orc.conv2d_fwd(xx, ww, bb, stride, pad) * c))
+        eps = 1e-6
+        for arr, grad, which in ((x, dx, 0), (w, dw, 1), (b, db, 2)):
+            for _ in range(6):
+                idx = tuple(rng.randint(0, s) for s in arr.shape)
+                old = arr[idx]
+                arr[idx] = old + eps
+                fp = f(x, w, b)
+                arr[idx] = old - eps
+                fm = f(x, w, b)
+                arr[idx] = old
+                assert abs((fp - fm) / (2 * eps) - grad[idx]) <= 1e-5 * max(1.0, abs(grad[idx])), (stride, pad, which)
+    # direct definition on one output element
+    y = orc.conv2d_fwd(x, w, b, 1, 1)
+    xp = np.pad(x, ((0, 0), (0, 0), (1, 1), (1, 1)))
+    assert abs(y[1, 2, 3, 4] - (np.sum(xp[1, :, 3:6, 4:7] * w[2]) + b[2])) < 1e-12
+    p, arg = orc.maxpool2d_fwd(x, 2, 2)
+    assert p.shape == (2, 3, 3, 3) and p[0, 1, 2, 1] == x[0, 1, 4:6, 2:4].max()
+    dxp = orc.maxpool2d_bwd(np.ones_like(p), arg, x.shape)
+    assert dxp.sum() == p.size and set(np.unique(dxp)) <= {0.0, 1.0}
+
+
+# ------------------------------------------------------------------------------- GPU ------
+def _oracle_trunk(x, params, convs, pad):
+    h = x
+    for c in convs:
+        h = orc.maxpool2d(orc.relu_mx(orc.conv2d(h, params[c + '_weight'], params[c + '_bias'], 1, pad)), 2, 2)
+    return orc.flatten(h)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('mode,tol', [('fp32', 2e-5), ('tf32', 1e-2)])
+@pytest.mark.parametrize('net', ['ref7x7', 'c4'])
+def test_function_conv_trunk_matches_oracle(net, mode, tol):
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    import minpy.numpy as mnp
+    import mxnet as mx
+    from minpy import core
+    from minpy_b200 import ops
+    rng = np.random.RandomState(3)
+    N = 6
+    sym = mx.sym.Variable(name='X')
+    if net == 'ref7x7':
+        spec, pad = [('conv', 7, 32)], 0
+    else:
+        spec, pad = [('conv0', 3, 32), ('conv1', 3, 64), ('conv2', 3, 128)], 1
+    for name, k, f in spec:
+        sym = mx.sym.Convolution(data=sym, name=name, kernel=(k, k), pad=(pad, pad), num_filter=f)
+        sym = mx.sym.Activation(data=sym, act_type='relu')
+        sym = mx.sym.Pooling(data=sym, pool_type='max', kernel=(2, 2), stride=(2, 2))
+    sym = mx.sym.Flatten(data=sym)
+    fn = core.Function(sym, input_shapes={'X': (N, 3, 32, 32)}, name='trunk')
+    x = rng.randn(N, 3, 32, 32).astype(np.float32)
+    params = dict((k, (rng.randn(*v['shape']) * (0.2 if k.endswith('weight') else 0.05)).astype(np.float32))
+                  for k, v in fn.get_params().items())
+    names = sorted(params)
+    cw = rng.randn(*fn.get_one_output_shape()).astype(np.float32)
+    ops.set_gemm_precision(mode)
+    try:
+        def loss(xx, *ps):
+            return mnp.sum(fn(X=xx, **dict(zip(names, ps))) * mnp.array(cw))
+        grads, val = core.grad_and_loss(loss, argnum=range(len(names) + 1))(mnp.array(x), *[mnp.array(params[k]) for k in names])
+    finally:
+        ops.set_gemm_precision('tf32')
+    p64 = dict((k, v.astype(np.float64)) for k, v in params.items())
+    convs = [s[0] for s in spec]
+
+    def oloss(xx, *ps):
+        return orc.sum(_oracle_trunk(xx, dict(zip(names, ps)), convs, pad) * cw.astype(np.float64))
+    ograds, oval = orc.grad_and_loss(oloss, argnum=range(len(names) + 1))(x.astype(np.float64), *[p64[k] for k in names])
+    assert abs(float(val.asnumpy()) - float(oval)) <= tol * max(1.0, abs(float(oval)))
+    for g, og, nm in zip(grads, ograds, ['X'] + names):
+        assert rel(g.asnumpy(), og) <= tol * (3 if mode == 'tf32' else 1), nm
+
+
+@pytest.mark.gpu
+def test_function_skips_data_gradient_and_trains_reference_cnn():
+    """Solver steps of the examples/nn/cnn.py network (small batch) against the oracle."""
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    import minpy.numpy as mnp
+    from minpy.nn.io import NDArrayIter
+    from minpy.nn.solver import Solver
+    from minpy_b200 import workloads, ops
+    B = 8
+    model = workloads.RefConvNet(batch=B, hidden=32)
+    X, Y = workloads.cifar_like(B * 2, seed=9)
+    it = NDArrayIter(X, Y, batch_size=B, shuffle=False)
+    solver = Solver(model, it, it, update_rule='sgd_momentum', optim_config={'learning_rate': 1e-2, 'momentum': 0.9},
+                    init_rule='gaussian', init_config={'stdvar': 0.05}, verbose=False)
+    solver.init()
+    init = workloads.init_params(model, 5, scale=0.05)
+    for k, v in init.items():
+        model.params[k] = mnp.array(v)
+    ops.set_gemm_precision('fp32')
+    try:
+        for batch in it:
+            solver._step(batch)  # pylint: disable=protected-access
+    finally:
+        ops.set_gemm_precision('tf32')
+    # oracle: same two steps
+    names = list(init.keys())
+    p = dict((k, v.astype(np.float64)) for k, v in init.items())
+    cfg = dict((k, {'learning_rate': 1e-2, 'momentum': 0.9}) for k in names)
+    losses = []
+    for i in range(2):
+        xb, yb = X[i * B:(i + 1) * B].astype(np.float64), Y[i * B:(i + 1) * B]
+
+        def f(*ps):
+            q = dict(zip(names, ps))
+            h = _oracle_trunk(xb, q, ['conv'], 0)
+            h = orc.relu(orc.affine(h, q['w1'], q['b1']))
+            return orc.softmax_loss(orc.affine(h, q['w2'], q['b2']), yb)
+        grads, loss = orc.grad_and_loss(f, argnum=range(len(names)))(*[p[k] for k in names])
+        losses.append(float(loss))
+        for k, g in zip(names, grads):
+            p[k], cfg[k] = orc.sgd_momentum(p[k], g, cfg[k])
+    got = [float(l.asnumpy()) for l in solver.loss_history]
+    assert rel(np.array(got), np.array(losses)) <= 1e-4
+    for k in names:
+        assert rel(model.params[k].asnumpy(), p[k]) <= 1e-4, k
