@@ -1,0 +1,62 @@
+#!/usr/bin/env python
+"""Summaries of ncu output kept under profiles/ (run in the build container; no GPU needed).
+
+    python profiles/summarize_ncu.py launches gpurun_out/x_launches.csv  > profiles/x_launches.txt
+    python profiles/summarize_ncu.py full gpurun_out/x_prof.ncu-rep      > profiles/x_prof.txt
+"""
+import collections
+import csv
+import re
+import subprocess
+import sys
+
+FULL_METRICS = [
+    'gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'launch__registers_per_thread',
+    'launch__shared_mem_per_block_dynamic', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
+    'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', 'lts__throughput.avg.pct_of_peak_sustained_elapsed',
+    'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active',
+    'sm__warps_active.avg.pct_of_peak_sustained_active', 'sm__cycles_elapsed.max',
+    'l1tex__t_bytes.sum', 'lts__t_bytes.sum', 'smsp__inst_executed.sum',
+]
+
+
+def launches(path):
+    with open(path) as f:
+        lines = [l for l in f if l.startswith('"')]
+    r = csv.reader(lines)
+    hdr = next(r)
+    ki, vi, ui = hdr.index('Kernel Name'), hdr.index('Metric Value'), hdr.index('Metric Unit')
+    agg = collections.OrderedDict()
+    n = 0
+    for row in r:
+        v = float(row[vi].replace(',', ''))
+        v = v / 1000 if row[ui] == 'ns' else (v * 1000 if row[ui] == 'ms' else v)
+        short = re.sub(r'<.*', '', re.sub(r'\(.*', '', row[ki])).replace('void ', '')
+        a = agg.setdefault(short, [0, 0.0])
+        a[0] += 1
+        a[1] += v
+        n += 1
+    tot = sum(v[1] for v in agg.values())
+    print('# ncu --metrics gpu__time_duration.sum --clock-control none  (cold-cache, serialised: compare SHARES)')
+    print('# %s: %d launches, %.1f us summed kernel time' % (path, n, tot))
+    print('%-44s %7s %12s %8s' % ('kernel', 'count', 'us/launch', 'share'))
+    for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print('%-44s %7d %12.2f %7.1f%%' % (k[-44:], v[0], v[1] / v[0], 100 * v[1] / tot))
+
+
+def full(path):
+    out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    print('# ncu --set full --clock-control none --import-source on : %s' % path)
+    ki = hdr.index('Kernel Name')
+    for j, row in enumerate(data):
+        print('launch %d: %s' % (j, row[ki][:110]))
+        for m in FULL_METRICS:
+            if m in hdr:
+                i = hdr.index(m)
+                print('    %-66s %16s %s' % (m, row[i], units[i]))
+
+
+if __name__ == '__main__':
+    {'launches': launches, 'full': full}[sys.argv[1]](sys.argv[2])
