@@ -263,6 +263,9 @@ int mc_rand_normal(float* out, int64_t n, uint64_t seed, uint64_t offset);
 /* ---------------------------------------------------- convolution / pooling -- */
 /* NCHW cross-correlation, the MXNet `Convolution` / `Pooling(max)` / `Activation(relu)`
  * symbols reached through core.Function (minpy/core.py:148-190; examples/nn/cnn.py:32-40). */
+/* precision (mc_gemm_precision): 1 = implicit GEMM on tcgen05 (kind::tf32, TMA-gathered windows, FP32
+ * accumulate in TMEM) when stride == 1 and rows are 16-byte multiples; 0 = direct FP32 CUDA-core kernels
+ * (exact accumulate; also the fallback for shapes the tensor-core path does not cover). */
 int mc_conv2d_fwd(const float* x, const float* w, const float* bias, float* y,
                   int64_t N, int64_t C, int64_t H, int64_t W, int64_t F, int64_t KH, int64_t KW,
                   int64_t stride, int64_t pad, int relu, int precision);
@@ -272,6 +275,35 @@ int mc_conv2d_dgrad(const float* dy, const float* w, float* dx,
 int mc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* dbias,
                     int64_t N, int64_t C, int64_t H, int64_t W, int64_t F, int64_t KH, int64_t KW,
                     int64_t stride, int64_t pad, int precision);
+/* Channels-last (NHWC) convolution path -- what the tensor-core kernels natively consume.  TMA needs
+ * the innermost box coordinate 16-byte aligned, so the filter-tap shifts must fall on outer
+ * dimensions: activations are (N, H, W, Cp) with Cp = channel pitch, a multiple of 4.  The symbol
+ * executor (minpy_b200/symbol_exec.py, the stand-in for the MXNet executor of minpy/core.py:148-190)
+ * keeps a whole conv trunk in this layout and converts at its boundaries.
+ *   x  : (N, H, W + 2*wpad, Cp), physically zero-padded along W by wpad pixels per side; wpad is
+ *        either 0 or == pad with KW*Cp <= 32 ("merged" few-channel mode: one k-block per filter row);
+ *   w  : (F, C, KH, KW), the reference layout (examples/nn/cnn.py conv_weight);   stride is 1;
+ *   y / dy : (N, OH, OW, Fp);  pitch channels (>= C / >= F) are written as zeros by the producers. */
+int mc_nchw_to_nhwc(const float* x, float* y, int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp, int64_t wpad);
+int mc_nhwc_to_nchw(const float* x, float* y, int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp);
+int mc_conv2d_nhwc_fwd(const float* x, const float* w, const float* bias, float* y,
+                       int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp, int64_t wpad,
+                       int64_t F, int64_t Fp, int64_t KH, int64_t KW, int64_t pad, int relu);
+int mc_conv2d_nhwc_dgrad(const float* dy, const float* w, float* dx,
+                         int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp,
+                         int64_t F, int64_t Fp, int64_t KH, int64_t KW, int64_t pad);
+int mc_conv2d_nhwc_wgrad(const float* x, const float* dy, float* dw, float* dbias,
+                         int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp, int64_t wpad,
+                         int64_t F, int64_t Fp, int64_t KH, int64_t KW, int64_t pad);
+/* NHWC max pooling; idx_u8 = kh*KW + kw of the first maximal element of each window.  bwd needs
+ * non-overlapping windows (stride == K): a gather, no atomics; relu_y (optional, the pooled output of
+ * a relu'd tensor) folds the producer's relu mask `out > 0` into the same pass. */
+int mc_maxpool2d_nhwc_fwd(const float* x, float* y, uint8_t* idx_u8, int64_t N, int64_t H, int64_t W, int64_t Cp,
+                          int64_t KH, int64_t KW, int64_t stride);
+int mc_maxpool2d_nhwc_bwd(const float* dy, const uint8_t* idx_u8, const float* relu_y, float* dx,
+                          int64_t N, int64_t H, int64_t W, int64_t Cp, int64_t K, int64_t OH, int64_t OW);
+/* Which path the last mc_conv2d_* call on this thread took (0 direct fp32, 1 tcgen05 implicit GEMM). */
+int mc_conv_last_path(int* path);
 int mc_maxpool2d_fwd(const float* x, float* y, int32_t* argmax_i32, int64_t NC, int64_t H, int64_t W,
                      int64_t KH, int64_t KW, int64_t stride);
 int mc_maxpool2d_bwd(const float* dy, const int32_t* argmax_i32, float* dx_zeroed, int64_t NC,

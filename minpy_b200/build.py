@@ -18,7 +18,7 @@ BUILD_DIR = os.path.join(HERE, '_build')
 LIB_PATH = os.path.join(HERE, 'libminpy_cuda.so')
 HEADER = os.path.join(os.path.dirname(HERE), 'include', 'minpy_cuda.h')
 
-SOURCES = ['runtime.cu', 'elementwise.cu', 'reduce.cu', 'softmax.cu', 'index.cu', 'gemm.cu', 'layers.cu', 'conv.cu']
+SOURCES = ['runtime.cu', 'elementwise.cu', 'reduce.cu', 'softmax.cu', 'index.cu', 'gemm.cu', 'layers.cu', 'conv.cu', 'conv_tc.cu']
 
 NVCC_FLAGS = [
     '-gencode', 'arch=compute_100a,code=sm_100a',
@@ -45,7 +45,7 @@ def _stale(target: str, deps: list[str]) -> bool:
 
 def _compile(src: str, force: bool, verbose: bool) -> str:
     obj = os.path.join(BUILD_DIR, os.path.splitext(src)[0] + '.o')
-    deps = [os.path.join(CSRC, src), os.path.join(CSRC, 'common.cuh'), HEADER, os.path.abspath(__file__)]
+    deps = [os.path.join(CSRC, src), os.path.join(CSRC, 'common.cuh'), os.path.join(CSRC, 'tc_common.cuh'), HEADER, os.path.abspath(__file__)]
     if force or _stale(obj, deps):
         cmd = [_nvcc()] + NVCC_FLAGS + ['-c', os.path.join(CSRC, src), '-o', obj]
         res = subprocess.run(cmd, capture_output=True, text=True)

@@ -145,6 +145,28 @@ __global__ void __launch_bounds__(CV_THREADS) maxpool_bwd_kernel(const float* __
 
 int reduce_sum_internal(const float* x, float* out, int64_t outer, int64_t red, int64_t inner);
 
+static int round4(int64_t v) { return (int)((v + 3) / 4 * 4); }
+
+// Scratch device buffer freed (stream-ordered) when it goes out of scope.
+struct Scratch {
+  float* p = nullptr;
+  int alloc(size_t n) {
+    cudaError_t e = cudaMallocAsync((void**)&p, sizeof(float) * (n ? n : 1), stream());
+    if (e != cudaSuccess) { set_error("cudaMallocAsync(conv scratch): %s", cudaGetErrorString(e)); p = nullptr; return 1; }
+    return 0;
+  }
+  ~Scratch() { if (p) cudaFreeAsync(p, stream()); }
+};
+
+// The tensor-core path works on channels-last tensors (conv_tc.cu).  Stride-1 convolutions on
+// NCHW tensors are served by converting at the boundary; callers that keep activations
+// channels-last (the symbol executor) use the mc_conv2d_nhwc_* entry points directly.
+static bool tc_eligible(int64_t stride, int64_t C, int64_t KH, int64_t KW) {
+  return stride == 1 && round4(C) <= 256 && KH * KW <= 255;
+}
+
+static thread_local int g_conv_last_path = -1;
+
 }  // namespace mc
 
 using namespace mc;
@@ -153,10 +175,20 @@ extern "C" {
 
 int mc_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int64_t N, int64_t C, int64_t H, int64_t W,
                   int64_t F, int64_t KH, int64_t KW, int64_t stride, int64_t pad, int relu, int precision) {
-  (void)precision;
   MC_REQUIRE(stride >= 1 && pad >= 0, "bad stride/pad");
   const int64_t OH = (H + 2 * pad - KH) / stride + 1, OW = (W + 2 * pad - KW) / stride + 1;
   MC_REQUIRE(OH > 0 && OW > 0, "kernel larger than padded input");
+  if (precision == MC_GEMM_TF32 && tc_eligible(stride, C, KH, KW) && N * C * H * W > 0) {
+    g_conv_last_path = 1;
+    const int Cp = round4(C), Fp = round4(F);
+    const int64_t wpad = (KW * Cp <= 32) ? pad : 0;
+    Scratch xh, yh;
+    if (xh.alloc((size_t)N * H * (W + 2 * wpad) * Cp) || yh.alloc((size_t)N * OH * OW * Fp)) return 1;
+    if (int rc = mc_nchw_to_nhwc(x, xh.p, N, C, H, W, Cp, wpad)) return rc;
+    if (int rc = mc_conv2d_nhwc_fwd(xh.p, w, bias, yh.p, N, C, H, W, Cp, wpad, F, Fp, KH, KW, pad, relu)) return rc;
+    return mc_nhwc_to_nchw(yh.p, y, N, F, OH, OW, Fp);
+  }
+  g_conv_last_path = 0;
   MC_REQUIRE(F <= 65535 && N <= 65535, "F and N must be <= 65535");
   const size_t smem = sizeof(float) * C * KH * KW;
   MC_REQUIRE(smem <= 48 * 1024, "filter slice exceeds 48 KB of shared memory");
@@ -169,9 +201,19 @@ int mc_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, i
 
 int mc_conv2d_dgrad(const float* dy, const float* w, float* dx, int64_t N, int64_t C, int64_t H, int64_t W, int64_t F,
                     int64_t KH, int64_t KW, int64_t stride, int64_t pad, int precision) {
-  (void)precision;
   const int64_t OH = (H + 2 * pad - KH) / stride + 1, OW = (W + 2 * pad - KW) / stride + 1;
   MC_REQUIRE(OH > 0 && OW > 0, "kernel larger than padded input");
+  // data gradient = stride-1 correlation of dy with the flipped filter, pad' = K - 1 - pad
+  if (precision == MC_GEMM_TF32 && KH == KW && KH - 1 - pad >= 0 && tc_eligible(stride, F, KH, KW) && N * C * H * W > 0) {
+    g_conv_last_path = 1;
+    const int Cp = round4(C), Fp = round4(F);
+    Scratch dyh, dxh;
+    if (dyh.alloc((size_t)N * OH * OW * Fp) || dxh.alloc((size_t)N * H * W * Cp)) return 1;
+    if (int rc = mc_nchw_to_nhwc(dy, dyh.p, N, F, OH, OW, Fp, 0)) return rc;
+    if (int rc = mc_conv2d_nhwc_dgrad(dyh.p, w, dxh.p, N, C, H, W, Cp, F, Fp, KH, KW, pad)) return rc;
+    return mc_nhwc_to_nchw(dxh.p, dx, N, C, H, W, Cp);
+  }
+  g_conv_last_path = 0;
   MC_REQUIRE(C <= 65535 && N <= 65535, "C and N must be <= 65535");
   const size_t smem = sizeof(float) * F * KH * KW;
   MC_REQUIRE(smem <= 48 * 1024, "filter slice exceeds 48 KB of shared memory");
@@ -184,11 +226,24 @@ int mc_conv2d_dgrad(const float* dy, const float* w, float* dx, int64_t N, int64
 
 int mc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* dbias, int64_t N, int64_t C, int64_t H, int64_t W,
                     int64_t F, int64_t KH, int64_t KW, int64_t stride, int64_t pad, int precision) {
-  (void)precision;
   const int64_t OH = (H + 2 * pad - KH) / stride + 1, OW = (W + 2 * pad - KW) / stride + 1;
   MC_REQUIRE(OH > 0 && OW > 0, "kernel larger than padded input");
   const int64_t nw = F * C * KH * KW;
-  if (dw) {
+  bool dw_done = false;
+  if (dw && precision == MC_GEMM_TF32 && tc_eligible(stride, C, KH, KW) && N * C * H * W > 0) {
+    g_conv_last_path = 1;
+    const int Cp = round4(C), Fp = round4(F);
+    const int64_t wpad = (KW * Cp <= 32) ? pad : 0;
+    Scratch xh, dyh;
+    if (xh.alloc((size_t)N * H * (W + 2 * wpad) * Cp) || dyh.alloc((size_t)N * OH * OW * Fp)) return 1;
+    if (int rc = mc_nchw_to_nhwc(x, xh.p, N, C, H, W, Cp, wpad)) return rc;
+    if (int rc = mc_nchw_to_nhwc(dy, dyh.p, N, F, OH, OW, Fp, 0)) return rc;
+    if (int rc = mc_conv2d_nhwc_wgrad(xh.p, dyh.p, dw, nullptr, N, C, H, W, Cp, wpad, F, Fp, KH, KW, pad)) return rc;
+    dw_done = true;
+  } else if (dw) {
+    g_conv_last_path = 0;
+  }
+  if (dw && !dw_done) {
     int splits = 1;
     if (nw < 4 * (int64_t)sm_count()) {
       splits = (int)((4 * (int64_t)sm_count() + nw - 1) / nw);
@@ -217,6 +272,11 @@ int mc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* dbias, in
     MC_CHECK(cudaFreeAsync(tmp, stream()));
     if (rc) return rc;
   }
+  return 0;
+}
+
+int mc_conv_last_path(int* path) {
+  *path = g_conv_last_path;
   return 0;
 }
 

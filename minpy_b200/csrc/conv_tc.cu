@@ -1,0 +1,712 @@
+// Implicit-GEMM convolution on the sm_100a tensor cores: the `Convolution` symbol the reference
+// reaches through core.Function (minpy/core.py:148-190; examples/nn/cnn.py:32-40), which MXNet
+// ran through cuDNN.  No im2col buffer ever exists in HBM: TMA gathers the shifted input windows
+// straight into the UMMA operand layout, tcgen05.mma (kind::tf32) accumulates in TMEM and the
+// epilogue writes the activation with bias / relu fused.
+//
+// Layout.  Activations are channels-last (N, H, W, Cp), Cp = channels rounded up to 4 (16 B):
+// TMA requires the innermost start coordinate of a box to be 16-byte aligned (measured on this
+// part: a +-1 element shift along W of an NCHW tensor raises "illegal instruction"), so the
+// filter-tap shifts must land on OUTER dimensions.  The symbol executor keeps whole conv trunks
+// in this layout and converts NCHW <-> NHWC only at their boundaries.
+//
+//   forward / data-gradient (stride 1):  D[pixel, n] = sum_{tap, k} A[pixel, (tap,k)] * B[n, (tap,k)]
+//       A: for one tap and a block of 32 channels, 32 consecutive output pixels (a "chunk") are
+//          ONE 4-D TMA box {32 ch, bw, bh, 1} at (c0, ow0+kw-pad, oh0+kh-pad, n) -> 32 rows of
+//          128 B = a K-major SWIZZLE_128B operand block; halo / channel overrun is zero-filled by
+//          TMA.  A CTA tile is 4 chunks = 128 pixels = the 128 TMEM lanes.
+//       B: weights repacked per call to [tap][n][k] (k contiguous): K-major too.
+//       "merged" mode for few channels (KW * Cp <= 32, e.g. RGB): the input is physically padded
+//          along W and one box row is the contiguous run of KW pixels x Cp channels, so a tap is a
+//          filter ROW and the first layer costs KH k-blocks instead of KH*KW.
+//       dgrad is the same kernel on dy with the filter flipped and k/n swapped (pad' = K-1-pad).
+//   weight-gradient:  D[f, n] = sum_{pixel} dy[pixel, f] * x[pixel + tap, n]   per tap
+//       both operands MN-major (f / channels contiguous), SWIZZLE_128B_ATOM_32B blocks of
+//       [32 pixels][32 f|c]; the pixel range is split over CTAs and reduced deterministically.
+//
+// Output pixels are enumerated over a "virtual" image whose row width is a divisor or multiple of
+// 32 so that a chunk is a rectangle; virtual pixels outside the real output are computed on zeros
+// and masked in the epilogue.
+#include "tc_common.cuh"
+
+namespace mc {
+
+int reduce_sum_internal(const float* x, float* out, int64_t outer, int64_t red, int64_t inner);   // reduce.cu
+
+namespace tc {
+
+constexpr int CONV_THREADS = 128;
+constexpr int BKC = 32;        // channels (fp32) per k-block = one 128-byte swizzle row
+
+struct ConvGeom {
+  int N, OH, OW;         // real output extent (pixels the epilogue keeps)
+  int OHv, OWv;          // virtual extent enumerated by chunks
+  int bw, bh;            // chunk rectangle: bw * bh == 32
+  int cpr, cpi;          // chunks per virtual row (OWv >= 32) / per image
+  int total_chunks;
+  int dh0, dw0;          // input coordinate = output coordinate + tap + d?0
+  int TH, TW;            // taps along h / w enumerated by the kernel
+};
+
+__device__ __forceinline__ void chunk_origin(const ConvGeom& g, int chunk, int& n, int& oh0, int& ow0) {
+  n = chunk / g.cpi;
+  const int r = chunk - n * g.cpi;
+  if (g.OWv >= 32) { oh0 = r / g.cpr; ow0 = (r - oh0 * g.cpr) * 32; }
+  else { oh0 = r * g.bh; ow0 = 0; }
+  if (chunk >= g.total_chunks) n = g.N;   // fully out of bounds: TMA fills zeros, epilogue masks
+}
+
+struct ConvFwdParams {
+  ConvGeom g;
+  float* y;              // (N, OH, OW, ldy)
+  const float* bias;     // (Nout,) or nullptr
+  int Nout, ldy;         // real output channels, channel pitch of y
+  int BN, ncb, stages, relu;
+};
+
+// grid.x = tiles of 4 chunks, grid.y = tiles of BN output channels
+__global__ void __launch_bounds__(CONV_THREADS, 1) conv_igemm_kernel(const __grid_constant__ CUtensorMap tmX,
+                                                                      const __grid_constant__ CUtensorMap tmW,
+                                                                      const ConvFwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  constexpr uint32_t chunk_bytes = 32u * 128u;                    // [32 pixels][32 ch]
+  constexpr uint32_t a_bytes = 4u * chunk_bytes;
+  const uint32_t b_bytes = (uint32_t)p.BN * 128u;                 // [BN][32 ch]
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const int STAGES = p.stages;
+  const uint32_t bar_base = smem_base + STAGES * stage_bytes;
+  const uint32_t tmem_slot = bar_base + (2 * STAGES + 1) * 8;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int chunk0 = blockIdx.x * 4;
+  const int n0 = blockIdx.y * p.BN;
+  const int taps = p.g.TH * p.g.TW;
+  const int num_it = taps * p.ncb;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)p.BN)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------ TMA producer ------------------------------------
+    int cn[4], coh[4], cow[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) chunk_origin(p.g, chunk0 + j, cn[j], coh[j], cow[j]);
+    int it = 0;
+    for (int tap = 0; tap < taps; ++tap) {
+      const int th = tap / p.g.TW, tw = tap - th * p.g.TW;
+      for (int cb = 0; cb < p.ncb; ++cb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        mbar_wait(empty_bar(s), ph ^ 1u);
+        mbar_expect_tx(full_bar(s), stage_bytes);
+        const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          tma_load_4d(sa + j * chunk_bytes, &tmX, full_bar(s), cb * BKC, cow[j] + tw + p.g.dw0, coh[j] + th + p.g.dh0, cn[j]);
+        tma_load_3d(sb, &tmW, full_bar(s), cb * BKC, n0, tap);
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ------------------------------ MMA issuer --------------------------------------
+    // c_format F32, a/b TF32, both operands K-major, N>>3 at [17,23), M>>4 at [24,29)
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    for (int it = 0; it < num_it; ++it) {
+      const int s = it % STAGES;
+      const uint32_t ph = (it / STAGES) & 1;
+      mbar_wait(full_bar(s), ph);
+      tcgen05_fence_after();
+      const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+#pragma unroll
+      for (int k = 0; k < BKC / UMMA_K; ++k) {
+        const uint64_t adesc = make_desc(sa + k * 32, 16, 1024, 2);
+        const uint64_t bdesc = make_desc(sb + k * 32, 16, 1024, 2);
+        umma_tf32(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+      }
+      umma_commit(empty_bar(s));
+    }
+    umma_commit(tmem_full_bar);
+  }
+  __syncwarp();
+
+  // ---------------------------------- epilogue ----------------------------------------
+  mbar_wait(tmem_full_bar, 0);
+  tcgen05_fence_after();
+  __syncwarp();
+  int n, oh0, ow0;
+  chunk_origin(p.g, chunk0 + warp, n, oh0, ow0);
+  int oh, ow;
+  if (p.g.OWv >= 32) { oh = oh0; ow = ow0 + lane; }
+  else { oh = oh0 + lane / p.g.OWv; ow = lane % p.g.OWv; }
+  const bool live = (n < p.g.N) && (oh < p.g.OH) && (ow < p.g.OW);
+  float* __restrict__ yrow = p.y + (((int64_t)n * p.g.OH + oh) * p.g.OW + ow) * p.ldy;
+  const bool vec_ok = ((p.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15u) == 0);
+#pragma unroll 1
+  for (int c0 = 0; c0 < p.BN; c0 += 32) {
+    float v[32];
+    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+    if (live) {
+      const int f0 = n0 + c0;
+      if (vec_ok && f0 + 32 <= p.Nout) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          if (p.bias) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + f0 + j));
+            o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+          }
+          if (p.relu) {
+            o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
+            o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
+          }
+          *reinterpret_cast<float4*>(yrow + f0 + j) = o;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int f = f0 + j;
+          if (f < p.ldy) {                       // pitch padding is written as zeros
+            float o = 0.f;
+            if (f < p.Nout) {
+              o = v[j];
+              if (p.bias) o += __ldg(p.bias + f);
+              if (p.relu) o = (o != o) ? o : fmaxf(o, 0.f);
+            }
+            yrow[f] = o;
+          }
+        }
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.BN) : "memory");
+  }
+}
+
+// wp[tap][n][k] (k pitch Kp, zero padded) from w (F, C, KH, KW).
+//   mode 0 (forward)       : tap = kh*KW + kw, n = f, k = c
+//   mode 1 (forward merged): tap = kh,         n = f, k = kw*Cp + c
+//   mode 2 (dgrad)         : tap = (KH-1-kh)*KW + (KW-1-kw), n = c, k = f
+__global__ void __launch_bounds__(256) conv_pack_weights_kernel(const float* __restrict__ w, float* __restrict__ wp, int F,
+                                                                int C, int KH, int KW, int Cp, int taps, int Nn, int Kp,
+                                                                int mode) {
+  const int64_t total = (int64_t)taps * Nn * Kp;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+    const int k = (int)(i % Kp);
+    const int n = (int)((i / Kp) % Nn);
+    const int tap = (int)(i / ((int64_t)Kp * Nn));
+    float v = 0.f;
+    if (mode == 0) {
+      if (k < C) v = w[((int64_t)n * C + k) * KH * KW + tap];
+    } else if (mode == 1) {
+      const int kw = k / Cp, c = k - kw * Cp;
+      if (kw < KW && c < C) v = w[(((int64_t)n * C + c) * KH + tap) * KW + kw];
+    } else {
+      const int kh = KH - 1 - tap / KW, kw = KW - 1 - tap % KW;
+      if (k < F) v = w[(((int64_t)k * C + n) * KH + kh) * KW + kw];
+    }
+    wp[i] = v;
+  }
+}
+
+// ------------------------------------ weight gradient --------------------------------------
+struct ConvWgradParams {
+  ConvGeom g;            // geometry of dy (the output pixels)
+  float* ws;             // [splits][taps][F][Nn]
+  int F, Nn;             // filters; columns per tap (channel pitch, or KW*Cp merged)
+  int BNc, stages;       // BNc: Nn rounded up to 32
+  int chunks_per_split;
+};
+
+// grid.x = taps, grid.y = splits of the pixel range, grid.z = tiles of 128 filters
+__global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy,
+                                                                      const __grid_constant__ CUtensorMap tmX,
+                                                                      const ConvWgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  constexpr uint32_t blk = 32u * 128u;                          // [32 pixels][32 f|c]
+  constexpr uint32_t a_bytes = 4u * blk;                        // 128 filters
+  const uint32_t b_bytes = (uint32_t)(p.BNc / 32) * blk;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const int STAGES = p.stages;
+  const uint32_t bar_base = smem_base + STAGES * stage_bytes;
+  const uint32_t tmem_slot = bar_base + (2 * STAGES + 1) * 8;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tap = blockIdx.x;
+  const int th = tap / p.g.TW, tw = tap - th * p.g.TW;
+  const int f0 = blockIdx.z * 128;
+  const int cbeg = blockIdx.y * p.chunks_per_split;
+  const int cend = min(p.g.total_chunks, cbeg + p.chunks_per_split);
+  const int num_it = max(0, cend - cbeg);
+  uint32_t tcols = 32;
+  while ((int)tcols < p.BNc) tcols <<= 1;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tcols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0 && lane == 0) {
+    for (int it = 0; it < num_it; ++it) {
+      const int s = it % STAGES;
+      const uint32_t ph = (it / STAGES) & 1;
+      int n, oh0, ow0;
+      chunk_origin(p.g, cbeg + it, n, oh0, ow0);
+      mbar_wait(empty_bar(s), ph ^ 1u);
+      mbar_expect_tx(full_bar(s), stage_bytes);
+      const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) tma_load_4d(sa + j * blk, &tmDy, full_bar(s), f0 + 32 * j, ow0, oh0, n);
+      for (int j = 0; j < p.BNc / 32; ++j)
+        tma_load_4d(sb + j * blk, &tmX, full_bar(s), 32 * j, ow0 + tw + p.g.dw0, oh0 + th + p.g.dh0, n);
+    }
+  } else if (warp == 1 && lane == 0) {
+    // both operands MN-major (f / channels contiguous, pixels = K): major bits 15, 16 set
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(p.BNc >> 3) << 17) |
+                           ((uint32_t)(128 >> 4) << 24);
+    for (int it = 0; it < num_it; ++it) {
+      const int s = it % STAGES;
+      const uint32_t ph = (it / STAGES) & 1;
+      mbar_wait(full_bar(s), ph);
+      tcgen05_fence_after();
+      const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+#pragma unroll
+      for (int k = 0; k < 32 / UMMA_K; ++k) {
+        const uint64_t adesc = make_desc(sa + k * 1024, blk, 512, 1);
+        const uint64_t bdesc = make_desc(sb + k * 1024, blk, 512, 1);
+        umma_tf32(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+      }
+      umma_commit(empty_bar(s));
+    }
+    umma_commit(tmem_full_bar);
+  }
+  __syncwarp();
+
+  mbar_wait(tmem_full_bar, 0);
+  tcgen05_fence_after();
+  __syncwarp();
+  const int f = f0 + warp * 32 + lane;
+  const int taps = p.g.TH * p.g.TW;
+  float* __restrict__ dst = p.ws + (((int64_t)blockIdx.y * taps + tap) * p.F + f) * p.Nn;
+#pragma unroll 1
+  for (int c0 = 0; c0 < p.BNc; c0 += 32) {
+    float v[32];
+    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);   // c0 + 32 <= tcols always
+    if (f < p.F) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (c0 + j < p.Nn) dst[c0 + j] = (num_it > 0) ? v[j] : 0.f;
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tcols) : "memory");
+  }
+}
+
+// dw (F, C, KH, KW) = sum_s ws[s][tap][f][n]; merged: tap = kh, n = kw*Cp + c; else tap = kh*KW+kw, n = c
+__global__ void __launch_bounds__(256) conv_wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int splits,
+                                                                int taps, int F, int Nn, int C, int KH, int KW, int Cp,
+                                                                int merged) {
+  const int64_t total = (int64_t)F * C * KH * KW;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+    const int kw = (int)(i % KW), kh = (int)((i / KW) % KH);
+    const int c = (int)((i / (KW * KH)) % C), f = (int)(i / ((int64_t)KW * KH * C));
+    const int tap = merged ? kh : kh * KW + kw;
+    const int n = merged ? kw * Cp + c : c;
+    float s = 0.f;
+    for (int z = 0; z < splits; ++z) s += ws[(((int64_t)z * taps + tap) * F + f) * Nn + n];
+    dw[i] = s;
+  }
+}
+
+// ----------------------------------- layout conversion -------------------------------------
+// y (N, H, W + 2*wpad, Cp) <- x (N, C, H, W); pad pixels and pad channels are zero.
+// One CTA: 32 channels x 32 (padded) pixels of one (n, h) row, transposed through shared memory
+// so that both the NCHW reads (along w) and the NHWC writes (along c) are coalesced.
+__global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restrict__ x, float* __restrict__ y, int N, int C,
+                                                           int H, int W, int Cp, int wpad) {
+  __shared__ float tile[32][33];
+  const int Wp = W + 2 * wpad;
+  const int n = blockIdx.z / H, h = blockIdx.z % H;
+  const int c0 = blockIdx.y * 32, w0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = c0 + ty + 8 * j, w = w0 + tx - wpad;      // w0 indexes the padded row
+    float v = 0.f;
+    if (c < C && w >= 0 && w < W) v = x[(((int64_t)n * C + c) * H + h) * W + w];
+    tile[ty + 8 * j][tx] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int wp = w0 + ty + 8 * j, c = c0 + tx;
+    if (wp < Wp && c < Cp) y[(((int64_t)n * H + h) * Wp + wp) * Cp + c] = tile[tx][ty + 8 * j];
+  }
+}
+
+// y (N, C, H, W) <- x (N, H, W, Cp)
+__global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* __restrict__ x, float* __restrict__ y, int N, int C,
+                                                           int H, int W, int Cp) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z / H, h = blockIdx.z % H;
+  const int c0 = blockIdx.y * 32, w0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int w = w0 + ty + 8 * j, c = c0 + tx;
+    float v = 0.f;
+    if (w < W && c < C) v = x[(((int64_t)n * H + h) * W + w) * Cp + c];
+    tile[ty + 8 * j][tx] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = c0 + ty + 8 * j, w = w0 + tx;
+    if (c < C && w < W) y[(((int64_t)n * C + c) * H + h) * W + w] = tile[tx][ty + 8 * j];
+  }
+}
+
+// channels-last max pooling (window KH x KW, stride s, 'valid'); idx = kh*KW + kw of the FIRST
+// maximal element in row-major window order (the arg-max the NCHW kernel and the oracle pick).
+__global__ void __launch_bounds__(256) maxpool_nhwc_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                               uint8_t* __restrict__ idx, int N, int H, int W, int Cp, int KH,
+                                                               int KW, int stride, int OH, int OW) {
+  const int64_t total = (int64_t)N * OH * OW * Cp;
+  for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+    const int c = (int)(t % Cp);
+    const int ow = (int)((t / Cp) % OW), oh = (int)((t / ((int64_t)Cp * OW)) % OH);
+    const int n = (int)(t / ((int64_t)Cp * OW * OH));
+    float best = 0.f;
+    int bi = -1;
+    for (int kh = 0; kh < KH; ++kh)
+      for (int kw = 0; kw < KW; ++kw) {
+        const float v = x[(((int64_t)n * H + oh * stride + kh) * W + ow * stride + kw) * Cp + c];
+        if (bi < 0 || v > best || (v != v && best == best)) { best = v; bi = kh * KW + kw; }
+      }
+    y[t] = best;
+    if (idx) idx[t] = (uint8_t)bi;
+  }
+}
+
+// dx (N, H, W, Cp): non-overlapping windows (stride == kernel) -> every input element belongs to
+// at most one window: a pure gather, no atomics, no memset.  If `relu_y` is given (the pooled
+// activation of a relu'd tensor), the relu mask of the producer is applied here as well:
+// dx = dy * (y > 0) at the arg-max position (MXNet Activation backward: out_grad * (out > 0)).
+__global__ void __launch_bounds__(256) maxpool_nhwc_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ idx,
+                                                               const float* __restrict__ relu_y, float* __restrict__ dx, int N,
+                                                               int H, int W, int Cp, int K, int OH, int OW) {
+  const int64_t total = (int64_t)N * H * W * Cp;
+  for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+    const int c = (int)(t % Cp);
+    const int w = (int)((t / Cp) % W), h = (int)((t / ((int64_t)Cp * W)) % H);
+    const int n = (int)(t / ((int64_t)Cp * W * H));
+    const int oh = h / K, ow = w / K;
+    float g = 0.f;
+    if (oh < OH && ow < OW) {
+      const int64_t o = (((int64_t)n * OH + oh) * OW + ow) * Cp + c;
+      if ((int)idx[o] == (h - oh * K) * K + (w - ow * K)) {
+        g = dy[o];
+        if (relu_y && !(relu_y[o] > 0.f)) g = 0.f;
+      }
+    }
+    dx[t] = g;
+  }
+}
+
+// ------------------------------------- host side --------------------------------------------
+static ConvGeom make_geom(int N, int OH, int OW) {
+  ConvGeom g;
+  g.N = N; g.OH = OH; g.OW = OW;
+  if (OW <= 8) g.OWv = 8;
+  else if (OW <= 16) g.OWv = 16;
+  else g.OWv = (OW + 31) / 32 * 32;
+  g.bw = g.OWv < 32 ? g.OWv : 32;
+  g.bh = 32 / g.bw;
+  g.OHv = (OH + g.bh - 1) / g.bh * g.bh;
+  g.cpr = g.OWv >= 32 ? g.OWv / 32 : 1;
+  g.cpi = (g.OHv / g.bh) * g.cpr;
+  g.total_chunks = N * g.cpi;
+  g.dh0 = g.dw0 = 0; g.TH = g.TW = 1;
+  return g;
+}
+
+// Channels-last activation (N, H, Wt, Cp) as the 4-D map (K, Wdim, H, N): dim 0 is a contiguous
+// run of K floats starting at a pixel (K == Cp: that pixel's channels; merged: KW pixels' worth,
+// overlapping the next start pixel), dim 1 walks Wdim start pixels.  Box {32, bw, bh, 1}.
+static int make_act_tmap(CUtensorMap* map, const float* ptr, int N, int H, int Wt, int Cp, int K, int Wdim, int bw, int bh,
+                         bool atom32) {
+  const uint64_t dims[4] = {(uint64_t)K, (uint64_t)Wdim, (uint64_t)H, (uint64_t)N};
+  const uint64_t strides[3] = {(uint64_t)Cp * 4, (uint64_t)Wt * Cp * 4, (uint64_t)H * Wt * Cp * 4};
+  const uint32_t box[4] = {32, (uint32_t)bw, (uint32_t)bh, 1};
+  return make_tmap(map, ptr, 4, dims, strides, box, atom32);
+}
+
+static int set_max_smem(const void* fn, const char* what) {
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(220 * 1024));
+  if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(%s): %s", what, cudaGetErrorString(e)); return 1; }
+  return 0;
+}
+
+// y (N, OH, OW, ldy) = conv over x (N, H, Wt, Cp) with `Kreal` contraction channels per pixel.
+// mode 0 forward, 1 forward merged (x physically W-padded by `pad`), 2 dgrad (x := dy, w flipped,
+// `pad` already K-1-pad).  Nout = output channels (F for forward, C for dgrad).
+int conv_igemm(const float* x, const float* w, const float* bias, float* y, int N, int H, int Wt, int Cp, int Kreal,
+               int Nout, int ldy, int F, int C, int KH, int KW, int pad, int OH, int OW, int relu, int mode) {
+  ConvFwdParams p;
+  p.g = make_geom(N, OH, OW);
+  int K, Wdim;                     // contraction length per tap; number of start pixels along W
+  if (mode == 1) { p.g.TH = KH; p.g.TW = 1; p.g.dh0 = -pad; p.g.dw0 = 0; K = KW * Cp; Wdim = Wt - KW + 1; }
+  else { p.g.TH = KH; p.g.TW = KW; p.g.dh0 = -pad; p.g.dw0 = -pad; K = Kreal; Wdim = Wt; }
+  const int taps = p.g.TH * p.g.TW;
+  const int Kp = (K + 3) / 4 * 4;
+  float* wp = nullptr;
+  MC_CHECK(cudaMallocAsync((void**)&wp, sizeof(float) * (size_t)taps * Nout * Kp, stream()));
+  conv_pack_weights_kernel<<<grid_for((int64_t)taps * Nout * Kp, 256), 256, 0, stream()>>>(w, wp, F, C, KH, KW, Cp, taps, Nout,
+                                                                                          Kp, mode);
+  MC_LAUNCHED();
+
+  p.y = y; p.bias = bias; p.Nout = Nout; p.ldy = ldy; p.relu = relu;
+  p.ncb = (K + BKC - 1) / BKC;
+  int bn = 32;
+  while (bn < Nout && bn < 256) bn <<= 1;
+  p.BN = bn;
+  const size_t stage_bytes = 4 * 4096 + (size_t)p.BN * 128;
+  int stages = (int)((200 * 1024) / stage_bytes);
+  if (stages > 8) stages = 8;
+  if (stages > taps * p.ncb) stages = taps * p.ncb;
+  if (stages < 1) stages = 1;
+  p.stages = stages;
+  const size_t smem = stages * stage_bytes + (2 * stages + 1) * 8 + 16 + 1024;
+
+  CUtensorMap tmX, tmW;
+  int rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, K, Wdim, p.g.bw, p.g.bh, false);
+  if (rc == 0) {
+    const uint64_t dims[3] = {(uint64_t)Kp, (uint64_t)Nout, (uint64_t)taps};
+    const uint64_t strides[2] = {(uint64_t)Kp * 4, (uint64_t)Kp * Nout * 4};
+    const uint32_t box[3] = {32, (uint32_t)p.BN, 1};
+    rc = make_tmap(&tmW, wp, 3, dims, strides, box, false);
+  }
+  static bool configured = false;
+  if (rc == 0 && !configured) { rc = set_max_smem((const void*)conv_igemm_kernel, "conv_igemm_kernel"); configured = rc == 0; }
+  if (rc == 0) {
+    dim3 grid((unsigned)((p.g.total_chunks + 3) / 4), (unsigned)((Nout + p.BN - 1) / p.BN));
+    conv_igemm_kernel<<<grid, CONV_THREADS, smem, stream()>>>(tmX, tmW, p);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("conv_igemm_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
+    else count_launch();
+  }
+  cudaFreeAsync(wp, stream());
+  return rc;
+}
+
+// dw (F, C, KH, KW) from x (N, H, Wt, Cp) and dy (N, OH, OW, Fp); merged as in conv_igemm mode 1.
+int conv_wgrad_tc(const float* x, const float* dy, float* dw, int N, int H, int Wt, int Cp, int C, int F, int Fp, int KH,
+                  int KW, int pad, int OH, int OW, int merged) {
+  ConvWgradParams p;
+  p.g = make_geom(N, OH, OW);
+  int Wdim;
+  if (merged) { p.g.TH = KH; p.g.TW = 1; p.g.dh0 = -pad; p.g.dw0 = 0; p.Nn = KW * Cp; Wdim = Wt - KW + 1; }
+  else { p.g.TH = KH; p.g.TW = KW; p.g.dh0 = -pad; p.g.dw0 = -pad; p.Nn = Cp; Wdim = Wt; }
+  const int taps = p.g.TH * p.g.TW;
+  p.F = F;
+  p.BNc = (p.Nn + 31) / 32 * 32;
+  if (p.BNc > 256) { set_error("conv_wgrad_tc: more than 256 input channels is not supported"); return 2; }
+  const int ftiles = (F + 127) / 128;
+  int splits = (2 * sm_count() + taps * ftiles - 1) / (taps * ftiles);   // ~2 CTAs per SM in flight
+  const int max_splits = (p.g.total_chunks + 15) / 16;                   // >= 16 chunks (512 pixels) per CTA
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  p.chunks_per_split = (p.g.total_chunks + splits - 1) / splits;
+  splits = (p.g.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
+  const size_t stage_bytes = 4 * 4096 + (size_t)(p.BNc / 32) * 4096;
+  int stages = (int)((200 * 1024) / stage_bytes);
+  if (stages > 8) stages = 8;
+  p.stages = stages;
+  const size_t smem = stages * stage_bytes + (2 * stages + 1) * 8 + 16 + 1024;
+
+  float* ws = nullptr;
+  MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * (size_t)splits * taps * F * p.Nn, stream()));
+  p.ws = ws;
+  CUtensorMap tmDy, tmX;
+  int rc = make_act_tmap(&tmDy, dy, N, OH, OW, Fp, Fp, OW, p.g.bw, p.g.bh, true);
+  if (rc == 0) rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, p.Nn, Wdim, p.g.bw, p.g.bh, true);
+  static bool configured = false;
+  if (rc == 0 && !configured) { rc = set_max_smem((const void*)conv_wgrad_kernel, "conv_wgrad_kernel"); configured = rc == 0; }
+  if (rc == 0) {
+    dim3 grid((unsigned)taps, (unsigned)splits, (unsigned)ftiles);
+    conv_wgrad_kernel<<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, p);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("conv_wgrad_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
+    else count_launch();
+  }
+  if (rc == 0) {
+    conv_wgrad_reduce_kernel<<<grid_for((int64_t)F * C * KH * KW, 256), 256, 0, stream()>>>(ws, dw, splits, taps, F, p.Nn, C, KH,
+                                                                                          KW, Cp, merged);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("conv_wgrad_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
+    else count_launch();
+  }
+  cudaFreeAsync(ws, stream());
+  return rc;
+}
+
+int nchw_to_nhwc(const float* x, float* y, int N, int C, int H, int W, int Cp, int wpad) {
+  dim3 grid((unsigned)((W + 2 * wpad + 31) / 32), (unsigned)((Cp + 31) / 32), (unsigned)(N * H));
+  nchw_to_nhwc_kernel<<<grid, 256, 0, stream()>>>(x, y, N, C, H, W, Cp, wpad);
+  MC_LAUNCHED();
+  return 0;
+}
+
+int nhwc_to_nchw(const float* x, float* y, int N, int C, int H, int W, int Cp) {
+  dim3 grid((unsigned)((W + 31) / 32), (unsigned)((C + 31) / 32), (unsigned)(N * H));
+  nhwc_to_nchw_kernel<<<grid, 256, 0, stream()>>>(x, y, N, C, H, W, Cp);
+  MC_LAUNCHED();
+  return 0;
+}
+
+}  // namespace tc
+}  // namespace mc
+
+using namespace mc;
+
+namespace {
+
+bool merged_mode(int64_t KW, int64_t Cp, int64_t wpad, int64_t pad) { return KW * Cp <= 32 && wpad == pad; }
+
+int check_nhwc(const void* a, const void* b, const void* c, int64_t Cp, int64_t Fp, const char* who) {
+  if ((Cp & 3) || (Fp & 3)) { set_error("%s: channel pitches must be multiples of 4 (got %lld, %lld)", who, (long long)Cp, (long long)Fp); return 2; }
+  if (!aligned16(a) || !aligned16(b) || !aligned16(c)) { set_error("%s: tensors must be 16-byte aligned", who); return 2; }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mc_nchw_to_nhwc(const float* x, float* y, int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp, int64_t wpad) {
+  MC_REQUIRE(Cp >= C && wpad >= 0, "Cp must be >= C and wpad >= 0");
+  if (N * H * W == 0) return 0;
+  MC_REQUIRE(N * H <= 2147483647LL, "N*H exceeds the grid limit");
+  return tc::nchw_to_nhwc(x, y, (int)N, (int)C, (int)H, (int)W, (int)Cp, (int)wpad);
+}
+
+int mc_nhwc_to_nchw(const float* x, float* y, int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp) {
+  MC_REQUIRE(Cp >= C, "Cp must be >= C");
+  if (N * H * W * C == 0) return 0;
+  MC_REQUIRE(N * H <= 2147483647LL, "N*H exceeds the grid limit");
+  return tc::nhwc_to_nchw(x, y, (int)N, (int)C, (int)H, (int)W, (int)Cp);
+}
+
+int mc_conv2d_nhwc_fwd(const float* x, const float* w, const float* bias, float* y, int64_t N, int64_t C, int64_t H,
+                       int64_t W, int64_t Cp, int64_t wpad, int64_t F, int64_t Fp, int64_t KH, int64_t KW, int64_t pad,
+                       int relu) {
+  if (int rc = check_nhwc(x, y, y, Cp, Fp, "mc_conv2d_nhwc_fwd")) return rc;
+  const int64_t OH = H + 2 * pad - KH + 1, OW = W + 2 * pad - KW + 1;
+  MC_REQUIRE(OH > 0 && OW > 0, "kernel larger than padded input");
+  MC_REQUIRE(wpad == 0 || merged_mode(KW, Cp, wpad, pad), "a W-padded input needs wpad == pad and KW*Cp <= 32");
+  if (N == 0) return 0;
+  const int mode = merged_mode(KW, Cp, wpad, pad) ? 1 : 0;
+  return tc::conv_igemm(x, w, bias, y, (int)N, (int)H, (int)(W + 2 * wpad), (int)Cp, (int)C, (int)F, (int)Fp, (int)F, (int)C,
+                        (int)KH, (int)KW, (int)pad, (int)OH, (int)OW, relu, mode);
+}
+
+int mc_conv2d_nhwc_dgrad(const float* dy, const float* w, float* dx, int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp,
+                         int64_t F, int64_t Fp, int64_t KH, int64_t KW, int64_t pad) {
+  if (int rc = check_nhwc(dy, dx, dx, Cp, Fp, "mc_conv2d_nhwc_dgrad")) return rc;
+  MC_REQUIRE(KH == KW && KH - 1 - pad >= 0, "dgrad needs a square filter with pad <= K-1");
+  const int64_t OH = H + 2 * pad - KH + 1, OW = W + 2 * pad - KW + 1;
+  MC_REQUIRE(OH > 0 && OW > 0, "kernel larger than padded input");
+  if (N == 0) return 0;
+  // dx[pixel, c] = sum_{tap', f} dy[pixel + tap' - (K-1-pad), f] * w[f, c, flipped tap']
+  return tc::conv_igemm(dy, w, nullptr, dx, (int)N, (int)OH, (int)OW, (int)Fp, (int)F, (int)C, (int)Cp, (int)F, (int)C, (int)KH,
+                        (int)KW, (int)(KH - 1 - pad), (int)H, (int)W, 0, 2);
+}
+
+int mc_conv2d_nhwc_wgrad(const float* x, const float* dy, float* dw, float* dbias, int64_t N, int64_t C, int64_t H, int64_t W,
+                         int64_t Cp, int64_t wpad, int64_t F, int64_t Fp, int64_t KH, int64_t KW, int64_t pad) {
+  if (int rc = check_nhwc(x, dy, dy, Cp, Fp, "mc_conv2d_nhwc_wgrad")) return rc;
+  const int64_t OH = H + 2 * pad - KH + 1, OW = W + 2 * pad - KW + 1;
+  MC_REQUIRE(OH > 0 && OW > 0, "kernel larger than padded input");
+  MC_REQUIRE(wpad == 0 || merged_mode(KW, Cp, wpad, pad), "a W-padded input needs wpad == pad and KW*Cp <= 32");
+  if (dw) {
+    if (N == 0) { if (int rc = mc_fill(dw, 0.f, F * C * KH * KW)) return rc; }
+    else {
+      const int merged = merged_mode(KW, Cp, wpad, pad) ? 1 : 0;
+      int rc = tc::conv_wgrad_tc(x, dy, dw, (int)N, (int)H, (int)(W + 2 * wpad), (int)Cp, (int)C, (int)F, (int)Fp, (int)KH, (int)KW,
+                                 (int)pad, (int)OH, (int)OW, merged);
+      if (rc) return rc;
+    }
+  }
+  if (dbias) {
+    // column sums of dy viewed as (pixels, Fp); only the first F entries are real channels
+    if (Fp == F) return reduce_sum_internal(dy, dbias, 1, N * OH * OW, F);
+    float* tmp = nullptr;
+    MC_CHECK(cudaMallocAsync((void**)&tmp, sizeof(float) * Fp, stream()));
+    int rc = reduce_sum_internal(dy, tmp, 1, N * OH * OW, Fp);
+    if (rc == 0) rc = mc_memcpy_d2d(dbias, tmp, sizeof(float) * F);
+    cudaFreeAsync(tmp, stream());
+    return rc;
+  }
+  return 0;
+}
+
+int mc_maxpool2d_nhwc_fwd(const float* x, float* y, uint8_t* idx_u8, int64_t N, int64_t H, int64_t W, int64_t Cp, int64_t KH,
+                          int64_t KW, int64_t stride) {
+  const int64_t OH = (H - KH) / stride + 1, OW = (W - KW) / stride + 1;
+  MC_REQUIRE(OH > 0 && OW > 0 && KH * KW <= 255, "bad pooling window");
+  const int64_t n = N * OH * OW * Cp;
+  if (n <= 0) return 0;
+  tc::maxpool_nhwc_fwd_kernel<<<grid_for(n, 256), 256, 0, stream()>>>(x, y, idx_u8, (int)N, (int)H, (int)W, (int)Cp, (int)KH,
+                                                                     (int)KW, (int)stride, (int)OH, (int)OW);
+  MC_LAUNCHED();
+  return 0;
+}
+
+int mc_maxpool2d_nhwc_bwd(const float* dy, const uint8_t* idx_u8, const float* relu_y, float* dx, int64_t N, int64_t H,
+                          int64_t W, int64_t Cp, int64_t K, int64_t OH, int64_t OW) {
+  const int64_t n = N * H * W * Cp;
+  if (n <= 0) return 0;
+  tc::maxpool_nhwc_bwd_kernel<<<grid_for(n, 256), 256, 0, stream()>>>(dy, idx_u8, relu_y, dx, (int)N, (int)H, (int)W, (int)Cp,
+                                                                     (int)K, (int)OH, (int)OW);
+  MC_LAUNCHED();
+  return 0;
+}
+
+}  // extern "C"
