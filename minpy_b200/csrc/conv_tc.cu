@@ -450,6 +450,78 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_bwd_kernel(const float* __re
   }
 }
 
+// 128-bit versions: one thread = 4 channels of one pooled pixel (Cp is a multiple of 4).
+__global__ void __launch_bounds__(256) maxpool_nhwc_fwd_vec_kernel(const float4* __restrict__ x, float4* __restrict__ y,
+                                                                   uchar4* __restrict__ idx, int N, int H, int W, int C4,
+                                                                   int KH, int KW, int stride, int OH, int OW) {
+  const int64_t total = (int64_t)N * OH * OW * C4;
+  for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+    const int c = (int)(t % C4);
+    const int ow = (int)((t / C4) % OW), oh = (int)((t / ((int64_t)C4 * OW)) % OH);
+    const int n = (int)(t / ((int64_t)C4 * OW * OH));
+    float4 best = make_float4(0.f, 0.f, 0.f, 0.f);
+    uchar4 bi = make_uchar4(255, 255, 255, 255);
+    for (int kh = 0; kh < KH; ++kh)
+      for (int kw = 0; kw < KW; ++kw) {
+        const float4 v = __ldg(x + (((int64_t)n * H + oh * stride + kh) * W + ow * stride + kw) * C4 + c);
+        const unsigned char k = (unsigned char)(kh * KW + kw);
+#define MC_POOL_PICK(f)                                                                   \
+        if (bi.f == 255 || v.f > best.f || (v.f != v.f && best.f == best.f)) { best.f = v.f; bi.f = k; }
+        MC_POOL_PICK(x) MC_POOL_PICK(y) MC_POOL_PICK(z) MC_POOL_PICK(w)
+#undef MC_POOL_PICK
+      }
+    y[t] = best;
+    if (idx) idx[t] = bi;
+  }
+}
+
+// requires H == OH*K and W == OW*K: every input element is written exactly once
+__global__ void __launch_bounds__(256) maxpool_nhwc_bwd_vec_kernel(const float4* __restrict__ dy, const uchar4* __restrict__ idx,
+                                                                   const float4* __restrict__ relu_y, float4* __restrict__ dx,
+                                                                   int N, int H, int W, int C4, int K, int OH, int OW) {
+  const int64_t total = (int64_t)N * OH * OW * C4;
+  for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+    const int c = (int)(t % C4);
+    const int ow = (int)((t / C4) % OW), oh = (int)((t / ((int64_t)C4 * OW)) % OH);
+    const int n = (int)(t / ((int64_t)C4 * OW * OH));
+    float4 g = __ldg(dy + t);
+    const uchar4 bi = idx[t];
+    if (relu_y) {
+      const float4 r = __ldg(relu_y + t);
+      if (!(r.x > 0.f)) g.x = 0.f;
+      if (!(r.y > 0.f)) g.y = 0.f;
+      if (!(r.z > 0.f)) g.z = 0.f;
+      if (!(r.w > 0.f)) g.w = 0.f;
+    }
+    for (int kh = 0; kh < K; ++kh)
+      for (int kw = 0; kw < K; ++kw) {
+        const unsigned char k = (unsigned char)(kh * K + kw);
+        const float4 o = make_float4(bi.x == k ? g.x : 0.f, bi.y == k ? g.y : 0.f, bi.z == k ? g.z : 0.f, bi.w == k ? g.w : 0.f);
+        dx[(((int64_t)n * H + oh * K + kh) * W + ow * K + kw) * C4 + c] = o;
+      }
+  }
+}
+
+// few channels (C <= 4 -> Cp == 4): one thread = one (padded) pixel, one 16-byte store
+__global__ void __launch_bounds__(256) nchw_to_nhwc4_kernel(const float* __restrict__ x, float4* __restrict__ y, int N, int C,
+                                                            int H, int W, int wpad) {
+  const int Wp = W + 2 * wpad;
+  const int64_t total = (int64_t)N * H * Wp;
+  const int64_t plane = (int64_t)H * W;
+  for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
+    const int wp = (int)(t % Wp);
+    const int h = (int)((t / Wp) % H);
+    const int64_t n = t / ((int64_t)Wp * H);
+    const int w = wp - wpad;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (w >= 0 && w < W) {
+      const float* __restrict__ src = x + n * C * plane + (int64_t)h * W + w;
+      for (int c = 0; c < C; ++c) v[c] = __ldg(src + c * plane);
+    }
+    y[t] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
 // ------------------------------------- host side --------------------------------------------
 static ConvGeom make_geom(int N, int OH, int OW) {
   ConvGeom g;
@@ -588,6 +660,12 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, int N, int H, int 
 }
 
 int nchw_to_nhwc(const float* x, float* y, int N, int C, int H, int W, int Cp, int wpad) {
+  if (Cp == 4 && aligned16(y)) {
+    const int64_t total = (int64_t)N * H * (W + 2 * wpad);
+    nchw_to_nhwc4_kernel<<<grid_for(total, 256), 256, 0, stream()>>>(x, reinterpret_cast<float4*>(y), N, C, H, W, wpad);
+    MC_LAUNCHED();
+    return 0;
+  }
   dim3 grid((unsigned)((W + 2 * wpad + 31) / 32), (unsigned)((Cp + 31) / 32), (unsigned)(N * H));
   nchw_to_nhwc_kernel<<<grid, 256, 0, stream()>>>(x, y, N, C, H, W, Cp, wpad);
   MC_LAUNCHED();
@@ -693,8 +771,14 @@ int mc_maxpool2d_nhwc_fwd(const float* x, float* y, uint8_t* idx_u8, int64_t N, 
   MC_REQUIRE(OH > 0 && OW > 0 && KH * KW <= 255, "bad pooling window");
   const int64_t n = N * OH * OW * Cp;
   if (n <= 0) return 0;
-  tc::maxpool_nhwc_fwd_kernel<<<grid_for(n, 256), 256, 0, stream()>>>(x, y, idx_u8, (int)N, (int)H, (int)W, (int)Cp, (int)KH,
-                                                                     (int)KW, (int)stride, (int)OH, (int)OW);
+  if ((Cp & 3) == 0 && aligned16(x) && aligned16(y) && (!idx_u8 || (reinterpret_cast<uintptr_t>(idx_u8) & 3u) == 0)) {
+    tc::maxpool_nhwc_fwd_vec_kernel<<<grid_for(n / 4, 256), 256, 0, stream()>>>(
+        reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), reinterpret_cast<uchar4*>(idx_u8), (int)N, (int)H,
+        (int)W, (int)(Cp / 4), (int)KH, (int)KW, (int)stride, (int)OH, (int)OW);
+  } else {
+    tc::maxpool_nhwc_fwd_kernel<<<grid_for(n, 256), 256, 0, stream()>>>(x, y, idx_u8, (int)N, (int)H, (int)W, (int)Cp, (int)KH,
+                                                                       (int)KW, (int)stride, (int)OH, (int)OW);
+  }
   MC_LAUNCHED();
   return 0;
 }
@@ -703,8 +787,15 @@ int mc_maxpool2d_nhwc_bwd(const float* dy, const uint8_t* idx_u8, const float* r
                           int64_t W, int64_t Cp, int64_t K, int64_t OH, int64_t OW) {
   const int64_t n = N * H * W * Cp;
   if (n <= 0) return 0;
-  tc::maxpool_nhwc_bwd_kernel<<<grid_for(n, 256), 256, 0, stream()>>>(dy, idx_u8, relu_y, dx, (int)N, (int)H, (int)W, (int)Cp,
-                                                                     (int)K, (int)OH, (int)OW);
+  if ((Cp & 3) == 0 && H == OH * K && W == OW * K && aligned16(dy) && aligned16(dx) && (!relu_y || aligned16(relu_y)) &&
+      (reinterpret_cast<uintptr_t>(idx_u8) & 3u) == 0) {
+    tc::maxpool_nhwc_bwd_vec_kernel<<<grid_for(N * OH * OW * (Cp / 4), 256), 256, 0, stream()>>>(
+        reinterpret_cast<const float4*>(dy), reinterpret_cast<const uchar4*>(idx_u8), reinterpret_cast<const float4*>(relu_y),
+        reinterpret_cast<float4*>(dx), (int)N, (int)H, (int)W, (int)(Cp / 4), (int)K, (int)OH, (int)OW);
+  } else {
+    tc::maxpool_nhwc_bwd_kernel<<<grid_for(n, 256), 256, 0, stream()>>>(dy, idx_u8, relu_y, dx, (int)N, (int)H, (int)W, (int)Cp,
+                                                                       (int)K, (int)OH, (int)OW);
+  }
   MC_LAUNCHED();
   return 0;
 }

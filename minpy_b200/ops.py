@@ -715,3 +715,104 @@ def maxpool2d_bwd(dy, arg, xshape):
     if dy.size:
         lib.mc_maxpool2d_bwd(dy.ptr, arg.ptr, dx.ptr, N * C, H, W, dy.shape[2], dy.shape[3])
     return dx
+
+
+# ------------------------------------------------------- channels-last (NHWC) conv trunk ----
+class Nhwc(object):
+    """A channels-last activation: buffer (N, H, W + 2*wpad, Cp) for the logical NCHW tensor
+    (N, C, H, W).  What the tensor-core convolution consumes and produces (csrc/conv_tc.cu)."""
+    __slots__ = ('data', 'N', 'C', 'H', 'W', 'Cp', 'wpad')
+
+    def __init__(self, data, N, C, H, W, Cp, wpad=0):
+        self.data, self.N, self.C, self.H, self.W, self.Cp, self.wpad = data, N, C, H, W, Cp, wpad
+
+    @property
+    def shape(self):
+        return (self.N, self.C, self.H, self.W)
+
+
+def _round4(c):
+    return (c + 3) // 4 * 4
+
+
+def to_nhwc(x, wpad=0):
+    """NCHW CudaArray -> Nhwc (zero pad pixels / pad channels)."""
+    x = as_f32(x)
+    N, C, H, W = x.shape
+    Cp = _round4(C)
+    out = CudaArray.empty((N, H, W + 2 * wpad, Cp))
+    if out.size:
+        L().mc_nchw_to_nhwc(x.ptr, out.ptr, N, C, H, W, Cp, wpad)
+    return Nhwc(out, N, C, H, W, Cp, wpad)
+
+
+def to_nchw(a):
+    """Nhwc (un-padded) -> NCHW CudaArray."""
+    if a.wpad:
+        raise ValueError('to_nchw: W-padded activations are inputs only')
+    out = CudaArray.empty((a.N, a.C, a.H, a.W))
+    if out.size:
+        L().mc_nhwc_to_nchw(a.data.ptr, out.ptr, a.N, a.C, a.H, a.W, a.Cp)
+    return out
+
+
+def conv_merged_ok(C, KW):
+    """Few-channel 'merged' mode (one k-block per filter row) needs KW * Cp <= 32."""
+    return KW * _round4(C) <= 32
+
+
+def conv2d_nhwc_fwd(a, w, b=None, pad=0, relu=False):
+    lib = L()
+    w = as_f32(w)
+    F, C, KH, KW = w.shape
+    if C != a.C:
+        raise ValueError('conv2d: input has %d channels, filter expects %d' % (a.C, C))
+    OH, OW = a.H + 2 * pad - KH + 1, a.W + 2 * pad - KW + 1
+    if OH <= 0 or OW <= 0:
+        raise ValueError('conv2d: kernel larger than padded input')
+    Fp = _round4(F)
+    y = CudaArray.empty((a.N, OH, OW, Fp))
+    if y.size:
+        lib.mc_conv2d_nhwc_fwd(a.data.ptr, w.ptr, as_f32(b).ptr if b is not None else None, y.ptr, a.N, C, a.H, a.W,
+                               a.Cp, a.wpad, F, Fp, KH, KW, pad, 1 if relu else 0)
+    return Nhwc(y, a.N, F, OH, OW, Fp)
+
+
+def conv2d_nhwc_bwd(a, w, dy, pad=0, need_dx=True, need_db=True):
+    """(dx Nhwc or None, dw, db) for y = conv(a, w); dy is the Nhwc gradient of y."""
+    lib = L()
+    w = as_f32(w)
+    F, C, KH, KW = w.shape
+    dx = None
+    if need_dx:
+        d = CudaArray.empty((a.N, a.H, a.W, a.Cp))
+        if d.size:
+            lib.mc_conv2d_nhwc_dgrad(dy.data.ptr, w.ptr, d.ptr, a.N, C, a.H, a.W, a.Cp, F, dy.Cp, KH, KW, pad)
+        dx = Nhwc(d, a.N, C, a.H, a.W, a.Cp)
+    dw = CudaArray.empty(w.shape)
+    db = CudaArray.empty((F,)) if need_db else None
+    lib.mc_conv2d_nhwc_wgrad(a.data.ptr, dy.data.ptr, dw.ptr, db.ptr if db is not None else None, a.N, C, a.H, a.W, a.Cp,
+                             a.wpad, F, dy.Cp, KH, KW, pad)
+    return dx, dw, db
+
+
+def maxpool2d_nhwc_fwd(a, k, want_idx=True):
+    """k x k / stride k max pooling on an Nhwc activation; returns (Nhwc, uint8 window index)."""
+    OH, OW = (a.H - k) // k + 1, (a.W - k) // k + 1
+    if OH <= 0 or OW <= 0:
+        raise ValueError('maxpool2d: kernel larger than input')
+    y = CudaArray.empty((a.N, OH, OW, a.Cp))
+    idx = CudaArray.empty((a.N, OH, OW, a.Cp), np.dtype('uint8')) if want_idx else None
+    if y.size:
+        L().mc_maxpool2d_nhwc_fwd(a.data.ptr, y.ptr, idx.ptr if idx is not None else None, a.N, a.H, a.W, a.Cp, k, k, k)
+    return Nhwc(y, a.N, a.C, OH, OW, a.Cp), idx
+
+
+def maxpool2d_nhwc_bwd(dy, idx, like, k, relu_y=None):
+    """Gradient of maxpool2d_nhwc_fwd w.r.t. its input `like`; `relu_y` (the pooled output) folds
+    the producing relu's mask into the same pass."""
+    dx = CudaArray.empty((like.N, like.H, like.W, like.Cp))
+    if dx.size:
+        L().mc_maxpool2d_nhwc_bwd(dy.data.ptr, idx.ptr, relu_y.data.ptr if relu_y is not None else None, dx.ptr,
+                                  like.N, like.H, like.W, like.Cp, k, dy.H, dy.W)
+    return Nhwc(dx, like.N, like.C, like.H, like.W, like.Cp)

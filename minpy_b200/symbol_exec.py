@@ -30,12 +30,21 @@ def _sq(pair, what):
     return int(pair[0])
 
 
+def _nchw(v):
+    """Dense NCHW CudaArray of a value that may be a channels-last activation."""
+    return ops.to_nchw(v) if isinstance(v, ops.Nhwc) else v
+
+
+def _tc_mode():
+    return ops._gemm_precision['mode'] == 1  # pylint: disable=protected-access
+
+
 class Run(object):
     """State of one forward pass: outputs, updated auxiliary states and the backward closure."""
 
     def __init__(self, plan, values, saved, new_aux, train):
         self.plan, self._values, self._saved, self.new_aux, self._train = plan, values, saved, new_aux, train
-        self.outputs = [values[id(plan.head)]]
+        self.outputs = [_nchw(values[id(plan.head)])]
 
     def backward(self, out_grad=None):
         return self.plan._backward(self, out_grad)  # pylint: disable=protected-access
@@ -62,6 +71,15 @@ class Plan(object):
                 src = node.inputs[0]
                 if src.op == 'Convolution' and consumers.get(id(src), 0) == 1 and src is not self.head:
                     self.fused_relu[id(src)] = node
+        # Pooling whose input is such a fused relu (and its only consumer): the relu mask is
+        # applied by the pooling backward kernel, not by a separate pass over the conv output
+        self.pool_masks_relu = {}
+        for node in self.order:
+            if node.op == 'Pooling':
+                src = node.inputs[0]
+                if src.op == 'Activation' and consumers.get(id(src), 0) == 1 and \
+                        any(act is src for act in self.fused_relu.values()):
+                    self.pool_masks_relu[id(node)] = src.inputs[0]
         # which nodes need a gradient: anything downstream of a non-input argument
         self.needs_grad = {}
         for node in self.order:
@@ -99,24 +117,44 @@ class Plan(object):
                 w = values[id(node.inputs[1])]
                 b = values[id(node.inputs[2])] if not a['no_bias'] else None
                 relu = key in self.fused_relu
-                y = ops.conv2d_fwd(x, w, b, _sq(a['stride'], 'stride'), _sq(a['pad'], 'pad'), relu=relu)
-                values[key] = y
+                stride, pad = _sq(a['stride'], 'stride'), _sq(a['pad'], 'pad')
+                if stride == 1 and _tc_mode() and w.shape[1] <= 256:
+                    # tensor-core path: channels-last in, channels-last out (no conversion between
+                    # consecutive conv / relu / pool nodes)
+                    if not isinstance(x, ops.Nhwc):
+                        x = ops.to_nhwc(x, pad if ops.conv_merged_ok(w.shape[1], w.shape[3]) else 0)
+                    values[key] = ops.conv2d_nhwc_fwd(x, w, b, pad, relu=relu)
+                else:
+                    x = _nchw(x)
+                    values[key] = ops.conv2d_fwd(x, w, b, stride, pad, relu=relu)
                 saved[key] = (x, w)
             elif node.op == 'Activation':
                 if key in skip_relu:
                     values[key] = x                     # already applied by the producing convolution
                 else:
                     op = {'relu': lib.MC_RELU, 'sigmoid': lib.MC_SIGMOID, 'tanh': lib.MC_TANH}[a['act_type']]
-                    values[key] = ops.unary(op, x)
+                    if isinstance(x, ops.Nhwc):     # elementwise: layout-agnostic (pad channels are never read as data)
+                        values[key] = ops.Nhwc(ops.unary(op, x.data), x.N, x.C, x.H, x.W, x.Cp, x.wpad)
+                    else:
+                        values[key] = ops.unary(op, x)
             elif node.op == 'Pooling':
                 if a['pool_type'] != 'max' or a['global_pool'] or a['pad'] != (0, 0):
                     raise NotImplementedError('only un-padded max pooling is lowered (avg / global pooling: next)')
-                y, arg = ops.maxpool2d_fwd(x, a['kernel'], _sq(a['stride'], 'stride'), want_argmax=train)
-                values[key] = y
-                saved[key] = (arg, x.shape)
+                k, stride = a['kernel'], _sq(a['stride'], 'stride')
+                if isinstance(x, ops.Nhwc) and k[0] == k[1] == stride and not x.wpad:
+                    y, idx = ops.maxpool2d_nhwc_fwd(x, stride, want_idx=train)
+                    values[key] = y
+                    saved[key] = (idx, x)
+                else:
+                    x = _nchw(x)
+                    y, arg = ops.maxpool2d_fwd(x, k, stride, want_argmax=train)
+                    values[key] = y
+                    saved[key] = (arg, x.shape)
             elif node.op == 'Flatten':
+                x = _nchw(x)                    # Flatten is defined on the NCHW element order
                 values[key] = x.reshape((x.shape[0], x.size // max(1, x.shape[0])))
             elif node.op == 'FullyConnected':
+                x = _nchw(x)
                 w = values[id(node.inputs[1])]
                 b = values[id(node.inputs[2])] if not a['no_bias'] else None
                 x2 = x.reshape((x.shape[0], x.size // max(1, x.shape[0])))
@@ -152,7 +190,7 @@ class Plan(object):
                     saved[key] = None
                     values[key] = out
             elif node.op == '_Plus':
-                values[key] = ops.binary(lib.MC_ADD, x, values[id(node.inputs[1])])
+                values[key] = ops.binary(lib.MC_ADD, _nchw(x), _nchw(values[id(node.inputs[1])]))
             else:
                 raise NotImplementedError('operator %s is not lowered' % node.op)
         run = Run(self, values, saved, [new_aux[k] for k in self.aux_names], train)
@@ -171,7 +209,10 @@ class Plan(object):
             if isinstance(out_grad, (tuple, list)):
                 out_grad = out_grad[0]
             grads[id(head)] = concrete(out_grad, values[id(head)].shape)
+            if isinstance(values[id(head)], ops.Nhwc):
+                grads[id(head)] = ops.to_nhwc(grads[id(head)])
         wanted = run.data_needs_grad
+        relu_masked = set()        # convolutions whose relu mask a pooling backward already applied
 
         def want(node):
             if node.op != 'null':
@@ -179,10 +220,28 @@ class Plan(object):
             return wanted is None or node.name in wanted
 
         def add(node, g):
+            """Accumulate g into node's gradient, in the layout of the node's forward value."""
             if g is None or not want(node):
                 return
+            like = values.get(id(node))
+            if isinstance(like, ops.Nhwc) and not isinstance(g, ops.Nhwc):
+                g = ops.to_nhwc(g.reshape(like.shape))
+            elif isinstance(g, ops.Nhwc) and not isinstance(like, ops.Nhwc):
+                g = ops.to_nchw(g)
             have = grads.get(id(node))
-            grads[id(node)] = g if have is None else ops.binary(lib.MC_ADD, have, g)
+            if have is None:
+                grads[id(node)] = g
+            elif isinstance(g, ops.Nhwc):
+                grads[id(node)] = ops.Nhwc(ops.binary(lib.MC_ADD, have.data, g.data), g.N, g.C, g.H, g.W, g.Cp)
+            else:
+                grads[id(node)] = ops.binary(lib.MC_ADD, have, g)
+
+        def chain1(g, opname, y):
+            """g * f'(y) elementwise in one kernel, on either layout."""
+            step = [(lib.enums[opname], y.data if isinstance(y, ops.Nhwc) else y, 0, None, 0, 0.0, 1)]
+            if isinstance(y, ops.Nhwc):
+                return ops.Nhwc(ops.run_chain(g.data, 1.0, step, y.data.shape), y.N, y.C, y.H, y.W, y.Cp)
+            return ops.run_chain(g, 1.0, step, y.shape)
 
         fused_act = dict((id(act), cid) for cid, act in self.fused_relu.items())
         for node in reversed(self.order):
@@ -215,27 +274,36 @@ class Plan(object):
                 if key in fused_act:
                     add(x_node, g)            # the convolution applies the relu mask to its own output
                 elif want(x_node):
-                    y = values[key]
                     op = {'relu': _GT0, 'sigmoid': 'MC_VJP_SIGMOID_ANS', 'tanh': 'MC_VJP_TANH_ANS'}[a['act_type']]
-                    add(x_node, ops.run_chain(g, 1.0, [(lib.enums[op], y, 0, None, 0, 0.0, 1)], y.shape))
+                    add(x_node, chain1(g, op, values[key]))
             elif node.op == 'Convolution':
                 x, w = saved[key]
-                if key in self.fused_relu:
-                    y = values[key]
-                    g = ops.run_chain(g, 1.0, [(lib.enums[_GT0], y, 0, None, 0, 0.0, 1)], y.shape)
+                if key in self.fused_relu and key not in relu_masked:
+                    g = chain1(g, _GT0, values[key])
                 need_dx = want(x_node)
-                dx, dw, db = ops.conv2d_bwd(x, w, g, _sq(a['stride'], 'stride'), _sq(a['pad'], 'pad'),
-                                            need_dx=need_dx, need_db=not a['no_bias'])
+                if isinstance(x, ops.Nhwc):
+                    dx, dw, db = ops.conv2d_nhwc_bwd(x, w, g, _sq(a['pad'], 'pad'), need_dx=need_dx,
+                                                     need_db=not a['no_bias'])
+                else:
+                    dx, dw, db = ops.conv2d_bwd(x, w, g, _sq(a['stride'], 'stride'), _sq(a['pad'], 'pad'),
+                                                need_dx=need_dx, need_db=not a['no_bias'])
                 add(x_node, dx)
                 add(node.inputs[1], dw)
                 if not a['no_bias']:
                     add(node.inputs[2], db)
             elif node.op == 'Pooling':
                 if want(x_node):
-                    arg, xshape = saved[key]
-                    add(x_node, ops.maxpool2d_bwd(g, arg, xshape))
+                    arg, xin = saved[key]
+                    if isinstance(xin, ops.Nhwc):
+                        conv = self.pool_masks_relu.get(key)
+                        relu_y = values[key] if conv is not None else None
+                        add(x_node, ops.maxpool2d_nhwc_bwd(g, arg, xin, _sq(a['stride'], 'stride'), relu_y=relu_y))
+                        if conv is not None:
+                            relu_masked.add(id(conv))
+                    else:
+                        add(x_node, ops.maxpool2d_bwd(g, arg, xin))
             elif node.op == 'Flatten':
-                add(x_node, g.reshape(values[id(x_node)].shape))
+                add(x_node, g.reshape(values[id(x_node)].shape))      # logical NCHW shape; add() re-lays it out
             elif node.op == 'FullyConnected':
                 x2, w = saved[key]
                 if want(x_node):

@@ -137,3 +137,38 @@ def test_maxpool_fwd_bwd(cuda, shape):
     dy = rng.randn(*ref.shape).astype(np.float32)
     dx = cuda.maxpool2d_bwd(CudaArray.from_numpy(dy), arg, x.shape)
     assert rel(dx.asnumpy(), orc.maxpool2d_bwd(dy.astype(np.float64), rarg, x.shape)) <= 1e-6
+
+
+# ------------------------------------------------------------- channels-last building blocks --
+@pytest.mark.parametrize('shape,wpad', [((3, 3, 8, 8), 1), ((2, 5, 7, 9), 0), ((2, 64, 6, 6), 0), ((4, 3, 32, 32), 3),
+                                        ((1, 33, 5, 40), 2)])
+def test_nhwc_layout_round_trip_is_bit_exact(cuda, shape, wpad):
+    from minpy_b200.cuda_array import CudaArray
+    rng = np.random.RandomState(2)
+    x = rng.randn(*shape).astype(np.float32)
+    a = cuda.to_nhwc(CudaArray.from_numpy(x), wpad)
+    N, C, H, W = shape
+    h = a.data.asnumpy()
+    assert h.shape == (N, H, W + 2 * wpad, (C + 3) // 4 * 4)
+    assert np.array_equal(h[:, :, wpad:wpad + W, :C], x.transpose(0, 2, 3, 1))
+    assert not h[:, :, :wpad].any() and not h[:, :, wpad + W:].any() and not h[..., C:].any()    # pads are zero
+    if not wpad:
+        assert np.array_equal(cuda.to_nchw(a).asnumpy(), x)
+
+
+@pytest.mark.parametrize('shape,k', [((4, 32, 16, 16), 2), ((2, 6, 12, 12), 3), ((3, 8, 9, 7), 2), ((2, 3, 8, 8), 2)])
+def test_maxpool_nhwc_matches_oracle_and_folds_relu_mask(cuda, shape, k):
+    from minpy_b200.cuda_array import CudaArray
+    rng = np.random.RandomState(4)
+    x = np.maximum(rng.randn(*shape), 0).astype(np.float32)      # a relu'd tensor: exact zeros, ties in windows
+    a = cuda.to_nhwc(CudaArray.from_numpy(x))
+    y, idx = cuda.maxpool2d_nhwc_fwd(a, k)
+    ref, rarg = orc.maxpool2d_fwd(x.astype(np.float64), k, k)
+    assert np.array_equal(cuda.to_nchw(y).asnumpy(), ref.astype(np.float32))
+    dy = rng.randn(*ref.shape).astype(np.float32)
+    dyh = cuda.to_nhwc(CudaArray.from_numpy(dy))
+    dx = cuda.to_nchw(cuda.maxpool2d_nhwc_bwd(dyh, idx, a, k)).asnumpy()
+    assert np.array_equal(dx, orc.maxpool2d_bwd(dy.astype(np.float64), rarg, x.shape).astype(np.float32))   # same arg-max
+    dxm = cuda.to_nchw(cuda.maxpool2d_nhwc_bwd(dyh, idx, a, k, relu_y=y)).asnumpy()
+    want = orc.maxpool2d_bwd((dy * (ref > 0)).astype(np.float64), rarg, x.shape).astype(np.float32)
+    assert np.array_equal(dxm, want)                               # == pool bwd followed by the relu mask out > 0
