@@ -238,8 +238,9 @@ int mc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* dbias, in
     if (xh.alloc((size_t)N * H * (W + 2 * wpad) * Cp) || dyh.alloc((size_t)N * OH * OW * Fp)) return 1;
     if (int rc = mc_nchw_to_nhwc(x, xh.p, N, C, H, W, Cp, wpad)) return rc;
     if (int rc = mc_nchw_to_nhwc(dy, dyh.p, N, F, OH, OW, Fp, 0)) return rc;
-    if (int rc = mc_conv2d_nhwc_wgrad(xh.p, dyh.p, dw, nullptr, N, C, H, W, Cp, wpad, F, Fp, KH, KW, pad)) return rc;
+    if (int rc = mc_conv2d_nhwc_wgrad(xh.p, dyh.p, dw, dbias, N, C, H, W, Cp, wpad, F, Fp, KH, KW, pad)) return rc;
     dw_done = true;
+    dbias = nullptr;   // computed by the same kernel
   } else if (dw) {
     g_conv_last_path = 0;
   }

@@ -64,10 +64,16 @@ struct ConvFwdParams {
   int BN, ncb, stages, relu;
 };
 
-// grid.x = tiles of 4 chunks, grid.y = tiles of BN output channels
-__global__ void __launch_bounds__(CONV_THREADS, 1) conv_igemm_kernel(const __grid_constant__ CUtensorMap tmX,
-                                                                      const __grid_constant__ CUtensorMap tmW,
-                                                                      const ConvFwdParams p) {
+// Persistent: grid = min(#tiles, #SMs); a CTA walks tiles t = blockIdx.x, += gridDim.x, where a
+// tile is (4 chunks of pixels) x (BN output channels).  Six warps: 0-3 epilogue (TMEM lanes
+// 32w..32w+31), 4 TMA producer, 5 MMA issuer.  The shared-memory ring runs continuously across
+// tiles and the accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of tile
+// i overlaps the loads and MMAs of tile i+1 and the per-CTA set-up cost is paid once per SM.
+constexpr int IGEMM_THREADS = 192;
+
+__global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __grid_constant__ CUtensorMap tmX,
+                                                                       const __grid_constant__ CUtensorMap tmW,
+                                                                       const ConvFwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   constexpr uint32_t chunk_bytes = 32u * 128u;                    // [32 pixels][32 ch]
@@ -76,26 +82,28 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_igemm_kernel(const __gri
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const int STAGES = p.stages;
   const uint32_t bar_base = smem_base + STAGES * stage_bytes;
-  const uint32_t tmem_slot = bar_base + (2 * STAGES + 1) * 8;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
-  const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
+  auto tmem_full_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+  auto tmem_empty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar_base + (2 * STAGES + 4) * 8;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int chunk0 = blockIdx.x * 4;
-  const int n0 = blockIdx.y * p.BN;
   const int taps = p.g.TH * p.g.TW;
   const int num_it = taps * p.ncb;
+  const int ptiles = (p.g.total_chunks + 3) / 4;
+  const int ntiles = (p.Nout + p.BN - 1) / p.BN;
+  const int total_tiles = ptiles * ntiles;
+  const uint32_t tcols = (uint32_t)(2 * p.BN);                    // BN is a power of two in [32, 256]
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 4 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    mbar_init(tmem_full_bar, 1);
+    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full_bar(a), 1); mbar_init(tmem_empty_bar(a), 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)p.BN)
-                 : "memory");
+  if (warp == 5) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tcols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tcgen05_fence_before();
@@ -104,101 +112,124 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_igemm_kernel(const __gri
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-  if (warp == 0 && lane == 0) {
-    // ------------------------------ TMA producer ------------------------------------
-    int cn[4], coh[4], cow[4];
+  if (warp == 4) {
+    if (lane == 0) {
+      // ------------------------------ TMA producer ------------------------------------
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int chunk0 = (tile % ptiles) * 4;
+        const int n0 = (tile / ptiles) * p.BN;
+        int cn[4], coh[4], cow[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) chunk_origin(p.g, chunk0 + j, cn[j], coh[j], cow[j]);
-    int it = 0;
-    for (int tap = 0; tap < taps; ++tap) {
-      const int th = tap / p.g.TW, tw = tap - th * p.g.TW;
-      for (int cb = 0; cb < p.ncb; ++cb, ++it) {
-        const int s = it % STAGES;
-        const uint32_t ph = (it / STAGES) & 1;
-        mbar_wait(empty_bar(s), ph ^ 1u);
-        mbar_expect_tx(full_bar(s), stage_bytes);
-        const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+        for (int j = 0; j < 4; ++j) chunk_origin(p.g, chunk0 + j, cn[j], coh[j], cow[j]);
+        for (int tap = 0; tap < taps; ++tap) {
+          const int th = tap / p.g.TW, tw = tap - th * p.g.TW;
+          for (int cb = 0; cb < p.ncb; ++cb, ++it) {
+            const int s = it % STAGES;
+            const uint32_t ph = (it / STAGES) & 1;
+            mbar_wait(empty_bar(s), ph ^ 1u);
+            mbar_expect_tx(full_bar(s), stage_bytes);
+            const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          tma_load_4d(sa + j * chunk_bytes, &tmX, full_bar(s), cb * BKC, cow[j] + tw + p.g.dw0, coh[j] + th + p.g.dh0, cn[j]);
-        tma_load_3d(sb, &tmW, full_bar(s), cb * BKC, n0, tap);
+            for (int j = 0; j < 4; ++j)
+              tma_load_4d(sa + j * chunk_bytes, &tmX, full_bar(s), cb * BKC, cow[j] + tw + p.g.dw0, coh[j] + th + p.g.dh0, cn[j]);
+            tma_load_3d(sb, &tmW, full_bar(s), cb * BKC, n0, tap);
+          }
+        }
       }
     }
-  } else if (warp == 1 && lane == 0) {
-    // ------------------------------ MMA issuer --------------------------------------
-    // c_format F32, a/b TF32, both operands K-major, N>>3 at [17,23), M>>4 at [24,29)
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-    for (int it = 0; it < num_it; ++it) {
-      const int s = it % STAGES;
-      const uint32_t ph = (it / STAGES) & 1;
-      mbar_wait(full_bar(s), ph);
+  } else if (warp == 5) {
+    if (lane == 0) {
+      // ------------------------------ MMA issuer --------------------------------------
+      // c_format F32, a/b TF32, both operands K-major, N>>3 at [17,23), M>>4 at [24,29)
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      int it = 0, ti = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
+        const int acc = ti & 1;
+        mbar_wait(tmem_empty_bar(acc), (((uint32_t)ti >> 1) & 1u) ^ 1u);   // epilogue drained this accumulator
+        tcgen05_fence_after();
+        const uint32_t tacc = tmem_base + (uint32_t)(acc * p.BN);
+        for (int i = 0; i < num_it; ++i, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(full_bar(s), ph);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+#pragma unroll
+          for (int k = 0; k < BKC / UMMA_K; ++k) {
+            const uint64_t adesc = make_desc(sa + k * 32, 16, 1024, 2);
+            const uint64_t bdesc = make_desc(sb + k * 32, 16, 1024, 2);
+            umma_tf32(tacc, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar(s));
+        }
+        umma_commit(tmem_full_bar(acc));
+      }
+    }
+  } else {
+    // ---------------------------------- epilogue (warps 0-3) ----------------------------
+    const bool vec_ok = ((p.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15u) == 0);
+    int ti = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
+      const int acc = ti & 1;
+      const int chunk0 = (tile % ptiles) * 4;
+      const int n0 = (tile / ptiles) * p.BN;
+      int n, oh0, ow0;
+      chunk_origin(p.g, chunk0 + warp, n, oh0, ow0);
+      int oh, ow;
+      if (p.g.OWv >= 32) { oh = oh0; ow = ow0 + lane; }
+      else { oh = oh0 + lane / p.g.OWv; ow = lane % p.g.OWv; }
+      const bool live = (n < p.g.N) && (oh < p.g.OH) && (ow < p.g.OW);
+      float* __restrict__ yrow = p.y + (((int64_t)n * p.g.OH + oh) * p.g.OW + ow) * p.ldy;
+      mbar_wait(tmem_full_bar(acc), ((uint32_t)ti >> 1) & 1u);
       tcgen05_fence_after();
-      const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
-#pragma unroll
-      for (int k = 0; k < BKC / UMMA_K; ++k) {
-        const uint64_t adesc = make_desc(sa + k * 32, 16, 1024, 2);
-        const uint64_t bdesc = make_desc(sb + k * 32, 16, 1024, 2);
-        umma_tf32(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
-      }
-      umma_commit(empty_bar(s));
-    }
-    umma_commit(tmem_full_bar);
-  }
-  __syncwarp();
-
-  // ---------------------------------- epilogue ----------------------------------------
-  mbar_wait(tmem_full_bar, 0);
-  tcgen05_fence_after();
-  __syncwarp();
-  int n, oh0, ow0;
-  chunk_origin(p.g, chunk0 + warp, n, oh0, ow0);
-  int oh, ow;
-  if (p.g.OWv >= 32) { oh = oh0; ow = ow0 + lane; }
-  else { oh = oh0 + lane / p.g.OWv; ow = lane % p.g.OWv; }
-  const bool live = (n < p.g.N) && (oh < p.g.OH) && (ow < p.g.OW);
-  float* __restrict__ yrow = p.y + (((int64_t)n * p.g.OH + oh) * p.g.OW + ow) * p.ldy;
-  const bool vec_ok = ((p.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15u) == 0);
+      const uint32_t tacc = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * p.BN);
 #pragma unroll 1
-  for (int c0 = 0; c0 < p.BN; c0 += 32) {
-    float v[32];
-    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
-    if (live) {
-      const int f0 = n0 + c0;
-      if (vec_ok && f0 + 32 <= p.Nout) {
+      for (int c0 = 0; c0 < p.BN; c0 += 32) {
+        float v[32];
+        tmem_ld32(tacc + (uint32_t)c0, v);
+        if (live) {
+          const int f0 = n0 + c0;
+          if (vec_ok && f0 + 32 <= p.Nout) {
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-          if (p.bias) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + f0 + j));
-            o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-          }
-          if (p.relu) {
-            o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
-            o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
-          }
-          *reinterpret_cast<float4*>(yrow + f0 + j) = o;
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int f = f0 + j;
-          if (f < p.ldy) {                       // pitch padding is written as zeros
-            float o = 0.f;
-            if (f < p.Nout) {
-              o = v[j];
-              if (p.bias) o += __ldg(p.bias + f);
-              if (p.relu) o = (o != o) ? o : fmaxf(o, 0.f);
+            for (int j = 0; j < 32; j += 4) {
+              float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              if (p.bias) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + f0 + j));
+                o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+              }
+              if (p.relu) {
+                o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
+                o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
+              }
+              *reinterpret_cast<float4*>(yrow + f0 + j) = o;
             }
-            yrow[f] = o;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int f = f0 + j;
+              if (f < p.ldy) {                       // pitch padding is written as zeros
+                float o = 0.f;
+                if (f < p.Nout) {
+                  o = v[j];
+                  if (p.bias) o += __ldg(p.bias + f);
+                  if (p.relu) o = (o != o) ? o : fmaxf(o, 0.f);
+                }
+                yrow[f] = o;
+              }
+            }
           }
         }
       }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tmem_empty_bar(acc)) : "memory");
     }
   }
   tcgen05_fence_before();
   __syncthreads();
-  if (warp == 1) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.BN) : "memory");
+  if (warp == 5) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tcols) : "memory");
   }
 }
 
@@ -232,48 +263,62 @@ __global__ void __launch_bounds__(256) conv_pack_weights_kernel(const float* __r
 struct ConvWgradParams {
   ConvGeom g;            // geometry of dy (the output pixels)
   float* ws;             // [splits][taps][F][Nn]
+  float* ws_bias;        // [splits][F] or nullptr: column sums of dy (the bias gradient), fused as one more "tap"
   int F, Nn;             // filters; columns per tap (channel pitch, or KW*Cp merged)
   int BNc, stages;       // BNc: Nn rounded up to 32
+  int tpc;               // taps per CTA: their accumulators sit side by side in TMEM
   int chunks_per_split;
 };
 
-// grid.x = taps, grid.y = splits of the pixel range, grid.z = tiles of 128 filters
+// grid.x = groups of `tpc` taps, grid.y = splits of the pixel range, grid.z = tiles of 128 filters.
+// Per 32-pixel chunk a CTA loads dy ONCE (only the 32-filter blocks that exist) and one shifted
+// window of x per tap; tap t accumulates into TMEM columns [t*BNc, (t+1)*BNc).  The CTA of tap
+// group 0 also multiplies dy by a block of ones: that is the bias gradient, for free.
 __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy,
                                                                       const __grid_constant__ CUtensorMap tmX,
                                                                       const ConvWgradParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   constexpr uint32_t blk = 32u * 128u;                          // [32 pixels][32 f|c]
-  constexpr uint32_t a_bytes = 4u * blk;                        // 128 filters
-  const uint32_t b_bytes = (uint32_t)(p.BNc / 32) * blk;
+  const int taps = p.g.TH * p.g.TW;
+  const int tap0 = blockIdx.x * p.tpc;
+  const int ntap = min(p.tpc, taps - tap0);
+  const int f0 = blockIdx.z * 128;
+  const int fblocks = min(4, (p.F - f0 + 31) / 32);
+  const int nb = p.BNc / 32;
+  const bool do_bias = (p.ws_bias != nullptr) && (blockIdx.x == 0);
+  constexpr uint32_t a_bytes = 4u * blk;                        // room for 128 filters
+  const uint32_t b_bytes = (uint32_t)(p.tpc * nb) * blk;
   const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t tx_bytes = (uint32_t)(fblocks + ntap * nb) * blk;
   const int STAGES = p.stages;
-  const uint32_t bar_base = smem_base + STAGES * stage_bytes;
+  const uint32_t ones_base = smem_base + STAGES * stage_bytes;  // [32 pixels][32] block of 1.0f
+  const uint32_t bar_base = ones_base + blk;
   const uint32_t tmem_slot = bar_base + (2 * STAGES + 1) * 8;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tap = blockIdx.x;
-  const int th = tap / p.g.TW, tw = tap - th * p.g.TW;
-  const int f0 = blockIdx.z * 128;
   const int cbeg = blockIdx.y * p.chunks_per_split;
   const int cend = min(p.g.total_chunks, cbeg + p.chunks_per_split);
   const int num_it = max(0, cend - cbeg);
+  const uint32_t bias_col = (uint32_t)(p.tpc * p.BNc);
   uint32_t tcols = 32;
-  while ((int)tcols < p.BNc) tcols <<= 1;
+  while (tcols < bias_col + 32u) tcols <<= 1;
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tcols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  for (uint32_t i = threadIdx.x; i < blk / 4; i += CONV_THREADS)   // all ones: invariant under the swizzle
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(ones_base + 4u * i), "f"(1.0f) : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> visible to the MMA
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -287,28 +332,44 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
       int n, oh0, ow0;
       chunk_origin(p.g, cbeg + it, n, oh0, ow0);
       mbar_wait(empty_bar(s), ph ^ 1u);
-      mbar_expect_tx(full_bar(s), stage_bytes);
+      mbar_expect_tx(full_bar(s), tx_bytes);
       const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) tma_load_4d(sa + j * blk, &tmDy, full_bar(s), f0 + 32 * j, ow0, oh0, n);
-      for (int j = 0; j < p.BNc / 32; ++j)
-        tma_load_4d(sb + j * blk, &tmX, full_bar(s), 32 * j, ow0 + tw + p.g.dw0, oh0 + th + p.g.dh0, n);
+      for (int j = 0; j < fblocks; ++j) tma_load_4d(sa + j * blk, &tmDy, full_bar(s), f0 + 32 * j, ow0, oh0, n);
+      for (int t = 0; t < ntap; ++t) {
+        const int tap = tap0 + t;
+        const int th = tap / p.g.TW, tw = tap - th * p.g.TW;
+        for (int j = 0; j < nb; ++j)
+          tma_load_4d(sb + (t * nb + j) * blk, &tmX, full_bar(s), 32 * j, ow0 + tw + p.g.dw0, oh0 + th + p.g.dh0, n);
+      }
     }
   } else if (warp == 1 && lane == 0) {
-    // both operands MN-major (f / channels contiguous, pixels = K): major bits 15, 16 set
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(p.BNc >> 3) << 17) |
-                           ((uint32_t)(128 >> 4) << 24);
+    // both operands MN-major (f / channels contiguous, pixels = K): major bits 15, 16 set.
+    // Filter blocks that were not loaded hold stale shared memory: they only reach accumulator
+    // rows >= F, which the epilogue never reads (row m of D depends on row m of A alone).
+    const uint32_t idesc0 = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t idesc = idesc0 | ((uint32_t)(p.BNc >> 3) << 17);
+    const uint32_t idesc_b = idesc0 | ((uint32_t)(32 >> 3) << 17);
     for (int it = 0; it < num_it; ++it) {
       const int s = it % STAGES;
       const uint32_t ph = (it / STAGES) & 1;
       mbar_wait(full_bar(s), ph);
       tcgen05_fence_after();
       const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+      for (int t = 0; t < ntap; ++t) {
 #pragma unroll
-      for (int k = 0; k < 32 / UMMA_K; ++k) {
-        const uint64_t adesc = make_desc(sa + k * 1024, blk, 512, 1);
-        const uint64_t bdesc = make_desc(sb + k * 1024, blk, 512, 1);
-        umma_tf32(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < 32 / UMMA_K; ++k) {
+          const uint64_t adesc = make_desc(sa + k * 1024, blk, 512, 1);
+          const uint64_t bdesc = make_desc(sb + t * nb * blk + k * 1024, blk, 512, 1);
+          umma_tf32(tmem_base + (uint32_t)(t * p.BNc), adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+        }
+      }
+      if (do_bias) {
+#pragma unroll
+        for (int k = 0; k < 32 / UMMA_K; ++k) {
+          const uint64_t adesc = make_desc(sa + k * 1024, blk, 512, 1);
+          const uint64_t bdesc = make_desc(ones_base + k * 1024, blk, 512, 1);
+          umma_tf32(tmem_base + bias_col, adesc, bdesc, idesc_b, (it > 0 || k > 0) ? 1u : 0u);
+        }
       }
       umma_commit(empty_bar(s));
     }
@@ -320,23 +381,40 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   tcgen05_fence_after();
   __syncwarp();
   const int f = f0 + warp * 32 + lane;
-  const int taps = p.g.TH * p.g.TW;
-  float* __restrict__ dst = p.ws + (((int64_t)blockIdx.y * taps + tap) * p.F + f) * p.Nn;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  for (int t = 0; t < ntap; ++t) {
+    float* __restrict__ dst = p.ws + (((int64_t)blockIdx.y * taps + tap0 + t) * p.F + f) * p.Nn;
 #pragma unroll 1
-  for (int c0 = 0; c0 < p.BNc; c0 += 32) {
-    float v[32];
-    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);   // c0 + 32 <= tcols always
-    if (f < p.F) {
+    for (int c0 = 0; c0 < p.BNc; c0 += 32) {
+      float v[32];
+      tmem_ld32(lane_addr + (uint32_t)(t * p.BNc + c0), v);
+      if (f < p.F) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (c0 + j < p.Nn) dst[c0 + j] = (num_it > 0) ? v[j] : 0.f;
+        for (int j = 0; j < 32; ++j)
+          if (c0 + j < p.Nn) dst[c0 + j] = (num_it > 0) ? v[j] : 0.f;
+      }
     }
+  }
+  if (do_bias) {
+    float v[32];
+    tmem_ld32(lane_addr + bias_col, v);
+    if (f < p.F) p.ws_bias[(int64_t)blockIdx.y * p.F + f] = (num_it > 0) ? v[0] : 0.f;
   }
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tcols) : "memory");
   }
+}
+
+// dbias[f] = sum_s ws_bias[s][f]
+__global__ void __launch_bounds__(256) conv_bias_reduce_kernel(const float* __restrict__ wsb, float* __restrict__ dbias, int splits,
+                                                               int F) {
+  const int f = blockIdx.x * 256 + threadIdx.x;
+  if (f >= F) return;
+  float s = 0.f;
+  for (int z = 0; z < splits; ++z) s += wsb[(int64_t)z * F + f];
+  dbias[f] = s;
 }
 
 // dw (F, C, KH, KW) = sum_s ws[s][tap][f][n]; merged: tap = kh, n = kw*Cp + c; else tap = kh*KW+kw, n = c
@@ -582,10 +660,9 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   const size_t stage_bytes = 4 * 4096 + (size_t)p.BN * 128;
   int stages = (int)((200 * 1024) / stage_bytes);
   if (stages > 8) stages = 8;
-  if (stages > taps * p.ncb) stages = taps * p.ncb;
   if (stages < 1) stages = 1;
   p.stages = stages;
-  const size_t smem = stages * stage_bytes + (2 * stages + 1) * 8 + 16 + 1024;
+  const size_t smem = stages * stage_bytes + (2 * stages + 4) * 8 + 16 + 1024;
 
   CUtensorMap tmX, tmW;
   int rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, K, Wdim, p.g.bw, p.g.bh, false);
@@ -598,8 +675,9 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   static bool configured = false;
   if (rc == 0 && !configured) { rc = set_max_smem((const void*)conv_igemm_kernel, "conv_igemm_kernel"); configured = rc == 0; }
   if (rc == 0) {
-    dim3 grid((unsigned)((p.g.total_chunks + 3) / 4), (unsigned)((Nout + p.BN - 1) / p.BN));
-    conv_igemm_kernel<<<grid, CONV_THREADS, smem, stream()>>>(tmX, tmW, p);
+    const int64_t tiles = (int64_t)((p.g.total_chunks + 3) / 4) * ((Nout + p.BN - 1) / p.BN);
+    const unsigned grid = (unsigned)(tiles < sm_count() ? tiles : sm_count());
+    conv_igemm_kernel<<<grid, IGEMM_THREADS, smem, stream()>>>(tmX, tmW, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("conv_igemm_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();
@@ -608,9 +686,10 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   return rc;
 }
 
-// dw (F, C, KH, KW) from x (N, H, Wt, Cp) and dy (N, OH, OW, Fp); merged as in conv_igemm mode 1.
-int conv_wgrad_tc(const float* x, const float* dy, float* dw, int N, int H, int Wt, int Cp, int C, int F, int Fp, int KH,
-                  int KW, int pad, int OH, int OW, int merged) {
+// dw (F, C, KH, KW) [and dbias (F,) when non-null] from x (N, H, Wt, Cp) and dy (N, OH, OW, Fp);
+// merged as in conv_igemm mode 1.
+int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int N, int H, int Wt, int Cp, int C, int F, int Fp,
+                  int KH, int KW, int pad, int OH, int OW, int merged) {
   ConvWgradParams p;
   p.g = make_geom(N, OH, OW);
   int Wdim;
@@ -620,29 +699,42 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, int N, int H, int 
   p.F = F;
   p.BNc = (p.Nn + 31) / 32 * 32;
   if (p.BNc > 256) { set_error("conv_wgrad_tc: more than 256 input channels is not supported"); return 2; }
+  // taps per CTA: as many accumulators as TMEM (512 columns, 32 kept for the bias) and a >= 2-stage
+  // shared-memory ring allow, balanced over the tap groups
+  int tpc = (512 - 32) / p.BNc;
+  const int smem_cap = (int)((100 * 1024 - 4 * 4096) / ((p.BNc / 32) * 4096));
+  if (tpc > smem_cap) tpc = smem_cap;
+  if (tpc > taps) tpc = taps;
+  if (tpc < 1) tpc = 1;
+  const int groups = (taps + tpc - 1) / tpc;
+  tpc = (taps + groups - 1) / groups;
+  p.tpc = tpc;
   const int ftiles = (F + 127) / 128;
-  int splits = (2 * sm_count() + taps * ftiles - 1) / (taps * ftiles);   // ~2 CTAs per SM in flight
-  const int max_splits = (p.g.total_chunks + 15) / 16;                   // >= 16 chunks (512 pixels) per CTA
+  int splits = (sm_count() + groups * ftiles - 1) / (groups * ftiles);   // ~1 CTA per SM (each owns ~100-200 KB smem)
+  const int max_splits = (p.g.total_chunks + 7) / 8;                     // >= 8 chunks (256 pixels) per CTA
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
   p.chunks_per_split = (p.g.total_chunks + splits - 1) / splits;
   splits = (p.g.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
-  const size_t stage_bytes = 4 * 4096 + (size_t)(p.BNc / 32) * 4096;
+  const size_t stage_bytes = 4 * 4096 + (size_t)tpc * (p.BNc / 32) * 4096;
   int stages = (int)((200 * 1024) / stage_bytes);
   if (stages > 8) stages = 8;
+  if (stages < 1) stages = 1;
   p.stages = stages;
-  const size_t smem = stages * stage_bytes + (2 * stages + 1) * 8 + 16 + 1024;
+  const size_t smem = stages * stage_bytes + 4096 + (2 * stages + 1) * 8 + 16 + 1024;
 
   float* ws = nullptr;
-  MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * (size_t)splits * taps * F * p.Nn, stream()));
+  const size_t ws_elems = (size_t)splits * taps * F * p.Nn;
+  MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * (ws_elems + (dbias ? (size_t)splits * F : 0)), stream()));
   p.ws = ws;
+  p.ws_bias = dbias ? ws + ws_elems : nullptr;
   CUtensorMap tmDy, tmX;
   int rc = make_act_tmap(&tmDy, dy, N, OH, OW, Fp, Fp, OW, p.g.bw, p.g.bh, true);
   if (rc == 0) rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, p.Nn, Wdim, p.g.bw, p.g.bh, true);
   static bool configured = false;
   if (rc == 0 && !configured) { rc = set_max_smem((const void*)conv_wgrad_kernel, "conv_wgrad_kernel"); configured = rc == 0; }
   if (rc == 0) {
-    dim3 grid((unsigned)taps, (unsigned)splits, (unsigned)ftiles);
+    dim3 grid((unsigned)groups, (unsigned)splits, (unsigned)ftiles);
     conv_wgrad_kernel<<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("conv_wgrad_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
@@ -653,6 +745,12 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, int N, int H, int 
                                                                                           KW, Cp, merged);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("conv_wgrad_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
+    else count_launch();
+  }
+  if (rc == 0 && dbias) {
+    conv_bias_reduce_kernel<<<(F + 255) / 256, 256, 0, stream()>>>(p.ws_bias, dbias, splits, F);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("conv_bias_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();
   }
   cudaFreeAsync(ws, stream());
@@ -746,10 +844,10 @@ int mc_conv2d_nhwc_wgrad(const float* x, const float* dy, float* dw, float* dbia
   if (dw) {
     if (N == 0) { if (int rc = mc_fill(dw, 0.f, F * C * KH * KW)) return rc; }
     else {
+      // the bias gradient rides along as one more accumulator of the same kernel
       const int merged = merged_mode(KW, Cp, wpad, pad) ? 1 : 0;
-      int rc = tc::conv_wgrad_tc(x, dy, dw, (int)N, (int)H, (int)(W + 2 * wpad), (int)Cp, (int)C, (int)F, (int)Fp, (int)KH, (int)KW,
-                                 (int)pad, (int)OH, (int)OW, merged);
-      if (rc) return rc;
+      return tc::conv_wgrad_tc(x, dy, dw, dbias, (int)N, (int)H, (int)(W + 2 * wpad), (int)Cp, (int)C, (int)F, (int)Fp, (int)KH,
+                               (int)KW, (int)pad, (int)OH, (int)OW, merged);
     }
   }
   if (dbias) {

@@ -74,7 +74,9 @@ def test_conv_fwd_dgrad_wgrad(cuda, shape, mode, tol):
         rdx, rdw, rdb = orc.conv2d_bwd(x64, w64, dy.astype(np.float64), 1, pad)
         assert rel(dx.asnumpy(), rdx) <= tol
         assert rel(dw.asnumpy(), rdw) <= tol
-        assert rel(db.asnumpy(), rdb) <= 2e-5
+        # tf32 mode: the bias gradient is one more accumulator of the wgrad kernel (dy x ones on the
+        # tensor cores), so dy is rounded to TF32 there as well
+        assert rel(db.asnumpy(), rdb) <= (tol if mode == 'tf32' else 2e-5)
         _, dw2, _ = cuda.conv2d_bwd(xd, wd, CudaArray.from_numpy(dy), 1, pad, need_dx=False, need_db=False)
         assert np.array_equal(dw2.asnumpy(), dw.asnumpy())       # deterministic split reduction
     finally:
