@@ -34,22 +34,61 @@ def ensure_device(device: int = None):
 
 
 class _Buffer(object):
-    """Owns one device allocation."""
-    __slots__ = ('ptr', 'nbytes', '_free')
+    """Owns one device allocation.
+
+    Released blocks go to a host-side free list keyed by (rounded) size and are handed out again
+    without calling into the library: every kernel of this process is enqueued on ONE stream, so
+    reuse in program order is reuse in stream order -- the same guarantee the library's
+    cudaMallocAsync pool gives, minus two ctypes round trips per temporary (a training step
+    creates ~100 temporaries of a handful of distinct sizes).  The list is bounded; beyond the
+    bound blocks really go back to the library."""
+    __slots__ = ('ptr', 'nbytes')
+    _free_lists = {}
+    _cached_bytes = 0
+    _cache_limit = 32 << 30
+    _lib_alloc = None
+    _lib_free = None
 
     def __init__(self, nbytes):
-        lib = get_lib()
-        p = ctypes.c_void_p()
-        lib.mc_alloc(ctypes.byref(p), nbytes)
-        self.ptr = p.value
+        nbytes = (nbytes + 511) & ~511 if nbytes else 512
         self.nbytes = nbytes
-        self._free = lib.cdll.mc_free
+        free = _Buffer._free_lists.get(nbytes)
+        if free:
+            self.ptr = free.pop()
+            _Buffer._cached_bytes -= nbytes
+            return
+        if _Buffer._lib_alloc is None:
+            lib = get_lib()
+            _Buffer._lib_alloc, _Buffer._lib_free = lib.mc_alloc, lib.cdll.mc_free
+        p = ctypes.c_void_p()
+        try:
+            _Buffer._lib_alloc(ctypes.byref(p), nbytes)
+        except Exception:
+            _Buffer.trim()                  # give the cached blocks back and retry once
+            _Buffer._lib_alloc(ctypes.byref(p), nbytes)
+        self.ptr = p.value
 
     def __del__(self):
         try:
-            self._free(self.ptr)
+            if _Buffer._cached_bytes + self.nbytes <= _Buffer._cache_limit:
+                free = _Buffer._free_lists.get(self.nbytes)
+                if free is None:
+                    free = _Buffer._free_lists[self.nbytes] = []
+                free.append(self.ptr)
+                _Buffer._cached_bytes += self.nbytes
+            else:
+                _Buffer._lib_free(self.ptr)
         except Exception:  # interpreter shutdown
             pass
+
+    @staticmethod
+    def trim():
+        """Return every cached block to the library's pool."""
+        lists, _Buffer._free_lists = _Buffer._free_lists, {}
+        _Buffer._cached_bytes = 0
+        for blocks in lists.values():
+            for ptr in blocks:
+                _Buffer._lib_free(ptr)
 
 
 def _prod(shape):
