@@ -254,6 +254,15 @@ int mc_adam(const float* w, const float* dw, const float* m, const float* v,
             float* w_out, float* m_out, float* v_out,
             float lr, float beta1, float beta2, float eps, int64_t t, int64_t n);
 
+/* The per-parameter update loop of nn/solver.py:190-195 as ONE launch per 32 tensors: rule 0 sgd,
+ * 1 sgd_momentum, 2 rmsprop, 3 adam, same formulas as above.  w / dw / s1 / s2 / *_out / ns are HOST
+ * arrays of `count` device pointers / element counts; s1 = velocity | cache | m, s2 = v (entries may be
+ * NULL = zero state; unused arrays may be NULL).  hyper (host, 4 floats): sgd {lr}; sgd_momentum
+ * {lr, momentum}; rmsprop {lr, decay, eps}; adam {lr, beta1, beta2, eps} with step count t. */
+int mc_multi_update(int rule, int count, const void* const* w, const void* const* dw, const void* const* s1,
+                    const void* const* s2, void* const* w_out, void* const* s1_out, void* const* s2_out,
+                    const int64_t* ns, const float* hyper, int64_t t);
+
 /* -------------------------------------------------------------------- RNG ---- */
 /* Philox4x32-10 counter RNG: replaces numpy.random.rand/randn (array_variants/numpy/random.py)
  * and mx.random.uniform/normal (array_variants/mxnet/random.py:11-16). */

@@ -92,3 +92,95 @@ def adam(x, dx, config=None):
         next_x = x - config['learning_rate'] * m_hat / (np.sqrt(v_hat) + config['epsilon'])
     config['m'], config['v'], config['t'] = m, v, t
     return next_x, config
+
+
+# ------------------------------------------------------------------ multi-tensor fast path --
+_RULE_SPEC = {
+    # rule name: (code, defaults in order, state keys, hyper keys -> the 4 floats of mc_multi_update)
+    'sgd': (0, (('learning_rate', 1e-2),), (), ('learning_rate',)),
+    'sgd_momentum': (1, (('learning_rate', 1e-2), ('momentum', 0.9)), ('velocity',), ('learning_rate', 'momentum')),
+    'rmsprop': (2, (('learning_rate', 1e-2), ('decay_rate', 0.99), ('epsilon', 1e-8)), ('cache',),
+                ('learning_rate', 'decay_rate', 'epsilon')),
+    'adam': (3, (('learning_rate', 1e-3), ('beta1', 0.9), ('beta2', 0.999), ('epsilon', 1e-8)), ('m', 'v'),
+             ('learning_rate', 'beta1', 'beta2', 'epsilon')),
+}
+
+
+def multi_update(rule, params, grads, configs):
+    """Apply update rule `rule` (one of this module's functions) to every (param, grad, config)
+    triple: same results and same config contents as calling the rule once per parameter (the
+    loop of the reference's nn/solver.py:190-195), but ONE kernel launch per group of tensors that
+    share hyper-parameters when everything lives on the device.  Returns (next_params, configs),
+    or None when the fast path does not apply (host arrays, scalar gradients, unknown rule) --
+    the caller then runs the per-parameter loop."""
+    spec = _RULE_SPEC.get(getattr(rule, '__name__', None))
+    if spec is None or _cuda('fused_sgd') is None or rule is not globals().get(rule.__name__):
+        return None
+    import ctypes
+    from minpy import array as marray
+    from minpy_b200 import ops
+    from minpy_b200.cuda_array import CudaArray, _F32
+    code, defaults, state_keys, hyper_keys = spec
+
+    def raw(v):
+        if isinstance(v, marray.Array) and v.on_device():
+            v = v.get_data(ArrayType.CUDA)
+        return v if isinstance(v, CudaArray) and v.dtype == _F32 else None
+
+    ws, gs, states = [], [], []
+    for w, g, cfg in zip(params, grads, configs):
+        rw, rg = raw(w), raw(g)
+        if rw is None or rg is None or rw.size != rg.size:
+            return None
+        st = []
+        for key in state_keys:
+            cur = cfg.get(key)
+            if cur is None:
+                st.append(None)
+            else:
+                rs = raw(cur)
+                if rs is None or rs.size != rw.size:
+                    return None
+                st.append(rs)
+        ws.append(rw)
+        gs.append(rg)
+        states.append(st)
+    for cfg in configs:
+        for key, val in defaults:
+            cfg.setdefault(key, val)
+        if code == 3:
+            cfg.setdefault('t', 0)
+    # group by identical hyper-parameters (normally one group: Solver copies one optim_config)
+    groups = {}
+    for i, cfg in enumerate(configs):
+        sig = tuple(float(cfg[k]) for k in hyper_keys) + ((int(cfg['t']) + 1,) if code == 3 else ())
+        groups.setdefault(sig, []).append(i)
+    lib = ops.L()
+    outs = [None] * len(ws)
+    new_states = [None] * len(ws)
+    for sig, idxs in groups.items():
+        k = len(idxs)
+        vp = ctypes.c_void_p * k
+        w_out = [CudaArray.empty(ws[i].shape) for i in idxs]
+        s_out = [[CudaArray.empty(ws[i].shape) for i in idxs] for _ in state_keys]
+        hyper = (ctypes.c_float * 4)(*(list(sig[:len(hyper_keys)]) + [0.0] * (4 - len(hyper_keys))))
+
+        def arr(items):
+            return vp(*[x.ptr if x is not None else None for x in items])
+        s1 = arr([states[i][0] for i in idxs]) if len(state_keys) >= 1 else None
+        s2 = arr([states[i][1] for i in idxs]) if len(state_keys) >= 2 else None
+        lib.mc_multi_update(code, k, arr([ws[i] for i in idxs]), arr([gs[i] for i in idxs]), s1, s2, arr(w_out),
+                            arr(s_out[0]) if len(state_keys) >= 1 else None,
+                            arr(s_out[1]) if len(state_keys) >= 2 else None,
+                            (ctypes.c_int64 * k)(*[ws[i].size for i in idxs]), hyper, sig[-1] if code == 3 else 0)
+        for j, i in enumerate(idxs):
+            outs[i] = w_out[j]
+            new_states[i] = [s_out[q][j] for q in range(len(state_keys))]
+    next_params = []
+    for i, cfg in enumerate(configs):
+        for q, key in enumerate(state_keys):
+            cfg[key] = marray.wrap(new_states[i][q])
+        if code == 3:
+            cfg['t'] = int(cfg['t']) + 1
+        next_params.append(marray.wrap(outs[i]))
+    return next_params, configs

@@ -111,6 +111,15 @@ class Solver(object):
         # the reference fetches the loss here (solver.py:187), a device->host sync every step;
         # the entry stays a lazy device scalar instead: float(entry) / entry.asnumpy() fetch it
         self.loss_history.append(loss)
+        # same arithmetic as the per-parameter loop below (reference solver.py:190-195); when every
+        # tensor is on the device the whole loop is one multi-tensor kernel launch
+        fast = optim.multi_update(self.update_rule, [self.model.params[k] for k in names], grads,
+                                  [self.optim_configs[k] for k in names])
+        if fast is not None:
+            for name, next_w, next_config in zip(names, fast[0], fast[1]):
+                self.model.params[name] = next_w
+                self.optim_configs[name] = next_config
+            return
         for name, dw in zip(names, grads):
             next_w, next_config = self.update_rule(self.model.params[name], dw, self.optim_configs[name])
             self.model.params[name] = next_w

@@ -513,3 +513,97 @@ int mc_adam(const float* w, const float* dw, const float* m, const float* v, flo
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------- multi-tensor update ------
+// One launch updates up to MU_MAX parameter tensors (the per-parameter loop of
+// nn/solver.py:190-195 made one kernel): block b works on tile (b - first[t]) of tensor t.
+namespace mc {
+constexpr int MU_MAX = 32;
+constexpr int MU_TILE = L_THREADS * 8;
+struct MultiUpdateDesc {
+  int count, rule;
+  float h[6];                   // lr, (momentum | decay | beta1), (eps | beta2), eps, bc1, bc2
+  int first[MU_MAX + 1];
+  int64_t n[MU_MAX];
+  const float* w[MU_MAX];
+  const float* dw[MU_MAX];
+  const float* s1[MU_MAX];      // velocity / cache / m   (nullptr = zeros)
+  const float* s2[MU_MAX];      // v (adam)
+  float* wo[MU_MAX];
+  float* s1o[MU_MAX];
+  float* s2o[MU_MAX];
+};
+
+__global__ void __launch_bounds__(L_THREADS) multi_update_kernel(const __grid_constant__ MultiUpdateDesc d) {
+  int t = 0;
+  while (t + 1 < d.count && (int)blockIdx.x >= d.first[t + 1]) ++t;
+  const float* __restrict__ w = d.w[t];
+  const float* __restrict__ dw = d.dw[t];
+  const float* __restrict__ s1 = d.s1[t];
+  const float* __restrict__ s2 = d.s2[t];
+  float* __restrict__ wo = d.wo[t];
+  float* __restrict__ s1o = d.s1o[t];
+  float* __restrict__ s2o = d.s2o[t];
+  const int64_t lo = (int64_t)(blockIdx.x - d.first[t]) * MU_TILE;
+  const int64_t hi = (lo + MU_TILE < d.n[t]) ? lo + MU_TILE : d.n[t];
+  const float lr = d.h[0];
+  for (int64_t i = lo + threadIdx.x; i < hi; i += L_THREADS) {
+    const float g = dw[i];
+    if (d.rule == 0) {
+      wo[i] = w[i] - lr * g;                                                     // optim.py:33-46
+    } else if (d.rule == 1) {
+      const float nv = (s1 ? s1[i] : 0.f) * d.h[1] - g * lr;                     // optim.py:64
+      s1o[i] = nv;
+      wo[i] = w[i] + nv;
+    } else if (d.rule == 2) {
+      const float c = (s1 ? s1[i] : 0.f) * d.h[1] + g * g * (1.f - d.h[1]);      // optim.py:93
+      s1o[i] = c;
+      wo[i] = w[i] - lr * g / (sqrtf(c) + d.h[2]);
+    } else {
+      const float nm = d.h[1] * (s1 ? s1[i] : 0.f) + (1.f - d.h[1]) * g;         // optim.py:128-134
+      const float nv = d.h[2] * (s2 ? s2[i] : 0.f) + (1.f - d.h[2]) * (g * g);
+      s1o[i] = nm;
+      s2o[i] = nv;
+      wo[i] = w[i] - lr * (nm / d.h[4]) / (sqrtf(nv / d.h[5]) + d.h[3]);
+    }
+  }
+}
+}  // namespace mc
+
+extern "C" {
+
+int mc_multi_update(int rule, int count, const void* const* w, const void* const* dw, const void* const* s1,
+                    const void* const* s2, void* const* w_out, void* const* s1_out, void* const* s2_out, const int64_t* ns,
+                    const float* hyper, int64_t t) {
+  MC_REQUIRE(rule >= 0 && rule <= 3 && count >= 0, "bad rule / count");
+  for (int base = 0; base < count; base += mc::MU_MAX) {
+    mc::MultiUpdateDesc d;
+    d.count = 0;
+    d.rule = rule;
+    for (int k = 0; k < 4; ++k) d.h[k] = hyper[k];
+    d.h[4] = d.h[5] = 1.f;
+    if (rule == 3) {
+      d.h[4] = (float)(1.0 - pow((double)hyper[1], (double)t));
+      d.h[5] = (float)(1.0 - pow((double)hyper[2], (double)t));
+    }
+    int blocks = 0;
+    for (int k = base; k < count && d.count < mc::MU_MAX; ++k) {
+      if (ns[k] <= 0) continue;
+      const int j = d.count++;
+      d.first[j] = blocks;
+      d.n[j] = ns[k];
+      d.w[j] = (const float*)w[k]; d.dw[j] = (const float*)dw[k];
+      d.s1[j] = s1 ? (const float*)s1[k] : nullptr; d.s2[j] = s2 ? (const float*)s2[k] : nullptr;
+      d.wo[j] = (float*)w_out[k];
+      d.s1o[j] = s1_out ? (float*)s1_out[k] : nullptr; d.s2o[j] = s2_out ? (float*)s2_out[k] : nullptr;
+      blocks += (int)((ns[k] + mc::MU_TILE - 1) / mc::MU_TILE);
+    }
+    if (d.count == 0) continue;
+    d.first[d.count] = blocks;
+    mc::multi_update_kernel<<<blocks, mc::L_THREADS, 0, mc::stream()>>>(d);
+    MC_LAUNCHED();
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -457,3 +457,44 @@ def test_solver_check_accuracy_on_device(mp):
     model.params['w0'] = mnp.array(W)
     model.params['b0'] = mnp.zeros(C)
     assert solver.check_accuracy(it) == 1.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('rule', ['sgd', 'sgd_momentum', 'rmsprop', 'adam'])
+def test_multi_tensor_update_equals_per_parameter_loop(rule):
+    """optim.multi_update (one launch for all parameters, used by Solver._step) must leave the
+    same parameters AND the same config contents as the reference's per-parameter loop
+    (nn/solver.py:190-195), step after step, including tensors of odd sizes."""
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    import minpy.numpy as mnp
+    from minpy.nn import optim
+    rng = np.random.RandomState(12)
+    shapes = [(33, 17), (5,), (128, 64), (1,), (7, 3, 3, 3)] * 8          # 40 tensors: more than one launch group
+    w0 = [rng.randn(*s).astype(np.float32) for s in shapes]
+    fn = getattr(optim, rule)
+    base = {'learning_rate': 0.05}
+    pa, pb = [mnp.array(w) for w in w0], [mnp.array(w) for w in w0]
+    ca, cb = [dict(base) for _ in shapes], [dict(base) for _ in shapes]
+    for step in range(3):
+        grads = [rng.randn(*s).astype(np.float32) for s in shapes]
+        ga, gb = [mnp.array(g) for g in grads], [mnp.array(g) for g in grads]
+        out = optim.multi_update(fn, pa, ga, ca)
+        assert out is not None, 'fast path must apply to device tensors'
+        pa, ca = out
+        for i in range(len(shapes)):
+            pb[i], cb[i] = fn(pb[i], gb[i], cb[i])
+        for i in range(len(shapes)):
+            assert pa[i].shape == pb[i].shape
+            # same fp32 formulas; the two kernels may contract a*b+c into an fma differently: 1 ulp
+            assert rel(pa[i].asnumpy(), pb[i].asnumpy()) <= 1e-6, (rule, step, i)
+            assert set(ca[i].keys()) == set(cb[i].keys())
+            for k in ca[i]:
+                va, vb = ca[i][k], cb[i][k]
+                if hasattr(va, 'asnumpy'):
+                    assert rel(va.asnumpy(), vb.asnumpy()) <= 1e-6, (rule, step, i, k)
+                else:
+                    assert va == vb, (rule, k)
+    # host arrays -> no fast path
+    assert optim.multi_update(fn, [w0[0]], [w0[0]], [{}]) is None
+    minpy.set_global_policy('prefer_cuda')
