@@ -101,11 +101,13 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_cols_kernel(const float* _
     const float* __restrict__ p = x + o * red * inner + col;
     if (VEC == 4) {
       int64_t r = begin + ty;
-      for (; r + 8 < end; r += 16) {  // two independent loads in flight
-        float4 a = *reinterpret_cast<const float4*>(p + r * inner);
-        float4 b = *reinterpret_cast<const float4*>(p + (r + 8) * inner);
-        acc[0] = op(acc[0], op(a.x, b.x)); acc[1] = op(acc[1], op(a.y, b.y));
-        acc[2] = op(acc[2], op(a.z, b.z)); acc[3] = op(acc[3], op(a.w, b.w));
+      for (; r + 24 < end; r += 32) {  // four independent 16-byte loads in flight per thread
+        float4 a = __ldg(reinterpret_cast<const float4*>(p + r * inner));
+        float4 b = __ldg(reinterpret_cast<const float4*>(p + (r + 8) * inner));
+        float4 c = __ldg(reinterpret_cast<const float4*>(p + (r + 16) * inner));
+        float4 d = __ldg(reinterpret_cast<const float4*>(p + (r + 24) * inner));
+        acc[0] = op(acc[0], op(op(a.x, b.x), op(c.x, d.x))); acc[1] = op(acc[1], op(op(a.y, b.y), op(c.y, d.y)));
+        acc[2] = op(acc[2], op(op(a.z, b.z), op(c.z, d.z))); acc[3] = op(acc[3], op(op(a.w, b.w), op(c.w, d.w)));
       }
       for (; r < end; r += 8) {
         float4 a = *reinterpret_cast<const float4*>(p + r * inner);
@@ -141,8 +143,8 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
       return 0;
     }
     int splits = 1;
-    if (outer < 2 * sms && red > 8192) {
-      int64_t want = (2 * sms + outer - 1) / outer;
+    if (outer < 8 * sms && red > 8192) {     // 8 CTAs of 256 threads per SM keep enough loads in flight
+      int64_t want = (8 * sms + outer - 1) / outer;
       int64_t maxs = red / 4096;
       splits = (int)(want < maxs ? want : maxs);
       if (splits < 1) splits = 1;
@@ -170,9 +172,9 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
   const int64_t col_tiles = (inner + 32 * vecw - 1) / (32 * vecw);
   MC_REQUIRE(outer <= 65535, "outer too large for column reduction");
   int splits = 1;
-  if (col_tiles * outer < 2 * sms && red > 64) {
-    int64_t want = (2 * sms + col_tiles * outer - 1) / (col_tiles * outer);
-    int64_t maxs = red / 32;
+  if (col_tiles * outer < 8 * sms && red > 64) {
+    int64_t want = (8 * sms + col_tiles * outer - 1) / (col_tiles * outer);
+    int64_t maxs = red / 64;
     splits = (int)(want < maxs ? want : maxs);
     if (splits < 1) splits = 1;
     if (splits > 1024) splits = 1024;

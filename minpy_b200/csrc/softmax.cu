@@ -15,6 +15,16 @@ constexpr int ROW_REGS = 32;  // floats cached per lane -> cols <= 1024
 
 enum { MODE_SOFTMAX = 0, MODE_LSE = 1, MODE_CE = 2 };
 
+// exp(x - m) as ONE fma + ONE ex2.approx (2^-22 relative): with accurate expf and a NaN-checking max
+// the row kernels were instruction-bound (43 % of the HBM roofline at 1024 columns, profiles/r1a).
+// NaN needs no special max: fmaxf skips it, exp(NaN - m) is NaN, so the row sum and with it every
+// output of that row is NaN -- what NumPy's max-subtracted softmax yields as well.
+__device__ __forceinline__ float exp_sub(float x, float m_log2e) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(x, 1.4426950408889634f, -m_log2e)));
+  return r;
+}
+
 // One warp per row, whole row in registers.
 // MODE_SOFTMAX: out = softmax(x).  MODE_LSE: out[row] = logsumexp.  MODE_CE: out = probs and
 // rowloss[row] = -log p[label] (labels) or -sum_j onehot[j] * log p[j].
@@ -41,32 +51,33 @@ __global__ void __launch_bounds__(SM_THREADS) softmax_warp_kernel(const float* _
         if (i < c4) {
           float4 t = p4[i];
           v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
-          m = nanmax(m, nanmax(nanmax(t.x, t.y), nanmax(t.z, t.w)));
+          m = fmaxf(m, fmaxf(fmaxf(t.x, t.y), fmaxf(t.z, t.w)));
         }
       }
     } else {
 #pragma unroll
       for (int j = 0; j < ROW_REGS; ++j) {
         int64_t i = lane + 32 * j;
-        if (i < cols) { v[j] = p[i]; m = nanmax(m, v[j]); }
+        if (i < cols) { v[j] = p[i]; m = fmaxf(m, v[j]); }
       }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = nanmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     float s = 0.f;
+    const float ml2 = m * 1.4426950408889634f;
     if (vec) {
       const int64_t c4 = cols >> 2;
 #pragma unroll
       for (int j = 0; j < ROW_REGS / 4; ++j) {
         if (lane + 32 * j < c4) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) { v[4 * j + k] = expf(v[4 * j + k] - m); s += v[4 * j + k]; }
+          for (int k = 0; k < 4; ++k) { v[4 * j + k] = exp_sub(v[4 * j + k], ml2); s += v[4 * j + k]; }
         }
       }
     } else {
 #pragma unroll
       for (int j = 0; j < ROW_REGS; ++j)
-        if (lane + 32 * j < cols) { v[j] = expf(v[j] - m); s += v[j]; }
+        if (lane + 32 * j < cols) { v[j] = exp_sub(v[j], ml2); s += v[j]; }
     }
     s = warp_sum(s);
     if (MODE == MODE_LSE) {
@@ -135,10 +146,11 @@ __global__ void __launch_bounds__(SM_THREADS) softmax_block_kernel(const float* 
   const int64_t row = blockIdx.x;
   const float* __restrict__ p = x + row * cols;
   float m = -INFINITY;
-  for (int64_t i = threadIdx.x; i < cols; i += SM_THREADS) m = nanmax(m, p[i]);
+  for (int64_t i = threadIdx.x; i < cols; i += SM_THREADS) m = fmaxf(m, p[i]);
   m = block_reduce(m, MaxOp(), smem);
   float s = 0.f;
-  for (int64_t i = threadIdx.x; i < cols; i += SM_THREADS) s += expf(p[i] - m);
+  const float ml2 = m * 1.4426950408889634f;
+  for (int64_t i = threadIdx.x; i < cols; i += SM_THREADS) s += exp_sub(p[i], ml2);
   s = block_reduce(s, SumOp(), smem);
   if (MODE == MODE_LSE) {
     if (threadIdx.x == 0) out[row] = m + logf(s);
@@ -149,7 +161,7 @@ __global__ void __launch_bounds__(SM_THREADS) softmax_block_kernel(const float* 
   float loss = 0.f;
   for (int64_t i = threadIdx.x; i < cols; i += SM_THREADS) {
     float d = p[i] - m;
-    q[i] = expf(d) * inv;
+    q[i] = exp_sub(p[i], ml2) * inv;
     if (MODE == MODE_CE && onehot) {
       float y = __ldg(onehot + row * cols + i);
       if (y != 0.f) loss -= y * (d - logs);
