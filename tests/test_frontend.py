@@ -486,13 +486,15 @@ def test_multi_tensor_update_equals_per_parameter_loop(rule):
             pb[i], cb[i] = fn(pb[i], gb[i], cb[i])
         for i in range(len(shapes)):
             assert pa[i].shape == pb[i].shape
-            # same fp32 formulas; the two kernels may contract a*b+c into an fma differently: 1 ulp
-            assert rel(pa[i].asnumpy(), pb[i].asnumpy()) <= 1e-6, (rule, step, i)
+            # same fp32 formulas; the two kernels may contract a*b+c into an fma differently: 1 ulp of
+            # the update term, which after cancellation in w - update can be several ulp of a small
+            # w (seen: 1.01e-6 on a 1-element tensor) -> the north_star fp32 elementwise bound, 1e-5
+            assert rel(pa[i].asnumpy(), pb[i].asnumpy()) <= 1e-5, (rule, step, i)
             assert set(ca[i].keys()) == set(cb[i].keys())
             for k in ca[i]:
                 va, vb = ca[i][k], cb[i][k]
                 if hasattr(va, 'asnumpy'):
-                    assert rel(va.asnumpy(), vb.asnumpy()) <= 1e-6, (rule, step, i, k)
+                    assert rel(va.asnumpy(), vb.asnumpy()) <= 1e-5, (rule, step, i, k)
                 else:
                     assert va == vb, (rule, k)
     # host arrays -> no fast path
