@@ -231,13 +231,13 @@ def pinned_array(lib, shape, dtype):
     return arr
 
 
-def build_solver(workload, train_iter):
+def build_solver(workload, train_iter, step_graph=False):
     from minpy.nn.solver import Solver
     from minpy_b200 import workloads
     factory, _, rule, optim_config, _, _ = workloads.WORKLOADS[workload]
     model = factory()
     solver = Solver(model, train_iter, train_iter, update_rule=rule, optim_config=dict(optim_config),
-                    init_rule='gaussian', init_config={'stdvar': 0.01}, verbose=False)
+                    init_rule='gaussian', init_config={'stdvar': 0.01}, verbose=False, step_graph=step_graph)
     solver.init()
     return model, solver
 
@@ -270,7 +270,7 @@ def run_b200(args):
     Xp[...] = X
     Yp[...] = Y
     host_iter = NDArrayIter(Xp, Yp, batch_size=batch, shuffle=False, num_parts=1, part_index=0)
-    model, solver = build_solver(args.workload, host_iter)
+    model, solver = build_solver(args.workload, host_iter, step_graph=bool(args.graph))
 
     # device-resident batches for the kernel-only leg
     dev_batches = []
@@ -326,8 +326,21 @@ def run_b200(args):
     e2e_ms, _, e2e_wall = timed(step_e2e, args.steps, args.warmup)
     clocks = sampler.stop() if rank == 0 else None
     last_loss = float(solver.loss_history[-1])
+    graph_info = None
+    sg = getattr(solver, '_step_graph', None)
+    if sg is not None:
+        # the same steps launched eagerly from Python (one library call per kernel): the launch count
+        # per step (= kernel nodes each replay executes) and the host-bound time it replaces
+        graph_info = {'replays': sg.replays, 'captures': sg.captures, 'fell_back_to_eager': bool(sg.disabled)}
+        was = sg.disabled
+        sg.disabled = True
+        eager_ms, launches, _ = timed(step_device, args.steps, args.warmup)
+        sg.disabled = was
+        graph_info['eager_ms_per_step'] = round(eager_ms / args.steps, 4)
 
     # instrumented pass: event pair around every library call of the same steps
+    if sg is not None:
+        sg.disabled = True
     timer = CallTimer(lib)
     timer.install()
     try:
@@ -388,6 +401,7 @@ def run_b200(args):
             'e2e': {'value': round(e2e_value, 1), 'unit': 'samples/s', 'h2d_bytes_per_step': int(in_bytes),
                     'd2h_bytes_per_step': 4, 'ms_per_step': round(e2e_ms / args.steps, 4)},
             'gpu_launches': int(launches), 'launches_per_step': round(launches / args.steps, 1),
+            'step_graph': graph_info,
             'wall_ms_per_step': round(dev_wall / args.steps, 4), 'final_loss': last_loss,
             'clocks': clocks, 'roofline': roofline,
             'kernel_families': dict((k, {'calls_per_step': round(v['calls'] / inst_steps, 1),
@@ -596,6 +610,7 @@ def main():
     ap.add_argument('--workload', default='mlp_c3')
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--pool', type=int, default=16, help='distinct batches cycled per rank')
+    ap.add_argument('--graph', type=int, default=1, help='replay the step as a CUDA graph (0 = eager launches)')
     ap.add_argument('--no-ufunc', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()

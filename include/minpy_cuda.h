@@ -67,6 +67,8 @@ int mc_graph_begin(void);
 int mc_graph_end(void** graph_exec);
 int mc_graph_launch(void* graph_exec);
 int mc_graph_destroy(void* graph_exec);
+int mc_graph_abort(void);
+int mc_graph_capturing(int* flag);
 
 /* ------------------------------------------------------------- elementwise --- */
 /* Unary ufuncs: numpy_core.py:228-230,267-276,303 / mxnet_core.py:116-118,150-159. */

@@ -41,6 +41,10 @@ class Solver(object):
         for key, default in self._DEFAULTS:
             value = kwargs.pop(key, default)
             setattr(self, key, dict(value) if isinstance(default, dict) else value)
+        # not in the reference: replay the step as a CUDA graph (minpy_b200/step_graph.py)
+        import os
+        self.step_graph = bool(kwargs.pop('step_graph', os.environ.get('MINPY_STEP_GRAPH', '0') == '1'))
+        self._step_graph = None
         if kwargs:
             raise ValueError('Unrecognized arguments %s' % ', '.join('"%s"' % k for k in kwargs))
         if not hasattr(optim, self.update_rule):
@@ -91,7 +95,27 @@ class Solver(object):
             parallel.broadcast_params(self.model.params)
 
     def _step(self, batch):
-        """One gradient update on `batch`."""
+        """One gradient update on `batch` (eager, or a CUDA-graph replay of the same launch
+        sequence when the solver was created with step_graph=True / MINPY_STEP_GRAPH=1)."""
+        if self.step_graph and self._step_graph is None:
+            from minpy_b200.step_graph import StepGraph
+            self._step_graph = StepGraph(self)
+        if self._step_graph is not None:
+            return self._step_graph.step(batch)
+        return self._step_eager(batch)
+
+    def _step_eager(self, batch):
+        names, grads, loss = self._step_grads(batch)
+        from minpy_b200 import parallel
+        if parallel.world_size() > 1:
+            grads = parallel.allreduce_mean(grads)
+        # the reference fetches the loss here (solver.py:187), a device->host sync every step;
+        # the entry stays a lazy device scalar instead: float(entry) / entry.asnumpy() fetch it
+        self.loss_history.append(loss)
+        self._step_update(names, grads)
+
+    def _step_grads(self, batch):
+        """Forward + tape backward: (parameter names, gradients, loss)."""
         def loss_func(*_params):
             # the parameters are read from self.model.params by the model; passing them as
             # arguments is what puts them on the tape
@@ -103,16 +127,12 @@ class Solver(object):
         grads, loss = core.grad_and_loss(loss_func, argnum=range(len(values)))(*values)
         if len(values) == 1:
             grads = [grads]
+        return names, grads, loss
 
-        from minpy_b200 import parallel
-        if parallel.world_size() > 1:
-            grads = parallel.allreduce_mean(grads)
-
-        # the reference fetches the loss here (solver.py:187), a device->host sync every step;
-        # the entry stays a lazy device scalar instead: float(entry) / entry.asnumpy() fetch it
-        self.loss_history.append(loss)
-        # same arithmetic as the per-parameter loop below (reference solver.py:190-195); when every
-        # tensor is on the device the whole loop is one multi-tensor kernel launch
+    def _step_update(self, names, grads):
+        """The update rules (reference solver.py:190-195)."""
+        # same arithmetic as the per-parameter loop below; when every tensor is on the device the
+        # whole loop is one multi-tensor kernel launch
         fast = optim.multi_update(self.update_rule, [self.model.params[k] for k in names], grads,
                                   [self.optim_configs[k] for k in names])
         if fast is not None:

@@ -14,6 +14,11 @@ void set_error(const char* fmt, ...);
 cudaStream_t stream();
 int sm_count();
 void count_launch(int n = 1);
+// Non-null while a step graph is being captured (mc_graph_begin .. mc_graph_end): device counter
+// that the graph increments once per replay (1 on the first).  Kernels whose host-side
+// arguments change every step (Philox offsets, adam's t) read it so that a replay is a NEW
+// step, not a repetition of the captured one.
+const unsigned long long* graph_epoch();
 
 #define MC_CHECK(expr)                                                              \
   do {                                                                              \

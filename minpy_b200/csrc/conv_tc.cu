@@ -46,6 +46,8 @@ struct ConvGeom {
   int total_chunks;
   int dh0, dw0;          // input coordinate = output coordinate + tap + d?0
   int TH, TW;            // taps along h / w enumerated by the kernel
+  int one_box;           // the 4 chunks of a tile form ONE TMA box {32, bw, box_h, box_n}
+  int box_h, box_n;
 };
 
 __device__ __forceinline__ void chunk_origin(const ConvGeom& g, int chunk, int& n, int& oh0, int& ow0) {
@@ -130,9 +132,13 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
             mbar_wait(empty_bar(s), ph ^ 1u);
             mbar_expect_tx(full_bar(s), stage_bytes);
             const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+            if (p.g.one_box) {
+              tma_load_4d(sa, &tmX, full_bar(s), cb * BKC, cow[0] + tw + p.g.dw0, coh[0] + th + p.g.dh0, cn[0]);
+            } else {
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-              tma_load_4d(sa + j * chunk_bytes, &tmX, full_bar(s), cb * BKC, cow[j] + tw + p.g.dw0, coh[j] + th + p.g.dh0, cn[j]);
+              for (int j = 0; j < 4; ++j)
+                tma_load_4d(sa + j * chunk_bytes, &tmX, full_bar(s), cb * BKC, cow[j] + tw + p.g.dw0, coh[j] + th + p.g.dh0, cn[j]);
+            }
             tma_load_3d(sb, &tmW, full_bar(s), cb * BKC, n0, tap);
           }
         }
@@ -601,7 +607,10 @@ __global__ void __launch_bounds__(256) nchw_to_nhwc4_kernel(const float* __restr
 }
 
 // ------------------------------------- host side --------------------------------------------
-static ConvGeom make_geom(int N, int OH, int OW) {
+// tile_box: round the virtual height so that the 4 chunks of every 128-pixel tile are one
+// rectangle {bw, box_h rows, box_n images} -- one TMA box per operand tile instead of four (the
+// producer thread is issue-bound: ~130 ns per UTMALDG.4D, profiles/r1i).
+static ConvGeom make_geom(int N, int OH, int OW, bool tile_box = false) {
   ConvGeom g;
   g.N = N; g.OH = OH; g.OW = OW;
   if (OW <= 8) g.OWv = 8;
@@ -610,6 +619,18 @@ static ConvGeom make_geom(int N, int OH, int OW) {
   g.bw = g.OWv < 32 ? g.OWv : 32;
   g.bh = 32 / g.bw;
   g.OHv = (OH + g.bh - 1) / g.bh * g.bh;
+  g.one_box = 0; g.box_h = g.bh; g.box_n = 1;
+  if (tile_box && g.OWv <= 32) {
+    const int BH = 128 / g.bw;                 // rows of a whole tile
+    if (OH <= BH) {
+      int ohv = g.bh;
+      while (ohv < OH) ohv <<= 1;              // power of two: divides BH
+      g.OHv = ohv; g.box_h = ohv; g.box_n = BH / ohv;
+    } else {
+      g.OHv = (OH + BH - 1) / BH * BH; g.box_h = BH; g.box_n = 1;
+    }
+    g.one_box = 1;
+  }
   g.cpr = g.OWv >= 32 ? g.OWv / 32 : 1;
   g.cpi = (g.OHv / g.bh) * g.cpr;
   g.total_chunks = N * g.cpi;
@@ -621,10 +642,10 @@ static ConvGeom make_geom(int N, int OH, int OW) {
 // run of K floats starting at a pixel (K == Cp: that pixel's channels; merged: KW pixels' worth,
 // overlapping the next start pixel), dim 1 walks Wdim start pixels.  Box {32, bw, bh, 1}.
 static int make_act_tmap(CUtensorMap* map, const float* ptr, int N, int H, int Wt, int Cp, int K, int Wdim, int bw, int bh,
-                         bool atom32) {
+                         bool atom32, int bn = 1) {
   const uint64_t dims[4] = {(uint64_t)K, (uint64_t)Wdim, (uint64_t)H, (uint64_t)N};
   const uint64_t strides[3] = {(uint64_t)Cp * 4, (uint64_t)Wt * Cp * 4, (uint64_t)H * Wt * Cp * 4};
-  const uint32_t box[4] = {32, (uint32_t)bw, (uint32_t)bh, 1};
+  const uint32_t box[4] = {32, (uint32_t)bw, (uint32_t)bh, (uint32_t)bn};
   return make_tmap(map, ptr, 4, dims, strides, box, atom32);
 }
 
@@ -640,7 +661,7 @@ static int set_max_smem(const void* fn, const char* what) {
 int conv_igemm(const float* x, const float* w, const float* bias, float* y, int N, int H, int Wt, int Cp, int Kreal,
                int Nout, int ldy, int F, int C, int KH, int KW, int pad, int OH, int OW, int relu, int mode) {
   ConvFwdParams p;
-  p.g = make_geom(N, OH, OW);
+  p.g = make_geom(N, OH, OW, true);
   int K, Wdim;                     // contraction length per tap; number of start pixels along W
   if (mode == 1) { p.g.TH = KH; p.g.TW = 1; p.g.dh0 = -pad; p.g.dw0 = 0; K = KW * Cp; Wdim = Wt - KW + 1; }
   else { p.g.TH = KH; p.g.TW = KW; p.g.dh0 = -pad; p.g.dw0 = -pad; K = Kreal; Wdim = Wt; }
@@ -665,7 +686,8 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   const size_t smem = stages * stage_bytes + (2 * stages + 4) * 8 + 16 + 1024;
 
   CUtensorMap tmX, tmW;
-  int rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, K, Wdim, p.g.bw, p.g.bh, false);
+  int rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, K, Wdim, p.g.bw, p.g.one_box ? p.g.box_h : p.g.bh, false,
+                         p.g.one_box ? p.g.box_n : 1);
   if (rc == 0) {
     const uint64_t dims[3] = {(uint64_t)Kp, (uint64_t)Nout, (uint64_t)taps};
     const uint64_t strides[2] = {(uint64_t)Kp * 4, (uint64_t)Kp * Nout * 4};

@@ -32,7 +32,8 @@ struct Philox {
 __device__ __forceinline__ float u01(uint32_t r) { return (float)(r >> 8) * (1.0f / 16777216.0f); }  // [0,1)
 
 __global__ void __launch_bounds__(L_THREADS) rand_uniform_kernel(float* __restrict__ out, int64_t n, uint64_t seed,
-                                                                 uint64_t offset) {
+                                                                 uint64_t offset, const unsigned long long* epoch) {
+  if (epoch) offset += (uint64_t)(*epoch) << 40;     // graph replay r draws from its own counter range
   const Philox rng(seed);
   const int64_t n4 = (n + 3) >> 2;
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
@@ -46,7 +47,8 @@ __global__ void __launch_bounds__(L_THREADS) rand_uniform_kernel(float* __restri
 }
 
 __global__ void __launch_bounds__(L_THREADS) rand_normal_kernel(float* __restrict__ out, int64_t n, uint64_t seed,
-                                                                uint64_t offset) {
+                                                                uint64_t offset, const unsigned long long* epoch) {
+  if (epoch) offset += (uint64_t)(*epoch) << 40;
   const Philox rng(seed);
   const int64_t n4 = (n + 3) >> 2;
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
@@ -67,7 +69,9 @@ __global__ void __launch_bounds__(L_THREADS) rand_normal_kernel(float* __restric
 
 // out = x * (u > p); the (seed, offset) pair regenerates the identical mask for the VJP.
 __global__ void __launch_bounds__(L_THREADS) dropout_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n,
-                                                            float p, uint64_t seed, uint64_t offset, int vec_ok) {
+                                                            float p, uint64_t seed, uint64_t offset, int vec_ok,
+                                                            const unsigned long long* epoch) {
+  if (epoch) offset += (uint64_t)(*epoch) << 40;     // same shift in forward and VJP of one replay
   const Philox rng(seed);
   const int64_t n4 = (n + 3) >> 2;
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
@@ -389,20 +393,20 @@ extern "C" {
 
 int mc_rand_uniform(float* out, int64_t n, uint64_t seed, uint64_t offset) {
   if (n <= 0) return 0;
-  rand_uniform_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(out, n, seed, offset);
+  rand_uniform_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(out, n, seed, offset, graph_epoch());
   MC_LAUNCHED();
   return 0;
 }
 int mc_rand_normal(float* out, int64_t n, uint64_t seed, uint64_t offset) {
   if (n <= 0) return 0;
-  rand_normal_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(out, n, seed, offset);
+  rand_normal_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(out, n, seed, offset, graph_epoch());
   MC_LAUNCHED();
   return 0;
 }
 int mc_dropout(const float* x, float* out, int64_t n, float p, uint64_t seed, uint64_t offset) {
   if (n <= 0) return 0;
   const int vec_ok = aligned16(x) && aligned16(out);
-  dropout_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(x, out, n, p, seed, offset, vec_ok);
+  dropout_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(x, out, n, p, seed, offset, vec_ok, graph_epoch());
   MC_LAUNCHED();
   return 0;
 }
@@ -532,6 +536,8 @@ struct MultiUpdateDesc {
   float* wo[MU_MAX];
   float* s1o[MU_MAX];
   float* s2o[MU_MAX];
+  const unsigned long long* epoch;   // graph replay counter (adam: t = t0 + epoch - 1) or nullptr
+  int64_t t0;
 };
 
 __global__ void __launch_bounds__(L_THREADS) multi_update_kernel(const __grid_constant__ MultiUpdateDesc d) {
@@ -547,6 +553,12 @@ __global__ void __launch_bounds__(L_THREADS) multi_update_kernel(const __grid_co
   const int64_t lo = (int64_t)(blockIdx.x - d.first[t]) * MU_TILE;
   const int64_t hi = (lo + MU_TILE < d.n[t]) ? lo + MU_TILE : d.n[t];
   const float lr = d.h[0];
+  float bc1 = d.h[4], bc2 = d.h[5];
+  if (d.rule == 3 && d.epoch) {
+    const double t = (double)(d.t0 + (int64_t)(*d.epoch) - 1);
+    bc1 = (float)(1.0 - pow((double)d.h[1], t));
+    bc2 = (float)(1.0 - pow((double)d.h[2], t));
+  }
   for (int64_t i = lo + threadIdx.x; i < hi; i += L_THREADS) {
     const float g = dw[i];
     if (d.rule == 0) {
@@ -564,7 +576,7 @@ __global__ void __launch_bounds__(L_THREADS) multi_update_kernel(const __grid_co
       const float nv = d.h[2] * (s2 ? s2[i] : 0.f) + (1.f - d.h[2]) * (g * g);
       s1o[i] = nm;
       s2o[i] = nv;
-      wo[i] = w[i] - lr * (nm / d.h[4]) / (sqrtf(nv / d.h[5]) + d.h[3]);
+      wo[i] = w[i] - lr * (nm / bc1) / (sqrtf(nv / bc2) + d.h[3]);
     }
   }
 }
@@ -580,6 +592,8 @@ int mc_multi_update(int rule, int count, const void* const* w, const void* const
     mc::MultiUpdateDesc d;
     d.count = 0;
     d.rule = rule;
+    d.epoch = mc::graph_epoch();
+    d.t0 = t;
     for (int k = 0; k < 4; ++k) d.h[k] = hyper[k];
     d.h[4] = d.h[5] = 1.f;
     if (rule == 3) {

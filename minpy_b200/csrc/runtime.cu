@@ -11,6 +11,10 @@ static cudaStream_t g_stream = nullptr;
 static int g_device = -1;
 static int g_sm_count = 148;
 static std::atomic<uint64_t> g_launches{0};
+static unsigned long long* g_epoch = nullptr;     // counter of the graph being captured
+static bool g_capturing = false;
+
+__global__ void graph_epoch_inc_kernel(unsigned long long* e) { *e += 1ull; }
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -21,6 +25,7 @@ void set_error(const char* fmt, ...) {
 cudaStream_t stream() { return g_stream; }
 int sm_count() { return g_sm_count; }
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+const unsigned long long* graph_epoch() { return g_capturing ? g_epoch : nullptr; }
 
 static int configure_device(int device) {
   MC_CHECK(cudaSetDevice(device));
@@ -32,6 +37,10 @@ static int configure_device(int device) {
   }
   g_sm_count = prop.multiProcessorCount;
   g_device = device;
+  // The library's own stream.  A BLOCKING stream: it keeps the implicit ordering with the legacy
+  // default stream (where torch.distributed enqueues the NCCL all-reduce), and unlike the legacy
+  // stream it can be captured into a CUDA graph (mc_graph_begin).
+  if (g_stream == nullptr) MC_CHECK(cudaStreamCreateWithFlags(&g_stream, cudaStreamDefault));
   // Keep freed blocks cached in the default mempool instead of returning them to the
   // driver at every synchronisation: training steps reuse the same sizes every step.
   cudaMemPool_t pool;
@@ -82,7 +91,11 @@ int mc_launch_count(uint64_t* count) {
 
 int mc_alloc(void** ptr, size_t nbytes) {
   if (nbytes == 0) nbytes = 16;
-  MC_CHECK(cudaMallocAsync(ptr, nbytes, g_stream));
+  // During capture a stream-ordered allocation would become a graph-owned node whose address
+  // dies with the replay, while the caller keeps the pointer (host-side free list): take the
+  // memory from the driver instead (legal in relaxed capture mode; cudaFreeAsync accepts it later).
+  if (g_capturing) MC_CHECK(cudaMalloc(ptr, nbytes));
+  else MC_CHECK(cudaMallocAsync(ptr, nbytes, g_stream));
   return 0;
 }
 int mc_free(void* ptr) {
@@ -149,17 +162,43 @@ int mc_event_destroy(void* ev) {
 }
 
 int mc_graph_begin(void) {
-  MC_REQUIRE(g_stream != nullptr, "graph capture needs a non-default stream (mc_set_stream)");
-  MC_CHECK(cudaStreamBeginCapture(g_stream, cudaStreamCaptureModeThreadLocal));
+  MC_REQUIRE(g_stream != nullptr, "graph capture needs the library stream (mc_init first)");
+  MC_REQUIRE(!g_capturing, "a capture is already in progress");
+  // one replay counter per graph; it lives as long as the process (8 bytes per captured graph)
+  MC_CHECK(cudaMalloc((void**)&g_epoch, sizeof(unsigned long long)));
+  MC_CHECK(cudaMemsetAsync(g_epoch, 0, sizeof(unsigned long long), g_stream));
+  MC_CHECK(cudaStreamSynchronize(g_stream));
+  MC_CHECK(cudaStreamBeginCapture(g_stream, cudaStreamCaptureModeRelaxed));
+  g_capturing = true;
+  graph_epoch_inc_kernel<<<1, 1, 0, g_stream>>>(g_epoch);
+  MC_LAUNCHED();
   return 0;
 }
 int mc_graph_end(void** graph_exec) {
-  cudaGraph_t graph;
+  MC_REQUIRE(g_capturing, "no capture in progress");
+  g_capturing = false;
+  cudaGraph_t graph = nullptr;
   MC_CHECK(cudaStreamEndCapture(g_stream, &graph));
+  MC_REQUIRE(graph != nullptr, "capture was invalidated");
   cudaGraphExec_t exec;
   MC_CHECK(cudaGraphInstantiate(&exec, graph, 0));
   MC_CHECK(cudaGraphDestroy(graph));
   *graph_exec = (void*)exec;
+  return 0;
+}
+/* Give up a capture after an error inside it: ends the capture, discards the partial graph and
+ * clears the sticky capture error so that eager work can continue. */
+int mc_graph_abort(void) {
+  if (!g_capturing) return 0;
+  g_capturing = false;
+  cudaGraph_t graph = nullptr;
+  cudaStreamEndCapture(g_stream, &graph);
+  if (graph) cudaGraphDestroy(graph);
+  cudaGetLastError();
+  return 0;
+}
+int mc_graph_capturing(int* flag) {
+  *flag = g_capturing ? 1 : 0;
   return 0;
 }
 int mc_graph_launch(void* graph_exec) {

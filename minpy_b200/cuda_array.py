@@ -33,6 +33,23 @@ def ensure_device(device: int = None):
     return _state['device']
 
 
+class BufferPool(object):
+    """Blocks reserved for the temporaries of one captured step graph."""
+    __slots__ = ('lists', 'released')
+
+    def __init__(self):
+        self.lists = {}
+        self.released = False
+
+    def release(self):
+        """The graph is gone: the blocks rejoin the general free list."""
+        self.released = True
+        lists, self.lists = self.lists, {}
+        for nbytes, blocks in lists.items():
+            _Buffer._free_lists.setdefault(nbytes, []).extend(blocks)   # pylint: disable=protected-access
+            _Buffer._cached_bytes += nbytes * len(blocks)               # pylint: disable=protected-access
+
+
 class _Buffer(object):
     """Owns one device allocation.
 
@@ -42,21 +59,29 @@ class _Buffer(object):
     cudaMallocAsync pool gives, minus two ctypes round trips per temporary (a training step
     creates ~100 temporaries of a handful of distinct sizes).  The list is bounded; beyond the
     bound blocks really go back to the library."""
-    __slots__ = ('ptr', 'nbytes')
+    __slots__ = ('ptr', 'nbytes', 'pool')
     _free_lists = {}
     _cached_bytes = 0
     _cache_limit = 32 << 30
     _lib_alloc = None
     _lib_free = None
+    _active_pool = None      # a BufferPool while a step graph is being captured (step_graph.py)
 
     def __init__(self, nbytes):
         nbytes = (nbytes + 511) & ~511 if nbytes else 512
         self.nbytes = nbytes
-        free = _Buffer._free_lists.get(nbytes)
-        if free:
-            self.ptr = free.pop()
-            _Buffer._cached_bytes -= nbytes
-            return
+        pool = self.pool = _Buffer._active_pool
+        if pool is not None:
+            free = pool.lists.get(nbytes)
+            if free:
+                self.ptr = free.pop()
+                return
+        else:
+            free = _Buffer._free_lists.get(nbytes)
+            if free:
+                self.ptr = free.pop()
+                _Buffer._cached_bytes -= nbytes
+                return
         if _Buffer._lib_alloc is None:
             lib = get_lib()
             _Buffer._lib_alloc, _Buffer._lib_free = lib.mc_alloc, lib.cdll.mc_free
@@ -70,7 +95,15 @@ class _Buffer(object):
 
     def __del__(self):
         try:
-            if _Buffer._cached_bytes + self.nbytes <= _Buffer._cache_limit:
+            pool = self.pool
+            if pool is not None and not pool.released:
+                # a block a captured graph writes on every replay: it may only ever be handed to
+                # another capture-time temporary of the same graph, whenever this object dies
+                free = pool.lists.get(self.nbytes)
+                if free is None:
+                    free = pool.lists[self.nbytes] = []
+                free.append(self.ptr)
+            elif _Buffer._cached_bytes + self.nbytes <= _Buffer._cache_limit:
                 free = _Buffer._free_lists.get(self.nbytes)
                 if free is None:
                     free = _Buffer._free_lists[self.nbytes] = []

@@ -113,16 +113,8 @@ def _flat_buffer(total):
     return flat, _state['flat_t']
 
 
-def allreduce_mean(grads):
-    """Average a list of gradients (MinPy Arrays, raw arrays or the Python scalar 0.0 for
-    parameters the loss does not reach) over all ranks; returns a list of the same form."""
-    world = _state['world']
-    if world <= 1:
-        return grads
+def _raw_grads(grads):
     from minpy import array as marray
-    from minpy.array_variants import ArrayType
-    from .cuda_array import CudaArray
-    dist = _dist()
     raws = []
     for g in grads:
         if isinstance(g, marray.Array):
@@ -131,39 +123,70 @@ def allreduce_mean(grads):
             raws.append(float(g.val))
         else:
             raws.append(g)
-    if any(isinstance(r, CudaArray) for r in raws):
-        from . import ops
-        lib = ops.L()
-        shapes = [r.shape if isinstance(r, (CudaArray, np.ndarray)) else None for r in raws]
-        offs, total = _segments([ops._prod(s) if s is not None else 0 for s in shapes])  # pylint: disable=protected-access
-        # a fresh flat buffer per step: the views handed back stay valid for as long as the
-        # caller keeps them (the pool recycles the block as soon as they die)
-        flat = CudaArray.empty((total,))
-        srcs, dsts, ns = [], [], []
-        for r, off, shape in zip(raws, offs, shapes):
-            if shape is None:
-                continue
-            if isinstance(r, np.ndarray):
-                r = CudaArray.from_numpy(r)
-            r = ops.as_f32(r)
-            srcs.append(r.ptr)
-            dsts.append(flat.ptr + 4 * off)
-            ns.append(r.size)
-        k = len(srcs)
-        if k:
-            lib.mc_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_void_p * k)(*dsts), (ctypes.c_int64 * k)(*ns), k)
-        t = torch_view(flat)
-        if _state['backend'] == 'nccl':
-            dist.all_reduce(t, op=dist.ReduceOp.AVG)
-        else:   # pragma: no cover  (device arrays with a host backend)
-            raise RuntimeError('device gradients need the nccl backend')
-        out = []
-        for r, off, shape in zip(raws, offs, shapes):
-            if shape is None:
-                out.append(r)
-            else:
-                out.append(marray.wrap(CudaArray(flat.buf, flat.ptr + 4 * off, tuple(shape))))
+    return raws
+
+
+def pack_gradients(grads):
+    """Device gradients -> ONE flat buffer (the multi-tensor pack kernel) + zero-copy views of it in
+    the form of `grads`.  Returns (flat, views); flat is None when no gradient lives on the device."""
+    from minpy import array as marray
+    from .cuda_array import CudaArray
+    raws = _raw_grads(grads)
+    if not any(isinstance(r, CudaArray) for r in raws):
+        return None, grads
+    from . import ops
+    lib = ops.L()
+    shapes = [r.shape if isinstance(r, (CudaArray, np.ndarray)) else None for r in raws]
+    offs, total = _segments([ops._prod(s) if s is not None else 0 for s in shapes])  # pylint: disable=protected-access
+    # a fresh flat buffer per call: the views handed back stay valid for as long as the
+    # caller keeps them (the pool recycles the block as soon as they die)
+    flat = CudaArray.empty((total,))
+    srcs, dsts, ns = [], [], []
+    for r, off, shape in zip(raws, offs, shapes):
+        if shape is None:
+            continue
+        if isinstance(r, np.ndarray):
+            r = CudaArray.from_numpy(r)
+        r = ops.as_f32(r)
+        srcs.append(r.ptr)
+        dsts.append(flat.ptr + 4 * off)
+        ns.append(r.size)
+    k = len(srcs)
+    if k:
+        lib.mc_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_void_p * k)(*dsts), (ctypes.c_int64 * k)(*ns), k)
+    out = []
+    for r, off, shape in zip(raws, offs, shapes):
+        if shape is None:
+            out.append(r)
+        else:
+            out.append(marray.wrap(CudaArray(flat.buf, flat.ptr + 4 * off, tuple(shape))))
+    return flat, out
+
+
+def reduce_flat(flat, view=None):
+    """In-place average of a flat device buffer over all ranks (NCCL on torch's stream, which is
+    ordered with the library's blocking stream through the legacy default stream)."""
+    if _state['world'] <= 1:
+        return
+    if _state['backend'] != 'nccl':   # pragma: no cover  (device arrays with a host backend)
+        raise RuntimeError('device gradients need the nccl backend')
+    dist = _dist()
+    dist.all_reduce(view if view is not None else torch_view(flat), op=dist.ReduceOp.AVG)
+
+
+def allreduce_mean(grads):
+    """Average a list of gradients (MinPy Arrays, raw arrays or the Python scalar 0.0 for
+    parameters the loss does not reach) over all ranks; returns a list of the same form."""
+    world = _state['world']
+    if world <= 1:
+        return grads
+    from minpy import array as marray
+    dist = _dist()
+    flat, out = pack_gradients(grads)
+    if flat is not None:
+        reduce_flat(flat)
         return out
+    raws = _raw_grads(grads)
     # host gradients (NumPy policy): used by the CPU tests of this logic and by the CPU baseline
     import torch
     host = [np.asarray(r, dtype=np.float64) for r in raws if isinstance(r, np.ndarray)]
