@@ -220,6 +220,21 @@ int mc_gemm(int trans_a, int trans_b, int64_t M, int64_t N, int64_t K,
 /* Which path the last mc_gemm call on this thread took (0 fp32, 1 tf32 tcgen05). */
 int mc_gemm_last_path(int* path);
 
+/* ------------------------------------------------- data-parallel exchange ---- */
+/* The one collective of the path (no reference counterpart: the reference has no
+ * multi-device training loop, minpy/context.py:92-98): in-place all-reduce of the flat fp32
+ * gradient buffer between the tape's backward pass and the update rules (the gap between
+ * minpy/nn/solver.py:184 and :190), NCCL over NVLink/NVSwitch on the LIBRARY stream, so that it
+ * is captured into the step graph.  One process per GPU: rank 0 calls mc_comm_unique_id, the
+ * 128 bytes travel through the launcher's rendezvous, every rank calls mc_comm_init. */
+int mc_comm_unique_id(void* id128);
+int mc_comm_init(int rank, int world, const void* id128);
+int mc_comm_info(int* rank, int* world, int* nccl_version);
+int mc_allreduce_avg(float* buf, int64_t n);
+int mc_allreduce_sum(float* buf, int64_t n);
+int mc_broadcast(float* buf, int64_t n, int root);
+int mc_comm_destroy(void);
+
 /* ------------------------------------------------------------ nn.layers ------ */
 /* layers.batchnorm train mode, nn/layers.py:93-110: biased variance, returns updated
  * running stats (momentum*r + (1-momentum)*stat). save_mean/save_invstd feed the VJP. */

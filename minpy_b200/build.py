@@ -18,7 +18,7 @@ BUILD_DIR = os.path.join(HERE, '_build')
 LIB_PATH = os.path.join(HERE, 'libminpy_cuda.so')
 HEADER = os.path.join(os.path.dirname(HERE), 'include', 'minpy_cuda.h')
 
-SOURCES = ['runtime.cu', 'elementwise.cu', 'reduce.cu', 'softmax.cu', 'index.cu', 'gemm.cu', 'layers.cu', 'conv.cu', 'conv_tc.cu']
+SOURCES = ['runtime.cu', 'elementwise.cu', 'reduce.cu', 'softmax.cu', 'index.cu', 'gemm.cu', 'layers.cu', 'conv.cu', 'conv_tc.cu', 'comm.cu']
 
 NVCC_FLAGS = [
     '-gencode', 'arch=compute_100a,code=sm_100a',
@@ -70,7 +70,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         with open(vers, 'w') as f:
             f.write('{ global: mc_*; local: *; };\n')
         cmd = [_nvcc(), '-shared', '-o', LIB_PATH] + objs + [
-            '-gencode', 'arch=compute_100a,code=sm_100a', '-Xlinker', '--version-script=' + vers]
+            '-gencode', 'arch=compute_100a,code=sm_100a', '-Xlinker', '--version-script=' + vers, '-ldl']
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError('link failed:\n' + res.stderr[-4000:])

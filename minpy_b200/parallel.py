@@ -19,7 +19,7 @@ import os
 
 import numpy as np
 
-_state = {'initialised': False, 'world': 1, 'rank': 0, 'backend': None, 'flat': None, 'flat_t': None}
+_state = {'initialised': False, 'world': 1, 'rank': 0, 'backend': None, 'flat': None, 'flat_t': None, 'native': False}
 
 
 def _dist():
@@ -54,13 +54,39 @@ def init(backend=None):
             kwargs['device_id'] = torch.device('cuda', int(os.environ.get('LOCAL_RANK', str(rank))))
         dist.init_process_group(backend=backend, rank=rank, world_size=world, **kwargs)
     _state.update(initialised=True, world=world, rank=rank, backend=backend)
+    if backend == 'nccl' and os.environ.get('MINPY_NATIVE_NCCL', '1') == '1':
+        _init_native_comm(rank, world)
     return world
 
 
+def _init_native_comm(rank, world):
+    """The library's own NCCL communicator (csrc/comm.cu): collectives on the library stream, hence
+    inside the captured step graph.  torch.distributed stays the rendezvous (it carries the 128-byte
+    unique id) and the barrier."""
+    from .ops import L
+    lib = L()
+    dist = _dist()
+    uid = ctypes.create_string_buffer(128)
+    if rank == 0:
+        lib.mc_comm_unique_id(uid)
+    box = [uid.raw]
+    dist.broadcast_object_list(box, src=0)
+    lib.mc_comm_init(rank, world, ctypes.create_string_buffer(box[0], 128))
+    _state['native'] = True
+
+
+def native_comm():
+    """True when gradients are exchanged by the library's own communicator (capturable)."""
+    return bool(_state['native'])
+
+
 def shutdown():
+    # The library communicator is NOT destroyed here: step graphs that captured its all-reduce keep
+    # it referenced and ncclCommDestroy then blocks forever (seen on 2 x B200, gpurun_out/r1n); the
+    # process exit reclaims it.  mc_comm_destroy stays available for callers that own no graphs.
     if _state['world'] > 1 and _dist().is_initialized():
         _dist().destroy_process_group()
-    _state.update(initialised=False, world=1, rank=0, backend=None, flat=None, flat_t=None)
+    _state.update(initialised=False, world=1, rank=0, backend=None, flat=None, flat_t=None, native=False)
 
 
 def world_size():
@@ -167,6 +193,10 @@ def reduce_flat(flat, view=None):
     """In-place average of a flat device buffer over all ranks (NCCL on torch's stream, which is
     ordered with the library's blocking stream through the legacy default stream)."""
     if _state['world'] <= 1:
+        return
+    if _state['native']:
+        from .ops import L
+        L().mc_allreduce_avg(flat.ptr, flat.size)
         return
     if _state['backend'] != 'nccl':   # pragma: no cover  (device arrays with a host backend)
         raise RuntimeError('device gradients need the nccl backend')

@@ -20,7 +20,9 @@ What makes a replay a NEW step instead of a repetition of the captured one:
     advances;
   * hyper-parameters baked into kernel arguments (learning rate ...): a signature of every scalar in
     the optimizer configs is checked before each replay; a change (lr decay) triggers re-capture.
-Data parallel (world > 1): two graphs, the NCCL all-reduce of the flat gradient buffer between them.
+Data parallel (world > 1): the all-reduce of the flat gradient buffer is a node of the same graph when
+the library's own NCCL communicator is up (csrc/comm.cu); with torch's communicator it runs between
+two graphs.
 
 Anything the capture cannot express (a device->host read inside the loss function, a host array
 created inside the step, shapes that change) aborts the capture, restores the Python state and
@@ -195,10 +197,13 @@ class StepGraph(object):
                 if flat is None:
                     raise StepGraphUnsupported('gradients are not on the device')
                 self.flat = flat
-                ex = ctypes.c_void_p()
-                lib.mc_graph_end(ctypes.byref(ex))
-                execs.append(ex)
-                lib.mc_graph_begin()
+                if parallel.native_comm():
+                    parallel.reduce_flat(flat)            # NCCL on the library stream: captured
+                else:
+                    ex = ctypes.c_void_p()
+                    lib.mc_graph_end(ctypes.byref(ex))
+                    execs.append(ex)
+                    lib.mc_graph_begin()
             solver._step_update(names, grads)                 # pylint: disable=protected-access
             loss_raw = _raw(loss)
             if loss_raw is None:
