@@ -107,6 +107,7 @@ class CallTimer(object):
         self.lib = lib
         self.records = []          # (name, start_event, stop_event, work) ; work = (flops, bytes)
         self.pool = []
+        self.calls = []            # (name, raw function, args) in launch order, for replay_family
 
     def _event(self):
         if self.pool:
@@ -134,7 +135,44 @@ class CallTimer(object):
             fn(*args)
             self.lib.mc_event_record(e1)
             self.records.append((name, e0, e1, _work_of(name, args)))
+            self.calls.append((name, fn, args))
         return call
+
+    def replay_family(self, family, steps_recorded, reps=20):
+        """Average device time of ONE step's worth of `family` calls, launched back to back from a
+        CUDA graph (no host gaps between kernels), CUDA events on the library stream.  The calls are
+        the recorded ones with their recorded arguments; their outputs land in pool memory nobody
+        reads afterwards (this runs last)."""
+        lib = self.lib
+        calls = [(fn, args) for name, fn, args in self.calls if name == family]
+        per_step = len(calls) // max(1, steps_recorded)
+        calls = calls[-per_step:] if per_step else []
+        if not calls:
+            return None
+        try:
+            lib.mc_sync()
+            lib.mc_graph_begin()
+            for fn, args in calls:
+                fn(*args)
+            ex = ctypes.c_void_p()
+            lib.mc_graph_end(ctypes.byref(ex))
+        except Exception as exc:  # pylint: disable=broad-except
+            lib.cdll.mc_graph_abort()
+            log('replay of %s not possible: %s' % (family, exc))
+            return None
+        for _ in range(3):
+            lib.mc_graph_launch(ex)
+        e0, e1 = self._event(), self._event()
+        lib.mc_sync()
+        lib.mc_event_record(e0)
+        for _ in range(reps):
+            lib.mc_graph_launch(ex)
+        lib.mc_event_record(e1)
+        lib.mc_sync()
+        ms = ctypes.c_float()
+        lib.mc_event_elapsed_ms(e0, e1, ctypes.byref(ms))
+        lib.mc_graph_destroy(ex)
+        return {'calls': len(calls), 'ms_per_step': ms.value / reps}
 
     def uninstall(self):
         for name, fn in self.saved.items():
@@ -197,6 +235,30 @@ def _work_of(name, a):
             return 0.0, 28.0 * _i(a[12])
         if name in ('mc_memcpy_d2d', 'mc_memset'):
             return 0.0, (2.0 if name == 'mc_memcpy_d2d' else 1.0) * _i(a[2])
+        if name in ('mc_conv2d_nhwc_fwd', 'mc_conv2d_nhwc_wgrad'):
+            N, C, H, W, Cp, wpad, F, Fp, KH, KW, pad = [_i(v) for v in a[4:15]]
+            OH, OW = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+            return (2.0 * N * OH * OW * F * C * KH * KW,
+                    4.0 * (N * H * W * Cp + N * OH * OW * Fp + F * C * KH * KW))
+        if name == 'mc_conv2d_nhwc_dgrad':
+            N, C, H, W, Cp, F, Fp, KH, KW, pad = [_i(v) for v in a[3:13]]
+            OH, OW = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+            return (2.0 * N * OH * OW * F * C * KH * KW,
+                    4.0 * (N * H * W * Cp + N * OH * OW * Fp + F * C * KH * KW))
+        if name == 'mc_maxpool2d_nhwc_fwd':
+            N, H, W, Cp, KH, KW, st = [_i(v) for v in a[3:10]]
+            OH, OW = (H - KH) // st + 1, (W - KW) // st + 1
+            return 0.0, 4.0 * N * H * W * Cp + 5.0 * N * OH * OW * Cp
+        if name == 'mc_maxpool2d_nhwc_bwd':
+            N, H, W, Cp, K, OH, OW = [_i(v) for v in a[4:11]]
+            return 0.0, 4.0 * N * H * W * Cp + 9.0 * N * OH * OW * Cp
+        if name in ('mc_nchw_to_nhwc', 'mc_nhwc_to_nchw'):
+            N, C, H, W = [_i(v) for v in a[2:6]]
+            return 0.0, 8.0 * N * C * H * W
+        if name == 'mc_multi_update':
+            k = _i(a[1])
+            per = {0: 12.0, 1: 20.0, 2: 20.0, 3: 28.0}[_i(a[0])]
+            return 0.0, per * sum(int(a[9][j]) for j in range(k))
         if name == 'mc_lstm_cell_fwd':
             N, H = _i(a[5]), _i(a[6])
             return 0.0, 4.0 * N * H * (4 + 1 + 2 + 4)
@@ -217,6 +279,17 @@ def measured_peaks():
         return {'hbm_gbs': p['hbm_gbs'], 'bf16_tflops': p['bf16_tflops'],
                 'bf16_tflops_sustained': p.get('bf16_tflops_sustained', p['bf16_tflops']), 'source': 'measured'}
     return {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0, 'source': 'fallback'}
+
+
+def ncu_traffic(workload, family):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `family` from the committed
+    `ncu --set full` capture (profiles/traffic.json, written by profiles/summarize_ncu.py), or None."""
+    path = os.path.join(ROOT, 'profiles', 'traffic.json')
+    try:
+        with open(path) as f:
+            return json.load(f).get(workload, {}).get(family)
+    except (OSError, ValueError):
+        return None
 
 
 # ---------------------------------------------------------------- the b200 training arm ----
@@ -366,29 +439,47 @@ def run_b200(args):
                 name, f['calls'] / inst_steps, 1e3 * f['ms'] / f['calls'], 100 * f['ms'] / tot,
                 f['bytes'] / (f['ms'] * 1e-3) / 1e9 if f['ms'] else 0, f['flops'] / (f['ms'] * 1e-3) / 1e12 if f['ms'] else 0))
         top_name, top = ranked[0]
-        if top['flops'] > 0:
-            # TF32 runs at half the bf16 tensor rate; the denominator is still the measured bf16
-            # cuBLAS figure (sustained: the kernel is timed inside a long step) as the recipe asks
-            ai = top['flops'] / max(1.0, top['bytes'])
-            achieved = top['flops'] / (top['ms'] * 1e-3) / 1e12
+        # duration of the dominant family: its recorded calls of one step, replayed back to back from a
+        # CUDA graph (the event pairs above include the host gap in front of every small kernel)
+        rep = None if top_name.startswith(('mc_allreduce', 'mc_broadcast')) else timer.replay_family(top_name, inst_steps)
+        calls_per_step = top['calls'] / inst_steps
+        if rep is not None:
+            fam_ms = rep['ms_per_step']
+            timing = 'graph replay of the %d %s calls of one step, 20 repetitions, CUDA events' % (rep['calls'], top_name)
+        else:
+            fam_ms = top['ms'] / inst_steps
+            timing = 'CUDA-event pair around every call'
+        flops, nbytes = top['flops'] / inst_steps, top['bytes'] / inst_steps
+        tf32_peak = peaks['bf16_tflops_sustained'] / 2.0          # kind::tf32 issues at half the bf16 rate
+        t_tensor = flops / (tf32_peak * 1e12)
+        t_hbm = nbytes / (peaks['hbm_gbs'] * 1e9)
+        traffic = ncu_traffic(args.workload, top_name)
+        if flops > 0 and t_tensor >= t_hbm:
+            achieved = flops / (fam_ms * 1e-3) / 1e12
             peak = peaks['bf16_tflops_sustained']
             roofline = {'kernel': top_name + ' (tcgen05 kind::tf32)', 'bound': 'tensor', 'achieved': round(achieved, 2),
-                        'peak': peak, 'unit': 'TFLOP/s', 'frac': round(achieved / peak, 4), 'traffic': None,
-                        'peak_source': peaks['source'] + ' bf16 cuBLAS sustained; tf32 nominal rate is half of bf16',
-                        'avg_us_per_launch': round(1e3 * top['ms'] / top['calls'], 2),
-                        'share_of_kernel_time': round(top['ms'] / tot, 3),
-                        'arith_intensity_flop_per_byte': round(ai, 1),
-                        'hbm_bound_equiv_gbs': round(top['bytes'] / (top['ms'] * 1e-3) / 1e9, 1)}
+                        'peak': peak, 'unit': 'TFLOP/s', 'frac': round(achieved / peak, 4), 'traffic': traffic,
+                        'frac_of_tf32_rate': round(achieved / tf32_peak, 4),
+                        'peak_source': peaks['source'] + ' bf16 cuBLAS sustained (MEASURED_PEAKS.json); kind::tf32 runs '
+                                       'at half that rate, frac_of_tf32_rate uses the halved figure'}
         else:
-            achieved = top['bytes'] / (top['ms'] * 1e-3) / 1e9
+            achieved = nbytes / (fam_ms * 1e-3) / 1e9
             roofline = {'kernel': top_name, 'bound': 'hbm', 'achieved': round(achieved, 1), 'peak': peaks['hbm_gbs'],
-                        'unit': 'GB/s', 'frac': round(achieved / peaks['hbm_gbs'], 4), 'traffic': None,
-                        'peak_source': peaks['source'],
-                        'avg_us_per_launch': round(1e3 * top['ms'] / top['calls'], 2),
-                        'share_of_kernel_time': round(top['ms'] / tot, 3)}
-        roofline['how'] = ('CUDA-event pair around every library call in a second pass of %d steps; '
-                           'summed kernel time %.3f ms/step vs %.3f ms/step wall' % (inst_steps, tot / inst_steps,
-                                                                                     dev_ms / args.steps))
+                        'unit': 'GB/s', 'frac': round(achieved / peaks['hbm_gbs'], 4), 'traffic': traffic,
+                        'peak_source': peaks['source'] + ' copy bandwidth (MEASURED_PEAKS.json)'}
+            if flops > 0:
+                roofline['tflops'] = round(flops / (fam_ms * 1e-3) / 1e12, 2)
+        roofline.update({
+            'avg_us_per_launch': round(1e3 * fam_ms / max(1.0, calls_per_step), 2),
+            'launches_per_step': round(calls_per_step, 1),
+            'algorithmic_flops_per_step': flops, 'algorithmic_bytes_per_step': nbytes,
+            'arith_intensity_flop_per_byte': round(flops / max(1.0, nbytes), 1),
+            'share_of_kernel_time': round(top['ms'] / tot, 3),
+            'ideal_us_per_step': round(1e6 * max(t_tensor, t_hbm), 2), 'timing': timing})
+        roofline['how'] = ('families ranked by a CUDA-event pair around every library call in an eager pass of %d '
+                           'steps (summed %.3f ms/step, host gaps included) vs %.3f ms/step for the timed steps; '
+                           'the dominant family is then re-timed without host gaps (see timing)' % (
+                               inst_steps, tot / inst_steps, dev_ms / args.steps))
         out = {
             'metric': METRIC, 'value': round(value, 1), 'unit': 'samples/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': round(dev_ms / args.steps, 4), 'higher_is_better': True,

@@ -48,10 +48,12 @@ struct ConvGeom {
   int TH, TW;            // taps along h / w enumerated by the kernel
   int one_box;           // the 4 chunks of a tile form ONE TMA box {32, bw, box_h, box_n}
   int box_h, box_n;
+  int cpi_shift;         // log2(cpi) when cpi is a power of two, else -1
+  int owv_shift;         // log2(OWv) when OWv < 32 (8 or 16)
 };
 
 __device__ __forceinline__ void chunk_origin(const ConvGeom& g, int chunk, int& n, int& oh0, int& ow0) {
-  n = chunk / g.cpi;
+  n = g.cpi_shift >= 0 ? (chunk >> g.cpi_shift) : chunk / g.cpi;
   const int r = chunk - n * g.cpi;
   if (g.OWv >= 32) { oh0 = r / g.cpr; ow0 = (r - oh0 * g.cpr) * 32; }
   else { oh0 = r * g.bh; ow0 = 0; }
@@ -64,6 +66,8 @@ struct ConvFwdParams {
   const float* bias;     // (Nout,) or nullptr
   int Nout, ldy;         // real output channels, channel pitch of y
   int BN, ncb, stages, relu;
+  int nacc;              // accumulator tiles in the TMEM ring (nacc * BN <= 512 columns)
+  int wres;              // all weight blocks stay resident in shared memory (one n-tile, <= 96 KB)
 };
 
 // Persistent: grid = min(#tiles, #SMs); a CTA walks tiles t = blockIdx.x, += gridDim.x, where a
@@ -81,14 +85,18 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
   constexpr uint32_t chunk_bytes = 32u * 128u;                    // [32 pixels][32 ch]
   constexpr uint32_t a_bytes = 4u * chunk_bytes;
   const uint32_t b_bytes = (uint32_t)p.BN * 128u;                 // [BN][32 ch]
-  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t w_bytes = p.wres ? (uint32_t)(p.g.TH * p.g.TW * p.ncb) * b_bytes : 0u;   // resident weights first
+  const uint32_t stage_bytes = a_bytes + (p.wres ? 0u : b_bytes);
   const int STAGES = p.stages;
-  const uint32_t bar_base = smem_base + STAGES * stage_bytes;
+  const int NACC = p.nacc;
+  const uint32_t ring_base = smem_base + w_bytes;
+  const uint32_t bar_base = ring_base + STAGES * stage_bytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto tmem_full_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
-  auto tmem_empty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
-  const uint32_t tmem_slot = bar_base + (2 * STAGES + 4) * 8;
+  auto tmem_empty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + NACC + a); };
+  const uint32_t w_bar = bar_base + 8u * (2 * STAGES + 2 * NACC);
+  const uint32_t tmem_slot = w_bar + 8u;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int taps = p.g.TH * p.g.TW;
@@ -96,11 +104,12 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
   const int ptiles = (p.g.total_chunks + 3) / 4;
   const int ntiles = (p.Nout + p.BN - 1) / p.BN;
   const int total_tiles = ptiles * ntiles;
-  const uint32_t tcols = (uint32_t)(2 * p.BN);                    // BN is a power of two in [32, 256]
+  const uint32_t tcols = (uint32_t)(p.nacc * p.BN);               // BN, nacc powers of two; nacc * BN in [64, 512]
 
   if (warp == 4 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full_bar(a), 1); mbar_init(tmem_empty_bar(a), 4); }
+    for (int a = 0; a < NACC; ++a) { mbar_init(tmem_full_bar(a), 1); mbar_init(tmem_empty_bar(a), 4); }
+    mbar_init(w_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -117,29 +126,54 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
   if (warp == 4) {
     if (lane == 0) {
       // ------------------------------ TMA producer ------------------------------------
-      int it = 0;
+      // One thread: every instruction here is serial latency (an EMPTY mainloop still cost 0.2 us
+      // per k-block, profiles/r1p), so everything loop-invariant lives in registers, the stage
+      // index / phase are carried incrementally and nothing is divided inside the tap loop.
+      int s = 0;
+      uint32_t ph = 0;
+      const int TH = p.g.TH, TW = p.g.TW, ncb = p.ncb, dh0 = p.g.dh0, dw0 = p.g.dw0, BN = p.BN;
+      const bool one_box = p.g.one_box != 0, wres = p.wres != 0;
+      int pt = blockIdx.x % ptiles, nt = blockIdx.x / ptiles;
+      const int dpt = gridDim.x % ptiles, dnt = gridDim.x / ptiles;
+      if (wres && (int)blockIdx.x < total_tiles) {
+        // every CTA needs every weight block for every tile: fetch them once per CTA instead of
+        // once per tile (148 SMs re-reading the same few L2 lines per k-block was the bottleneck
+        // of the first layer: 50 of 120 us, profiles/r1p)
+        mbar_expect_tx(w_bar, w_bytes);
+        for (int t = 0; t < taps; ++t)
+          for (int cb = 0; cb < ncb; ++cb)
+            tma_load_3d(smem_base + (uint32_t)(t * ncb + cb) * b_bytes, &tmW, w_bar, cb * BKC, 0, t);
+      }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int chunk0 = (tile % ptiles) * 4;
-        const int n0 = (tile / ptiles) * p.BN;
+        const int chunk0 = pt * 4;
+        const int n0 = nt * BN;
+        pt += dpt; nt += dnt;
+        if (pt >= ptiles) { pt -= ptiles; ++nt; }
         int cn[4], coh[4], cow[4];
+        if (one_box) {
+          chunk_origin(p.g, chunk0, cn[0], coh[0], cow[0]);
+        } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) chunk_origin(p.g, chunk0 + j, cn[j], coh[j], cow[j]);
-        for (int tap = 0; tap < taps; ++tap) {
-          const int th = tap / p.g.TW, tw = tap - th * p.g.TW;
-          for (int cb = 0; cb < p.ncb; ++cb, ++it) {
-            const int s = it % STAGES;
-            const uint32_t ph = (it / STAGES) & 1;
-            mbar_wait(empty_bar(s), ph ^ 1u);
-            mbar_expect_tx(full_bar(s), stage_bytes);
-            const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
-            if (p.g.one_box) {
-              tma_load_4d(sa, &tmX, full_bar(s), cb * BKC, cow[0] + tw + p.g.dw0, coh[0] + th + p.g.dh0, cn[0]);
-            } else {
+          for (int j = 0; j < 4; ++j) chunk_origin(p.g, chunk0 + j, cn[j], coh[j], cow[j]);
+        }
+        int tap = 0;
+        for (int th = 0; th < TH; ++th) {
+          for (int tw = 0; tw < TW; ++tw, ++tap) {
+            for (int cb = 0; cb < ncb; ++cb) {
+              mbar_wait(empty_bar(s), ph ^ 1u);
+              const uint32_t fb = full_bar(s);
+              mbar_expect_tx(fb, stage_bytes);
+              const uint32_t sa = ring_base + s * stage_bytes;
+              if (one_box) {
+                tma_load_4d(sa, &tmX, fb, cb * BKC, cow[0] + tw + dw0, coh[0] + th + dh0, cn[0]);
+              } else {
 #pragma unroll
-              for (int j = 0; j < 4; ++j)
-                tma_load_4d(sa + j * chunk_bytes, &tmX, full_bar(s), cb * BKC, cow[j] + tw + p.g.dw0, coh[j] + th + p.g.dh0, cn[j]);
+                for (int j = 0; j < 4; ++j)
+                  tma_load_4d(sa + j * chunk_bytes, &tmX, fb, cb * BKC, cow[j] + tw + dw0, coh[j] + th + dh0, cn[j]);
+              }
+              if (!wres) tma_load_3d(sa + a_bytes, &tmW, fb, cb * BKC, n0, tap);
+              if (++s == STAGES) { s = 0; ph ^= 1u; }
             }
-            tma_load_3d(sb, &tmW, full_bar(s), cb * BKC, n0, tap);
           }
         }
       }
@@ -149,45 +183,55 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
       // ------------------------------ MMA issuer --------------------------------------
       // c_format F32, a/b TF32, both operands K-major, N>>3 at [17,23), M>>4 at [24,29)
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-      int it = 0, ti = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
-        const int acc = ti & 1;
-        mbar_wait(tmem_empty_bar(acc), (((uint32_t)ti >> 1) & 1u) ^ 1u);   // epilogue drained this accumulator
+      int s = 0, acc = 0;
+      uint32_t ph = 0, aph = 0;
+      const bool wres = p.wres != 0;
+      const int BN = p.BN;
+      // descriptor of address A = constant bits | (A >> 4): stepping 32 bytes along K adds 2
+      const uint64_t desc0 = make_desc(0, 16, 1024, 2);
+      if (wres && (int)blockIdx.x < total_tiles) mbar_wait(w_bar, 0);
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(tmem_empty_bar(acc), aph ^ 1u);                          // epilogue drained this accumulator
         tcgen05_fence_after();
-        const uint32_t tacc = tmem_base + (uint32_t)(acc * p.BN);
-        for (int i = 0; i < num_it; ++i, ++it) {
-          const int s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
+        const uint32_t tacc = tmem_base + (uint32_t)(acc * BN);
+        uint32_t wb = smem_base;                                           // resident weight block of iteration i
+        for (int i = 0; i < num_it; ++i, wb += b_bytes) {
           mbar_wait(full_bar(s), ph);
           tcgen05_fence_after();
-          const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+          const uint32_t sa = ring_base + s * stage_bytes;
+          const uint32_t sb = wres ? wb : sa + a_bytes;
+          const uint64_t adesc = desc0 + (uint64_t)((sa & 0x3FFFFu) >> 4);
+          const uint64_t bdesc = desc0 + (uint64_t)((sb & 0x3FFFFu) >> 4);
 #pragma unroll
-          for (int k = 0; k < BKC / UMMA_K; ++k) {
-            const uint64_t adesc = make_desc(sa + k * 32, 16, 1024, 2);
-            const uint64_t bdesc = make_desc(sb + k * 32, 16, 1024, 2);
-            umma_tf32(tacc, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
-          }
+          for (int k = 0; k < BKC / UMMA_K; ++k)
+            umma_tf32(tacc, adesc + 2u * k, bdesc + 2u * k, idesc, (i > 0 || k > 0) ? 1u : 0u);
           umma_commit(empty_bar(s));
+          if (++s == STAGES) { s = 0; ph ^= 1u; }
         }
         umma_commit(tmem_full_bar(acc));
+        if (++acc == NACC) { acc = 0; aph ^= 1u; }
       }
     }
   } else {
     // ---------------------------------- epilogue (warps 0-3) ----------------------------
     const bool vec_ok = ((p.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15u) == 0);
-    int ti = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
-      const int acc = ti & 1;
-      const int chunk0 = (tile % ptiles) * 4;
-      const int n0 = (tile / ptiles) * p.BN;
+    int acc = 0;
+    uint32_t aph = 0;
+    int pt = blockIdx.x % ptiles, nt = blockIdx.x / ptiles;
+    const int dpt = gridDim.x % ptiles, dnt = gridDim.x / ptiles;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int chunk0 = pt * 4;
+      const int n0 = nt * p.BN;
+      pt += dpt; nt += dnt;
+      if (pt >= ptiles) { pt -= ptiles; ++nt; }
       int n, oh0, ow0;
       chunk_origin(p.g, chunk0 + warp, n, oh0, ow0);
       int oh, ow;
       if (p.g.OWv >= 32) { oh = oh0; ow = ow0 + lane; }
-      else { oh = oh0 + lane / p.g.OWv; ow = lane % p.g.OWv; }
+      else { oh = oh0 + (lane >> p.g.owv_shift); ow = lane & (p.g.OWv - 1); }
       const bool live = (n < p.g.N) && (oh < p.g.OH) && (ow < p.g.OW);
       float* __restrict__ yrow = p.y + (((int64_t)n * p.g.OH + oh) * p.g.OW + ow) * p.ldy;
-      mbar_wait(tmem_full_bar(acc), ((uint32_t)ti >> 1) & 1u);
+      mbar_wait_warp(tmem_full_bar(acc), aph);
       tcgen05_fence_after();
       const uint32_t tacc = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * p.BN);
 #pragma unroll 1
@@ -230,6 +274,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tmem_empty_bar(acc)) : "memory");
+      if (++acc == NACC) { acc = 0; aph ^= 1u; }
     }
   }
   tcgen05_fence_before();
@@ -383,7 +428,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   }
   __syncwarp();
 
-  mbar_wait(tmem_full_bar, 0);
+  mbar_wait_warp(tmem_full_bar, 0);
   tcgen05_fence_after();
   __syncwarp();
   const int f = f0 + warp * 32 + lane;
@@ -635,6 +680,9 @@ static ConvGeom make_geom(int N, int OH, int OW, bool tile_box = false) {
   g.cpi = (g.OHv / g.bh) * g.cpr;
   g.total_chunks = N * g.cpi;
   g.dh0 = g.dw0 = 0; g.TH = g.TW = 1;
+  g.cpi_shift = -1;
+  for (int b = 0; b < 30; ++b) if ((1 << b) == g.cpi) g.cpi_shift = b;
+  g.owv_shift = g.OWv == 8 ? 3 : (g.OWv == 16 ? 4 : 5);
   return g;
 }
 
@@ -678,12 +726,21 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   int bn = 32;
   while (bn < Nout && bn < 256) bn <<= 1;
   p.BN = bn;
-  const size_t stage_bytes = 4 * 4096 + (size_t)p.BN * 128;
-  int stages = (int)((200 * 1024) / stage_bytes);
+  // TMEM ring: as many accumulator tiles as fit in the 512 columns (power of two, at most 8): the
+  // tcgen05.commit -> epilogue -> release chain of one tile is ~1 us, which two buffers cannot hide
+  // when a tile is only a few k-blocks long
+  int nacc = 2;
+  while (nacc * 2 * p.BN <= 512 && nacc < 8) nacc <<= 1;
+  p.nacc = nacc;
+  const int ntiles_n = (Nout + p.BN - 1) / p.BN;
+  const size_t w_bytes = (size_t)taps * p.ncb * p.BN * 128;
+  p.wres = (ntiles_n == 1 && w_bytes <= 96 * 1024) ? 1 : 0;
+  const size_t stage_bytes = 4 * 4096 + (p.wres ? 0 : (size_t)p.BN * 128);
+  int stages = (int)((200 * 1024 - (p.wres ? w_bytes : 0)) / stage_bytes);
   if (stages > 8) stages = 8;
   if (stages < 1) stages = 1;
   p.stages = stages;
-  const size_t smem = stages * stage_bytes + (2 * stages + 4) * 8 + 16 + 1024;
+  const size_t smem = (p.wres ? w_bytes : 0) + stages * stage_bytes + (2 * stages + 2 * nacc + 1) * 8 + 16 + 1024;
 
   CUtensorMap tmX, tmW;
   int rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, K, Wdim, p.g.bw, p.g.one_box ? p.g.box_h : p.g.bh, false,

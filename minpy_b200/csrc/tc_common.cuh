@@ -19,19 +19,48 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 }
 // Bounded wait: a pipeline bug must surface as a trap (reported by the next CUDA call),
 // never as a hung GPU.  ~2 s at 2 GHz is far beyond any legitimate wait in these kernels.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// Whole-warp wait: ONE lane polls (with a short sleep between polls), the others park at the
+// warp barrier.  128 epilogue threads polling the same mbarrier flood the SM's barrier unit and
+// slow down the TMA transaction counts and tcgen05.commit arrivals that share it (measured: the
+// conv mainloop cost 0.63 us per k-block whatever was loaded or multiplied, profiles/r1p).
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
+  if ((threadIdx.x & 31) == 0) {
+    uint32_t done;
+    const long long t0 = clock64();
+    do {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(bar), "r"(parity)
+          : "memory");
+      if (!done && clock64() - t0 > 4000000000LL) __trap();
+    } while (!done);
+  }
+  __syncwarp();
+}
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
   uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done != 0;
+}
+// The producer / MMA loops are ONE thread each: every instruction on their path is serial
+// latency (measured: an empty mainloop cost 0.5 us per k-block through runtime divisions and the
+// clock reads of the old wait).  The fast path is a single try_wait; the watchdog clock is only
+// read once a wait has already failed.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try(bar, parity)) return;
   const long long t0 = clock64();
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (!done && clock64() - t0 > 4000000000LL) __trap();
-  } while (!done);
+  while (!mbar_try(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) __trap();
+  }
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
   asm volatile(
