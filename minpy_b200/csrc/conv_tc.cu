@@ -339,12 +339,16 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   const int nb = p.BNc / 32;
   const bool do_bias = (p.ws_bias != nullptr) && (blockIdx.x == 0);
   constexpr uint32_t a_bytes = 4u * blk;                        // room for 128 filters
-  const uint32_t b_bytes = (uint32_t)(p.tpc * nb) * blk;
+  // B region of a stage: the shifted x windows of the CTA's taps side by side, then one
+  // [32 pixels][32] block of 1.0f (written once, never touched by TMA).  Side by side in shared
+  // memory = side by side along N of ONE tcgen05.mma: all taps (and the bias column sums, dy x
+  // ones) accumulate with 4 instructions per 256 columns instead of 4 per tap -- the MMA issuer is
+  // a single thread and its instruction latency, not the tensor pipe, bounded this kernel.
+  const uint32_t b_bytes = (uint32_t)(p.tpc * nb + 1) * blk;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t tx_bytes = (uint32_t)(fblocks + ntap * nb) * blk;
   const int STAGES = p.stages;
-  const uint32_t ones_base = smem_base + STAGES * stage_bytes;  // [32 pixels][32] block of 1.0f
-  const uint32_t bar_base = ones_base + blk;
+  const uint32_t bar_base = smem_base + STAGES * stage_bytes;
   const uint32_t tmem_slot = bar_base + (2 * STAGES + 1) * 8;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
@@ -367,8 +371,11 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tcols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  for (uint32_t i = threadIdx.x; i < blk / 4; i += CONV_THREADS)   // all ones: invariant under the swizzle
-    asm volatile("st.shared.f32 [%0], %1;" ::"r"(ones_base + 4u * i), "f"(1.0f) : "memory");
+  for (int s = 0; s < STAGES; ++s) {
+    const uint32_t ones_base = smem_base + s * stage_bytes + a_bytes + (uint32_t)(ntap * nb) * blk;
+    for (uint32_t i = threadIdx.x; i < blk / 4; i += CONV_THREADS)   // all ones: invariant under the swizzle
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(ones_base + 4u * i), "f"(1.0f) : "memory");
+  }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> visible to the MMA
   tcgen05_fence_before();
   __syncthreads();
@@ -377,52 +384,57 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
   if (warp == 0 && lane == 0) {
+    // single thread: loop-invariant values in registers, chunk coordinates carried incrementally
+    const int TW = p.g.TW, dh0 = p.g.dh0, dw0 = p.g.dw0, cpi = p.g.cpi, cpr = p.g.cpr, bh = p.g.bh;
+    const bool wide = p.g.OWv >= 32;
+    const int th0 = tap0 / TW, tw0 = tap0 - th0 * TW;
+    int n = cbeg / cpi, r = cbeg - n * cpi;          // image, chunk within the image
+    int row = wide ? r / cpr : r, col = wide ? r - row * cpr : 0;
+    int s = 0;
+    uint32_t ph = 0;
     for (int it = 0; it < num_it; ++it) {
-      const int s = it % STAGES;
-      const uint32_t ph = (it / STAGES) & 1;
-      int n, oh0, ow0;
-      chunk_origin(p.g, cbeg + it, n, oh0, ow0);
+      const int oh0 = wide ? row : row * bh, ow0 = col * 32;
       mbar_wait(empty_bar(s), ph ^ 1u);
-      mbar_expect_tx(full_bar(s), tx_bytes);
-      const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
-      for (int j = 0; j < fblocks; ++j) tma_load_4d(sa + j * blk, &tmDy, full_bar(s), f0 + 32 * j, ow0, oh0, n);
+      const uint32_t fb = full_bar(s);
+      mbar_expect_tx(fb, tx_bytes);
+      const uint32_t sa = smem_base + s * stage_bytes;
+      uint32_t sb = sa + a_bytes;
+      for (int j = 0; j < fblocks; ++j) tma_load_4d(sa + j * blk, &tmDy, fb, f0 + 32 * j, ow0, oh0, n);
+      int th = th0, tw = tw0;
       for (int t = 0; t < ntap; ++t) {
-        const int tap = tap0 + t;
-        const int th = tap / p.g.TW, tw = tap - th * p.g.TW;
-        for (int j = 0; j < nb; ++j)
-          tma_load_4d(sb + (t * nb + j) * blk, &tmX, full_bar(s), 32 * j, ow0 + tw + p.g.dw0, oh0 + th + p.g.dh0, n);
+        for (int j = 0; j < nb; ++j, sb += blk) tma_load_4d(sb, &tmX, fb, 32 * j, ow0 + tw + dw0, oh0 + th + dh0, n);
+        if (++tw == TW) { tw = 0; ++th; }
       }
+      if (++s == STAGES) { s = 0; ph ^= 1u; }
+      if (wide) { if (++col == cpr) { col = 0; ++row; } }
+      else ++row;
+      if (++r == cpi) { r = 0; row = 0; col = 0; ++n; }
     }
   } else if (warp == 1 && lane == 0) {
     // both operands MN-major (f / channels contiguous, pixels = K): major bits 15, 16 set.
     // Filter blocks that were not loaded hold stale shared memory: they only reach accumulator
     // rows >= F, which the epilogue never reads (row m of D depends on row m of A alone).
     const uint32_t idesc0 = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(128 >> 4) << 24);
-    const uint32_t idesc = idesc0 | ((uint32_t)(p.BNc >> 3) << 17);
-    const uint32_t idesc_b = idesc0 | ((uint32_t)(32 >> 3) << 17);
+    const int ntot = ntap * p.BNc + (do_bias ? 32 : 0);             // accumulator columns of this CTA
+    const int ngroups = (ntot + 255) / 256;
+    const uint64_t desc0 = make_desc(0, blk, 512, 1);
+    int s = 0;
+    uint32_t ph = 0;
     for (int it = 0; it < num_it; ++it) {
-      const int s = it % STAGES;
-      const uint32_t ph = (it / STAGES) & 1;
       mbar_wait(full_bar(s), ph);
       tcgen05_fence_after();
       const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
-      for (int t = 0; t < ntap; ++t) {
+      const uint64_t adesc = desc0 + (uint64_t)((sa & 0x3FFFFu) >> 4);
+      for (int g = 0; g < ngroups; ++g) {
+        const int width = min(256, ntot - g * 256);
+        const uint32_t idesc = idesc0 | ((uint32_t)(width >> 3) << 17);
+        const uint64_t bdesc = desc0 + (uint64_t)(((sb + (uint32_t)g * 8u * blk) & 0x3FFFFu) >> 4);
 #pragma unroll
-        for (int k = 0; k < 32 / UMMA_K; ++k) {
-          const uint64_t adesc = make_desc(sa + k * 1024, blk, 512, 1);
-          const uint64_t bdesc = make_desc(sb + t * nb * blk + k * 1024, blk, 512, 1);
-          umma_tf32(tmem_base + (uint32_t)(t * p.BNc), adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
-        }
-      }
-      if (do_bias) {
-#pragma unroll
-        for (int k = 0; k < 32 / UMMA_K; ++k) {
-          const uint64_t adesc = make_desc(sa + k * 1024, blk, 512, 1);
-          const uint64_t bdesc = make_desc(ones_base + k * 1024, blk, 512, 1);
-          umma_tf32(tmem_base + bias_col, adesc, bdesc, idesc_b, (it > 0 || k > 0) ? 1u : 0u);
-        }
+        for (int k = 0; k < 32 / UMMA_K; ++k)                        // 8 pixel rows = 1024 bytes per K step
+          umma_tf32(tmem_base + (uint32_t)(g * 256), adesc + 64u * k, bdesc + 64u * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
       }
       umma_commit(empty_bar(s));
+      if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
     umma_commit(tmem_full_bar);
   }
@@ -458,30 +470,44 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   }
 }
 
-// dbias[f] = sum_s ws_bias[s][f]
-__global__ void __launch_bounds__(256) conv_bias_reduce_kernel(const float* __restrict__ wsb, float* __restrict__ dbias, int splits,
-                                                               int F) {
-  const int f = blockIdx.x * 256 + threadIdx.x;
-  if (f >= F) return;
-  float s = 0.f;
-  for (int z = 0; z < splits; ++z) s += wsb[(int64_t)z * F + f];
-  dbias[f] = s;
-}
-
-// dw (F, C, KH, KW) = sum_s ws[s][tap][f][n]; merged: tap = kh, n = kw*Cp + c; else tap = kh*KW+kw, n = c
-__global__ void __launch_bounds__(256) conv_wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int splits,
-                                                                int taps, int F, int Nn, int C, int KH, int KW, int Cp,
-                                                                int merged) {
-  const int64_t total = (int64_t)F * C * KH * KW;
-  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
-    const int kw = (int)(i % KW), kh = (int)((i / KW) % KH);
-    const int c = (int)((i / (KW * KH)) % C), f = (int)(i / ((int64_t)KW * KH * C));
-    const int tap = merged ? kh : kh * KW + kw;
-    const int n = merged ? kw * Cp + c : c;
-    float s = 0.f;
-    for (int z = 0; z < splits; ++z) s += ws[(((int64_t)z * taps + tap) * F + f) * Nn + n];
-    dw[i] = s;
+// dw (F, C, KH, KW) = sum_z ws[z][tap][f][n] (merged: tap = kh, n = kw*Cp + c; else tap = kh*KW+kw, n = c)
+// and, in the trailing blocks of the same launch, dbias[f] = sum_z ws_bias[z][f].
+// A block is 32 consecutive workspace columns x 8 slices of the split range: the reads are
+// coalesced along the workspace row and 8-way parallel along z (the first version summed up to
+// 148 splits serially per thread: 16-26 us for a few thousand outputs); the slices are combined
+// in a fixed order, so the result is deterministic.
+__global__ void __launch_bounds__(256) conv_wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw,
+                                                                const float* __restrict__ wsb, float* __restrict__ dbias,
+                                                                int splits, int taps, int F, int Nn, int C, int KH, int KW,
+                                                                int Cp, int merged, int wblocks) {
+  __shared__ float part[8][33];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const bool bias_block = (int)blockIdx.x >= wblocks;
+  const int64_t total = bias_block ? F : (int64_t)taps * F * Nn;
+  const float* __restrict__ src = bias_block ? wsb : ws;
+  const int64_t j = (int64_t)(bias_block ? blockIdx.x - wblocks : blockIdx.x) * 32 + lane;
+  float acc = 0.f;
+  if (j < total) {
+    int z = slice;
+    for (; z + 24 < splits; z += 32) {     // 4 independent loads in flight
+      const float a0 = src[(int64_t)z * total + j], a1 = src[(int64_t)(z + 8) * total + j];
+      const float a2 = src[(int64_t)(z + 16) * total + j], a3 = src[(int64_t)(z + 24) * total + j];
+      acc += a0; acc += a1; acc += a2; acc += a3;
+    }
+    for (; z < splits; z += 8) acc += src[(int64_t)z * total + j];
   }
+  part[slice][lane] = acc;
+  __syncthreads();
+  if (slice != 0 || j >= total) return;
+  float sum = part[0][lane];
+#pragma unroll
+  for (int q = 1; q < 8; ++q) sum += part[q][lane];
+  if (bias_block) { dbias[j] = sum; return; }
+  const int n = (int)(j % Nn), f = (int)((j / Nn) % F), tap = (int)(j / ((int64_t)Nn * F));
+  int kh, kw, c;
+  if (merged) { kh = tap; kw = n / Cp; c = n - kw * Cp; }
+  else { kh = tap / KW; kw = tap - kh * KW; c = n; }
+  if (c < C && kw < KW) dw[(((int64_t)f * C + c) * KH + kh) * KW + kw] = sum;
 }
 
 // ----------------------------------- layout conversion -------------------------------------
@@ -781,7 +807,7 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
   // taps per CTA: as many accumulators as TMEM (512 columns, 32 kept for the bias) and a >= 2-stage
   // shared-memory ring allow, balanced over the tap groups
   int tpc = (512 - 32) / p.BNc;
-  const int smem_cap = (int)((100 * 1024 - 4 * 4096) / ((p.BNc / 32) * 4096));
+  const int smem_cap = (int)((100 * 1024 - 5 * 4096) / ((p.BNc / 32) * 4096));
   if (tpc > smem_cap) tpc = smem_cap;
   if (tpc > taps) tpc = taps;
   if (tpc < 1) tpc = 1;
@@ -795,12 +821,12 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
   if (splits < 1) splits = 1;
   p.chunks_per_split = (p.g.total_chunks + splits - 1) / splits;
   splits = (p.g.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
-  const size_t stage_bytes = 4 * 4096 + (size_t)tpc * (p.BNc / 32) * 4096;
+  const size_t stage_bytes = 4 * 4096 + ((size_t)tpc * (p.BNc / 32) + 1) * 4096;
   int stages = (int)((200 * 1024) / stage_bytes);
   if (stages > 8) stages = 8;
   if (stages < 1) stages = 1;
   p.stages = stages;
-  const size_t smem = stages * stage_bytes + 4096 + (2 * stages + 1) * 8 + 16 + 1024;
+  const size_t smem = stages * stage_bytes + (2 * stages + 1) * 8 + 16 + 1024;
 
   float* ws = nullptr;
   const size_t ws_elems = (size_t)splits * taps * F * p.Nn;
@@ -820,16 +846,12 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
     else count_launch();
   }
   if (rc == 0) {
-    conv_wgrad_reduce_kernel<<<grid_for((int64_t)F * C * KH * KW, 256), 256, 0, stream()>>>(ws, dw, splits, taps, F, p.Nn, C, KH,
-                                                                                          KW, Cp, merged);
+    const int wblocks = (int)(((int64_t)taps * F * p.Nn + 31) / 32);
+    const int bblocks = dbias ? (F + 31) / 32 : 0;
+    conv_wgrad_reduce_kernel<<<wblocks + bblocks, 256, 0, stream()>>>(ws, dw, p.ws_bias, dbias, splits, taps, F, p.Nn, C, KH, KW,
+                                                                     Cp, merged, wblocks);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("conv_wgrad_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
-    else count_launch();
-  }
-  if (rc == 0 && dbias) {
-    conv_bias_reduce_kernel<<<(F + 255) / 256, 256, 0, stream()>>>(p.ws_bias, dbias, splits, F);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) { set_error("conv_bias_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();
   }
   cudaFreeAsync(ws, stream());
