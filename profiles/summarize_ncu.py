@@ -58,5 +58,30 @@ def full(path):
                 print('    %-66s %16s %s' % (m, row[i], units[i]))
 
 
+def traffic(path, workload, family, calls):
+    """dram bytes (read + write) of every launch in an `ncu --set full` capture that covers `calls`
+    library calls of `family`, averaged per call -> profiles/traffic.json (read by bench.py)."""
+    import json
+    import os
+    out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    total = 0.0
+    for m in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
+        i = hdr.index(m)
+        total += sum(float(r[i].replace(',', '')) * scale[units[i]] for r in data)
+    dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'traffic.json')
+    table = json.load(open(dst)) if os.path.exists(dst) else {}
+    table.setdefault(workload, {})[family] = round(total / float(calls), 1)
+    table.setdefault('_source', {})['%s/%s' % (workload, family)] = '%s: %d kernel launches over %s calls' % (
+        os.path.basename(path), len(data), calls)
+    json.dump(table, open(dst, 'w'), indent=1, sort_keys=True)
+    print('%s %s: %.1f dram bytes per call' % (workload, family, total / float(calls)))
+
+
 if __name__ == '__main__':
-    {'launches': launches, 'full': full}[sys.argv[1]](sys.argv[2])
+    if sys.argv[1] == 'traffic':
+        traffic(sys.argv[2], sys.argv[3], sys.argv[4], sys.argv[5])
+    else:
+        {'launches': launches, 'full': full}[sys.argv[1]](sys.argv[2])
