@@ -135,6 +135,171 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
 }
 
 // =====================================================================================
+//                 skinny contractions: the 10-class output layer and its two VJPs
+// =====================================================================================
+// logits = h . W (N = classes <= 16), dW = h^T . g (N <= 16, long K = batch), dh = g . W^T (K <= 16).
+// TMA cannot describe a 40-byte row pitch and a 64x64 SIMT tile wastes 54 of 64 columns plus a
+// split-K pass (10 + 10 us per call measured); these three are bandwidth-trivial, so each gets the
+// access pattern that makes its one big operand a coalesced stream.  FP32 FMA accumulation.
+constexpr int SK_MAXN = 16;
+
+__device__ __forceinline__ float sk_epilogue(float v, const float* bias, int n, const float* cptr, int relu, int accumulate) {
+  if (bias) v += bias[n];
+  if (accumulate) v += *cptr;
+  if (relu) v = (v != v) ? v : fmaxf(v, 0.f);
+  return v;
+}
+
+// C(M,N) = A(M,K) . B(K,N), N <= 16: a block of 8 warps = (8 / S) rows x S slices of K; lanes stride K
+// inside a slice (A row segments are coalesced streams), 4 independent loads in flight per lane.
+template <int S>
+__global__ void __launch_bounds__(256) skinny_nn_kernel(int M, int N, int K, const float* __restrict__ A, int64_t lda,
+                                                        const float* __restrict__ B, int64_t ldb, float* __restrict__ C,
+                                                        int64_t ldc, const float* __restrict__ bias, int relu, int accumulate) {
+  constexpr int ROWS = 8 / S;
+  __shared__ float red[8][SK_MAXN];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slice = warp % S, rloc = warp / S;
+  const int m = blockIdx.x * ROWS + rloc;
+  float acc[SK_MAXN];
+#pragma unroll
+  for (int n = 0; n < SK_MAXN; ++n) acc[n] = 0.f;
+  if (m < M) {
+    const float* __restrict__ a = A + (int64_t)m * lda;
+    int k = slice * 32 + lane;
+    for (; k + 3 * 32 * S < K; k += 4 * 32 * S) {
+      const float a0 = a[k], a1 = a[k + 32 * S], a2 = a[k + 64 * S], a3 = a[k + 96 * S];
+      const float* __restrict__ b0 = B + (int64_t)k * ldb;
+      const float* __restrict__ b1 = b0 + (int64_t)32 * S * ldb;
+      const float* __restrict__ b2 = b1 + (int64_t)32 * S * ldb;
+      const float* __restrict__ b3 = b2 + (int64_t)32 * S * ldb;
+#pragma unroll
+      for (int n = 0; n < SK_MAXN; ++n)
+        if (n < N) {
+          acc[n] = fmaf(a0, __ldg(b0 + n), acc[n]); acc[n] = fmaf(a1, __ldg(b1 + n), acc[n]);
+          acc[n] = fmaf(a2, __ldg(b2 + n), acc[n]); acc[n] = fmaf(a3, __ldg(b3 + n), acc[n]);
+        }
+    }
+    for (; k < K; k += 32 * S) {
+      const float av = a[k];
+      const float* __restrict__ b = B + (int64_t)k * ldb;
+#pragma unroll
+      for (int n = 0; n < SK_MAXN; ++n) if (n < N) acc[n] = fmaf(av, __ldg(b + n), acc[n]);
+    }
+  }
+#pragma unroll
+  for (int n = 0; n < SK_MAXN; ++n) {
+    if (n < N) {
+      float v = acc[n];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) red[warp][n] = v;
+    }
+  }
+  __syncthreads();
+  if (slice == 0 && lane < N && m < M) {
+    float v = 0.f;
+#pragma unroll
+    for (int q = 0; q < S; ++q) v += red[rloc * S + q][lane];
+    float* cptr = C + (int64_t)m * ldc + lane;
+    *cptr = sk_epilogue(v, bias, lane, cptr, relu, accumulate);
+  }
+}
+
+// C(M,N) = A^T . B with A stored (K,M), B (K,N), N <= 16: a block owns 32 columns m and splits K over
+// its 16 warps (A rows are coalesced along m, B rows are broadcasts); fixed-order combine in smem.
+constexpr int SK_TN_SLICES = 16;
+__global__ void __launch_bounds__(32 * SK_TN_SLICES) skinny_tn_kernel(int M, int N, int K, const float* __restrict__ A,
+                                                                      int64_t lda, const float* __restrict__ B, int64_t ldb,
+                                                                      float* __restrict__ C, int64_t ldc,
+                                                                      const float* __restrict__ bias, int relu, int accumulate) {
+  __shared__ float red[SK_TN_SLICES][SK_MAXN][33];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const int m = blockIdx.x * 32 + lane;
+  float acc[SK_MAXN];
+#pragma unroll
+  for (int n = 0; n < SK_MAXN; ++n) acc[n] = 0.f;
+  if (m < M) {
+    const float* __restrict__ a = A + m;
+    int k = slice;
+    constexpr int ST = SK_TN_SLICES;
+    for (; k + 3 * ST < K; k += 4 * ST) {
+      const float a0 = a[(int64_t)k * lda], a1 = a[(int64_t)(k + ST) * lda];
+      const float a2 = a[(int64_t)(k + 2 * ST) * lda], a3 = a[(int64_t)(k + 3 * ST) * lda];
+      const float* __restrict__ b0 = B + (int64_t)k * ldb;
+      const float* __restrict__ b1 = b0 + (int64_t)ST * ldb;
+      const float* __restrict__ b2 = b1 + (int64_t)ST * ldb;
+      const float* __restrict__ b3 = b2 + (int64_t)ST * ldb;
+#pragma unroll
+      for (int n = 0; n < SK_MAXN; ++n)
+        if (n < N) {
+          acc[n] = fmaf(a0, __ldg(b0 + n), acc[n]); acc[n] = fmaf(a1, __ldg(b1 + n), acc[n]);
+          acc[n] = fmaf(a2, __ldg(b2 + n), acc[n]); acc[n] = fmaf(a3, __ldg(b3 + n), acc[n]);
+        }
+    }
+    for (; k < K; k += ST) {
+      const float av = a[(int64_t)k * lda];
+      const float* __restrict__ b = B + (int64_t)k * ldb;
+#pragma unroll
+      for (int n = 0; n < SK_MAXN; ++n) if (n < N) acc[n] = fmaf(av, __ldg(b + n), acc[n]);
+    }
+  }
+#pragma unroll
+  for (int n = 0; n < SK_MAXN; ++n) red[slice][n][lane] = acc[n];
+  __syncthreads();
+  // thread (slice, lane) finishes output n = slice of column m
+  if (slice < N && m < M) {
+    float v = 0.f;
+#pragma unroll
+    for (int q = 0; q < SK_TN_SLICES; ++q) v += red[q][slice][lane];
+    float* cptr = C + (int64_t)m * ldc + slice;
+    *cptr = sk_epilogue(v, bias, slice, cptr, relu, accumulate);
+  }
+}
+
+// C(M,N) = A(M,K) . B^T with B stored (N,K), K <= 16: one thread per output, the output row is the
+// coalesced stream; A row and B rows are a few cached floats.
+__global__ void __launch_bounds__(256) skinny_nt_kernel(int M, int N, int K, const float* __restrict__ A, int64_t lda,
+                                                        const float* __restrict__ B, int64_t ldb, float* __restrict__ C,
+                                                        int64_t ldc, const float* __restrict__ bias, int relu, int accumulate) {
+  const int64_t total = (int64_t)M * N;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+    const int m = (int)(i / N), n = (int)(i - (int64_t)m * N);
+    const float* __restrict__ a = A + (int64_t)m * lda;
+    const float* __restrict__ b = B + (int64_t)n * ldb;
+    float v = 0.f;
+    for (int k = 0; k < K; ++k) v = fmaf(__ldg(a + k), __ldg(b + k), v);
+    float* cptr = C + (int64_t)m * ldc + n;
+    *cptr = sk_epilogue(v, bias, n, cptr, relu, accumulate);
+  }
+}
+
+// returns true when a skinny kernel took the call
+static bool gemm_skinny(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
+                        int64_t ldb, float* C, int64_t ldc, const float* bias, int relu, int accumulate) {
+  if (N <= SK_MAXN && !ta && !tb && K >= 64) {
+    if (M >= 2048)
+      skinny_nn_kernel<1><<<(unsigned)((M + 7) / 8), 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias,
+                                                                       relu, accumulate);
+    else if (M >= 512 && K < 1024)
+      skinny_nn_kernel<2><<<(unsigned)((M + 3) / 4), 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias,
+                                                                       relu, accumulate);
+    else
+      skinny_nn_kernel<8><<<(unsigned)M, 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
+                                                             accumulate);
+  } else if (N <= SK_MAXN && ta && !tb && K >= 64) {
+    skinny_tn_kernel<<<(unsigned)((M + 31) / 32), 32 * SK_TN_SLICES, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
+                                                                    accumulate);
+  } else if (K <= SK_MAXN && !ta && tb && M * N >= 4096) {
+    skinny_nt_kernel<<<grid_for(M * N, 256), 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
+                                                               accumulate);
+  } else {
+    return false;
+  }
+  return true;
+}
+
+// =====================================================================================
 //                         TF32 tcgen05 / TMEM / TMA GEMM (sm_100a)
 // =====================================================================================
 namespace tc {
@@ -148,6 +313,7 @@ struct GemmParams {
   int64_t ldc;
   const float* bias;
   float* ws;           // split-K workspace [splits][M][N] or nullptr
+  int* counters;       // split-K: arrival count per output tile (self-resetting) or nullptr = separate reduce kernel
   int M, N, K;
   int relu, accumulate;
   int a_mn, b_mn;      // operand tile is MN-major (1) or K-major (0)
@@ -306,6 +472,66 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
   }
+  if (p.ws && p.counters) {
+    // Split-K without a second kernel: the LAST slice CTA of a tile to arrive adds the partials in
+    // slice order 0..S-1 (the same order whichever CTA happens to be last: deterministic) and
+    // applies the epilogue.  The counter resets itself for the next call.
+    __shared__ int s_last;
+    __threadfence();
+    __syncthreads();
+    const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
+    if (threadIdx.x == 0) {
+      const int ticket = atomicAdd(p.counters + tile_id, 1);
+      s_last = (ticket == (int)gridDim.z - 1) ? 1 : 0;
+      if (s_last) p.counters[tile_id] = 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int splits = gridDim.z;
+    const int64_t slice = (int64_t)p.M * p.N;
+    const int rows = min(BM, p.M - m0), cols = min(BN, p.N - n0);
+    const bool vec = ((p.N & 3) == 0) && ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(p.ws) & 15u) == 0);
+    if (vec) {
+      const int c4n = cols >> 2;                      // N % 4 == 0 and n0 % 4 == 0 -> cols % 4 == 0
+      for (int i = threadIdx.x; i < rows * c4n; i += THREADS) {
+        const int r = i / c4n, c = (i - r * c4n) << 2;
+        const float* src = p.ws + (int64_t)(m0 + r) * p.N + n0 + c;
+        float4 o = __ldcg(reinterpret_cast<const float4*>(src));
+        for (int z = 1; z < splits; ++z) {
+          const float4 q = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)z * slice));
+          o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
+        }
+        float* dst = p.C + (int64_t)(m0 + r) * p.ldc + n0 + c;
+        if (p.bias) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c));
+          o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+        }
+        if (p.accumulate) {
+          const float4 q = *reinterpret_cast<const float4*>(dst);
+          o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
+        }
+        if (p.relu) {
+          o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
+          o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
+        }
+        *reinterpret_cast<float4*>(dst) = o;
+      }
+    } else {
+      for (int i = threadIdx.x; i < rows * cols; i += THREADS) {
+        const int r = i / cols, c = i - r * cols;
+        const float* src = p.ws + (int64_t)(m0 + r) * p.N + n0 + c;
+        float o = __ldcg(src);
+        for (int z = 1; z < splits; ++z) o += __ldcg(src + (int64_t)z * slice);
+        float* dst = p.C + (int64_t)(m0 + r) * p.ldc + n0 + c;
+        if (p.bias) o += __ldg(p.bias + n0 + c);
+        if (p.accumulate) o += *dst;
+        if (p.relu) o = (o != o) ? o : fmaxf(o, 0.f);
+        *dst = o;
+      }
+    }
+  }
 }
 
 // ------------------------------- host side --------------------------------------------
@@ -408,6 +634,16 @@ static int gemm_fp32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   return 0;
 }
 
+constexpr int kMaxFixupTiles = 16384;
+static int* splitk_counters() {
+  static int* g_counters = nullptr;
+  if (!g_counters) {
+    if (cudaMalloc((void**)&g_counters, sizeof(int) * kMaxFixupTiles) != cudaSuccess) { g_counters = nullptr; return nullptr; }
+    cudaMemset(g_counters, 0, sizeof(int) * kMaxFixupTiles);
+  }
+  return g_counters;
+}
+
 static bool tma_ok(const float* p, int64_t ld) { return aligned16(p) && (ld % 4 == 0); }
 
 static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
@@ -442,9 +678,18 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   p.a_mn = ta ? 1 : 0;
   p.b_mn = tb ? 0 : 1;
   p.kb_per_split = kb_per;
-  if (splits > 1) MC_CHECK(cudaMallocAsync((void**)&p.ws, sizeof(float) * splits * M * N, stream()));
+  p.counters = nullptr;
+  if (splits > 1) {
+    MC_CHECK(cudaMallocAsync((void**)&p.ws, sizeof(float) * splits * M * N, stream()));
+    // In-kernel fixup (last-arriving slice CTA reduces) is OFF by default: one SM streaming S x 64 KB
+    // of partials is latency-bound (c3_fwd2: 9.9 -> 27 us measured, r1t); the separate reduce kernel
+    // spreads the same bytes over every SM.  MC_GEMM_FIXUP=1 re-enables it for experiments.
+    static int fixup = -1;
+    if (fixup < 0) { const char* e = getenv("MC_GEMM_FIXUP"); fixup = (e && atoi(e) == 1) ? 1 : 0; }
+    if (fixup && tiles <= kMaxFixupTiles) p.counters = splitk_counters();
+  }
   int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
-  if (rc == 0 && splits > 1) {
+  if (rc == 0 && splits > 1 && !p.counters) {
     splitk_reduce_kernel<<<grid_for(M * N / 4 + 1, 256), 256, 0, stream()>>>(p.ws, splits, M, N, C, ldc, bias, relu, accumulate);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("splitk reduce launch failed: %s", cudaGetErrorString(e)); rc = 1; }
@@ -471,6 +716,13 @@ int mc_gemm(int trans_a, int trans_b, int64_t M, int64_t N, int64_t K, const flo
       for (int64_t m = 0; m < M; ++m) if (mc_fill(C + m * ldc, 0.f, N)) return 1;
     }
     if (bias) return mc_binary_vec(MC_ADD, C, bias, 0, 0, C, M, N);
+    return 0;
+  }
+  if (gemm_skinny(trans_a, trans_b, M, N, K, A, lda, B, ldb, C, ldc, bias, relu, accumulate)) {
+    g_last_path = 0;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("skinny gemm launch failed: %s", cudaGetErrorString(e)); return 1; }
+    count_launch();
     return 0;
   }
   const bool tma = tma_ok(A, lda) && tma_ok(B, ldb) && (M >= 32 || N >= 32);
