@@ -642,6 +642,82 @@ def _lstm_step_vjp(ans, x, prev_h, prev_c, Wx, Wh, b):
     return vjp
 
 
+def _view(base, byte_offset, shape):
+    """Zero-copy view of `base`'s buffer starting `byte_offset` bytes in."""
+    return CudaArray(base.buf, base.ptr + byte_offset, tuple(shape), base.dtype)
+
+
+def fused_lstm_temporal(x, h0, Wx, Wh, b):
+    """lstm_temporal of nn/layers.py:383-420 (x (N,T,D), h0 (N,H), zero initial cell) as ONE primitive.
+
+    The reference slices `x[:, t, :]`, runs `lstm_step` and `append`s the new hidden state to a growing
+    (N, t, H) array: O(T^2) copies forward, a scatter-add into a fresh zero tensor per slice
+    backward.  Here the sequence lives TIME-MAJOR on the device, so every
+    per-step operand is a contiguous slice of one big buffer and nothing is sliced or appended:
+      * the input projection of all T steps is one GEMM, x_tm (T*N, D) . Wx + b;
+      * step t is one accumulate-GEMM  a_t += h_{t-1} . Wh  and one gate kernel that writes h_t / c_t
+        straight into slot t+1 of the (T+1, N, H) state buffers and the gates into (T, N, 4H);
+      * the result is one transpose back to (N, T, H).
+    Same arithmetic per element as T calls of `fused_lstm_step` (gate order i, f, o, g)."""
+    lib = ops.L()
+    x, h0 = ops.as_f32(x), ops.as_f32(h0)
+    N, T, D = x.shape
+    H = h0.shape[1]
+    prec = ops._gemm_precision['mode']  # pylint: disable=protected-access
+    x_tm = ops.transpose(x, (1, 0, 2)).reshape((T * N, D))
+    A = ops.gemm(x_tm, Wx, bias=b)                                   # (T*N, 4H), rows of step t contiguous
+    hbuf, cbuf = CudaArray.empty((T + 1, N, H)), CudaArray.empty((T + 1, N, H))
+    gates = CudaArray.empty((T, N, 4 * H))
+    lib.mc_memcpy_d2d(hbuf.ptr, h0.ptr, 4 * N * H)
+    lib.mc_memset(cbuf.ptr, 0, 4 * N * H)
+    sH, sA = 4 * N * H, 4 * N * 4 * H
+    for t in range(T):
+        a_t = A.ptr + t * sA
+        lib.mc_gemm(0, 0, N, 4 * H, H, hbuf.ptr + t * sH, H, Wh.ptr, 4 * H, a_t, 4 * H, None, 0, 1, prec)
+        lib.mc_lstm_cell_fwd(a_t, cbuf.ptr + t * sH, hbuf.ptr + (t + 1) * sH, cbuf.ptr + (t + 1) * sH,
+                             gates.ptr + t * sA, N, H)
+    hs = ops.transpose(_view(hbuf, sH, (T, N, H)), (1, 0, 2))
+    hs._saved = (x_tm, hbuf, cbuf, gates)  # pylint: disable=protected-access
+    return hs
+
+
+def _lstm_temporal_vjp(ans, x, h0, Wx, Wh, b):
+    x_tm, hbuf, cbuf, gates = ans._saved  # pylint: disable=protected-access
+
+    def vjp(g):
+        """BPTT over the time-major buffers: per step one gate-backward kernel and one
+        accumulate-GEMM dH[t] += da_t . Wh^T (dH[t] already holds the upstream gradient of h_{t-1},
+        so no separate add); the weight gradients are three reductions over ALL steps at once."""
+        lib = ops.L()
+        N, T, _ = x.shape
+        H = h0.shape[1]
+        D = x.shape[2]
+        prec = ops._gemm_precision['mode']  # pylint: disable=protected-access
+        g = concrete(g, ans.shape)
+        sH, sA = 4 * N * H, 4 * N * 4 * H
+        dH = CudaArray.empty((T + 1, N, H))
+        lib.mc_memset(dH.ptr, 0, sH)
+        g_tm = ops.transpose(g, (1, 0, 2))
+        lib.mc_memcpy_d2d(dH.ptr + sH, g_tm.ptr, T * sH)
+        del g_tm
+        dA = CudaArray.empty((T * N, 4 * H))
+        dc = [CudaArray.empty((N, H)), CudaArray.empty((N, H))]
+        for t in range(T - 1, -1, -1):
+            dnext_c = dc[(t + 1) & 1].ptr if t < T - 1 else None
+            lib.mc_lstm_cell_bwd(gates.ptr + t * sA, cbuf.ptr + t * sH, cbuf.ptr + (t + 1) * sH, dH.ptr + (t + 1) * sH,
+                                 dnext_c, dA.ptr + t * sA, dc[t & 1].ptr, N, H)
+            lib.mc_gemm(0, 1, N, H, 4 * H, dA.ptr + t * sA, 4 * H, Wh.ptr, 4 * H, dH.ptr + t * sH, H, None, 0, 1, prec)
+        h_prev = _view(hbuf, 0, (T * N, H))
+        dWx = ops.gemm(x_tm, dA, trans_a=True)
+        dWh = ops.gemm(h_prev, dA, trans_a=True)
+        db = ops.reduce(E['MC_RED_SUM'], dA, 0).reshape(b.shape)
+        dh0 = CudaArray.empty((N, H))
+        lib.mc_memcpy_d2d(dh0.ptr, dH.ptr, sH)
+        dx = ops.transpose(ops.gemm(dA, Wx, trans_b=True).reshape((T, N, D)), (1, 0, 2))
+        return [dx, dh0, dWx, dWh, db]
+    return vjp
+
+
 # ---- optimizer updates (nn/optim.py:33-141), one kernel per parameter tensor ------------
 def fused_sgd(w, dw, lr):
     out = CudaArray.empty(w.shape)
@@ -685,7 +761,7 @@ def register_primitives(reg, prim_wrapper):
                append, concatenate, stack, _minpy_getitem, zeros, ones, empty, full, zeros_like, ones_like,
                array, arange, eye, dot, softmax_output, onehot_encode,
                fused_affine, fused_relu, fused_batchnorm, fused_batchnorm_test, fused_dropout,
-               fused_softmax_loss, fused_lstm_step, fused_sgd, fused_sgd_momentum, fused_rmsprop, fused_adam):
+               fused_softmax_loss, fused_lstm_step, fused_lstm_temporal, fused_sgd, fused_sgd_momentum, fused_rmsprop, fused_adam):
         reg.register(fn.__name__, prim_wrapper(fn))
 
 
@@ -738,3 +814,4 @@ def def_grads(prims):
     prims('fused_dropout').def_grad(_dropout_vjp)
     prims('fused_softmax_loss').def_grad(_softmax_loss_vjp)
     prims('fused_lstm_step').def_multiple_grad(_lstm_step_vjp, (0, 1, 2, 3, 4, 5))
+    prims('fused_lstm_temporal').def_multiple_grad(_lstm_temporal_vjp, (0, 1, 2, 3, 4))
