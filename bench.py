@@ -342,7 +342,8 @@ def run_b200(args):
     Yp = pinned_array(lib, Y.shape, Y.dtype)
     Xp[...] = X
     Yp[...] = Y
-    host_iter = NDArrayIter(Xp, Yp, batch_size=batch, shuffle=False, num_parts=1, part_index=0)
+    host_iter = NDArrayIter(Xp, Yp, batch_size=batch, shuffle=False, num_parts=1, part_index=0,
+                            device_prefetch=bool(args.prefetch))
     model, solver = build_solver(args.workload, host_iter, step_graph=bool(args.graph))
 
     # device-resident batches for the kernel-only leg
@@ -702,6 +703,7 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--pool', type=int, default=16, help='distinct batches cycled per rank')
     ap.add_argument('--graph', type=int, default=1, help='replay the step as a CUDA graph (0 = eager launches)')
+    ap.add_argument('--prefetch', type=int, default=1, help='e2e leg: NDArrayIter copies batch i+1 on a second stream')
     ap.add_argument('--no-ufunc', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()

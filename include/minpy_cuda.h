@@ -56,6 +56,13 @@ int mc_memcpy_d2h(void* dst_host, const void* src_dev, size_t nbytes);
 int mc_memcpy_d2h_async(void* dst_host, const void* src_dev, size_t nbytes);
 int mc_memcpy_d2d(void* dst_dev, const void* src_dev, size_t nbytes);
 int mc_memset(void* dst_dev, int byte, size_t nbytes);
+/* Input prefetch beside the compute stream (minpy/nn/io.py:238-258 sliced on the host and copied
+ * every step; here batch i+1 is copied on a second stream while step i runs).
+ * acquire: the compute stream waits for all prefetch copies enqueued so far;
+ * release: later prefetch copies wait for the compute work enqueued so far. */
+int mc_prefetch_h2d(void* dst_dev, const void* src_host, size_t nbytes);
+int mc_prefetch_acquire(void);
+int mc_prefetch_release(void);
 /* CUDA events on the current stream (bench timing). */
 int mc_event_create(void** ev);
 int mc_event_record(void* ev);

@@ -97,6 +97,49 @@ def _default_partition():
         return 1, 0
 
 
+class _DevicePrefetch(object):
+    """Two device staging slots filled by host->device copies on the library's copy stream
+    (mc_prefetch_h2d): while the step on batch i runs on the compute stream, batch i+1 is already
+    travelling.  The reference slices on the host and copies inside the step (io.py:238-258 +
+    array.py:388-389), which serialises PCIe and compute.  A batch handed out stays valid until two
+    more batches have been drawn (its slot is then overwritten)."""
+
+    def __init__(self):
+        self.slots = [None, None]      # per slot: list of CudaArray
+        self.turn = 0
+        self.cursor = None             # cursor of the batch in flight
+        self.pending = None
+        self.keep = [None, None]       # host arrays of in-flight copies
+
+    def forget(self):
+        self.cursor, self.pending = None, None
+
+    def start(self, cursor, host_arrays, pad):
+        from minpy_b200.cuda_array import CudaArray
+        from minpy_b200.ops import L
+        from minpy_b200.step_graph import _dtype_on_device
+        lib = L()
+        slot = self.turn
+        self.turn ^= 1
+        hosts = [np.ascontiguousarray(h, dtype=_dtype_on_device(np.asarray(h))) for h in host_arrays]
+        dev = self.slots[slot]
+        if dev is None or [d.shape for d in dev] != [tuple(h.shape) for h in hosts] or \
+                [d.dtype for d in dev] != [h.dtype for h in hosts]:
+            dev = self.slots[slot] = [CudaArray.empty(h.shape, h.dtype) for h in hosts]
+        lib.mc_prefetch_release()          # the slot's previous consumer was enqueued before this point
+        for d, h in zip(dev, hosts):
+            lib.mc_prefetch_h2d(d.ptr, h.ctypes.data, h.nbytes)
+        self.keep[slot] = hosts            # pinned sources are read asynchronously: keep them alive
+        self.cursor, self.pending = cursor, (slot, pad)
+
+    def take(self):
+        from minpy_b200.ops import L
+        slot, pad = self.pending
+        L().mc_prefetch_acquire()          # the compute stream waits for the copies
+        self.pending = None
+        return [array.wrap(d) for d in self.slots[slot]], pad
+
+
 class NDArrayIter(DataIter):
     # pylint: disable=too-many-instance-attributes
     """Batches over in-memory arrays.
@@ -107,9 +150,12 @@ class NDArrayIter(DataIter):
     """
 
     def __init__(self, data, label=None, batch_size=1, shuffle=False, last_batch_handle='pad',
-                 num_parts=None, part_index=None):
+                 num_parts=None, part_index=None, device_prefetch=False):
         # pylint: disable=too-many-arguments
         super(NDArrayIter, self).__init__()
+        # not in the reference: copy batch i+1 to the device on a second stream while step i computes
+        # (see _DevicePrefetch); the batches handed out are then device arrays
+        self._prefetch = _DevicePrefetch() if device_prefetch else None
         self.data = _init_data(data, allow_empty=False, default_name='data')
         self.label = _init_data(label, allow_empty=True, default_name='softmax_label')
 
@@ -163,9 +209,40 @@ class NDArrayIter(DataIter):
         return self.cursor < self.num_data
 
     def next(self):
+        if self._prefetch is not None:
+            return self._next_prefetched()
         if self.iter_next():
             return DataBatch(data=self.getdata(), label=self.getlabel(), pad=self.getpad(), index=None)
         raise StopIteration
+
+    def _host_batch(self, cursor):
+        """Host arrays (data + label tensors) of the batch starting at `cursor`, and its pad: VIEWS of
+        the sources (a pinned source is then copied to the device without touching the host again)."""
+        lo, hi = cursor, cursor + self.batch_size
+        out = []
+        for _, v in self.data + self.label:
+            if isinstance(v, array.Array):
+                v = v.get_data(array.ArrayType.NUMPY)
+            if hi <= self.num_data:
+                out.append(v[lo:hi])
+            else:
+                out.append(np.concatenate((v[lo:], v[:hi - self.num_data]), axis=0))
+        pad = hi - self.num_data if (self.last_batch_handle == 'pad' and hi > self.num_data) else 0
+        return out, pad
+
+    def _next_prefetched(self):
+        if not self.iter_next():
+            self._prefetch.forget()
+            raise StopIteration
+        pf = self._prefetch
+        if pf.cursor != self.cursor:                       # first batch of an epoch (or after a reset)
+            pf.start(self.cursor, *self._host_batch(self.cursor))
+        arrays, pad = pf.take()
+        nxt = self.cursor + self.batch_size
+        if nxt < self.num_data:
+            pf.start(nxt, *self._host_batch(nxt))
+        nd = len(self.data)
+        return DataBatch(data=arrays[:nd], label=arrays[nd:], pad=pad, index=None)
 
     def _getdata(self, source):
         assert self.cursor < self.num_data, 'DataIter needs reset.'

@@ -13,6 +13,8 @@ static int g_sm_count = 148;
 static std::atomic<uint64_t> g_launches{0};
 static unsigned long long* g_epoch = nullptr;     // counter of the graph being captured
 static bool g_capturing = false;
+static cudaStream_t g_copy_stream = nullptr;     // input prefetch (host -> device) beside the compute stream
+static cudaEvent_t g_copy_done = nullptr, g_main_done = nullptr;
 
 __global__ void graph_epoch_inc_kernel(unsigned long long* e) { *e += 1ull; }
 
@@ -135,6 +137,36 @@ int mc_memcpy_d2d(void* dst, const void* src, size_t n) {
 }
 int mc_memset(void* dst, int byte, size_t n) {
   if (n) MC_CHECK(cudaMemsetAsync(dst, byte, n, g_stream));
+  return 0;
+}
+
+/* Input pipeline (minpy/nn/io.py NDArrayIter prefetch): host->device copies on a second,
+ * non-blocking stream so that batch i+1 travels while step i computes. */
+static int ensure_copy_stream() {
+  if (g_copy_stream) return 0;
+  MC_CHECK(cudaStreamCreateWithFlags(&g_copy_stream, cudaStreamNonBlocking));
+  MC_CHECK(cudaEventCreateWithFlags(&g_copy_done, cudaEventDisableTiming));
+  MC_CHECK(cudaEventCreateWithFlags(&g_main_done, cudaEventDisableTiming));
+  return 0;
+}
+int mc_prefetch_h2d(void* dst, const void* src, size_t n) {
+  if (ensure_copy_stream()) return 1;
+  if (n) MC_CHECK(cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, g_copy_stream));
+  return 0;
+}
+/* The compute stream waits for every prefetch copy enqueued so far. */
+int mc_prefetch_acquire(void) {
+  if (ensure_copy_stream()) return 1;
+  MC_CHECK(cudaEventRecord(g_copy_done, g_copy_stream));
+  MC_CHECK(cudaStreamWaitEvent(g_stream, g_copy_done, 0));
+  return 0;
+}
+/* Later prefetch copies wait for everything enqueued on the compute stream so far (the
+ * consumer of the staging buffer they are about to overwrite). */
+int mc_prefetch_release(void) {
+  if (ensure_copy_stream()) return 1;
+  MC_CHECK(cudaEventRecord(g_main_done, g_stream));
+  MC_CHECK(cudaStreamWaitEvent(g_copy_stream, g_main_done, 0));
   return 0;
 }
 
