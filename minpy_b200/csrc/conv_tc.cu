@@ -68,6 +68,7 @@ struct ConvFwdParams {
   int BN, ncb, stages, relu;
   int nacc;              // accumulator tiles in the TMEM ring (nacc * BN <= 512 columns)
   int wres;              // all weight blocks stay resident in shared memory (one n-tile, <= 96 KB)
+  long long* dbg;        // MC_CONV_DBG: clock64 stamps of CTA 0 [role][tile][slot] (nullptr = off)
 };
 
 // Persistent: grid = min(#tiles, #SMs); a CTA walks tiles t = blockIdx.x, += gridDim.x, where a
@@ -75,7 +76,7 @@ struct ConvFwdParams {
 // 32w..32w+31), 4 TMA producer, 5 MMA issuer.  The shared-memory ring runs continuously across
 // tiles and the accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of tile
 // i overlaps the loads and MMAs of tile i+1 and the per-CTA set-up cost is paid once per SM.
-constexpr int IGEMM_THREADS = 192;
+constexpr int IGEMM_THREADS = 320;   // warps 0-7: two epilogue groups (alternate tiles), 8: TMA producer, 9: MMA issuer
 
 __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __grid_constant__ CUtensorMap tmX,
                                                                        const __grid_constant__ CUtensorMap tmW,
@@ -106,14 +107,14 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
   const int total_tiles = ptiles * ntiles;
   const uint32_t tcols = (uint32_t)(p.nacc * p.BN);               // BN, nacc powers of two; nacc * BN in [64, 512]
 
-  if (warp == 4 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < NACC; ++a) { mbar_init(tmem_full_bar(a), 1); mbar_init(tmem_empty_bar(a), 4); }
     mbar_init(w_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  if (warp == 5) {
+  if (warp == 9) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tcols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -123,7 +124,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0) {
       // ------------------------------ TMA producer ------------------------------------
       // One thread: every instruction here is serial latency (an EMPTY mainloop still cost 0.2 us
@@ -156,11 +157,14 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
 #pragma unroll
           for (int j = 0; j < 4; ++j) chunk_origin(p.g, chunk0 + j, cn[j], coh[j], cow[j]);
         }
+        const int dti = (tile - (int)blockIdx.x) / (int)gridDim.x;
+        if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(0 * 32 + dti) * 4 + 0] = clock64();
         int tap = 0;
         for (int th = 0; th < TH; ++th) {
           for (int tw = 0; tw < TW; ++tw, ++tap) {
             for (int cb = 0; cb < ncb; ++cb) {
               mbar_wait(empty_bar(s), ph ^ 1u);
+              if (p.dbg && blockIdx.x == 0 && dti < 32 && tap == 0 && cb == 0) p.dbg[(0 * 32 + dti) * 4 + 1] = clock64();
               const uint32_t fb = full_bar(s);
               mbar_expect_tx(fb, stage_bytes);
               const uint32_t sa = ring_base + s * stage_bytes;
@@ -176,9 +180,10 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
             }
           }
         }
+        if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(0 * 32 + dti) * 4 + 2] = clock64();
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     if (lane == 0) {
       // ------------------------------ MMA issuer --------------------------------------
       // c_format F32, a/b TF32, both operands K-major, N>>3 at [17,23), M>>4 at [24,29)
@@ -191,13 +196,17 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
       const uint64_t desc0 = make_desc(0, 16, 1024, 2);
       if (wres && (int)blockIdx.x < total_tiles) mbar_wait(w_bar, 0);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int dti = (tile - (int)blockIdx.x) / (int)gridDim.x;
+        if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(1 * 32 + dti) * 4 + 0] = clock64();
         mbar_wait(tmem_empty_bar(acc), aph ^ 1u);                          // epilogue drained this accumulator
         tcgen05_fence_after();
+        if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(1 * 32 + dti) * 4 + 1] = clock64();
         const uint32_t tacc = tmem_base + (uint32_t)(acc * BN);
         uint32_t wb = smem_base;                                           // resident weight block of iteration i
         for (int i = 0; i < num_it; ++i, wb += b_bytes) {
           mbar_wait(full_bar(s), ph);
           tcgen05_fence_after();
+          if (p.dbg && blockIdx.x == 0 && dti < 32 && i == 0) p.dbg[(1 * 32 + dti) * 4 + 2] = clock64();
           const uint32_t sa = ring_base + s * stage_bytes;
           const uint32_t sb = wres ? wb : sa + a_bytes;
           const uint64_t adesc = desc0 + (uint64_t)((sa & 0x3FFFFu) >> 4);
@@ -209,31 +218,41 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
           if (++s == STAGES) { s = 0; ph ^= 1u; }
         }
         umma_commit(tmem_full_bar(acc));
+        if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(1 * 32 + dti) * 4 + 3] = clock64();
         if (++acc == NACC) { acc = 0; aph ^= 1u; }
       }
     }
   } else {
-    // ---------------------------------- epilogue (warps 0-3) ----------------------------
+    // ------------------------- epilogue (warps 0-3: even tiles, 4-7: odd tiles) -----------------
+    // One tile's epilogue (barrier wait, tcgen05.ld, 8 scattered 16-byte stores per 32 columns,
+    // release) is ~1 us of serial latency per warp; with a few k-blocks per tile that, not the
+    // loads or the MMAs, set the tile rate.  Two groups of four warps drain alternate accumulators.
     const bool vec_ok = ((p.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15u) == 0);
-    int acc = 0;
+    const int grp = warp >> 2, quarter = warp & 3;
+    int acc = grp % NACC;
     uint32_t aph = 0;
-    int pt = blockIdx.x % ptiles, nt = blockIdx.x / ptiles;
-    const int dpt = gridDim.x % ptiles, dnt = gridDim.x / ptiles;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    const int first = blockIdx.x + grp * gridDim.x, stride = 2 * gridDim.x;
+    int pt = first % ptiles, nt = first / ptiles;
+    const int dpt = stride % ptiles, dnt = stride / ptiles;
+    for (int tile = first; tile < total_tiles; tile += stride) {
       const int chunk0 = pt * 4;
       const int n0 = nt * p.BN;
       pt += dpt; nt += dnt;
       if (pt >= ptiles) { pt -= ptiles; ++nt; }
       int n, oh0, ow0;
-      chunk_origin(p.g, chunk0 + warp, n, oh0, ow0);
+      chunk_origin(p.g, chunk0 + quarter, n, oh0, ow0);
       int oh, ow;
       if (p.g.OWv >= 32) { oh = oh0; ow = ow0 + lane; }
       else { oh = oh0 + (lane >> p.g.owv_shift); ow = lane & (p.g.OWv - 1); }
       const bool live = (n < p.g.N) && (oh < p.g.OH) && (ow < p.g.OW);
       float* __restrict__ yrow = p.y + (((int64_t)n * p.g.OH + oh) * p.g.OW + ow) * p.ldy;
+      const int dti = (tile - (int)blockIdx.x) / (int)gridDim.x;
+      const bool dbgw = p.dbg && blockIdx.x == 0 && dti < 32 && quarter == 0 && lane == 0;
+      if (dbgw) p.dbg[(2 * 32 + dti) * 4 + 0] = clock64();
       mbar_wait_warp(tmem_full_bar(acc), aph);
       tcgen05_fence_after();
-      const uint32_t tacc = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * p.BN);
+      if (dbgw) p.dbg[(2 * 32 + dti) * 4 + 1] = clock64();
+      const uint32_t tacc = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * p.BN);
 #pragma unroll 1
       for (int c0 = 0; c0 < p.BN; c0 += 32) {
         float v[32];
@@ -273,13 +292,15 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
       }
       tcgen05_fence_before();
       __syncwarp();
+      if (dbgw) p.dbg[(2 * 32 + dti) * 4 + 2] = clock64();
       if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tmem_empty_bar(acc)) : "memory");
-      if (++acc == NACC) { acc = 0; aph ^= 1u; }
+      acc += 2;                                        // NACC is an even power of two
+      if (acc >= NACC) { acc -= NACC; aph ^= 1u; }
     }
   }
   tcgen05_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == 9) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tcols) : "memory");
   }
 }
@@ -782,7 +803,27 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   if (rc == 0) {
     const int64_t tiles = (int64_t)((p.g.total_chunks + 3) / 4) * ((Nout + p.BN - 1) / p.BN);
     const unsigned grid = (unsigned)(tiles < sm_count() ? tiles : sm_count());
+    p.dbg = nullptr;
+    static long long* dbg_buf = nullptr;
+    const bool dbg = getenv("MC_CONV_DBG") != nullptr;
+    if (dbg) {
+      if (!dbg_buf) cudaMalloc((void**)&dbg_buf, sizeof(long long) * 3 * 32 * 4);
+      cudaMemset(dbg_buf, 0, sizeof(long long) * 3 * 32 * 4);
+      p.dbg = dbg_buf;
+    }
     conv_igemm_kernel<<<grid, IGEMM_THREADS, smem, stream()>>>(tmX, tmW, p);
+    if (dbg) {
+      static long long host[3 * 32 * 4];
+      cudaDeviceSynchronize();
+      cudaMemcpy(host, dbg_buf, sizeof(host), cudaMemcpyDeviceToHost);
+      const long long t0 = host[0];
+      fprintf(stderr, "conv dbg: tiles/CTA~%d num_it=%d stages=%d nacc=%d wres=%d\n", (int)(tiles / grid), taps * p.ncb, p.stages, p.nacc, p.wres);
+      for (int t = 0; t < 12; ++t)
+        fprintf(stderr, "  tile %2d  prod start %6lld first-wait-done %6lld issued %6lld | mma start %6lld acc-free %6lld first-full %6lld committed %6lld | epi start %6lld full %6lld done %6lld\n", t,
+                host[(0 * 32 + t) * 4 + 0] - t0, host[(0 * 32 + t) * 4 + 1] - t0, host[(0 * 32 + t) * 4 + 2] - t0,
+                host[(1 * 32 + t) * 4 + 0] - t0, host[(1 * 32 + t) * 4 + 1] - t0, host[(1 * 32 + t) * 4 + 2] - t0, host[(1 * 32 + t) * 4 + 3] - t0,
+                host[(2 * 32 + t) * 4 + 0] - t0, host[(2 * 32 + t) * 4 + 1] - t0, host[(2 * 32 + t) * 4 + 2] - t0);
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("conv_igemm_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();

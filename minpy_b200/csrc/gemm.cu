@@ -367,25 +367,28 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
 
   if (warp == 0 && lane == 0) {
     // ------------------------------ TMA producer ------------------------------------
-    for (int i = 0; i < num_kb; ++i) {
-      const int s = i % STAGES;
-      const uint32_t ph = (i / STAGES) & 1;
+    // (one thread: stage / phase / coordinates are carried, not recomputed -- see conv_tc.cu)
+    const bool a_mn = p.a_mn != 0, b_mn = p.b_mn != 0;
+    int s = 0, k0 = kb_begin * BK;
+    uint32_t ph = 0;
+    for (int i = 0; i < num_kb; ++i, k0 += BK) {
       mbar_wait(empty_bar(s), ph ^ 1u);
-      mbar_expect_tx(full_bar(s), STAGE_BYTES);
+      const uint32_t fb = full_bar(s);
+      mbar_expect_tx(fb, STAGE_BYTES);
       const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
-      const int k0 = (kb_begin + i) * BK;
-      if (!p.a_mn) {
-        tma_load_2d(sa, &tmA, full_bar(s), k0, m0);
+      if (!a_mn) {
+        tma_load_2d(sa, &tmA, fb, k0, m0);
       } else {
 #pragma unroll
-        for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, full_bar(s), m0 + 32 * j, k0);
+        for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, fb, m0 + 32 * j, k0);
       }
-      if (!p.b_mn) {
-        tma_load_2d(sb, &tmB, full_bar(s), k0, n0);
+      if (!b_mn) {
+        tma_load_2d(sb, &tmB, fb, k0, n0);
       } else {
 #pragma unroll
-        for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, full_bar(s), n0 + 32 * j, k0);
+        for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, fb, n0 + 32 * j, k0);
       }
+      if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
   } else if (warp == 1 && lane == 0) {
     // ------------------------------ MMA issuer --------------------------------------
@@ -393,19 +396,24 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
     // (2<<7, 2<<10), a_major bit 15, b_major bit 16, N>>3 at [17,23), M>>4 at [24,29).
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
                            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    // shared-memory descriptor = layout bits | (address >> 4): one K step (8 tf32) is +32 B inside a
+    // K-major swizzled row (+2) or +1024 B = 8 k-rows of an MN-major block (+64)
+    const uint64_t adesc0 = p.a_mn ? make_desc(0, 4096, 512, 1) : make_desc(0, 16, 1024, 2);
+    const uint64_t bdesc0 = p.b_mn ? make_desc(0, 4096, 512, 1) : make_desc(0, 16, 1024, 2);
+    const uint32_t astep = p.a_mn ? 64u : 2u, bstep = p.b_mn ? 64u : 2u;
+    int s = 0;
+    uint32_t ph = 0;
     for (int i = 0; i < num_kb; ++i) {
-      const int s = i % STAGES;
-      const uint32_t ph = (i / STAGES) & 1;
       mbar_wait(full_bar(s), ph);
       tcgen05_fence_after();
       const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
+      const uint64_t adesc = adesc0 + (uint64_t)((sa & 0x3FFFFu) >> 4);
+      const uint64_t bdesc = bdesc0 + (uint64_t)((sb & 0x3FFFFu) >> 4);
 #pragma unroll
-      for (int k = 0; k < BK / UMMA_K; ++k) {
-        const uint64_t adesc = p.a_mn ? make_desc(sa + k * 1024, 4096, 512, 1) : make_desc(sa + k * 32, 16, 1024, 2);
-        const uint64_t bdesc = p.b_mn ? make_desc(sb + k * 1024, 4096, 512, 1) : make_desc(sb + k * 32, 16, 1024, 2);
-        umma_tf32(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
-      }
+      for (int k = 0; k < BK / UMMA_K; ++k)
+        umma_tf32(tmem_base, adesc + (uint64_t)(astep * k), bdesc + (uint64_t)(bstep * k), idesc, (i > 0 || k > 0) ? 1u : 0u);
       umma_commit(empty_bar(s));  // frees the smem stage once these MMAs have read it
+      if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
     umma_commit(tmem_full_bar);   // accumulator complete
   }
@@ -649,7 +657,10 @@ static bool tma_ok(const float* p, int64_t ld) { return aligned16(p) && (ld % 4 
 static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
                      int64_t ldb, float* C, int64_t ldc, const float* bias, int relu, int accumulate) {
   using namespace tc;
-  const int BN = (N > 64) ? 128 : 64;
+  static int force_bn = -1, min_kb = -1;
+  if (force_bn < 0) { const char* e = getenv("MC_GEMM_BN"); force_bn = e ? atoi(e) : 0; }
+  if (min_kb < 0) { const char* e = getenv("MC_GEMM_MIN_KB"); min_kb = e ? atoi(e) : 8; }
+  const int BN = force_bn ? force_bn : ((N > 64) ? 128 : 64);
   CUtensorMap tmA, tmB;
   // A operand: op(A) is (M, K).  Stored (M,K) row-major -> K-major tile {BK x BM};
   // stored (K,M) (trans_a) -> MN-major: boxes of {32 (M) x BK (K)}.
@@ -664,7 +675,7 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   int splits = 1;
   if (tiles < sm_count() && num_kb >= 16) {
     splits = (int)(sm_count() / tiles);
-    const int maxs = num_kb / 8;  // at least 8 k-blocks (K = 256) per slice
+    const int maxs = num_kb / min_kb;  // at least 8 k-blocks (K = 256) per slice
     if (splits > maxs) splits = maxs;
     if (splits < 1) splits = 1;
   }

@@ -192,12 +192,13 @@ class StepGraph(object):
         try:
             lib.mc_graph_begin()
             names, grads, loss = solver._step_grads(sbatch)   # pylint: disable=protected-access
-            if parallel.world_size() > 1:
+            import os
+            if parallel.world_size() > 1 or os.environ.get('MINPY_DP_DEBUG_FORCE_PACK') == '1':
                 flat, grads = parallel.pack_gradients(grads)
                 if flat is None:
                     raise StepGraphUnsupported('gradients are not on the device')
                 self.flat = flat
-                if parallel.native_comm():
+                if parallel.native_comm() or parallel.world_size() <= 1:
                     parallel.reduce_flat(flat)            # NCCL on the library stream: captured
                 else:
                     ex = ctypes.c_void_p()

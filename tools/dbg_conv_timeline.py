@@ -1,0 +1,18 @@
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+from minpy_b200._lib import get_lib
+from minpy_b200.cuda_array import CudaArray
+lib = get_lib()
+N=512
+rng=np.random.RandomState(0)
+for name, C, H, F in [('conv1', 3, 32, 32), ('conv2', 32, 16, 64)]:
+    Cp=(C+3)//4*4; wpad = 1 if 3*Cp<=32 else 0
+    x = CudaArray.from_numpy(rng.randn(N, H, H + 2 * wpad, Cp).astype(np.float32))
+    w = CudaArray.from_numpy(rng.randn(F, C, 3, 3).astype(np.float32))
+    b = CudaArray.from_numpy(np.zeros(F, np.float32))
+    y = CudaArray.empty((N, H, H, F))
+    for i in range(2):
+        sys.stderr.write('== %s run %d\n' % (name, i))
+        lib.mc_conv2d_nhwc_fwd(x.ptr, w.ptr, b.ptr, y.ptr, N, C, H, H, Cp, wpad, F, F, 3, 3, 1, 1)
+        lib.mc_sync()
