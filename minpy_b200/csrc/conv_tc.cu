@@ -69,6 +69,8 @@ struct ConvFwdParams {
   int nacc;              // accumulator tiles in the TMEM ring (nacc * BN <= 512 columns)
   int wres;              // all weight blocks stay resident in shared memory (one n-tile, <= 96 KB)
   long long* dbg;        // MC_CONV_DBG: clock64 stamps of CTA 0 [role][tile][slot] (nullptr = off)
+  int halo;              // stage = one channel block of a whole tile WITH its filter halo (see below)
+  uint32_t copy_bytes;   // halo mode: bytes of one column-shifted copy, (box_h + TH - 1) * bw * 128
 };
 
 // Persistent: grid = min(#tiles, #SMs); a CTA walks tiles t = blockIdx.x, += gridDim.x, where a
@@ -87,7 +89,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
   constexpr uint32_t a_bytes = 4u * chunk_bytes;
   const uint32_t b_bytes = (uint32_t)p.BN * 128u;                 // [BN][32 ch]
   const uint32_t w_bytes = p.wres ? (uint32_t)(p.g.TH * p.g.TW * p.ncb) * b_bytes : 0u;   // resident weights first
-  const uint32_t stage_bytes = a_bytes + (p.wres ? 0u : b_bytes);
+  const uint32_t stage_bytes = p.halo ? (uint32_t)p.g.TW * p.copy_bytes : a_bytes + (p.wres ? 0u : b_bytes);
   const int STAGES = p.stages;
   const int NACC = p.nacc;
   const uint32_t ring_base = smem_base + w_bytes;
@@ -101,7 +103,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int taps = p.g.TH * p.g.TW;
-  const int num_it = taps * p.ncb;
+  const int num_it = p.halo ? p.ncb : taps * p.ncb;       // pipeline stages per tile
   const int ptiles = (p.g.total_chunks + 3) / 4;
   const int ntiles = (p.Nout + p.BN - 1) / p.BN;
   const int total_tiles = ptiles * ntiles;
@@ -159,6 +161,26 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
         }
         const int dti = (tile - (int)blockIdx.x) / (int)gridDim.x;
         if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(0 * 32 + dti) * 4 + 0] = clock64();
+        if (p.halo) {
+          // Halo mode.  The TMA unit, not the tensor pipe, bounds this kernel (~5 cycles per 128-byte
+          // pixel row, MC_CONV_DBG timeline), and loading one box per filter tap fetches every input
+          // row TH*TW times.  Here a stage holds, per column shift tw, ONE box of the tile's rows plus
+          // the TH-1 halo rows; the row shifts th are then just +th*bw*128 bytes on the shared-memory
+          // descriptor (a multiple of the 1024-byte swizzle atom since bw >= 8): TW boxes of
+          // (box_h + TH - 1) * bw rows instead of TH*TW boxes of box_h * bw rows.
+          for (int cb = 0; cb < ncb; ++cb) {
+            mbar_wait(empty_bar(s), ph ^ 1u);
+            if (p.dbg && blockIdx.x == 0 && dti < 32 && cb == 0) p.dbg[(0 * 32 + dti) * 4 + 1] = clock64();
+            const uint32_t fb = full_bar(s);
+            mbar_expect_tx(fb, stage_bytes);
+            uint32_t sa = ring_base + s * stage_bytes;
+            for (int tw = 0; tw < TW; ++tw, sa += p.copy_bytes)
+              tma_load_4d(sa, &tmX, fb, cb * BKC, cow[0] + tw + dw0, coh[0] + dh0, cn[0]);
+            if (++s == STAGES) { s = 0; ph ^= 1u; }
+          }
+          if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(0 * 32 + dti) * 4 + 2] = clock64();
+          continue;
+        }
         int tap = 0;
         for (int th = 0; th < TH; ++th) {
           for (int tw = 0; tw < TW; ++tw, ++tap) {
@@ -202,6 +224,33 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
         tcgen05_fence_after();
         if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(1 * 32 + dti) * 4 + 1] = clock64();
         const uint32_t tacc = tmem_base + (uint32_t)(acc * BN);
+        if (p.halo) {
+          const int TH = p.g.TH, TW = p.g.TW, ncb = p.ncb;
+          const uint32_t row_bytes = (uint32_t)p.g.bw * 128u;
+          for (int cb = 0; cb < ncb; ++cb) {
+            mbar_wait(full_bar(s), ph);
+            tcgen05_fence_after();
+            if (p.dbg && blockIdx.x == 0 && dti < 32 && cb == 0) p.dbg[(1 * 32 + dti) * 4 + 2] = clock64();
+            const uint32_t sa = ring_base + s * stage_bytes;
+            uint32_t wb = smem_base + (uint32_t)cb * b_bytes;              // weight block (tap 0, cb); taps are ncb blocks apart
+            for (int th = 0; th < TH; ++th) {
+              uint32_t at = sa + (uint32_t)th * row_bytes;
+              for (int tw = 0; tw < TW; ++tw, at += p.copy_bytes, wb += (uint32_t)ncb * b_bytes) {
+                const uint64_t adesc = desc0 + (uint64_t)((at & 0x3FFFFu) >> 4);
+                const uint64_t bdesc = desc0 + (uint64_t)((wb & 0x3FFFFu) >> 4);
+#pragma unroll
+                for (int k = 0; k < BKC / UMMA_K; ++k)
+                  umma_tf32(tacc, adesc + 2u * k, bdesc + 2u * k, idesc, (cb > 0 || th > 0 || tw > 0 || k > 0) ? 1u : 0u);
+              }
+            }
+            umma_commit(empty_bar(s));
+            if (++s == STAGES) { s = 0; ph ^= 1u; }
+          }
+          umma_commit(tmem_full_bar(acc));
+          if (p.dbg && blockIdx.x == 0 && dti < 32) p.dbg[(1 * 32 + dti) * 4 + 3] = clock64();
+          if (++acc == NACC) { acc = 0; aph ^= 1u; }
+          continue;
+        }
         uint32_t wb = smem_base;                                           // resident weight block of iteration i
         for (int i = 0; i < num_it; ++i, wb += b_bytes) {
           mbar_wait(full_bar(s), ph);
@@ -782,7 +831,13 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   const int ntiles_n = (Nout + p.BN - 1) / p.BN;
   const size_t w_bytes = (size_t)taps * p.ncb * p.BN * 128;
   p.wres = (ntiles_n == 1 && w_bytes <= 96 * 1024) ? 1 : 0;
-  const size_t stage_bytes = 4 * 4096 + (p.wres ? 0 : (size_t)p.BN * 128);
+  // halo mode: needs resident weights, one image per tile box, and room for >= 2 stages
+  p.halo = 0;
+  p.copy_bytes = (uint32_t)((p.g.box_h + p.g.TH - 1) * p.g.bw * 128);
+  if (p.wres && p.g.one_box && p.g.box_n == 1 && taps > 1 && getenv("MC_CONV_NO_HALO") == nullptr &&
+      2 * (size_t)p.g.TW * p.copy_bytes + w_bytes <= 200 * 1024)
+    p.halo = 1;
+  const size_t stage_bytes = p.halo ? (size_t)p.g.TW * p.copy_bytes : 4 * 4096 + (p.wres ? 0 : (size_t)p.BN * 128);
   int stages = (int)((200 * 1024 - (p.wres ? w_bytes : 0)) / stage_bytes);
   if (stages > 8) stages = 8;
   if (stages < 1) stages = 1;
@@ -790,7 +845,8 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   const size_t smem = (p.wres ? w_bytes : 0) + stages * stage_bytes + (2 * stages + 2 * nacc + 1) * 8 + 16 + 1024;
 
   CUtensorMap tmX, tmW;
-  int rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, K, Wdim, p.g.bw, p.g.one_box ? p.g.box_h : p.g.bh, false,
+  int rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, K, Wdim, p.g.bw,
+                         p.halo ? p.g.box_h + p.g.TH - 1 : (p.g.one_box ? p.g.box_h : p.g.bh), false,
                          p.g.one_box ? p.g.box_n : 1);
   if (rc == 0) {
     const uint64_t dims[3] = {(uint64_t)Kp, (uint64_t)Nout, (uint64_t)taps};
