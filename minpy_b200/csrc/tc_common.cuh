@@ -23,20 +23,13 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 // warp barrier.  128 epilogue threads polling the same mbarrier flood the SM's barrier unit and
 // slow down the TMA transaction counts and tcgen05.commit arrivals that share it (measured: the
 // conv mainloop cost 0.63 us per k-block whatever was loaded or multiplied, profiles/r1p).
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity);
 __device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
-  if ((threadIdx.x & 31) == 0) {
-    uint32_t done;
-    const long long t0 = clock64();
-    do {
-      asm volatile(
-          "{\n\t.reg .pred p;\n\t"
-          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-          "selp.u32 %0, 1, 0, p;\n\t}"
-          : "=r"(done)
-          : "r"(bar), "r"(parity)
-          : "memory");
-      if (!done && clock64() - t0 > 4000000000LL) __trap();
-    } while (!done);
+  if ((threadIdx.x & 31) == 0 && !mbar_try(bar, parity)) {
+    const long long t0 = clock64();          // watchdog clock only once a wait has failed (reading it is slow)
+    while (!mbar_try(bar, parity)) {
+      if (clock64() - t0 > 4000000000LL) __trap();
+    }
   }
   __syncwarp();
 }
