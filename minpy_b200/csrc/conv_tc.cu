@@ -540,6 +540,158 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   }
 }
 
+// ------------------------------ weight gradient, halo mode ---------------------------------
+// Same contraction as conv_wgrad_kernel, for layers with at most 32 contraction columns per tap
+// (RGB merged rows, or <= 32 input channels) whose 128-pixel tiles are one rectangle of one image.
+// A stage is a whole TILE (box_h rows x bw pixels = 128 pixels = 16 K-steps):
+//   dy : one box per 32-filter block, [128 pixels][32 f]                         (MN-major A, LBO 16 KB)
+//   x  : one box per column shift tw, [(box_h + TH - 1) * bw pixels][32 c]      (MN-major B)
+// The row shift th of a tap is an offset of th*bw pixel rows inside the x box, so the TH taps of one
+// column shift are TH overlapping N-blocks at a uniform stride of bw*128 bytes (the descriptor's
+// LBO): ONE tcgen05.mma per (K-step, tw) covers them, and every input row is fetched TW times
+// instead of TH*TW times in 32-row boxes (the TMA unit retires ~5 cycles per row and was the bound).
+// TMEM columns: tap (th, tw) at (tw*TH + th)*32, bias (dy x ones) at TW*TH*32.
+struct ConvWgradHaloParams {
+  ConvGeom g;
+  float* ws;             // [splits][taps][F][Nn]
+  float* ws_bias;        // [splits][F] or nullptr
+  int F, Nn, stages, fbmax;
+  int tiles_per_split, total_tiles, tiles_per_image;
+  uint32_t copy_bytes;   // (box_h + TH - 1) * bw * 128
+  uint32_t ring_bytes;   // stages * stage_bytes, padded so that the 4-block A descriptor of the last stage stays inside
+};
+
+template <int TWC>   // column shifts known at compile time (1 = merged rows, 3 = 3x3 filter), 0 = run time
+__global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const __grid_constant__ CUtensorMap tmDy,
+                                                                           const __grid_constant__ CUtensorMap tmX,
+                                                                           const ConvWgradHaloParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  constexpr uint32_t fblk = 128u * 128u;                        // [128 pixels][32 f]
+  const int TH = p.g.TH, TW = TWC ? TWC : p.g.TW, taps = TH * TW;
+  const int f0 = blockIdx.z * 128;
+  const int fblocks = min(4, (p.F - f0 + 31) / 32);
+  const uint32_t a_bytes = (uint32_t)p.fbmax * fblk;
+  const uint32_t stage_bytes = a_bytes + (uint32_t)TW * p.copy_bytes;
+  const uint32_t tx_bytes = (uint32_t)fblocks * fblk + (uint32_t)TW * p.copy_bytes;
+  const int STAGES = p.stages;
+  const uint32_t ones_base = smem_base + p.ring_bytes;          // [32 pixels][32] of 1.0f
+  const uint32_t bar_base = ones_base + 4096u;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
+  const uint32_t tmem_slot = tmem_full_bar + 8u;
+  const bool do_bias = p.ws_bias != nullptr;
+  const uint32_t bias_col = (uint32_t)(taps * 32);
+  uint32_t tcols = 32;
+  while (tcols < bias_col + 32u) tcols <<= 1;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tbeg = blockIdx.y * p.tiles_per_split;
+  const int tend = min(p.total_tiles, tbeg + p.tiles_per_split);
+  const int num_it = max(0, tend - tbeg);
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tcols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  for (uint32_t i = threadIdx.x; i < 1024u; i += CONV_THREADS)
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(ones_base + 4u * i), "f"(1.0f) : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0 && lane == 0) {
+    const int dh0 = p.g.dh0, dw0 = p.g.dw0, BH = p.g.box_h, tpi = p.tiles_per_image;
+    int n = tbeg / tpi, r = tbeg - n * tpi;
+    int s = 0;
+    uint32_t ph = 0;
+    for (int it = 0; it < num_it; ++it) {
+      const int oh0 = r * BH;
+      mbar_wait(empty_bar(s), ph ^ 1u);
+      const uint32_t fb = full_bar(s);
+      mbar_expect_tx(fb, tx_bytes);
+      const uint32_t sa = smem_base + s * stage_bytes;
+      for (int j = 0; j < fblocks; ++j) tma_load_4d(sa + j * fblk, &tmDy, fb, f0 + 32 * j, 0, oh0, n);
+      uint32_t sb = sa + a_bytes;
+      for (int tw = 0; tw < TW; ++tw, sb += p.copy_bytes) tma_load_4d(sb, &tmX, fb, 0, tw + dw0, oh0 + dh0, n);
+      if (++s == STAGES) { s = 0; ph ^= 1u; }
+      if (++r == tpi) { r = 0; ++n; }
+    }
+  } else if (warp == 1 && lane == 0) {
+    const uint32_t idesc0 = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t idesc_t = idesc0 | ((uint32_t)((TH * 32) >> 3) << 17);       // TH taps of one column shift
+    const uint32_t idesc_b = idesc0 | ((uint32_t)(32 >> 3) << 17);
+    const uint64_t adesc0 = make_desc(0, fblk, 512, 1);                         // filter blocks 16 KB apart
+    const uint64_t bdesc0 = make_desc(0, (uint32_t)p.g.bw * 128u, 512, 1);      // taps bw pixel rows apart
+    const uint64_t odesc = make_desc(ones_base, 4096, 512, 1);
+    const uint32_t tw_cols = (uint32_t)(TH * 32);
+    int s = 0;
+    uint32_t ph = 0;
+    for (int it = 0; it < num_it; ++it) {
+      mbar_wait(full_bar(s), ph);
+      tcgen05_fence_after();
+      const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
+      uint64_t adesc = adesc0 + (uint64_t)((sa & 0x3FFFFu) >> 4);
+      uint64_t bdesc = bdesc0 + (uint64_t)((sb & 0x3FFFFu) >> 4);
+      const uint64_t cstep = (uint64_t)(p.copy_bytes >> 4);
+#pragma unroll 4
+      for (int kk = 0; kk < 16; ++kk, adesc += 64u, bdesc += 64u) {             // 8 pixel rows = 1024 bytes per K step
+        const uint32_t accf = (it > 0 || kk > 0) ? 1u : 0u;
+        if (TWC) {
+#pragma unroll
+          for (int tw = 0; tw < TWC; ++tw) umma_tf32(tmem_base + tw * tw_cols, adesc, bdesc + tw * cstep, idesc_t, accf);
+        } else {
+          uint64_t bd = bdesc;
+          uint32_t col = tmem_base;
+          for (int tw = 0; tw < TW; ++tw, bd += cstep, col += tw_cols) umma_tf32(col, adesc, bd, idesc_t, accf);
+        }
+        if (do_bias) umma_tf32(tmem_base + bias_col, adesc, odesc, idesc_b, accf);
+      }
+      umma_commit(empty_bar(s));
+      if (++s == STAGES) { s = 0; ph ^= 1u; }
+    }
+    umma_commit(tmem_full_bar);
+  }
+  __syncwarp();
+
+  mbar_wait_warp(tmem_full_bar, 0);
+  tcgen05_fence_after();
+  __syncwarp();
+  const int f = f0 + warp * 32 + lane;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  for (int tw = 0; tw < TW; ++tw) {
+    for (int th = 0; th < TH; ++th) {
+      float v[32];
+      tmem_ld32(lane_addr + (uint32_t)((tw * TH + th) * 32), v);
+      if (f < p.F) {
+        float* __restrict__ dst = p.ws + (((int64_t)blockIdx.y * taps + th * TW + tw) * p.F + f) * p.Nn;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < p.Nn) dst[j] = (num_it > 0) ? v[j] : 0.f;
+      }
+    }
+  }
+  if (do_bias) {
+    float v[32];
+    tmem_ld32(lane_addr + bias_col, v);
+    if (f < p.F) p.ws_bias[(int64_t)blockIdx.y * p.F + f] = (num_it > 0) ? v[0] : 0.f;
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tcols) : "memory");
+  }
+}
+
 // dw (F, C, KH, KW) = sum_z ws[z][tap][f][n] (merged: tap = kh, n = kw*Cp + c; else tap = kh*KW+kw, n = c)
 // and, in the trailing blocks of the same launch, dbias[f] = sum_z ws_bias[z][f].
 // A block is 32 consecutive workspace columns x 8 slices of the split range: the reads are
@@ -901,6 +1053,68 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
   p.F = F;
   p.BNc = (p.Nn + 31) / 32 * 32;
   if (p.BNc > 256) { set_error("conv_wgrad_tc: more than 256 input channels is not supported"); return 2; }
+  {
+    // halo mode (conv_wgrad_halo_kernel): <= 32 columns per tap, rectangular one-image tiles, room for >= 2 stages
+    ConvGeom hg = make_geom(N, OH, OW, true);
+    hg.TH = p.g.TH; hg.TW = p.g.TW; hg.dh0 = p.g.dh0; hg.dw0 = p.g.dw0;
+    const int fbmax = F >= 128 ? 4 : (F + 31) / 32;
+    const size_t copy_bytes = (size_t)(hg.box_h + hg.TH - 1) * hg.bw * 128;
+    const size_t stage_bytes = (size_t)fbmax * 16384 + (size_t)hg.TW * copy_bytes;
+    int stages = (int)((196 * 1024) / stage_bytes);
+    if (stages > 4) stages = 4;
+    size_t ring = (size_t)stages * stage_bytes;
+    if (stages >= 1 && (size_t)(stages - 1) * stage_bytes + 65536 > ring) ring = (size_t)(stages - 1) * stage_bytes + 65536;
+    if (p.BNc == 32 && hg.one_box && hg.box_n == 1 && taps * 32 + 32 <= 512 && stages >= 2 && ring <= 200 * 1024 &&
+        getenv("MC_CONV_NO_HALO") == nullptr) {
+      ConvWgradHaloParams h;
+      h.g = hg; h.F = F; h.Nn = p.Nn; h.stages = stages; h.fbmax = fbmax;
+      h.copy_bytes = (uint32_t)copy_bytes; h.ring_bytes = (uint32_t)ring;
+      h.tiles_per_image = hg.OHv / hg.box_h;
+      h.total_tiles = N * h.tiles_per_image;
+      const int ftiles = (F + 127) / 128;
+      int splits = sm_count() / ftiles;
+      if (splits > h.total_tiles) splits = h.total_tiles;
+      if (splits < 1) splits = 1;
+      h.tiles_per_split = (h.total_tiles + splits - 1) / splits;
+      splits = (h.total_tiles + h.tiles_per_split - 1) / h.tiles_per_split;
+      float* ws = nullptr;
+      const size_t ws_elems = (size_t)splits * taps * F * p.Nn;
+      MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * (ws_elems + (dbias ? (size_t)splits * F : 0)), stream()));
+      h.ws = ws;
+      h.ws_bias = dbias ? ws + ws_elems : nullptr;
+      CUtensorMap tmDy, tmX;
+      int rc = make_act_tmap(&tmDy, dy, N, OH, OW, Fp, Fp, OW, hg.bw, hg.box_h, true);
+      if (rc == 0) rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, p.Nn, Wdim, hg.bw, hg.box_h + hg.TH - 1, true);
+      static bool configured = false;
+      if (rc == 0 && !configured) {
+        rc = set_max_smem((const void*)conv_wgrad_halo_kernel<0>, "conv_wgrad_halo_kernel") ||
+             set_max_smem((const void*)conv_wgrad_halo_kernel<1>, "conv_wgrad_halo_kernel") ||
+             set_max_smem((const void*)conv_wgrad_halo_kernel<3>, "conv_wgrad_halo_kernel");
+        configured = rc == 0;
+      }
+      if (rc == 0) {
+        const size_t smem = ring + 4096 + (2 * stages + 1) * 8 + 16 + 1024;
+        dim3 grid(1, (unsigned)splits, (unsigned)ftiles);
+        if (hg.TW == 1) conv_wgrad_halo_kernel<1><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
+        else if (hg.TW == 3) conv_wgrad_halo_kernel<3><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
+        else conv_wgrad_halo_kernel<0><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("conv_wgrad_halo_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
+        else count_launch();
+      }
+      if (rc == 0) {
+        const int wblocks = (int)(((int64_t)taps * F * p.Nn + 31) / 32);
+        const int bblocks = dbias ? (F + 31) / 32 : 0;
+        conv_wgrad_reduce_kernel<<<wblocks + bblocks, 256, 0, stream()>>>(ws, dw, h.ws_bias, dbias, splits, taps, F, p.Nn, C, KH,
+                                                                         KW, Cp, merged, wblocks);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("conv_wgrad_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
+        else count_launch();
+      }
+      cudaFreeAsync(ws, stream());
+      return rc;
+    }
+  }
   // taps per CTA: as many accumulators as TMEM (512 columns, 32 kept for the bias) and a >= 2-stage
   // shared-memory ring allow, balanced over the tap groups
   int tpc = (512 - 32) / p.BNc;
