@@ -233,6 +233,21 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
             if (p.dbg && blockIdx.x == 0 && dti < 32 && cb == 0) p.dbg[(1 * 32 + dti) * 4 + 2] = clock64();
             const uint32_t sa = ring_base + s * stage_bytes;
             uint32_t wb = smem_base + (uint32_t)cb * b_bytes;              // weight block (tap 0, cb); taps are ncb blocks apart
+            if (TH == 3 && TW == 3) {
+              // 3x3: the 36 MMAs of a stage as straight-line code -- every descriptor is a constant
+              // offset from two bases, so the issuing thread spends ~30 instead of ~100 cycles per MMA
+              const uint64_t a0 = desc0 + (uint64_t)((sa & 0x3FFFFu) >> 4);
+              const uint64_t b0 = desc0 + (uint64_t)((wb & 0x3FFFFu) >> 4);
+              const uint32_t rstep = row_bytes >> 4, cstep = p.copy_bytes >> 4, wstep = ((uint32_t)ncb * b_bytes) >> 4;
+#pragma unroll
+              for (int th = 0; th < 3; ++th)
+#pragma unroll
+                for (int tw = 0; tw < 3; ++tw)
+#pragma unroll
+                  for (int k = 0; k < BKC / UMMA_K; ++k)
+                    umma_tf32(tacc, a0 + (uint64_t)(th * rstep + tw * cstep + 2u * k), b0 + (uint64_t)((th * 3 + tw) * wstep + 2u * k), idesc,
+                              (cb > 0 || th > 0 || tw > 0 || k > 0) ? 1u : 0u);
+            } else
             for (int th = 0; th < TH; ++th) {
               uint32_t at = sa + (uint32_t)th * row_bytes;
               for (int tw = 0; tw < TW; ++tw, at += p.copy_bytes, wb += (uint32_t)ncb * b_bytes) {
