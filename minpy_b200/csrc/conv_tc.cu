@@ -572,7 +572,10 @@ struct ConvWgradHaloParams {
   float* ws_bias;        // [splits][F] or nullptr
   int F, Nn, stages, fbmax;
   int tiles_per_split, total_tiles, tiles_per_image;
-  uint32_t copy_bytes;   // (box_h + TH - 1) * bw * 128
+  uint32_t copy_bytes;   // box_n * (box_h + TH - 1) * bw * 128
+  int kpi;               // K-steps (8 pixels) per image inside a tile: 16 / box_n
+  uint32_t img_skip16;   // (TH - 1) * bw * 128 / 16: halo rows between two images of one x box (descriptor units)
+  long long* dbg;        // MC_CONV_DBG: clock64 stamps of CTA 0 [role][tile][slot] (nullptr = off)
   uint32_t ring_bytes;   // stages * stage_bytes, padded so that the 4-block A descriptor of the last stage stays inside
 };
 
@@ -584,8 +587,9 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   constexpr uint32_t fblk = 128u * 128u;                        // [128 pixels][32 f]
   const int TH = p.g.TH, TW = TWC ? TWC : p.g.TW, taps = TH * TW;
-  const int f0 = blockIdx.z * 128;
-  const int fblocks = min(4, (p.F - f0 + 31) / 32);
+  const int f0 = blockIdx.z * (p.fbmax * 32);
+  const int fblocks = min(p.fbmax, (p.F - f0 + 31) / 32);
+  const int c0 = blockIdx.x * 32;                               // this CTA's 32 contraction columns of every tap
   const uint32_t a_bytes = (uint32_t)p.fbmax * fblk;
   const uint32_t stage_bytes = a_bytes + (uint32_t)TW * p.copy_bytes;
   const uint32_t tx_bytes = (uint32_t)fblocks * fblk + (uint32_t)TW * p.copy_bytes;
@@ -596,7 +600,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
   const uint32_t tmem_slot = tmem_full_bar + 8u;
-  const bool do_bias = p.ws_bias != nullptr;
+  const bool do_bias = p.ws_bias != nullptr && blockIdx.x == 0;
   const uint32_t bias_col = (uint32_t)(taps * 32);
   uint32_t tcols = 32;
   while (tcols < bias_col + 32u) tcols <<= 1;
@@ -625,23 +629,28 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
   if (warp == 0 && lane == 0) {
-    const int dh0 = p.g.dh0, dw0 = p.g.dw0, BH = p.g.box_h, tpi = p.tiles_per_image;
+    const int dh0 = p.g.dh0, dw0 = p.g.dw0, BH = p.g.box_h, tpi = p.tiles_per_image, bn = p.g.box_n;
     int n = tbeg / tpi, r = tbeg - n * tpi;
+    n *= bn;                                                     // bn > 1: whole images, tpi == 1
     int s = 0;
     uint32_t ph = 0;
     for (int it = 0; it < num_it; ++it) {
       const int oh0 = r * BH;
+      const bool dbgw = p.dbg && blockIdx.x + blockIdx.y + blockIdx.z == 0 && it < 32;
+      if (dbgw) p.dbg[(0 * 32 + it) * 4 + 0] = clock64();
       mbar_wait(empty_bar(s), ph ^ 1u);
+      if (dbgw) p.dbg[(0 * 32 + it) * 4 + 1] = clock64();
       const uint32_t fb = full_bar(s);
       mbar_expect_tx(fb, tx_bytes);
       const uint32_t sa = smem_base + s * stage_bytes;
       for (int j = 0; j < fblocks; ++j) tma_load_4d(sa + j * fblk, &tmDy, fb, f0 + 32 * j, 0, oh0, n);
       uint32_t sb = sa + a_bytes;
-      for (int tw = 0; tw < TW; ++tw, sb += p.copy_bytes) tma_load_4d(sb, &tmX, fb, 0, tw + dw0, oh0 + dh0, n);
+      for (int tw = 0; tw < TW; ++tw, sb += p.copy_bytes) tma_load_4d(sb, &tmX, fb, c0, tw + dw0, oh0 + dh0, n);
+      if (dbgw) p.dbg[(0 * 32 + it) * 4 + 2] = clock64();
       if (++s == STAGES) { s = 0; ph ^= 1u; }
-      if (++r == tpi) { r = 0; ++n; }
+      if (++r == tpi) { r = 0; n += bn; }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1 && elect_one()) {
     const uint32_t idesc0 = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(128 >> 4) << 24);
     const uint32_t idesc_t = idesc0 | ((uint32_t)((TH * 32) >> 3) << 17);       // TH taps of one column shift
     const uint32_t idesc_b = idesc0 | ((uint32_t)(32 >> 3) << 17);
@@ -652,15 +661,21 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
     int s = 0;
     uint32_t ph = 0;
     for (int it = 0; it < num_it; ++it) {
+      const bool dbgw = p.dbg && blockIdx.x + blockIdx.y + blockIdx.z == 0 && it < 32;
+      if (dbgw) p.dbg[(1 * 32 + it) * 4 + 0] = clock64();
       mbar_wait(full_bar(s), ph);
       tcgen05_fence_after();
+      if (dbgw) p.dbg[(1 * 32 + it) * 4 + 1] = clock64();
       const uint32_t sa = smem_base + s * stage_bytes, sb = sa + a_bytes;
       uint64_t adesc = adesc0 + (uint64_t)((sa & 0x3FFFFu) >> 4);
       uint64_t bdesc = bdesc0 + (uint64_t)((sb & 0x3FFFFu) >> 4);
       const uint64_t cstep = (uint64_t)(p.copy_bytes >> 4);
+      const int kmask = p.kpi - 1;                                              // kpi: 4, 8 or 16
+      const uint64_t skip = (uint64_t)p.img_skip16;
 #pragma unroll 4
       for (int kk = 0; kk < 16; ++kk, adesc += 64u, bdesc += 64u) {             // 8 pixel rows = 1024 bytes per K step
         const uint32_t accf = (it > 0 || kk > 0) ? 1u : 0u;
+        if (kk > 0 && (kk & kmask) == 0) bdesc += skip;                         // next image of the box: over its halo rows
         if (TWC) {
 #pragma unroll
           for (int tw = 0; tw < TWC; ++tw) umma_tf32(tmem_base + tw * tw_cols, adesc, bdesc + tw * cstep, idesc_t, accf);
@@ -672,34 +687,38 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
         if (do_bias) umma_tf32(tmem_base + bias_col, adesc, odesc, idesc_b, accf);
       }
       umma_commit(empty_bar(s));
+      if (dbgw) p.dbg[(1 * 32 + it) * 4 + 2] = clock64();
       if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
     umma_commit(tmem_full_bar);
   }
   __syncwarp();
 
+  if (p.dbg && blockIdx.x + blockIdx.y + blockIdx.z == 0 && threadIdx.x == 64) p.dbg[(2 * 32 + 0) * 4 + 0] = clock64();
   mbar_wait_warp(tmem_full_bar, 0);
   tcgen05_fence_after();
   __syncwarp();
+  if (p.dbg && blockIdx.x + blockIdx.y + blockIdx.z == 0 && threadIdx.x == 64) p.dbg[(2 * 32 + 0) * 4 + 1] = clock64();
   const int f = f0 + warp * 32 + lane;
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
   for (int tw = 0; tw < TW; ++tw) {
     for (int th = 0; th < TH; ++th) {
       float v[32];
       tmem_ld32(lane_addr + (uint32_t)((tw * TH + th) * 32), v);
-      if (f < p.F) {
-        float* __restrict__ dst = p.ws + (((int64_t)blockIdx.y * taps + th * TW + tw) * p.F + f) * p.Nn;
+      if (f < p.F && warp < fblocks) {
+        float* __restrict__ dst = p.ws + (((int64_t)blockIdx.y * taps + th * TW + tw) * p.F + f) * p.Nn + c0;
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-          if (j < p.Nn) dst[j] = (num_it > 0) ? v[j] : 0.f;
+          if (c0 + j < p.Nn) dst[j] = (num_it > 0) ? v[j] : 0.f;
       }
     }
   }
   if (do_bias) {
     float v[32];
     tmem_ld32(lane_addr + bias_col, v);
-    if (f < p.F) p.ws_bias[(int64_t)blockIdx.y * p.F + f] = (num_it > 0) ? v[0] : 0.f;
+    if (f < p.F && warp < fblocks) p.ws_bias[(int64_t)blockIdx.y * p.F + f] = (num_it > 0) ? v[0] : 0.f;
   }
+  if (p.dbg && blockIdx.x + blockIdx.y + blockIdx.z == 0 && threadIdx.x == 64) p.dbg[(2 * 32 + 0) * 4 + 2] = clock64();
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -1072,22 +1091,29 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
     // halo mode (conv_wgrad_halo_kernel): <= 32 columns per tap, rectangular one-image tiles, room for >= 2 stages
     ConvGeom hg = make_geom(N, OH, OW, true);
     hg.TH = p.g.TH; hg.TW = p.g.TW; hg.dh0 = p.g.dh0; hg.dw0 = p.g.dw0;
-    const int fbmax = F >= 128 ? 4 : (F + 31) / 32;
-    const size_t copy_bytes = (size_t)(hg.box_h + hg.TH - 1) * hg.bw * 128;
-    const size_t stage_bytes = (size_t)fbmax * 16384 + (size_t)hg.TW * copy_bytes;
-    int stages = (int)((196 * 1024) / stage_bytes);
-    if (stages > 4) stages = 4;
-    size_t ring = (size_t)stages * stage_bytes;
-    if (stages >= 1 && (size_t)(stages - 1) * stage_bytes + 65536 > ring) ring = (size_t)(stages - 1) * stage_bytes + 65536;
-    if (p.BNc == 32 && hg.one_box && hg.box_n == 1 && taps * 32 + 32 <= 512 && stages >= 2 && ring <= 200 * 1024 &&
-        getenv("MC_CONV_NO_HALO") == nullptr) {
+    int fbmax = F >= 128 ? 4 : (F + 31) / 32;                    // 32-filter blocks per CTA: fewer when the x boxes are large
+    const size_t copy_bytes = (size_t)hg.box_n * (hg.box_h + hg.TH - 1) * hg.bw * 128;
+    size_t stage_bytes = 0, ring = 0;
+    int stages = 0;
+    for (;; fbmax = (fbmax + 1) / 2) {
+      stage_bytes = (size_t)fbmax * 16384 + (size_t)hg.TW * copy_bytes;
+      stages = (int)((196 * 1024) / stage_bytes);
+      if (stages > 4) stages = 4;
+      ring = (size_t)stages * stage_bytes;
+      if (stages >= 1 && (size_t)(stages - 1) * stage_bytes + 65536 > ring) ring = (size_t)(stages - 1) * stage_bytes + 65536;
+      if ((stages >= 2 && ring <= 200 * 1024) || fbmax == 1) break;
+    }
+    const int cblocks = p.BNc / 32;
+    if (hg.one_box && taps * 32 + 32 <= 512 && stages >= 2 && ring <= 200 * 1024 && getenv("MC_CONV_NO_HALO") == nullptr) {
       ConvWgradHaloParams h;
       h.g = hg; h.F = F; h.Nn = p.Nn; h.stages = stages; h.fbmax = fbmax;
       h.copy_bytes = (uint32_t)copy_bytes; h.ring_bytes = (uint32_t)ring;
+      h.kpi = 16 / hg.box_n;
+      h.img_skip16 = (uint32_t)((hg.TH - 1) * hg.bw * 128) >> 4;
       h.tiles_per_image = hg.OHv / hg.box_h;
-      h.total_tiles = N * h.tiles_per_image;
-      const int ftiles = (F + 127) / 128;
-      int splits = sm_count() / ftiles;
+      h.total_tiles = (N + hg.box_n - 1) / hg.box_n * h.tiles_per_image;
+      const int ftiles = (F + fbmax * 32 - 1) / (fbmax * 32);
+      int splits = sm_count() / (ftiles * cblocks);
       if (splits > h.total_tiles) splits = h.total_tiles;
       if (splits < 1) splits = 1;
       h.tiles_per_split = (h.total_tiles + splits - 1) / splits;
@@ -1098,8 +1124,8 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
       h.ws = ws;
       h.ws_bias = dbias ? ws + ws_elems : nullptr;
       CUtensorMap tmDy, tmX;
-      int rc = make_act_tmap(&tmDy, dy, N, OH, OW, Fp, Fp, OW, hg.bw, hg.box_h, true);
-      if (rc == 0) rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, p.Nn, Wdim, hg.bw, hg.box_h + hg.TH - 1, true);
+      int rc = make_act_tmap(&tmDy, dy, N, OH, OW, Fp, Fp, OW, hg.bw, hg.box_h, true, hg.box_n);
+      if (rc == 0) rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, p.Nn, Wdim, hg.bw, hg.box_h + hg.TH - 1, true, hg.box_n);
       static bool configured = false;
       if (rc == 0 && !configured) {
         rc = set_max_smem((const void*)conv_wgrad_halo_kernel<0>, "conv_wgrad_halo_kernel") ||
@@ -1109,10 +1135,30 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
       }
       if (rc == 0) {
         const size_t smem = ring + 4096 + (2 * stages + 1) * 8 + 16 + 1024;
-        dim3 grid(1, (unsigned)splits, (unsigned)ftiles);
+        dim3 grid((unsigned)cblocks, (unsigned)splits, (unsigned)ftiles);
+        h.dbg = nullptr;
+        static long long* dbg_buf = nullptr;
+        const bool dbg = getenv("MC_CONV_DBG") != nullptr;
+        if (dbg) {
+          if (!dbg_buf) cudaMalloc((void**)&dbg_buf, sizeof(long long) * 3 * 32 * 4);
+          cudaMemset(dbg_buf, 0, sizeof(long long) * 3 * 32 * 4);
+          h.dbg = dbg_buf;
+        }
         if (hg.TW == 1) conv_wgrad_halo_kernel<1><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
         else if (hg.TW == 3) conv_wgrad_halo_kernel<3><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
         else conv_wgrad_halo_kernel<0><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
+        if (dbg) {
+          static long long host[3 * 32 * 4];
+          cudaDeviceSynchronize();
+          cudaMemcpy(host, dbg_buf, sizeof(host), cudaMemcpyDeviceToHost);
+          const long long t0 = host[0];
+          fprintf(stderr, "wgrad halo dbg: tiles/CTA=%d stages=%d fbmax=%d grid=(%d,%d,%d) stage_bytes=%d\n", h.tiles_per_split, stages, fbmax, cblocks, splits, ftiles, (int)stage_bytes);
+          for (int t = 0; t < 10 && t < h.tiles_per_split; ++t)
+            fprintf(stderr, "  tile %2d  prod start %6lld slot-free %6lld issued %6lld | mma start %6lld full %6lld committed %6lld\n", t,
+                    host[(0 * 32 + t) * 4 + 0] - t0, host[(0 * 32 + t) * 4 + 1] - t0, host[(0 * 32 + t) * 4 + 2] - t0,
+                    host[(1 * 32 + t) * 4 + 0] - t0, host[(1 * 32 + t) * 4 + 1] - t0, host[(1 * 32 + t) * 4 + 2] - t0);
+          fprintf(stderr, "  epilogue wait %6lld accumulators complete %6lld stored %6lld\n", host[(2 * 32) * 4 + 0] - t0, host[(2 * 32) * 4 + 1] - t0, host[(2 * 32) * 4 + 2] - t0);
+        }
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("conv_wgrad_halo_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
         else count_launch();
@@ -1191,6 +1237,7 @@ int nchw_to_nhwc(const float* x, float* y, int N, int C, int H, int W, int Cp, i
     MC_LAUNCHED();
     return 0;
   }
+  if (wpad == 0) { W *= H; H = 1; }            // no pad columns: (h, w) is one flat pixel axis, full 32-pixel tiles for small images
   dim3 grid((unsigned)((W + 2 * wpad + 31) / 32), (unsigned)((Cp + 31) / 32), (unsigned)(N * H));
   nchw_to_nhwc_kernel<<<grid, 256, 0, stream()>>>(x, y, N, C, H, W, Cp, wpad);
   MC_LAUNCHED();
@@ -1198,6 +1245,7 @@ int nchw_to_nhwc(const float* x, float* y, int N, int C, int H, int W, int Cp, i
 }
 
 int nhwc_to_nchw(const float* x, float* y, int N, int C, int H, int W, int Cp) {
+  W *= H; H = 1;                               // (h, w) as one flat pixel axis
   dim3 grid((unsigned)((W + 31) / 32), (unsigned)((C + 31) / 32), (unsigned)(N * H));
   nhwc_to_nchw_kernel<<<grid, 256, 0, stream()>>>(x, y, N, C, H, W, Cp);
   MC_LAUNCHED();

@@ -40,3 +40,23 @@ for name, C, H, F in [('conv1', 3, 32, 32), ('conv2', 32, 16, 64), ('conv3', 64,
         print('%s dgrad %8.2f us  %6.1f TF/s  %7.1f GB/s' % (name, t, flops / t / 1e6, nbytes / t / 1e3), flush=True)
     t = timeit(lambda: lib.mc_conv2d_nhwc_wgrad(x.ptr, y.ptr, dw.ptr, db.ptr, N, C, H, H, Cp, wpad, F, Fp, 3, 3, 1))
     print('%s wgrad %8.2f us  %6.1f TF/s  %7.1f GB/s' % (name, t, flops / t / 1e6, nbytes / t / 1e3), flush=True)
+
+# pooling and layout conversion at the same layer shapes
+for name, Cp, H in [('pool1', 32, 32), ('pool2', 64, 16), ('pool3', 128, 8)]:
+    x = CudaArray.from_numpy(rng.randn(N, H, H, Cp).astype(np.float32))
+    y = CudaArray.empty((N, H // 2, H // 2, Cp)); dx = CudaArray.empty((N, H, H, Cp))
+    idx = CudaArray.empty((N * (H // 2) * (H // 2) * Cp // 4,))
+    nb_f = 4.0 * N * H * H * Cp * 1.25 + N * H * H * Cp / 4
+    t = timeit(lambda: lib.mc_maxpool2d_nhwc_fwd(x.ptr, y.ptr, idx.ptr, N, H, H, Cp, 2, 2, 2))
+    print('%s fwd   %8.2f us  %7.1f GB/s' % (name, t, nb_f / t / 1e3), flush=True)
+    nb_b = 4.0 * N * H * H * Cp * 1.5 + N * H * H * Cp / 4
+    t = timeit(lambda: lib.mc_maxpool2d_nhwc_bwd(y.ptr, idx.ptr, y.ptr, dx.ptr, N, H, H, Cp, 2, H // 2, H // 2))
+    print('%s bwd   %8.2f us  %7.1f GB/s' % (name, t, nb_b / t / 1e3), flush=True)
+xin = CudaArray.from_numpy(rng.randn(N, 3, 32, 32).astype(np.float32)); xo = CudaArray.empty((N, 32, 34, 4))
+t = timeit(lambda: lib.mc_nchw_to_nhwc(xin.ptr, xo.ptr, N, 3, 32, 32, 4, 1))
+print('input nchw->nhwc4 %8.2f us  %7.1f GB/s' % (t, 4.0 * N * 32 * (32 * 3 + 34 * 4) / t / 1e3), flush=True)
+a = CudaArray.from_numpy(rng.randn(N, 4, 4, 128).astype(np.float32)); bb = CudaArray.empty((N, 128, 4, 4))
+t = timeit(lambda: lib.mc_nhwc_to_nchw(a.ptr, bb.ptr, N, 128, 4, 4, 128))
+print('trunk nhwc->nchw  %8.2f us  %7.1f GB/s' % (t, 8.0 * N * 2048 / t / 1e3), flush=True)
+t = timeit(lambda: lib.mc_nchw_to_nhwc(bb.ptr, a.ptr, N, 128, 4, 4, 128, 0))
+print('trunk nchw->nhwc  %8.2f us  %7.1f GB/s' % (t, 8.0 * N * 2048 / t / 1e3), flush=True)
