@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
   if (warp == 8) {
-    if (lane == 0) {
+    if (elect_one()) {
       // ------------------------------ TMA producer ------------------------------------
       // One thread: every instruction here is serial latency (an EMPTY mainloop still cost 0.2 us
       // per k-block, profiles/r1p), so everything loop-invariant lives in registers, the stage
@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
       }
     }
   } else if (warp == 9) {
-    if (lane == 0) {
+    if (elect_one()) {
       // ------------------------------ MMA issuer --------------------------------------
       // c_format F32, a/b TF32, both operands K-major, N>>3 at [17,23), M>>4 at [24,29)
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);

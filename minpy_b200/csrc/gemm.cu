@@ -318,7 +318,65 @@ struct GemmParams {
   int relu, accumulate;
   int a_mn, b_mn;      // operand tile is MN-major (1) or K-major (0)
   int kb_per_split;    // k-blocks (of BK) per grid.z slice
+  int cluster;         // > 1: the grid.z slices of a tile are one thread-block cluster; partials meet in DSMEM
 };
+
+// CTA q of an S-CTA cluster sums rows [q*BM/S, (q+1)*BM/S) of the parked partial tiles of all S peers
+// (distributed shared memory), slice order 0..S-1, and applies the epilogue.  All S loads of an output
+// chunk are issued before the first add: DSMEM latency is paid once per chunk, not S times.
+template <int BN, int S>
+__device__ __forceinline__ void cluster_reduce(const GemmParams& p, uint32_t smem_base, int m0, int n0, bool vec_ok) {
+  constexpr int rows_per = BM / S;
+  constexpr int F4 = BN / 4;
+  constexpr int ITEMS = rows_per * F4;
+  const int q = blockIdx.z;                           // cluster dims (1,1,S), gridDim.z == S: rank in cluster
+  uint32_t peer[S];
+#pragma unroll
+  for (int z = 0; z < S; ++z) asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(peer[z]) : "r"(smem_base), "r"(z));
+#pragma unroll (S >= 8 ? 1 : 2)
+  for (int i = threadIdx.x; i < ITEMS; i += THREADS) {
+    const int r = q * rows_per + i / F4, j = i % F4;
+    const uint32_t off = (uint32_t)r * (BN * 4u) + (uint32_t)(j ^ (r & 7)) * 16u;
+    float4 t[S];
+#pragma unroll
+    for (int z = 0; z < S; ++z)
+      asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(t[z].x), "=f"(t[z].y), "=f"(t[z].z), "=f"(t[z].w) : "r"(peer[z] + off) : "memory");
+    float4 o = t[0];
+#pragma unroll
+    for (int z = 1; z < S; ++z) { o.x += t[z].x; o.y += t[z].y; o.z += t[z].z; o.w += t[z].w; }
+    const int grow = m0 + r, col = n0 + 4 * j;
+    if (grow < p.M && col < p.N) {
+      float* dst = p.C + (int64_t)grow * p.ldc + col;
+      if (vec_ok && col + 4 <= p.N) {
+        if (p.bias) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+          o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+        }
+        if (p.accumulate) {
+          const float4 c = *reinterpret_cast<const float4*>(dst);
+          o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
+        }
+        if (p.relu) {
+          o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
+          o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
+        }
+        *reinterpret_cast<float4*>(dst) = o;
+      } else {
+        const float e[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (col + u < p.N) {
+            float w = e[u];
+            if (p.bias) w += __ldg(p.bias + col + u);
+            if (p.accumulate) w += dst[u];
+            if (p.relu) w = (w != w) ? w : fmaxf(w, 0.f);
+            dst[u] = w;
+          }
+        }
+      }
+    }
+  }
+}
 
 // Stage layout (each operand tile is a stack of SWIZZLE_128B atoms: 8 rows x 128 B):
 //   K-major  tile (R rows of MN, BK of K): R rows x 128 B; 8-row groups 1024 B apart (SBO).
@@ -365,7 +423,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0 && elect_one()) {
     // ------------------------------ TMA producer ------------------------------------
     // (one thread: stage / phase / coordinates are carried, not recomputed -- see conv_tc.cu)
     const bool a_mn = p.a_mn != 0, b_mn = p.b_mn != 0;
@@ -390,7 +448,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
       }
       if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1 && elect_one()) {
     // ------------------------------ MMA issuer --------------------------------------
     // Instruction descriptor (cute UMMA::InstrDescriptor): c_format F32 (1<<4), a/b TF32
     // (2<<7, 2<<10), a_major bit 15, b_major bit 16, N>>3 at [17,23), M>>4 at [24,29).
@@ -425,6 +483,42 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   __syncwarp();
   const int row = m0 + warp * 32 + lane;
   const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+  if (p.cluster > 1) {
+    // Split-K inside a thread-block cluster: the S = gridDim.z CTAs of one output tile each hold a
+    // partial accumulator.  Every CTA parks its partial in its own shared memory (the operand ring is
+    // idle now), the cluster synchronises, and CTA q sums rows [q*BM/S, (q+1)*BM/S) over the S peers
+    // through distributed shared memory, in slice order 0..S-1 (deterministic), and applies the
+    // epilogue.  No workspace in HBM, no second kernel (splitk_reduce_kernel + its launch gap were
+    // 12% of the C3 step).  Parked layout: row r at r*BN*4, its 16-byte chunk j at slot j ^ (r & 7).
+    const int r_local = warp * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      float v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+      const uint32_t rbase = smem_base + (uint32_t)r_local * (BN * 4u);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint32_t slot = (uint32_t)((c0 >> 2) + j) ^ (uint32_t)(r_local & 7);
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(rbase + slot * 16u), "f"(v[4 * j]), "f"(v[4 * j + 1]),
+                     "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+      }
+    }
+    tcgen05_fence_before();
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    const bool vec_c = vec_ok;
+    switch (p.cluster) {
+      case 2: cluster_reduce<BN, 2>(p, smem_base, m0, n0, vec_c); break;
+      case 4: cluster_reduce<BN, 4>(p, smem_base, m0, n0, vec_c); break;
+      case 8: cluster_reduce<BN, 8>(p, smem_base, m0, n0, vec_c); break;
+      default: cluster_reduce<BN, 16>(p, smem_base, m0, n0, vec_c); break;
+    }
+    // peers may still be reading this CTA's shared memory
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (warp == 1) {
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
+    }
+    return;
+  }
 #pragma unroll 1
   for (int c0 = 0; c0 < BN; c0 += 32) {
     float v[32];
@@ -599,6 +693,22 @@ static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     configured = true;
   }
   dim3 grid((unsigned)((p.N + BN - 1) / BN), (unsigned)((p.M + BM - 1) / BM), (unsigned)splits);
+  if (p.cluster > 1) {
+    static bool big_ok = false;
+    if (p.cluster > 8 && !big_ok) {
+      MC_CHECK(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      big_ok = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = SMEM; cfg.stream = stream();
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)p.cluster;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    MC_CHECK(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<BN, STAGES>, tmA, tmB, p));
+    count_launch();
+    return 0;
+  }
   gemm_tf32_kernel<BN, STAGES><<<grid, THREADS, SMEM, stream()>>>(tmA, tmB, p);
   MC_LAUNCHED();
   return 0;
@@ -690,7 +800,24 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   p.b_mn = tb ? 0 : 1;
   p.kb_per_split = kb_per;
   p.counters = nullptr;
-  if (splits > 1) {
+  p.cluster = 0;
+  // Cluster split-K (partials reduced through distributed shared memory, S in {2,4,8,16} slices, every
+  // slice non-empty) is OFF by default: it removes splitk_reduce_kernel and the HBM workspace, and is
+  // -1..+1 us per call in isolation, but whole steps got slower (C3 0.341 -> 0.348 ms, C5 3.83 -> 4.06 ms,
+  // profiles/r1z: S co-scheduled SMs per tile delay the next kernel's start).  MC_GEMM_CLUSTER=<max S>
+  // enables it for experiments.
+  static int use_cluster = -1;
+  if (use_cluster < 0) { const char* e = getenv("MC_GEMM_CLUSTER"); use_cluster = e ? atoi(e) : 0; }
+  if (splits > 1 && use_cluster > 1) {
+    int S = 2;
+    while (S * 2 <= splits && S * 2 <= use_cluster && S * 2 <= 16) S *= 2;
+    for (; S > 1; S /= 2) {
+      const int per = (num_kb + S - 1) / S;
+      if ((S - 1) * per < num_kb) { kb_per = per; break; }
+    }
+    if (S > 1) { splits = S; p.kb_per_split = kb_per; p.cluster = S; }
+  }
+  if (splits > 1 && !p.cluster) {
     MC_CHECK(cudaMallocAsync((void**)&p.ws, sizeof(float) * splits * M * N, stream()));
     // In-kernel fixup (last-arriving slice CTA reduces) is OFF by default: one SM streaming S x 64 KB
     // of partials is latency-bound (c3_fwd2: 9.9 -> 27 us measured, r1t); the separate reduce kernel
@@ -700,7 +827,7 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     if (fixup && tiles <= kMaxFixupTiles) p.counters = splitk_counters();
   }
   int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
-  if (rc == 0 && splits > 1 && !p.counters) {
+  if (rc == 0 && splits > 1 && !p.counters && !p.cluster) {
     splitk_reduce_kernel<<<grid_for(M * N / 4 + 1, 256), 256, 0, stream()>>>(p.ws, splits, M, N, C, ldc, bias, relu, accumulate);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("splitk reduce launch failed: %s", cudaGetErrorString(e)); rc = 1; }

@@ -181,6 +181,37 @@ def test_gemm(cuda, M, N, K, ta, tb):
     cuda.set_gemm_precision('tf32')
 
 
+def test_gemm_cluster_splitk_opt_in():
+    """MC_GEMM_CLUSTER=8 (split-K slices of a tile as one thread-block cluster, partials summed through
+    distributed shared memory) gives the same products as the default workspace + reduce path."""
+    import os, subprocess, sys
+    code = r"""
+import numpy as np
+from minpy_b200 import ops as cuda
+from minpy_b200.cuda_array import CudaArray
+cuda.L()
+cuda.set_gemm_precision('tf32')
+rng = np.random.RandomState(0)
+for M, N, K, ta, tb in [(256, 512, 3072, 0, 0), (1024, 512, 512, 0, 1), (512, 512, 1024, 1, 0), (128, 1024, 4096, 0, 1),
+                        (130, 260, 1000, 0, 0), (128, 4096, 1024, 0, 0)]:
+    a = rng.randn(*((K, M) if ta else (M, K))).astype(np.float32)
+    b = rng.randn(*((N, K) if tb else (K, N))).astype(np.float32)
+    bias = rng.randn(N).astype(np.float32)
+    ref = (a.T if ta else a).astype(np.float64) @ (b.T if tb else b).astype(np.float64)
+    ad, bd = CudaArray.from_numpy(a), CudaArray.from_numpy(b)
+    got = cuda.gemm(ad, bd, bool(ta), bool(tb), bias=CudaArray.from_numpy(bias), relu=True).asnumpy()
+    err = float(np.max(np.abs(got - np.maximum(ref + bias, 0))) / (3 * np.sqrt(K)))
+    assert err <= 1e-2, (M, N, K, err)
+    acc = cuda.gemm(ad, bd, bool(ta), bool(tb), out=CudaArray.from_numpy(ref.astype(np.float32)), accumulate=True).asnumpy()
+    assert float(np.max(np.abs(acc - 2 * ref)) / (3 * np.sqrt(K))) <= 1e-2, (M, N, K, 'accumulate')
+print('cluster ok')
+"""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, MC_GEMM_CLUSTER='8', PYTHONPATH=root)
+    out = subprocess.run([sys.executable, '-c', code], env=env, cwd=root, capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and 'cluster ok' in out.stdout, out.stdout + out.stderr
+
+
 def test_gemm_tf32_path_taken(cuda):
     """The tensor-core path must actually run for TMA-describable shapes (no silent fallback)."""
     import ctypes
