@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0 && elect_one()) {
     // single thread: loop-invariant values in registers, chunk coordinates carried incrementally
     const int TW = p.g.TW, dh0 = p.g.dh0, dw0 = p.g.dw0, cpi = p.g.cpi, cpr = p.g.cpr, bh = p.g.bh;
     const bool wide = p.g.OWv >= 32;
@@ -495,7 +495,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
       else ++row;
       if (++r == cpi) { r = 0; row = 0; col = 0; ++n; }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1 && elect_one()) {
     // both operands MN-major (f / channels contiguous, pixels = K): major bits 15, 16 set.
     // Filter blocks that were not loaded hold stale shared memory: they only reach accumulator
     // rows >= F, which the epilogue never reads (row m of D depends on row m of A alone).
@@ -628,7 +628,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0 && elect_one()) {
     const int dh0 = p.g.dh0, dw0 = p.g.dw0, BH = p.g.box_h, tpi = p.tiles_per_image, bn = p.g.box_n;
     int n = tbeg / tpi, r = tbeg - n * tpi;
     n *= bn;                                                     // bn > 1: whole images, tpi == 1

@@ -206,23 +206,27 @@ __global__ void __launch_bounds__(256) skinny_nn_kernel(int M, int N, int K, con
   }
 }
 
-// C(M,N) = A^T . B with A stored (K,M), B (K,N), N <= 16: a block owns 32 columns m and splits K over
-// its 16 warps (A rows are coalesced along m, B rows are broadcasts); fixed-order combine in smem.
-constexpr int SK_TN_SLICES = 16;
-__global__ void __launch_bounds__(32 * SK_TN_SLICES) skinny_tn_kernel(int M, int N, int K, const float* __restrict__ A,
-                                                                      int64_t lda, const float* __restrict__ B, int64_t ldb,
-                                                                      float* __restrict__ C, int64_t ldc,
-                                                                      const float* __restrict__ bias, int relu, int accumulate) {
-  __shared__ float red[SK_TN_SLICES][SK_MAXN][33];
-  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
-  const int m = blockIdx.x * 32 + lane;
+// C(M,N) = A^T . B with A stored (K,M), B (K,N), N <= 16.  A block owns 8 columns m (one 32-byte
+// sector of every A row) and splits K 64 ways (4 lane groups x 16 warps), four rows in flight per
+// thread: M = 512 gives 64 blocks with 4 dependent load rounds each (the first version -- 32 columns
+// per block, 16 K slices -- ran 16 blocks x 16 rounds of DRAM latency: 14 us for 2 MB).  The 64 partial
+// sums are combined in a fixed order (lane groups by shuffle, warps through shared memory).
+constexpr int SK_TN_WARPS = 16;
+__global__ void __launch_bounds__(32 * SK_TN_WARPS) skinny_tn_kernel(int M, int N, int K, const float* __restrict__ A,
+                                                                     int64_t lda, const float* __restrict__ B, int64_t ldb,
+                                                                     float* __restrict__ C, int64_t ldc,
+                                                                     const float* __restrict__ bias, int relu, int accumulate) {
+  __shared__ float red[SK_TN_WARPS][SK_MAXN][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int mi = lane & 7, ks = lane >> 3;
+  const int m = blockIdx.x * 8 + mi;
+  constexpr int ST = 4 * SK_TN_WARPS;               // K slices
   float acc[SK_MAXN];
 #pragma unroll
   for (int n = 0; n < SK_MAXN; ++n) acc[n] = 0.f;
   if (m < M) {
     const float* __restrict__ a = A + m;
-    int k = slice;
-    constexpr int ST = SK_TN_SLICES;
+    int k = warp * 4 + ks;
     for (; k + 3 * ST < K; k += 4 * ST) {
       const float a0 = a[(int64_t)k * lda], a1 = a[(int64_t)(k + ST) * lda];
       const float a2 = a[(int64_t)(k + 2 * ST) * lda], a3 = a[(int64_t)(k + 3 * ST) * lda];
@@ -245,15 +249,20 @@ __global__ void __launch_bounds__(32 * SK_TN_SLICES) skinny_tn_kernel(int M, int
     }
   }
 #pragma unroll
-  for (int n = 0; n < SK_MAXN; ++n) red[slice][n][lane] = acc[n];
+  for (int n = 0; n < SK_MAXN; ++n) {
+    acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], 8);
+    acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], 16);
+    if (ks == 0) red[warp][n][mi] = acc[n];
+  }
   __syncthreads();
-  // thread (slice, lane) finishes output n = slice of column m
-  if (slice < N && m < M) {
+  // thread t finishes output (m = t % 8, n = t / 8)
+  const int on = threadIdx.x >> 3, om = blockIdx.x * 8 + (threadIdx.x & 7);
+  if (on < N && om < M) {
     float v = 0.f;
 #pragma unroll
-    for (int q = 0; q < SK_TN_SLICES; ++q) v += red[q][slice][lane];
-    float* cptr = C + (int64_t)m * ldc + slice;
-    *cptr = sk_epilogue(v, bias, slice, cptr, relu, accumulate);
+    for (int q = 0; q < SK_TN_WARPS; ++q) v += red[q][on][threadIdx.x & 7];
+    float* cptr = C + (int64_t)om * ldc + on;
+    *cptr = sk_epilogue(v, bias, on, cptr, relu, accumulate);
   }
 }
 
@@ -288,7 +297,7 @@ static bool gemm_skinny(int ta, int tb, int64_t M, int64_t N, int64_t K, const f
       skinny_nn_kernel<8><<<(unsigned)M, 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
                                                              accumulate);
   } else if (N <= SK_MAXN && ta && !tb && K >= 64) {
-    skinny_tn_kernel<<<(unsigned)((M + 31) / 32), 32 * SK_TN_SLICES, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
+    skinny_tn_kernel<<<(unsigned)((M + 7) / 8), 32 * SK_TN_WARPS, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
                                                                     accumulate);
   } else if (K <= SK_MAXN && !ta && tb && M * N >= 4096) {
     skinny_nt_kernel<<<grid_for(M * N, 256), 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,

@@ -589,6 +589,29 @@ __global__ void __launch_bounds__(L_THREADS) multi_update_kernel(const __grid_co
     bc1 = (float)(1.0 - pow((double)d.h[1], t));
     bc2 = (float)(1.0 - pow((double)d.h[2], t));
   }
+  // whole tile, every stream 16-byte aligned: two float4 per thread and stream, all loads issued first
+  const uintptr_t align_bits = (uintptr_t)w | (uintptr_t)dw | (uintptr_t)s1 | (uintptr_t)s2 | (uintptr_t)wo | (uintptr_t)s1o |
+                               (uintptr_t)s2o;
+  if (hi - lo == MU_TILE && (align_bits & 15u) == 0 && d.rule <= 1) {
+    const int64_t i0 = lo + 4 * threadIdx.x, i1 = i0 + 4 * L_THREADS;
+    const float4 g0 = *reinterpret_cast<const float4*>(dw + i0), g1 = *reinterpret_cast<const float4*>(dw + i1);
+    const float4 w0 = *reinterpret_cast<const float4*>(w + i0), w1 = *reinterpret_cast<const float4*>(w + i1);
+    if (d.rule == 0) {
+      *reinterpret_cast<float4*>(wo + i0) = make_float4(w0.x - lr * g0.x, w0.y - lr * g0.y, w0.z - lr * g0.z, w0.w - lr * g0.w);
+      *reinterpret_cast<float4*>(wo + i1) = make_float4(w1.x - lr * g1.x, w1.y - lr * g1.y, w1.z - lr * g1.z, w1.w - lr * g1.w);
+    } else {
+      float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+      if (s1) { v0 = *reinterpret_cast<const float4*>(s1 + i0); v1 = *reinterpret_cast<const float4*>(s1 + i1); }
+      const float mu = d.h[1];
+      v0 = make_float4(v0.x * mu - g0.x * lr, v0.y * mu - g0.y * lr, v0.z * mu - g0.z * lr, v0.w * mu - g0.w * lr);
+      v1 = make_float4(v1.x * mu - g1.x * lr, v1.y * mu - g1.y * lr, v1.z * mu - g1.z * lr, v1.w * mu - g1.w * lr);
+      *reinterpret_cast<float4*>(s1o + i0) = v0;
+      *reinterpret_cast<float4*>(s1o + i1) = v1;
+      *reinterpret_cast<float4*>(wo + i0) = make_float4(w0.x + v0.x, w0.y + v0.y, w0.z + v0.z, w0.w + v0.w);
+      *reinterpret_cast<float4*>(wo + i1) = make_float4(w1.x + v1.x, w1.y + v1.y, w1.z + v1.z, w1.w + v1.w);
+    }
+    return;
+  }
   for (int64_t i = lo + threadIdx.x; i < hi; i += L_THREADS) {
     const float g = dw[i];
     if (d.rule == 0) {
