@@ -285,6 +285,131 @@ __global__ void __launch_bounds__(L_THREADS) bn_bwd_apply_kernel(const float* __
   }
 }
 
+// ---- small batches: statistics + apply in ONE kernel ("slab" kernels) ----------------------
+// (1024, 512) is 2 MB: the two-kernel path above costs two launches (~4-6 us each inside a step
+// graph) for ~1 us of memory time.  Here a block owns 8 columns (one 32-byte sector of every row)
+// and keeps its whole N x 8 slab in registers: thread = (row lane 0..127, column half), up to
+// SLAB_RPT rows each.  Sums: per thread, then 16 row lanes by shuffle, then 8 warps through shared
+// memory -- a fixed order, so results are deterministic.
+constexpr int SLAB_RPT = 8;                    // rows per thread: N <= 128 * SLAB_RPT
+__device__ __forceinline__ void slab_block_sums(float (&a)[4], float (&b)[4], float (&ta)[4], float (&tb)[4]) {
+  __shared__ float red[8][2][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, half = threadIdx.x & 1;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+#pragma unroll
+    for (int o = 2; o < 32; o <<= 1) { a[k] += __shfl_xor_sync(0xffffffffu, a[k], o); b[k] += __shfl_xor_sync(0xffffffffu, b[k], o); }
+    if (lane < 2) { red[warp][half][k] = a[k]; red[warp][half][4 + k] = b[k]; }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float x = 0.f, y = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { x += red[w][half][k]; y += red[w][half][4 + k]; }
+    ta[k] = x; tb[k] = y;
+  }
+}
+
+__global__ void __launch_bounds__(L_THREADS) bn_slab_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                                const float* __restrict__ beta, const float* __restrict__ rmean,
+                                                                const float* __restrict__ rvar, float* __restrict__ out,
+                                                                float* __restrict__ new_rmean, float* __restrict__ new_rvar,
+                                                                float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                                                                int N, int64_t D, float eps, float momentum) {
+  const int half = threadIdx.x & 1, rl = threadIdx.x >> 1;
+  const int64_t col = (int64_t)blockIdx.x * 8 + 4 * half;
+  float4 v[SLAB_RPT];
+#pragma unroll
+  for (int i = 0; i < SLAB_RPT; ++i) {
+    const int r = rl + 128 * i;
+    if (r < N) v[i] = *reinterpret_cast<const float4*>(x + (int64_t)r * D + col);
+  }
+  const float4 x0 = *reinterpret_cast<const float4*>(x + col);       // shift: no cancellation blow-up
+  float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f}, s1[4], s2[4];
+#pragma unroll
+  for (int i = 0; i < SLAB_RPT; ++i) {
+    if (rl + 128 * i < N) {
+      const float d0 = v[i].x - x0.x, d1 = v[i].y - x0.y, d2 = v[i].z - x0.z, d3 = v[i].w - x0.w;
+      a[0] += d0; a[1] += d1; a[2] += d2; a[3] += d3;
+      b[0] += d0 * d0; b[1] += d1 * d1; b[2] += d2 * d2; b[3] += d3 * d3;
+    }
+  }
+  slab_block_sums(a, b, s1, s2);
+  const float x0v[4] = {x0.x, x0.y, x0.z, x0.w};
+  float sc[4], sh[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float dm = s1[k] / (float)N;
+    float var = fmaxf(s2[k] / (float)N - dm * dm, 0.f);               // biased variance (layers.py:103)
+    const float mean = x0v[k] + dm, inv = 1.0f / sqrtf(var + eps);
+    sc[k] = gamma[col + k] * inv;
+    sh[k] = beta[col + k] - mean * sc[k];
+    if (rl == 0) {
+      save_mean[col + k] = mean;
+      save_invstd[col + k] = inv;
+      new_rmean[col + k] = momentum * rmean[col + k] + (1.0f - momentum) * mean;
+      new_rvar[col + k] = momentum * rvar[col + k] + (1.0f - momentum) * var;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < SLAB_RPT; ++i) {
+    const int r = rl + 128 * i;
+    if (r < N)
+      *reinterpret_cast<float4*>(out + (int64_t)r * D + col) =
+          make_float4(fmaf(v[i].x, sc[0], sh[0]), fmaf(v[i].y, sc[1], sh[1]), fmaf(v[i].z, sc[2], sh[2]), fmaf(v[i].w, sc[3], sh[3]));
+  }
+}
+
+__global__ void __launch_bounds__(L_THREADS) bn_slab_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                                const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                                const float* __restrict__ invstd, float* __restrict__ dx,
+                                                                float* __restrict__ dgamma, float* __restrict__ dbeta, int N,
+                                                                int64_t D) {
+  const int half = threadIdx.x & 1, rl = threadIdx.x >> 1;
+  const int64_t col = (int64_t)blockIdx.x * 8 + 4 * half;
+  float4 xh[SLAB_RPT], g[SLAB_RPT];
+  const float4 mu = *reinterpret_cast<const float4*>(mean + col), iv = *reinterpret_cast<const float4*>(invstd + col);
+#pragma unroll
+  for (int i = 0; i < SLAB_RPT; ++i) {
+    const int r = rl + 128 * i;
+    if (r < N) {
+      xh[i] = *reinterpret_cast<const float4*>(x + (int64_t)r * D + col);
+      g[i] = *reinterpret_cast<const float4*>(dy + (int64_t)r * D + col);
+    }
+  }
+  float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f}, s1[4], s2[4];
+#pragma unroll
+  for (int i = 0; i < SLAB_RPT; ++i) {
+    if (rl + 128 * i < N) {
+      xh[i] = make_float4((xh[i].x - mu.x) * iv.x, (xh[i].y - mu.y) * iv.y, (xh[i].z - mu.z) * iv.z, (xh[i].w - mu.w) * iv.w);
+      a[0] += g[i].x; a[1] += g[i].y; a[2] += g[i].z; a[3] += g[i].w;
+      b[0] += g[i].x * xh[i].x; b[1] += g[i].y * xh[i].y; b[2] += g[i].z * xh[i].z; b[3] += g[i].w * xh[i].w;
+    }
+  }
+  slab_block_sums(a, b, s1, s2);
+  const float ivv[4] = {iv.x, iv.y, iv.z, iv.w};
+  float k1[4], k2[4], k3[4];                       // dx = k1 * (dy - k2 - xhat * k3)
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (rl == 0) { dbeta[col + k] = s1[k]; dgamma[col + k] = s2[k]; }
+    k1[k] = gamma[col + k] * ivv[k];
+    k2[k] = s1[k] / (float)N;
+    k3[k] = s2[k] / (float)N;
+  }
+#pragma unroll
+  for (int i = 0; i < SLAB_RPT; ++i) {
+    const int r = rl + 128 * i;
+    if (r < N)
+      *reinterpret_cast<float4*>(dx + (int64_t)r * D + col) =
+          make_float4(k1[0] * (g[i].x - k2[0] - xh[i].x * k3[0]), k1[1] * (g[i].y - k2[1] - xh[i].y * k3[1]),
+                      k1[2] * (g[i].z - k2[2] - xh[i].z * k3[2]), k1[3] * (g[i].w - k2[3] - xh[i].w * k3[3]));
+  }
+}
+static bool bn_slab_ok(int64_t N, int64_t D, bool aligned) {
+  return aligned && N <= 128 * SLAB_RPT && (D % 8) == 0 && N * D <= (1 << 20);
+}
+
 template <int VEC>
 __global__ void __launch_bounds__(L_THREADS) bn_test_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, const float* __restrict__ rmean,
@@ -445,6 +570,12 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
                            const float* running_var, float* out, float* new_running_mean, float* new_running_var,
                            float* save_mean, float* save_invstd, int64_t N, int64_t D, float eps, float momentum) {
   MC_REQUIRE(N > 0 && D > 0, "empty batch");
+  if (bn_slab_ok(N, D, aligned16(x) && aligned16(out))) {
+    bn_slab_fwd_kernel<<<(unsigned)(D / 8), L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, out, new_running_mean,
+                                                                     new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum);
+    MC_LAUNCHED();
+    return 0;
+  }
   const BnTiling t = bn_tiling(aligned16(x) && aligned16(out) && aligned16(gamma) && aligned16(beta), N, D);
   float* part = nullptr;
   MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * t.chunks * 2 * D, stream()));
@@ -470,6 +601,11 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
 int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma, const float* save_mean,
                            const float* save_invstd, float* dx, float* dgamma, float* dbeta, int64_t N, int64_t D) {
   MC_REQUIRE(N > 0 && D > 0, "empty batch");
+  if (bn_slab_ok(N, D, aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(save_mean) && aligned16(save_invstd))) {
+    bn_slab_bwd_kernel<<<(unsigned)(D / 8), L_THREADS, 0, stream()>>>(x, dy, gamma, save_mean, save_invstd, dx, dgamma, dbeta, (int)N, D);
+    MC_LAUNCHED();
+    return 0;
+  }
   const BnTiling t = bn_tiling(aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(gamma), N, D);
   float* part = nullptr;
   MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * t.chunks * 2 * D, stream()));
