@@ -79,6 +79,48 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_rows_warp_kernel(const flo
   }
 }
 
+// Small column reductions (the bias gradient of a (1024, 512) layer is 2 MB) in ONE launch: a block
+// owns 8 columns (one 32-byte sector per row), thread = (row lane 0..127, column half); four rows
+// in flight per thread; 16 row lanes combine by shuffle, the 8 warps through shared memory, in a
+// fixed order.  The split + second-pass path below costs two launches for ~1 us of memory time.
+template <class Op>
+__global__ void __launch_bounds__(RED_THREADS) reduce_cols_slab_kernel(const float* __restrict__ x, float* __restrict__ out,
+                                                                       int64_t red, int64_t inner) {
+  __shared__ float sm[8][2][4];
+  Op op;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, half = threadIdx.x & 1, rl = threadIdx.x >> 1;
+  const int64_t col = (int64_t)blockIdx.x * 8 + 4 * half;
+  const float* __restrict__ p = x + (int64_t)blockIdx.y * red * inner + col;
+  float acc[4] = {Op::identity(), Op::identity(), Op::identity(), Op::identity()};
+  int64_t r = rl;
+  for (; r + 384 < red; r += 512) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p + r * inner));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(p + (r + 128) * inner));
+    const float4 c = __ldg(reinterpret_cast<const float4*>(p + (r + 256) * inner));
+    const float4 d = __ldg(reinterpret_cast<const float4*>(p + (r + 384) * inner));
+    acc[0] = op(acc[0], op(op(a.x, b.x), op(c.x, d.x))); acc[1] = op(acc[1], op(op(a.y, b.y), op(c.y, d.y)));
+    acc[2] = op(acc[2], op(op(a.z, b.z), op(c.z, d.z))); acc[3] = op(acc[3], op(op(a.w, b.w), op(c.w, d.w)));
+  }
+  for (; r < red; r += 128) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p + r * inner));
+    acc[0] = op(acc[0], a.x); acc[1] = op(acc[1], a.y); acc[2] = op(acc[2], a.z); acc[3] = op(acc[3], a.w);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+#pragma unroll
+    for (int o = 2; o < 32; o <<= 1) acc[k] = op(acc[k], __shfl_xor_sync(0xffffffffu, acc[k], o));
+    if (lane < 2) sm[warp][half][k] = acc[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    const int h = threadIdx.x >> 2, k = threadIdx.x & 3;
+    float v = sm[0][h][k];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) v = op(v, sm[w][h][k]);
+    out[(int64_t)blockIdx.y * inner + (int64_t)blockIdx.x * 8 + threadIdx.x] = v;
+  }
+}
+
 // Column reduction: block = 32 (x) * 8 (y) threads; each x-thread owns VEC columns.
 // grid = (col_tiles, splits, outer).  out index: ((o*splits + s) * inner + col).
 template <class Op, int VEC>
@@ -167,6 +209,12 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
     return rc;
   }
   // ---- column reduction ----
+  if ((inner % 8) == 0 && aligned16(x) && red >= 128 && red * inner <= (1 << 20) && outer <= 65535) {
+    dim3 grid((unsigned)(inner / 8), (unsigned)outer);
+    reduce_cols_slab_kernel<Op><<<grid, RED_THREADS, 0, stream()>>>(x, out, red, inner);
+    MC_LAUNCHED();
+    return 0;
+  }
   const bool vec = (inner % 4 == 0) && aligned16(x);
   const int vecw = vec ? 4 : 1;
   const int64_t col_tiles = (inner + 32 * vecw - 1) / (32 * vecw);
