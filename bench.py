@@ -265,6 +265,12 @@ def _work_of(name, a):
         if name == 'mc_lstm_cell_bwd':
             N, H = _i(a[7]), _i(a[8])
             return 0.0, 4.0 * N * H * (4 + 2 + 2 + 4 + 1)
+        if name in ('mc_lstm_seq_fwd', 'mc_lstm_seq_bwd'):
+            # per time step: the recurrent GEMM (N,H)x(H,4H) [bwd: (N,4H)x(4H,H)] with Wh read once, plus the
+            # gate kernel's operands (fwd: a, c in; h, c, gates out; bwd: gates, c, c', dh, dc in; da, dc, dh out)
+            T, N, H = _i(a[5]), _i(a[6]), _i(a[7])
+            per_nh = 12 if name == 'mc_lstm_seq_fwd' else 14
+            return T * 2.0 * N * H * 4 * H, T * 4.0 * (per_nh * N * H + 4 * H * H)
     except Exception:  # pylint: disable=broad-except
         pass
     return 0.0, 0.0
@@ -366,9 +372,20 @@ def run_b200(args):
 
     def step_e2e(_i):
         solver._step(next(hb))  # pylint: disable=protected-access
-        return float(solver.loss_history[-1])          # D2H read of the step's result
+        # D2H read of a step's result, every step: each loss travels to pinned host memory behind its
+        # step (mc_readback_begin, third stream); the host reads it ONE STEP BEHIND, i.e. it waits for
+        # step i-1 while step i runs (the reference blocks on step i itself, solver.py:187)
+        hist = solver.loss_history
+        return float(hist[-2]) if len(hist) >= 2 else None
 
-    def timed(step_fn, steps, warmup):
+    def step_e2e_blocking(_i):
+        solver._step(next(hb))  # pylint: disable=protected-access
+        return float(solver.loss_history[-1])          # the reference's pattern: wait for this very step
+
+    def finish_e2e():
+        return float(solver.loss_history[-1])          # the last step's loss, inside the timed region
+
+    def timed(step_fn, steps, warmup, finish=None):
         for i in range(warmup):
             step_fn(i)
         solver.loss_history = []
@@ -384,6 +401,8 @@ def run_b200(args):
         lib.mc_event_record(e0)
         for i in range(steps):
             step_fn(warmup + i)
+        if finish is not None:
+            finish()
         lib.mc_event_record(e1)
         lib.mc_sync()
         parallel.barrier()
@@ -397,7 +416,8 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     dev_ms, launches, dev_wall = timed(step_device, args.steps, args.warmup)
-    e2e_ms, _, e2e_wall = timed(step_e2e, args.steps, args.warmup)
+    e2e_ms, _, e2e_wall = timed(step_e2e, args.steps, args.warmup, finish=finish_e2e)
+    e2e_blocking_ms, _, _ = timed(step_e2e_blocking, args.steps, args.warmup)
     clocks = sampler.stop() if rank == 0 else None
     last_loss = float(solver.loss_history[-1])
     graph_info = None
@@ -491,7 +511,9 @@ def run_b200(args):
                        'l2': '%d distinct batches/rank (%.0f MB) cycled, larger than the 126 MB L2' % (
                            nbatch, nbatch * in_bytes / 1e6)},
             'e2e': {'value': round(e2e_value, 1), 'unit': 'samples/s', 'h2d_bytes_per_step': int(in_bytes),
-                    'd2h_bytes_per_step': 4, 'ms_per_step': round(e2e_ms / args.steps, 4)},
+                    'd2h_bytes_per_step': 4, 'ms_per_step': round(e2e_ms / args.steps, 4),
+                    'loss_read': 'every step, one step behind its launch (pinned readback ring, third stream)',
+                    'ms_per_step_blocking_read': round(e2e_blocking_ms / args.steps, 4)},
             'gpu_launches': int(launches), 'launches_per_step': round(launches / args.steps, 1),
             'step_graph': graph_info,
             'wall_ms_per_step': round(dev_wall / args.steps, 4), 'final_loss': last_loss,

@@ -63,6 +63,13 @@ int mc_memset(void* dst_dev, int byte, size_t nbytes);
 int mc_prefetch_h2d(void* dst_dev, const void* src_host, size_t nbytes);
 int mc_prefetch_acquire(void);
 int mc_prefetch_release(void);
+/* Deferred read of a small device value (<= 64 bytes) -- replaces the blocking loss read of
+ * minpy/nn/solver.py:187 (`loss.asnumpy()` every step): `begin` enqueues a device->host copy into a
+ * pinned ring slot on a third stream, ordered after the compute work enqueued so far; `wait` blocks
+ * on that copy alone (not on later compute work) and copies the value out.  A ticket is valid for
+ * the next 256 begins; `wait` on an older ticket returns status 4. */
+int mc_readback_begin(const void* src_dev, size_t nbytes, uint64_t* ticket);
+int mc_readback_wait(uint64_t ticket, void* dst_host, size_t nbytes);
 /* CUDA events on the current stream (bench timing). */
 int mc_event_create(void** ev);
 int mc_event_record(void* ev);
@@ -266,6 +273,18 @@ int mc_lstm_cell_fwd(const float* a, const float* prev_c, float* next_h, float* 
 int mc_lstm_cell_bwd(const float* gates, const float* prev_c, const float* next_c,
                      const float* dnext_h, const float* dnext_c /* may be NULL */,
                      float* da /* (N,4H) */, float* dprev_c, int64_t N, int64_t H);
+/* lstm_temporal of nn/layers.py:383-420 on TIME-MAJOR buffers, the whole loop over t in one call
+ * (the reference issues 26 primitive dispatches + a slice + an append per step from Python).
+ *   fwd: A (T,N,4H) holds x_t.Wx + b on entry; hbuf / cbuf (T+1,N,H) hold h0 / c0 in slot 0 and receive
+ *        h_t / c_t in slot t+1; gates (T,N,4H) receives i,f,o,g.  Per step: the K-sliced GEMM
+ *        h_{t-1}.Wh leaves raw partials, the gate kernel adds them to A[t] while it reads it.
+ *   bwd: dH (T+1,N,H) holds the upstream gradient of h_t in slot t+1 (slot 0 zero) on entry; on exit
+ *        slot 0 is dL/dh0 and dA (T,N,4H) the pre-activation gradients (slots 1..T of dH are scratch).
+ * precision as mc_gemm (MC_GEMM_FP32 runs the exact-accumulate GEMM per step). */
+int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* gates,
+                    int64_t T, int64_t N, int64_t H, int precision);
+int mc_lstm_seq_bwd(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA,
+                    int64_t T, int64_t N, int64_t H, int precision);
 
 /* --------------------------------------------------------------- nn.optim ---- */
 /* Update rules of nn/optim.py:33-141; outputs may alias inputs. */

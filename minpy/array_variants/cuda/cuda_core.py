@@ -671,11 +671,9 @@ def fused_lstm_temporal(x, h0, Wx, Wh, b):
     lib.mc_memcpy_d2d(hbuf.ptr, h0.ptr, 4 * N * H)
     lib.mc_memset(cbuf.ptr, 0, 4 * N * H)
     sH, sA = 4 * N * H, 4 * N * 4 * H
-    for t in range(T):
-        a_t = A.ptr + t * sA
-        lib.mc_gemm(0, 0, N, 4 * H, H, hbuf.ptr + t * sH, H, Wh.ptr, 4 * H, a_t, 4 * H, None, 0, 1, prec)
-        lib.mc_lstm_cell_fwd(a_t, cbuf.ptr + t * sH, hbuf.ptr + (t + 1) * sH, cbuf.ptr + (t + 1) * sH,
-                             gates.ptr + t * sA, N, H)
+    # the loop over t runs in the library (csrc/lstm.cu): per step one K-sliced GEMM h_{t-1}.Wh whose
+    # partials the gate kernel adds while reading a_t -- two launches, no split-K combine pass
+    lib.mc_lstm_seq_fwd(A.ptr, Wh.ptr, hbuf.ptr, cbuf.ptr, gates.ptr, T, N, H, prec)
     hs = ops.transpose(_view(hbuf, sH, (T, N, H)), (1, 0, 2))
     hs._saved = (x_tm, hbuf, cbuf, gates)  # pylint: disable=protected-access
     return hs
@@ -701,12 +699,7 @@ def _lstm_temporal_vjp(ans, x, h0, Wx, Wh, b):
         lib.mc_memcpy_d2d(dH.ptr + sH, g_tm.ptr, T * sH)
         del g_tm
         dA = CudaArray.empty((T * N, 4 * H))
-        dc = [CudaArray.empty((N, H)), CudaArray.empty((N, H))]
-        for t in range(T - 1, -1, -1):
-            dnext_c = dc[(t + 1) & 1].ptr if t < T - 1 else None
-            lib.mc_lstm_cell_bwd(gates.ptr + t * sA, cbuf.ptr + t * sH, cbuf.ptr + (t + 1) * sH, dH.ptr + (t + 1) * sH,
-                                 dnext_c, dA.ptr + t * sA, dc[t & 1].ptr, N, H)
-            lib.mc_gemm(0, 1, N, H, 4 * H, dA.ptr + t * sA, 4 * H, Wh.ptr, 4 * H, dH.ptr + t * sH, H, None, 0, 1, prec)
+        lib.mc_lstm_seq_bwd(gates.ptr, cbuf.ptr, Wh.ptr, dH.ptr, dA.ptr, T, N, H, prec)
         h_prev = _view(hbuf, 0, (T * N, H))
         dWx = ops.gemm(x_tm, dA, trans_a=True)
         dWh = ops.gemm(h_prev, dA, trans_a=True)

@@ -231,16 +231,21 @@ class NDArrayIter(DataIter):
         return out, pad
 
     def _next_prefetched(self):
-        if not self.iter_next():
-            self._prefetch.forget()
-            raise StopIteration
         pf = self._prefetch
-        if pf.cursor != self.cursor:                       # first batch of an epoch (or after a reset)
+        if not self.iter_next():
+            if pf.cursor != 0:                             # keep a first batch already travelling (below)
+                pf.forget()
+            raise StopIteration
+        if pf.cursor != self.cursor:                       # first batch ever (or after an unusual reset)
             pf.start(self.cursor, *self._host_batch(self.cursor))
         arrays, pad = pf.take()
         nxt = self.cursor + self.batch_size
         if nxt < self.num_data:
             pf.start(nxt, *self._host_batch(nxt))
+        elif self.last_batch_handle != 'roll_over':
+            # last batch of the epoch: the order is fixed at construction (shuffle happens once, :173-177),
+            # so the next epoch's first batch is known -- send it now instead of stalling after reset()
+            pf.start(0, *self._host_batch(0))
         nd = len(self.data)
         return DataBatch(data=arrays[:nd], label=arrays[nd:], pad=pad, index=None)
 

@@ -19,6 +19,17 @@ from minpy.nn import optim, init
 # pylint: disable=no-member, too-many-instance-attributes
 
 
+def _begin_loss_readback(loss):
+    """Start the device->host copy of a step's loss right away, on the library's readback stream
+    (CudaArray.begin_readback): reading entry i of `loss_history` later waits for step i only, so a
+    training loop can print / log losses one step behind without draining the GPU."""
+    raw = getattr(loss, '_data', None)
+    if isinstance(raw, dict):
+        for value in raw.values():
+            if hasattr(value, 'begin_readback'):
+                value.begin_readback()
+
+
 class Solver(object):
     """Trains a `ModelBase` with mini-batch gradient descent.
 
@@ -112,6 +123,7 @@ class Solver(object):
         # the reference fetches the loss here (solver.py:187), a device->host sync every step;
         # the entry stays a lazy device scalar instead: float(entry) / entry.asnumpy() fetch it
         self.loss_history.append(loss)
+        _begin_loss_readback(loss)
         self._step_update(names, grads)
 
     def _step_grads(self, batch):

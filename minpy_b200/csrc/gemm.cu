@@ -773,13 +773,26 @@ static int* splitk_counters() {
 
 static bool tma_ok(const float* p, int64_t ld) { return aligned16(p) && (ld % 4 == 0); }
 
+// `ext_ws` non-null = raw-partials mode (gemm_tf32_partials below): the K slices land in
+// ext_ws[z][M][N], z < *splits_out <= max_splits, and nobody adds them up here.
 static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
-                     int64_t ldb, float* C, int64_t ldc, const float* bias, int relu, int accumulate) {
+                     int64_t ldb, float* C, int64_t ldc, const float* bias, int relu, int accumulate,
+                     float* ext_ws = nullptr, int max_splits = 0, int* splits_out = nullptr) {
   using namespace tc;
   static int force_bn = -1, min_kb = -1;
   if (force_bn < 0) { const char* e = getenv("MC_GEMM_BN"); force_bn = e ? atoi(e) : 0; }
   if (min_kb < 0) { const char* e = getenv("MC_GEMM_MIN_KB"); min_kb = e ? atoi(e) : 8; }
-  const int BN = force_bn ? force_bn : ((N > 64) ? 128 : 64);
+  // Tile width: 128 columns, except (measured, profiles/r1za gemm sweeps) for problems that are both few
+  // tiles and short in K -- there 64-column tiles double the CTAs without deepening split-K:
+  // (1024,512,512) 9.4 -> 8.2 us, (512,512,1024) 9.5 -> 8.3, (256,512,3072) 10.7 -> 9.5, (128,1024,4096)
+  // 11.0 -> 10.2; the large-K / many-tile shapes ((1024,512,3072) 13.9 vs 16.7 us) keep 128.
+  int BN = (N > 64) ? 128 : 64;
+  if (BN == 128) {
+    const int64_t tiles128 = ((M + BM - 1) / BM) * ((N + 127) / 128);
+    const int64_t kb = (K + BK - 1) / BK;
+    if (tiles128 <= 32 && kb >= 16 && tiles128 * kb <= 1024) BN = 64;
+  }
+  if (force_bn) BN = force_bn;
   CUtensorMap tmA, tmB;
   // A operand: op(A) is (M, K).  Stored (M,K) row-major -> K-major tile {BK x BM};
   // stored (K,M) (trans_a) -> MN-major: boxes of {32 (M) x BK (K)}.
@@ -798,6 +811,7 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     if (splits > maxs) splits = maxs;
     if (splits < 1) splits = 1;
   }
+  if (ext_ws && splits > max_splits) splits = max_splits;
   int kb_per = (num_kb + splits - 1) / splits;
   splits = (num_kb + kb_per - 1) / kb_per;
 
@@ -817,6 +831,12 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   // enables it for experiments.
   static int use_cluster = -1;
   if (use_cluster < 0) { const char* e = getenv("MC_GEMM_CLUSTER"); use_cluster = e ? atoi(e) : 0; }
+  if (ext_ws) {
+    if (splits > 1) p.ws = ext_ws;
+    else { p.C = ext_ws; p.ldc = N; p.bias = nullptr; p.relu = 0; p.accumulate = 0; }
+    *splits_out = splits;
+    return (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
+  }
   if (splits > 1 && use_cluster > 1) {
     int S = 2;
     while (S * 2 <= splits && S * 2 <= use_cluster && S * 2 <= 16) S *= 2;
@@ -844,6 +864,18 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   }
   if (p.ws) MC_CHECK(cudaFreeAsync(p.ws, stream()));
   return rc;
+}
+
+// The split-K GEMM without its combine pass, for consumers that add the slices themselves (the LSTM gate
+// kernels of lstm.cu read  a + sum_z ws[z]  and so save a launch and a round trip of the (N,4H) tile
+// per time step).  Returns 0 and *splits = 0 when the problem does not take the tensor-core path
+// (the caller then uses mc_gemm).
+int gemm_tf32_partials(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
+                       int64_t ldb, float* ws, int max_splits, int* splits) {
+  *splits = 0;
+  if (M <= 0 || N <= 0 || K <= 0 || max_splits < 1) return 0;
+  if (N <= 16 || K <= 16 || !(tma_ok(A, lda) && tma_ok(B, ldb) && (M >= 32 || N >= 32)) || !aligned16(ws) || (N & 3)) return 0;
+  return gemm_tf32(ta, tb, M, N, K, A, lda, B, ldb, nullptr, N, nullptr, 0, 0, ws, max_splits, splits);
 }
 
 }  // namespace mc

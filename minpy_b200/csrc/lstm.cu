@@ -1,0 +1,137 @@
+// lstm_temporal of nn/layers.py:383-420 as two native loops over time-major buffers.
+//
+// Per time step the reference runs lstm_step (layers.py:353-380): 2 dots, 4 slices, 3 sigmoids of 4
+// primitives each, 2 tanh, adds / muls = 26 dispatches forward and 32 VJP records backward.  Here a
+// step is TWO launches:
+//   forward   K-sliced tensor-core GEMM  h_{t-1} . Wh  ->  raw partials ws[z] (no combine pass)
+//             gate kernel reading  a_t + sum_z ws[z]  (a_t = x_t . Wx + b, computed for all steps at once)
+//   backward  gate-backward kernel reading  dH[t+1] + sum_z ws[z]  (ws = partials of the step after it)
+//             K-sliced GEMM  da_t . Wh^T  ->  ws
+// i.e. the split-K combine (a launch plus a write and a read of the (N,4H) / (N,H) tile per step;
+// 22% of the C5 step in profiles/r1z) is folded into the kernel that consumes the sum.
+#include "common.cuh"
+
+namespace mc {
+
+int gemm_tf32_partials(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
+                       int64_t ldb, float* ws, int max_splits, int* splits);   // gemm.cu
+
+constexpr int LS_THREADS = 256;
+constexpr int LS_MAX_SPLITS = 16;
+
+__device__ __forceinline__ float ls_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }  // layers.py:243
+
+// a (N,4H) + sum over `splits` slices of ws (each N*4H) -> gates i,f,o,g; c' = f*c + i*g; h' = o*tanh(c')
+__global__ void __launch_bounds__(LS_THREADS) lstm_fwd_part_kernel(const float* __restrict__ a, const float* __restrict__ ws,
+                                                                   int splits, const float* __restrict__ prev_c,
+                                                                   float* __restrict__ next_h, float* __restrict__ next_c,
+                                                                   float* __restrict__ gates, int64_t N, int64_t H) {
+  const int64_t n = N * H, slice = n * 4;
+  const int64_t stride = (int64_t)gridDim.x * LS_THREADS;
+  for (int64_t t = (int64_t)blockIdx.x * LS_THREADS + threadIdx.x; t < n; t += stride) {
+    const int64_t r = t / H, j = t % H;
+    const int64_t base = r * 4 * H + j;
+    float p0 = a[base], p1 = a[base + H], p2 = a[base + 2 * H], p3 = a[base + 3 * H];
+    for (int z = 0; z < splits; ++z) {      // slice order: deterministic
+      const float* __restrict__ w = ws + (int64_t)z * slice + base;
+      p0 += __ldcg(w); p1 += __ldcg(w + H); p2 += __ldcg(w + 2 * H); p3 += __ldcg(w + 3 * H);
+    }
+    const float i = ls_sigmoid(p0), f = ls_sigmoid(p1), o = ls_sigmoid(p2), g = tanhf(p3);
+    const float c = f * prev_c[t] + i * g;
+    next_c[t] = c;
+    next_h[t] = o * tanhf(c);
+    gates[base] = i; gates[base + H] = f; gates[base + 2 * H] = o; gates[base + 3 * H] = g;
+  }
+}
+
+// dh = dnext_h + sum over slices of ws (each N*H); the rest as lstm_bwd_kernel (layers.cu)
+__global__ void __launch_bounds__(LS_THREADS) lstm_bwd_part_kernel(const float* __restrict__ gates, const float* __restrict__ prev_c,
+                                                                   const float* __restrict__ next_c,
+                                                                   const float* __restrict__ dnext_h,
+                                                                   const float* __restrict__ ws, int splits,
+                                                                   const float* __restrict__ dnext_c, float* __restrict__ da,
+                                                                   float* __restrict__ dprev_c, int64_t N, int64_t H) {
+  const int64_t n = N * H;
+  const int64_t stride = (int64_t)gridDim.x * LS_THREADS;
+  for (int64_t t = (int64_t)blockIdx.x * LS_THREADS + threadIdx.x; t < n; t += stride) {
+    const int64_t r = t / H, j = t % H;
+    const int64_t base = r * 4 * H + j;
+    const float i = gates[base], f = gates[base + H], o = gates[base + 2 * H], g = gates[base + 3 * H];
+    const float tc = tanhf(next_c[t]);
+    float dh = dnext_h[t];
+    for (int z = 0; z < splits; ++z) dh += __ldcg(ws + (int64_t)z * n + t);
+    float dc = dh * o * (1.f - tc * tc);
+    if (dnext_c) dc += dnext_c[t];
+    da[base] = dc * g * i * (1.f - i);
+    da[base + H] = dc * prev_c[t] * f * (1.f - f);
+    da[base + 2 * H] = dh * tc * o * (1.f - o);
+    da[base + 3 * H] = dc * i * (1.f - g * g);
+    dprev_c[t] = dc * f;
+  }
+}
+
+}  // namespace mc
+
+using namespace mc;
+
+extern "C" {
+
+int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* gates, int64_t T, int64_t N, int64_t H,
+                    int precision) {
+  MC_REQUIRE(T >= 0 && N > 0 && H > 0, "bad extents");
+  const int64_t sH = N * H, sA = N * 4 * H;
+  float* ws = nullptr;
+  const bool try_partials = (precision == MC_GEMM_TF32);
+  if (try_partials) MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * LS_MAX_SPLITS * sA, stream()));
+  int rc = 0;
+  for (int64_t t = 0; t < T && rc == 0; ++t) {
+    float* a_t = A + t * sA;
+    int splits = 0;
+    if (try_partials) rc = gemm_tf32_partials(0, 0, N, 4 * H, H, hbuf + t * sH, H, Wh, 4 * H, ws, LS_MAX_SPLITS, &splits);
+    if (rc) break;
+    if (splits == 0) {   // exact-FP32 mode or a shape TMA cannot describe: the two public calls
+      rc = mc_gemm(0, 0, N, 4 * H, H, hbuf + t * sH, H, Wh, 4 * H, a_t, 4 * H, nullptr, 0, 1, precision);
+      if (rc) break;
+    }
+    lstm_fwd_part_kernel<<<grid_for(sH, LS_THREADS), LS_THREADS, 0, stream()>>>(
+        a_t, ws, splits, cbuf + t * sH, hbuf + (t + 1) * sH, cbuf + (t + 1) * sH, gates + t * sA, N, H);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("lstm_fwd_part_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; break; }
+    count_launch();
+  }
+  if (ws) MC_CHECK(cudaFreeAsync(ws, stream()));
+  return rc;
+}
+
+int mc_lstm_seq_bwd(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA, int64_t T, int64_t N,
+                    int64_t H, int precision) {
+  MC_REQUIRE(T >= 0 && N > 0 && H > 0, "bad extents");
+  const int64_t sH = N * H, sA = N * 4 * H;
+  float *ws = nullptr, *dc = nullptr;
+  const bool try_partials = (precision == MC_GEMM_TF32);
+  if (try_partials) MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * LS_MAX_SPLITS * sH, stream()));
+  MC_CHECK(cudaMallocAsync((void**)&dc, sizeof(float) * 2 * sH, stream()));
+  int rc = 0, pending = 0;
+  for (int64_t t = T - 1; t >= 0 && rc == 0; --t) {
+    const float* dnext_c = (t < T - 1) ? dc + ((t + 1) & 1) * sH : nullptr;
+    lstm_bwd_part_kernel<<<grid_for(sH, LS_THREADS), LS_THREADS, 0, stream()>>>(
+        gates + t * sA, cbuf + t * sH, cbuf + (t + 1) * sH, dH + (t + 1) * sH, ws, pending, dnext_c, dA + t * sA,
+        dc + (t & 1) * sH, N, H);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("lstm_bwd_part_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; break; }
+    count_launch();
+    pending = 0;
+    // dH[t] += da_t . Wh^T: left as partials for the next gate kernel, except the last one (dh0 is read
+    // by the caller, so it is combined in memory)
+    if (try_partials && t > 0) {
+      rc = gemm_tf32_partials(0, 1, N, H, 4 * H, dA + t * sA, 4 * H, Wh, 4 * H, ws, LS_MAX_SPLITS, &pending);
+      if (rc) break;
+    }
+    if (pending == 0) rc = mc_gemm(0, 1, N, H, 4 * H, dA + t * sA, 4 * H, Wh, 4 * H, dH + t * sH, H, nullptr, 0, 1, precision);
+  }
+  if (ws) MC_CHECK(cudaFreeAsync(ws, stream()));
+  MC_CHECK(cudaFreeAsync(dc, stream()));
+  return rc;
+}
+
+}  // extern "C"

@@ -170,6 +170,56 @@ int mc_prefetch_release(void) {
   return 0;
 }
 
+/* Deferred read of a small device value (the loss of a step, minpy/nn/solver.py:187 reads it with a
+ * blocking asnumpy()): the device->host copy runs on a third stream behind an event of the compute
+ * stream and lands in a pinned slot of a ring, so waiting for step i's loss does not wait for
+ * step i+1 that was enqueued after it.  A ticket stays valid until MC_READBACK_SLOTS later begins. */
+#define MC_READBACK_SLOTS 256
+#define MC_READBACK_BYTES 64
+static cudaStream_t g_rb_stream = nullptr;
+static char* g_rb_host = nullptr;
+static cudaEvent_t g_rb_ready[MC_READBACK_SLOTS], g_rb_done[MC_READBACK_SLOTS];
+static uint64_t g_rb_next = 0;
+
+int mc_readback_begin(const void* src_dev, size_t nbytes, uint64_t* ticket) {
+  MC_REQUIRE(nbytes > 0 && nbytes <= MC_READBACK_BYTES, "mc_readback_begin: 1..64 bytes");
+  MC_REQUIRE(!g_capturing, "mc_readback_begin inside a graph capture");
+  if (g_rb_stream == nullptr) {
+    MC_CHECK(cudaStreamCreateWithFlags(&g_rb_stream, cudaStreamNonBlocking));
+    MC_CHECK(cudaMallocHost((void**)&g_rb_host, (size_t)MC_READBACK_SLOTS * MC_READBACK_BYTES));
+    for (int i = 0; i < MC_READBACK_SLOTS; ++i) {
+      MC_CHECK(cudaEventCreateWithFlags(&g_rb_ready[i], cudaEventDisableTiming));
+      MC_CHECK(cudaEventCreateWithFlags(&g_rb_done[i], cudaEventDisableTiming));
+    }
+  }
+  const uint64_t t = g_rb_next++;
+  const int slot = (int)(t % MC_READBACK_SLOTS);
+  MC_CHECK(cudaEventRecord(g_rb_ready[slot], g_stream));
+  MC_CHECK(cudaStreamWaitEvent(g_rb_stream, g_rb_ready[slot], 0));
+  MC_CHECK(cudaMemcpyAsync(g_rb_host + (size_t)slot * MC_READBACK_BYTES, src_dev, nbytes, cudaMemcpyDeviceToHost,
+                           g_rb_stream));
+  MC_CHECK(cudaEventRecord(g_rb_done[slot], g_rb_stream));
+  *ticket = t;
+  return 0;
+}
+/* Blocks until the copy of `ticket` has landed, then copies it out.  Status 4: the ticket's slot has
+ * been reused (the caller falls back to a blocking read of the device value). */
+int mc_readback_wait(uint64_t ticket, void* dst_host, size_t nbytes) {
+  MC_REQUIRE(nbytes > 0 && nbytes <= MC_READBACK_BYTES, "mc_readback_wait: 1..64 bytes");
+  if (ticket >= g_rb_next || g_rb_next - ticket > MC_READBACK_SLOTS) {
+    set_error("mc_readback_wait: ticket %llu is no longer in the ring", (unsigned long long)ticket);
+    return 4;
+  }
+  const int slot = (int)(ticket % MC_READBACK_SLOTS);
+  MC_CHECK(cudaEventSynchronize(g_rb_done[slot]));
+  if (g_rb_next - ticket > MC_READBACK_SLOTS) {      // overwritten while we waited
+    set_error("mc_readback_wait: ticket %llu was overwritten", (unsigned long long)ticket);
+    return 4;
+  }
+  memcpy(dst_host, g_rb_host + (size_t)slot * MC_READBACK_BYTES, nbytes);
+  return 0;
+}
+
 int mc_event_create(void** ev) {
   cudaEvent_t e;
   MC_CHECK(cudaEventCreate(&e));

@@ -133,7 +133,7 @@ def _prod(shape):
 
 class CudaArray(object):
     """Dense row-major device array (float32 / int32 / int64)."""
-    __slots__ = ('buf', 'ptr', 'shape', 'size', 'dtype', '_saved', '_tag', '__weakref__')
+    __slots__ = ('buf', 'ptr', 'shape', 'size', 'dtype', '_saved', '_tag', '_readback', '__weakref__')
     __array_priority__ = 200.0
 
     def __init__(self, buf, ptr, shape, dtype=_F32):
@@ -144,6 +144,7 @@ class CudaArray(object):
         self.dtype = dtype
         self._saved = None    # forward state a fused primitive keeps for its VJP
         self._tag = None      # ('arange', n) for index vectors known to be 0..n-1
+        self._readback = None  # ticket of a device->host copy already in flight (begin_readback)
 
     # ---- construction -------------------------------------------------------------
     @staticmethod
@@ -189,8 +190,23 @@ class CudaArray(object):
     def context(self):
         return ('gpu', _state['device'])
 
+    def begin_readback(self):
+        """Start copying a small value (<= 64 bytes, never written again) to the host on the
+        library's readback stream; a later asnumpy() / float() waits for that copy only, not for
+        compute work enqueued after this call (the Solver does this for every step's loss)."""
+        if 0 < self.nbytes <= 64:
+            ticket = ctypes.c_uint64()
+            get_lib().mc_readback_begin(self.ptr, self.nbytes, ctypes.byref(ticket))
+            self._readback = ticket.value
+        return self
+
     def asnumpy(self):
         out = np.empty(self.shape, dtype=self.dtype)
+        if self._readback is not None:
+            lib = get_lib()
+            if lib.mc_readback_wait.raw(self._readback, out.ctypes.data, self.nbytes) == 0:
+                return out
+            self._readback = None     # the ring moved on (status 4): blocking read below
         get_lib().mc_memcpy_d2h(out.ctypes.data, self.ptr, self.nbytes)
         return out
 

@@ -263,6 +263,7 @@ class StepGraph(object):
         self.replays += 1
         keep = CudaArray.empty(())
         lib.mc_memcpy_d2d(keep.ptr, self.loss_raw.ptr, 4)
+        keep.begin_readback()          # the loss travels to the host behind this step, on a third stream
         self.solver.loss_history.append(marray.wrap(keep))
 
     # ---- the step -------------------------------------------------------------------------

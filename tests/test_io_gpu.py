@@ -15,7 +15,7 @@ def test_prefetched_batches_equal_host_batches():
     Y = rng.randint(0, 10, size=70)
     plain = NDArrayIter(X, Y, batch_size=16, shuffle=False, num_parts=1, part_index=0)
     ahead = NDArrayIter(X, Y, batch_size=16, shuffle=False, num_parts=1, part_index=0, device_prefetch=True)
-    for _epoch in range(2):
+    for _epoch in range(3):
         plain.reset()
         ahead.reset()
         a_batches = []
@@ -29,6 +29,29 @@ def test_prefetched_batches_equal_host_batches():
             assert ax.dtype == np.float32 and ax.shape == px.shape
             assert np.array_equal(ax, px.astype(np.float32))
             assert np.array_equal(ay, py)
+        # the next epoch's first batch is already on its way when the epoch ends
+        assert ahead._prefetch.cursor == 0 and ahead._prefetch.pending is not None
+
+
+def test_prefetch_roll_over_does_not_speculate():
+    """'roll_over' starts the next epoch at a data-dependent cursor: no batch is sent ahead across
+    the epoch boundary, and the batches still equal the plain iterator's."""
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    from minpy.nn.io import NDArrayIter
+    rng = np.random.RandomState(1)
+    X = rng.randn(40, 5).astype(np.float32)
+    Y = rng.randint(0, 3, size=40)
+    kw = dict(batch_size=16, shuffle=False, num_parts=1, part_index=0, last_batch_handle='roll_over')
+    plain, ahead = NDArrayIter(X, Y, **kw), NDArrayIter(X, Y, device_prefetch=True, **kw)
+    for _epoch in range(3):
+        plain.reset()
+        ahead.reset()
+        a = [(b.data[0].asnumpy().copy(), b.label[0].asnumpy().copy()) for b in ahead]
+        p = [(b.data[0].asnumpy(), b.label[0].asnumpy()) for b in plain]
+        assert len(a) == len(p)
+        for (ax, ay), (px, py) in zip(a, p):
+            assert np.array_equal(ax, px) and np.array_equal(ay, py)
 
 
 def test_prefetch_feeds_the_step_graph():
