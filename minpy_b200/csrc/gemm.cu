@@ -805,7 +805,9 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   const int64_t tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int num_kb = (int)((K + BK - 1) / BK);
   int splits = 1;
-  if (tiles < sm_count() && num_kb >= 16) {
+  // K >= 1024 only: with 16..31 k-blocks the combine launch costs more than the second slice saves
+  // (profiles/r1za: (1024,512,512) 8.2 us split in two, 7.6 us whole)
+  if (tiles < sm_count() && num_kb >= 32) {
     splits = (int)(sm_count() / tiles);
     const int maxs = num_kb / min_kb;  // at least 8 k-blocks (K = 256) per slice
     if (splits > maxs) splits = maxs;

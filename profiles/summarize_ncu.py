@@ -63,9 +63,17 @@ def traffic(path, workload, family, calls):
     library calls of `family`, averaged per call -> profiles/traffic.json (read by bench.py)."""
     import json
     import os
-    out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    if path.endswith('.csv'):      # `ncu -i x.ncu-rep --page raw --csv` written on the GPU box (reports > 64 MiB stay there)
+        out = open(path).read()
+    else:
+        out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     hdr, units, data = rows[0], rows[1], rows[2:]
+    if len(sys.argv) > 6:          # optional: kernel-name regex and number of matching launches to keep
+        ki = hdr.index('Kernel Name')
+        data = [r for r in data if re.search(sys.argv[6], r[ki])]
+        if len(sys.argv) > 7:
+            data = data[:int(sys.argv[7])]
     scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
     total = 0.0
     for m in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
