@@ -248,6 +248,15 @@ int mc_allreduce_avg(float* buf, int64_t n);
 int mc_allreduce_sum(float* buf, int64_t n);
 int mc_broadcast(float* buf, int64_t n, int root);
 int mc_comm_destroy(void);
+/* Peer-memory window for the gradient bucket (one node, 2..8 ranks).  Every rank calls mc_p2p_create
+ * (cudaMalloc + two IPC handles, 128 bytes), the handles of all ranks travel through the rendezvous
+ * (world x 128 bytes, rank-major) into mc_p2p_connect.  From then on mc_allreduce_avg on a range inside
+ * the window runs the library's own two-shot all-reduce over NVLink peer loads (csrc/comm.cu) instead
+ * of ncclAllReduce; ranges elsewhere still go to NCCL.  mc_p2p_info: the window (NULL while inactive)
+ * and whether a cross-GPU barrier ever timed out (20 s; the results are then invalid). */
+int mc_p2p_create(int rank, int world, size_t bytes, void* handles128);
+int mc_p2p_connect(const void* all_handles);
+int mc_p2p_info(void** ptr, size_t* bytes, int* timed_out);
 
 /* ------------------------------------------------------------ nn.layers ------ */
 /* layers.batchnorm train mode, nn/layers.py:93-110: biased variance, returns updated

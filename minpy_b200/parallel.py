@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import ctypes
 import os
+import sys
 
 import numpy as np
 
@@ -73,6 +74,68 @@ def _init_native_comm(rank, world):
     dist.broadcast_object_list(box, src=0)
     lib.mc_comm_init(rank, world, ctypes.create_string_buffer(box[0], 128))
     _state['native'] = True
+    _init_p2p_window(rank, world)
+
+
+def _init_p2p_window(rank, world):
+    """Peer-memory window for the gradient bucket (csrc/comm.cu, two-shot all-reduce over NVLink peer
+    loads): every rank allocates it, the IPC handles travel through torch.distributed, and the window
+    is used only if EVERY rank could map every peer.  MINPY_P2P_ALLREDUCE: 'auto' (default) uses the
+    window at world size 2, where it is the faster exchange inside the step (mlp_c3 0.400 -> 0.384 ms,
+    profiles/r1z/n2); at 4 ranks it ties with NCCL in the step and loses alone (73 vs 52 us for 9.5 MB,
+    profiles/r1z/n4), so 3..8 ranks need an explicit '1'; '0' always keeps NCCL.
+    MINPY_P2P_MB sizes the window (default 64 MB, buckets beyond it go to NCCL)."""
+    _state['p2p'] = None
+    mode = os.environ.get('MINPY_P2P_ALLREDUCE', 'auto')
+    if world < 2 or world > 8 or mode == '0' or (mode != '1' and world != 2):
+        return
+    from .ops import L
+    lib = L()
+    dist = _dist()
+    nbytes = int(float(os.environ.get('MINPY_P2P_MB', '64')) * (1 << 20))
+    handles = ctypes.create_string_buffer(128)
+    ok, err = True, ''
+    try:
+        lib.mc_p2p_create(rank, world, nbytes, handles)
+    except Exception as exc:  # pylint: disable=broad-except
+        ok, err = False, str(exc)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (ok, handles.raw))
+    if not all(g[0] for g in gathered):
+        if rank == 0:
+            print('minpy_b200.parallel: peer-memory window unavailable (%s); gradients go through NCCL' % err,
+                  file=sys.stderr)
+        return
+    try:
+        lib.mc_p2p_connect(ctypes.create_string_buffer(b''.join(g[1] for g in gathered), 128 * world))
+    except Exception as exc:  # pylint: disable=broad-except
+        ok, err = False, str(exc)
+    flags = [None] * world
+    dist.all_gather_object(flags, ok)
+    if not all(flags):
+        # a rank that did connect must not use the window alone (the kernel's barriers need everyone):
+        # _state['p2p'] stays None on every rank, so no bucket is ever placed in the window
+        if rank == 0:
+            print('minpy_b200.parallel: peer mapping failed on a rank (%s); gradients go through NCCL' % err,
+                  file=sys.stderr)
+        return
+    ptr, size, bad = ctypes.c_void_p(), ctypes.c_size_t(), ctypes.c_int()
+    lib.mc_p2p_info(ctypes.byref(ptr), ctypes.byref(size), ctypes.byref(bad))
+    if ptr.value:
+        _state['p2p'] = (ptr.value, size.value)
+
+
+class _WindowBuffer(object):
+    """Stand-in for cuda_array._Buffer over the peer-memory window: owned by the library, never freed."""
+    __slots__ = ('ptr', 'nbytes', 'pool')
+
+    def __init__(self, ptr, nbytes):
+        self.ptr, self.nbytes, self.pool = ptr, nbytes, None
+
+
+def p2p_active():
+    """True when the gradient bucket is exchanged by the library's own peer-memory all-reduce."""
+    return _state.get('p2p') is not None
 
 
 def native_comm():
@@ -86,7 +149,7 @@ def shutdown():
     # process exit reclaims it.  mc_comm_destroy stays available for callers that own no graphs.
     if _state['world'] > 1 and _dist().is_initialized():
         _dist().destroy_process_group()
-    _state.update(initialised=False, world=1, rank=0, backend=None, flat=None, flat_t=None, native=False)
+    _state.update(initialised=False, world=1, rank=0, backend=None, flat=None, flat_t=None, native=False, p2p=None)
 
 
 def world_size():
@@ -166,7 +229,13 @@ def pack_gradients(grads):
     offs, total = _segments([ops._prod(s) if s is not None else 0 for s in shapes])  # pylint: disable=protected-access
     # a fresh flat buffer per call: the views handed back stay valid for as long as the
     # caller keeps them (the pool recycles the block as soon as they die)
-    flat = CudaArray.empty((total,))
+    window = _state.get('p2p')
+    if window is not None and 4 * total <= window[1] and _state['world'] > 1:
+        # the bucket lives in the peer-memory window (same offset on every rank): mc_allreduce_avg then
+        # runs the two-shot peer all-reduce.  The views stay valid until the next step packs again.
+        flat = CudaArray(_WindowBuffer(window[0], window[1]), window[0], (total,))
+    else:
+        flat = CudaArray.empty((total,))
     srcs, dsts, ns = [], [], []
     for r, off, shape in zip(raws, offs, shapes):
         if shape is None:

@@ -2,6 +2,7 @@
 import os, sys, ctypes
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
+os.environ.setdefault('MINPY_P2P_ALLREDUCE', '1')   # time the peer-memory window at any world size
 import minpy
 minpy.set_global_policy('only_cuda')
 from minpy_b200 import parallel
@@ -17,8 +18,16 @@ def elapsed(fn, reps):
     lib.mc_event_record(e1); lib.mc_sync()
     ms = ctypes.c_float(); lib.mc_event_elapsed_ms(e0, e1, ctypes.byref(ms))
     return ms.value / reps * 1e3
-for n in (113738, 1578506, 2372106, 4853888):
-    a = CudaArray.from_numpy(np.ones(n, np.float32))
+WINDOW = parallel._state.get('p2p')   # peer-memory window (two-shot all-reduce) or None
+cases = [(n, False) for n in (113738, 1578506, 2372106, 4853888)]
+if WINDOW is not None:
+    cases += [(n, True) for n in (113728, 1578496, 2372096, 4853888)]
+for n, in_window in cases:
+    if in_window:
+        a = CudaArray(parallel._WindowBuffer(*WINDOW), WINDOW[0], (n,))
+        lib.mc_fill(a.ptr, 1.0, n)
+    else:
+        a = CudaArray.from_numpy(np.ones(n, np.float32))
     for _ in range(5): lib.mc_allreduce_avg(a.ptr, n)
     eager = elapsed(lambda: lib.mc_allreduce_avg(a.ptr, n), 50)
     lib.mc_sync()
@@ -28,7 +37,7 @@ for n in (113738, 1578506, 2372106, 4853888):
     lib.mc_graph_launch(ex)
     graph = elapsed(lambda: lib.mc_graph_launch(ex), 10) / 10
     if parallel.rank() == 0:
-        print('world %d  n %8d (%.2f MB)  eager %7.1f us  in-graph %7.1f us  algbw %.0f GB/s' % (
-            world, n, 4 * n / 1e6, eager, graph, 4 * n / graph / 1e3), flush=True)
+        print('world %d  %-4s n %8d (%.2f MB)  eager %7.1f us  in-graph %7.1f us  algbw %.0f GB/s' % (
+            world, 'p2p' if in_window else 'nccl', n, 4 * n / 1e6, eager, graph, 4 * n / graph / 1e3), flush=True)
 parallel.barrier()
 parallel.shutdown()
