@@ -459,7 +459,10 @@ def run_b200(args):
             log('  %-26s calls/step %6.1f  us/call %8.2f  share %5.1f%%  %8.1f GB/s  %8.2f TFLOP/s' % (
                 name, f['calls'] / inst_steps, 1e3 * f['ms'] / f['calls'], 100 * f['ms'] / tot,
                 f['bytes'] / (f['ms'] * 1e-3) / 1e9 if f['ms'] else 0, f['flops'] / (f['ms'] * 1e-3) / 1e12 if f['ms'] else 0))
-        top_name, top = ranked[0]
+        # the roofline is about the dominant COMPUTE kernel: the collective's event time is mostly the wait
+        # for the slowest rank (it stays in kernel_families)
+        compute = [kv for kv in ranked if not kv[0].startswith(('mc_allreduce', 'mc_broadcast'))] or ranked
+        top_name, top = compute[0]
         # duration of the dominant family: its recorded calls of one step, replayed back to back from a
         # CUDA graph (the event pairs above include the host gap in front of every small kernel)
         rep = None if top_name.startswith(('mc_allreduce', 'mc_broadcast')) else timer.replay_family(top_name, inst_steps)
