@@ -9,6 +9,7 @@
 //             K-sliced GEMM  da_t . Wh^T  ->  ws
 // i.e. the split-K combine (a launch plus a write and a read of the (N,4H) / (N,H) tile per step;
 // 22% of the C5 step in profiles/r1z) is folded into the kernel that consumes the sum.
+#include <initializer_list>
 #include "common.cuh"
 
 namespace mc {
@@ -70,6 +71,87 @@ __global__ void __launch_bounds__(LS_THREADS) lstm_bwd_part_kernel(const float* 
   }
 }
 
+// 128-bit versions (H % 4 == 0, 16-byte aligned operands): four hidden units per thread, every operand a
+// float4 load/store, the slices unrolled by the compiler -- same arithmetic per element as the scalar
+// kernels above (which remain for odd H); the scalar versions ran at 0.9 TB/s on cold operands
+// (profiles/r1z/prof_lstm_c5.txt), i.e. they were latency-, not bandwidth-bound.
+constexpr int LS4_THREADS = 128;
+
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 ld4cg(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void add4(float4& a, float4 b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+
+__global__ void __launch_bounds__(LS4_THREADS) lstm_fwd_part4_kernel(const float* __restrict__ a, const float* __restrict__ ws,
+                                                                     int splits, const float* __restrict__ prev_c,
+                                                                     float* __restrict__ next_h, float* __restrict__ next_c,
+                                                                     float* __restrict__ gates, int64_t N, int64_t H) {
+  const int64_t H4 = H >> 2, n4 = N * H4, slice = N * H * 4;
+  const int64_t stride = (int64_t)gridDim.x * LS4_THREADS;
+  for (int64_t t = (int64_t)blockIdx.x * LS4_THREADS + threadIdx.x; t < n4; t += stride) {
+    const int64_t r = t / H4, j = (t - r * H4) << 2;
+    const int64_t base = r * 4 * H + j, cell = r * H + j;
+    float4 p0 = ld4(a + base), p1 = ld4(a + base + H), p2 = ld4(a + base + 2 * H), p3 = ld4(a + base + 3 * H);
+    const float4 c0 = ld4(prev_c + cell);
+    for (int z = 0; z < splits; ++z) {      // slice order: deterministic
+      const float* __restrict__ w = ws + (int64_t)z * slice + base;
+      const float4 q0 = ld4cg(w), q1 = ld4cg(w + H), q2 = ld4cg(w + 2 * H), q3 = ld4cg(w + 3 * H);
+      add4(p0, q0); add4(p1, q1); add4(p2, q2); add4(p3, q3);
+    }
+    float4 gi, gf, go, gg, c, h;
+#define LS_CELL(m)                                                                                   \
+    gi.m = ls_sigmoid(p0.m); gf.m = ls_sigmoid(p1.m); go.m = ls_sigmoid(p2.m); gg.m = tanhf(p3.m);    \
+    c.m = gf.m * c0.m + gi.m * gg.m; h.m = go.m * tanhf(c.m);
+    LS_CELL(x) LS_CELL(y) LS_CELL(z) LS_CELL(w)
+#undef LS_CELL
+    st4(next_c + cell, c);
+    st4(next_h + cell, h);
+    st4(gates + base, gi); st4(gates + base + H, gf); st4(gates + base + 2 * H, go); st4(gates + base + 3 * H, gg);
+  }
+}
+
+__global__ void __launch_bounds__(LS4_THREADS) lstm_bwd_part4_kernel(const float* __restrict__ gates, const float* __restrict__ prev_c,
+                                                                     const float* __restrict__ next_c,
+                                                                     const float* __restrict__ dnext_h,
+                                                                     const float* __restrict__ ws, int splits,
+                                                                     const float* __restrict__ dnext_c, float* __restrict__ da,
+                                                                     float* __restrict__ dprev_c, int64_t N, int64_t H) {
+  const int64_t H4 = H >> 2, n4 = N * H4, n = N * H;
+  const int64_t stride = (int64_t)gridDim.x * LS4_THREADS;
+  for (int64_t t = (int64_t)blockIdx.x * LS4_THREADS + threadIdx.x; t < n4; t += stride) {
+    const int64_t r = t / H4, j = (t - r * H4) << 2;
+    const int64_t base = r * 4 * H + j, cell = r * H + j;
+    const float4 gi = ld4(gates + base), gf = ld4(gates + base + H), go = ld4(gates + base + 2 * H), gg = ld4(gates + base + 3 * H);
+    const float4 cn = ld4(next_c + cell), cp = ld4(prev_c + cell);
+    float4 dh = ld4(dnext_h + cell);
+    for (int z = 0; z < splits; ++z) add4(dh, ld4cg(ws + (int64_t)z * n + cell));
+    float4 dcn = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (dnext_c) dcn = ld4(dnext_c + cell);
+    float4 d0, d1, d2, d3, dpc;
+#define LS_CELL(m)                                                                       \
+    {                                                                                    \
+      const float tc = tanhf(cn.m);                                                      \
+      float dc = dh.m * go.m * (1.f - tc * tc);                                          \
+      if (dnext_c) dc += dcn.m;                                                          \
+      d0.m = dc * gg.m * gi.m * (1.f - gi.m);                                            \
+      d1.m = dc * cp.m * gf.m * (1.f - gf.m);                                            \
+      d2.m = dh.m * tc * go.m * (1.f - go.m);                                            \
+      d3.m = dc * gi.m * (1.f - gg.m * gg.m);                                            \
+      dpc.m = dc * gf.m;                                                                 \
+    }
+    LS_CELL(x) LS_CELL(y) LS_CELL(z) LS_CELL(w)
+#undef LS_CELL
+    st4(da + base, d0); st4(da + base + H, d1); st4(da + base + 2 * H, d2); st4(da + base + 3 * H, d3);
+    st4(dprev_c + cell, dpc);
+  }
+}
+
+static inline bool ls_vec_ok(int64_t H, std::initializer_list<const void*> ptrs) {
+  if (H & 3) return false;
+  for (const void* p : ptrs) if (p && !aligned16(p)) return false;
+  return true;
+}
+
 }  // namespace mc
 
 using namespace mc;
@@ -84,6 +166,7 @@ int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* 
   const bool try_partials = (precision == MC_GEMM_TF32);
   if (try_partials) MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * LS_MAX_SPLITS * sA, stream()));
   int rc = 0;
+  const bool vec = ls_vec_ok(H, {A, ws, hbuf, cbuf, gates});
   for (int64_t t = 0; t < T && rc == 0; ++t) {
     float* a_t = A + t * sA;
     int splits = 0;
@@ -93,8 +176,12 @@ int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* 
       rc = mc_gemm(0, 0, N, 4 * H, H, hbuf + t * sH, H, Wh, 4 * H, a_t, 4 * H, nullptr, 0, 1, precision);
       if (rc) break;
     }
-    lstm_fwd_part_kernel<<<grid_for(sH, LS_THREADS), LS_THREADS, 0, stream()>>>(
-        a_t, ws, splits, cbuf + t * sH, hbuf + (t + 1) * sH, cbuf + (t + 1) * sH, gates + t * sA, N, H);
+    if (vec)
+      lstm_fwd_part4_kernel<<<grid_for(sH / 4, LS4_THREADS), LS4_THREADS, 0, stream()>>>(
+          a_t, ws, splits, cbuf + t * sH, hbuf + (t + 1) * sH, cbuf + (t + 1) * sH, gates + t * sA, N, H);
+    else
+      lstm_fwd_part_kernel<<<grid_for(sH, LS_THREADS), LS_THREADS, 0, stream()>>>(
+          a_t, ws, splits, cbuf + t * sH, hbuf + (t + 1) * sH, cbuf + (t + 1) * sH, gates + t * sA, N, H);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("lstm_fwd_part_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; break; }
     count_launch();
@@ -112,11 +199,17 @@ int mc_lstm_seq_bwd(const float* gates, const float* cbuf, const float* Wh, floa
   if (try_partials) MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * LS_MAX_SPLITS * sH, stream()));
   MC_CHECK(cudaMallocAsync((void**)&dc, sizeof(float) * 2 * sH, stream()));
   int rc = 0, pending = 0;
+  const bool vec = ls_vec_ok(H, {gates, cbuf, dH, dA, ws, dc});
   for (int64_t t = T - 1; t >= 0 && rc == 0; --t) {
     const float* dnext_c = (t < T - 1) ? dc + ((t + 1) & 1) * sH : nullptr;
-    lstm_bwd_part_kernel<<<grid_for(sH, LS_THREADS), LS_THREADS, 0, stream()>>>(
-        gates + t * sA, cbuf + t * sH, cbuf + (t + 1) * sH, dH + (t + 1) * sH, ws, pending, dnext_c, dA + t * sA,
-        dc + (t & 1) * sH, N, H);
+    if (vec)
+      lstm_bwd_part4_kernel<<<grid_for(sH / 4, LS4_THREADS), LS4_THREADS, 0, stream()>>>(
+          gates + t * sA, cbuf + t * sH, cbuf + (t + 1) * sH, dH + (t + 1) * sH, ws, pending, dnext_c, dA + t * sA,
+          dc + (t & 1) * sH, N, H);
+    else
+      lstm_bwd_part_kernel<<<grid_for(sH, LS_THREADS), LS_THREADS, 0, stream()>>>(
+          gates + t * sA, cbuf + t * sH, cbuf + (t + 1) * sH, dH + (t + 1) * sH, ws, pending, dnext_c, dA + t * sA,
+          dc + (t & 1) * sH, N, H);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("lstm_bwd_part_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; break; }
     count_launch();
