@@ -410,6 +410,8 @@ def run_b200(args):
         lib.mc_launch_count(ctypes.byref(n1))
         ms = ctypes.c_float()
         lib.mc_event_elapsed_ms(e0, e1, ctypes.byref(ms))
+        if world > 1:
+            log('rank %d: %s %.4f ms/step on its own device' % (rank, step_fn.__name__, ms.value / steps))
         return parallel.max_over_ranks(ms.value), n1.value - n0.value, parallel.max_over_ranks(wall * 1e3)
 
     sampler = ClockSampler(device)
