@@ -721,7 +721,21 @@ def run_reference(args):
     }
 
 
+def pin_visible_device():
+    """One process per GPU: optionally make ONLY this rank's GPU visible to the process before CUDA starts
+    (MINPY_PIN_VISIBLE=1; the rank then addresses it as device 0).  Experiment switch for the per-kernel
+    slowdown seen in ranks that can see several GPUs."""
+    if os.environ.get('MINPY_PIN_VISIBLE') != '1' or int(os.environ.get('WORLD_SIZE', '1')) <= 1:
+        return
+    local = os.environ.get('LOCAL_RANK', os.environ.get('RANK', '0'))
+    visible = os.environ.get('CUDA_VISIBLE_DEVICES')
+    ids = visible.split(',') if visible else None
+    os.environ['CUDA_VISIBLE_DEVICES'] = ids[int(local)] if ids else local
+    os.environ['LOCAL_RANK'] = '0'
+
+
 def main():
+    pin_visible_device()
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=50)

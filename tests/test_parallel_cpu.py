@@ -99,3 +99,25 @@ def test_two_rank_data_parallel_matches_full_batch(tmp_path):
             assert np.allclose(model.params[k].asnumpy(), r0['final_' + k], rtol=1e-10, atol=1e-12), k
     finally:
         minpy.set_global_policy('prefer_cuda')
+
+
+def test_peer_memory_window_is_opt_in_beyond_two_ranks(monkeypatch):
+    """_init_p2p_window: 'auto' uses the window only at world size 2 (where it was measured faster inside
+    the step), '0' never, and outside 2..8 ranks never -- decided before the library is touched."""
+    from minpy_b200 import parallel
+
+    class Boom(object):
+        def __getattr__(self, name):
+            raise AssertionError('the library must not be called: %s' % name)
+
+    import minpy_b200.ops as ops
+    monkeypatch.setattr(ops, 'L', lambda: Boom())
+    monkeypatch.setattr(parallel, '_dist', lambda: Boom())
+    for world, mode in ((4, 'auto'), (8, 'auto'), (2, '0'), (9, '1'), (1, '1')):
+        if mode == 'auto':
+            monkeypatch.delenv('MINPY_P2P_ALLREDUCE', raising=False)
+        else:
+            monkeypatch.setenv('MINPY_P2P_ALLREDUCE', mode)
+        parallel._state['p2p'] = 'stale'                         # pylint: disable=protected-access
+        parallel._init_p2p_window(0, world)                      # pylint: disable=protected-access
+        assert parallel._state['p2p'] is None and not parallel.p2p_active()   # pylint: disable=protected-access
