@@ -592,9 +592,11 @@ def run_ufunc_sweep(sizes=(10 ** 4, 10 ** 5, 10 ** 6, 10 ** 7, 10 ** 8, 10 ** 9 
 
 
 # ------------------------------------------------------------- CPU arm (oracle port) -------
-def oracle_step_fn(workload):
+def oracle_step_fn(workload, mask_fn=None, with_grads=False):
     """One training step of `workload` on the NumPy oracle (float64, as the reference's NumPy
-    variant computes): returns (step(xb, yb) -> loss, batch)."""
+    variant computes): returns (step(xb, yb) -> loss, batch).  `mask_fn(i, shape)` supplies the
+    dropout mask of hidden layer i (parity tests hand in the device's Philox masks); with
+    `with_grads` the step returns (loss, {name: gradient}) and `step.params` exposes the state."""
     from oracle import minpy_oracle as orc
     from minpy_b200 import workloads
     factory, batch, rule, optim_config, _, _ = workloads.WORKLOADS[workload]
@@ -626,7 +628,8 @@ def oracle_step_fn(workload):
                                               running_mean=state['aux'].get('rm%d' % i),
                                               running_var=state['aux'].get('rv%d' % i))
                     state['aux']['rm%d' % i], state['aux']['rv%d' % i] = orc.raw(rm), orc.raw(rv)
-                    mask = rng.rand(*orc.raw(h).shape) > 0.5
+                    shape = orc.raw(h).shape
+                    mask = mask_fn(i, shape) if mask_fn is not None else rng.rand(*shape) > 0.5
                     h = orc.dropout(h, 0.5, mask=mask)
                 return orc.softmax_loss(orc.affine(h, p['wo'], p['bo']), yb)
             return f
@@ -670,7 +673,10 @@ def oracle_step_fn(workload):
         grads, loss = orc.grad_and_loss(loss_of(xb, yb), argnum=range(len(names)))(*[params[n] for n in names])
         for n, g in zip(names, grads):
             params[n], cfgs[n] = update(params[n], g, cfgs[n])
+        if with_grads:
+            return float(loss), dict((n, np.asarray(orc.raw(g), np.float64)) for n, g in zip(names, grads))
         return float(loss)
+    step.params, step.aux, step.configs = params, state['aux'], cfgs
     return step, batch
 
 

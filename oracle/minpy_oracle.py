@@ -582,7 +582,9 @@ def constant(shape, config):  # init.py:37-57
 # ======================================================================================
 #  Convolution / pooling -- MXNet 0.9 operator semantics as used through core.Function
 #  (minpy/core.py:148-190; examples/nn/cnn.py:32-40).  NO reference CPU code exists
-#  (MXNet is an un-vendored dependency): PARITY UNPINNED, validated by central differences.
+#  (MXNet is an un-vendored dependency): PARITY UNPINNED against the reference.  Held to an independent
+#  implementation instead -- torch.nn.functional.conv2d / max_pool2d + autograd, CPU float64, incl. the
+#  relu-at-zero and first-maximum tie choices (tests/test_conv_oracle_torch.py) -- and to central differences.
 # ======================================================================================
 def conv2d_fwd(x, w, b, stride=1, pad=0):
     """NCHW cross-correlation: y[n,f,i,j] = b[f] + sum x[n,c,i*s+kh-p,j*s+kw-p] * w[f,c,kh,kw]."""

@@ -48,7 +48,8 @@ def last_path(lib):
     return p.value
 
 
-@pytest.mark.parametrize('mode,tol', [('tf32', 1e-2), ('fp32', 2e-5)])
+# TF32 tolerance ~3x the measured worst case (gpurun_out/parity_errors.json), inside north_star's 1e-2
+@pytest.mark.parametrize('mode,tol', [('tf32', 4e-3), ('fp32', 2e-5)])
 @pytest.mark.parametrize('shape', SHAPES)
 def test_conv_fwd_dgrad_wgrad(cuda, shape, mode, tol):
     N, C, H, W, F, K, pad = shape
@@ -66,14 +67,15 @@ def test_conv_fwd_dgrad_wgrad(cuda, shape, mode, tol):
         path_f = last_path(lib)
         yr = cuda.conv2d_fwd(xd, wd, bd, 1, pad, relu=True)
         ref = orc.conv2d_fwd(x64, w64, b64, 1, pad)
-        assert rel(y.asnumpy(), ref) <= tol
+        from conftest import record_err
+        assert record_err('conv_fwd_' + mode, rel(y.asnumpy(), ref)) <= tol
         assert rel(yr.asnumpy(), np.maximum(ref, 0)) <= tol
         dy = rng.randn(*ref.shape).astype(np.float32)
         dx, dw, db = cuda.conv2d_bwd(xd, wd, CudaArray.from_numpy(dy), 1, pad)
         path_w = last_path(lib)
         rdx, rdw, rdb = orc.conv2d_bwd(x64, w64, dy.astype(np.float64), 1, pad)
-        assert rel(dx.asnumpy(), rdx) <= tol
-        assert rel(dw.asnumpy(), rdw) <= tol
+        assert record_err('conv_dgrad_' + mode, rel(dx.asnumpy(), rdx)) <= tol
+        assert record_err('conv_wgrad_' + mode, rel(dw.asnumpy(), rdw)) <= tol
         # tf32 mode: the bias gradient is one more accumulator of the wgrad kernel (dy x ones on the
         # tensor cores), so dy is rounded to TF32 there as well
         assert rel(db.asnumpy(), rdb) <= (tol if mode == 'tf32' else 2e-5)

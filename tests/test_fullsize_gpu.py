@@ -1,0 +1,221 @@
+"""Full-size parity of the BASELINE configurations (C1, C3, C4, the reference-shaped
+cnn.py net, C5) against the oracle: one `Solver` step through the eager path AND one CUDA-graph
+replay of the same step, at the real shapes bench.py times -- the split-K 1024x3072x512 GEMMs,
+the batchnorm slab kernels at 1024x512, the halo convolution kernels at 512x32x32, the LSTM
+sequence loops at T=100 / H=1024.
+
+Reference shapes: examples/nn/mlp.py:23-60, mlp_bn_dropout.py:26-60, cnn.py:26-60, lstm.py:9-60.
+
+How the comparison is made
+  * eager: `Solver._step_grads` gives the loss and the gradient of EVERY parameter; they are held
+    to `oracle_step_fn(workload, with_grads=True)` on the same batch and the same initial weights.
+  * graph: the optimizer state is created (zeros) before the first step and the step graph is
+    captured with no eager warm-up, so after ONE replay `velocity == -lr * g` (sgd_momentum) or
+    `m == (1 - beta1) * g` (adam): the optimizer state is read back and held to the same oracle
+    gradients, and the updated parameters to `w + velocity` / the oracle's adam step.
+  * dropout (C3): the device draws Philox masks, the reference MT19937 ones, so the
+    oracle is handed the device's own masks: `mc_dropout` on ones with the (seed, offset) the
+    step used (graph replays shift the offset by epoch << 40, csrc/layers.cu).
+Tolerances (north_star): everything here is downstream of a TF32 tensor-core contraction: 1e-2
+relative to the largest entry of the tensor; the loss (a mean over the batch) 2e-3.
+"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+pytestmark = pytest.mark.gpu
+
+GRAD_TOL = 1e-2      # TF32 contraction path (north_star)
+LOSS_TOL = 2e-3
+
+
+def rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.max(np.abs(a - b)) / max(1e-30, np.max(np.abs(b))))
+
+
+class _Streams(object):
+    """Logs the (seed, offset, size) of every Philox stream the step reserves."""
+
+    def __init__(self):
+        from minpy.array_variants.cuda import random as crandom
+        self.mod = crandom
+        self.orig = crandom.next_stream
+        self.log = []
+
+    def __enter__(self):
+        def logged(n):
+            seed, offset = self.orig(n)
+            self.log.append((seed, offset, int(n)))
+            return seed, offset
+        self.mod.next_stream = logged
+        return self
+
+    def __exit__(self, *exc):
+        self.mod.next_stream = self.orig
+
+
+def _device_masks(streams, shape, prob, epoch=0):
+    """The keep-masks the device drew for `streams`: mc_dropout applied to ones."""
+    from minpy_b200 import ops
+    from minpy_b200.cuda_array import CudaArray
+    lib = ops.L()
+    ones = ops.full(shape, 1.0)
+    masks = []
+    for seed, offset, n in streams:
+        assert n == ones.size
+        out = CudaArray.empty(shape)
+        lib.mc_dropout(ones.ptr, out.ptr, ones.size, float(prob), int(seed), int(offset) + (int(epoch) << 40))
+        masks.append(out.asnumpy() > 0.5)
+    return masks
+
+
+def _make(workload, graph):
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    from minpy import array as marray
+    from minpy.nn.solver import Solver
+    from minpy_b200 import workloads
+    from minpy_b200.cuda_array import CudaArray
+    import minpy.numpy.random as mrandom
+    mrandom.seed(11)
+    factory, batch, rule, cfg, make_data, _ = workloads.WORKLOADS[workload]
+    model = factory()
+    solver = Solver(model, None, None, update_rule=rule, optim_config=dict(cfg), init_rule='gaussian',
+                    init_config={'stdvar': 0.01}, verbose=False, step_graph=graph)
+    solver.init()
+    init = workloads.init_params(model, 3)
+    for k, v in init.items():
+        model.params[k] = marray.wrap(CudaArray.from_numpy(v))
+    X, Y = make_data(batch, seed=100)
+    return model, solver, init, X, Y, rule, cfg
+
+
+def _batch(X, Y):
+    from minpy import array as marray
+    from minpy.nn.io import DataBatch
+    from minpy_b200.cuda_array import CudaArray
+    return DataBatch([marray.wrap(CudaArray.from_numpy(X))], [marray.wrap(CudaArray.from_numpy(Y))], pad=0, index=0)
+
+
+def _oracle(workload, X, Y, masks=None):
+    import bench
+    mask_fn = (lambda i, shape: masks[i]) if masks is not None else None
+    step, _ = bench.oracle_step_fn(workload, mask_fn=mask_fn, with_grads=True)
+    loss, grads = step(X, Y)
+    return loss, grads, step
+
+
+def _check_grads(got, want, what):
+    assert set(got) == set(want)
+    worst = {}
+    for name in want:
+        assert got[name].shape == want[name].shape, (what, name)
+        assert np.all(np.isfinite(got[name])), (what, name)
+        worst[name] = rel(got[name], want[name])
+    from conftest import record_err
+    record_err('fullsize ' + what, max(worst.values()))
+    bad = dict((k, v) for k, v in worst.items() if v > GRAD_TOL)
+    assert not bad, '%s: gradients beyond %g: %r (all: %r)' % (what, GRAD_TOL, bad, worst)
+
+
+def _run_case(workload):
+    from minpy_b200.step_graph import StepGraph
+    from minpy_b200 import ops
+    import minpy.numpy as mnp
+    drop = workload == 'mlp_c3'
+
+    # ---- eager: loss and every gradient ------------------------------------------------------
+    model, solver, init, X, Y, rule, cfg = _make(workload, graph=False)
+    with _Streams() as streams:
+        names, grads, loss = solver._step_grads(_batch(X, Y))  # pylint: disable=protected-access
+    got = dict((n, g.asnumpy()) for n, g in zip(names, grads))
+    masks = None
+    if drop:
+        assert len(streams.log) == model.depth
+        masks = _device_masks(streams.log, (X.shape[0], 512), model.drop)
+        keep = np.mean([m.mean() for m in masks])
+        assert abs(keep - (1 - model.drop)) < 5e-3, keep
+    oloss, ograds, ostep = _oracle(workload, X, Y, masks)
+    assert abs(float(loss) - oloss) <= LOSS_TOL * abs(oloss), (float(loss), oloss)
+    _check_grads(got, ograds, workload + ' eager')
+    if drop:
+        # the running statistics the eager step produced (momentum 0.9 from zeros)
+        for i in range(model.depth):
+            assert rel(model.aux_params['running_mean%d' % i].asnumpy(), ostep.aux['rm%d' % i]) <= GRAD_TOL
+            assert rel(model.aux_params['running_var%d' % i].asnumpy(), ostep.aux['rv%d' % i]) <= GRAD_TOL
+    del solver, model, grads
+
+    # ---- graph: one replay from a fresh optimizer state --------------------------------------
+    model, solver, init, X, Y, rule, cfg = _make(workload, graph=True)
+    for name in model.params:
+        c = solver.optim_configs[name]
+        if rule == 'sgd_momentum':
+            c['velocity'] = mnp.zeros(model.params[name].shape)
+        else:
+            c['m'], c['v'], c['t'] = mnp.zeros(model.params[name].shape), mnp.zeros(model.params[name].shape), 0
+    if drop:     # running statistics must exist before capture (state created inside a step aborts it)
+        for i in range(model.depth):
+            model.aux_params['running_mean%d' % i] = mnp.zeros(512)
+            model.aux_params['running_var%d' % i] = mnp.zeros(512)
+    solver._step_graph = StepGraph(solver, warmup=0)  # pylint: disable=protected-access
+    with _Streams() as streams:
+        solver._step(_batch(X, Y))  # pylint: disable=protected-access
+    sg = solver._step_graph  # pylint: disable=protected-access
+    assert not sg.disabled and sg.captures == 1 and sg.replays == 1, (sg.disabled, sg.captures, sg.replays)
+    if drop:
+        masks = _device_masks(streams.log, (X.shape[0], 512), model.drop, epoch=1)
+        oloss, ograds, ostep = _oracle(workload, X, Y, masks)
+    gloss = float(solver.loss_history[-1])
+    assert abs(gloss - oloss) <= LOSS_TOL * abs(oloss), (gloss, oloss)
+    got = {}
+    for name in model.params:
+        c = solver.optim_configs[name]
+        if rule == 'sgd_momentum':
+            got[name] = c['velocity'].asnumpy().astype(np.float64) / (-cfg['learning_rate'])
+        else:
+            got[name] = c['m'].asnumpy().astype(np.float64) / (1.0 - 0.9)
+            assert int(c['t']) == 1
+    _check_grads(got, ograds, workload + ' graph replay')
+    # the update itself, from the device's own optimizer state (float64 restatement of optim.py:52-141);
+    # measured on the step the optimizer took (w_new - w_old): the weights barely move in one step
+    for name in model.params:
+        c = solver.optim_configs[name]
+        step_got = model.params[name].asnumpy().astype(np.float64) - init[name]
+        if rule == 'sgd_momentum':
+            step_want = c['velocity'].asnumpy().astype(np.float64)
+        else:
+            m_hat = c['m'].asnumpy().astype(np.float64) / (1 - 0.9)
+            v_hat = c['v'].asnumpy().astype(np.float64) / (1 - 0.999)
+            step_want = -cfg['learning_rate'] * m_hat / (np.sqrt(v_hat) + 1e-8)
+        scale = max(np.max(np.abs(step_want)), 1e-30)
+        # float32 rounding of w + dw at |w| ~ 0.05 is ~4e-9; in units of the step that is <= 2e-3
+        assert np.max(np.abs(step_got - step_want)) / scale <= 1e-2, name
+    ops.L().mc_sync()
+
+
+def test_mlp_c1_full_size():
+    _run_case('mlp_c1')
+
+
+def test_mlp_c3_full_size():
+    _run_case('mlp_c3')
+
+
+def test_cnn_ref_full_size():
+    _run_case('cnn_ref')
+
+
+def test_cnn_c4_full_size():
+    _run_case('cnn_c4')
+
+
+def test_lstm_c5_full_size():
+    _run_case('lstm_c5')

@@ -166,11 +166,14 @@ def test_gemm(cuda, M, N, K, ta, tb):
     ad, bd, biasd = up(cuda, a), up(cuda, b), up(cuda, bias)
     import ctypes
     path = ctypes.c_int(-1)
-    for mode, tol in (('fp32', 1e-5), ('tf32', 1e-2)):
+    # tolerances ~3x the measured worst case (profiles/r1z/gemm_sweep.log: 7e-4 in TF32 mode), well inside
+    # north_star's 1e-2: a dropped k-block or split-K slice changes an entry by ~sqrt(32/K) >> 2.5e-3
+    from conftest import record_err
+    for mode, tol in (('fp32', 1e-5), ('tf32', 2.5e-3)):
         cuda.set_gemm_precision(mode)
         got = cuda.gemm(ad, bd, ta, tb).asnumpy()
         cuda.L().mc_gemm_last_path(ctypes.byref(path))
-        err = float(np.max(np.abs(got - ref)) / (scale * 3))
+        err = record_err('gemm_' + mode, float(np.max(np.abs(got - ref)) / (scale * 3)))
         assert got.shape == ref.shape
         assert err <= tol, (mode, path.value, err)
         got2 = cuda.gemm(ad, bd, ta, tb, bias=biasd, relu=True).asnumpy()
