@@ -97,6 +97,15 @@ def _default_partition():
         return 1, 0
 
 
+def _shared_order(order):
+    """Rank 0's permutation on every rank of an initialised process group (else `order` unchanged)."""
+    try:
+        from minpy_b200 import parallel
+        return parallel.broadcast_host_array(order)
+    except ImportError:
+        return order
+
+
 class _DevicePrefetch(object):
     """Two device staging slots filled by host->device copies on the library's copy stream
     (mc_prefetch_h2d): while the step on batch i runs on the compute stream, batch i+1 is already
@@ -159,14 +168,18 @@ class NDArrayIter(DataIter):
         self.data = _init_data(data, allow_empty=False, default_name='data')
         self.label = _init_data(label, allow_empty=True, default_name='softmax_label')
 
+        if num_parts is None:
+            num_parts, part_index = _default_partition()
         if shuffle:   # once, at construction, with the global NumPy RNG (reference :173-177)
             order = np.arange(self.data[0][1].shape[0])
             np.random.shuffle(order)
+            if num_parts > 1:
+                # data parallel: the strided shards below partition the data only if every rank
+                # permutes with the SAME order -- rank 0's (each process has its own unseeded RNG)
+                order = _shared_order(order)
             self.data = [(k, v[order]) for k, v in self.data]
             self.label = [(k, v[order]) for k, v in self.label]
 
-        if num_parts is None:
-            num_parts, part_index = _default_partition()
         if num_parts > 1:   # data-parallel shard: rows part_index, part_index + num_parts, ...
             self.data = [(k, v[part_index::num_parts]) for k, v in self.data]
             self.label = [(k, v[part_index::num_parts]) for k, v in self.label]

@@ -147,6 +147,7 @@ class Solver(object):
         # whole loop is one multi-tensor kernel launch
         fast = optim.multi_update(self.update_rule, [self.model.params[k] for k in names], grads,
                                   [self.optim_configs[k] for k in names])
+        self._update_was_multi_tensor = fast is not None
         if fast is not None:
             for name, next_w, next_config in zip(names, fast[0], fast[1]):
                 self.model.params[name] = next_w
@@ -156,6 +157,20 @@ class Solver(object):
             next_w, next_config = self.update_rule(self.model.params[name], dw, self.optim_configs[name])
             self.model.params[name] = next_w
             self.optim_configs[name] = next_config
+
+    def _snapshot_params(self):
+        """The parameters to keep as `best_params`.  The reference stores references (solver.py:295-301):
+        updates rebind parameters, they never write in place.  A step graph DOES write in place (its
+        replays update the buffers the captured kernels read), so then device copies are taken."""
+        sg = self._step_graph
+        if sg is None or not sg.writes_in_place():
+            return dict(self.model.params)
+        from minpy import array as marray
+        out = {}
+        for name, value in self.model.params.items():
+            raw = value._get_latest_data() if isinstance(value, marray.Array) else value  # pylint: disable=protected-access
+            out[name] = marray.wrap(raw.copy()) if hasattr(raw, 'copy') else value
+        return out
 
     def check_accuracy(self, dataiter, num_samples=None):
         """Classification: fraction of correct arg-max predictions; regression: mean loss.
@@ -172,6 +187,11 @@ class Solver(object):
                 correct = correct + np.sum(np.argmax(predict, axis=1) == batch.label[0])
                 seen += check.batch_size      # padded rows are counted too, as in the reference (:232)
             correct = correct.asnumpy() if hasattr(correct, 'asnumpy') else correct
+            # data parallel: every rank scored its own shard; all ranks must see the SAME accuracy, or
+            # `val_acc > best_val_acc` picks different epochs on different ranks and the weights diverge
+            from minpy_b200 import parallel
+            correct = parallel.allreduce_scalar_sum(float(correct))
+            seen = parallel.allreduce_scalar_sum(seen)
             return float(correct) / seen
         if self.task_type == 'regression':
             total, batches = 0, 0
@@ -180,6 +200,9 @@ class Solver(object):
                 total = total + self.model.loss(predict, batch.label[0])
                 batches += 1
             total = total.asnumpy() if hasattr(total, 'asnumpy') else total
+            from minpy_b200 import parallel
+            total = parallel.allreduce_scalar_sum(float(total))
+            batches = parallel.allreduce_scalar_sum(batches)
             return float(total) / batches
         raise ValueError('Task type is either classification or regression.')
 
@@ -209,8 +232,7 @@ class Solver(object):
                     self.epoch, self.num_epochs, what, train_acc, what, val_acc, time.time() - start))
             if val_acc > self.best_val_acc:
                 self.best_val_acc = val_acc
-                # references, not copies: updates rebind parameters, they never write in place
-                self.best_params = dict(self.model.params)
+                self.best_params = self._snapshot_params()
             for config in self.optim_configs.values():
                 config['learning_rate'] *= self.lr_decay
         self.model.params = self.best_params

@@ -119,6 +119,9 @@ int mc_mem_info(size_t* free_bytes, size_t* total_bytes) {
 }
 int mc_memcpy_h2d(void* dst, const void* src, size_t n) {
   if (n == 0) return 0;
+  // a captured memcpy node would re-read `src` (usually a temporary pageable NumPy buffer) on every
+  // replay, long after it was freed: refuse, so that the step graph falls back to eager execution
+  MC_REQUIRE(!g_capturing, "mc_memcpy_h2d inside a graph capture (a host array was created inside the step)");
   MC_CHECK(cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, g_stream));
   return 0;
 }
@@ -150,6 +153,7 @@ static int ensure_copy_stream() {
   return 0;
 }
 int mc_prefetch_h2d(void* dst, const void* src, size_t n) {
+  MC_REQUIRE(!g_capturing, "mc_prefetch_h2d inside a graph capture");
   if (ensure_copy_stream()) return 1;
   if (n) MC_CHECK(cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, g_copy_stream));
   return 0;

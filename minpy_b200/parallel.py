@@ -329,6 +329,16 @@ def broadcast_params(params, src=0):
             params[name] = marray.wrap(host)
 
 
+def broadcast_host_array(arr, src=0):
+    """Rank `src`'s copy of a small host array (same shape and dtype on every rank), e.g. the shuffle
+    order of NDArrayIter.  A no-op without a process group."""
+    if _state['world'] <= 1:
+        return arr
+    box = [np.asarray(arr) if _state['rank'] == src else None]
+    _dist().broadcast_object_list(box, src=src)
+    return box[0]
+
+
 def allreduce_scalar_sum(value):
     """Sum of a Python number over ranks (accuracy counts, loss for printing)."""
     if _state['world'] <= 1:

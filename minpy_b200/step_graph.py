@@ -116,6 +116,7 @@ class StepGraph(object):
         self.flat_view = None
         self.private_pool = None      # device blocks reserved for the graph's temporaries
         self.adam_cfgs = []
+        self.state_objs = []
         self.replays = 0
         self.captures = 0
         self.h2d_bytes = 0
@@ -206,6 +207,11 @@ class StepGraph(object):
                     execs.append(ex)
                     lib.mc_graph_begin()
             solver._step_update(names, grads)                 # pylint: disable=protected-access
+            if not getattr(solver, '_update_was_multi_tensor', False) and \
+                    any('t' in cfg for cfg in solver.optim_configs.values()):
+                # the per-parameter mc_adam bakes its bias correction from the host-side t at launch:
+                # a replay would reuse the capture-time value.  Only mc_multi_update reads the replay counter.
+                raise StepGraphUnsupported('a step-counting update rule ran outside the multi-tensor kernel')
             loss_raw = _raw(loss)
             if loss_raw is None:
                 raise StepGraphUnsupported('the loss is not a device scalar')
@@ -239,6 +245,7 @@ class StepGraph(object):
             _Buffer._active_pool = None                        # pylint: disable=protected-access
         self.private_pool = pool
         self.execs = execs
+        self.state_objs = [obj for _, _, obj, _ in entries]
         self.loss_raw = loss_raw
         self.flat_view = parallel.torch_view(self.flat) if len(execs) == 2 else None
         self.adam_cfgs = [cfg for cfg in solver.optim_configs.values() if 't' in cfg]
@@ -261,10 +268,29 @@ class StepGraph(object):
             for cfg in self.adam_cfgs:
                 cfg['t'] = int(cfg['t']) + 1
         self.replays += 1
+        if self.replays % 64 == 0 and parallel.p2p_active():
+            # the peer all-reduce kernel gives up on a missing rank after its watchdog (csrc/comm.cu) and
+            # flags it in host-visible memory; replays launch the captured kernel directly, so look here
+            ptr, size, bad = ctypes.c_void_p(), ctypes.c_size_t(), ctypes.c_int()
+            lib.mc_p2p_info(ctypes.byref(ptr), ctypes.byref(size), ctypes.byref(bad))
+            if bad.value:
+                raise RuntimeError('peer-memory all-reduce timed out waiting for a rank: gradients of the last '
+                                   'steps were not reduced')
+        # every replay rewrites parameters / running statistics / optimizer state IN PLACE: a host copy an
+        # earlier asnumpy() cached inside the Array is stale from here on (minpy/array.py get_data)
+        for obj in self.state_objs:
+            if isinstance(obj, marray.Array) and len(obj._data) > 1:   # pylint: disable=protected-access
+                obj._data = {2: obj._data[2]}                           # pylint: disable=protected-access
+                obj._latest_version = 2                                 # ArrayType.CUDA
         keep = CudaArray.empty(())
         lib.mc_memcpy_d2d(keep.ptr, self.loss_raw.ptr, 4)
         keep.begin_readback()          # the loss travels to the host behind this step, on a third stream
         self.solver.loss_history.append(marray.wrap(keep))
+
+    def writes_in_place(self):
+        """True while replays update the solver's state inside its existing buffers (callers that keep
+        references to old parameter values -- Solver.best_params -- must copy instead)."""
+        return self.execs is not None and not self.disabled
 
     # ---- the step -------------------------------------------------------------------------
     def step(self, batch):

@@ -49,9 +49,18 @@ def _worker(rank, world, port, out_dir):
     for batch in it:
         solver._step(batch)  # pylint: disable=protected-access
     final = dict((k, np.array(v.asnumpy())) for k, v in model.params.items())
+    # shuffled iterators must shard ONE permutation (rank 0's), and check_accuracy must give
+    # every rank the same number (each rank scores its own shard)
+    np.random.seed(1000 + rank)                 # per-rank RNG streams, as in separate processes
+    ids = np.arange(world * B * 2)
+    sit = NDArrayIter(ids.reshape(-1, 1).astype(np.float64), ids, batch_size=B, shuffle=True, num_parts=world,
+                      part_index=rank)
+    shard_ids = np.asarray(sit.label[0][1]).astype(np.int64)
+    acc = solver.check_accuracy(it)
     mx = parallel.max_over_ranks(float(rank + 1))
     sm = parallel.allreduce_scalar_sum(float(rank + 1))
     np.savez(os.path.join(out_dir, 'rank%d.npz' % rank), mx=mx, sm=sm, nbatches=len(solver.loss_history),
+             shard_ids=shard_ids, acc=acc,
              **dict([('start_' + k, v) for k, v in start.items()] + [('final_' + k, v) for k, v in final.items()]))
     parallel.barrier()
     parallel.shutdown()
@@ -71,6 +80,10 @@ def test_two_rank_data_parallel_matches_full_batch(tmp_path):
         assert np.allclose(r0['final_' + k], r1['final_' + k], rtol=0, atol=1e-12), k
     assert float(r0['mx']) == 2.0 and float(r0['sm']) == 3.0        # (3)
     assert int(r0['nbatches']) == 2
+    both = np.concatenate([r0['shard_ids'], r1['shard_ids']])
+    assert sorted(both.tolist()) == list(range(len(both)))           # the shards partition the data set
+    assert not np.array_equal(np.sort(r0['shard_ids']), r0['shard_ids'])   # and it really was shuffled
+    assert float(r0['acc']) == float(r1['acc'])                      # one accuracy for the whole job
 
     # (2) single process, whole global batch per step, from the same start
     sys.path.insert(0, ROOT)

@@ -175,3 +175,95 @@ def test_graph_replay_lstm_adam():
     graph = _run(make, 'adam', {'learning_rate': 1e-2}, X, Y, 8, 6, True)
     assert graph[4]._step_graph.replays == 4   # pylint: disable=protected-access
     _same(graph, eager, 1e-5)
+
+
+def test_graph_falls_back_when_the_step_uploads_a_host_constant():
+    """A loss that builds a device array from a NumPy constant inside the step: the host->device copy
+    must not become a graph node (every replay would re-read a freed host buffer): the capture is
+    refused (mc_memcpy_h2d requires !capturing) and training continues eagerly, correctly."""
+    import minpy.numpy as mnp
+    from minpy_b200 import workloads
+    weights = np.linspace(0.5, 1.5, 10).astype(np.float32)
+
+    class Weighted(workloads.MLP):
+        def loss(self, predict, y):
+            return super(Weighted, self).loss(predict * mnp.array(weights), y)
+
+    make = lambda: Weighted(in_dim=96, hidden=64, classes=10)
+    X, Y = _data(2 * 32, seed=6)
+    cfg = {'learning_rate': 0.05, 'momentum': 0.9}
+    eager = _run(make, 'sgd_momentum', cfg, X, Y, 32, 6, False)
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter('always')
+        graph = _run(make, 'sgd_momentum', cfg, X, Y, 32, 6, True)
+    assert graph[4]._step_graph.disabled   # pylint: disable=protected-access
+    assert any('step graph disabled' in str(x.message) for x in w)
+    _same(graph, eager, 1e-6)
+
+
+def test_graph_adam_outside_the_multi_tensor_kernel_is_refused():
+    """A parameter the loss does not reach has gradient 0.0: optim.multi_update declines and the
+    per-parameter mc_adam (bias correction baked from the host-side t) would be captured -- the step
+    graph must refuse rather than replay a stale t."""
+    from minpy_b200 import workloads
+
+    class Unused(workloads.MLP):
+        def __init__(self, **kw):
+            super(Unused, self).__init__(**kw)
+            self.add_param(name='unused', shape=(4,))
+
+    make = lambda: Unused(in_dim=96, hidden=64, classes=10)
+    X, Y = _data(2 * 32, seed=7)
+    eager = _run(make, 'adam', {'learning_rate': 1e-2}, X, Y, 32, 6, False)
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter('always')
+        graph = _run(make, 'adam', {'learning_rate': 1e-2}, X, Y, 32, 6, True)
+    assert graph[4]._step_graph.disabled   # pylint: disable=protected-access
+    assert any('multi-tensor' in str(x.message) for x in w)
+    _same(graph, eager, 1e-6)
+
+
+def test_graph_training_keeps_best_params_and_fresh_host_views():
+    """Solver.train with step_graph=True: replays write parameters IN PLACE, so (a)
+    `best_params` must be a snapshot, not an alias of the live buffers, and (b) a host copy cached by
+    an earlier asnumpy() must not be served after later replays."""
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    import minpy.numpy as mnp
+    from minpy.nn.io import NDArrayIter
+    from minpy.nn.solver import Solver
+    from minpy_b200 import workloads
+    rng = np.random.RandomState(8)
+    X = rng.randn(256, 96).astype(np.float32)
+    W = rng.randn(96, 10).astype(np.float32)
+    Y = np.argmax(X.dot(W), axis=1)
+    train = NDArrayIter(X, Y, batch_size=32, shuffle=False)
+    # the validation set is RANDOM labels scored after a huge-lr epoch: accuracy moves around, so the
+    # best epoch is (almost surely) not the last one
+    test = NDArrayIter(X[:64], rng.randint(0, 10, 64), batch_size=32, shuffle=False)
+    model = workloads.MLP(in_dim=96, hidden=64, classes=10)
+    solver = Solver(model, train, test, update_rule='sgd_momentum', optim_config={'learning_rate': 0.5, 'momentum': 0.9},
+                    init_rule='gaussian', init_config={'stdvar': 0.05}, num_epochs=6, verbose=False, step_graph=True)
+    solver.init()
+    seen = []
+    orig = solver.check_accuracy
+
+    def spy(it, num_samples=None):
+        seen.append(dict((k, v.asnumpy().copy()) for k, v in model.params.items()))   # caches a host copy
+        return orig(it, num_samples=num_samples)
+    solver.check_accuracy = spy
+    solver.train()
+    sg = solver._step_graph  # pylint: disable=protected-access
+    assert sg is not None and not sg.disabled and sg.replays > 20
+    # (b) the per-epoch host views differ from epoch to epoch (they would all equal the first one if
+    # the cached NumPy copy were served)
+    per_epoch = seen[0::2]
+    assert len(per_epoch) == 6
+    for a, b in zip(per_epoch[:-1], per_epoch[1:]):
+        assert np.max(np.abs(a['w1'] - b['w1'])) > 0
+    # (a) best_params equals the snapshot of the best epoch, not necessarily the last
+    best_epoch = int(np.argmax(solver.val_acc_history))       # first maximum: `>` keeps the earliest
+    for k in model.params:
+        assert np.array_equal(model.params[k].asnumpy(), per_epoch[best_epoch][k]), k
+    if best_epoch != 5:
+        assert np.max(np.abs(model.params['w1'].asnumpy() - per_epoch[5]['w1'])) > 0
