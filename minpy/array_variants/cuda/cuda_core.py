@@ -712,28 +712,37 @@ def _lstm_temporal_vjp(ans, x, h0, Wx, Wh, b):
 
 
 # ---- optimizer updates (nn/optim.py:33-141), one kernel per parameter tensor ------------
+def _grad_like(w, dw):
+    """The gradient as a float32 device array of w's shape.  A parameter the loss does not reach
+    gets the Python scalar 0.0 from the tape (tape.py:249-257); the reference's NumPy arithmetic
+    broadcasts it, so do the kernels' callers."""
+    if ops.is_scalar(dw):
+        return ops.full(w.shape, float(dw))
+    return ops.as_f32(dw)
+
+
 def fused_sgd(w, dw, lr):
     out = CudaArray.empty(w.shape)
-    ops.L().mc_sgd(w.ptr, ops.as_f32(dw).ptr, out.ptr, float(lr), w.size)
+    ops.L().mc_sgd(w.ptr, _grad_like(w, dw).ptr, out.ptr, float(lr), w.size)
     return out
 
 
 def fused_sgd_momentum(w, dw, v, lr, momentum):
     w_out, v_out = CudaArray.empty(w.shape), CudaArray.empty(w.shape)
-    ops.L().mc_sgd_momentum(w.ptr, ops.as_f32(dw).ptr, v.ptr, w_out.ptr, v_out.ptr, float(lr), float(momentum), w.size)
+    ops.L().mc_sgd_momentum(w.ptr, _grad_like(w, dw).ptr, v.ptr, w_out.ptr, v_out.ptr, float(lr), float(momentum), w.size)
     return w_out, v_out
 
 
 def fused_rmsprop(w, dw, cache, lr, decay, eps):
     w_out, c_out = CudaArray.empty(w.shape), CudaArray.empty(w.shape)
-    ops.L().mc_rmsprop(w.ptr, ops.as_f32(dw).ptr, cache.ptr, w_out.ptr, c_out.ptr, float(lr), float(decay), float(eps),
+    ops.L().mc_rmsprop(w.ptr, _grad_like(w, dw).ptr, cache.ptr, w_out.ptr, c_out.ptr, float(lr), float(decay), float(eps),
                        w.size)
     return w_out, c_out
 
 
 def fused_adam(w, dw, m, v, lr, beta1, beta2, eps, t):
     w_out, m_out, v_out = CudaArray.empty(w.shape), CudaArray.empty(w.shape), CudaArray.empty(w.shape)
-    ops.L().mc_adam(w.ptr, ops.as_f32(dw).ptr, m.ptr, v.ptr, w_out.ptr, m_out.ptr, v_out.ptr, float(lr), float(beta1),
+    ops.L().mc_adam(w.ptr, _grad_like(w, dw).ptr, m.ptr, v.ptr, w_out.ptr, m_out.ptr, v_out.ptr, float(lr), float(beta1),
                     float(beta2), float(eps), int(t), w.size)
     return w_out, m_out, v_out
 

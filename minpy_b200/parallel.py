@@ -351,6 +351,15 @@ def allreduce_scalar_sum(value):
     return float(t.item())
 
 
+def allgather_int(value):
+    """The integer every rank holds, as a list indexed by rank (checksums in bench.py's dp_parity)."""
+    if _state['world'] <= 1:
+        return [int(value)]
+    out = [None] * _state['world']
+    _dist().all_gather_object(out, int(value))
+    return out
+
+
 def max_over_ranks(value):
     """Max of a Python number over ranks (bench timing)."""
     if _state['world'] <= 1:

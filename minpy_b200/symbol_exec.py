@@ -23,6 +23,11 @@ from .lazy import concrete
 
 _GT0 = 'MC_VJP_GT0_A'
 
+# test hook: when a list, `Plan.forward` appends the (NCHW, host) output of every Convolution node
+# (post-relu when the activation is fused) -- the full-size parity tests read the device's relu /
+# arg-max decisions from it.  Never set on the product path.
+trace = None
+
 
 def _sq(pair, what):
     if pair[0] != pair[1]:
@@ -128,6 +133,8 @@ class Plan(object):
                     x = _nchw(x)
                     values[key] = ops.conv2d_fwd(x, w, b, stride, pad, relu=relu)
                 saved[key] = (x, w)
+                if trace is not None:
+                    trace.append(_nchw(values[key]).asnumpy())
             elif node.op == 'Activation':
                 if key in skip_relu:
                     values[key] = x                     # already applied by the producing convolution

@@ -20,13 +20,9 @@ reference.  Nothing in this file is imported by the product path.
 """
 from __future__ import print_function
 
-import builtins
 import collections
-import collections.abc
 import os
 import sys
-import tempfile
-import types
 
 import numpy as onp
 
@@ -34,78 +30,19 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 REF = os.environ.get('MINPY_REFERENCE', '/root/reference')
 OUT = os.path.join(ROOT, 'tests', 'golden')
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
 
 
 # ------------------------------------------------------------------ reference loader ------
-MXNET_STUB = '''
-__version__ = "0.9.2"
-import types, sys
-class Context(object):
-    def __init__(self, device_type="cpu", device_id=0):
-        self.device_type, self.device_id = device_type, device_id
-    def __enter__(self): return self
-    def __exit__(self, *a): return False
-def cpu(i=0): return Context("cpu", i)
-def gpu(i=0): return Context("gpu", i)
-def _op(*a, **k): raise RuntimeError("mxnet stub: no arithmetic here")
-class _Mod(types.ModuleType):
-    def __getattr__(self, name):
-        if name.startswith("__"): raise AttributeError(name)
-        return _op
-class NDArray(object): pass
-ndarray = _Mod("mxnet.ndarray"); ndarray.NDArray = NDArray
-nd = ndarray
-random = _Mod("mxnet.random")
-symbol = _Mod("mxnet.symbol"); sym = symbol
-class _Sym(object): pass
-symbol.Symbol = _Sym
-io = _Mod("mxnet.io")
-class DataIter(object): pass
-class DataBatch(object): pass
-io.DataIter = DataIter; io.DataBatch = DataBatch
-def _mk(name):
-    def f(*a, **k): raise RuntimeError("mxnet stub: %s has no arithmetic" % name)
-    f.__name__ = name
-    return f
-for _name in ("abs add ceil cos divide dot exp expand_dims floor log max maximum min minimum multiply negative "
-              "power round sign sin sqrt subtract sum tanh transpose true_divide").split():
-    ndarray.__dict__[_name] = _mk(_name)
-for _name in ("normal", "uniform"):
-    random.__dict__[_name] = _mk(_name)
-NDArray.reshape = _mk("reshape")
-for _n, _m in (("ndarray", ndarray), ("nd", nd), ("random", random), ("symbol", symbol), ("io", io)):
-    sys.modules["mxnet." + _n] = _m
-'''
+from oracle.ref_env import MXNET_STUB, activate  # noqa: E402,F401  (the stub text lives beside the loader)
 
 
 def load_reference():
-    """Import the reference's `minpy` (NumPy variant only) and return the module."""
+    """Import the reference's `minpy` (NumPy variant only) straight from /root/reference."""
     if not os.path.isdir(os.path.join(REF, 'minpy')):
         raise SystemExit('reference not found at %s (this script runs in the build container only)' % REF)
-    stub = tempfile.mkdtemp(prefix='minpy_ref_stubs_')
-    os.makedirs(os.path.join(stub, 'mxnet'))
-    with open(os.path.join(stub, 'mxnet', '__init__.py'), 'w') as f:
-        f.write(MXNET_STUB)
-    os.makedirs(os.path.join(stub, 'h5py'))
-    with open(os.path.join(stub, 'h5py', '__init__.py'), 'w') as f:
-        f.write('')
-    for alias, target in (('float', float), ('int', int), ('bool', bool), ('object', object), ('complex', complex)):
-        if not hasattr(onp, alias):
-            setattr(onp, alias, target)
-    for name in ('Iterable', 'Mapping', 'Sequence', 'Callable'):
-        if not hasattr(collections, name):
-            setattr(collections, name, getattr(collections.abc, name))
-    builtins.xrange = range
-    # the repo root must NOT be importable here: it holds the new `minpy` package
-    sys.path[:] = [p for p in sys.path if os.path.abspath(p or '.') not in (ROOT, HERE)]
-    sys.path.insert(0, REF)
-    sys.path.insert(0, stub)
-    import warnings
-    warnings.simplefilter('ignore')
-    import minpy
-    assert os.path.abspath(minpy.__file__).startswith(REF), minpy.__file__
-    minpy.set_global_policy('only_numpy')
-    return minpy
+    return activate(REF)
 
 
 def to_np(v):
