@@ -28,7 +28,8 @@ extern "C" {
 #endif
 
 /* ------------------------------------------------------------------ runtime --- */
-/* Device selection: replaces minpy/context.py:55-56 (mxnet.Context construction). */
+/* Device selection: replaces minpy/context.py:55-56 (mxnet.Context construction).  Each device gets
+ * its own compute stream on first selection; later calls run on the CURRENT device's stream. */
 int mc_init(int device);
 int mc_device_count(int* count);
 int mc_set_device(int device);
@@ -55,6 +56,10 @@ int mc_memcpy_h2d(void* dst_dev, const void* src_host, size_t nbytes);
 int mc_memcpy_d2h(void* dst_host, const void* src_dev, size_t nbytes);
 int mc_memcpy_d2h_async(void* dst_host, const void* src_dev, size_t nbytes);
 int mc_memcpy_d2d(void* dst_dev, const void* src_dev, size_t nbytes);
+/* Copy between two devices of this process: replaces NDArray.copyto(ctx) / as_in_context for operands
+ * that live on another device than the `with gpu(i):` scope (minpy/context.py:92-98, array.py:375-390).
+ * Drains the source device's stream, then copies on the current device's stream. */
+int mc_memcpy_peer(void* dst_dev, int dst_device, const void* src_dev, int src_device, size_t nbytes);
 int mc_memset(void* dst_dev, int byte, size_t nbytes);
 /* Input prefetch beside the compute stream (minpy/nn/io.py:238-258 sliced on the host and copied
  * every step; here batch i+1 is copied on a second stream while step i runs).

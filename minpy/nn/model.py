@@ -68,7 +68,9 @@ class ModelBase(object):
     def save(self, prefix):
         """Write `<prefix>.params`."""
         path = '%s.params' % prefix
-        tensors = dict((k, numpy.asarray(v.asnumpy())) for k, v in self._named_tensors())
+        # auxiliary states that do not exist yet (batchnorm running statistics before the first step) are skipped
+        tensors = dict((k, numpy.asarray(v.asnumpy() if hasattr(v, 'asnumpy') else v))
+                       for k, v in self._named_tensors() if v is not None)
         try:
             import h5py
         except ImportError:
@@ -90,6 +92,11 @@ class ModelBase(object):
             with numpy.load(path) as z:
                 stored = dict((k, z[k]) for k in z.files)
         for key, tensor in self._named_tensors():
+            if tensor is None:
+                if key in stored:          # an auxiliary state the checkpoint has and this model has not created yet
+                    import minpy.numpy as mnp
+                    self.aux_params[key[len('aux_param_'):]] = mnp.array(stored[key])
+                continue
             if key not in stored:
                 raise ParamsNameNotFoundError('%s not found in %s' % (key, path))
             tensor[:] = stored[key]

@@ -172,6 +172,52 @@ class Solver(object):
             out[name] = marray.wrap(raw.copy()) if hasattr(raw, 'copy') else value
         return out
 
+    # -- checkpoint / resume (the reference saves parameters only, model.py:141-163) --
+    def save_checkpoint(self, prefix):
+        """`<prefix>.params` (ModelBase.save: parameters + auxiliary states, device arrays are read
+        back) and `<prefix>.solver` (.npz: every optimizer state tensor and scalar per parameter --
+        velocity / cache / m, v, t, the decayed learning rate --, epoch, best score, the curves)."""
+        import numpy
+        self.model.save(prefix)
+        blob = {'epoch': numpy.asarray(self.epoch), 'best_val_acc': numpy.asarray(float(self.best_val_acc)),
+                'train_acc_history': numpy.asarray(self.train_acc_history, dtype=numpy.float64),
+                'val_acc_history': numpy.asarray(self.val_acc_history, dtype=numpy.float64),
+                'loss_history': numpy.asarray([float(l) for l in self.loss_history], dtype=numpy.float64)}
+        for name, config in self.optim_configs.items():
+            for key, value in config.items():
+                host = value.asnumpy() if hasattr(value, 'asnumpy') else value
+                blob['optim/%s/%s' % (name, key)] = numpy.asarray(host)
+        with open('%s.solver' % prefix, 'wb') as f:
+            numpy.savez(f, **blob)
+
+    def load_checkpoint(self, prefix):
+        """Inverse of `save_checkpoint` into an initialised solver (`init()` first): parameters are
+        written into the existing arrays, optimizer state is re-created in the bound array namespace
+        (so on the device under a CUDA policy), and a captured step graph is dropped -- its replays
+        read the old buffers -- so the next step captures afresh."""
+        import numpy
+        self.model.load(prefix)
+        with numpy.load('%s.solver' % prefix) as z:
+            blob = dict((k, z[k]) for k in z.files)
+        self.epoch = int(blob['epoch'])
+        self.best_val_acc = float(blob['best_val_acc'])
+        self.train_acc_history = [float(v) for v in blob['train_acc_history']]
+        self.val_acc_history = [float(v) for v in blob['val_acc_history']]
+        self.loss_history = [float(v) for v in blob['loss_history']]
+        for name in self.optim_configs:
+            config = dict(self.optim_config)
+            lead = 'optim/%s/' % name
+            for key, value in blob.items():
+                if not key.startswith(lead):
+                    continue
+                if value.ndim == 0:
+                    item = value.item()
+                    config[key[len(lead):]] = int(item) if value.dtype.kind in 'iu' else float(item)
+                else:
+                    config[key[len(lead):]] = np.array(value)
+            self.optim_configs[name] = config
+        self._step_graph = None
+
     def check_accuracy(self, dataiter, num_samples=None):
         """Classification: fraction of correct arg-max predictions; regression: mean loss.
         With `num_samples`, a random sub-iterator of that many rows is scored instead."""

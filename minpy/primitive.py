@@ -20,7 +20,8 @@ from minpy import tape as tape_mod
 from minpy.array import Value
 from minpy.array_variants import ArrayType, variants, variants_repr
 from minpy.utils import log
-from minpy_b200.cuda_array import CudaArray
+from minpy.context import Context
+from minpy_b200.cuda_array import CudaArray, _state as _cuda_state, enter_context_device, ensure_device
 from minpy_b200.lazy import ChainGrad
 
 _logger = log.get_logger(__name__)
@@ -70,13 +71,17 @@ def to_raw(value, vtype):
 
 class _TapedGrad(object):
     """What the tape calls: converts the stored gradient to this primitive's raw type."""
-    __slots__ = ('fn', 'vtype')
+    __slots__ = ('fn', 'vtype', 'dev')
 
     def __init__(self, fn, vtype):
         self.fn = fn
         self.vtype = vtype
+        # the VJP runs where the forward ran, also when backward is called outside the `with gpu(i):` scope
+        self.dev = _cuda_state['device'] if vtype == ArrayType.CUDA else None
 
     def __call__(self, grad_value):
+        if self.dev is not None and self.dev != _cuda_state['device']:
+            ensure_device(self.dev)
         return self.fn(to_raw(grad_value, self.vtype))
 
 
@@ -112,7 +117,15 @@ class Primitive(object):
     # -- argument conversion ----------------------------------------------------------------
     def _raw(self, arg, mutate):
         if isinstance(arg, Value):
-            return arg.get_data_mutable(self._type) if mutate else arg.get_data(self._type)
+            raw = arg.get_data_mutable(self._type) if mutate else arg.get_data(self._type)
+            if self._type == ArrayType.CUDA and isinstance(raw, CudaArray) and raw.buf.device != _cuda_state['device']:
+                # an operand that lives on another device than the `with gpu(i):` scope: a transient copy
+                # (MXNet raised here; the array itself stays where it is, minpy/context.py:92-98)
+                if mutate:
+                    raise ValueError('cannot mutate an array that lives on gpu(%d) from a gpu(%d) scope' % (
+                        raw.buf.device, _cuda_state['device']))
+                raw = raw.to_device(_cuda_state['device'])
+            return raw
         if isinstance(arg, list) and arg and isinstance(arg[0], Value):
             return [self._raw(item, mutate) for item in arg]     # np.stack / np.concatenate
         if self._type == ArrayType.CUDA:
@@ -132,6 +145,10 @@ class Primitive(object):
     def call(self, args, kwargs):
         """Run the forward function on raw data, wrap the result and, while a tape records,
         register the VJP closures of every argument that is being differentiated."""
+        if self._type == ArrayType.CUDA:
+            ctx = Context.default_ctx
+            if ctx.device_typeid == 2 or _cuda_state['device'] != _cuda_state['home']:
+                enter_context_device(ctx)     # `with gpu(i):` places the primitive on device i
         arg_values, kwarg_values = self._convert_args(args, kwargs)
         result_value = self._func(*arg_values, **kwarg_values)
         if isinstance(result_value, tuple):

@@ -13,6 +13,10 @@ namespace mc {
 void set_error(const char* fmt, ...);
 cudaStream_t stream();
 int sm_count();
+int device();
+// true exactly once per (mask, current device): per-device one-time set-up such as
+// cudaFuncSetAttribute, which applies to the current device only
+bool first_use_on_device(uint32_t* mask);
 void count_launch(int n = 1);
 // Non-null while a step graph is being captured (mc_graph_begin .. mc_graph_end): device counter
 // that the graph increments once per replay (1 on the first).  Kernels whose host-side

@@ -1040,8 +1040,8 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
     const uint32_t box[3] = {32, (uint32_t)p.BN, 1};
     rc = make_tmap(&tmW, wp, 3, dims, strides, box, false);
   }
-  static bool configured = false;
-  if (rc == 0 && !configured) { rc = set_max_smem((const void*)conv_igemm_kernel, "conv_igemm_kernel"); configured = rc == 0; }
+  static uint32_t configured = 0;      // function attributes are per device
+  if (rc == 0 && first_use_on_device(&configured)) rc = set_max_smem((const void*)conv_igemm_kernel, "conv_igemm_kernel");
   if (rc == 0) {
     const int64_t tiles = (int64_t)((p.g.total_chunks + 3) / 4) * ((Nout + p.BN - 1) / p.BN);
     const unsigned grid = (unsigned)(tiles < sm_count() ? tiles : sm_count());
@@ -1126,12 +1126,11 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
       CUtensorMap tmDy, tmX;
       int rc = make_act_tmap(&tmDy, dy, N, OH, OW, Fp, Fp, OW, hg.bw, hg.box_h, true, hg.box_n);
       if (rc == 0) rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, p.Nn, Wdim, hg.bw, hg.box_h + hg.TH - 1, true, hg.box_n);
-      static bool configured = false;
-      if (rc == 0 && !configured) {
+      static uint32_t configured = 0;
+      if (rc == 0 && first_use_on_device(&configured)) {
         rc = set_max_smem((const void*)conv_wgrad_halo_kernel<0>, "conv_wgrad_halo_kernel") ||
              set_max_smem((const void*)conv_wgrad_halo_kernel<1>, "conv_wgrad_halo_kernel") ||
              set_max_smem((const void*)conv_wgrad_halo_kernel<3>, "conv_wgrad_halo_kernel");
-        configured = rc == 0;
       }
       if (rc == 0) {
         const size_t smem = ring + 4096 + (2 * stages + 1) * 8 + 16 + 1024;
@@ -1208,8 +1207,8 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
   CUtensorMap tmDy, tmX;
   int rc = make_act_tmap(&tmDy, dy, N, OH, OW, Fp, Fp, OW, p.g.bw, p.g.bh, true);
   if (rc == 0) rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, p.Nn, Wdim, p.g.bw, p.g.bh, true);
-  static bool configured = false;
-  if (rc == 0 && !configured) { rc = set_max_smem((const void*)conv_wgrad_kernel, "conv_wgrad_kernel"); configured = rc == 0; }
+  static uint32_t configured = 0;
+  if (rc == 0 && first_use_on_device(&configured)) rc = set_max_smem((const void*)conv_wgrad_kernel, "conv_wgrad_kernel");
   if (rc == 0) {
     dim3 grid((unsigned)groups, (unsigned)splits, (unsigned)ftiles);
     conv_wgrad_kernel<<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, p);

@@ -696,18 +696,14 @@ int make_tmap_2d(CUtensorMap* map, const float* ptr, int64_t inner, int64_t oute
 template <int BN, int STAGES>
 static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits) {
   constexpr size_t SMEM = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) + (2 * STAGES + 1) * 8 + 16 + 1024;
-  static bool configured = false;
-  if (!configured) {
+  static uint32_t configured = 0;      // function attributes are per device
+  if (first_use_on_device(&configured))
     MC_CHECK(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    configured = true;
-  }
   dim3 grid((unsigned)((p.N + BN - 1) / BN), (unsigned)((p.M + BM - 1) / BM), (unsigned)splits);
   if (p.cluster > 1) {
-    static bool big_ok = false;
-    if (p.cluster > 8 && !big_ok) {
+    static uint32_t big_ok = 0;
+    if (p.cluster > 8 && first_use_on_device(&big_ok))
       MC_CHECK(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-      big_ok = true;
-    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = SMEM; cfg.stream = stream();
     cudaLaunchAttribute attr[1];
@@ -763,12 +759,13 @@ static int gemm_fp32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
 
 constexpr int kMaxFixupTiles = 16384;
 static int* splitk_counters() {
-  static int* g_counters = nullptr;
-  if (!g_counters) {
-    if (cudaMalloc((void**)&g_counters, sizeof(int) * kMaxFixupTiles) != cudaSuccess) { g_counters = nullptr; return nullptr; }
-    cudaMemset(g_counters, 0, sizeof(int) * kMaxFixupTiles);
+  static int* g_counters[16] = {};      // device memory: one block per device
+  int*& c = g_counters[device() & 15];
+  if (!c) {
+    if (cudaMalloc((void**)&c, sizeof(int) * kMaxFixupTiles) != cudaSuccess) { c = nullptr; return nullptr; }
+    cudaMemset(c, 0, sizeof(int) * kMaxFixupTiles);
   }
-  return g_counters;
+  return c;
 }
 
 static bool tma_ok(const float* p, int64_t ld) { return aligned16(p) && (ld % 4 == 0); }

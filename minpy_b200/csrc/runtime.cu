@@ -7,7 +7,9 @@
 namespace mc {
 
 static thread_local char g_err[512] = "";
-static cudaStream_t g_stream = nullptr;
+#define MC_MAX_DEVICES 16
+static cudaStream_t g_stream = nullptr;                  // the CURRENT device's compute stream
+static cudaStream_t g_streams[MC_MAX_DEVICES] = {};      // one blocking compute stream per device ever selected
 static int g_device = -1;
 static int g_sm_count = 148;
 static std::atomic<uint64_t> g_launches{0};
@@ -26,6 +28,13 @@ void set_error(const char* fmt, ...) {
 }
 cudaStream_t stream() { return g_stream; }
 int sm_count() { return g_sm_count; }
+int device() { return g_device; }
+bool first_use_on_device(uint32_t* mask) {
+  const uint32_t bit = 1u << (g_device < 0 ? 0 : g_device);
+  if (*mask & bit) return false;
+  *mask |= bit;
+  return true;
+}
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 const unsigned long long* graph_epoch() { return g_capturing ? g_epoch : nullptr; }
 
@@ -37,12 +46,22 @@ static int configure_device(int device) {
     set_error("libminpy_cuda is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
     return 3;
   }
+  if (device < 0 || device >= MC_MAX_DEVICES) {
+    set_error("device %d out of range (0..%d)", device, MC_MAX_DEVICES - 1);
+    return 2;
+  }
+  if (g_capturing && device != g_device) {
+    set_error("cannot change the device while a step graph is being captured");
+    return 2;
+  }
   g_sm_count = prop.multiProcessorCount;
   g_device = device;
   // The library's own stream.  A BLOCKING stream: it keeps the implicit ordering with the legacy
   // default stream (where torch.distributed enqueues the NCCL all-reduce), and unlike the legacy
   // stream it can be captured into a CUDA graph (mc_graph_begin).
-  if (g_stream == nullptr) MC_CHECK(cudaStreamCreateWithFlags(&g_stream, cudaStreamDefault));
+  // One such stream PER DEVICE (minpy/context.py:92-98 `with gpu(i):` places work on device i).
+  if (g_streams[device] == nullptr) MC_CHECK(cudaStreamCreateWithFlags(&g_streams[device], cudaStreamDefault));
+  g_stream = g_streams[device];
   // Keep freed blocks cached in the default mempool instead of returning them to the
   // driver at every synchronisation: training steps reuse the same sizes every step.
   cudaMemPool_t pool;
@@ -136,6 +155,18 @@ int mc_memcpy_d2h_async(void* dst, const void* src, size_t n) {
 }
 int mc_memcpy_d2d(void* dst, const void* src, size_t n) {
   if (n) MC_CHECK(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToDevice, g_stream));
+  return 0;
+}
+/* Copy between two devices of this process (`with gpu(i):` operands that live on another device,
+ * minpy/context.py:92-98).  The source device's stream is drained first -- the producer of `src` ran
+ * there --, then the copy is enqueued on the CURRENT device's stream. */
+int mc_memcpy_peer(void* dst, int dst_device, const void* src, int src_device, size_t n) {
+  MC_REQUIRE(!g_capturing, "mc_memcpy_peer inside a graph capture");
+  MC_REQUIRE(src_device >= 0 && src_device < MC_MAX_DEVICES && dst_device >= 0 && dst_device < MC_MAX_DEVICES,
+             "device out of range");
+  if (n == 0) return 0;
+  if (g_streams[src_device]) MC_CHECK(cudaStreamSynchronize(g_streams[src_device]));
+  MC_CHECK(cudaMemcpyPeerAsync(dst, dst_device, src, src_device, n, g_stream));
   return 0;
 }
 int mc_memset(void* dst, int byte, size_t n) {

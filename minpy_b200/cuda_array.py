@@ -20,17 +20,35 @@ _I32 = np.dtype('int32')
 _I64 = np.dtype('int64')
 _DTYPE_CODE = {_F32: 0, _I32: 1, _I64: 2, np.dtype('float64'): 3, np.dtype('uint8'): 4, np.dtype('bool'): 4}
 
-_state = {'device': None}
+_state = {'device': None, 'home': None}
 
 
 def ensure_device(device: int = None):
-    """Initialise the library on `device` (default: LOCAL_RANK or 0) once per process."""
-    if _state['device'] is None or (device is not None and device != _state['device']):
+    """Make `device` the library's current device (default: the process's home device = LOCAL_RANK
+    or 0, chosen at the first call).  Switching is cheap: each device keeps its own stream."""
+    cur = _state['device']
+    if cur is None or (device is not None and device != cur):
         import os
         dev = device if device is not None else int(os.environ.get('LOCAL_RANK', '0'))
         get_lib().mc_init(dev)
         _state['device'] = dev
-    return _state['device']
+        if _state['home'] is None:
+            _state['home'] = dev
+        return dev
+    return cur
+
+
+def enter_context_device(ctx):
+    """Select the device a MinPy context names (`with gpu(i):`, minpy/context.py:92-98); a cpu context
+    means "no placement request": the process's home device."""
+    want = ctx.cuda_device() if ctx is not None else None
+    if want is None:
+        want = _state['home']
+        if want is None:
+            return ensure_device()
+    if want != _state['device']:
+        ensure_device(want)
+    return want
 
 
 class BufferPool(object):
@@ -45,8 +63,9 @@ class BufferPool(object):
         """The graph is gone: the blocks rejoin the general free list."""
         self.released = True
         lists, self.lists = self.lists, {}
-        for nbytes, blocks in lists.items():
-            _Buffer._free_lists.setdefault(nbytes, []).extend(blocks)   # pylint: disable=protected-access
+        for key, blocks in lists.items():
+            nbytes = key[1] if isinstance(key, tuple) else key
+            _Buffer._free_lists.setdefault(key, []).extend(blocks)      # pylint: disable=protected-access
             _Buffer._cached_bytes += nbytes * len(blocks)               # pylint: disable=protected-access
 
 
@@ -59,7 +78,7 @@ class _Buffer(object):
     cudaMallocAsync pool gives, minus two ctypes round trips per temporary (a training step
     creates ~100 temporaries of a handful of distinct sizes).  The list is bounded; beyond the
     bound blocks really go back to the library."""
-    __slots__ = ('ptr', 'nbytes', 'pool')
+    __slots__ = ('ptr', 'nbytes', 'pool', 'device')
     _free_lists = {}
     _cached_bytes = 0
     _cache_limit = 32 << 30
@@ -70,14 +89,17 @@ class _Buffer(object):
     def __init__(self, nbytes):
         nbytes = (nbytes + 511) & ~511 if nbytes else 512
         self.nbytes = nbytes
+        dev = self.device = _state['device']
+        # blocks of a `with gpu(i):` scope off the home device live in free lists of their own
+        key = nbytes if dev == _state['home'] else (dev, nbytes)
         pool = self.pool = _Buffer._active_pool
         if pool is not None:
-            free = pool.lists.get(nbytes)
+            free = pool.lists.get(key)
             if free:
                 self.ptr = free.pop()
                 return
         else:
-            free = _Buffer._free_lists.get(nbytes)
+            free = _Buffer._free_lists.get(key)
             if free:
                 self.ptr = free.pop()
                 _Buffer._cached_bytes -= nbytes
@@ -96,17 +118,19 @@ class _Buffer(object):
     def __del__(self):
         try:
             pool = self.pool
+            key = self.nbytes if self.device == _state['home'] else (self.device, self.nbytes)
             if pool is not None and not pool.released:
                 # a block a captured graph writes on every replay: it may only ever be handed to
                 # another capture-time temporary of the same graph, whenever this object dies
-                free = pool.lists.get(self.nbytes)
+                free = pool.lists.get(key)
                 if free is None:
-                    free = pool.lists[self.nbytes] = []
+                    free = pool.lists[key] = []
                 free.append(self.ptr)
-            elif _Buffer._cached_bytes + self.nbytes <= _Buffer._cache_limit:
-                free = _Buffer._free_lists.get(self.nbytes)
+            elif _Buffer._cached_bytes + self.nbytes <= _Buffer._cache_limit or self.device != _state['device']:
+                # (a block of another device is always cached: freeing needs that device's stream)
+                free = _Buffer._free_lists.get(key)
                 if free is None:
-                    free = _Buffer._free_lists[self.nbytes] = []
+                    free = _Buffer._free_lists[key] = []
                 free.append(self.ptr)
                 _Buffer._cached_bytes += self.nbytes
             else:
@@ -116,12 +140,18 @@ class _Buffer(object):
 
     @staticmethod
     def trim():
-        """Return every cached block to the library's pool."""
+        """Return every cached block to the library's pool (each on the device that owns it)."""
         lists, _Buffer._free_lists = _Buffer._free_lists, {}
         _Buffer._cached_bytes = 0
-        for blocks in lists.values():
+        cur = _state['device']
+        for key, blocks in lists.items():
+            dev = key[0] if isinstance(key, tuple) else _state['home']
+            if dev != _state['device']:
+                ensure_device(dev)
             for ptr in blocks:
                 _Buffer._lib_free(ptr)
+        if cur is not None and cur != _state['device']:
+            ensure_device(cur)
 
 
 def _prod(shape):
@@ -187,8 +217,23 @@ class CudaArray(object):
         return self.size * self.dtype.itemsize
 
     @property
+    def device(self):
+        """CUDA ordinal of the device that holds the data."""
+        return self.buf.device
+
+    @property
     def context(self):
-        return ('gpu', _state['device'])
+        return ('gpu', self.buf.device)
+
+    def to_device(self, device):
+        """A copy on `device` of this process (the current device is switched to it)."""
+        device = int(device)
+        ensure_device(device)
+        if self.buf.device == device:
+            return self
+        out = CudaArray.empty(self.shape, self.dtype)
+        get_lib().mc_memcpy_peer(out.ptr, device, self.ptr, self.buf.device, self.nbytes)
+        return out
 
     def begin_readback(self):
         """Start copying a small value (<= 64 bytes, never written again) to the host on the
@@ -201,6 +246,8 @@ class CudaArray(object):
         return self
 
     def asnumpy(self):
+        if self.buf.device != _state['device']:
+            ensure_device(self.buf.device)        # the copy runs on the owning device's stream
         out = np.empty(self.shape, dtype=self.dtype)
         if self._readback is not None:
             lib = get_lib()

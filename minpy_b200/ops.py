@@ -816,3 +816,37 @@ def maxpool2d_nhwc_bwd(dy, idx, like, k, relu_y=None):
         L().mc_maxpool2d_nhwc_bwd(dy.data.ptr, idx.ptr, relu_y.data.ptr if relu_y is not None else None, dx.ptr,
                                   like.N, like.H, like.W, like.Cp, k, dy.H, dy.W)
     return Nhwc(dx, like.N, like.C, like.H, like.W, like.Cp)
+
+
+# ------------------------------------------------------- operators of the raw array type ----
+def _install_operators():
+    """The raw-array duck type MinPy's core and user-written VJPs / `customop('cuda')` bodies use
+    (arithmetic operators, unary minus, comparisons as methods, `.sum() .max() .T`,
+    `.broadcast_to`; indexing is `ops.getitem` -- a `__getitem__` would make NumPy treat the object as a sequence).  `==` stays identity (CudaArrays live in dicts / sets of the step
+    graph); elementwise equality is `ops.binary(L().MC_EQ, a, b)`."""
+    def bop(name):
+        def fwd(a, b):
+            return binary(getattr(L(), name), a, b)
+
+        def rev(a, b):
+            return binary(getattr(L(), name), b, a)
+        return fwd, rev
+    for py, mc in (('add', 'MC_ADD'), ('sub', 'MC_SUB'), ('mul', 'MC_MUL'), ('truediv', 'MC_DIV'), ('pow', 'MC_POW'),
+                   ('mod', 'MC_MOD')):
+        fwd, rev = bop(mc)
+        setattr(CudaArray, '__%s__' % py, fwd)
+        setattr(CudaArray, '__r%s__' % py, rev)
+    for py, mc in (('lt', 'MC_LT'), ('gt', 'MC_GT'), ('le', 'MC_LE'), ('ge', 'MC_GE')):
+        setattr(CudaArray, '__%s__' % py, bop(mc)[0])
+    CudaArray.__neg__ = lambda a: unary(L().MC_NEG, a)
+    CudaArray.__abs__ = lambda a: unary(L().MC_ABS, a)
+    CudaArray.sum = lambda a, axis=None, keepdims=False: reduce(L().MC_RED_SUM, a, axis, keepdims)
+    CudaArray.max = lambda a, axis=None, keepdims=False: reduce(L().MC_RED_MAX, a, axis, keepdims)
+    CudaArray.min = lambda a, axis=None, keepdims=False: reduce(L().MC_RED_MIN, a, axis, keepdims)
+    CudaArray.transpose = lambda a, *axes: transpose(a, axes[0] if len(axes) == 1 and not is_scalar(axes[0]) else (axes or None))
+    CudaArray.T = property(lambda a: transpose(a))
+    CudaArray.broadcast_to = lambda a, shape: broadcast_to(a, shape)
+    CudaArray.dot = lambda a, b: dot(a, b)
+
+
+_install_operators()

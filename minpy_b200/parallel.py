@@ -127,10 +127,11 @@ def _init_p2p_window(rank, world):
 
 class _WindowBuffer(object):
     """Stand-in for cuda_array._Buffer over the peer-memory window: owned by the library, never freed."""
-    __slots__ = ('ptr', 'nbytes', 'pool')
+    __slots__ = ('ptr', 'nbytes', 'pool', 'device')
 
     def __init__(self, ptr, nbytes):
-        self.ptr, self.nbytes, self.pool = ptr, nbytes, None
+        from .cuda_array import ensure_device
+        self.ptr, self.nbytes, self.pool, self.device = ptr, nbytes, None, ensure_device()
 
 
 def p2p_active():
