@@ -223,6 +223,15 @@ def _work_of(name, a):
         if name == 'mc_batchnorm_train_bwd':
             N, D = _i(a[8]), _i(a[9])
             return 0.0, 4.0 * (3 * N * D + 4 * D)
+        if name == 'mc_bn_dropout_fwd':
+            N, D = _i(a[10]), _i(a[11])
+            return 0.0, 4.0 * (2 * N * D + 6 * D)            # batchnorm fwd with the dropout mask folded in
+        if name == 'mc_bn_dropout_relu_bwd':
+            N, D = _i(a[9]), _i(a[10])
+            return 0.0, 4.0 * (3 * N * D + 5 * D)            # x, dy in; dx out; dgamma, dbeta, dbias
+        if name == 'mc_softmax_ce_fused':
+            r, c = _i(a[-2]), _i(a[-1])
+            return 0.0, 8.0 * r * c
         if name == 'mc_dropout':
             return 0.0, 8.0 * _i(a[2])
         if name == 'mc_vjp_chain':

@@ -153,6 +153,7 @@ enum mc_vjp_op {
   MC_VJP_RECIP_ANS,     /* -g * a * a               1/x (a = ans)                      */
   MC_VJP_GT0_A,         /* g * (a > 0)                                                  */
   MC_VJP_GE0_A,         /* g * (a >= 0)             layers.relu: maximum(0,x) passes g at x == 0 */
+  MC_VJP_SIGNPOS_A,     /* g * !signbit(a)          relu from its signed-zero OUTPUT (mc_gemm relu mode 2) */
   MC_VJP_COUNT
 };
 /* Operand addressing inside a step: how element i of the output maps to a / b. */
@@ -200,6 +201,11 @@ int mc_onehot(const int32_t* idx_i32, float* out, int64_t rows, int64_t cols);
  * Exactly one of labels_i32 / onehot is non-NULL. */
 int mc_softmax_ce_fwd(const float* x, const int32_t* labels_i32, const float* onehot,
                       float* probs, float* loss, int64_t rows, int64_t cols);
+/* softmax_loss forward AND its gradient in one call: probs (may be NULL), dx = (probs - y) / rows (may be
+ * NULL; the VJP ignores the upstream gradient, numpy_core.py:170-175, so it is known at forward time) and
+ * loss[0].  A classifier head (integer labels, cols <= 32, rows <= 16384) is ONE single-block launch. */
+int mc_softmax_ce_fused(const float* x, const int32_t* labels_i32, const float* onehot,
+                        float* probs, float* dx, float* loss, int64_t rows, int64_t cols);
 /* dx = (probs - y) / rows: `_softmax_output_grad` numpy_core.py:170-175 (ignores upstream g). */
 int mc_softmax_ce_bwd(const float* probs, const int32_t* labels_i32, const float* onehot,
                       float* dx, int64_t rows, int64_t cols);
@@ -229,6 +235,9 @@ int mc_concat_mid(const float* a, const float* b, float* out, int64_t outer, int
 /* C(M,N) = op(A) . op(B) [+ bias(N,)] [relu] [+ C if accumulate]; row-major, leading
  * dimensions in elements.  np.dot and its two VJPs: numpy_core.py:224-225,
  * mxnet_core.py:112-114; bias/relu epilogue = nn/layers.py:27,41.
+ * relu: 0 none, 1 max(0, v), 2 the same values with the sign of the pre-activation kept in the zero's sign
+ * bit (-0.0f where v < 0): the VJP of layers.relu passes the gradient where x >= 0 INCLUDING x == 0
+ * (numpy_core.py:284-286), and a fused affine+relu never stores x.
  * precision: 0 = FP32 CUDA-core (exact-accumulate cross-check), 1 = TF32 tcgen05/TMEM
  * fed by TMA (FP32 accumulate). Falls back from 1 to 0 only for shapes TMA cannot
  * describe (row pitch not a multiple of 16 bytes). */
@@ -274,6 +283,26 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
 int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma,
                            const float* save_mean, const float* save_invstd,
                            float* dx, float* dgamma, float* dbeta, int64_t N, int64_t D);
+/* The hidden-layer block of examples/nn/mlp_bn_dropout.py:41-54 -- affine, relu, batchnorm, dropout -- in
+ * TWO forward and ONE elementwise backward launch (plus the two VJP GEMMs):
+ *   forward : mc_gemm(..., relu = 2)  then  mc_bn_dropout_fwd  = batchnorm (train) with the dropout mask
+ *             applied at the store (mask of element i = lane i & 3 of Philox(seed)(offset + i / 4), as mc_dropout);
+ *   backward: mc_bn_dropout_relu_bwd  = dropout VJP (mask regenerated while dy is loaded, `dropout` != 0),
+ *             batchnorm VJP (nn/layers.py:93-110 differentiated), and -- `relu_signed` != 0, x produced by
+ *             mc_gemm relu mode 2 -- the relu VJP (numpy_core.py:284-286) plus the column sums of the result,
+ *             i.e. the bias gradient of the affine layer (nn/layers.py:27), into dbias.
+ * Small batches only (N <= 1024, N*D <= 2^20, D % 8 == 0: mc_bn_fused_supported); otherwise the callers
+ * compose mc_batchnorm_train_* / mc_dropout / mc_vjp_chain / mc_reduce. */
+int mc_bn_fused_supported(int64_t N, int64_t D, int* ok);
+int mc_bn_dropout_fwd(const float* x, const float* gamma, const float* beta,
+                      const float* running_mean, const float* running_var,
+                      float* out, float* new_running_mean, float* new_running_var,
+                      float* save_mean, float* save_invstd,
+                      int64_t N, int64_t D, float eps, float momentum, float p, uint64_t seed, uint64_t offset);
+int mc_bn_dropout_relu_bwd(const float* x, const float* dy, const float* gamma,
+                           const float* save_mean, const float* save_invstd,
+                           float* dx, float* dgamma, float* dbeta, float* dbias, int64_t N, int64_t D,
+                           int dropout, float p, uint64_t seed, uint64_t offset, int relu_signed);
 /* test mode, nn/layers.py:111-113. */
 int mc_batchnorm_test_fwd(const float* x, const float* gamma, const float* beta,
                           const float* running_mean, const float* running_var,

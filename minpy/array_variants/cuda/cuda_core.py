@@ -22,7 +22,7 @@ import numpy as np
 from minpy_b200 import ops
 from minpy_b200._lib import parse_enums
 from minpy_b200.cuda_array import CudaArray
-from minpy_b200.lazy import ChainGrad, as_chain, concrete, FULL, ROW, COL, ONE
+from minpy_b200.lazy import ChainGrad, LazyArray, as_chain, concrete, drop_step, DROPOUT, FULL, ROW, COL, ONE
 
 E = parse_enums()
 _prod = ops._prod  # pylint: disable=protected-access
@@ -479,12 +479,35 @@ def onehot_encode(indices, out):
 # ======================================================================================
 #  fused layers (picked by minpy.nn.layers when bound)
 # ======================================================================================
+import os as _os
+
+# Forward fusion across layer calls (MINPY_FUSE_FORWARD=0 turns it off): `layers.affine` and
+# `layers.batchnorm` return LazyArrays, so that a relu / dropout called on them next is absorbed into the
+# producing kernel -- the hidden block affine -> relu -> batchnorm -> dropout of mlp_bn_dropout.py:41-54 is
+# TWO launches forward (GEMM with bias + relu epilogue; batchnorm with the dropout mask applied at the store)
+# and its elementwise backward ONE (dropout + batchnorm + relu VJPs and the bias gradient, see _batchnorm_vjp).
+_FUSE_FORWARD = _os.environ.get('MINPY_FUSE_FORWARD', '1') != '0'
+_RELU_SIGNED = ('relu_signed',)     # tag of a relu output whose zeros carry the sign of the pre-activation
+
+
+def _relu_done(g, relu_out):
+    """True when gradient `g` (of `relu_out`) already had relu's mask applied by batchnorm's fused VJP."""
+    tag = g._tag if isinstance(g, CudaArray) else None  # pylint: disable=protected-access
+    return tag is not None and tag[0] == 'relu_done' and tag[1] is relu_out
+
+
 def fused_affine(x, w, b):
-    """dot(x, w) + b in one GEMM with a bias epilogue (nn/layers.py:27)."""
-    return ops.gemm(ops.as_f32(x), w, bias=b.reshape((b.size,)))
+    """dot(x, w) + b in one GEMM with a bias epilogue (nn/layers.py:27); evaluated lazily so that a
+    relu called on the result rides in the same epilogue."""
+    x = ops.as_f32(x)
+    b1 = b.reshape((b.size,))
+    if not _FUSE_FORWARD or x.ndim != 2 or w.ndim != 2 or x.shape[1] != w.shape[0] or b1.size != w.shape[1]:
+        return ops.gemm(x, w, bias=b1)
+    return LazyArray((x.shape[0], w.shape[1]), lambda self: self.bind(ops.gemm(x, w, bias=b1)), saved=('affine', x, w, b1))
 
 
 def _affine_vjps():
+    # (`ans` may be a LazyArray that was never evaluated: only its shape is used)
     def dx(ans, x, w, b):  # pylint: disable=unused-argument
         return lambda g: ops.gemm(concrete(g, ans.shape), w, trans_b=True)
 
@@ -492,25 +515,102 @@ def _affine_vjps():
         return lambda g: ops.gemm(ops.as_f32(x), concrete(g, ans.shape), trans_a=True)
 
     def db(ans, x, w, b):  # pylint: disable=unused-argument
-        return lambda g: ops.reduce(E['MC_RED_SUM'], concrete(g, ans.shape), 0).reshape(b.shape)
+        def vjp(g):
+            tag = g._tag if isinstance(g, CudaArray) else None  # pylint: disable=protected-access
+            if tag is not None and tag[0] == 'relu_done':
+                return tag[2].reshape(b.shape)          # column sums computed by batchnorm's fused VJP
+            return ops.reduce(E['MC_RED_SUM'], concrete(g, ans.shape), 0).reshape(b.shape)
+        return vjp
     return dx, dw, db
 
 
 def fused_relu(x):
-    """maximum(0, x) (nn/layers.py:41)."""
+    """maximum(0, x) (nn/layers.py:41).  On a pending affine: the GEMM runs now with bias + relu in its
+    epilogue (relu mode 2: zeros keep the sign of the pre-activation, which the VJP needs)."""
+    if type(x) is LazyArray and x.pending() and type(x._saved) is tuple and x._saved[0] == 'affine':  # pylint: disable=protected-access,unidiomatic-typecheck
+        _, xx, w, b1 = x._saved  # pylint: disable=protected-access
+        out = ops.gemm(xx, w, bias=b1, relu=2)
+        out._tag = _RELU_SIGNED  # pylint: disable=protected-access
+        return out
     return ops.unary(E['MC_RELU'], x)
 
 
 def _relu_vjp(ans, x):
+    if ans._tag is _RELU_SIGNED:  # pylint: disable=protected-access
+        # fused with its affine: x was never computed; g * !signbit(ans) == g * (x >= 0)
+        def vjp(g):
+            if _relu_done(g, ans):
+                return g
+            return as_chain(g, ans.shape).then(E['MC_VJP_SIGNPOS_A'], ans, FULL)
+        return vjp
     # g * (x == ans): passes g where x >= 0, including x == 0 (numpy_core.py:284-286)
     return lambda g: as_chain(g, ans.shape).then(E['MC_VJP_GE0_A'], x, FULL)
 
 
+class _BnPending(object):
+    """One train-mode batchnorm call whose kernel has not run yet: its three results (out, new running
+    mean, new running variance) are LazyArrays that share this record."""
+    __slots__ = ('x', 'gamma', 'beta', 'rm', 'rv', 'eps', 'momentum', 'out', 'new_rm', 'new_rv', 'save_mean',
+                 'save_invstd', 'stats_done', 'drop')
+
+    def __init__(self, x, gamma, beta, rm, rv, eps, momentum):
+        self.x, self.gamma, self.beta, self.rm, self.rv = x, gamma, beta, rm, rv
+        self.eps, self.momentum = float(eps), float(momentum)
+        self.save_mean = self.save_invstd = None
+        self.stats_done = False
+        self.drop = None            # (prob, seed, offset) of the dropout fused behind it
+
+    def _launch(self, out, drop):
+        lib = ops.L()
+        x = self.x
+        N, D = x.shape
+        new_rm, new_rv = CudaArray.empty(self.rm.shape), CudaArray.empty(self.rv.shape)
+        save_mean, save_invstd = CudaArray.empty((D,)), CudaArray.empty((D,))
+        if drop is None:
+            lib.mc_batchnorm_train_fwd(x.ptr, self.gamma.ptr, self.beta.ptr, self.rm.ptr, self.rv.ptr, out.ptr,
+                                       new_rm.ptr, new_rv.ptr, save_mean.ptr, save_invstd.ptr, N, D, self.eps,
+                                       self.momentum)
+        else:
+            lib.mc_bn_dropout_fwd(x.ptr, self.gamma.ptr, self.beta.ptr, self.rm.ptr, self.rv.ptr, out.ptr,
+                                  new_rm.ptr, new_rv.ptr, save_mean.ptr, save_invstd.ptr, N, D, self.eps,
+                                  self.momentum, float(drop[0]), int(drop[1]), int(drop[2]))
+        if not self.stats_done:
+            self.stats_done = True
+            self.save_mean, self.save_invstd = save_mean, save_invstd
+            for lazy, value in ((self.new_rm, new_rm), (self.new_rv, new_rv)):
+                if lazy.pending():
+                    lazy.bind(value)
+
+    def run_plain(self, _which=None):
+        """Evaluate everything that is still pending with the un-fused kernel."""
+        out = CudaArray.empty(self.x.shape)
+        self._launch(out, None)
+        if self.out.pending():
+            self.out.bind(out)
+
+    def run_with_dropout(self, prob, seed, offset):
+        """The fused launch: returns dropout(batchnorm(x)); `out` itself stays unevaluated."""
+        y = CudaArray.empty(self.x.shape)
+        self.drop = (float(prob), int(seed), int(offset))
+        self._launch(y, self.drop)
+        return y
+
+
+def _bn_fusable(N, D):
+    return N <= 1024 and D % 8 == 0 and N * D <= (1 << 20)      # mc_bn_fused_supported
+
+
 def fused_batchnorm(x, gamma, beta, running_mean, running_var, eps, momentum):
-    """Train-mode batchnorm of nn/layers.py:93-110 in two kernels: returns
-    (out, new_running_mean, new_running_var)."""
+    """Train-mode batchnorm of nn/layers.py:93-110: returns (out, new_running_mean, new_running_var).
+    Evaluated lazily so that a dropout called on `out` next is applied inside the same kernel."""
     lib = ops.L()
     N, D = x.shape
+    if _FUSE_FORWARD and _bn_fusable(N, D) and type(x) is not LazyArray:  # pylint: disable=unidiomatic-typecheck
+        pend = _BnPending(x, gamma, beta, running_mean, running_var, eps, momentum)
+        pend.out = LazyArray((N, D), pend.run_plain, saved=pend)
+        pend.new_rm = LazyArray(running_mean.shape, pend.run_plain)
+        pend.new_rv = LazyArray(running_var.shape, pend.run_plain)
+        return pend.out, pend.new_rm, pend.new_rv
     out = CudaArray.empty((N, D))
     new_rm, new_rv = CudaArray.empty(running_mean.shape), CudaArray.empty(running_var.shape)
     save_mean, save_invstd = CudaArray.empty((D,)), CudaArray.empty((D,))
@@ -523,17 +623,44 @@ def fused_batchnorm(x, gamma, beta, running_mean, running_var, eps, momentum):
 
 def _batchnorm_vjp(ans, x, gamma, beta, running_mean, running_var, eps, momentum):  # pylint: disable=unused-argument
     out = ans[0]
-    save_mean, save_invstd = out._saved  # pylint: disable=protected-access
+    saved = out._saved  # pylint: disable=protected-access
 
     def vjp(gs):
         g = gs[0] if isinstance(gs, tuple) else gs
         if g is None:
             return [0.0, 0.0, 0.0]
-        g = concrete(g, out.shape)
+        lib = ops.L()
         N, D = x.shape
+        if isinstance(saved, _BnPending):
+            if not saved.stats_done:
+                saved.run_plain()
+            save_mean, save_invstd = saved.save_mean, saved.save_invstd
+        else:
+            save_mean, save_invstd = saved
         dx, dgamma, dbeta = CudaArray.empty((N, D)), CudaArray.empty(gamma.shape), CudaArray.empty(beta.shape)
-        ops.L().mc_batchnorm_train_bwd(x.ptr, g.ptr, gamma.ptr, save_mean.ptr, save_invstd.ptr, dx.ptr,
-                                       dgamma.ptr, dbeta.ptr, N, D)
+        if not _bn_fusable(N, D):
+            g = concrete(g, out.shape)
+            lib.mc_batchnorm_train_bwd(x.ptr, g.ptr, gamma.ptr, save_mean.ptr, save_invstd.ptr, dx.ptr, dgamma.ptr,
+                                       dbeta.ptr, N, D)
+            return [dx, dgamma, dbeta]
+        # one kernel for: the VJP of the dropout behind this batchnorm (when the incoming gradient is exactly
+        # "dy times that dropout's keep-mask": the mask is regenerated while dy is loaded), the batchnorm VJP,
+        # and -- when x is the signed-zero output of a fused affine+relu -- the relu VJP plus the bias
+        # gradient of that affine layer (column sums of the result)
+        drop = None
+        if isinstance(g, ChainGrad) and len(g.steps) == 1 and g.steps[0][0] == DROPOUT and g.g is not None \
+                and g.g_mode == FULL and g.g_scalar == 1.0 and g.g.size == N * D:
+            drop, g = g.steps[0], g.g
+        else:
+            g = concrete(g, out.shape)
+        relu_src = x._tag is _RELU_SIGNED  # pylint: disable=protected-access
+        dbias = CudaArray.empty((D,)) if relu_src else None
+        lib.mc_bn_dropout_relu_bwd(x.ptr, g.ptr, gamma.ptr, save_mean.ptr, save_invstd.ptr, dx.ptr, dgamma.ptr, dbeta.ptr,
+                                   dbias.ptr if relu_src else None, N, D, 1 if drop is not None else 0,
+                                   drop[5] if drop is not None else 0.0, drop[1] if drop is not None else 0,
+                                   drop[3] if drop is not None else 0, 1 if relu_src else 0)
+        if relu_src:
+            dx._tag = ('relu_done', x, dbias)  # pylint: disable=protected-access
         return [dx, dgamma, dbeta]
     return vjp
 
@@ -564,7 +691,12 @@ def _batchnorm_test_vjp(ans, x, gamma, beta, running_mean, running_var, eps):  #
 
 
 def fused_dropout(x, prob, seed, offset):
-    """x * (u > prob), not rescaled (nn/layers.py:141-144); u from Philox(seed, offset)."""
+    """x * (u > prob), not rescaled (nn/layers.py:141-144); u from Philox(seed, offset).  On a pending
+    batchnorm: that batchnorm's kernel runs now and applies the mask at its store."""
+    if type(x) is LazyArray and x.pending() and isinstance(x._saved, _BnPending) and not x._saved.stats_done:  # pylint: disable=protected-access,unidiomatic-typecheck
+        out = x._saved.run_with_dropout(prob, seed, offset)  # pylint: disable=protected-access
+        out._saved = ('after_bn',)  # pylint: disable=protected-access
+        return out
     out = CudaArray.empty(x.shape)
     if x.size:
         ops.L().mc_dropout(x.ptr, out.ptr, x.size, float(prob), int(seed), int(offset))
@@ -572,6 +704,10 @@ def fused_dropout(x, prob, seed, offset):
 
 
 def _dropout_vjp(ans, x, prob, seed, offset):  # pylint: disable=unused-argument
+    if ans._saved == ('after_bn',):  # pylint: disable=protected-access
+        # fused behind a batchnorm: leave the mask as a marker factor; that batchnorm's VJP applies it
+        return lambda g: as_chain(g, ans.shape).then(*drop_step(prob, seed, offset))
+
     def vjp(g):
         g = concrete(g, ans.shape)
         return fused_dropout(g, prob, seed, offset)      # same (seed, offset) => same mask
@@ -583,31 +719,23 @@ def fused_softmax_loss(x, label):
     `label` is (N,) class indices or (N, C) one-hot / soft targets."""
     lib = ops.L()
     rows, cols = x.shape
-    probs = CudaArray.empty((rows, cols))
     loss = CudaArray.empty(())
+    # the VJP ignores its upstream gradient (numpy_core.py:170-175), so dx = (p - y) / N is known now: the
+    # forward kernel writes it instead of the probabilities and the backward pass launches nothing
+    dx = CudaArray.empty((rows, cols))
     if label.ndim == 1:
-        lab = ops.as_i32(label)
-        lib.mc_softmax_ce_fwd(x.ptr, lab.ptr, None, probs.ptr, loss.ptr, rows, cols)
+        lib.mc_softmax_ce_fused(x.ptr, ops.as_i32(label).ptr, None, None, dx.ptr, loss.ptr, rows, cols)
     else:
-        lab = ops.as_f32(label)
-        lib.mc_softmax_ce_fwd(x.ptr, None, lab.ptr, probs.ptr, loss.ptr, rows, cols)
-    loss._saved = (probs, lab)  # pylint: disable=protected-access
+        lib.mc_softmax_ce_fused(x.ptr, None, ops.as_f32(label).ptr, None, dx.ptr, loss.ptr, rows, cols)
+    loss._saved = dx  # pylint: disable=protected-access
     return loss
 
 
 def _softmax_loss_vjp(ans, x, label):  # pylint: disable=unused-argument
-    probs, lab = ans._saved  # pylint: disable=protected-access
-
-    def vjp(_g):
-        # (p - y) / N whatever the upstream gradient: the reference's softmax_output VJP
-        # discards it (numpy_core.py:170-175, SURVEY appendix A.1)
-        dx = CudaArray.empty(probs.shape)
-        if lab.ndim == 1:
-            ops.L().mc_softmax_ce_bwd(probs.ptr, lab.ptr, None, dx.ptr, probs.shape[0], probs.shape[1])
-        else:
-            ops.L().mc_softmax_ce_bwd(probs.ptr, None, lab.ptr, dx.ptr, probs.shape[0], probs.shape[1])
-        return dx
-    return vjp
+    dx = ans._saved  # pylint: disable=protected-access
+    # (p - y) / N whatever the upstream gradient: the reference's softmax_output VJP discards it
+    # (numpy_core.py:170-175, SURVEY appendix A.1); computed by the forward kernel
+    return lambda _g: dx
 
 
 def fused_lstm_step(x, prev_h, prev_c, Wx, Wh, b):

@@ -118,12 +118,12 @@ class Primitive(object):
     def _raw(self, arg, mutate):
         if isinstance(arg, Value):
             raw = arg.get_data_mutable(self._type) if mutate else arg.get_data(self._type)
-            if self._type == ArrayType.CUDA and isinstance(raw, CudaArray) and raw.buf.device != _cuda_state['device']:
+            if self._type == ArrayType.CUDA and isinstance(raw, CudaArray) and raw.device != _cuda_state['device']:
                 # an operand that lives on another device than the `with gpu(i):` scope: a transient copy
                 # (MXNet raised here; the array itself stays where it is, minpy/context.py:92-98)
                 if mutate:
                     raise ValueError('cannot mutate an array that lives on gpu(%d) from a gpu(%d) scope' % (
-                        raw.buf.device, _cuda_state['device']))
+                        raw.device, _cuda_state['device']))
                 raw = raw.to_device(_cuda_state['device'])
             return raw
         if isinstance(arg, list) and arg and isinstance(arg[0], Value):

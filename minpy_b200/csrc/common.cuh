@@ -52,6 +52,36 @@ const unsigned long long* graph_epoch();
     mc::count_launch();                                                             \
   } while (0)
 
+// ---- programmatic dependent launch (PDL) ------------------------------------------------
+// A training step is 30-450 small dependent kernels; between two of them the GPU drains, the next
+// grid is launched, its CTAs are scheduled and run their prologue (barrier init, TMEM allocation,
+// descriptor prefetch) -- 1-3 us during which the SMs idle.  Every kernel of this library is launched
+// with programmaticStreamSerializationAllowed and starts with pdl_sync(): `launch_dependents` lets the
+// NEXT grid's CTAs become resident as soon as all of this grid's CTAs have started, and `wait` holds
+// them until the previous grid has completed and flushed its memory, so the launch ramp and prologue
+// of kernel i+1 overlap the tail of kernel i.  Correctness rule: no global memory access before
+// pdl_sync() (kernel parameters live in the constant bank and are fine).  Works in eager streams and
+// inside captured graphs (programmatic dependency edges).  MC_PDL=0 turns the attribute off.
+bool pdl_enabled();
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_trigger(); pdl_wait(); }
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream();
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // Grid sizing for bandwidth-bound grid-stride kernels: enough CTAs to fill every SM
 // `waves` times over, never more than the work needs.
 inline int grid_for(int64_t work_items, int per_block, int ctas_per_sm = 8) {
@@ -87,6 +117,17 @@ __device__ __forceinline__ float nanmax(float a, float b) {
 }
 __device__ __forceinline__ float nanmin(float a, float b) {
   return (a != a) ? a : ((b != b) ? b : fminf(a, b));
+}
+
+// GEMM epilogue relu.  mode 1: max(0, v), NaN propagates.  mode 2 ("signed zero"): the same VALUES, but a
+// negative pre-activation is stored as -0.0f and a zero one as +0.0f, so the sign bit of the output still
+// tells x < 0 from x >= 0: layers.relu passes the gradient where x >= 0, INCLUDING x == 0
+// (numpy_core.py:284-286), and a fused affine+relu never materialises x.  -0.0f == 0.0f in every
+// comparison and sum downstream.
+__device__ __forceinline__ float relu_apply(float v, int mode) {
+  if (v != v) return v;
+  if (v < 0.f) return mode == 2 ? -0.0f : 0.f;
+  return v == 0.f ? 0.f : v;
 }
 
 // Block-wide reduction through shared memory; `Op` is a functor with ::identity() and

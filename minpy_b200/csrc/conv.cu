@@ -16,6 +16,7 @@ __global__ void __launch_bounds__(CV_THREADS) conv_fwd_kernel(const float* __res
                                                               const float* __restrict__ bias, float* __restrict__ y, int C,
                                                               int H, int W, int F, int KH, int KW, int stride, int pad,
                                                               int OH, int OW, int relu) {
+  mc::pdl_sync();
   extern __shared__ float wsm[];
   const int f = blockIdx.y, n = blockIdx.z;
   const int wsz = C * KH * KW;
@@ -48,6 +49,7 @@ __global__ void __launch_bounds__(CV_THREADS) conv_fwd_kernel(const float* __res
 __global__ void __launch_bounds__(CV_THREADS) conv_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
                                                                 float* __restrict__ dx, int C, int H, int W, int F, int KH,
                                                                 int KW, int stride, int pad, int OH, int OW) {
+  mc::pdl_sync();
   extern __shared__ float wsm[];  // w[:, c, :, :] -> (F, KH, KW)
   const int c = blockIdx.y, n = blockIdx.z;
   const int ksz = KH * KW;
@@ -87,6 +89,7 @@ __global__ void __launch_bounds__(CV_THREADS) conv_wgrad_kernel(const float* __r
                                                                 float* __restrict__ part, int N, int C, int H, int W, int F,
                                                                 int KH, int KW, int stride, int pad, int OH, int OW,
                                                                 int n_per_split) {
+  mc::pdl_sync();
   __shared__ float smem[32];
   const int idx = blockIdx.x;  // ((f*C + c)*KH + kh)*KW + kw
   const int kw = idx % KW, kh = (idx / KW) % KH, c = (idx / (KW * KH)) % C, f = idx / (KW * KH * C);
@@ -109,6 +112,7 @@ __global__ void __launch_bounds__(CV_THREADS) conv_wgrad_kernel(const float* __r
 __global__ void __launch_bounds__(CV_THREADS) maxpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
                                                                  int32_t* __restrict__ amax, int64_t NC, int H, int W, int KH,
                                                                  int KW, int stride, int OH, int OW) {
+  mc::pdl_sync();
   const int64_t n = NC * OH * OW;
   const int64_t gs = (int64_t)gridDim.x * CV_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * CV_THREADS + threadIdx.x; t < n; t += gs) {
@@ -135,6 +139,7 @@ __global__ void __launch_bounds__(CV_THREADS) maxpool_fwd_kernel(const float* __
 __global__ void __launch_bounds__(CV_THREADS) maxpool_bwd_kernel(const float* __restrict__ dy, const int32_t* __restrict__ amax,
                                                                  float* __restrict__ dx, int64_t NC, int H, int W, int OH,
                                                                  int OW) {
+  mc::pdl_sync();
   const int64_t n = NC * OH * OW;
   const int64_t gs = (int64_t)gridDim.x * CV_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * CV_THREADS + threadIdx.x; t < n; t += gs) {
@@ -193,7 +198,7 @@ int mc_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, i
   const size_t smem = sizeof(float) * C * KH * KW;
   MC_REQUIRE(smem <= 48 * 1024, "filter slice exceeds 48 KB of shared memory");
   dim3 grid((unsigned)((OH * OW + CV_THREADS - 1) / CV_THREADS), (unsigned)F, (unsigned)N);
-  conv_fwd_kernel<<<grid, CV_THREADS, smem, stream()>>>(x, w, bias, y, (int)C, (int)H, (int)W, (int)F, (int)KH, (int)KW,
+  mc::launch(conv_fwd_kernel, grid, CV_THREADS, smem, x, w, bias, y, (int)C, (int)H, (int)W, (int)F, (int)KH, (int)KW,
                                                         (int)stride, (int)pad, (int)OH, (int)OW, relu);
   MC_LAUNCHED();
   return 0;
@@ -218,7 +223,7 @@ int mc_conv2d_dgrad(const float* dy, const float* w, float* dx, int64_t N, int64
   const size_t smem = sizeof(float) * F * KH * KW;
   MC_REQUIRE(smem <= 48 * 1024, "filter slice exceeds 48 KB of shared memory");
   dim3 grid((unsigned)((H * W + CV_THREADS - 1) / CV_THREADS), (unsigned)C, (unsigned)N);
-  conv_dgrad_kernel<<<grid, CV_THREADS, smem, stream()>>>(dy, w, dx, (int)C, (int)H, (int)W, (int)F, (int)KH, (int)KW,
+  mc::launch(conv_dgrad_kernel, grid, CV_THREADS, smem, dy, w, dx, (int)C, (int)H, (int)W, (int)F, (int)KH, (int)KW,
                                                           (int)stride, (int)pad, (int)OH, (int)OW);
   MC_LAUNCHED();
   return 0;
@@ -255,7 +260,7 @@ int mc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* dbias, in
     float* part = dw;
     if (splits > 1) MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * splits * nw, stream()));
     dim3 grid((unsigned)nw, (unsigned)splits);
-    conv_wgrad_kernel<<<grid, CV_THREADS, 0, stream()>>>(x, dy, part, (int)N, (int)C, (int)H, (int)W, (int)F, (int)KH, (int)KW,
+    mc::launch(conv_wgrad_kernel, grid, CV_THREADS, 0, x, dy, part, (int)N, (int)C, (int)H, (int)W, (int)F, (int)KH, (int)KW,
                                                          (int)stride, (int)pad, (int)OH, (int)OW, n_per);
     MC_LAUNCHED();
     if (splits > 1) {
@@ -287,7 +292,7 @@ int mc_maxpool2d_fwd(const float* x, float* y, int32_t* argmax, int64_t NC, int6
   MC_REQUIRE(OH > 0 && OW > 0, "pool kernel larger than input");
   const int64_t n = NC * OH * OW;
   if (n <= 0) return 0;
-  maxpool_fwd_kernel<<<grid_for(n, CV_THREADS), CV_THREADS, 0, stream()>>>(x, y, argmax, NC, (int)H, (int)W, (int)KH, (int)KW,
+  mc::launch(maxpool_fwd_kernel, grid_for(n, CV_THREADS), CV_THREADS, 0, x, y, argmax, NC, (int)H, (int)W, (int)KH, (int)KW,
                                                                         (int)stride, (int)OH, (int)OW);
   MC_LAUNCHED();
   return 0;
@@ -297,7 +302,7 @@ int mc_maxpool2d_bwd(const float* dy, const int32_t* argmax, float* dx, int64_t 
                      int64_t OW) {
   const int64_t n = NC * OH * OW;
   if (n <= 0) return 0;
-  maxpool_bwd_kernel<<<grid_for(n, CV_THREADS), CV_THREADS, 0, stream()>>>(dy, argmax, dx, NC, (int)H, (int)W, (int)OH, (int)OW);
+  mc::launch(maxpool_bwd_kernel, grid_for(n, CV_THREADS), CV_THREADS, 0, dy, argmax, dx, NC, (int)H, (int)W, (int)OH, (int)OW);
   MC_LAUNCHED();
   return 0;
 }

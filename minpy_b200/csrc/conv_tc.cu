@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  mc::pdl_sync();      // prologue done (on-chip state only); global memory from here on
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
@@ -376,6 +377,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
 __global__ void __launch_bounds__(256) conv_pack_weights_kernel(const float* __restrict__ w, float* __restrict__ wp, int F,
                                                                 int C, int KH, int KW, int Cp, int taps, int Nn, int Kp,
                                                                 int mode) {
+  mc::pdl_sync();
   const int64_t total = (int64_t)taps * Nn * Kp;
   for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
     const int k = (int)(i % Kp);
@@ -465,6 +467,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  mc::pdl_sync();      // prologue done (on-chip state only); global memory from here on
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
@@ -625,6 +628,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  mc::pdl_sync();      // prologue done (on-chip state only); global memory from here on
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
@@ -736,6 +740,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_reduce_kernel(const float* __r
                                                                 const float* __restrict__ wsb, float* __restrict__ dbias,
                                                                 int splits, int taps, int F, int Nn, int C, int KH, int KW,
                                                                 int Cp, int merged, int wblocks) {
+  mc::pdl_sync();
   __shared__ float part[8][33];
   const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
   const bool bias_block = (int)blockIdx.x >= wblocks;
@@ -772,6 +777,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_reduce_kernel(const float* __r
 // so that both the NCHW reads (along w) and the NHWC writes (along c) are coalesced.
 __global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restrict__ x, float* __restrict__ y, int N, int C,
                                                            int H, int W, int Cp, int wpad) {
+  mc::pdl_sync();
   __shared__ float tile[32][33];
   const int Wp = W + 2 * wpad;
   const int n = blockIdx.z / H, h = blockIdx.z % H;
@@ -795,6 +801,7 @@ __global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restri
 // y (N, C, H, W) <- x (N, H, W, Cp)
 __global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* __restrict__ x, float* __restrict__ y, int N, int C,
                                                            int H, int W, int Cp) {
+  mc::pdl_sync();
   __shared__ float tile[32][33];
   const int n = blockIdx.z / H, h = blockIdx.z % H;
   const int c0 = blockIdx.y * 32, w0 = blockIdx.x * 32;
@@ -819,6 +826,7 @@ __global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* __restri
 __global__ void __launch_bounds__(256) maxpool_nhwc_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
                                                                uint8_t* __restrict__ idx, int N, int H, int W, int Cp, int KH,
                                                                int KW, int stride, int OH, int OW) {
+  mc::pdl_sync();
   const int64_t total = (int64_t)N * OH * OW * Cp;
   for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
     const int c = (int)(t % Cp);
@@ -843,6 +851,7 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_fwd_kernel(const float* __re
 __global__ void __launch_bounds__(256) maxpool_nhwc_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ idx,
                                                                const float* __restrict__ relu_y, float* __restrict__ dx, int N,
                                                                int H, int W, int Cp, int K, int OH, int OW) {
+  mc::pdl_sync();
   const int64_t total = (int64_t)N * H * W * Cp;
   for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
     const int c = (int)(t % Cp);
@@ -865,6 +874,7 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_bwd_kernel(const float* __re
 __global__ void __launch_bounds__(256) maxpool_nhwc_fwd_vec_kernel(const float4* __restrict__ x, float4* __restrict__ y,
                                                                    uchar4* __restrict__ idx, int N, int H, int W, int C4,
                                                                    int KH, int KW, int stride, int OH, int OW) {
+  mc::pdl_sync();
   const int64_t total = (int64_t)N * OH * OW * C4;
   for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
     const int c = (int)(t % C4);
@@ -890,6 +900,7 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_fwd_vec_kernel(const float4*
 __global__ void __launch_bounds__(256) maxpool_nhwc_bwd_vec_kernel(const float4* __restrict__ dy, const uchar4* __restrict__ idx,
                                                                    const float4* __restrict__ relu_y, float4* __restrict__ dx,
                                                                    int N, int H, int W, int C4, int K, int OH, int OW) {
+  mc::pdl_sync();
   const int64_t total = (int64_t)N * OH * OW * C4;
   for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
     const int c = (int)(t % C4);
@@ -916,6 +927,7 @@ __global__ void __launch_bounds__(256) maxpool_nhwc_bwd_vec_kernel(const float4*
 // few channels (C <= 4 -> Cp == 4): one thread = one (padded) pixel, one 16-byte store
 __global__ void __launch_bounds__(256) nchw_to_nhwc4_kernel(const float* __restrict__ x, float4* __restrict__ y, int N, int C,
                                                             int H, int W, int wpad) {
+  mc::pdl_sync();
   const int Wp = W + 2 * wpad;
   const int64_t total = (int64_t)N * H * Wp;
   const int64_t plane = (int64_t)H * W;
@@ -999,7 +1011,7 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   const int Kp = (K + 3) / 4 * 4;
   float* wp = nullptr;
   MC_CHECK(cudaMallocAsync((void**)&wp, sizeof(float) * (size_t)taps * Nout * Kp, stream()));
-  conv_pack_weights_kernel<<<grid_for((int64_t)taps * Nout * Kp, 256), 256, 0, stream()>>>(w, wp, F, C, KH, KW, Cp, taps, Nout,
+  mc::launch(conv_pack_weights_kernel, grid_for((int64_t)taps * Nout * Kp, 256), 256, 0, w, wp, F, C, KH, KW, Cp, taps, Nout,
                                                                                           Kp, mode);
   MC_LAUNCHED();
 
@@ -1053,7 +1065,7 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
       cudaMemset(dbg_buf, 0, sizeof(long long) * 3 * 32 * 4);
       p.dbg = dbg_buf;
     }
-    conv_igemm_kernel<<<grid, IGEMM_THREADS, smem, stream()>>>(tmX, tmW, p);
+    mc::launch(conv_igemm_kernel, grid, IGEMM_THREADS, smem, tmX, tmW, p);
     if (dbg) {
       static long long host[3 * 32 * 4];
       cudaDeviceSynchronize();
@@ -1143,9 +1155,9 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
           cudaMemset(dbg_buf, 0, sizeof(long long) * 3 * 32 * 4);
           h.dbg = dbg_buf;
         }
-        if (hg.TW == 1) conv_wgrad_halo_kernel<1><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
-        else if (hg.TW == 3) conv_wgrad_halo_kernel<3><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
-        else conv_wgrad_halo_kernel<0><<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, h);
+        if (hg.TW == 1) mc::launch(conv_wgrad_halo_kernel<1>, grid, CONV_THREADS, smem, tmDy, tmX, h);
+        else if (hg.TW == 3) mc::launch(conv_wgrad_halo_kernel<3>, grid, CONV_THREADS, smem, tmDy, tmX, h);
+        else mc::launch(conv_wgrad_halo_kernel<0>, grid, CONV_THREADS, smem, tmDy, tmX, h);
         if (dbg) {
           static long long host[3 * 32 * 4];
           cudaDeviceSynchronize();
@@ -1165,7 +1177,7 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
       if (rc == 0) {
         const int wblocks = (int)(((int64_t)taps * F * p.Nn + 31) / 32);
         const int bblocks = dbias ? (F + 31) / 32 : 0;
-        conv_wgrad_reduce_kernel<<<wblocks + bblocks, 256, 0, stream()>>>(ws, dw, h.ws_bias, dbias, splits, taps, F, p.Nn, C, KH,
+        mc::launch(conv_wgrad_reduce_kernel, wblocks + bblocks, 256, 0, ws, dw, h.ws_bias, dbias, splits, taps, F, p.Nn, C, KH,
                                                                          KW, Cp, merged, wblocks);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("conv_wgrad_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
@@ -1211,7 +1223,7 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
   if (rc == 0 && first_use_on_device(&configured)) rc = set_max_smem((const void*)conv_wgrad_kernel, "conv_wgrad_kernel");
   if (rc == 0) {
     dim3 grid((unsigned)groups, (unsigned)splits, (unsigned)ftiles);
-    conv_wgrad_kernel<<<grid, CONV_THREADS, smem, stream()>>>(tmDy, tmX, p);
+    mc::launch(conv_wgrad_kernel, grid, CONV_THREADS, smem, tmDy, tmX, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("conv_wgrad_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();
@@ -1219,7 +1231,7 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
   if (rc == 0) {
     const int wblocks = (int)(((int64_t)taps * F * p.Nn + 31) / 32);
     const int bblocks = dbias ? (F + 31) / 32 : 0;
-    conv_wgrad_reduce_kernel<<<wblocks + bblocks, 256, 0, stream()>>>(ws, dw, p.ws_bias, dbias, splits, taps, F, p.Nn, C, KH, KW,
+    mc::launch(conv_wgrad_reduce_kernel, wblocks + bblocks, 256, 0, ws, dw, p.ws_bias, dbias, splits, taps, F, p.Nn, C, KH, KW,
                                                                      Cp, merged, wblocks);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("conv_wgrad_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
@@ -1232,13 +1244,13 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
 int nchw_to_nhwc(const float* x, float* y, int N, int C, int H, int W, int Cp, int wpad) {
   if (Cp == 4 && aligned16(y)) {
     const int64_t total = (int64_t)N * H * (W + 2 * wpad);
-    nchw_to_nhwc4_kernel<<<grid_for(total, 256), 256, 0, stream()>>>(x, reinterpret_cast<float4*>(y), N, C, H, W, wpad);
+    mc::launch(nchw_to_nhwc4_kernel, grid_for(total, 256), 256, 0, x, reinterpret_cast<float4*>(y), N, C, H, W, wpad);
     MC_LAUNCHED();
     return 0;
   }
   if (wpad == 0) { W *= H; H = 1; }            // no pad columns: (h, w) is one flat pixel axis, full 32-pixel tiles for small images
   dim3 grid((unsigned)((W + 2 * wpad + 31) / 32), (unsigned)((Cp + 31) / 32), (unsigned)(N * H));
-  nchw_to_nhwc_kernel<<<grid, 256, 0, stream()>>>(x, y, N, C, H, W, Cp, wpad);
+  mc::launch(nchw_to_nhwc_kernel, grid, 256, 0, x, y, N, C, H, W, Cp, wpad);
   MC_LAUNCHED();
   return 0;
 }
@@ -1246,7 +1258,7 @@ int nchw_to_nhwc(const float* x, float* y, int N, int C, int H, int W, int Cp, i
 int nhwc_to_nchw(const float* x, float* y, int N, int C, int H, int W, int Cp) {
   W *= H; H = 1;                               // (h, w) as one flat pixel axis
   dim3 grid((unsigned)((W + 31) / 32), (unsigned)((C + 31) / 32), (unsigned)(N * H));
-  nhwc_to_nchw_kernel<<<grid, 256, 0, stream()>>>(x, y, N, C, H, W, Cp);
+  mc::launch(nhwc_to_nchw_kernel, grid, 256, 0, x, y, N, C, H, W, Cp);
   MC_LAUNCHED();
   return 0;
 }
@@ -1344,11 +1356,11 @@ int mc_maxpool2d_nhwc_fwd(const float* x, float* y, uint8_t* idx_u8, int64_t N, 
   const int64_t n = N * OH * OW * Cp;
   if (n <= 0) return 0;
   if ((Cp & 3) == 0 && aligned16(x) && aligned16(y) && (!idx_u8 || (reinterpret_cast<uintptr_t>(idx_u8) & 3u) == 0)) {
-    tc::maxpool_nhwc_fwd_vec_kernel<<<grid_for(n / 4, 256), 256, 0, stream()>>>(
+    mc::launch(tc::maxpool_nhwc_fwd_vec_kernel, grid_for(n / 4, 256), 256, 0, 
         reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), reinterpret_cast<uchar4*>(idx_u8), (int)N, (int)H,
         (int)W, (int)(Cp / 4), (int)KH, (int)KW, (int)stride, (int)OH, (int)OW);
   } else {
-    tc::maxpool_nhwc_fwd_kernel<<<grid_for(n, 256), 256, 0, stream()>>>(x, y, idx_u8, (int)N, (int)H, (int)W, (int)Cp, (int)KH,
+    mc::launch(tc::maxpool_nhwc_fwd_kernel, grid_for(n, 256), 256, 0, x, y, idx_u8, (int)N, (int)H, (int)W, (int)Cp, (int)KH,
                                                                        (int)KW, (int)stride, (int)OH, (int)OW);
   }
   MC_LAUNCHED();
@@ -1361,11 +1373,11 @@ int mc_maxpool2d_nhwc_bwd(const float* dy, const uint8_t* idx_u8, const float* r
   if (n <= 0) return 0;
   if ((Cp & 3) == 0 && H == OH * K && W == OW * K && aligned16(dy) && aligned16(dx) && (!relu_y || aligned16(relu_y)) &&
       (reinterpret_cast<uintptr_t>(idx_u8) & 3u) == 0) {
-    tc::maxpool_nhwc_bwd_vec_kernel<<<grid_for(N * OH * OW * (Cp / 4), 256), 256, 0, stream()>>>(
+    mc::launch(tc::maxpool_nhwc_bwd_vec_kernel, grid_for(N * OH * OW * (Cp / 4), 256), 256, 0, 
         reinterpret_cast<const float4*>(dy), reinterpret_cast<const uchar4*>(idx_u8), reinterpret_cast<const float4*>(relu_y),
         reinterpret_cast<float4*>(dx), (int)N, (int)H, (int)W, (int)(Cp / 4), (int)K, (int)OH, (int)OW);
   } else {
-    tc::maxpool_nhwc_bwd_kernel<<<grid_for(n, 256), 256, 0, stream()>>>(dy, idx_u8, relu_y, dx, (int)N, (int)H, (int)W, (int)Cp,
+    mc::launch(tc::maxpool_nhwc_bwd_kernel, grid_for(n, 256), 256, 0, dy, idx_u8, relu_y, dx, (int)N, (int)H, (int)W, (int)Cp,
                                                                        (int)K, (int)OH, (int)OW);
   }
   MC_LAUNCHED();

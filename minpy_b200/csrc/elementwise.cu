@@ -89,6 +89,7 @@ __device__ __forceinline__ float binary_apply_rt(int op, float a, float b) {
 template <int OP>
 __global__ void __launch_bounds__(EW_THREADS) unary_vec_kernel(const float* __restrict__ x,
                                                                float* __restrict__ y, int64_t n) {
+  mc::pdl_sync();
   const int64_t n4 = n >> 2;
   const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
   float4* __restrict__ y4 = reinterpret_cast<float4*>(y);
@@ -122,6 +123,7 @@ __global__ void __launch_bounds__(EW_THREADS) unary_vec_kernel(const float* __re
 template <int OP>
 __global__ void __launch_bounds__(EW_THREADS) unary_scalar_kernel(const float* __restrict__ x,
                                                                   float* __restrict__ y, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * EW_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride)
     y[i] = unary_apply<OP>(x[i]);
@@ -131,6 +133,7 @@ template <int OP>
 __global__ void __launch_bounds__(EW_THREADS) binary_vec_kernel(const float* __restrict__ a,
                                                                 const float* __restrict__ b,
                                                                 float* __restrict__ out, int64_t n) {
+  mc::pdl_sync();
   const int64_t n4 = n >> 2;
   const float4* __restrict__ a4 = reinterpret_cast<const float4*>(a);
   const float4* __restrict__ b4 = reinterpret_cast<const float4*>(b);
@@ -166,6 +169,7 @@ template <int OP>
 __global__ void __launch_bounds__(EW_THREADS) binary_scalar_elems_kernel(const float* __restrict__ a,
                                                                          const float* __restrict__ b,
                                                                          float* __restrict__ out, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * EW_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride)
     out[i] = binary_apply<OP>(a[i], b[i]);
@@ -174,6 +178,7 @@ __global__ void __launch_bounds__(EW_THREADS) binary_scalar_elems_kernel(const f
 template <int OP, bool LEFT>
 __global__ void __launch_bounds__(EW_THREADS) binary_const_kernel(const float* __restrict__ a, float s,
                                                                   float* __restrict__ out, int64_t n, int vec_ok) {
+  mc::pdl_sync();
   if (vec_ok) {
     const int64_t n4 = n >> 2;
     const float4* __restrict__ a4 = reinterpret_cast<const float4*>(a);
@@ -219,6 +224,7 @@ __global__ void __launch_bounds__(EW_THREADS) binary_vec_bcast_kernel(const floa
                                                                       const float* __restrict__ v,
                                                                       float* __restrict__ out, int64_t rows,
                                                                       int64_t cols, int vec_ok) {
+  mc::pdl_sync();
   const int64_t n = rows * cols;
   if (vec_ok) {
     const int64_t n4 = n >> 2;
@@ -279,6 +285,7 @@ __global__ void __launch_bounds__(EW_THREADS) binary_bcast_kernel(const float* _
                                                                   const float* __restrict__ b,
                                                                   float* __restrict__ out, int64_t n,
                                                                   const __grid_constant__ BcastDesc d) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * EW_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride) {
     int64_t rem = i, oa = 0, ob = 0;
@@ -296,6 +303,7 @@ __global__ void __launch_bounds__(EW_THREADS) binary_bcast_kernel(const float* _
 }
 
 __global__ void __launch_bounds__(EW_THREADS) fill_kernel(float* __restrict__ dst, float v, int64_t n, int vec_ok) {
+  mc::pdl_sync();
   if (vec_ok) {
     const int64_t n4 = n >> 2;
     float4* d4 = reinterpret_cast<float4*>(dst);
@@ -313,6 +321,7 @@ __global__ void __launch_bounds__(EW_THREADS) fill_kernel(float* __restrict__ ds
 }
 
 __global__ void __launch_bounds__(EW_THREADS) arange_kernel(float* __restrict__ dst, float start, float step, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * EW_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride)
     dst[i] = start + step * (float)i;
@@ -320,6 +329,7 @@ __global__ void __launch_bounds__(EW_THREADS) arange_kernel(float* __restrict__ 
 
 template <class S, class D>
 __global__ void __launch_bounds__(EW_THREADS) cast_kernel(const S* __restrict__ src, D* __restrict__ dst, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * EW_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride) dst[i] = (D)src[i];
 }
@@ -375,6 +385,7 @@ __device__ __forceinline__ float vjp_factor(int op, float g, float a, float b, f
     case MC_VJP_RECIP_ANS: return -g * a * a;
     case MC_VJP_GT0_A: return (a > 0.f) ? g : g * 0.f;
     case MC_VJP_GE0_A: return (a >= 0.f) ? g : g * 0.f;
+    case MC_VJP_SIGNPOS_A: return (__float_as_uint(a) >> 31) ? g * 0.f : g;
     default: return g;
   }
 }
@@ -383,6 +394,7 @@ __global__ void __launch_bounds__(EW_THREADS) vjp_chain_kernel(const float* __re
                                                                const float* __restrict__ acc,
                                                                float* __restrict__ out, int64_t n, int vec_ok,
                                                                const __grid_constant__ ChainDesc d) {
+  mc::pdl_sync();
   if (vec_ok) {
     const int64_t n4 = n >> 2;
     const int64_t stride = (int64_t)gridDim.x * EW_THREADS;
@@ -450,6 +462,7 @@ struct MultiCopyDesc {
 };
 
 __global__ void __launch_bounds__(EW_THREADS) multi_copy_kernel(const __grid_constant__ MultiCopyDesc d) {
+  mc::pdl_sync();
   int t = 0;
   while (t + 1 < d.count && (int)blockIdx.x >= d.first[t + 1]) ++t;
   const float* __restrict__ src = d.src[t];
@@ -472,10 +485,10 @@ template <int OP>
 static int launch_unary(const float* x, float* y, int64_t n) {
   if (aligned16(x) && aligned16(y)) {
     int grid = grid_for((n >> 2) + 1, EW_THREADS * EW_UNROLL);
-    unary_vec_kernel<OP><<<grid, EW_THREADS, 0, stream()>>>(x, y, n);
+    mc::launch(unary_vec_kernel<OP>, grid, EW_THREADS, 0, x, y, n);
   } else {
     int grid = grid_for(n, EW_THREADS);
-    unary_scalar_kernel<OP><<<grid, EW_THREADS, 0, stream()>>>(x, y, n);
+    mc::launch(unary_scalar_kernel<OP>, grid, EW_THREADS, 0, x, y, n);
   }
   MC_LAUNCHED();
   return 0;
@@ -485,10 +498,10 @@ template <int OP>
 static int launch_binary(const float* a, const float* b, float* out, int64_t n) {
   if (aligned16(a) && aligned16(b) && aligned16(out)) {
     int grid = grid_for((n >> 2) + 1, EW_THREADS * EW_UNROLL);
-    binary_vec_kernel<OP><<<grid, EW_THREADS, 0, stream()>>>(a, b, out, n);
+    mc::launch(binary_vec_kernel<OP>, grid, EW_THREADS, 0, a, b, out, n);
   } else {
     int grid = grid_for(n, EW_THREADS);
-    binary_scalar_elems_kernel<OP><<<grid, EW_THREADS, 0, stream()>>>(a, b, out, n);
+    mc::launch(binary_scalar_elems_kernel<OP>, grid, EW_THREADS, 0, a, b, out, n);
   }
   MC_LAUNCHED();
   return 0;
@@ -498,8 +511,8 @@ template <int OP>
 static int launch_binary_const(const float* a, float s, int left, float* out, int64_t n) {
   int vec_ok = aligned16(a) && aligned16(out);
   int grid = vec_ok ? grid_for((n >> 2) + 1, EW_THREADS * EW_UNROLL) : grid_for(n, EW_THREADS);
-  if (left) binary_const_kernel<OP, true><<<grid, EW_THREADS, 0, stream()>>>(a, s, out, n, vec_ok);
-  else binary_const_kernel<OP, false><<<grid, EW_THREADS, 0, stream()>>>(a, s, out, n, vec_ok);
+  if (left) mc::launch(binary_const_kernel<OP, true>, grid, EW_THREADS, 0, a, s, out, n, vec_ok);
+  else mc::launch(binary_const_kernel<OP, false>, grid, EW_THREADS, 0, a, s, out, n, vec_ok);
   MC_LAUNCHED();
   return 0;
 }
@@ -511,11 +524,11 @@ static int launch_binary_vecb(const float* a, const float* v, int is_col, int le
   int64_t n = rows * cols;
   int grid = vec_ok ? grid_for((n >> 2) + 1, EW_THREADS * EW_UNROLL) : grid_for(n, EW_THREADS);
   if (is_col) {
-    if (left) binary_vec_bcast_kernel<OP, true, true><<<grid, EW_THREADS, 0, stream()>>>(a, v, out, rows, cols, vec_ok);
-    else binary_vec_bcast_kernel<OP, true, false><<<grid, EW_THREADS, 0, stream()>>>(a, v, out, rows, cols, vec_ok);
+    if (left) mc::launch(binary_vec_bcast_kernel<OP, true, true>, grid, EW_THREADS, 0, a, v, out, rows, cols, vec_ok);
+    else mc::launch(binary_vec_bcast_kernel<OP, true, false>, grid, EW_THREADS, 0, a, v, out, rows, cols, vec_ok);
   } else {
-    if (left) binary_vec_bcast_kernel<OP, false, true><<<grid, EW_THREADS, 0, stream()>>>(a, v, out, rows, cols, vec_ok);
-    else binary_vec_bcast_kernel<OP, false, false><<<grid, EW_THREADS, 0, stream()>>>(a, v, out, rows, cols, vec_ok);
+    if (left) mc::launch(binary_vec_bcast_kernel<OP, false, true>, grid, EW_THREADS, 0, a, v, out, rows, cols, vec_ok);
+    else mc::launch(binary_vec_bcast_kernel<OP, false, false>, grid, EW_THREADS, 0, a, v, out, rows, cols, vec_ok);
   }
   MC_LAUNCHED();
   return 0;
@@ -525,11 +538,11 @@ template <class S>
 static int cast_from(const S* src, void* dst, int dst_dtype, int64_t n) {
   int grid = grid_for(n, EW_THREADS);
   switch (dst_dtype) {
-    case MC_F32: cast_kernel<S, float><<<grid, EW_THREADS, 0, stream()>>>(src, (float*)dst, n); break;
-    case MC_I32: cast_kernel<S, int32_t><<<grid, EW_THREADS, 0, stream()>>>(src, (int32_t*)dst, n); break;
-    case MC_I64: cast_kernel<S, int64_t><<<grid, EW_THREADS, 0, stream()>>>(src, (int64_t*)dst, n); break;
-    case MC_F64: cast_kernel<S, double><<<grid, EW_THREADS, 0, stream()>>>(src, (double*)dst, n); break;
-    case MC_U8: cast_kernel<S, uint8_t><<<grid, EW_THREADS, 0, stream()>>>(src, (uint8_t*)dst, n); break;
+    case MC_F32: mc::launch(cast_kernel<S, float>, grid, EW_THREADS, 0, src, (float*)dst, n); break;
+    case MC_I32: mc::launch(cast_kernel<S, int32_t>, grid, EW_THREADS, 0, src, (int32_t*)dst, n); break;
+    case MC_I64: mc::launch(cast_kernel<S, int64_t>, grid, EW_THREADS, 0, src, (int64_t*)dst, n); break;
+    case MC_F64: mc::launch(cast_kernel<S, double>, grid, EW_THREADS, 0, src, (double*)dst, n); break;
+    case MC_U8: mc::launch(cast_kernel<S, uint8_t>, grid, EW_THREADS, 0, src, (uint8_t*)dst, n); break;
     default: mc::set_error("unknown dst dtype %d", dst_dtype); return 2;
   }
   MC_LAUNCHED();
@@ -605,7 +618,7 @@ int mc_binary_bcast(int op, const float* a, const float* b, float* out, int ndim
   }
   if (n <= 0) return 0;
   int grid = grid_for(n, EW_THREADS);
-  binary_bcast_kernel<<<grid, EW_THREADS, 0, stream()>>>(a, b, out, n, d);
+  mc::launch(binary_bcast_kernel, grid, EW_THREADS, 0, a, b, out, n, d);
   MC_LAUNCHED();
   return 0;
 }
@@ -614,14 +627,14 @@ int mc_fill(float* dst, float value, int64_t n) {
   if (n <= 0) return 0;
   int vec_ok = aligned16(dst);
   int grid = grid_for(vec_ok ? (n >> 2) + 1 : n, EW_THREADS);
-  fill_kernel<<<grid, EW_THREADS, 0, stream()>>>(dst, value, n, vec_ok);
+  mc::launch(fill_kernel, grid, EW_THREADS, 0, dst, value, n, vec_ok);
   MC_LAUNCHED();
   return 0;
 }
 
 int mc_arange(float* dst, float start, float step, int64_t n) {
   if (n <= 0) return 0;
-  arange_kernel<<<grid_for(n, EW_THREADS), EW_THREADS, 0, stream()>>>(dst, start, step, n);
+  mc::launch(arange_kernel, grid_for(n, EW_THREADS), EW_THREADS, 0, dst, start, step, n);
   MC_LAUNCHED();
   return 0;
 }
@@ -656,7 +669,7 @@ int mc_vjp_chain(const float* g, int g_mode, int64_t g_inner, float g_scalar, co
     if (steps[k].b && !aligned16(steps[k].b)) vec_ok = 0;
   }
   int grid = grid_for(vec_ok ? (n >> 2) + 1 : n, EW_THREADS);
-  vjp_chain_kernel<<<grid, EW_THREADS, 0, stream()>>>(g, acc, out, n, vec_ok, d);
+  mc::launch(vjp_chain_kernel, grid, EW_THREADS, 0, g, acc, out, n, vec_ok, d);
   MC_LAUNCHED();
   return 0;
 }
@@ -678,7 +691,7 @@ int mc_multi_copy(const void* const* srcs, void* const* dsts, const int64_t* ns,
     }
     if (d.count == 0) continue;
     d.first[d.count] = blocks;
-    multi_copy_kernel<<<blocks, EW_THREADS, 0, stream()>>>(d);
+    mc::launch(multi_copy_kernel, blocks, EW_THREADS, 0, d);
     MC_LAUNCHED();
   }
   return 0;

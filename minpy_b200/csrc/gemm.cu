@@ -28,6 +28,7 @@ __global__ void __launch_bounds__(SG_THREADS) sgemm_kernel(int M, int N, int K, 
                                                            float* __restrict__ C, int64_t ldc,
                                                            const float* __restrict__ bias, int relu, int accumulate,
                                                            int k_per_split, float* __restrict__ ws) {
+  mc::pdl_sync();
   __shared__ float As[SG_BK][SG_BM + 4];
   __shared__ float Bs[SG_BK][SG_BN + 4];
   const int t = threadIdx.x;
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(SG_THREADS) sgemm_kernel(int M, int N, int K, 
       } else {
         if (bias) v += bias[gn];
         if (accumulate) v += C[(int64_t)gm * ldc + gn];
-        if (relu) v = (v != v) ? v : fmaxf(v, 0.f);
+        if (relu) v = relu_apply(v, relu);
         C[(int64_t)gm * ldc + gn] = v;
       }
     }
@@ -100,6 +101,7 @@ __global__ void __launch_bounds__(SG_THREADS) sgemm_kernel(int M, int N, int K, 
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ ws, int splits, int64_t M, int64_t N,
                                                             float* __restrict__ C, int64_t ldc,
                                                             const float* __restrict__ bias, int relu, int accumulate) {
+  mc::pdl_sync();
   const int64_t total = M * N;
   const int64_t stride = (int64_t)gridDim.x * 256;
   if ((N & 3) == 0 && (ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(C) & 15u) == 0)) {
@@ -116,8 +118,8 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
       float4* dst = reinterpret_cast<float4*>(C + m * ldc + n);
       if (accumulate) { const float4 c = *dst; s.x += c.x; s.y += c.y; s.z += c.z; s.w += c.w; }
       if (relu) {
-        s.x = (s.x != s.x) ? s.x : fmaxf(s.x, 0.f); s.y = (s.y != s.y) ? s.y : fmaxf(s.y, 0.f);
-        s.z = (s.z != s.z) ? s.z : fmaxf(s.z, 0.f); s.w = (s.w != s.w) ? s.w : fmaxf(s.w, 0.f);
+        s.x = relu_apply(s.x, relu); s.y = relu_apply(s.y, relu);
+        s.z = relu_apply(s.z, relu); s.w = relu_apply(s.w, relu);
       }
       *dst = s;
     }
@@ -128,7 +130,7 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
       const int64_t m = i / N, n = i % N;
       if (bias) s += bias[n];
       if (accumulate) s += C[m * ldc + n];
-      if (relu) s = (s != s) ? s : fmaxf(s, 0.f);
+      if (relu) s = relu_apply(s, relu);
       C[m * ldc + n] = s;
     }
   }
@@ -146,7 +148,7 @@ constexpr int SK_MAXN = 16;
 __device__ __forceinline__ float sk_epilogue(float v, const float* bias, int n, const float* cptr, int relu, int accumulate) {
   if (bias) v += bias[n];
   if (accumulate) v += *cptr;
-  if (relu) v = (v != v) ? v : fmaxf(v, 0.f);
+  if (relu) v = relu_apply(v, relu);
   return v;
 }
 
@@ -156,6 +158,7 @@ template <int S>
 __global__ void __launch_bounds__(256) skinny_nn_kernel(int M, int N, int K, const float* __restrict__ A, int64_t lda,
                                                         const float* __restrict__ B, int64_t ldb, float* __restrict__ C,
                                                         int64_t ldc, const float* __restrict__ bias, int relu, int accumulate) {
+  mc::pdl_sync();
   constexpr int ROWS = 8 / S;
   __shared__ float red[8][SK_MAXN];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -216,6 +219,7 @@ __global__ void __launch_bounds__(32 * SK_TN_WARPS) skinny_tn_kernel(int M, int 
                                                                      int64_t lda, const float* __restrict__ B, int64_t ldb,
                                                                      float* __restrict__ C, int64_t ldc,
                                                                      const float* __restrict__ bias, int relu, int accumulate) {
+  mc::pdl_sync();
   __shared__ float red[SK_TN_WARPS][SK_MAXN][8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int mi = lane & 7, ks = lane >> 3;
@@ -271,6 +275,7 @@ __global__ void __launch_bounds__(32 * SK_TN_WARPS) skinny_tn_kernel(int M, int 
 __global__ void __launch_bounds__(256) skinny_nt_kernel(int M, int N, int K, const float* __restrict__ A, int64_t lda,
                                                         const float* __restrict__ B, int64_t ldb, float* __restrict__ C,
                                                         int64_t ldc, const float* __restrict__ bias, int relu, int accumulate) {
+  mc::pdl_sync();
   const int64_t total = (int64_t)M * N;
   for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
     const int m = (int)(i / N), n = (int)(i - (int64_t)m * N);
@@ -288,19 +293,19 @@ static bool gemm_skinny(int ta, int tb, int64_t M, int64_t N, int64_t K, const f
                         int64_t ldb, float* C, int64_t ldc, const float* bias, int relu, int accumulate) {
   if (N <= SK_MAXN && !ta && !tb && K >= 64) {
     if (M >= 2048)
-      skinny_nn_kernel<1><<<(unsigned)((M + 7) / 8), 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias,
+      mc::launch(skinny_nn_kernel<1>, (unsigned)((M + 7) / 8), 256, 0, (int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias,
                                                                        relu, accumulate);
     else if (M >= 512 && K < 1024)
-      skinny_nn_kernel<2><<<(unsigned)((M + 3) / 4), 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias,
+      mc::launch(skinny_nn_kernel<2>, (unsigned)((M + 3) / 4), 256, 0, (int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias,
                                                                        relu, accumulate);
     else
-      skinny_nn_kernel<8><<<(unsigned)M, 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
+      mc::launch(skinny_nn_kernel<8>, (unsigned)M, 256, 0, (int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
                                                              accumulate);
   } else if (N <= SK_MAXN && ta && !tb && K >= 64) {
-    skinny_tn_kernel<<<(unsigned)((M + 7) / 8), 32 * SK_TN_WARPS, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
+    mc::launch(skinny_tn_kernel, (unsigned)((M + 7) / 8), 32 * SK_TN_WARPS, 0, (int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
                                                                     accumulate);
   } else if (K <= SK_MAXN && !ta && tb && M * N >= 4096) {
-    skinny_nt_kernel<<<grid_for(M * N, 256), 256, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
+    mc::launch(skinny_nt_kernel, grid_for(M * N, 256), 256, 0, (int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu,
                                                                accumulate);
   } else {
     return false;
@@ -366,8 +371,8 @@ __device__ __forceinline__ void cluster_reduce(const GemmParams& p, uint32_t sme
           o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
         }
         if (p.relu) {
-          o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
-          o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
+          o.x = relu_apply(o.x, p.relu); o.y = relu_apply(o.y, p.relu);
+          o.z = relu_apply(o.z, p.relu); o.w = relu_apply(o.w, p.relu);
         }
         *reinterpret_cast<float4*>(dst) = o;
       } else {
@@ -378,7 +383,7 @@ __device__ __forceinline__ void cluster_reduce(const GemmParams& p, uint32_t sme
             float w = e[u];
             if (p.bias) w += __ldg(p.bias + col + u);
             if (p.accumulate) w += dst[u];
-            if (p.relu) w = (w != w) ? w : fmaxf(w, 0.f);
+            if (p.relu) w = relu_apply(w, p.relu);
             dst[u] = w;
           }
         }
@@ -429,6 +434,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  mc::pdl_sync();      // prologue done (on-chip state only); global memory from here on
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
@@ -558,8 +564,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
               o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
             }
             if (p.relu) {
-              o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
-              o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
+              o.x = relu_apply(o.x, p.relu); o.y = relu_apply(o.y, p.relu);
+              o.z = relu_apply(o.z, p.relu); o.w = relu_apply(o.w, p.relu);
             }
             *reinterpret_cast<float4*>(dst + j) = o;
           }
@@ -570,7 +576,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
               float o = v[j];
               if (p.bias) o += __ldg(p.bias + col0 + j);
               if (p.accumulate) o += dst[j];
-              if (p.relu) o = (o != o) ? o : fmaxf(o, 0.f);
+              if (p.relu) o = relu_apply(o, p.relu);
               dst[j] = o;
             }
           }
@@ -624,8 +630,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
           o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w;
         }
         if (p.relu) {
-          o.x = (o.x != o.x) ? o.x : fmaxf(o.x, 0.f); o.y = (o.y != o.y) ? o.y : fmaxf(o.y, 0.f);
-          o.z = (o.z != o.z) ? o.z : fmaxf(o.z, 0.f); o.w = (o.w != o.w) ? o.w : fmaxf(o.w, 0.f);
+          o.x = relu_apply(o.x, p.relu); o.y = relu_apply(o.y, p.relu);
+          o.z = relu_apply(o.z, p.relu); o.w = relu_apply(o.w, p.relu);
         }
         *reinterpret_cast<float4*>(dst) = o;
       }
@@ -638,7 +644,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
         float* dst = p.C + (int64_t)(m0 + r) * p.ldc + n0 + c;
         if (p.bias) o += __ldg(p.bias + n0 + c);
         if (p.accumulate) o += *dst;
-        if (p.relu) o = (o != o) ? o : fmaxf(o, 0.f);
+        if (p.relu) o = relu_apply(o, p.relu);
         *dst = o;
       }
     }
@@ -714,7 +720,7 @@ static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     count_launch();
     return 0;
   }
-  gemm_tf32_kernel<BN, STAGES><<<grid, THREADS, SMEM, stream()>>>(tmA, tmB, p);
+  mc::launch(gemm_tf32_kernel<BN, STAGES>, grid, THREADS, SMEM, tmA, tmB, p);
   MC_LAUNCHED();
   return 0;
 }
@@ -741,7 +747,7 @@ static int gemm_fp32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   if (splits > 1) MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * splits * M * N, stream()));
   dim3 grid((unsigned)((N + SG_BN - 1) / SG_BN), (unsigned)((M + SG_BM - 1) / SG_BM), (unsigned)splits);
 #define SG_LAUNCH(TA, TB)                                                                                          \
-  sgemm_kernel<TA, TB><<<grid, SG_THREADS, 0, stream()>>>((int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu, \
+  mc::launch(sgemm_kernel<TA, TB>, grid, SG_THREADS, 0, (int)M, (int)N, (int)K, A, lda, B, ldb, C, ldc, bias, relu, \
                                                           accumulate, k_per, ws)
   if (ta && tb) SG_LAUNCH(true, true);
   else if (ta) SG_LAUNCH(true, false);
@@ -750,7 +756,7 @@ static int gemm_fp32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
 #undef SG_LAUNCH
   MC_LAUNCHED();
   if (splits > 1) {
-    splitk_reduce_kernel<<<grid_for(M * N / 4 + 1, 256), 256, 0, stream()>>>(ws, splits, M, N, C, ldc, bias, relu, accumulate);
+    mc::launch(splitk_reduce_kernel, grid_for(M * N / 4 + 1, 256), 256, 0, ws, splits, M, N, C, ldc, bias, relu, accumulate);
     MC_LAUNCHED();
     MC_CHECK(cudaFreeAsync(ws, stream()));
   }
@@ -766,6 +772,24 @@ static int* splitk_counters() {
     cudaMemset(c, 0, sizeof(int) * kMaxFixupTiles);
   }
   return c;
+}
+
+// Split-K partials live in ONE persistent block per device (grown on demand, old blocks are kept alive
+// because captured graphs may still reference them).  Every kernel of the library runs on one stream, so
+// reuse in program order is safe; a cudaMallocAsync / cudaFreeAsync pair per call put two memory nodes
+// per GEMM into the captured step graph (suspected part of the per-node cost).
+static float* splitk_workspace(size_t bytes) {
+  static float* ws[16] = {};
+  static size_t cap[16] = {};
+  const int d = device() & 15;
+  if (cap[d] < bytes) {
+    size_t want = bytes < ((size_t)32 << 20) ? ((size_t)32 << 20) : bytes * 2;
+    float* fresh = nullptr;
+    if (cudaMalloc((void**)&fresh, want) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    ws[d] = fresh;
+    cap[d] = want;
+  }
+  return ws[d];
 }
 
 static bool tma_ok(const float* p, int64_t ld) { return aligned16(p) && (ld % 4 == 0); }
@@ -846,7 +870,8 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     if (S > 1) { splits = S; p.kb_per_split = kb_per; p.cluster = S; }
   }
   if (splits > 1 && !p.cluster) {
-    MC_CHECK(cudaMallocAsync((void**)&p.ws, sizeof(float) * splits * M * N, stream()));
+    p.ws = splitk_workspace(sizeof(float) * splits * M * N);
+    MC_REQUIRE(p.ws != nullptr, "split-K workspace allocation failed");
     // In-kernel fixup (last-arriving slice CTA reduces) is OFF by default: one SM streaming S x 64 KB
     // of partials is latency-bound (c3_fwd2: 9.9 -> 27 us measured, r1t); the separate reduce kernel
     // spreads the same bytes over every SM.  MC_GEMM_FIXUP=1 re-enables it for experiments.
@@ -856,12 +881,11 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   }
   int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
   if (rc == 0 && splits > 1 && !p.counters && !p.cluster) {
-    splitk_reduce_kernel<<<grid_for(M * N / 4 + 1, 256), 256, 0, stream()>>>(p.ws, splits, M, N, C, ldc, bias, relu, accumulate);
+    mc::launch(splitk_reduce_kernel, grid_for(M * N / 4 + 1, 256), 256, 0, p.ws, splits, M, N, C, ldc, bias, relu, accumulate);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("splitk reduce launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();
   }
-  if (p.ws) MC_CHECK(cudaFreeAsync(p.ws, stream()));
   return rc;
 }
 

@@ -20,6 +20,7 @@ struct StridedDesc {
 template <bool ADD>
 __global__ void __launch_bounds__(IX_THREADS) strided_kernel(const float* __restrict__ src, float* __restrict__ dst,
                                                              int64_t n, const __grid_constant__ StridedDesc d) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * IX_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * IX_THREADS + threadIdx.x; i < n; i += stride) {
     int64_t rem = i, off = d.offset;
@@ -39,6 +40,7 @@ __global__ void __launch_bounds__(IX_THREADS) strided_kernel(const float* __rest
 // src is (rows, cols) with row pitch `ld`, dst is (cols, rows) dense; batched over z.
 __global__ void __launch_bounds__(256) transpose_tile_kernel(const float* __restrict__ src, float* __restrict__ dst,
                                                              int64_t rows, int64_t cols) {
+  mc::pdl_sync();
   __shared__ float tile[32][33];
   const int64_t b = blockIdx.z;
   const float* __restrict__ s = src + b * rows * cols;
@@ -60,6 +62,7 @@ __global__ void __launch_bounds__(256) transpose_tile_kernel(const float* __rest
 
 __global__ void __launch_bounds__(IX_THREADS) pick_cols_kernel(const float* __restrict__ x, const int32_t* __restrict__ idx,
                                                                float* __restrict__ out, int64_t rows, int64_t cols) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * IX_THREADS;
   for (int64_t r = (int64_t)blockIdx.x * IX_THREADS + threadIdx.x; r < rows; r += stride) {
     int32_t c = idx[r];
@@ -71,6 +74,7 @@ __global__ void __launch_bounds__(IX_THREADS) pick_cols_kernel(const float* __re
 __global__ void __launch_bounds__(IX_THREADS) pick_cols_grad_kernel(const float* __restrict__ g,
                                                                     const int32_t* __restrict__ idx, float* __restrict__ dx,
                                                                     int64_t rows, int64_t cols) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * IX_THREADS;
   for (int64_t r = (int64_t)blockIdx.x * IX_THREADS + threadIdx.x; r < rows; r += stride) {
     int32_t c = idx[r];
@@ -82,6 +86,7 @@ __global__ void __launch_bounds__(IX_THREADS) pick_cols_grad_kernel(const float*
 __global__ void __launch_bounds__(IX_THREADS) take_rows_kernel(const float* __restrict__ x, const int32_t* __restrict__ idx,
                                                                float* __restrict__ out, int64_t nidx, int64_t row_elems,
                                                                int64_t src_rows) {
+  mc::pdl_sync();
   const int64_t n = nidx * row_elems;
   const int64_t stride = (int64_t)gridDim.x * IX_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * IX_THREADS + threadIdx.x; t < n; t += stride) {
@@ -95,6 +100,7 @@ __global__ void __launch_bounds__(IX_THREADS) take_rows_kernel(const float* __re
 __global__ void __launch_bounds__(IX_THREADS) take_rows_grad_kernel(const float* __restrict__ g,
                                                                     const int32_t* __restrict__ idx, float* __restrict__ dx,
                                                                     int64_t nidx, int64_t row_elems, int64_t src_rows) {
+  mc::pdl_sync();
   const int64_t n = nidx * row_elems;
   const int64_t stride = (int64_t)gridDim.x * IX_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * IX_THREADS + threadIdx.x; t < n; t += stride) {
@@ -108,6 +114,7 @@ __global__ void __launch_bounds__(IX_THREADS) take_rows_grad_kernel(const float*
 __global__ void __launch_bounds__(IX_THREADS) concat_mid_kernel(const float* __restrict__ a, const float* __restrict__ b,
                                                                 float* __restrict__ out, int64_t na, int64_t nb,
                                                                 int64_t inner, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * IX_THREADS;
   const int64_t mid = na + nb;
   for (int64_t t = (int64_t)blockIdx.x * IX_THREADS + threadIdx.x; t < n; t += stride) {
@@ -156,12 +163,12 @@ int mc_strided_copy(const float* src, float* dst, int ndim, const int64_t* shape
     }
     if (ok && batch <= 65535 && (rows + 31) / 32 <= 65535) {
       dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32), (unsigned)batch);
-      transpose_tile_kernel<<<grid, 256, 0, stream()>>>(src, dst, rows, cols);
+      mc::launch(transpose_tile_kernel, grid, 256, 0, src, dst, rows, cols);
       MC_LAUNCHED();
       return 0;
     }
   }
-  strided_kernel<false><<<grid_for(n, IX_THREADS), IX_THREADS, 0, stream()>>>(src, dst, n, d);
+  mc::launch(strided_kernel<false>, grid_for(n, IX_THREADS), IX_THREADS, 0, src, dst, n, d);
   MC_LAUNCHED();
   return 0;
 }
@@ -172,28 +179,28 @@ int mc_strided_add(float* dst, const float* src, int ndim, const int64_t* shape,
   int64_t n;
   MC_REQUIRE(fill_desc(d, ndim, shape, dst_strides, dst_offset, &n) == 0, "ndim must be in 0..6");
   if (n <= 0) return 0;
-  strided_kernel<true><<<grid_for(n, IX_THREADS), IX_THREADS, 0, stream()>>>(src, dst, n, d);
+  mc::launch(strided_kernel<true>, grid_for(n, IX_THREADS), IX_THREADS, 0, src, dst, n, d);
   MC_LAUNCHED();
   return 0;
 }
 
 int mc_pick_cols(const float* x, const int32_t* idx, float* out, int64_t rows, int64_t cols) {
   if (rows <= 0) return 0;
-  pick_cols_kernel<<<grid_for(rows, IX_THREADS), IX_THREADS, 0, stream()>>>(x, idx, out, rows, cols);
+  mc::launch(pick_cols_kernel, grid_for(rows, IX_THREADS), IX_THREADS, 0, x, idx, out, rows, cols);
   MC_LAUNCHED();
   return 0;
 }
 
 int mc_pick_cols_grad(const float* g, const int32_t* idx, float* dx, int64_t rows, int64_t cols) {
   if (rows <= 0) return 0;
-  pick_cols_grad_kernel<<<grid_for(rows, IX_THREADS), IX_THREADS, 0, stream()>>>(g, idx, dx, rows, cols);
+  mc::launch(pick_cols_grad_kernel, grid_for(rows, IX_THREADS), IX_THREADS, 0, g, idx, dx, rows, cols);
   MC_LAUNCHED();
   return 0;
 }
 
 int mc_take_rows(const float* x, const int32_t* idx, float* out, int64_t nidx, int64_t row_elems) {
   if (nidx * row_elems <= 0) return 0;
-  take_rows_kernel<<<grid_for(nidx * row_elems, IX_THREADS), IX_THREADS, 0, stream()>>>(x, idx, out, nidx, row_elems,
+  mc::launch(take_rows_kernel, grid_for(nidx * row_elems, IX_THREADS), IX_THREADS, 0, x, idx, out, nidx, row_elems,
                                                                                        (int64_t)1 << 40);
   MC_LAUNCHED();
   return 0;
@@ -201,7 +208,7 @@ int mc_take_rows(const float* x, const int32_t* idx, float* out, int64_t nidx, i
 
 int mc_take_rows_grad(const float* g, const int32_t* idx, float* dx, int64_t nidx, int64_t row_elems) {
   if (nidx * row_elems <= 0) return 0;
-  take_rows_grad_kernel<<<grid_for(nidx * row_elems, IX_THREADS), IX_THREADS, 0, stream()>>>(g, idx, dx, nidx, row_elems,
+  mc::launch(take_rows_grad_kernel, grid_for(nidx * row_elems, IX_THREADS), IX_THREADS, 0, g, idx, dx, nidx, row_elems,
                                                                                             (int64_t)1 << 40);
   MC_LAUNCHED();
   return 0;
@@ -210,7 +217,7 @@ int mc_take_rows_grad(const float* g, const int32_t* idx, float* dx, int64_t nid
 int mc_concat_mid(const float* a, const float* b, float* out, int64_t outer, int64_t na, int64_t nb, int64_t inner) {
   const int64_t n = outer * (na + nb) * inner;
   if (n <= 0) return 0;
-  concat_mid_kernel<<<grid_for(n, IX_THREADS), IX_THREADS, 0, stream()>>>(a, b, out, na, nb, inner, n);
+  mc::launch(concat_mid_kernel, grid_for(n, IX_THREADS), IX_THREADS, 0, a, b, out, na, nb, inner, n);
   MC_LAUNCHED();
   return 0;
 }

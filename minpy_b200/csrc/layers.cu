@@ -33,6 +33,7 @@ __device__ __forceinline__ float u01(uint32_t r) { return (float)(r >> 8) * (1.0
 
 __global__ void __launch_bounds__(L_THREADS) rand_uniform_kernel(float* __restrict__ out, int64_t n, uint64_t seed,
                                                                  uint64_t offset, const unsigned long long* epoch) {
+  mc::pdl_sync();
   if (epoch) offset += (uint64_t)(*epoch) << 40;     // graph replay r draws from its own counter range
   const Philox rng(seed);
   const int64_t n4 = (n + 3) >> 2;
@@ -48,6 +49,7 @@ __global__ void __launch_bounds__(L_THREADS) rand_uniform_kernel(float* __restri
 
 __global__ void __launch_bounds__(L_THREADS) rand_normal_kernel(float* __restrict__ out, int64_t n, uint64_t seed,
                                                                 uint64_t offset, const unsigned long long* epoch) {
+  mc::pdl_sync();
   if (epoch) offset += (uint64_t)(*epoch) << 40;
   const Philox rng(seed);
   const int64_t n4 = (n + 3) >> 2;
@@ -71,6 +73,7 @@ __global__ void __launch_bounds__(L_THREADS) rand_normal_kernel(float* __restric
 __global__ void __launch_bounds__(L_THREADS) dropout_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n,
                                                             float p, uint64_t seed, uint64_t offset, int vec_ok,
                                                             const unsigned long long* epoch) {
+  mc::pdl_sync();
   if (epoch) offset += (uint64_t)(*epoch) << 40;     // same shift in forward and VJP of one replay
   const Philox rng(seed);
   const int64_t n4 = (n + 3) >> 2;
@@ -128,6 +131,7 @@ __global__ void __launch_bounds__(L_THREADS) bn_partial_kernel(const float* __re
                                                                const float* __restrict__ mean,
                                                                const float* __restrict__ invstd, float* __restrict__ part,
                                                                int64_t N, int64_t D, int64_t rows_per_chunk) {
+  mc::pdl_sync();
   __shared__ float sm1[8][32 * VEC + 1];
   __shared__ float sm2[8][32 * VEC + 1];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -212,6 +216,7 @@ __global__ void __launch_bounds__(L_THREADS) bn_fwd_apply_kernel(const float* __
                                                                  float* __restrict__ save_mean, float* __restrict__ save_invstd,
                                                                  int64_t N, int64_t D, int64_t rows_per_chunk, float eps,
                                                                  float momentum) {
+  mc::pdl_sync();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * VEC;
   float t1[VEC], t2[VEC];
@@ -256,6 +261,7 @@ __global__ void __launch_bounds__(L_THREADS) bn_bwd_apply_kernel(const float* __
                                                                  float* __restrict__ dx, float* __restrict__ dgamma,
                                                                  float* __restrict__ dbeta, int64_t N, int64_t D,
                                                                  int64_t rows_per_chunk) {
+  mc::pdl_sync();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * VEC;
   float t1[VEC], t2[VEC];
@@ -311,12 +317,19 @@ __device__ __forceinline__ void slab_block_sums(float (&a)[4], float (&b)[4], fl
   }
 }
 
+// DROP: the dropout that follows batchnorm in the reference's block (mlp_bn_dropout.py:41-54) is applied
+// at the store -- out = bn(x) * (u > p), the mask of element i being lane (i & 3) of Philox(seed)(offset + i/4),
+// exactly dropout_kernel's -- so the normalised activations are never written unmasked.
+template <bool DROP>
 __global__ void __launch_bounds__(L_THREADS) bn_slab_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                                 const float* __restrict__ beta, const float* __restrict__ rmean,
                                                                 const float* __restrict__ rvar, float* __restrict__ out,
                                                                 float* __restrict__ new_rmean, float* __restrict__ new_rvar,
                                                                 float* __restrict__ save_mean, float* __restrict__ save_invstd,
-                                                                int N, int64_t D, float eps, float momentum) {
+                                                                int N, int64_t D, float eps, float momentum, float p,
+                                                                uint64_t seed, uint64_t offset, const unsigned long long* epoch) {
+  mc::pdl_sync();
+  if (DROP && epoch) offset += (uint64_t)(*epoch) << 40;
   const int half = threadIdx.x & 1, rl = threadIdx.x >> 1;
   const int64_t col = (int64_t)blockIdx.x * 8 + 4 * half;
   float4 v[SLAB_RPT];
@@ -352,20 +365,38 @@ __global__ void __launch_bounds__(L_THREADS) bn_slab_fwd_kernel(const float* __r
       new_rvar[col + k] = momentum * rvar[col + k] + (1.0f - momentum) * var;
     }
   }
+  const Philox rng(seed);
 #pragma unroll
   for (int i = 0; i < SLAB_RPT; ++i) {
     const int r = rl + 128 * i;
-    if (r < N)
-      *reinterpret_cast<float4*>(out + (int64_t)r * D + col) =
-          make_float4(fmaf(v[i].x, sc[0], sh[0]), fmaf(v[i].y, sc[1], sh[1]), fmaf(v[i].z, sc[2], sh[2]), fmaf(v[i].w, sc[3], sh[3]));
+    if (r < N) {
+      float4 o = make_float4(fmaf(v[i].x, sc[0], sh[0]), fmaf(v[i].y, sc[1], sh[1]), fmaf(v[i].z, sc[2], sh[2]), fmaf(v[i].w, sc[3], sh[3]));
+      if (DROP) {
+        const uint4 q = rng(offset + (uint64_t)(((int64_t)r * D + col) >> 2));
+        o.x = (u01(q.x) > p) ? o.x : 0.f; o.y = (u01(q.y) > p) ? o.y : 0.f;
+        o.z = (u01(q.z) > p) ? o.z : 0.f; o.w = (u01(q.w) > p) ? o.w : 0.f;
+      }
+      *reinterpret_cast<float4*>(out + (int64_t)r * D + col) = o;
+    }
   }
 }
 
+// DROP: dy is the gradient of the dropout that followed this batchnorm; its keep-mask is regenerated from
+// (seed, offset) while dy is loaded.  RELU: x is the output of a fused affine+relu (signed-zero mode, see
+// relu_apply): dx is zeroed where x's sign bit is set, i.e. the result is already the gradient of the affine
+// PRE-activation, and its column sums (the bias gradient of that affine layer) are written to `dbias`.
+// One launch instead of dropout-bwd + batchnorm-bwd + relu-bwd + a column reduction.
+template <bool DROP, bool RELU>
 __global__ void __launch_bounds__(L_THREADS) bn_slab_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy,
                                                                 const float* __restrict__ gamma, const float* __restrict__ mean,
                                                                 const float* __restrict__ invstd, float* __restrict__ dx,
-                                                                float* __restrict__ dgamma, float* __restrict__ dbeta, int N,
-                                                                int64_t D) {
+                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                                float* __restrict__ dbias, int N, int64_t D, float p,
+                                                                uint64_t seed, uint64_t offset, const unsigned long long* epoch) {
+  mc::pdl_sync();
+  if (DROP && epoch) offset += (uint64_t)(*epoch) << 40;
+  const Philox rng(seed);
+  uint32_t neg = 0;            // RELU: bit 4*i+k set when x[row i of this thread][column k] has its sign bit set
   const int half = threadIdx.x & 1, rl = threadIdx.x >> 1;
   const int64_t col = (int64_t)blockIdx.x * 8 + 4 * half;
   float4 xh[SLAB_RPT], g[SLAB_RPT];
@@ -376,6 +407,14 @@ __global__ void __launch_bounds__(L_THREADS) bn_slab_bwd_kernel(const float* __r
     if (r < N) {
       xh[i] = *reinterpret_cast<const float4*>(x + (int64_t)r * D + col);
       g[i] = *reinterpret_cast<const float4*>(dy + (int64_t)r * D + col);
+      if (DROP) {
+        const uint4 q = rng(offset + (uint64_t)(((int64_t)r * D + col) >> 2));
+        g[i].x = (u01(q.x) > p) ? g[i].x : 0.f; g[i].y = (u01(q.y) > p) ? g[i].y : 0.f;
+        g[i].z = (u01(q.z) > p) ? g[i].z : 0.f; g[i].w = (u01(q.w) > p) ? g[i].w : 0.f;
+      }
+      if (RELU)
+        neg |= ((__float_as_uint(xh[i].x) >> 31) | ((__float_as_uint(xh[i].y) >> 31) << 1) |
+                ((__float_as_uint(xh[i].z) >> 31) << 2) | ((__float_as_uint(xh[i].w) >> 31) << 3)) << (4 * i);
     }
   }
   float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f}, s1[4], s2[4];
@@ -397,13 +436,32 @@ __global__ void __launch_bounds__(L_THREADS) bn_slab_bwd_kernel(const float* __r
     k2[k] = s1[k] / (float)N;
     k3[k] = s2[k] / (float)N;
   }
+  float c[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
   for (int i = 0; i < SLAB_RPT; ++i) {
     const int r = rl + 128 * i;
-    if (r < N)
-      *reinterpret_cast<float4*>(dx + (int64_t)r * D + col) =
-          make_float4(k1[0] * (g[i].x - k2[0] - xh[i].x * k3[0]), k1[1] * (g[i].y - k2[1] - xh[i].y * k3[1]),
-                      k1[2] * (g[i].z - k2[2] - xh[i].z * k3[2]), k1[3] * (g[i].w - k2[3] - xh[i].w * k3[3]));
+    if (r < N) {
+      float4 o = make_float4(k1[0] * (g[i].x - k2[0] - xh[i].x * k3[0]), k1[1] * (g[i].y - k2[1] - xh[i].y * k3[1]),
+                             k1[2] * (g[i].z - k2[2] - xh[i].z * k3[2]), k1[3] * (g[i].w - k2[3] - xh[i].w * k3[3]));
+      if (RELU) {
+        const uint32_t m = neg >> (4 * i);
+        if (m & 1u) o.x = 0.f;
+        if (m & 2u) o.y = 0.f;
+        if (m & 4u) o.z = 0.f;
+        if (m & 8u) o.w = 0.f;
+        c[0] += o.x; c[1] += o.y; c[2] += o.z; c[3] += o.w;
+      }
+      *reinterpret_cast<float4*>(dx + (int64_t)r * D + col) = o;
+    }
+  }
+  if (RELU) {
+    float z[4] = {0.f, 0.f, 0.f, 0.f}, t1[4], t2[4];
+    __syncthreads();                  // slab_block_sums reuses its shared buffer
+    slab_block_sums(c, z, t1, t2);
+    if (rl == 0) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) dbias[col + k] = t1[k];
+    }
   }
 }
 static bool bn_slab_ok(int64_t N, int64_t D, bool aligned) {
@@ -415,6 +473,7 @@ __global__ void __launch_bounds__(L_THREADS) bn_test_kernel(const float* __restr
                                                             const float* __restrict__ beta, const float* __restrict__ rmean,
                                                             const float* __restrict__ rvar, float* __restrict__ out, int64_t N,
                                                             int64_t D, int64_t rows_per_chunk, float eps) {
+  mc::pdl_sync();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * VEC;
   if (col >= D) return;
@@ -457,6 +516,7 @@ __device__ __forceinline__ float sigmoid_ref(float x) { return 1.0f / (1.0f + ex
 __global__ void __launch_bounds__(L_THREADS) lstm_fwd_kernel(const float* __restrict__ a, const float* __restrict__ prev_c,
                                                              float* __restrict__ next_h, float* __restrict__ next_c,
                                                              float* __restrict__ gates, int64_t N, int64_t H) {
+  mc::pdl_sync();
   const int64_t n = N * H;
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; t < n; t += stride) {
@@ -477,6 +537,7 @@ __global__ void __launch_bounds__(L_THREADS) lstm_bwd_kernel(const float* __rest
                                                              const float* __restrict__ dnext_h,
                                                              const float* __restrict__ dnext_c, float* __restrict__ da,
                                                              float* __restrict__ dprev_c, int64_t N, int64_t H) {
+  mc::pdl_sync();
   const int64_t n = N * H;
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; t < n; t += stride) {
@@ -499,12 +560,14 @@ __global__ void __launch_bounds__(L_THREADS) lstm_bwd_kernel(const float* __rest
 // ===================================== optimizers =====================================
 __global__ void __launch_bounds__(L_THREADS) sgd_kernel(const float* __restrict__ w, const float* __restrict__ dw,
                                                         float* __restrict__ wo, float lr, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i < n; i += stride) wo[i] = w[i] - lr * dw[i];
 }
 __global__ void __launch_bounds__(L_THREADS) sgd_momentum_kernel(const float* __restrict__ w, const float* __restrict__ dw,
                                                                  const float* __restrict__ v, float* __restrict__ wo,
                                                                  float* __restrict__ vo, float lr, float mu, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i < n; i += stride) {
     const float nv = (v ? v[i] : 0.f) * mu - dw[i] * lr;  // optim.py:64
@@ -516,6 +579,7 @@ __global__ void __launch_bounds__(L_THREADS) rmsprop_kernel(const float* __restr
                                                             const float* __restrict__ cache, float* __restrict__ wo,
                                                             float* __restrict__ co, float lr, float decay, float eps,
                                                             int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i < n; i += stride) {
     const float g = dw[i];
@@ -529,6 +593,7 @@ __global__ void __launch_bounds__(L_THREADS) adam_kernel(const float* __restrict
                                                          float* __restrict__ wo, float* __restrict__ mo, float* __restrict__ vo,
                                                          float lr, float b1, float b2, float eps, float bc1, float bc2,
                                                          int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * L_THREADS;
   for (int64_t i = (int64_t)blockIdx.x * L_THREADS + threadIdx.x; i < n; i += stride) {
     const float g = dw[i];
@@ -548,20 +613,20 @@ extern "C" {
 
 int mc_rand_uniform(float* out, int64_t n, uint64_t seed, uint64_t offset) {
   if (n <= 0) return 0;
-  rand_uniform_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(out, n, seed, offset, graph_epoch());
+  mc::launch(rand_uniform_kernel, grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, out, n, seed, offset, graph_epoch());
   MC_LAUNCHED();
   return 0;
 }
 int mc_rand_normal(float* out, int64_t n, uint64_t seed, uint64_t offset) {
   if (n <= 0) return 0;
-  rand_normal_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(out, n, seed, offset, graph_epoch());
+  mc::launch(rand_normal_kernel, grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, out, n, seed, offset, graph_epoch());
   MC_LAUNCHED();
   return 0;
 }
 int mc_dropout(const float* x, float* out, int64_t n, float p, uint64_t seed, uint64_t offset) {
   if (n <= 0) return 0;
   const int vec_ok = aligned16(x) && aligned16(out);
-  dropout_kernel<<<grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, stream()>>>(x, out, n, p, seed, offset, vec_ok, graph_epoch());
+  mc::launch(dropout_kernel, grid_for((n + 3) / 4, L_THREADS), L_THREADS, 0, x, out, n, p, seed, offset, vec_ok, graph_epoch());
   MC_LAUNCHED();
   return 0;
 }
@@ -571,8 +636,9 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
                            float* save_mean, float* save_invstd, int64_t N, int64_t D, float eps, float momentum) {
   MC_REQUIRE(N > 0 && D > 0, "empty batch");
   if (bn_slab_ok(N, D, aligned16(x) && aligned16(out))) {
-    bn_slab_fwd_kernel<<<(unsigned)(D / 8), L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, out, new_running_mean,
-                                                                     new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum);
+    mc::launch(bn_slab_fwd_kernel<false>, (unsigned)(D / 8), L_THREADS, 0, x, gamma, beta, running_mean, running_var, out,
+               new_running_mean, new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum, 0.f, (uint64_t)0,
+               (uint64_t)0, (const unsigned long long*)nullptr);
     MC_LAUNCHED();
     return 0;
   }
@@ -581,15 +647,15 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
   MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * t.chunks * 2 * D, stream()));
   dim3 grid((unsigned)t.col_tiles, (unsigned)t.chunks);
   if (t.vec == 4) {
-    bn_partial_kernel<4, false><<<grid, L_THREADS, 0, stream()>>>(x, nullptr, nullptr, nullptr, part, N, D, t.rows_per_chunk);
+    mc::launch(bn_partial_kernel<4, false>, grid, L_THREADS, 0, x, nullptr, nullptr, nullptr, part, N, D, t.rows_per_chunk);
     MC_LAUNCHED();
-    bn_fwd_apply_kernel<4><<<grid, L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, part, (int)t.chunks,
+    mc::launch(bn_fwd_apply_kernel<4>, grid, L_THREADS, 0, x, gamma, beta, running_mean, running_var, part, (int)t.chunks,
                                                             out, new_running_mean, new_running_var, save_mean, save_invstd,
                                                             N, D, t.rows_per_chunk, eps, momentum);
   } else {
-    bn_partial_kernel<1, false><<<grid, L_THREADS, 0, stream()>>>(x, nullptr, nullptr, nullptr, part, N, D, t.rows_per_chunk);
+    mc::launch(bn_partial_kernel<1, false>, grid, L_THREADS, 0, x, nullptr, nullptr, nullptr, part, N, D, t.rows_per_chunk);
     MC_LAUNCHED();
-    bn_fwd_apply_kernel<1><<<grid, L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, part, (int)t.chunks,
+    mc::launch(bn_fwd_apply_kernel<1>, grid, L_THREADS, 0, x, gamma, beta, running_mean, running_var, part, (int)t.chunks,
                                                             out, new_running_mean, new_running_var, save_mean, save_invstd,
                                                             N, D, t.rows_per_chunk, eps, momentum);
   }
@@ -598,11 +664,51 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
   return 0;
 }
 
+int mc_bn_fused_supported(int64_t N, int64_t D, int* ok) {
+  *ok = bn_slab_ok(N, D, true) ? 1 : 0;
+  return 0;
+}
+
+int mc_bn_dropout_fwd(const float* x, const float* gamma, const float* beta, const float* running_mean,
+                      const float* running_var, float* out, float* new_running_mean, float* new_running_var,
+                      float* save_mean, float* save_invstd, int64_t N, int64_t D, float eps, float momentum, float p,
+                      uint64_t seed, uint64_t offset) {
+  MC_REQUIRE(N > 0 && D > 0, "empty batch");
+  MC_REQUIRE(bn_slab_ok(N, D, aligned16(x) && aligned16(out)), "shape outside the fused kernel (mc_bn_fused_supported)");
+  mc::launch(bn_slab_fwd_kernel<true>, (unsigned)(D / 8), L_THREADS, 0, x, gamma, beta, running_mean, running_var, out,
+             new_running_mean, new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum, p, seed, offset,
+             (const unsigned long long*)graph_epoch());
+  MC_LAUNCHED();
+  return 0;
+}
+
+int mc_bn_dropout_relu_bwd(const float* x, const float* dy, const float* gamma, const float* save_mean,
+                           const float* save_invstd, float* dx, float* dgamma, float* dbeta, float* dbias, int64_t N,
+                           int64_t D, int dropout, float p, uint64_t seed, uint64_t offset, int relu_signed) {
+  MC_REQUIRE(N > 0 && D > 0, "empty batch");
+  MC_REQUIRE(bn_slab_ok(N, D, aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(save_mean) && aligned16(save_invstd)),
+             "shape outside the fused kernel (mc_bn_fused_supported)");
+  MC_REQUIRE(!relu_signed || dbias != nullptr, "relu_signed needs dbias");
+  const unsigned long long* ep = (const unsigned long long*)graph_epoch();
+  const unsigned grid = (unsigned)(D / 8);
+#define MC_BN_BWD(DR, RE)                                                                                            \
+  mc::launch(bn_slab_bwd_kernel<DR, RE>, grid, L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, dx, dgamma, dbeta, dbias, \
+             (int)N, D, p, seed, offset, ep)
+  if (dropout && relu_signed) MC_BN_BWD(true, true);
+  else if (dropout) MC_BN_BWD(true, false);
+  else if (relu_signed) MC_BN_BWD(false, true);
+  else MC_BN_BWD(false, false);
+#undef MC_BN_BWD
+  MC_LAUNCHED();
+  return 0;
+}
+
 int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma, const float* save_mean,
                            const float* save_invstd, float* dx, float* dgamma, float* dbeta, int64_t N, int64_t D) {
   MC_REQUIRE(N > 0 && D > 0, "empty batch");
   if (bn_slab_ok(N, D, aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(save_mean) && aligned16(save_invstd))) {
-    bn_slab_bwd_kernel<<<(unsigned)(D / 8), L_THREADS, 0, stream()>>>(x, dy, gamma, save_mean, save_invstd, dx, dgamma, dbeta, (int)N, D);
+    mc::launch(bn_slab_bwd_kernel<false, false>, (unsigned)(D / 8), L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, dx, dgamma,
+               dbeta, (float*)nullptr, (int)N, D, 0.f, (uint64_t)0, (uint64_t)0, (const unsigned long long*)nullptr);
     MC_LAUNCHED();
     return 0;
   }
@@ -611,14 +717,14 @@ int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma, 
   MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * t.chunks * 2 * D, stream()));
   dim3 grid((unsigned)t.col_tiles, (unsigned)t.chunks);
   if (t.vec == 4) {
-    bn_partial_kernel<4, true><<<grid, L_THREADS, 0, stream()>>>(x, dy, save_mean, save_invstd, part, N, D, t.rows_per_chunk);
+    mc::launch(bn_partial_kernel<4, true>, grid, L_THREADS, 0, x, dy, save_mean, save_invstd, part, N, D, t.rows_per_chunk);
     MC_LAUNCHED();
-    bn_bwd_apply_kernel<4><<<grid, L_THREADS, 0, stream()>>>(x, dy, gamma, save_mean, save_invstd, part, (int)t.chunks, dx,
+    mc::launch(bn_bwd_apply_kernel<4>, grid, L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, part, (int)t.chunks, dx,
                                                             dgamma, dbeta, N, D, t.rows_per_chunk);
   } else {
-    bn_partial_kernel<1, true><<<grid, L_THREADS, 0, stream()>>>(x, dy, save_mean, save_invstd, part, N, D, t.rows_per_chunk);
+    mc::launch(bn_partial_kernel<1, true>, grid, L_THREADS, 0, x, dy, save_mean, save_invstd, part, N, D, t.rows_per_chunk);
     MC_LAUNCHED();
-    bn_bwd_apply_kernel<1><<<grid, L_THREADS, 0, stream()>>>(x, dy, gamma, save_mean, save_invstd, part, (int)t.chunks, dx,
+    mc::launch(bn_bwd_apply_kernel<1>, grid, L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, part, (int)t.chunks, dx,
                                                             dgamma, dbeta, N, D, t.rows_per_chunk);
   }
   MC_LAUNCHED();
@@ -631,43 +737,43 @@ int mc_batchnorm_test_fwd(const float* x, const float* gamma, const float* beta,
   MC_REQUIRE(N > 0 && D > 0, "empty batch");
   const BnTiling t = bn_tiling(aligned16(x) && aligned16(out) && aligned16(gamma) && aligned16(beta), N, D);
   dim3 grid((unsigned)t.col_tiles, (unsigned)t.chunks);
-  if (t.vec == 4) bn_test_kernel<4><<<grid, L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, out, N, D, t.rows_per_chunk, eps);
-  else bn_test_kernel<1><<<grid, L_THREADS, 0, stream()>>>(x, gamma, beta, running_mean, running_var, out, N, D, t.rows_per_chunk, eps);
+  if (t.vec == 4) mc::launch(bn_test_kernel<4>, grid, L_THREADS, 0, x, gamma, beta, running_mean, running_var, out, N, D, t.rows_per_chunk, eps);
+  else mc::launch(bn_test_kernel<1>, grid, L_THREADS, 0, x, gamma, beta, running_mean, running_var, out, N, D, t.rows_per_chunk, eps);
   MC_LAUNCHED();
   return 0;
 }
 
 int mc_lstm_cell_fwd(const float* a, const float* prev_c, float* next_h, float* next_c, float* gates, int64_t N, int64_t H) {
   if (N * H <= 0) return 0;
-  lstm_fwd_kernel<<<grid_for(N * H, L_THREADS), L_THREADS, 0, stream()>>>(a, prev_c, next_h, next_c, gates, N, H);
+  mc::launch(lstm_fwd_kernel, grid_for(N * H, L_THREADS), L_THREADS, 0, a, prev_c, next_h, next_c, gates, N, H);
   MC_LAUNCHED();
   return 0;
 }
 int mc_lstm_cell_bwd(const float* gates, const float* prev_c, const float* next_c, const float* dnext_h,
                      const float* dnext_c, float* da, float* dprev_c, int64_t N, int64_t H) {
   if (N * H <= 0) return 0;
-  lstm_bwd_kernel<<<grid_for(N * H, L_THREADS), L_THREADS, 0, stream()>>>(gates, prev_c, next_c, dnext_h, dnext_c, da, dprev_c, N, H);
+  mc::launch(lstm_bwd_kernel, grid_for(N * H, L_THREADS), L_THREADS, 0, gates, prev_c, next_c, dnext_h, dnext_c, da, dprev_c, N, H);
   MC_LAUNCHED();
   return 0;
 }
 
 int mc_sgd(const float* w, const float* dw, float* w_out, float lr, int64_t n) {
   if (n <= 0) return 0;
-  sgd_kernel<<<grid_for(n, L_THREADS), L_THREADS, 0, stream()>>>(w, dw, w_out, lr, n);
+  mc::launch(sgd_kernel, grid_for(n, L_THREADS), L_THREADS, 0, w, dw, w_out, lr, n);
   MC_LAUNCHED();
   return 0;
 }
 int mc_sgd_momentum(const float* w, const float* dw, const float* v, float* w_out, float* v_out, float lr, float momentum,
                     int64_t n) {
   if (n <= 0) return 0;
-  sgd_momentum_kernel<<<grid_for(n, L_THREADS), L_THREADS, 0, stream()>>>(w, dw, v, w_out, v_out, lr, momentum, n);
+  mc::launch(sgd_momentum_kernel, grid_for(n, L_THREADS), L_THREADS, 0, w, dw, v, w_out, v_out, lr, momentum, n);
   MC_LAUNCHED();
   return 0;
 }
 int mc_rmsprop(const float* w, const float* dw, const float* cache, float* w_out, float* cache_out, float lr, float decay,
                float eps, int64_t n) {
   if (n <= 0) return 0;
-  rmsprop_kernel<<<grid_for(n, L_THREADS), L_THREADS, 0, stream()>>>(w, dw, cache, w_out, cache_out, lr, decay, eps, n);
+  mc::launch(rmsprop_kernel, grid_for(n, L_THREADS), L_THREADS, 0, w, dw, cache, w_out, cache_out, lr, decay, eps, n);
   MC_LAUNCHED();
   return 0;
 }
@@ -676,7 +782,7 @@ int mc_adam(const float* w, const float* dw, const float* m, const float* v, flo
   if (n <= 0) return 0;
   const float bc1 = (float)(1.0 - pow((double)beta1, (double)t));
   const float bc2 = (float)(1.0 - pow((double)beta2, (double)t));
-  adam_kernel<<<grid_for(n, L_THREADS), L_THREADS, 0, stream()>>>(w, dw, m, v, w_out, m_out, v_out, lr, beta1, beta2, eps, bc1,
+  mc::launch(adam_kernel, grid_for(n, L_THREADS), L_THREADS, 0, w, dw, m, v, w_out, m_out, v_out, lr, beta1, beta2, eps, bc1,
                                                                 bc2, n);
   MC_LAUNCHED();
   return 0;
@@ -707,6 +813,7 @@ struct MultiUpdateDesc {
 };
 
 __global__ void __launch_bounds__(L_THREADS) multi_update_kernel(const __grid_constant__ MultiUpdateDesc d) {
+  mc::pdl_sync();
   int t = 0;
   while (t + 1 < d.count && (int)blockIdx.x >= d.first[t + 1]) ++t;
   const float* __restrict__ w = d.w[t];
@@ -803,7 +910,7 @@ int mc_multi_update(int rule, int count, const void* const* w, const void* const
     }
     if (d.count == 0) continue;
     d.first[d.count] = blocks;
-    mc::multi_update_kernel<<<blocks, mc::L_THREADS, 0, mc::stream()>>>(d);
+    mc::launch(mc::multi_update_kernel, blocks, mc::L_THREADS, 0, d);
     MC_LAUNCHED();
   }
   return 0;

@@ -27,6 +27,7 @@ __global__ void __launch_bounds__(LS_THREADS) lstm_fwd_part_kernel(const float* 
                                                                    int splits, const float* __restrict__ prev_c,
                                                                    float* __restrict__ next_h, float* __restrict__ next_c,
                                                                    float* __restrict__ gates, int64_t N, int64_t H) {
+  mc::pdl_sync();
   const int64_t n = N * H, slice = n * 4;
   const int64_t stride = (int64_t)gridDim.x * LS_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * LS_THREADS + threadIdx.x; t < n; t += stride) {
@@ -52,6 +53,7 @@ __global__ void __launch_bounds__(LS_THREADS) lstm_bwd_part_kernel(const float* 
                                                                    const float* __restrict__ ws, int splits,
                                                                    const float* __restrict__ dnext_c, float* __restrict__ da,
                                                                    float* __restrict__ dprev_c, int64_t N, int64_t H) {
+  mc::pdl_sync();
   const int64_t n = N * H;
   const int64_t stride = (int64_t)gridDim.x * LS_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * LS_THREADS + threadIdx.x; t < n; t += stride) {
@@ -86,6 +88,7 @@ __global__ void __launch_bounds__(LS4_THREADS) lstm_fwd_part4_kernel(const float
                                                                      int splits, const float* __restrict__ prev_c,
                                                                      float* __restrict__ next_h, float* __restrict__ next_c,
                                                                      float* __restrict__ gates, int64_t N, int64_t H) {
+  mc::pdl_sync();
   const int64_t H4 = H >> 2, n4 = N * H4, slice = N * H * 4;
   const int64_t stride = (int64_t)gridDim.x * LS4_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * LS4_THREADS + threadIdx.x; t < n4; t += stride) {
@@ -116,6 +119,7 @@ __global__ void __launch_bounds__(LS4_THREADS) lstm_bwd_part4_kernel(const float
                                                                      const float* __restrict__ ws, int splits,
                                                                      const float* __restrict__ dnext_c, float* __restrict__ da,
                                                                      float* __restrict__ dprev_c, int64_t N, int64_t H) {
+  mc::pdl_sync();
   const int64_t H4 = H >> 2, n4 = N * H4, n = N * H;
   const int64_t stride = (int64_t)gridDim.x * LS4_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * LS4_THREADS + threadIdx.x; t < n4; t += stride) {
@@ -177,10 +181,10 @@ int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* 
       if (rc) break;
     }
     if (vec)
-      lstm_fwd_part4_kernel<<<grid_for(sH / 4, LS4_THREADS), LS4_THREADS, 0, stream()>>>(
+      mc::launch(lstm_fwd_part4_kernel, grid_for(sH / 4, LS4_THREADS), LS4_THREADS, 0, 
           a_t, ws, splits, cbuf + t * sH, hbuf + (t + 1) * sH, cbuf + (t + 1) * sH, gates + t * sA, N, H);
     else
-      lstm_fwd_part_kernel<<<grid_for(sH, LS_THREADS), LS_THREADS, 0, stream()>>>(
+      mc::launch(lstm_fwd_part_kernel, grid_for(sH, LS_THREADS), LS_THREADS, 0, 
           a_t, ws, splits, cbuf + t * sH, hbuf + (t + 1) * sH, cbuf + (t + 1) * sH, gates + t * sA, N, H);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("lstm_fwd_part_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; break; }
@@ -203,11 +207,11 @@ int mc_lstm_seq_bwd(const float* gates, const float* cbuf, const float* Wh, floa
   for (int64_t t = T - 1; t >= 0 && rc == 0; --t) {
     const float* dnext_c = (t < T - 1) ? dc + ((t + 1) & 1) * sH : nullptr;
     if (vec)
-      lstm_bwd_part4_kernel<<<grid_for(sH / 4, LS4_THREADS), LS4_THREADS, 0, stream()>>>(
+      mc::launch(lstm_bwd_part4_kernel, grid_for(sH / 4, LS4_THREADS), LS4_THREADS, 0, 
           gates + t * sA, cbuf + t * sH, cbuf + (t + 1) * sH, dH + (t + 1) * sH, ws, pending, dnext_c, dA + t * sA,
           dc + (t & 1) * sH, N, H);
     else
-      lstm_bwd_part_kernel<<<grid_for(sH, LS_THREADS), LS_THREADS, 0, stream()>>>(
+      mc::launch(lstm_bwd_part_kernel, grid_for(sH, LS_THREADS), LS_THREADS, 0, 
           gates + t * sA, cbuf + t * sH, cbuf + (t + 1) * sH, dH + (t + 1) * sH, ws, pending, dnext_c, dA + t * sA,
           dc + (t & 1) * sH, N, H);
     cudaError_t e = cudaGetLastError();

@@ -20,6 +20,7 @@ template <class Op>
 __global__ void __launch_bounds__(RED_THREADS) reduce_rows_block_kernel(const float* __restrict__ x,
                                                                         float* __restrict__ out, int64_t red,
                                                                         int splits, int64_t seg) {
+  mc::pdl_sync();
   // block b handles row = b / splits, segment s = b % splits: [s*seg, min(red,(s+1)*seg))
   __shared__ float smem[32];
   Op op;
@@ -58,6 +59,7 @@ template <class Op>
 __global__ void __launch_bounds__(RED_THREADS) reduce_rows_warp_kernel(const float* __restrict__ x,
                                                                        float* __restrict__ out, int64_t rows,
                                                                        int64_t red) {
+  mc::pdl_sync();
   Op op;
   const int lane = threadIdx.x & 31;
   const int64_t warps_per_grid = (int64_t)gridDim.x * (RED_THREADS / 32);
@@ -86,6 +88,7 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_rows_warp_kernel(const flo
 template <class Op>
 __global__ void __launch_bounds__(RED_THREADS) reduce_cols_slab_kernel(const float* __restrict__ x, float* __restrict__ out,
                                                                        int64_t red, int64_t inner) {
+  mc::pdl_sync();
   __shared__ float sm[8][2][4];
   Op op;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, half = threadIdx.x & 1, rl = threadIdx.x >> 1;
@@ -127,6 +130,7 @@ template <class Op, int VEC>
 __global__ void __launch_bounds__(RED_THREADS) reduce_cols_kernel(const float* __restrict__ x,
                                                                   float* __restrict__ out, int64_t red,
                                                                   int64_t inner, int64_t seg) {
+  mc::pdl_sync();
   __shared__ float smem[8][32 * VEC + 1];
   Op op;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -180,7 +184,7 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
     // ---- row reduction ----
     if (red <= 1024 && outer >= 64) {
       int grid = grid_for(outer, RED_THREADS / 32);
-      reduce_rows_warp_kernel<Op><<<grid, RED_THREADS, 0, stream()>>>(x, out, outer, red);
+      mc::launch(reduce_rows_warp_kernel<Op>, grid, RED_THREADS, 0, x, out, outer, red);
       MC_LAUNCHED();
       return 0;
     }
@@ -196,13 +200,13 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
     splits = (int)((red + seg - 1) / seg);
     MC_REQUIRE(outer * splits < (int64_t)2147483647, "too many rows");
     if (splits == 1) {
-      reduce_rows_block_kernel<Op><<<(unsigned)outer, RED_THREADS, 0, stream()>>>(x, out, red, 1, seg);
+      mc::launch(reduce_rows_block_kernel<Op>, (unsigned)outer, RED_THREADS, 0, x, out, red, 1, seg);
       MC_LAUNCHED();
       return 0;
     }
     float* ws = nullptr;
     MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * outer * splits, stream()));
-    reduce_rows_block_kernel<Op><<<(unsigned)(outer * splits), RED_THREADS, 0, stream()>>>(x, ws, red, splits, seg);
+    mc::launch(reduce_rows_block_kernel<Op>, (unsigned)(outer * splits), RED_THREADS, 0, x, ws, red, splits, seg);
     MC_LAUNCHED();
     int rc = reduce_impl<Op>(ws, out, outer, splits, 1);
     MC_CHECK(cudaFreeAsync(ws, stream()));
@@ -211,7 +215,7 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
   // ---- column reduction ----
   if ((inner % 8) == 0 && aligned16(x) && red >= 128 && red * inner <= (1 << 20) && outer <= 65535) {
     dim3 grid((unsigned)(inner / 8), (unsigned)outer);
-    reduce_cols_slab_kernel<Op><<<grid, RED_THREADS, 0, stream()>>>(x, out, red, inner);
+    mc::launch(reduce_cols_slab_kernel<Op>, grid, RED_THREADS, 0, x, out, red, inner);
     MC_LAUNCHED();
     return 0;
   }
@@ -236,8 +240,8 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
     MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * outer * splits * inner, stream()));
     dst = ws;
   }
-  if (vec) reduce_cols_kernel<Op, 4><<<grid, RED_THREADS, 0, stream()>>>(x, dst, red, inner, seg);
-  else reduce_cols_kernel<Op, 1><<<grid, RED_THREADS, 0, stream()>>>(x, dst, red, inner, seg);
+  if (vec) mc::launch(reduce_cols_kernel<Op, 4>, grid, RED_THREADS, 0, x, dst, red, inner, seg);
+  else mc::launch(reduce_cols_kernel<Op, 1>, grid, RED_THREADS, 0, x, dst, red, inner, seg);
   MC_LAUNCHED();
   if (splits > 1) {
     int rc = reduce_impl<Op>(ws, out, outer, splits, inner);
@@ -263,6 +267,7 @@ __device__ __forceinline__ bool arg_better(float v, int64_t i, float bv, int64_t
 __global__ void __launch_bounds__(RED_THREADS) argmax_thread_kernel(const float* __restrict__ x,
                                                                     int64_t* __restrict__ out, int64_t outer,
                                                                     int64_t red, int64_t inner) {
+  mc::pdl_sync();
   const int64_t n = outer * inner;
   const int64_t stride = (int64_t)gridDim.x * RED_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; t < n; t += stride) {
@@ -281,6 +286,7 @@ __global__ void __launch_bounds__(RED_THREADS) argmax_thread_kernel(const float*
 __global__ void __launch_bounds__(RED_THREADS) argmax_rows_warp_kernel(const float* __restrict__ x,
                                                                        int64_t* __restrict__ out, int64_t rows,
                                                                        int64_t red) {
+  mc::pdl_sync();
   const int lane = threadIdx.x & 31;
   const int64_t warps_per_grid = (int64_t)gridDim.x * (RED_THREADS / 32);
   for (int64_t row = (int64_t)blockIdx.x * (RED_THREADS / 32) + (threadIdx.x >> 5); row < rows; row += warps_per_grid) {
@@ -303,6 +309,7 @@ __global__ void __launch_bounds__(RED_THREADS) argmax_rows_warp_kernel(const flo
 
 __global__ void __launch_bounds__(RED_THREADS) bcast_mid_kernel(const float* __restrict__ g, float* __restrict__ out,
                                                                 float scale, int64_t red, int64_t inner, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * RED_THREADS;
   const int64_t ri = red * inner;
   for (int64_t t = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; t < n; t += stride) {
@@ -315,6 +322,7 @@ __global__ void __launch_bounds__(RED_THREADS) select_grad_kernel(const float* _
                                                                   const float* __restrict__ ans,
                                                                   const float* __restrict__ g, float* __restrict__ out,
                                                                   int64_t red, int64_t inner, int64_t n) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * RED_THREADS;
   const int64_t ri = red * inner;
   for (int64_t t = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; t < n; t += stride) {
@@ -349,9 +357,9 @@ int mc_argmax(const float* x, int64_t* out, int64_t outer, int64_t red, int64_t 
   MC_REQUIRE(red > 0, "argmax of an empty axis");
   if (outer * inner == 0) return 0;
   if (inner == 1 && red >= 64) {
-    argmax_rows_warp_kernel<<<grid_for(outer, RED_THREADS / 32), RED_THREADS, 0, stream()>>>(x, out, outer, red);
+    mc::launch(argmax_rows_warp_kernel, grid_for(outer, RED_THREADS / 32), RED_THREADS, 0, x, out, outer, red);
   } else {
-    argmax_thread_kernel<<<grid_for(outer * inner, RED_THREADS), RED_THREADS, 0, stream()>>>(x, out, outer, red, inner);
+    mc::launch(argmax_thread_kernel, grid_for(outer * inner, RED_THREADS), RED_THREADS, 0, x, out, outer, red, inner);
   }
   MC_LAUNCHED();
   return 0;
@@ -360,7 +368,7 @@ int mc_argmax(const float* x, int64_t* out, int64_t outer, int64_t red, int64_t 
 int mc_bcast_mid(const float* g, float* out, float scale, int64_t outer, int64_t red, int64_t inner) {
   const int64_t n = outer * red * inner;
   if (n <= 0) return 0;
-  bcast_mid_kernel<<<grid_for(n, RED_THREADS), RED_THREADS, 0, stream()>>>(g, out, scale, red, inner, n);
+  mc::launch(bcast_mid_kernel, grid_for(n, RED_THREADS), RED_THREADS, 0, g, out, scale, red, inner, n);
   MC_LAUNCHED();
   return 0;
 }
@@ -369,7 +377,7 @@ int mc_select_grad(const float* x, const float* ans, const float* g, float* out,
                    int64_t inner) {
   const int64_t n = outer * red * inner;
   if (n <= 0) return 0;
-  select_grad_kernel<<<grid_for(n, RED_THREADS), RED_THREADS, 0, stream()>>>(x, ans, g, out, red, inner, n);
+  mc::launch(select_grad_kernel, grid_for(n, RED_THREADS), RED_THREADS, 0, x, ans, g, out, red, inner, n);
   MC_LAUNCHED();
   return 0;
 }

@@ -2,6 +2,7 @@
 // caching allocator, copies, events, CUDA-graph capture and the launch counter.
 #include <atomic>
 #include <stdarg.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace mc {
@@ -29,6 +30,11 @@ void set_error(const char* fmt, ...) {
 cudaStream_t stream() { return g_stream; }
 int sm_count() { return g_sm_count; }
 int device() { return g_device; }
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("MC_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
+  return on == 1;
+}
 bool first_use_on_device(uint32_t* mask) {
   const uint32_t bit = 1u << (g_device < 0 ? 0 : g_device);
   if (*mask & bit) return false;

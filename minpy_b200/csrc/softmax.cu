@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(SM_THREADS) softmax_warp_kernel(const float* _
                                                                   const float* __restrict__ onehot,
                                                                   float* __restrict__ rowloss, int64_t rows,
                                                                   int64_t cols) {
+  mc::pdl_sync();
   const int lane = threadIdx.x & 31;
   const int64_t warps_per_grid = (int64_t)gridDim.x * (SM_THREADS / 32);
   const bool vec = ((cols & 3) == 0) && ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) &&
@@ -142,6 +143,7 @@ __global__ void __launch_bounds__(SM_THREADS) softmax_block_kernel(const float* 
                                                                    const int32_t* __restrict__ labels,
                                                                    const float* __restrict__ onehot,
                                                                    float* __restrict__ rowloss, int64_t cols) {
+  mc::pdl_sync();
   __shared__ float smem[32];
   const int64_t row = blockIdx.x;
   const float* __restrict__ p = x + row * cols;
@@ -185,21 +187,23 @@ static int launch_softmax(const float* x, float* out, const int32_t* labels, con
                           int64_t rows, int64_t cols) {
   if (cols <= 32 * ROW_REGS) {
     int grid = grid_for(rows, SM_THREADS / 32);
-    softmax_warp_kernel<MODE><<<grid, SM_THREADS, 0, stream()>>>(x, out, labels, onehot, rowloss, rows, cols);
+    mc::launch(softmax_warp_kernel<MODE>, grid, SM_THREADS, 0, x, out, labels, onehot, rowloss, rows, cols);
   } else {
     MC_REQUIRE(rows < (int64_t)2147483647, "too many rows");
-    softmax_block_kernel<MODE><<<(unsigned)rows, SM_THREADS, 0, stream()>>>(x, out, labels, onehot, rowloss, cols);
+    mc::launch(softmax_block_kernel<MODE>, (unsigned)rows, SM_THREADS, 0, x, out, labels, onehot, rowloss, cols);
   }
   MC_LAUNCHED();
   return 0;
 }
 
 __global__ void __launch_bounds__(SM_THREADS) scale_scalar_kernel(float* __restrict__ v, float s) {
+  mc::pdl_sync();
   if (threadIdx.x == 0 && blockIdx.x == 0) v[0] *= s;
 }
 
 __global__ void __launch_bounds__(SM_THREADS) onehot_kernel(const int32_t* __restrict__ idx, float* __restrict__ out,
                                                             int64_t rows, int64_t cols) {
+  mc::pdl_sync();
   const int64_t stride = (int64_t)gridDim.x * SM_THREADS;
   for (int64_t r = (int64_t)blockIdx.x * SM_THREADS + threadIdx.x; r < rows; r += stride) {
     int32_t c = idx[r];
@@ -213,6 +217,7 @@ __global__ void __launch_bounds__(SM_THREADS) softmax_ce_bwd_kernel(const float*
                                                                     const float* __restrict__ onehot,
                                                                     float* __restrict__ dx, int64_t rows, int64_t cols,
                                                                     float inv_rows) {
+  mc::pdl_sync();
   const int64_t n = rows * cols;
   const int64_t stride = (int64_t)gridDim.x * SM_THREADS;
   for (int64_t t = (int64_t)blockIdx.x * SM_THREADS + threadIdx.x; t < n; t += stride) {
@@ -224,6 +229,42 @@ __global__ void __launch_bounds__(SM_THREADS) softmax_ce_bwd_kernel(const float*
       y = onehot[t];
     }
     dx[t] = (probs[t] - y) * inv_rows;
+  }
+}
+
+// softmax_loss for a classifier head (cols <= 32, integer labels): ONE block does everything the three
+// launches of mc_softmax_ce_fwd plus mc_softmax_ce_bwd do -- probabilities, the mean cross-entropy (row
+// losses summed per warp in row order, the 32 warp sums in warp order: deterministic) and, because the VJP
+// of the reference's softmax_output ignores its upstream gradient (numpy_core.py:170-175), the gradient
+// (p - onehot) / rows itself.  The whole problem is a few tens of KB: one launch of latency instead of four.
+__global__ void __launch_bounds__(1024) softmax_ce_small_kernel(const float* __restrict__ x, const int32_t* __restrict__ labels,
+                                                                float* __restrict__ probs, float* __restrict__ dx,
+                                                                float* __restrict__ loss, int rows, int cols, float inv_rows) {
+  mc::pdl_sync();
+  __shared__ float wsum[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  float acc = 0.f;
+  for (int row = warp; row < rows; row += nw) {
+    const int64_t base = (int64_t)row * cols;
+    const float v = lane < cols ? x[base + lane] : -INFINITY;
+    const float m = warp_max(v);
+    const float e = lane < cols ? expf(v - m) : 0.f;
+    const float s = warp_sum(e);
+    const float pr = e / s;
+    const int lab = labels[row];
+    if (lane < cols) {
+      if (probs) probs[base + lane] = pr;
+      if (dx) dx[base + lane] = (pr - (lane == lab ? 1.f : 0.f)) * inv_rows;
+    }
+    const float pl = __shfl_sync(0xffffffffu, pr, lab & 31);
+    acc -= logf(pl);
+  }
+  if (lane == 0) wsum[warp] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < nw; ++w) t += wsum[w];
+    *loss = t * inv_rows;
   }
 }
 
@@ -246,7 +287,7 @@ int mc_logsumexp_rows(const float* x, float* out, int64_t rows, int64_t cols) {
 
 int mc_onehot(const int32_t* idx, float* out, int64_t rows, int64_t cols) {
   if (rows <= 0) return 0;
-  onehot_kernel<<<grid_for(rows, SM_THREADS), SM_THREADS, 0, stream()>>>(idx, out, rows, cols);
+  mc::launch(onehot_kernel, grid_for(rows, SM_THREADS), SM_THREADS, 0, idx, out, rows, cols);
   MC_LAUNCHED();
   return 0;
 }
@@ -260,7 +301,7 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels, const float* onehot
   int rc = launch_softmax<MODE_CE>(x, probs, labels, onehot, rowloss, rows, cols);
   if (rc == 0) rc = reduce_sum_internal(rowloss, loss, 1, rows, 1);
   if (rc == 0) {
-    scale_scalar_kernel<<<1, 32, 0, stream()>>>(loss, 1.f / (float)rows);
+    mc::launch(scale_scalar_kernel, 1, 32, 0, loss, 1.f / (float)rows);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { mc::set_error("scale launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else mc::count_launch();
@@ -269,11 +310,28 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels, const float* onehot
   return rc;
 }
 
+int mc_softmax_ce_fused(const float* x, const int32_t* labels, const float* onehot, float* probs, float* dx, float* loss,
+                        int64_t rows, int64_t cols) {
+  MC_REQUIRE((labels != nullptr) != (onehot != nullptr), "exactly one of labels / onehot");
+  MC_REQUIRE(rows > 0 && cols > 0, "empty input");
+  MC_REQUIRE(probs != nullptr || dx != nullptr, "nothing to write");
+  if (labels && cols <= 32 && rows <= 16384) {
+    mc::launch(softmax_ce_small_kernel, 1, 1024, 0, x, labels, probs, dx, loss, (int)rows, (int)cols, 1.f / (float)rows);
+    MC_LAUNCHED();
+    return 0;
+  }
+  // general shapes: the multi-launch forward, then the gradient from the probabilities
+  float* p = probs ? probs : dx;
+  if (mc_softmax_ce_fwd(x, labels, onehot, p, loss, rows, cols)) return 1;
+  if (dx) return mc_softmax_ce_bwd(p, labels, onehot, dx, rows, cols);
+  return 0;
+}
+
 int mc_softmax_ce_bwd(const float* probs, const int32_t* labels, const float* onehot, float* dx, int64_t rows,
                       int64_t cols) {
   MC_REQUIRE((labels != nullptr) != (onehot != nullptr), "exactly one of labels / onehot");
   if (rows * cols <= 0) return 0;
-  softmax_ce_bwd_kernel<<<grid_for(rows * cols, SM_THREADS), SM_THREADS, 0, stream()>>>(probs, labels, onehot, dx, rows,
+  mc::launch(softmax_ce_bwd_kernel, grid_for(rows * cols, SM_THREADS), SM_THREADS, 0, probs, labels, onehot, dx, rows,
                                                                                        cols, 1.f / (float)rows);
   MC_LAUNCHED();
   return 0;

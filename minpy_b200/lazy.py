@@ -13,9 +13,75 @@ from __future__ import annotations
 import numpy as np
 
 from . import ops
-from .cuda_array import CudaArray
+from .cuda_array import CudaArray, _Buffer, _state as _cuda_state
 
 FULL, ROW, COL, ONE = 0, 1, 2, 3
+DROPOUT = 'DROPOUT'     # marker step: the keep-mask of a dropout, regenerated from (seed, offset); see drop_step
+
+_PTR = CudaArray.__dict__['ptr']
+_BUF = CudaArray.__dict__['buf']
+
+
+class LazyArray(CudaArray):
+    """A forward value whose producing kernel has NOT been launched yet (the forward counterpart of
+    ChainGrad).  `layers.affine` and `layers.batchnorm` return one: if the very next layer call is one the
+    producer can absorb -- relu into the GEMM epilogue, dropout into the batchnorm store -- that call
+    launches the fused kernel and this object is never evaluated; anything else that touches `.ptr` /
+    `.buf` (any kernel argument, asnumpy, a reshape) evaluates it on the spot through `thunk(self)`,
+    which must end in `bind`.  Shape, dtype and device are known without evaluation."""
+    __slots__ = ('_thunk', '_pool', '_dev')
+
+    def __init__(self, shape, thunk, saved=None):  # pylint: disable=super-init-not-called
+        self.shape = tuple(int(s) for s in shape)
+        self.size = ops._prod(self.shape)  # pylint: disable=protected-access
+        self.dtype = ops._F32  # pylint: disable=protected-access
+        self._saved = saved
+        self._tag = None
+        self._readback = None
+        self._thunk = thunk
+        self._pool = _Buffer._active_pool  # pylint: disable=protected-access
+        self._dev = _cuda_state['device']
+
+    def pending(self):
+        return self._thunk is not None
+
+    def bind(self, arr):
+        """Adopt the storage of the computed array."""
+        _BUF.__set__(self, arr.buf)
+        _PTR.__set__(self, arr.ptr)
+        self._thunk = None
+
+    def _force(self):
+        thunk = self._thunk
+        if thunk is not None:
+            if self._pool is not _Buffer._active_pool:  # pylint: disable=protected-access
+                raise RuntimeError('a lazily evaluated value of a captured step was used outside that capture')
+            thunk(self)
+            if self._thunk is not None:
+                raise RuntimeError('lazy value: the thunk did not bind a result')
+
+    @property
+    def ptr(self):
+        if self._thunk is not None:
+            self._force()
+        return _PTR.__get__(self, CudaArray)
+
+    @property
+    def buf(self):
+        if self._thunk is not None:
+            self._force()
+        return _BUF.__get__(self, CudaArray)
+
+    @property
+    def device(self):
+        return self._dev
+
+
+def drop_step(prob, seed, offset):
+    """Marker factor of a ChainGrad: multiply by the keep-mask of dropout(prob, seed, offset).  Never reaches
+    mc_vjp_chain: batchnorm's VJP consumes it inside its fused kernel; `materialize` otherwise runs
+    mc_dropout between the chain segments."""
+    return (DROPOUT, int(seed), FULL, int(offset), FULL, float(prob), 1)
 
 
 class ChainGrad(object):
@@ -53,9 +119,30 @@ class ChainGrad(object):
             return ChainGrad(shape, g, self.g_scalar, self.g_mode, self.g_inner, self.steps)
         return ChainGrad(shape, self.materialize().reshape(shape))
 
+    def _materialize_mixed(self, acc):
+        """A recipe that contains dropout marker steps: chain segment, mc_dropout, chain segment, ..."""
+        cur = ChainGrad(self.shape, self.g, self.g_scalar, self.g_mode, self.g_inner)
+        pending = []
+        for step in self.steps:
+            if step[0] != DROPOUT:
+                pending.append(step)
+                continue
+            base = ChainGrad(cur.shape, cur.g, cur.g_scalar, cur.g_mode, cur.g_inner, tuple(pending)).materialize() \
+                if (pending or cur.g is None or cur.g_mode != FULL or cur.g_scalar != 1.0) else cur.g
+            if base.shape != self.shape:
+                base = base.reshape(self.shape)
+            out = CudaArray.empty(self.shape)
+            if out.size:
+                ops.L().mc_dropout(base.ptr, out.ptr, out.size, step[5], step[1], step[3])
+            cur, pending = ChainGrad(self.shape, out), []
+        return ChainGrad(self.shape, cur.g, cur.g_scalar, cur.g_mode, cur.g_inner, tuple(pending)).materialize(acc)
+
     def materialize(self, acc=None):
         """Run the recipe: one kernel per 12 steps; `acc` (same shape) is added in the same
         kernel, which is how gradient accumulation on the tape is fused."""
+        for step in self.steps:
+            if step[0] == DROPOUT:
+                return self._materialize_mixed(acc)
         if not self.steps and acc is None and self.g is not None and self.g_mode == FULL and self.g_scalar == 1.0:
             return self.g if self.g.shape == self.shape else self.g.reshape(self.shape)
         return ops.run_chain(self.g, self.g_scalar, list(self.steps), self.shape, acc=acc,

@@ -555,7 +555,8 @@ def set_gemm_precision(mode):
 
 
 def gemm(a, b, trans_a=False, trans_b=False, bias=None, relu=False, out=None, accumulate=False):
-    """op(a) @ op(b) for 2-D operands, optional fused bias / relu / accumulate."""
+    """op(a) @ op(b) for 2-D operands, optional fused bias / relu / accumulate (relu: False / True, or 2 =
+    the signed-zero mode of mc_gemm)."""
     lib = L()
     a, b = as_f32(a), as_f32(b)
     if a.ndim != 2 or b.ndim != 2:
@@ -567,7 +568,7 @@ def gemm(a, b, trans_a=False, trans_b=False, bias=None, relu=False, out=None, ac
     if out is None:
         out = CudaArray.empty((M, N))
     lib.mc_gemm(1 if trans_a else 0, 1 if trans_b else 0, M, N, K, a.ptr, a.shape[1], b.ptr, b.shape[1],
-                out.ptr, N, bias.ptr if bias is not None else None, 1 if relu else 0, 1 if accumulate else 0,
+                out.ptr, N, bias.ptr if bias is not None else None, int(relu), 1 if accumulate else 0,
                 _gemm_precision['mode'])
     return out
 

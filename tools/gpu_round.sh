@@ -1,0 +1,34 @@
+#!/bin/bash
+# One GPU-box visit: the GPU suite, the default bench line, the reference arm, toggled variants of the
+# mlp_c3 step (PDL on/off, forward fusion on/off, cluster split-K), and the ncu launch list of the default
+# command.  Usage (from the repo root, through gpurun):  bash tools/gpu_round.sh <tag>
+tag=${1:-run}
+out=gpurun_out/$tag
+mkdir -p $out
+python -m pytest tests -m gpu -q -x > $out/pytest.log 2>&1; echo "pytest rc=$?" | tee -a $out/pytest.log
+tail -3 $out/pytest.log
+quick="--no-ufunc --no-cpu-baseline --no-workloads --steps 50 --warmup 5"
+for w in mlp_c3 mlp_c1 cnn_c4 lstm_c5; do
+  python bench.py $quick --workload $w > $out/bench_$w.json 2> $out/bench_$w.err; echo "bench $w rc=$?"
+done
+MC_PDL=0 python bench.py $quick > $out/bench_mlp_c3_nopdl.json 2> $out/bench_mlp_c3_nopdl.err
+MC_PDL=0 python bench.py $quick --workload lstm_c5 > $out/bench_lstm_c5_nopdl.json 2> $out/bench_lstm_c5_nopdl.err
+MINPY_FUSE_FORWARD=0 python bench.py $quick > $out/bench_mlp_c3_nofuse.json 2> $out/bench_mlp_c3_nofuse.err
+MC_GEMM_CLUSTER=4 python bench.py $quick > $out/bench_mlp_c3_cluster4.json 2> $out/bench_mlp_c3_cluster4.err
+MC_GEMM_CLUSTER=8 python bench.py $quick > $out/bench_mlp_c3_cluster8.json 2> $out/bench_mlp_c3_cluster8.err
+python - <<PY
+import json, glob, os
+for f in sorted(glob.glob('$out/bench_*.json')):
+    try:
+        d = json.loads(open(f).read().strip().splitlines()[-1])
+        r = d['roofline']
+        print('%-34s %8.4f ms/step  e2e %8.4f  launches/step %6.1f  top %s %.2f us x %.1f frac %.3f' % (
+            os.path.basename(f), d['ms_per_step'], d['e2e']['ms_per_step'], d['launches_per_step'], r['kernel'].split()[0],
+            r['avg_us_per_launch'], r['launches_per_step'], r['frac']))
+    except Exception as e:
+        print(os.path.basename(f), 'FAILED', e)
+PY
+python bench.py > $out/bench_default.json 2> $out/bench_default.err; echo "default bench rc=$?"
+python bench.py --impl reference --steps 20 --warmup 5 > $out/bench_reference.json 2> $out/bench_reference.err; echo "reference rc=$?"
+ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file $out/launches_mlp_c3.csv \
+    python bench.py $quick --steps 10 > $out/ncu_launches.log 2>&1; echo "ncu rc=$?"
