@@ -403,6 +403,10 @@ int mc_maxpool2d_fwd(const float* x, float* y, int32_t* argmax_i32, int64_t NC, 
                      int64_t KH, int64_t KW, int64_t stride);
 int mc_maxpool2d_bwd(const float* dy, const int32_t* argmax_i32, float* dx_zeroed, int64_t NC,
                      int64_t H, int64_t W, int64_t OH, int64_t OW);
+/* MXNet Pooling(pool_type='avg'), 'valid' windows, NCHW planes (nn/modules.py:273-290, resnet.py:39):
+ * y = mean over the KH x KW window; dx gathers dy over the windows containing each element. */
+int mc_avgpool2d_fwd(const float* x, float* y, int64_t NC, int64_t H, int64_t W, int64_t KH, int64_t KW, int64_t stride);
+int mc_avgpool2d_bwd(const float* dy, float* dx, int64_t NC, int64_t H, int64_t W, int64_t KH, int64_t KW, int64_t stride);
 
 #ifdef __cplusplus
 }

@@ -148,6 +148,43 @@ __global__ void __launch_bounds__(CV_THREADS) maxpool_bwd_kernel(const float* __
   }
 }
 
+// 'valid' average pooling over NCHW planes (MXNet Pooling pool_type='avg': the mean over the kh x kw window).
+__global__ void __launch_bounds__(CV_THREADS) avgpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t NC,
+                                                                 int H, int W, int KH, int KW, int stride, int OH, int OW) {
+  mc::pdl_sync();
+  const int64_t n = NC * OH * OW;
+  const int64_t gs = (int64_t)gridDim.x * CV_THREADS;
+  const float inv = 1.0f / (float)(KH * KW);
+  for (int64_t t = (int64_t)blockIdx.x * CV_THREADS + threadIdx.x; t < n; t += gs) {
+    const int wo = (int)(t % OW), ho = (int)((t / OW) % OH);
+    const float* __restrict__ xp = x + (t / ((int64_t)OW * OH)) * H * W + (int64_t)ho * stride * W + wo * stride;
+    float acc = 0.f;
+    for (int kh = 0; kh < KH; ++kh)
+      for (int kw = 0; kw < KW; ++kw) acc += xp[kh * W + kw];
+    y[t] = acc * inv;
+  }
+}
+// dx[h, w] = (1 / (kh kw)) * sum of dy over the windows that contain (h, w): a gather in window order
+// (deterministic; overlapping windows need no atomics).
+__global__ void __launch_bounds__(CV_THREADS) avgpool_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int64_t NC,
+                                                                 int H, int W, int KH, int KW, int stride, int OH, int OW) {
+  mc::pdl_sync();
+  const int64_t n = NC * H * W;
+  const int64_t gs = (int64_t)gridDim.x * CV_THREADS;
+  const float inv = 1.0f / (float)(KH * KW);
+  for (int64_t t = (int64_t)blockIdx.x * CV_THREADS + threadIdx.x; t < n; t += gs) {
+    const int w = (int)(t % W), h = (int)((t / W) % H);
+    const float* __restrict__ gp = dy + (t / ((int64_t)W * H)) * OH * OW;
+    // windows ho with ho*stride <= h <= ho*stride + KH - 1
+    const int ho_lo = h - KH + 1 > 0 ? (h - KH + 1 + stride - 1) / stride : 0, ho_hi = min(OH - 1, h / stride);
+    const int wo_lo = w - KW + 1 > 0 ? (w - KW + 1 + stride - 1) / stride : 0, wo_hi = min(OW - 1, w / stride);
+    float acc = 0.f;
+    for (int ho = ho_lo; ho <= ho_hi; ++ho)
+      for (int wo = wo_lo; wo <= wo_hi; ++wo) acc += gp[ho * OW + wo];
+    dx[t] = acc * inv;
+  }
+}
+
 int reduce_sum_internal(const float* x, float* out, int64_t outer, int64_t red, int64_t inner);
 
 static int round4(int64_t v) { return (int)((v + 3) / 4 * 4); }
@@ -294,6 +331,28 @@ int mc_maxpool2d_fwd(const float* x, float* y, int32_t* argmax, int64_t NC, int6
   if (n <= 0) return 0;
   mc::launch(maxpool_fwd_kernel, grid_for(n, CV_THREADS), CV_THREADS, 0, x, y, argmax, NC, (int)H, (int)W, (int)KH, (int)KW,
                                                                         (int)stride, (int)OH, (int)OW);
+  MC_LAUNCHED();
+  return 0;
+}
+
+int mc_avgpool2d_fwd(const float* x, float* y, int64_t NC, int64_t H, int64_t W, int64_t KH, int64_t KW, int64_t stride) {
+  const int64_t OH = (H - KH) / stride + 1, OW = (W - KW) / stride + 1;
+  MC_REQUIRE(OH > 0 && OW > 0 && stride > 0, "pool kernel larger than input");
+  const int64_t n = NC * OH * OW;
+  if (n <= 0) return 0;
+  mc::launch(avgpool_fwd_kernel, grid_for(n, CV_THREADS), CV_THREADS, 0, x, y, NC, (int)H, (int)W, (int)KH, (int)KW, (int)stride,
+             (int)OH, (int)OW);
+  MC_LAUNCHED();
+  return 0;
+}
+
+int mc_avgpool2d_bwd(const float* dy, float* dx, int64_t NC, int64_t H, int64_t W, int64_t KH, int64_t KW, int64_t stride) {
+  const int64_t OH = (H - KH) / stride + 1, OW = (W - KW) / stride + 1;
+  MC_REQUIRE(OH > 0 && OW > 0 && stride > 0, "pool kernel larger than input");
+  const int64_t n = NC * H * W;
+  if (n <= 0) return 0;
+  mc::launch(avgpool_bwd_kernel, grid_for(n, CV_THREADS), CV_THREADS, 0, dy, dx, NC, (int)H, (int)W, (int)KH, (int)KW, (int)stride,
+             (int)OH, (int)OW);
   MC_LAUNCHED();
   return 0;
 }

@@ -718,6 +718,30 @@ def maxpool2d_bwd(dy, arg, xshape):
     return dx
 
 
+def avgpool2d_fwd(x, kernel, stride):
+    """'valid' average pooling over NCHW."""
+    x = as_f32(x)
+    N, C, H, W = x.shape
+    KH, KW = (kernel, kernel) if isinstance(kernel, int) else kernel
+    OH, OW = (H - KH) // stride + 1, (W - KW) // stride + 1
+    if OH <= 0 or OW <= 0:
+        raise ValueError('avgpool2d: kernel larger than input')
+    y = CudaArray.empty((N, C, OH, OW))
+    if y.size:
+        L().mc_avgpool2d_fwd(x.ptr, y.ptr, N * C, H, W, KH, KW, stride)
+    return y
+
+
+def avgpool2d_bwd(dy, xshape, kernel, stride):
+    dy = as_f32(dy)
+    N, C, H, W = xshape
+    KH, KW = (kernel, kernel) if isinstance(kernel, int) else kernel
+    dx = CudaArray.empty(xshape)
+    if dx.size:
+        L().mc_avgpool2d_bwd(dy.ptr, dx.ptr, N * C, H, W, KH, KW, stride)
+    return dx
+
+
 # ------------------------------------------------------- channels-last (NHWC) conv trunk ----
 class Nhwc(object):
     """A channels-last activation: buffer (N, H, W + 2*wpad, Cp) for the logical NCHW tensor

@@ -145,10 +145,16 @@ class Plan(object):
                     else:
                         values[key] = ops.unary(op, x)
             elif node.op == 'Pooling':
-                if a['pool_type'] != 'max' or a['global_pool'] or a['pad'] != (0, 0):
-                    raise NotImplementedError('only un-padded max pooling is lowered (avg / global pooling: next)')
+                if a['pad'] != (0, 0):
+                    raise NotImplementedError('padded pooling is not lowered')
                 k, stride = a['kernel'], _sq(a['stride'], 'stride')
-                if isinstance(x, ops.Nhwc) and k[0] == k[1] == stride and not x.wpad:
+                if a['global_pool']:
+                    k, stride = tuple(_nchw(x).shape[2:]), 1
+                if a['pool_type'] == 'avg':
+                    x = _nchw(x)
+                    values[key] = ops.avgpool2d_fwd(x, k, stride)
+                    saved[key] = ('avg', x.shape, k, stride)
+                elif isinstance(x, ops.Nhwc) and k[0] == k[1] == stride and not x.wpad:
                     y, idx = ops.maxpool2d_nhwc_fwd(x, stride, want_idx=train)
                     values[key] = y
                     saved[key] = (idx, x)
@@ -171,8 +177,15 @@ class Plan(object):
                 values[key] = ops.softmax_rows(x)
                 saved[key] = values[id(node.inputs[1])]
             elif node.op == 'BatchNorm':
-                if x.ndim != 2:
-                    raise NotImplementedError('spatial BatchNorm is not lowered yet (SURVEY.md 8f rank 1)')
+                x = _nchw(x)
+                spatial = None
+                if x.ndim == 4:
+                    # spatial batchnorm: statistics per channel over (N, H, W) = the 2-D kernels on the
+                    # (N*H*W, C) channels-last matrix
+                    spatial = x.shape
+                    x = ops.transpose(x, (0, 2, 3, 1)).reshape((x.shape[0] * x.shape[2] * x.shape[3], x.shape[1]))
+                elif x.ndim != 2:
+                    raise NotImplementedError('BatchNorm expects (N, C) or (N, C, H, W) data')
                 gamma, beta = values[id(node.inputs[1])], values[id(node.inputs[2])]
                 if a['fix_gamma']:
                     gamma = ops.ones(gamma.shape)
@@ -188,14 +201,16 @@ class Plan(object):
                     lib.mc_batchnorm_train_fwd(x.ptr, gamma.ptr, beta.ptr, rm.ptr, rv.ptr, out.ptr, nrm.ptr, nrv.ptr,
                                                sm.ptr, si.ptr, N, D, a['eps'], a['momentum'])
                     new_aux[node.aux[0]], new_aux[node.aux[1]] = nrm, nrv
-                    saved[key] = (x, gamma, sm, si)
-                    values[key] = out
+                    saved[key] = (x, gamma, sm, si, spatial)
                 else:
                     N, D = x.shape
                     out = CudaArray.empty((N, D))
                     lib.mc_batchnorm_test_fwd(x.ptr, gamma.ptr, beta.ptr, rm.ptr, rv.ptr, out.ptr, N, D, a['eps'])
                     saved[key] = None
-                    values[key] = out
+                if spatial is not None:
+                    n, c, h, w = spatial
+                    out = ops.transpose(out.reshape((n, h, w, c)), (0, 3, 1, 2))
+                values[key] = out
             elif node.op == '_Plus':
                 values[key] = ops.binary(lib.MC_ADD, _nchw(x), _nchw(values[id(node.inputs[1])]))
             else:
@@ -299,7 +314,10 @@ class Plan(object):
                 if not a['no_bias']:
                     add(node.inputs[2], db)
             elif node.op == 'Pooling':
-                if want(x_node):
+                if want(x_node) and saved[key][0] == 'avg':
+                    _, xshape, k, stride = saved[key]
+                    add(x_node, ops.avgpool2d_bwd(_nchw(g), xshape, k, stride))
+                elif want(x_node):
                     arg, xin = saved[key]
                     if isinstance(xin, ops.Nhwc):
                         conv = self.pool_masks_relu.get(key)
@@ -321,10 +339,16 @@ class Plan(object):
             elif node.op == 'BatchNorm':
                 if saved[key] is None:
                     raise NotImplementedError('backward through inference-mode BatchNorm')
-                x, gamma, sm, si = saved[key]
+                x, gamma, sm, si, spatial = saved[key]
                 N, D = x.shape
+                g = _nchw(g)
+                if spatial is not None:
+                    g = ops.transpose(g, (0, 2, 3, 1)).reshape((N, D))
                 dx, dgamma, dbeta = CudaArray.empty((N, D)), CudaArray.empty((D,)), CudaArray.empty((D,))
                 lib.mc_batchnorm_train_bwd(x.ptr, g.ptr, gamma.ptr, sm.ptr, si.ptr, dx.ptr, dgamma.ptr, dbeta.ptr, N, D)
+                if spatial is not None:
+                    n, c, h, w = spatial
+                    dx = ops.transpose(dx.reshape((n, h, w, c)), (0, 3, 1, 2))
                 add(x_node, dx)
                 add(node.inputs[1], ops.zeros((D,)) if a['fix_gamma'] else dgamma)
                 add(node.inputs[2], dbeta)

@@ -1,0 +1,300 @@
+"""f1: the object-oriented model-building API -- minpy/nn/model_builder.py
+(`Module`, `Sequential`, `Layer`, `Model`, `Updater`) and minpy/nn/modules.py -- re-created on this
+front end.  Reference: /root/reference/minpy/nn/model_builder.py:39-744, modules.py:12-401,
+examples/nn/resnet.py:6-78.
+
+CPU: the container / registration / lazy-initialisation / tape / updater logic on the NumPy variant,
+held to the functional API (`core.grad_and_loss` + `nn.optim`) on the same numbers.
+GPU: a resnet.py-shaped network (strided and 1x1 convolutions, spatial BatchNorm, average pooling,
+residual `+` of modules, FullyConnected) through the symbol façade on the device, held to an independent
+implementation: torch.nn.functional on CPU in float64 with autograd (third-party agreement, as for the
+convolution oracle -- MXNet, whose operators these are, is not vendored).
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+@pytest.fixture
+def host():
+    import minpy
+    minpy.set_global_policy('only_numpy')
+    yield
+    minpy.set_global_policy('prefer_cuda')
+
+
+def _affine_layer():
+    import minpy.nn.layers as layers
+    from minpy.nn.model_builder import Layer
+
+    class Affine(Layer):
+        _module_name = 'affine'
+
+        def __init__(self, hidden, **kw):
+            super(Affine, self).__init__(('weight', 'bias'), None, kw.get('name'))
+            self._hidden = hidden
+            self._register_init_configs(kw.get('init_configs'))
+            self._register_update_configs(kw.get('update_configs'))
+
+        def forward(self, X):
+            return layers.affine(X, *self._get_params(self.weight, self.bias))
+
+        def param_shapes(self, input_shape):
+            return {self.weight: (input_shape[1], self._hidden), self.bias: (self._hidden,)}
+    return Affine
+
+
+def test_model_builder_matches_the_functional_api(host):
+    import minpy.numpy as mnp
+    from minpy import core
+    from minpy.nn import layers, optim
+    from minpy.nn.model_builder import Model, Sequential, Updater
+    from minpy.nn.modules import ReLU
+    Affine = _affine_layer()
+
+    class Net(Model):
+        def __init__(self):
+            super(Net, self).__init__(loss='softmax_loss')
+            self.body = Sequential(Affine(16, name='fc1'), ReLU(), Affine(5, name='fc2', update_configs={'learning_rate': 0.05}))
+
+        def forward(self, data, mode='training'):
+            return self.body(data)
+
+    rng = np.random.RandomState(0)
+    X, y = rng.randn(12, 7), rng.randint(0, 5, 12)
+    net = Net()
+    assert net.params == {}                                  # layers initialise on first use
+    updater = Updater(net, update_rule='sgd_momentum', learning_rate=0.1, momentum=0.9)
+    assert updater['fc2_weight'].learning_rate == 0.1        # constructor attributes are global ...
+    updater['fc2_weight'].learning_rate = 0.05               # ... and can be overridden per parameter
+    loss = net(mnp.array(X), labels=mnp.array(y))
+    assert sorted(net.params) == ['fc1_bias', 'fc1_weight', 'fc2_bias', 'fc2_weight']
+    assert net.params['fc1_weight'].shape == (7, 16) and net.params['fc2_weight'].shape == (16, 5)
+    assert np.all(net.params['fc1_bias'].asnumpy() == 0)     # default init: weights xavier, biases 0
+    grads = net.backward()
+    assert sorted(grads) == sorted(net.params)
+
+    p0 = dict((k, v.asnumpy().copy()) for k, v in net.params.items())
+
+    def f(w1, b1, w2, b2):
+        return layers.softmax_loss(layers.affine(layers.relu(layers.affine(mnp.array(X), w1, b1)), w2, b2), mnp.array(y))
+    names = ['fc1_weight', 'fc1_bias', 'fc2_weight', 'fc2_bias']
+    want, want_loss = core.grad_and_loss(f, argnum=range(4))(*[mnp.array(p0[n]) for n in names])
+    assert abs(float(loss) - float(want_loss)) < 1e-12
+    for n, g in zip(names, want):
+        np.testing.assert_allclose(grads[n].asnumpy(), g.asnumpy(), rtol=1e-10, atol=1e-12)
+
+    # two updater steps == two optim.sgd_momentum steps per parameter (state kept in the configs)
+    cfg = dict((n, {'learning_rate': 0.05 if n == 'fc2_weight' else 0.1, 'momentum': 0.9}) for n in names)
+    ref = dict((n, mnp.array(p0[n])) for n in names)
+    for _ in range(2):
+        net(mnp.array(X), labels=mnp.array(y))
+        updater(net.backward())
+        g, _ = core.grad_and_loss(f, argnum=range(4))(*[ref[n] for n in names])
+        for n, gn in zip(names, g):
+            ref[n], cfg[n] = optim.sgd_momentum(ref[n], gn, cfg[n])
+    for n in names:
+        np.testing.assert_allclose(net.params[n].asnumpy(), ref[n].asnumpy(), rtol=1e-10, atol=1e-12)
+    # selective update: only what is in the gradient dict changes
+    before = dict((n, net.params[n].asnumpy().copy()) for n in names)
+    net(mnp.array(X), labels=mnp.array(y))
+    g = net.backward()
+    updater({'fc1_bias': g['fc1_bias']})
+    assert np.any(net.params['fc1_bias'].asnumpy() != before['fc1_bias'])
+    assert np.all(net.params['fc2_weight'].asnumpy() == before['fc2_weight'])
+
+
+def test_containers_registration_and_modes(host):
+    import minpy.numpy as mnp
+    from minpy.nn.model_builder import Model, Sequential, Updater, Add, Layer
+    from minpy.nn.modules import ReLU, Dropout, Identity, Variable, BatchFlatten, Reshape, Tanh, Logistic
+    Affine = _affine_layer()
+
+    class Net(Model):
+        def __init__(self):
+            super(Net, self).__init__()                         # no loss: __call__ returns predictions
+            self.blocks = (Affine(6, name='a'), (Affine(6, name='b'), Dropout(0.5)))     # nested containers register
+            self.res = Affine(6, name='r1') + Identity()       # module arithmetic builds Add
+            self.scale = Variable((6,), init_configs={'init_rule': 'constant', 'value': 2.0}, name='scale')
+
+        def forward(self, data, mode='training'):
+            h = self.blocks[0](data)
+            h = self.blocks[1][1](self.blocks[1][0](h))
+            return self.res(h) * self.scale()
+
+    net = Net()
+    assert isinstance(net.res, Add) and len(net._modules) == 5  # pylint: disable=protected-access
+    with pytest.raises(AssertionError):
+        net.again = net.blocks[0]                               # a module is registered once
+    with pytest.raises(AssertionError):
+        Affine(3, name='loose')(mnp.zeros((2, 3)))              # a layer outside a model cannot run
+    with pytest.raises(NotImplementedError):
+        net.add_param('w', (1,))
+    out = net(mnp.ones((4, 3)))
+    assert out.shape == (4, 6)
+    assert sorted(net.params) == ['a_bias', 'a_weight', 'b_bias', 'b_weight', 'r1_bias', 'r1_weight', 'scale_variable']
+    assert np.all(net.params['scale_variable'].asnumpy() == 2.0)
+    grads = net.backward()
+    assert grads['scale_variable'].shape == (6,)
+    # training / inference reaches every layer, through tuples and binary containers
+    net.inference()
+    drop = net.blocks[1][1]
+    assert drop._mode == 'inference'  # pylint: disable=protected-access
+    x = mnp.ones((3, 5))
+    np.testing.assert_allclose(drop.forward(x).asnumpy(), 0.5 * np.ones((3, 5)))
+    net.training()
+    kept = drop.forward(mnp.ones((200, 50))).asnumpy()
+    assert set(np.unique(kept)) == {0.0, 1.0} and abs(kept.mean() - 0.5) < 0.05
+    # the small shape layers
+    seq = Sequential(Reshape((2, 6)), BatchFlatten(), Tanh(), Logistic(), ReLU())
+    assert len(seq) == 5 and seq[1].name.startswith('batch_flatten')
+    net2 = Model()
+    net2.seq = seq
+    v = seq(mnp.array(np.arange(12.0).reshape(3, 4) / 10))
+    np.testing.assert_allclose(v.asnumpy(), 1 / (1 + np.exp(-np.tanh(np.arange(12.0).reshape(2, 6) / 10))))
+    # auto names count per kind
+    a, b = ReLU(), ReLU()
+    assert a.name != b.name and a.name.startswith('ReLU')
+    # updater attribute view
+    up = Updater(net, update_rule='sgd', learning_rate=0.3)
+    assert up.learning_rate == 0.3
+    up['a_weight'].learning_rate = 0.1
+    with pytest.raises(AssertionError):
+        up.learning_rate                                         # inconsistent now  # pylint: disable=pointless-statement
+    with pytest.raises(ValueError):
+        Updater(net)({'a_weight': grads['a_weight']})            # update_rule left 'unspecified'
+    assert isinstance(net.blocks[0], Layer)
+
+
+# ------------------------------------------------------------------------------- GPU -------
+def _resnet(filters=(4, 8, 16), blocks=1, classes=10):
+    """examples/nn/resnet.py:6-78, structure unchanged."""
+    from minpy.nn.model_builder import Model, Sequential
+    from minpy.nn.modules import Convolution, BatchNorm, ReLU, Pooling, BatchFlatten, FullyConnected
+
+    class ResNet(Model):
+        def __init__(self):
+            super(ResNet, self).__init__(loss='softmax_loss')
+            f0, f1, f2 = filters
+            self._shrinking_blocks = (
+                Convolution(num_filter=f0, kernel=(3, 3), stride=(1, 1), pad=(1, 1), no_bias=True),
+                self._shrinking_block(f1), self._shrinking_block(f2))
+            self._residual_blocks = tuple(tuple(self._residual_block(f) for _ in range(blocks)) for f in filters)
+            self._to_scores = Sequential(BatchNorm(fix_gamma=False), ReLU(), Pooling(pool_type='avg', kernel=(8, 8), stride=(1, 1)),
+                                         BatchFlatten(), FullyConnected(num_hidden=classes))
+
+        def forward(self, data, mode='training'):
+            if mode == 'training':
+                self.training()
+            else:
+                self.inference()
+            for shrink, residual in zip(self._shrinking_blocks, self._residual_blocks):
+                data = shrink(data)
+                for r in residual:
+                    data = data + r(data)
+            return self._to_scores(data)
+
+        @staticmethod
+        def _convolution(**kwargs):
+            defaults = {'kernel': (3, 3), 'stride': (1, 1), 'pad': (1, 1), 'no_bias': True}
+            defaults.update(kwargs)
+            return Sequential(BatchNorm(fix_gamma=False), ReLU(), Convolution(**defaults))
+
+        @staticmethod
+        def _residual_block(f):
+            return Sequential(ResNet._convolution(num_filter=f), ResNet._convolution(num_filter=f))
+
+        @staticmethod
+        def _shrinking_block(f):
+            return Sequential(ResNet._convolution(num_filter=f, stride=(2, 2)), ResNet._convolution(num_filter=f)) + \
+                ResNet._convolution(num_filter=f, kernel=(1, 1), stride=(2, 2), pad=(0, 0))
+    return ResNet()
+
+
+def _torch_forward(module, x, P, aux):
+    """The same module tree evaluated with torch.nn.functional (float64): an interpreter over the
+    model_builder objects, sharing nothing with the device path but the parameter values."""
+    import torch
+    import torch.nn.functional as F
+    from minpy.nn import model_builder as mb, modules as md
+    if isinstance(module, mb.Sequential):
+        for m in module:
+            x = _torch_forward(m, x, P, aux)
+        return x
+    if isinstance(module, mb.Add):
+        return _torch_forward(module._left, x, P, aux) + _torch_forward(module._right, x, P, aux)  # pylint: disable=protected-access
+    if isinstance(module, md.ReLU):
+        return F.relu(x)
+    if isinstance(module, md.BatchFlatten):
+        return x.reshape(x.shape[0], -1)
+    attrs = module._symbol._node.attrs  # pylint: disable=protected-access
+    full = dict(zip(module._module_param_names, module._param_names))  # pylint: disable=protected-access
+    get = lambda role: P[[v for k, v in full.items() if k.endswith(role)][0]]
+    if isinstance(module, md.Convolution):
+        return F.conv2d(x, get('weight'), None if attrs['no_bias'] else get('bias'), stride=attrs['stride'], padding=attrs['pad'])
+    if isinstance(module, md.BatchNorm):
+        return F.batch_norm(x, None, None, get('gamma'), get('beta'), training=True, eps=attrs['eps'])
+    if isinstance(module, md.Pooling):
+        assert attrs['pool_type'] == 'avg'
+        return F.avg_pool2d(x, attrs['kernel'], attrs['stride'])
+    if isinstance(module, md.FullyConnected):
+        return F.linear(x.reshape(x.shape[0], -1), get('weight'), get('bias'))
+    raise TypeError(type(module))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('precision,tol', [('fp32', 2e-4), ('tf32', 5e-2)])
+def test_resnet_shaped_model_matches_torch_float64(precision, tol):
+    import torch
+    import minpy
+    minpy.set_global_policy('prefer_cuda')
+    import minpy.numpy as mnp
+    from minpy_b200 import ops
+    from minpy.nn.model_builder import Updater
+    ops.set_gemm_precision(precision)
+    try:
+        rng = np.random.RandomState(1)
+        X = rng.randn(8, 3, 32, 32).astype(np.float32)
+        y = rng.randint(0, 10, 8)
+        net = _resnet()
+        loss = net(mnp.array(X), labels=mnp.array(y))
+        grads = net.backward()
+        assert len(net.params) == len(grads) and all(v.on_device() for v in net.params.values())
+        assert any(k.endswith('moving_mean') for k in net.aux_params)
+        P = dict((k, torch.tensor(v.asnumpy().astype(np.float64), requires_grad=True)) for k, v in net.params.items())
+        x = torch.tensor(X.astype(np.float64))
+        for shrink, residual in zip(net._shrinking_blocks, net._residual_blocks):  # pylint: disable=protected-access
+            x = _torch_forward(shrink, x, P, None)
+            for r in residual:
+                x = x + _torch_forward(r, x, P, None)
+        scores = _torch_forward(net._to_scores, x, P, None)  # pylint: disable=protected-access
+        tloss = torch.nn.functional.cross_entropy(scores, torch.tensor(y))
+        tloss.backward()
+        assert abs(float(loss) - float(tloss)) <= (1e-5 if precision == 'fp32' else 2e-3) * abs(float(tloss))
+        worst = 0.0
+        for name, t in P.items():
+            got, want = grads[name].asnumpy().astype(np.float64), t.grad.numpy()
+            assert got.shape == want.shape, name
+            # (a relu behind a TF32 contraction: Frobenius norm, see tests/test_frontend.py rel_l2)
+            err = np.linalg.norm(got - want) / max(1e-30, np.linalg.norm(want))
+            worst = max(worst, err)
+            assert err <= tol, (name, err)
+        from conftest import record_err
+        record_err('model_builder resnet %s' % precision, worst)
+        # one updater step moves every parameter and the model still evaluates (inference mode)
+        up = Updater(net, update_rule='sgd', learning_rate=0.01)
+        before = dict((k, v.asnumpy().copy()) for k, v in net.params.items())
+        up(grads)
+        assert all(np.any(net.params[k].asnumpy() != before[k]) for k in before if np.any(grads[k].asnumpy() != 0))
+        net.inference()
+        out = net.forward(mnp.array(X), mode='inference')
+        assert out.shape == (8, 10) and np.all(np.isfinite(out.asnumpy()))
+    finally:
+        ops.set_gemm_precision('tf32')
+        minpy.set_global_policy('prefer_cuda')
