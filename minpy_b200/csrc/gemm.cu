@@ -333,6 +333,7 @@ struct GemmParams {
   int a_mn, b_mn;      // operand tile is MN-major (1) or K-major (0)
   int kb_per_split;    // k-blocks (of BK) per grid.z slice
   int cluster;         // > 1: the grid.z slices of a tile are one thread-block cluster; partials meet in DSMEM
+  int group_m;         // tile raster: CTAs walk `group_m` M-tiles for each N-tile before moving on (0 = x-major)
 };
 
 // CTA q of an S-CTA cluster sums rows [q*BM/S, (q+1)*BM/S) of the parked partial tiles of all S peers
@@ -414,7 +415,23 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  // Tile raster.  CTAs are scheduled in linear block order; with the plain x-major order one wave of 148
+  // CTAs of a 4096^3 problem touches ~5 A panels and ALL 32 B panels, so B (64 MB) is streamed from HBM
+  // once per wave: 520 MB of DRAM reads for 134 MB of operands (profiles/r1z/prof_gemm_4096.txt).  Walking
+  // `group_m` M-tiles per N-tile keeps the group's A panels L2-resident while each B panel is fetched once
+  // per group.
+  int tile_m = blockIdx.y, tile_n = blockIdx.x;
+  if (p.group_m > 0) {
+    const int tiles_m = gridDim.y, tiles_n = gridDim.x;
+    const int lin = blockIdx.y * tiles_n + blockIdx.x;
+    const int per_group = p.group_m * tiles_n;
+    const int first_m = (lin / per_group) * p.group_m;
+    const int gsize = min(tiles_m - first_m, p.group_m);
+    const int r = lin % per_group;
+    tile_m = first_m + r % gsize;
+    tile_n = r / gsize;
+  }
+  const int m0 = tile_m * BM, n0 = tile_n * BN;
   const int num_kb_total = (p.K + BK - 1) / BK;
   const int kb_begin = blockIdx.z * p.kb_per_split;
   const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
@@ -596,7 +613,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
     __shared__ int s_last;
     __threadfence();
     __syncthreads();
-    const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
+    const int tile_id = tile_m * gridDim.x + tile_n;
     if (threadIdx.x == 0) {
       const int ticket = atomicAdd(p.counters + tile_id, 1);
       s_last = (ticket == (int)gridDim.z - 1) ? 1 : 0;
@@ -803,6 +820,8 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   static int force_bn = -1, min_kb = -1;
   if (force_bn < 0) { const char* e = getenv("MC_GEMM_BN"); force_bn = e ? atoi(e) : 0; }
   if (min_kb < 0) { const char* e = getenv("MC_GEMM_MIN_KB"); min_kb = e ? atoi(e) : 8; }
+  static int split_from_kb = -1;     // smallest k-block count that is split at all (experiments: MC_GEMM_SPLIT_FROM_KB)
+  if (split_from_kb < 0) { const char* e = getenv("MC_GEMM_SPLIT_FROM_KB"); split_from_kb = e ? atoi(e) : 32; }
   // Tile width: 128 columns, except (measured, profiles/r1za gemm sweeps) for problems that are both few
   // tiles and short in K -- there 64-column tiles double the CTAs without deepening split-K:
   // (1024,512,512) 9.4 -> 8.2 us, (512,512,1024) 9.5 -> 8.3, (256,512,3072) 10.7 -> 9.5, (128,1024,4096)
@@ -828,7 +847,7 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   int splits = 1;
   // K >= 1024 only: with 16..31 k-blocks the combine launch costs more than the second slice saves
   // (profiles/r1za: (1024,512,512) 8.2 us split in two, 7.6 us whole)
-  if (tiles < sm_count() && num_kb >= 32) {
+  if (tiles < sm_count() && num_kb >= split_from_kb) {
     splits = (int)(sm_count() / tiles);
     const int maxs = num_kb / min_kb;  // at least 8 k-blocks (K = 256) per slice
     if (splits > maxs) splits = maxs;
@@ -847,6 +866,20 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   p.kb_per_split = kb_per;
   p.counters = nullptr;
   p.cluster = 0;
+  // raster only when the grid is larger than one wave: keep <= ~48 MB of A panels resident in the 126 MB L2
+  p.group_m = 0;
+  {
+    static int raster = -1;
+    if (raster < 0) { const char* e = getenv("MC_GEMM_RASTER"); raster = (e && e[0] == '0') ? 0 : 1; }
+    const int64_t tiles_m = (M + BM - 1) / BM;
+    if (raster && tiles > sm_count() && tiles_m > 1) {
+      const int64_t panel = (int64_t)BM * K * 4;
+      int64_t g = ((int64_t)48 << 20) / (panel > 0 ? panel : 1);
+      if (g < 2) g = 2;
+      if (g > tiles_m) g = tiles_m;
+      p.group_m = (int)g;
+    }
+  }
   // Cluster split-K (partials reduced through distributed shared memory, S in {2,4,8,16} slices, every
   // slice non-empty) is OFF by default: it removes splitk_reduce_kernel and the HBM workspace, and is
   // -1..+1 us per call in isolation, but whole steps got slower (C3 0.341 -> 0.348 ms, C5 3.83 -> 4.06 ms,

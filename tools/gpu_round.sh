@@ -28,6 +28,13 @@ for f in sorted(glob.glob('$out/bench_*.json')):
     except Exception as e:
         print(os.path.basename(f), 'FAILED', e)
 PY
+python tools/gemm_sweep.py > $out/gemm_sweep.log 2>&1
+MC_GEMM_RASTER=0 python tools/gemm_sweep.py sq4096 sq4096_nt sq8192 > $out/gemm_sweep_noraster.log 2>&1
+MC_PDL=0 python tools/gemm_sweep.py c3_fwd1 c3_dw1 c3_fwd2 c3_dx2 c3_dw2 sq4096 > $out/gemm_sweep_nopdl.log 2>&1
+MC_GEMM_SPLIT_FROM_KB=16 MC_GEMM_CLUSTER=2 python tools/gemm_sweep.py c3_fwd1 c3_dw1 c3_fwd2 c3_dx2 c3_dw2 > $out/gemm_sweep_split16_cluster2.log 2>&1
+MC_GEMM_SPLIT_FROM_KB=16 python tools/gemm_sweep.py c3_fwd2 c3_dx2 c3_dw2 > $out/gemm_sweep_split16.log 2>&1
+MC_GEMM_SPLIT_FROM_KB=16 MC_GEMM_CLUSTER=2 python bench.py $quick > $out/bench_mlp_c3_split16_cluster2.json 2> $out/bench_mlp_c3_split16_cluster2.err
+tail -30 $out/gemm_sweep.log
 python bench.py > $out/bench_default.json 2> $out/bench_default.err; echo "default bench rc=$?"
 python bench.py --impl reference --steps 20 --warmup 5 > $out/bench_reference.json 2> $out/bench_reference.err; echo "reference rc=$?"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file $out/launches_mlp_c3.csv \
