@@ -82,6 +82,25 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// ---- kernel-internal scratch memory -------------------------------------------------------
+// One persistent arena per device, handed out LIFO: `ScratchFrame f; float* t = f.floats(n);` and the
+// space returns when `f` goes out of scope.  Every kernel of the library runs on one stream (and a PDL
+// kernel touches global memory only after the previous grid completed), so a later call may reuse the
+// bytes an earlier call's kernels used: no cudaMallocAsync / cudaFreeAsync pair per call, which inside a
+// captured step graph were two memory nodes each.  If the arena is too small a larger one is allocated;
+// old arenas stay alive (captured graphs and pointers handed out earlier in the same call refer to them).
+void* scratch_push(size_t bytes);          // nullptr (and the error string set) when out of memory
+size_t scratch_mark();
+void scratch_release(size_t mark);
+struct ScratchFrame {
+  size_t mark;
+  ScratchFrame() : mark(scratch_mark()) {}
+  ~ScratchFrame() { scratch_release(mark); }
+  ScratchFrame(const ScratchFrame&) = delete;
+  ScratchFrame& operator=(const ScratchFrame&) = delete;
+  float* floats(size_t n) { return static_cast<float*>(scratch_push(sizeof(float) * (n ? n : 1))); }
+};
+
 // Grid sizing for bandwidth-bound grid-stride kernels: enough CTAs to fill every SM
 // `waves` times over, never more than the work needs.
 inline int grid_for(int64_t work_items, int per_block, int ctas_per_sm = 8) {

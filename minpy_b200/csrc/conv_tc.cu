@@ -1009,8 +1009,9 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   else { p.g.TH = KH; p.g.TW = KW; p.g.dh0 = -pad; p.g.dw0 = -pad; K = Kreal; Wdim = Wt; }
   const int taps = p.g.TH * p.g.TW;
   const int Kp = (K + 3) / 4 * 4;
-  float* wp = nullptr;
-  MC_CHECK(cudaMallocAsync((void**)&wp, sizeof(float) * (size_t)taps * Nout * Kp, stream()));
+  ScratchFrame scratch;
+  float* wp = scratch.floats((size_t)taps * Nout * Kp);
+  if (!wp) return 1;
   mc::launch(conv_pack_weights_kernel, grid_for((int64_t)taps * Nout * Kp, 256), 256, 0, w, wp, F, C, KH, KW, Cp, taps, Nout,
                                                                                           Kp, mode);
   MC_LAUNCHED();
@@ -1082,7 +1083,6 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
     if (e != cudaSuccess) { set_error("conv_igemm_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();
   }
-  cudaFreeAsync(wp, stream());
   return rc;
 }
 
@@ -1130,9 +1130,10 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
       if (splits < 1) splits = 1;
       h.tiles_per_split = (h.total_tiles + splits - 1) / splits;
       splits = (h.total_tiles + h.tiles_per_split - 1) / h.tiles_per_split;
-      float* ws = nullptr;
       const size_t ws_elems = (size_t)splits * taps * F * p.Nn;
-      MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * (ws_elems + (dbias ? (size_t)splits * F : 0)), stream()));
+      ScratchFrame scratch;
+      float* ws = scratch.floats(ws_elems + (dbias ? (size_t)splits * F : 0));
+      if (!ws) return 1;
       h.ws = ws;
       h.ws_bias = dbias ? ws + ws_elems : nullptr;
       CUtensorMap tmDy, tmX;
@@ -1183,7 +1184,6 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
         if (e != cudaSuccess) { set_error("conv_wgrad_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
         else count_launch();
       }
-      cudaFreeAsync(ws, stream());
       return rc;
     }
   }
@@ -1211,9 +1211,10 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
   p.stages = stages;
   const size_t smem = stages * stage_bytes + (2 * stages + 1) * 8 + 16 + 1024;
 
-  float* ws = nullptr;
   const size_t ws_elems = (size_t)splits * taps * F * p.Nn;
-  MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * (ws_elems + (dbias ? (size_t)splits * F : 0)), stream()));
+  ScratchFrame scratch;
+  float* ws = scratch.floats(ws_elems + (dbias ? (size_t)splits * F : 0));
+  if (!ws) return 1;
   p.ws = ws;
   p.ws_bias = dbias ? ws + ws_elems : nullptr;
   CUtensorMap tmDy, tmX;
@@ -1237,7 +1238,6 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
     if (e != cudaSuccess) { set_error("conv_wgrad_reduce_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();
   }
-  cudaFreeAsync(ws, stream());
   return rc;
 }
 
@@ -1339,11 +1339,11 @@ int mc_conv2d_nhwc_wgrad(const float* x, const float* dy, float* dw, float* dbia
   if (dbias) {
     // column sums of dy viewed as (pixels, Fp); only the first F entries are real channels
     if (Fp == F) return reduce_sum_internal(dy, dbias, 1, N * OH * OW, F);
-    float* tmp = nullptr;
-    MC_CHECK(cudaMallocAsync((void**)&tmp, sizeof(float) * Fp, stream()));
+    ScratchFrame scratch;
+    float* tmp = scratch.floats(Fp);
+    if (!tmp) return 1;
     int rc = reduce_sum_internal(dy, tmp, 1, N * OH * OW, Fp);
     if (rc == 0) rc = mc_memcpy_d2d(dbias, tmp, sizeof(float) * F);
-    cudaFreeAsync(tmp, stream());
     return rc;
   }
   return 0;

@@ -643,8 +643,9 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
     return 0;
   }
   const BnTiling t = bn_tiling(aligned16(x) && aligned16(out) && aligned16(gamma) && aligned16(beta), N, D);
-  float* part = nullptr;
-  MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * t.chunks * 2 * D, stream()));
+  ScratchFrame scratch;
+  float* part = scratch.floats((size_t)(t.chunks * 2 * D));
+  if (!part) return 1;
   dim3 grid((unsigned)t.col_tiles, (unsigned)t.chunks);
   if (t.vec == 4) {
     mc::launch(bn_partial_kernel<4, false>, grid, L_THREADS, 0, x, nullptr, nullptr, nullptr, part, N, D, t.rows_per_chunk);
@@ -660,7 +661,6 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
                                                             N, D, t.rows_per_chunk, eps, momentum);
   }
   MC_LAUNCHED();
-  MC_CHECK(cudaFreeAsync(part, stream()));
   return 0;
 }
 
@@ -713,8 +713,9 @@ int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma, 
     return 0;
   }
   const BnTiling t = bn_tiling(aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(gamma), N, D);
-  float* part = nullptr;
-  MC_CHECK(cudaMallocAsync((void**)&part, sizeof(float) * t.chunks * 2 * D, stream()));
+  ScratchFrame scratch;
+  float* part = scratch.floats((size_t)(t.chunks * 2 * D));
+  if (!part) return 1;
   dim3 grid((unsigned)t.col_tiles, (unsigned)t.chunks);
   if (t.vec == 4) {
     mc::launch(bn_partial_kernel<4, true>, grid, L_THREADS, 0, x, dy, save_mean, save_invstd, part, N, D, t.rows_per_chunk);
@@ -728,7 +729,6 @@ int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma, 
                                                             dgamma, dbeta, N, D, t.rows_per_chunk);
   }
   MC_LAUNCHED();
-  MC_CHECK(cudaFreeAsync(part, stream()));
   return 0;
 }
 

@@ -168,7 +168,8 @@ int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* 
   const int64_t sH = N * H, sA = N * 4 * H;
   float* ws = nullptr;
   const bool try_partials = (precision == MC_GEMM_TF32);
-  if (try_partials) MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * LS_MAX_SPLITS * sA, stream()));
+  ScratchFrame scratch;
+  if (try_partials) { ws = scratch.floats((size_t)(LS_MAX_SPLITS * sA)); if (!ws) return 1; }
   int rc = 0;
   const bool vec = ls_vec_ok(H, {A, ws, hbuf, cbuf, gates});
   for (int64_t t = 0; t < T && rc == 0; ++t) {
@@ -190,7 +191,6 @@ int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* 
     if (e != cudaSuccess) { set_error("lstm_fwd_part_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; break; }
     count_launch();
   }
-  if (ws) MC_CHECK(cudaFreeAsync(ws, stream()));
   return rc;
 }
 
@@ -200,8 +200,10 @@ int mc_lstm_seq_bwd(const float* gates, const float* cbuf, const float* Wh, floa
   const int64_t sH = N * H, sA = N * 4 * H;
   float *ws = nullptr, *dc = nullptr;
   const bool try_partials = (precision == MC_GEMM_TF32);
-  if (try_partials) MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * LS_MAX_SPLITS * sH, stream()));
-  MC_CHECK(cudaMallocAsync((void**)&dc, sizeof(float) * 2 * sH, stream()));
+  ScratchFrame scratch;
+  if (try_partials) { ws = scratch.floats((size_t)(LS_MAX_SPLITS * sH)); if (!ws) return 1; }
+  dc = scratch.floats((size_t)(2 * sH));
+  if (!dc) return 1;
   int rc = 0, pending = 0;
   const bool vec = ls_vec_ok(H, {gates, cbuf, dH, dA, ws, dc});
   for (int64_t t = T - 1; t >= 0 && rc == 0; --t) {
@@ -226,8 +228,6 @@ int mc_lstm_seq_bwd(const float* gates, const float* cbuf, const float* Wh, floa
     }
     if (pending == 0) rc = mc_gemm(0, 1, N, H, 4 * H, dA + t * sA, 4 * H, Wh, 4 * H, dH + t * sH, H, nullptr, 0, 1, precision);
   }
-  if (ws) MC_CHECK(cudaFreeAsync(ws, stream()));
-  MC_CHECK(cudaFreeAsync(dc, stream()));
   return rc;
 }
 

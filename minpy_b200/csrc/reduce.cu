@@ -204,13 +204,12 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
       MC_LAUNCHED();
       return 0;
     }
-    float* ws = nullptr;
-    MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * outer * splits, stream()));
+    ScratchFrame scratch;
+    float* ws = scratch.floats((size_t)(outer * splits));
+    if (!ws) return 1;
     mc::launch(reduce_rows_block_kernel<Op>, (unsigned)(outer * splits), RED_THREADS, 0, x, ws, red, splits, seg);
     MC_LAUNCHED();
-    int rc = reduce_impl<Op>(ws, out, outer, splits, 1);
-    MC_CHECK(cudaFreeAsync(ws, stream()));
-    return rc;
+    return reduce_impl<Op>(ws, out, outer, splits, 1);
   }
   // ---- column reduction ----
   if ((inner % 8) == 0 && aligned16(x) && red >= 128 && red * inner <= (1 << 20) && outer <= 65535) {
@@ -236,17 +235,17 @@ static int reduce_impl(const float* x, float* out, int64_t outer, int64_t red, i
   dim3 grid((unsigned)col_tiles, (unsigned)splits, (unsigned)outer);
   float* dst = out;
   float* ws = nullptr;
+  ScratchFrame scratch;
   if (splits > 1) {
-    MC_CHECK(cudaMallocAsync((void**)&ws, sizeof(float) * outer * splits * inner, stream()));
+    ws = scratch.floats((size_t)(outer * splits * inner));
+    if (!ws) return 1;
     dst = ws;
   }
   if (vec) mc::launch(reduce_cols_kernel<Op, 4>, grid, RED_THREADS, 0, x, dst, red, inner, seg);
   else mc::launch(reduce_cols_kernel<Op, 1>, grid, RED_THREADS, 0, x, dst, red, inner, seg);
   MC_LAUNCHED();
   if (splits > 1) {
-    int rc = reduce_impl<Op>(ws, out, outer, splits, inner);
-    MC_CHECK(cudaFreeAsync(ws, stream()));
-    return rc;
+    return reduce_impl<Op>(ws, out, outer, splits, inner);
   }
   return 0;
 }

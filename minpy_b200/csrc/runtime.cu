@@ -44,6 +44,30 @@ bool first_use_on_device(uint32_t* mask) {
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 const unsigned long long* graph_epoch() { return g_capturing ? g_epoch : nullptr; }
 
+struct Arena { char* base; size_t cap, top; };
+static Arena g_arena[MC_MAX_DEVICES] = {};
+size_t scratch_mark() { return g_arena[g_device < 0 ? 0 : g_device].top; }
+void scratch_release(size_t mark) { g_arena[g_device < 0 ? 0 : g_device].top = mark; }
+void* scratch_push(size_t bytes) {
+  Arena& a = g_arena[g_device < 0 ? 0 : g_device];
+  bytes = (bytes + 255) & ~(size_t)255;
+  if (a.top + bytes > a.cap) {
+    size_t want = a.cap ? a.cap * 2 : ((size_t)64 << 20);
+    while (want < a.top + bytes) want *= 2;
+    char* fresh = nullptr;
+    if (cudaMalloc((void**)&fresh, want) != cudaSuccess) {
+      cudaGetLastError();
+      set_error("scratch arena: cudaMalloc of %zu bytes failed", want);
+      return nullptr;
+    }
+    a.base = fresh;              // the previous arena is kept alive on purpose (see common.cuh)
+    a.cap = want;
+  }
+  void* p = a.base + a.top;
+  a.top += bytes;
+  return p;
+}
+
 static int configure_device(int device) {
   MC_CHECK(cudaSetDevice(device));
   cudaDeviceProp prop;

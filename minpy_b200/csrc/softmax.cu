@@ -296,8 +296,9 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels, const float* onehot
                       int64_t rows, int64_t cols) {
   MC_REQUIRE((labels != nullptr) != (onehot != nullptr), "exactly one of labels / onehot");
   MC_REQUIRE(rows > 0 && cols > 0, "empty input");
-  float* rowloss = nullptr;
-  MC_CHECK(cudaMallocAsync((void**)&rowloss, sizeof(float) * rows, stream()));
+  ScratchFrame scratch;
+  float* rowloss = scratch.floats((size_t)rows);
+  if (!rowloss) return 1;
   int rc = launch_softmax<MODE_CE>(x, probs, labels, onehot, rowloss, rows, cols);
   if (rc == 0) rc = reduce_sum_internal(rowloss, loss, 1, rows, 1);
   if (rc == 0) {
@@ -306,7 +307,6 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels, const float* onehot
     if (e != cudaSuccess) { mc::set_error("scale launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else mc::count_launch();
   }
-  MC_CHECK(cudaFreeAsync(rowloss, stream()));
   return rc;
 }
 
