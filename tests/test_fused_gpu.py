@@ -1,0 +1,297 @@
+"""Round-2 fused entry points through the C ABI, against (a) the un-fused kernels they replace on the same
+device inputs -- bit-exact where the arithmetic is the same -- and (b) the float64 oracle:
+
+  mc_gemm(relu = 2)            signed-zero relu epilogue              nn/layers.py:27,41; numpy_core.py:284-286
+  mc_bn_dropout_fwd            batchnorm + dropout mask at the store  nn/layers.py:93-110,141-144
+  mc_bn_dropout_relu_bwd       dropout / batchnorm / relu VJPs + bias gradient
+  mc_softmax_ce_fused          softmax_loss and its gradient          nn/layers.py:201-221; numpy_core.py:170-175
+  mc_avgpool2d_fwd / _bwd      MXNet Pooling(pool_type='avg')
+and, through the front end, the lazy forward fusion (`MINPY_FUSE_FORWARD`) of the hidden block of
+examples/nn/mlp_bn_dropout.py:41-54: same losses, gradients and running statistics as the un-fused path,
+with fewer launches.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+from oracle import minpy_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    return float(np.max(np.abs(a - b)) / max(1e-30, np.max(np.abs(b)))) if a.size else 0.0
+
+
+def up(a):
+    from minpy_b200.cuda_array import CudaArray
+    return CudaArray.from_numpy(a)
+
+
+def empty(shape):
+    from minpy_b200.cuda_array import CudaArray
+    return CudaArray.empty(shape)
+
+
+def launches(lib):
+    n = ctypes.c_uint64()
+    lib.mc_launch_count(ctypes.byref(n))
+    return n.value
+
+
+@pytest.mark.parametrize('shape', [(64, 96, 32), (256, 512, 128), (1024, 512, 512), (100, 10, 64), (40, 24, 1000)])
+@pytest.mark.parametrize('precision', [0, 1])
+def test_gemm_signed_zero_relu(cuda, shape, precision):
+    """relu mode 2: the values of mode 1 exactly; the sign bit of every output equals (pre-activation < 0)."""
+    M, N, K = shape
+    lib = cuda.L()
+    rng = np.random.RandomState(M + N)
+    a = rng.randn(M, K).astype(np.float32)
+    b = rng.randn(K, N).astype(np.float32)
+    bias = rng.randn(N).astype(np.float32)
+    a[3, :] = 0.0                      # a row whose pre-activation is exactly the bias
+    bias[1] = 0.0                      # ... and exactly zero in column 1: gradient must pass (x >= 0)
+    A, B, bv = up(a), up(b), up(bias)
+    outs = []
+    for mode in (0, 1, 2):
+        C = empty((M, N))
+        lib.mc_gemm(0, 0, M, N, K, A.ptr, K, B.ptr, N, C.ptr, N, bv.ptr, mode, 0, precision)
+        outs.append(C.asnumpy())
+    pre, r1, r2 = outs
+    assert np.array_equal(r1, np.maximum(pre, 0))
+    assert np.array_equal(r2, r1)                                   # -0.0 == 0.0
+    assert np.array_equal(np.signbit(r2), pre < 0)
+    assert pre[3, 1] == 0.0 and not np.signbit(r2[3, 1])
+    # the VJP factor reads the sign bit
+    g = up(rng.randn(M, N).astype(np.float32))
+    got = cuda.run_chain(g, 1.0, [(lib.MC_VJP_SIGNPOS_A, up(r2), 0, None, 0, 0.0, 1)], (M, N)).asnumpy()
+    assert np.array_equal(got, g.asnumpy() * (pre >= 0))
+
+
+@pytest.mark.parametrize('N,D', [(1024, 512), (256, 64), (37, 8), (1000, 1000)])
+def test_bn_dropout_fwd_equals_the_two_kernels(cuda, N, D):
+    lib = cuda.L()
+    rng = np.random.RandomState(N)
+    x = (rng.randn(N, D) * 2 + 1).astype(np.float32)
+    gamma, beta = rng.rand(D).astype(np.float32) + 0.5, rng.randn(D).astype(np.float32)
+    rm, rv = rng.randn(D).astype(np.float32), rng.rand(D).astype(np.float32)
+    X, G, Bt, RM, RV = up(x), up(gamma), up(beta), up(rm), up(rv)
+    p, seed, offset = 0.4, 1234567, 4096
+    out1, nrm1, nrv1, sm1, si1 = empty((N, D)), empty((D,)), empty((D,)), empty((D,)), empty((D,))
+    lib.mc_batchnorm_train_fwd(X.ptr, G.ptr, Bt.ptr, RM.ptr, RV.ptr, out1.ptr, nrm1.ptr, nrv1.ptr, sm1.ptr, si1.ptr, N, D, 1e-5, 0.9)
+    y1 = empty((N, D))
+    lib.mc_dropout(out1.ptr, y1.ptr, N * D, p, seed, offset)
+    y2, nrm2, nrv2, sm2, si2 = empty((N, D)), empty((D,)), empty((D,)), empty((D,)), empty((D,))
+    n0 = launches(lib)
+    lib.mc_bn_dropout_fwd(X.ptr, G.ptr, Bt.ptr, RM.ptr, RV.ptr, y2.ptr, nrm2.ptr, nrv2.ptr, sm2.ptr, si2.ptr, N, D, 1e-5, 0.9,
+                          p, seed, offset)
+    assert launches(lib) - n0 == 1
+    for a, b in ((y1, y2), (nrm1, nrm2), (nrv1, nrv2), (sm1, sm2), (si1, si2)):
+        assert np.array_equal(a.asnumpy(), b.asnumpy())
+    keep = y2.asnumpy() != 0
+    assert abs(keep.mean() - (1 - p)) < 0.02
+    # oracle: batchnorm (layers.py:93-110) times the device's own mask
+    ones = empty((N, D))
+    lib.mc_dropout(cuda.full((N, D), 1.0).ptr, ones.ptr, N * D, p, seed, offset)
+    mask = ones.asnumpy() > 0.5
+    want, _, _ = orc.batchnorm(x.astype(np.float64), gamma.astype(np.float64), beta.astype(np.float64),
+                               running_mean=rm.astype(np.float64), running_var=rv.astype(np.float64))
+    assert rel(y2.asnumpy(), orc.raw(want) * mask) <= 2e-5
+
+
+@pytest.mark.parametrize('N,D', [(1024, 512), (256, 64), (37, 8)])
+@pytest.mark.parametrize('dropout,relu', [(1, 1), (1, 0), (0, 1), (0, 0)])
+def test_bn_dropout_relu_bwd_equals_the_separate_kernels(cuda, N, D, dropout, relu):
+    lib = cuda.L()
+    rng = np.random.RandomState(N + 2 * dropout + relu)
+    pre = rng.randn(N, D).astype(np.float32)
+    pre[5, :4] = 0.0                                   # zero pre-activations pass the gradient
+    # x = signed-zero relu output of the layer before (what mc_gemm relu = 2 stores)
+    x = np.where(pre < 0, np.float32(-0.0), pre).astype(np.float32) if relu else (pre * 2 + 1).astype(np.float32)
+    dy = rng.randn(N, D).astype(np.float32)
+    gamma = rng.rand(D).astype(np.float32) + 0.5
+    X, DY, G = up(x), up(dy), up(gamma)
+    out, nrm, nrv, sm, si = empty((N, D)), empty((D,)), empty((D,)), empty((D,)), empty((D,))
+    zeros, ones = cuda.zeros((D,)), cuda.ones((D,))
+    lib.mc_batchnorm_train_fwd(X.ptr, G.ptr, zeros.ptr, zeros.ptr, ones.ptr, out.ptr, nrm.ptr, nrv.ptr, sm.ptr, si.ptr, N, D, 1e-5, 0.9)
+    p, seed, offset = 0.5, 99, 1 << 20
+    # the separate kernels
+    g1 = DY
+    if dropout:
+        g1 = empty((N, D))
+        lib.mc_dropout(DY.ptr, g1.ptr, N * D, p, seed, offset)
+    dx1, dgam1, dbet1 = empty((N, D)), empty((D,)), empty((D,))
+    lib.mc_batchnorm_train_bwd(X.ptr, g1.ptr, G.ptr, sm.ptr, si.ptr, dx1.ptr, dgam1.ptr, dbet1.ptr, N, D)
+    dx1 = dx1.asnumpy()
+    if relu:
+        dx1 = dx1 * (pre >= 0)
+    # the fused kernel
+    dx2, dgam2, dbet2, dbias = empty((N, D)), empty((D,)), empty((D,)), empty((D,))
+    n0 = launches(lib)
+    lib.mc_bn_dropout_relu_bwd(X.ptr, DY.ptr, G.ptr, sm.ptr, si.ptr, dx2.ptr, dgam2.ptr, dbet2.ptr, dbias.ptr if relu else None,
+                               N, D, dropout, p, seed, offset, relu)
+    assert launches(lib) - n0 == 1
+    assert np.array_equal(dx2.asnumpy(), dx1.astype(np.float32))
+    assert np.array_equal(dgam2.asnumpy(), dgam1.asnumpy()) and np.array_equal(dbet2.asnumpy(), dbet1.asnumpy())
+    if relu:
+        assert rel(dbias.asnumpy(), dx1.astype(np.float64).sum(axis=0)) <= 2e-5
+        assert np.all(dx2.asnumpy()[5, :4] == dx1[5, :4])
+
+
+def test_bn_fused_shape_gate(cuda):
+    lib = cuda.L()
+    ok = ctypes.c_int()
+    for N, D, want in ((1024, 512, 1), (1025, 512, 0), (64, 12, 0), (2048, 512, 0), (1024, 1024, 1), (1024, 1032, 0)):
+        lib.mc_bn_fused_supported(N, D, ctypes.byref(ok))
+        assert ok.value == want, (N, D)
+    X = up(np.zeros((2048, 8), np.float32))
+    with pytest.raises(Exception):
+        lib.mc_bn_dropout_fwd(X.ptr, X.ptr, X.ptr, X.ptr, X.ptr, X.ptr, X.ptr, X.ptr, X.ptr, X.ptr, 2048, 8, 1e-5, 0.9, 0.5, 1, 0)
+
+
+@pytest.mark.parametrize('rows,cols', [(1024, 10), (256, 10), (7, 3), (513, 32), (300, 100), (20000, 10)])
+def test_softmax_ce_fused_equals_fwd_plus_bwd(cuda, rows, cols):
+    lib = cuda.L()
+    rng = np.random.RandomState(rows)
+    x = (rng.randn(rows, cols) * 3).astype(np.float32)
+    lab = rng.randint(0, cols, rows).astype(np.int32)
+    X, L = up(x), up(lab)
+    probs1, loss1, dx1 = empty((rows, cols)), empty(()), empty((rows, cols))
+    lib.mc_softmax_ce_fwd(X.ptr, L.ptr, None, probs1.ptr, loss1.ptr, rows, cols)
+    lib.mc_softmax_ce_bwd(probs1.ptr, L.ptr, None, dx1.ptr, rows, cols)
+    probs2, loss2, dx2 = empty((rows, cols)), empty(()), empty((rows, cols))
+    n0 = launches(lib)
+    lib.mc_softmax_ce_fused(X.ptr, L.ptr, None, probs2.ptr, dx2.ptr, loss2.ptr, rows, cols)
+    if cols <= 32 and rows <= 16384:
+        assert launches(lib) - n0 == 1
+    assert rel(probs2.asnumpy(), probs1.asnumpy()) <= 5e-6 and rel(dx2.asnumpy(), dx1.asnumpy()) <= 5e-6
+    assert abs(float(loss2.asnumpy()) - float(loss1.asnumpy())) <= 1e-6 * abs(float(loss1.asnumpy()))
+    # oracle
+    want = orc.softmax_loss(x.astype(np.float64), lab)
+    assert abs(float(loss2.asnumpy()) - float(orc.raw(want))) <= 1e-5 * abs(float(orc.raw(want)))
+    e = np.exp(x.astype(np.float64) - x.max(axis=1, keepdims=True))
+    pr = e / e.sum(axis=1, keepdims=True)
+    pr[np.arange(rows), lab] -= 1
+    assert rel(dx2.asnumpy(), pr / rows) <= 1e-5
+    # dx only (what the front end asks for) and one-hot labels
+    dx3, loss3 = empty((rows, cols)), empty(())
+    lib.mc_softmax_ce_fused(X.ptr, L.ptr, None, None, dx3.ptr, loss3.ptr, rows, cols)
+    assert np.array_equal(dx3.asnumpy(), dx2.asnumpy())
+    hot = np.zeros((rows, cols), np.float32)
+    hot[np.arange(rows), lab] = 1
+    dx4, loss4 = empty((rows, cols)), empty(())
+    lib.mc_softmax_ce_fused(X.ptr, None, up(hot).ptr, None, dx4.ptr, loss4.ptr, rows, cols)
+    assert rel(dx4.asnumpy(), dx1.asnumpy()) <= 5e-6
+
+
+@pytest.mark.parametrize('shape,k,stride', [((4, 6, 8, 8), 8, 1), ((2, 3, 9, 7), 2, 2), ((3, 5, 10, 10), 3, 1), ((2, 4, 7, 7), 3, 2)])
+def test_avgpool_matches_torch_float64(cuda, shape, k, stride):
+    import torch
+    rng = np.random.RandomState(k)
+    x = rng.randn(*shape).astype(np.float32)
+    y = cuda.avgpool2d_fwd(up(x), k, stride)
+    t = torch.tensor(x.astype(np.float64), requires_grad=True)
+    ty = torch.nn.functional.avg_pool2d(t, k, stride)
+    assert rel(y.asnumpy(), ty.detach().numpy()) <= 1e-6
+    g = rng.randn(*y.shape).astype(np.float32)
+    ty.backward(torch.tensor(g.astype(np.float64)))
+    dx = cuda.avgpool2d_bwd(up(g), shape, k, stride)
+    assert rel(dx.asnumpy(), t.grad.numpy()) <= 1e-6
+
+
+def _block_step(fuse, graph, drop=0.5):
+    """Three steps of a 2-hidden-layer affine-relu-batchnorm-dropout net (mlp_bn_dropout.py:41-54 block)."""
+    import importlib
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    from minpy.array_variants.cuda import cuda_core
+    import minpy.numpy.random as mrandom
+    from minpy import array as marray
+    from minpy.nn.io import DataBatch
+    from minpy.nn.solver import Solver
+    from minpy_b200 import workloads
+    from minpy_b200.cuda_array import CudaArray
+    from minpy_b200._lib import get_lib
+    saved = cuda_core._FUSE_FORWARD  # pylint: disable=protected-access
+    cuda_core._FUSE_FORWARD = fuse  # pylint: disable=protected-access
+    try:
+        mrandom.seed(21)
+        rng = np.random.RandomState(4)
+        model = workloads.DeepMLP(in_dim=96, hidden=(64, 64), classes=10, drop=drop)
+        solver = Solver(model, None, None, update_rule='sgd_momentum', optim_config={'learning_rate': 0.05, 'momentum': 0.9},
+                        init_rule='gaussian', init_config={'stdvar': 0.1}, verbose=False, step_graph=graph)
+        solver.init()
+        for k, v in workloads.init_params(model, 3, scale=0.1).items():
+            model.params[k] = marray.wrap(CudaArray.from_numpy(v))
+        lib = get_lib()
+        counts = []
+        for i in range(4):
+            X = rng.randn(128, 96).astype(np.float32)
+            Y = rng.randint(0, 10, 128)
+            n0 = launches(lib)
+            solver._step(DataBatch([marray.wrap(CudaArray.from_numpy(X))], [marray.wrap(CudaArray.from_numpy(Y))], pad=0, index=i))  # pylint: disable=protected-access
+            counts.append(launches(lib) - n0)
+        params = dict((k, v.asnumpy()) for k, v in model.params.items())
+        aux = dict((k, v.asnumpy()) for k, v in model.aux_params.items())
+        losses = [float(l) for l in solver.loss_history]
+        return params, aux, losses, counts
+    finally:
+        cuda_core._FUSE_FORWARD = saved  # pylint: disable=protected-access
+        minpy.set_global_policy('prefer_cuda')
+
+
+def test_forward_fusion_equals_the_unfused_step_with_fewer_launches():
+    fused = _block_step(True, False)
+    plain = _block_step(False, False)
+    for a, b in zip(fused[:2], plain[:2]):
+        for k in a:
+            assert rel(a[k], b[k]) <= 1e-5, k
+    assert np.allclose(fused[2], plain[2], rtol=1e-5)
+    # eager launches per step: 2 hidden blocks save >= 2 forward and >= 3 backward launches each, the loss 3
+    assert fused[3][-1] <= plain[3][-1] - 8, (fused[3], plain[3])
+
+
+def test_forward_fusion_inside_the_step_graph():
+    """The lazily evaluated values live and die inside the capture; replays equal eager stepping.  (p = 0:
+    a replay draws its masks from a shifted Philox offset, so only a keep-everything dropout is comparable.)"""
+    eager = _block_step(True, False, drop=0.0)
+    graph = _block_step(True, True, drop=0.0)
+    for a, b in zip(eager[:2], graph[:2]):
+        for k in a:
+            assert rel(a[k], b[k]) <= 1e-5, k
+    assert np.allclose(eager[2], graph[2], rtol=1e-5)
+
+
+def test_lazy_values_evaluate_on_demand():
+    """A pending affine / batchnorm result that is NOT followed by relu / dropout evaluates when touched."""
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    try:
+        import minpy.numpy as mnp
+        from minpy.nn import layers
+        from minpy.array_variants import ArrayType
+        from minpy_b200.lazy import LazyArray
+        rng = np.random.RandomState(0)
+        x, w, b = rng.randn(32, 16), rng.randn(16, 8), rng.randn(8)
+        a = layers.affine(mnp.array(x), mnp.array(w), mnp.array(b))
+        raw = a.get_data(ArrayType.CUDA)
+        assert isinstance(raw, LazyArray) and raw.pending() and a.shape == (32, 8)
+        h = layers.relu(a)
+        assert raw.pending()                                  # the relu ran the GEMM itself
+        assert rel(h.asnumpy(), np.maximum(x.dot(w) + b, 0)) <= 1e-2
+        assert rel(a.asnumpy(), x.dot(w) + b) <= 1e-2 and not raw.pending()      # ... and the pre-activation on demand
+        out, rm, rv = layers.batchnorm(h, mnp.ones((8,)), mnp.zeros((8,)))
+        assert out.get_data(ArrayType.CUDA).pending()
+        y = layers.dropout(out, 0.5)
+        assert out.get_data(ArrayType.CUDA).pending() and not rm.get_data(ArrayType.CUDA).pending()
+        hn = np.maximum(x.dot(w) + b, 0)
+        bn = (hn - hn.mean(0)) / np.sqrt(hn.var(0) + 1e-5)
+        yv = y.asnumpy()
+        assert rel(yv[yv != 0], bn[yv != 0]) <= 2e-2
+        assert rel(out.asnumpy(), bn) <= 2e-2                 # the un-dropped batchnorm output, on demand
+        assert rel(rm.asnumpy(), 0.1 * hn.mean(0)) <= 2e-2
+    finally:
+        minpy.set_global_policy('prefer_cuda')
