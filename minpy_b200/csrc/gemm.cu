@@ -438,6 +438,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   const int num_kb = kb_end - kb_begin;
 
   if (warp == 0 && lane == 0) {
+    // descriptor fetch overlaps the previous kernel's tail (the maps are kernel parameters: legal before pdl_sync)
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
