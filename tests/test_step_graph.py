@@ -267,3 +267,37 @@ def test_graph_training_keeps_best_params_and_fresh_host_views():
         assert np.array_equal(model.params[k].asnumpy(), per_epoch[best_epoch][k]), k
     if best_epoch != 5:
         assert np.max(np.abs(model.params['w1'].asnumpy() - per_epoch[5]['w1'])) > 0
+
+
+def test_what_a_script_observes_under_the_step_graph():
+    """what reference-style script code sees when `step_graph=True`.
+    (a) `solver.loss_history[-1]` read right after a step is THAT step's loss, as solver.py:187 gives it
+        (the entry is a lazy device scalar; float() waits for its own copy only);
+    (b) parameters: the reference REBINDS model.params[k] every step (solver.py:190-195), so an array a
+        script held from before the step keeps the old values.  Eager stepping here does the same.  A
+        replayed step writes the parameter buffers IN PLACE: the held array IS the live
+        parameter and shows the new values.  Documented difference of the opt-in mode; this test pins it."""
+    from minpy_b200 import workloads
+    make = lambda: workloads.MLP(in_dim=96, hidden=64, classes=10)
+    X, Y = _data(4 * 32, seed=11)
+    seen = {False: [], True: []}
+    held = {}
+
+    def hook_for(graph):
+        def hook(solver, i):
+            if i > 0:
+                seen[graph].append(float(solver.loss_history[-1]))        # the step just taken
+            if i == 4:
+                held[graph] = (solver.model.params['w1'], solver.model.params['w1'].asnumpy().copy())
+        return hook
+    eager = _run(make, 'sgd_momentum', {'learning_rate': 0.05, 'momentum': 0.9}, X, Y, 32, 6, False, hook=hook_for(False))
+    graph = _run(make, 'sgd_momentum', {'learning_rate': 0.05, 'momentum': 0.9}, X, Y, 32, 6, True, hook=hook_for(True))
+    assert not graph[4]._step_graph.disabled and graph[4]._step_graph.replays >= 3   # pylint: disable=protected-access
+    assert rel(seen[True], seen[False]) <= 1e-6 and rel(seen[False], eager[3][:-1]) == 0.0
+    _same(graph, eager, 1e-6)
+    obj, before = held[False]
+    assert np.array_equal(obj.asnumpy(), before)                 # eager: the held array kept the old values
+    assert eager[4].model.params['w1'] is not obj
+    obj, before = held[True]
+    assert graph[4].model.params['w1'] is obj                     # graph: the held array is the live parameter
+    assert rel(obj.asnumpy(), graph[0]['w1']) == 0.0 and not np.array_equal(obj.asnumpy(), before)
