@@ -36,6 +36,48 @@ __global__ void __launch_bounds__(IX_THREADS) strided_kernel(const float* __rest
   }
 }
 
+// The same, when the innermost dimension is contiguous on both sides and everything is 16-byte aligned
+// (axis swaps of (N, T, H) sequences, slices along outer axes): one float4 per item, the index
+// arithmetic once per four elements.  n4 = number of float4 items; shape[ndim-1] is in float4 units here.
+template <bool ADD>
+__global__ void __launch_bounds__(IX_THREADS) strided_rows4_kernel(const float4* __restrict__ src, float4* __restrict__ dst,
+                                                                   int64_t n4, const __grid_constant__ StridedDesc d) {
+  mc::pdl_sync();
+  const int64_t stride = (int64_t)gridDim.x * IX_THREADS;
+  for (int64_t i = (int64_t)blockIdx.x * IX_THREADS + threadIdx.x; i < n4; i += stride) {
+    int64_t rem = i, off = d.offset;
+#pragma unroll
+    for (int k = MC_MAX_DIMS - 1; k >= 0; --k) {
+      if (k < d.ndim) {
+        off += (rem % d.shape[k]) * d.strides[k];
+        rem /= d.shape[k];
+      }
+    }
+    if (ADD) {
+      float4 a = dst[off];
+      const float4 b = src[i];
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+      dst[off] = a;
+    } else {
+      dst[i] = src[off];
+    }
+  }
+}
+
+// float4 view of a strided description, or false when it does not apply
+static bool rows4_desc(const StridedDesc& d, const void* dense, const void* strided, StridedDesc* out) {
+  if (d.ndim < 1 || d.strides[d.ndim - 1] != 1 || (d.shape[d.ndim - 1] & 3) || (d.offset & 3)) return false;
+  if (!aligned16(dense) || !aligned16(strided)) return false;
+  *out = d;
+  for (int k = 0; k < d.ndim - 1; ++k) {
+    if (d.strides[k] & 3) return false;
+    out->strides[k] = d.strides[k] >> 2;
+  }
+  out->shape[d.ndim - 1] = d.shape[d.ndim - 1] >> 2;
+  out->offset = d.offset >> 2;
+  return true;
+}
+
 // 2-D tiled transpose through shared memory: both the read and the write are coalesced.
 // src is (rows, cols) with row pitch `ld`, dst is (cols, rows) dense; batched over z.
 __global__ void __launch_bounds__(256) transpose_tile_kernel(const float* __restrict__ src, float* __restrict__ dst,
@@ -168,6 +210,13 @@ int mc_strided_copy(const float* src, float* dst, int ndim, const int64_t* shape
       return 0;
     }
   }
+  StridedDesc d4;
+  if (rows4_desc(d, dst, src, &d4)) {
+    mc::launch(strided_rows4_kernel<false>, grid_for(n / 4, IX_THREADS), IX_THREADS, 0, reinterpret_cast<const float4*>(src),
+               reinterpret_cast<float4*>(dst), n / 4, d4);
+    MC_LAUNCHED();
+    return 0;
+  }
   mc::launch(strided_kernel<false>, grid_for(n, IX_THREADS), IX_THREADS, 0, src, dst, n, d);
   MC_LAUNCHED();
   return 0;
@@ -179,6 +228,13 @@ int mc_strided_add(float* dst, const float* src, int ndim, const int64_t* shape,
   int64_t n;
   MC_REQUIRE(fill_desc(d, ndim, shape, dst_strides, dst_offset, &n) == 0, "ndim must be in 0..6");
   if (n <= 0) return 0;
+  StridedDesc d4;
+  if (rows4_desc(d, src, dst, &d4)) {
+    mc::launch(strided_rows4_kernel<true>, grid_for(n / 4, IX_THREADS), IX_THREADS, 0, reinterpret_cast<const float4*>(src),
+               reinterpret_cast<float4*>(dst), n / 4, d4);
+    MC_LAUNCHED();
+    return 0;
+  }
   mc::launch(strided_kernel<true>, grid_for(n, IX_THREADS), IX_THREADS, 0, src, dst, n, d);
   MC_LAUNCHED();
   return 0;
