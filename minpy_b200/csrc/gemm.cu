@@ -719,6 +719,196 @@ int make_tmap_2d(CUtensorMap* map, const float* ptr, int64_t inner, int64_t oute
   return make_tmap(map, ptr, 2, dims, strides, box, mn_major);
 }
 
+// ---- persistent variant (grids beyond one wave) ----------------------------------------------
+// One CTA per SM walks the rastered tile list.  Six warps: 0-3 drain accumulators (warp q owns TMEM lanes
+// 32q..32q+31), warp 4 is the TMA producer, warp 5 issues the MMAs.  TWO accumulators in TMEM (2 x BN
+// columns): the MMA warp fills accumulator i+1 while the epilogue warps drain accumulator i, and the operand
+// ring never stops at a tile boundary -- the non-persistent kernel above pays TMEM allocation, barrier
+// set-up, a pipeline fill and an un-overlapped epilogue per 128 x BN tile (profiles/r1z/prof_gemm_4096.txt:
+// 54.7 % tensor-pipe active at 4096^3).
+constexpr int PTHREADS = 192;
+
+__device__ __forceinline__ void tile_of(const GemmParams& p, int lin, int tiles_m, int tiles_n, int& tile_m, int& tile_n) {
+  if (p.group_m > 0) {
+    const int per_group = p.group_m * tiles_n;
+    const int first_m = (lin / per_group) * p.group_m;
+    const int gsize = min(tiles_m - first_m, p.group_m);
+    const int r = lin % per_group;
+    tile_m = first_m + r % gsize;
+    tile_n = r / gsize;
+  } else {
+    tile_m = lin / tiles_n;
+    tile_n = lin % tiles_n;
+  }
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                           const __grid_constant__ CUtensorMap tmB,
+                                                                           const GemmParams p) {
+  constexpr uint32_t A_BYTES = BM * BK * 4;
+  constexpr uint32_t B_BYTES = BN * BK * 4;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;   // full[S], empty[S], tfull[2], tempty[2]
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_m = (p.M + BM - 1) / BM, tiles_n = (p.N + BN - 1) / BN;
+  const int total = tiles_m * tiles_n;
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 4 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 5) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)(2 * BN))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  mc::pdl_sync();      // prologue done (on-chip state only); global memory from here on
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 4) {
+    if (elect_one()) {
+      // ------------------------------ TMA producer ------------------------------------
+      const bool a_mn = p.a_mn != 0, b_mn = p.b_mn != 0;
+      int s = 0;
+      uint32_t ph = 0;
+      for (int lin = blockIdx.x; lin < total; lin += gridDim.x) {
+        int tile_m, tile_n;
+        tile_of(p, lin, tiles_m, tiles_n, tile_m, tile_n);
+        const int m0 = tile_m * BM, n0 = tile_n * BN;
+        int k0 = 0;
+        for (int i = 0; i < num_kb; ++i, k0 += BK) {
+          mbar_wait(empty_bar(s), ph ^ 1u);
+          const uint32_t fb = full_bar(s);
+          mbar_expect_tx(fb, STAGE_BYTES);
+          const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
+          if (!a_mn) {
+            tma_load_2d(sa, &tmA, fb, k0, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, fb, m0 + 32 * j, k0);
+          }
+          if (!b_mn) {
+            tma_load_2d(sb, &tmB, fb, k0, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, fb, n0 + 32 * j, k0);
+          }
+          if (++s == STAGES) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 5) {
+    if (elect_one()) {
+      // ------------------------------ MMA issuer --------------------------------------
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
+                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      const uint64_t adesc0 = p.a_mn ? make_desc(0, 4096, 512, 1) : make_desc(0, 16, 1024, 2);
+      const uint64_t bdesc0 = p.b_mn ? make_desc(0, 4096, 512, 1) : make_desc(0, 16, 1024, 2);
+      const uint32_t astep = p.a_mn ? 64u : 2u, bstep = p.b_mn ? 64u : 2u;
+      int s = 0, acc = 0;
+      uint32_t ph = 0, aph = 0;
+      for (int lin = blockIdx.x; lin < total; lin += gridDim.x) {
+        mbar_wait(tempty_bar(acc), aph ^ 1u);          // the epilogue has drained this accumulator
+        tcgen05_fence_after();
+        const uint32_t dacc = tmem_base + (uint32_t)(acc * BN);
+        for (int i = 0; i < num_kb; ++i) {
+          mbar_wait(full_bar(s), ph);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
+          const uint64_t adesc = adesc0 + (uint64_t)((sa & 0x3FFFFu) >> 4);
+          const uint64_t bdesc = bdesc0 + (uint64_t)((sb & 0x3FFFFu) >> 4);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_tf32(dacc, adesc + (uint64_t)(astep * k), bdesc + (uint64_t)(bstep * k), idesc, (i > 0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar(s));
+          if (++s == STAGES) { s = 0; ph ^= 1u; }
+        }
+        umma_commit(tfull_bar(acc));
+        if (++acc == 2) { acc = 0; aph ^= 1u; }
+      }
+    }
+  } else {
+    // ---------------------------------- epilogue (warps 0-3) ----------------------------
+    const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+    int acc = 0;
+    uint32_t aph = 0;
+    for (int lin = blockIdx.x; lin < total; lin += gridDim.x) {
+      int tile_m, tile_n;
+      tile_of(p, lin, tiles_m, tiles_n, tile_m, tile_n);
+      const int row = tile_m * BM + warp * 32 + lane, n0 = tile_n * BN;
+      mbar_wait_warp(tfull_bar(acc), aph);
+      tcgen05_fence_after();
+      const uint32_t tacc = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        float v[32];
+        tmem_ld32(tacc + (uint32_t)c0, v);
+        const int col0 = n0 + c0;
+        if (row < p.M && col0 < p.N) {
+          float* dst = p.C + (int64_t)row * p.ldc + col0;
+          if (vec_ok && col0 + 32 <= p.N) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              if (p.bias) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+                o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+              }
+              if (p.accumulate) {
+                const float4 c = *reinterpret_cast<const float4*>(dst + j);
+                o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
+              }
+              if (p.relu) {
+                o.x = relu_apply(o.x, p.relu); o.y = relu_apply(o.y, p.relu);
+                o.z = relu_apply(o.z, p.relu); o.w = relu_apply(o.w, p.relu);
+              }
+              *reinterpret_cast<float4*>(dst + j) = o;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (col0 + j < p.N) {
+                float o = v[j];
+                if (p.bias) o += __ldg(p.bias + col0 + j);
+                if (p.accumulate) o += dst[j];
+                if (p.relu) o = relu_apply(o, p.relu);
+                dst[j] = o;
+              }
+            }
+          }
+        }
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty_bar(acc)) : "memory");
+      if (++acc == 2) { acc = 0; aph ^= 1u; }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)(2 * BN)) : "memory");
+  }
+}
+
 template <int BN, int STAGES>
 static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits) {
   constexpr size_t SMEM = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) + (2 * STAGES + 1) * 8 + 16 + 1024;
@@ -780,6 +970,19 @@ static int gemm_fp32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     MC_LAUNCHED();
     MC_CHECK(cudaFreeAsync(ws, stream()));
   }
+  return 0;
+}
+
+template <int BN, int STAGES>
+static int launch_tf32_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const tc::GemmParams& p, int64_t tiles) {
+  using namespace tc;
+  constexpr size_t SMEM = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) + (2 * STAGES + 4) * 8 + 16 + 1024;
+  static uint32_t configured = 0;
+  if (first_use_on_device(&configured))
+    MC_CHECK(cudaFuncSetAttribute(gemm_tf32_persistent_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+  const unsigned grid = (unsigned)(tiles < sm_count() ? tiles : sm_count());
+  mc::launch(gemm_tf32_persistent_kernel<BN, STAGES>, grid, PTHREADS, SMEM, tmA, tmB, p);
+  MC_LAUNCHED();
   return 0;
 }
 
@@ -915,6 +1118,12 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     if (fixup < 0) { const char* e = getenv("MC_GEMM_FIXUP"); fixup = (e && atoi(e) == 1) ? 1 : 0; }
     if (fixup && tiles <= kMaxFixupTiles) p.counters = splitk_counters();
   }
+  // grids beyond one wave, no split: the persistent, TMEM-double-buffered kernel (MC_GEMM_PERSISTENT=1 until
+  // it is validated on hardware; then the default)
+  static int persistent = -1;
+  if (persistent < 0) { const char* e = getenv("MC_GEMM_PERSISTENT"); persistent = (e && e[0] == '1') ? 1 : 0; }
+  if (persistent && splits == 1 && BN == 128 && tiles > sm_count())
+    return launch_tf32_persistent<128, 6>(tmA, tmB, p, tiles);
   int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
   if (rc == 0 && splits > 1 && !p.counters && !p.cluster) {
     mc::launch(splitk_reduce_kernel, grid_for(M * N / 4 + 1, 256), 256, 0, p.ws, splits, M, N, C, ldc, bias, relu, accumulate);

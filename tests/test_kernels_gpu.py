@@ -184,6 +184,45 @@ def test_gemm(cuda, M, N, K, ta, tb):
     cuda.set_gemm_precision('tf32')
 
 
+_MULTIWAVE = r"""
+import numpy as np
+from minpy_b200 import ops as cuda
+from minpy_b200.cuda_array import CudaArray
+cuda.L()
+cuda.set_gemm_precision('tf32')
+rng = np.random.RandomState(0)
+# grids of more than 148 tiles (more than one wave): the rastered tile order / the persistent kernel
+for M, N, K, ta, tb in [(2048, 2048, 256, 0, 0), (2000, 1900, 136, 0, 1), (4096, 1024, 96, 1, 0), (1500, 2100, 64, 1, 1),
+                        (8192, 384, 40, 0, 0)]:
+    a = rng.randn(*((K, M) if ta else (M, K))).astype(np.float32)
+    b = rng.randn(*((N, K) if tb else (K, N))).astype(np.float32)
+    bias = rng.randn(N).astype(np.float32)
+    ref = (a.T if ta else a).astype(np.float64).dot((b.T if tb else b).astype(np.float64))
+    ad, bd = CudaArray.from_numpy(a), CudaArray.from_numpy(b)
+    got = cuda.gemm(ad, bd, bool(ta), bool(tb)).asnumpy()
+    err = float(np.max(np.abs(got - ref)) / (3 * np.sqrt(K)))
+    assert err <= 2.5e-3, (M, N, K, ta, tb, err)
+    got = cuda.gemm(ad, bd, bool(ta), bool(tb), bias=CudaArray.from_numpy(bias), relu=2).asnumpy()
+    want = np.maximum(ref + bias, 0)
+    assert float(np.max(np.abs(got - want)) / (3 * np.sqrt(K))) <= 2.5e-3, (M, N, K, 'epilogue')
+    acc = cuda.gemm(ad, bd, bool(ta), bool(tb), out=CudaArray.from_numpy(ref.astype(np.float32)), accumulate=True).asnumpy()
+    assert float(np.max(np.abs(acc - 2 * ref)) / (3 * np.sqrt(K))) <= 2.5e-3, (M, N, K, 'accumulate')
+print('multiwave ok')
+"""
+
+
+@pytest.mark.parametrize('env', [{}, {'MC_GEMM_RASTER': '0'}, {'MC_GEMM_PERSISTENT': '1'}, {'MC_GEMM_PERSISTENT': '1', 'MC_PDL': '0'}])
+def test_gemm_grids_beyond_one_wave(env):
+    """Default (rastered tile order), x-major order, and the opt-in persistent TMEM-double-buffered kernel all
+    give the float64 product within the TF32 bound, with bias / signed-zero relu / accumulate epilogues and
+    ragged M, N, K tails."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, '-c', _MULTIWAVE], env=dict(os.environ, PYTHONPATH=root, **env), cwd=root,
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and 'multiwave ok' in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
 def test_gemm_cluster_splitk_opt_in():
     """MC_GEMM_CLUSTER=8 (split-K slices of a tile as one thread-block cluster, partials summed through
     distributed shared memory) gives the same products as the default workspace + reduce path."""

@@ -30,6 +30,7 @@ for f in sorted(glob.glob('$out/bench_*.json')):
 PY
 python tools/gemm_sweep.py > $out/gemm_sweep.log 2>&1
 MC_GEMM_RASTER=0 python tools/gemm_sweep.py sq4096 sq4096_nt sq8192 > $out/gemm_sweep_noraster.log 2>&1
+MC_GEMM_PERSISTENT=1 python tools/gemm_sweep.py sq2048 sq4096 sq4096_nt sq4096_tn sq8192 c5_vocab > $out/gemm_sweep_persistent.log 2>&1
 MC_PDL=0 python tools/gemm_sweep.py c3_fwd1 c3_dw1 c3_fwd2 c3_dx2 c3_dw2 sq4096 > $out/gemm_sweep_nopdl.log 2>&1
 MC_GEMM_SPLIT_FROM_KB=16 MC_GEMM_CLUSTER=2 python tools/gemm_sweep.py c3_fwd1 c3_dw1 c3_fwd2 c3_dx2 c3_dw2 > $out/gemm_sweep_split16_cluster2.log 2>&1
 MC_GEMM_SPLIT_FROM_KB=16 python tools/gemm_sweep.py c3_fwd2 c3_dx2 c3_dw2 > $out/gemm_sweep_split16.log 2>&1
