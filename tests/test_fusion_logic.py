@@ -23,6 +23,7 @@ class _Lib(object):
         def call(*args):
             self.calls.append((name, args))
             return 0
+        call.raw = call
         return call
 
     def names(self):
