@@ -206,6 +206,11 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels_i32, const float* on
  * loss[0].  A classifier head (integer labels, cols <= 32, rows <= 16384) is ONE single-block launch. */
 int mc_softmax_ce_fused(const float* x, const int32_t* labels_i32, const float* onehot,
                         float* probs, float* dx, float* loss, int64_t rows, int64_t cols);
+/* temporal_softmax_loss of nn/layers.py:444-480 over rows = N*T score vectors of `cols` classes:
+ * loss[0] = -sum_r mask[r] * log softmax(x[r])[y[r]] / batch   and   dx = mask * (softmax(x) - onehot(y)) / batch
+ * (the derivative of that loss; the VJP multiplies it by the upstream scalar).  mask may be NULL (all ones). */
+int mc_temporal_softmax_loss(const float* x, const int32_t* y_i32, const float* mask, float* dx, float* loss,
+                             int64_t rows, int64_t cols, int64_t batch);
 /* dx = (probs - y) / rows: `_softmax_output_grad` numpy_core.py:170-175 (ignores upstream g). */
 int mc_softmax_ce_bwd(const float* probs, const int32_t* labels_i32, const float* onehot,
                       float* dx, int64_t rows, int64_t cols);

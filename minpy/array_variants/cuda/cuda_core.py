@@ -738,6 +738,30 @@ def _softmax_loss_vjp(ans, x, label):  # pylint: disable=unused-argument
     return lambda _g: dx
 
 
+def fused_temporal_softmax_loss(x, y, mask):
+    """temporal_softmax_loss of nn/layers.py:444-480 -- x (N, T, V) scores, y (N, T) targets, mask (N, T) -- in
+    one kernel (+ the row-loss sum): the loss and, kept for the VJP, its derivative with respect to x."""
+    N, T, V = x.shape
+    loss, dx = CudaArray.empty(()), CudaArray.empty((N, T, V))
+    m = ops.as_f32(mask) if _is_arr(mask) else None
+    ops.L().mc_temporal_softmax_loss(ops.as_f32(x).ptr, ops.as_i32(y).ptr, m.ptr if m is not None else None, dx.ptr,
+                                     loss.ptr, N * T, V, N)
+    loss._saved = dx  # pylint: disable=protected-access
+    return loss
+
+
+def _temporal_softmax_loss_vjp(ans, x, y, mask):  # pylint: disable=unused-argument
+    dx = ans._saved  # pylint: disable=protected-access
+
+    def vjp(g):
+        if isinstance(g, ChainGrad):
+            g = g.g_scalar if (g.g is None and not g.steps) else g.materialize()
+        if not _is_arr(g):
+            return ChainGrad(dx.shape, dx, float(g))          # upstream 1.0 (the usual seed): dx itself, no launch
+        return ChainGrad(dx.shape, g, g_mode=ONE).then(E['MC_VJP_MUL_A'], dx, FULL)
+    return vjp
+
+
 def fused_lstm_step(x, prev_h, prev_c, Wx, Wh, b):
     """lstm_step of nn/layers.py:353-380: two GEMMs accumulated into one (N, 4H) buffer
     (bias in the first epilogue) and one gate kernel."""
@@ -891,7 +915,7 @@ def register_primitives(reg, prim_wrapper):
                append, concatenate, stack, _minpy_getitem, zeros, ones, empty, full, zeros_like, ones_like,
                array, arange, eye, dot, softmax_output, onehot_encode,
                fused_affine, fused_relu, fused_batchnorm, fused_batchnorm_test, fused_dropout,
-               fused_softmax_loss, fused_lstm_step, fused_lstm_temporal, fused_sgd, fused_sgd_momentum, fused_rmsprop, fused_adam):
+               fused_softmax_loss, fused_temporal_softmax_loss, fused_lstm_step, fused_lstm_temporal, fused_sgd, fused_sgd_momentum, fused_rmsprop, fused_adam):
         reg.register(fn.__name__, prim_wrapper(fn))
 
 
@@ -943,5 +967,6 @@ def def_grads(prims):
     prims('fused_batchnorm_test').def_grad_zero(3).def_grad_zero(4)
     prims('fused_dropout').def_grad(_dropout_vjp)
     prims('fused_softmax_loss').def_grad(_softmax_loss_vjp)
+    prims('fused_temporal_softmax_loss').def_grad(_temporal_softmax_loss_vjp).def_grad_zero(1).def_grad_zero(2)
     prims('fused_lstm_step').def_multiple_grad(_lstm_step_vjp, (0, 1, 2, 3, 4, 5))
     prims('fused_lstm_temporal').def_multiple_grad(_lstm_temporal_vjp, (0, 1, 2, 3, 4))

@@ -210,6 +210,9 @@ def temporal_affine(x, w, b):
 def temporal_softmax_loss(x, y, mask):
     """Masked softmax cross entropy over scores x (N, T, V), targets y (N, T) and mask (N, T):
     summed over time, averaged over the batch."""
+    fused = _cuda('fused_temporal_softmax_loss')
+    if fused is not None and len(x.shape) == 3:
+        return fused(x, y, mask)
     N, T, V = x.shape
     x_flat = x.reshape(N * T, V)
     y_flat = y.reshape(N * T)

@@ -268,6 +268,37 @@ __global__ void __launch_bounds__(1024) softmax_ce_small_kernel(const float* __r
   }
 }
 
+// temporal_softmax_loss (nn/layers.py:444-480) over rows = N*T score vectors: one warp per row computes the
+// softmax, the masked cross-entropy term  -mask * log p[y] / N  and the gradient  mask * (p - onehot) / N.
+// The reference composes it from ~12 primitives (30 launches forward + backward on the device).
+__global__ void __launch_bounds__(SM_THREADS) temporal_ce_kernel(const float* __restrict__ x, const int32_t* __restrict__ y,
+                                                                 const float* __restrict__ mask, float* __restrict__ dx,
+                                                                 float* __restrict__ rowloss, int64_t rows, int64_t cols,
+                                                                 float inv_n) {
+  mc::pdl_sync();
+  const int lane = threadIdx.x & 31;
+  const int64_t warps_per_grid = (int64_t)gridDim.x * (SM_THREADS / 32);
+  for (int64_t row = (int64_t)blockIdx.x * (SM_THREADS / 32) + (threadIdx.x >> 5); row < rows; row += warps_per_grid) {
+    const float* __restrict__ xr = x + row * cols;
+    float m = -INFINITY;
+    for (int64_t c = lane; c < cols; c += 32) m = fmaxf(m, xr[c]);
+    m = warp_max(m);
+    float s = 0.f;
+    for (int64_t c = lane; c < cols; c += 32) s += expf(xr[c] - m);
+    s = warp_sum(s);
+    const float w = mask ? mask[row] : 1.f;
+    int32_t lab = y[row];
+    if (lab < 0) lab += (int32_t)cols;
+    float* __restrict__ dr = dx + row * cols;
+    const float scale = w * inv_n;
+    for (int64_t c = lane; c < cols; c += 32) {
+      const float pr = expf(xr[c] - m) / s;
+      dr[c] = (pr - (c == lab ? 1.f : 0.f)) * scale;
+    }
+    if (lane == 0) rowloss[row] = (w != 0.f) ? -(xr[lab] - m - logf(s)) * scale : 0.f;
+  }
+}
+
 }  // namespace mc
 
 using namespace mc;
@@ -325,6 +356,18 @@ int mc_softmax_ce_fused(const float* x, const int32_t* labels, const float* oneh
   if (mc_softmax_ce_fwd(x, labels, onehot, p, loss, rows, cols)) return 1;
   if (dx) return mc_softmax_ce_bwd(p, labels, onehot, dx, rows, cols);
   return 0;
+}
+
+int mc_temporal_softmax_loss(const float* x, const int32_t* y, const float* mask, float* dx, float* loss, int64_t rows,
+                             int64_t cols, int64_t batch) {
+  MC_REQUIRE(rows > 0 && cols > 0 && batch > 0, "empty input");
+  ScratchFrame scratch;
+  float* rowloss = scratch.floats((size_t)rows);
+  if (!rowloss) return 1;
+  mc::launch(temporal_ce_kernel, grid_for(rows * 32, SM_THREADS), SM_THREADS, 0, x, y, mask, dx, rowloss, rows, cols,
+             1.f / (float)batch);
+  MC_LAUNCHED();
+  return reduce_sum_internal(rowloss, loss, 1, rows, 1);
 }
 
 int mc_softmax_ce_bwd(const float* probs, const int32_t* labels, const float* onehot, float* dx, int64_t rows,

@@ -295,3 +295,28 @@ def test_lazy_values_evaluate_on_demand():
         assert rel(rm.asnumpy(), 0.1 * hn.mean(0)) <= 2e-2
     finally:
         minpy.set_global_policy('prefer_cuda')
+
+
+@pytest.mark.parametrize('N,T,V', [(128, 100, 128), (4, 7, 10), (16, 5, 300), (3, 2, 33)])
+def test_temporal_softmax_loss_matches_the_oracle(N, T, V):
+    """mc_temporal_softmax_loss through layers.temporal_softmax_loss: value and gradient equal the oracle's
+    composition (nn/layers.py:444-480 differentiated by its tape), including masked-out steps and a
+    non-unit upstream gradient."""
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    try:
+        import minpy.numpy as mnp
+        from minpy import core
+        from minpy.nn import layers
+        rng = np.random.RandomState(N + T)
+        x = (rng.randn(N, T, V) * 2).astype(np.float32)
+        y = rng.randint(0, V, (N, T))
+        mask = (rng.rand(N, T) > 0.3).astype(np.float32)
+        yd, md = mnp.array(y), mnp.array(mask)
+        g, loss = core.grad_and_loss(lambda v: layers.temporal_softmax_loss(v, yd, md) * 3.0)(mnp.array(x))
+        og, oloss = orc.grad_and_loss(lambda v: orc.temporal_softmax_loss(v, y, mask.astype(np.float64)) * 3.0)(x.astype(np.float64))
+        assert abs(float(loss) - float(oloss)) <= 2e-5 * abs(float(oloss))
+        assert rel(g.asnumpy(), orc.raw(og)) <= 2e-5
+        assert np.all(g.asnumpy()[mask == 0] == 0)
+    finally:
+        minpy.set_global_policy('prefer_cuda')
