@@ -204,6 +204,9 @@ def temporal_affine(x, w, b):
     """Affine map applied to every timestep: x (N, T, D), w (D, M), b (M,) -> (N, T, M)."""
     N, T, D = x.shape
     M = b.shape[0]
+    fused = _cuda('fused_affine')
+    if fused is not None:        # bias in the GEMM epilogue instead of a broadcast add (and its column-sum VJP pass)
+        return fused(x.reshape(N * T, D), w, b).reshape(N, T, M)
     return x.reshape(N * T, D).dot(w).reshape(N, T, M) + b
 
 
