@@ -203,7 +203,7 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels_i32, const float* on
                       float* probs, float* loss, int64_t rows, int64_t cols);
 /* softmax_loss forward AND its gradient in one call: probs (may be NULL), dx = (probs - y) / rows (may be
  * NULL; the VJP ignores the upstream gradient, numpy_core.py:170-175, so it is known at forward time) and
- * loss[0].  A classifier head (integer labels, cols <= 32, rows <= 16384) is ONE single-block launch. */
+ * loss[0].  A classifier head (integer labels, cols <= 32) is ONE launch (warp per row, last block sums). */
 int mc_softmax_ce_fused(const float* x, const int32_t* labels_i32, const float* onehot,
                         float* probs, float* dx, float* loss, int64_t rows, int64_t cols);
 /* temporal_softmax_loss of nn/layers.py:444-480 over rows = N*T score vectors of `cols` classes:

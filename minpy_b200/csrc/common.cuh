@@ -62,7 +62,15 @@ const unsigned long long* graph_epoch();
 // of kernel i+1 overlap the tail of kernel i.  Correctness rule: no global memory access before
 // pdl_sync() (kernel parameters live in the constant bank and are fine).  Works in eager streams and
 // inside captured graphs (programmatic dependency edges).  MC_PDL=0 turns the attribute off.
-bool pdl_enabled();
+// MEASURED (profiles/r2d): with the attribute on EVERY kernel the mlp_c3 step got 3 % SLOWER (0.287 -> 0.296 ms)
+// and lstm_c5 2 % slower, while a chain of GEMMs alone got 8 % faster (7.6 -> 7.0 us per 1024x512x512 call).
+// A dependent grid is placed when it is launched early: the blocks of a small multi-CTA-per-SM kernel
+// (batchnorm, dropout, reductions: 64-600 blocks) pile onto the few SMs the running GEMM leaves idle instead of
+// spreading over all 148 once it finishes.  The tcgen05 kernels hold one CTA per SM, so their early CTAs can
+// only take SMs that are really free.  Default therefore: the attribute only on launches that ask for it
+// (`launch_pdl`: GEMM and convolution kernels).  MC_PDL=0: never, MC_PDL=2: every kernel (the experiment).
+int pdl_mode();
+inline bool pdl_enabled() { return pdl_mode() == 2; }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_sync() { pdl_trigger(); pdl_wait(); }
@@ -79,6 +87,22 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+// The same with the programmatic-launch attribute unless MC_PDL=0: for kernels that keep one CTA per SM.
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream();
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_mode() != 0 ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

@@ -1066,7 +1066,7 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
       cudaMemset(dbg_buf, 0, sizeof(long long) * 3 * 32 * 4);
       p.dbg = dbg_buf;
     }
-    mc::launch(conv_igemm_kernel, grid, IGEMM_THREADS, smem, tmX, tmW, p);
+    mc::launch_pdl(conv_igemm_kernel, grid, IGEMM_THREADS, smem, tmX, tmW, p);
     if (dbg) {
       static long long host[3 * 32 * 4];
       cudaDeviceSynchronize();
@@ -1156,9 +1156,9 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
           cudaMemset(dbg_buf, 0, sizeof(long long) * 3 * 32 * 4);
           h.dbg = dbg_buf;
         }
-        if (hg.TW == 1) mc::launch(conv_wgrad_halo_kernel<1>, grid, CONV_THREADS, smem, tmDy, tmX, h);
-        else if (hg.TW == 3) mc::launch(conv_wgrad_halo_kernel<3>, grid, CONV_THREADS, smem, tmDy, tmX, h);
-        else mc::launch(conv_wgrad_halo_kernel<0>, grid, CONV_THREADS, smem, tmDy, tmX, h);
+        if (hg.TW == 1) mc::launch_pdl(conv_wgrad_halo_kernel<1>, grid, CONV_THREADS, smem, tmDy, tmX, h);
+        else if (hg.TW == 3) mc::launch_pdl(conv_wgrad_halo_kernel<3>, grid, CONV_THREADS, smem, tmDy, tmX, h);
+        else mc::launch_pdl(conv_wgrad_halo_kernel<0>, grid, CONV_THREADS, smem, tmDy, tmX, h);
         if (dbg) {
           static long long host[3 * 32 * 4];
           cudaDeviceSynchronize();
@@ -1224,7 +1224,7 @@ int conv_wgrad_tc(const float* x, const float* dy, float* dw, float* dbias, int 
   if (rc == 0 && first_use_on_device(&configured)) rc = set_max_smem((const void*)conv_wgrad_kernel, "conv_wgrad_kernel");
   if (rc == 0) {
     dim3 grid((unsigned)groups, (unsigned)splits, (unsigned)ftiles);
-    mc::launch(conv_wgrad_kernel, grid, CONV_THREADS, smem, tmDy, tmX, p);
+    mc::launch_pdl(conv_wgrad_kernel, grid, CONV_THREADS, smem, tmDy, tmX, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("conv_wgrad_kernel launch failed: %s", cudaGetErrorString(e)); rc = 1; }
     else count_launch();

@@ -930,7 +930,7 @@ static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     count_launch();
     return 0;
   }
-  mc::launch(gemm_tf32_kernel<BN, STAGES>, grid, THREADS, SMEM, tmA, tmB, p);
+  mc::launch_pdl(gemm_tf32_kernel<BN, STAGES>, grid, THREADS, SMEM, tmA, tmB, p);
   MC_LAUNCHED();
   return 0;
 }
@@ -981,7 +981,7 @@ static int launch_tf32_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
   if (first_use_on_device(&configured))
     MC_CHECK(cudaFuncSetAttribute(gemm_tf32_persistent_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
   const unsigned grid = (unsigned)(tiles < sm_count() ? tiles : sm_count());
-  mc::launch(gemm_tf32_persistent_kernel<BN, STAGES>, grid, PTHREADS, SMEM, tmA, tmB, p);
+  mc::launch_pdl(gemm_tf32_persistent_kernel<BN, STAGES>, grid, PTHREADS, SMEM, tmA, tmB, p);
   MC_LAUNCHED();
   return 0;
 }
@@ -1118,10 +1118,10 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     if (fixup < 0) { const char* e = getenv("MC_GEMM_FIXUP"); fixup = (e && atoi(e) == 1) ? 1 : 0; }
     if (fixup && tiles <= kMaxFixupTiles) p.counters = splitk_counters();
   }
-  // grids beyond one wave, no split: the persistent, TMEM-double-buffered kernel (MC_GEMM_PERSISTENT=1 until
-  // it is validated on hardware; then the default)
+  // grids beyond one wave, no split: the persistent, TMEM-double-buffered kernel (profiles/r2d: 4096^3 535 -> 570
+  // TF/s, 8192^3 560 -> 585; MC_GEMM_PERSISTENT=0 selects the one-tile-per-CTA kernel)
   static int persistent = -1;
-  if (persistent < 0) { const char* e = getenv("MC_GEMM_PERSISTENT"); persistent = (e && e[0] == '1') ? 1 : 0; }
+  if (persistent < 0) { const char* e = getenv("MC_GEMM_PERSISTENT"); persistent = (e && e[0] == '0') ? 0 : 1; }
   if (persistent && splits == 1 && BN == 128 && tiles > sm_count())
     return launch_tf32_persistent<128, 6>(tmA, tmB, p, tiles);
   int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);

@@ -30,10 +30,10 @@ void set_error(const char* fmt, ...) {
 cudaStream_t stream() { return g_stream; }
 int sm_count() { return g_sm_count; }
 int device() { return g_device; }
-bool pdl_enabled() {
-  static int on = -1;
-  if (on < 0) { const char* e = getenv("MC_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
-  return on == 1;
+int pdl_mode() {
+  static int mode = -1;
+  if (mode < 0) { const char* e = getenv("MC_PDL"); mode = e ? atoi(e) : 1; if (mode < 0 || mode > 2) mode = 1; }
+  return mode;
 }
 bool first_use_on_device(uint32_t* mask) {
   const uint32_t bit = 1u << (g_device < 0 ? 0 : g_device);

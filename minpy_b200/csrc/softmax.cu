@@ -232,40 +232,53 @@ __global__ void __launch_bounds__(SM_THREADS) softmax_ce_bwd_kernel(const float*
   }
 }
 
-// softmax_loss for a classifier head (cols <= 32, integer labels): ONE block does everything the three
-// launches of mc_softmax_ce_fwd plus mc_softmax_ce_bwd do -- probabilities, the mean cross-entropy (row
-// losses summed per warp in row order, the 32 warp sums in warp order: deterministic) and, because the VJP
-// of the reference's softmax_output ignores its upstream gradient (numpy_core.py:170-175), the gradient
-// (p - onehot) / rows itself.  The whole problem is a few tens of KB: one launch of latency instead of four.
-__global__ void __launch_bounds__(1024) softmax_ce_small_kernel(const float* __restrict__ x, const int32_t* __restrict__ labels,
-                                                                float* __restrict__ probs, float* __restrict__ dx,
-                                                                float* __restrict__ loss, int rows, int cols, float inv_rows) {
+// softmax_loss for a classifier head (cols <= 32, integer labels): ONE launch does everything the three
+// launches of mc_softmax_ce_fwd plus mc_softmax_ce_bwd do -- probabilities, the mean cross-entropy and, because
+// the VJP of the reference's softmax_output ignores its upstream gradient (numpy_core.py:170-175), the
+// gradient (p - onehot) / rows itself.  One warp per row; the block that finishes last (ticket counter, reset
+// for the next call) adds the row losses in a fixed order, so the mean is deterministic.
+// (First version: a single 1024-thread block looping over 32 rows per warp -- 45 us for 1024 x 10, every
+// iteration a dependent global-load round trip; profiles/r2d.)
+constexpr int CE_THREADS = 256;
+__global__ void __launch_bounds__(CE_THREADS) softmax_ce_small_kernel(const float* __restrict__ x, const int32_t* __restrict__ labels,
+                                                                      float* __restrict__ probs, float* __restrict__ dx,
+                                                                      float* __restrict__ loss, float* __restrict__ rowloss,
+                                                                      int* __restrict__ counter, int rows, int cols,
+                                                                      float inv_rows) {
   mc::pdl_sync();
-  __shared__ float wsum[32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  float acc = 0.f;
-  for (int row = warp; row < rows; row += nw) {
+  __shared__ float red[32];
+  __shared__ int s_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int row = blockIdx.x * (CE_THREADS / 32) + warp;
+  if (row < rows) {
     const int64_t base = (int64_t)row * cols;
     const float v = lane < cols ? x[base + lane] : -INFINITY;
+    const int lab = labels[row];
     const float m = warp_max(v);
     const float e = lane < cols ? expf(v - m) : 0.f;
     const float s = warp_sum(e);
     const float pr = e / s;
-    const int lab = labels[row];
     if (lane < cols) {
       if (probs) probs[base + lane] = pr;
       if (dx) dx[base + lane] = (pr - (lane == lab ? 1.f : 0.f)) * inv_rows;
     }
     const float pl = __shfl_sync(0xffffffffu, pr, lab & 31);
-    acc -= logf(pl);
+    if (lane == 0) rowloss[row] = -logf(pl);
   }
-  if (lane == 0) wsum[warp] = acc;
+  __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
-    float t = 0.f;
-    for (int w = 0; w < nw; ++w) t += wsum[w];
-    *loss = t * inv_rows;
+    const int ticket = atomicAdd(counter, 1);
+    s_last = (ticket == (int)gridDim.x - 1) ? 1 : 0;
+    if (s_last) *counter = 0;
   }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  float acc = 0.f;
+  for (int r = threadIdx.x; r < rows; r += CE_THREADS) acc += __ldcg(rowloss + r);
+  acc = block_reduce(acc, SumOp(), red);
+  if (threadIdx.x == 0) *loss = acc * inv_rows;
 }
 
 // temporal_softmax_loss (nn/layers.py:444-480) over rows = N*T score vectors: one warp per row computes the
@@ -346,8 +359,19 @@ int mc_softmax_ce_fused(const float* x, const int32_t* labels, const float* oneh
   MC_REQUIRE((labels != nullptr) != (onehot != nullptr), "exactly one of labels / onehot");
   MC_REQUIRE(rows > 0 && cols > 0, "empty input");
   MC_REQUIRE(probs != nullptr || dx != nullptr, "nothing to write");
-  if (labels && cols <= 32 && rows <= 16384) {
-    mc::launch(softmax_ce_small_kernel, 1, 1024, 0, x, labels, probs, dx, loss, (int)rows, (int)cols, 1.f / (float)rows);
+  if (labels && cols <= 32 && rows <= (1 << 20)) {
+    static int* counters[16] = {};             // one ticket counter per device, zero between calls
+    int*& counter = counters[device() & 15];
+    if (!counter) {
+      MC_CHECK(cudaMalloc((void**)&counter, sizeof(int)));
+      MC_CHECK(cudaMemsetAsync(counter, 0, sizeof(int), stream()));     // stream-ordered (legal inside a capture)
+    }
+    ScratchFrame scratch;
+    float* rowloss = scratch.floats((size_t)rows);
+    if (!rowloss) return 1;
+    const unsigned blocks = (unsigned)((rows + CE_THREADS / 32 - 1) / (CE_THREADS / 32));
+    mc::launch(softmax_ce_small_kernel, blocks, CE_THREADS, 0, x, labels, probs, dx, loss, rowloss, counter, (int)rows, (int)cols,
+               1.f / (float)rows);
     MC_LAUNCHED();
     return 0;
   }

@@ -211,10 +211,10 @@ print('multiwave ok')
 """
 
 
-@pytest.mark.parametrize('env', [{}, {'MC_GEMM_RASTER': '0'}, {'MC_GEMM_PERSISTENT': '1'}, {'MC_GEMM_PERSISTENT': '1', 'MC_PDL': '0'}])
+@pytest.mark.parametrize('env', [{}, {'MC_GEMM_PERSISTENT': '0'}, {'MC_GEMM_PERSISTENT': '0', 'MC_GEMM_RASTER': '0'}, {'MC_PDL': '0'}, {'MC_PDL': '2'}])
 def test_gemm_grids_beyond_one_wave(env):
-    """Default (rastered tile order), x-major order, and the opt-in persistent TMEM-double-buffered kernel all
-    give the float64 product within the TF32 bound, with bias / signed-zero relu / accumulate epilogues and
+    """Default (persistent TMEM-double-buffered kernel, rastered tile order), the one-tile-per-CTA kernel with and
+    without the raster, and the three programmatic-launch modes all give the float64 product within the TF32 bound, with bias / signed-zero relu / accumulate epilogues and
     ragged M, N, K tails."""
     import os, subprocess, sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

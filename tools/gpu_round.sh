@@ -5,17 +5,19 @@
 tag=${1:-run}
 out=gpurun_out/$tag
 mkdir -p $out
-python -m pytest tests -m gpu -q -x > $out/pytest.log 2>&1; echo "pytest rc=$?" | tee -a $out/pytest.log
+python -m pytest tests -m gpu -q > $out/pytest.log 2>&1; echo "pytest rc=$?" | tee -a $out/pytest.log
 tail -3 $out/pytest.log
 quick="--no-ufunc --no-cpu-baseline --no-workloads --steps 50 --warmup 5"
 for w in mlp_c3 mlp_c1 cnn_c4 lstm_c5; do
   python bench.py $quick --workload $w > $out/bench_$w.json 2> $out/bench_$w.err; echo "bench $w rc=$?"
 done
-MC_PDL=0 python bench.py $quick > $out/bench_mlp_c3_nopdl.json 2> $out/bench_mlp_c3_nopdl.err
-MC_PDL=0 python bench.py $quick --workload lstm_c5 > $out/bench_lstm_c5_nopdl.json 2> $out/bench_lstm_c5_nopdl.err
+for m in 0 2; do
+  for w in mlp_c3 lstm_c5 cnn_c4; do
+    MC_PDL=$m python bench.py $quick --no-family-replay --workload $w > $out/bench_${w}_pdl$m.json 2> $out/bench_${w}_pdl$m.err
+  done
+done
 MINPY_FUSE_FORWARD=0 python bench.py $quick > $out/bench_mlp_c3_nofuse.json 2> $out/bench_mlp_c3_nofuse.err
 MC_GEMM_CLUSTER=4 python bench.py $quick > $out/bench_mlp_c3_cluster4.json 2> $out/bench_mlp_c3_cluster4.err
-MC_GEMM_CLUSTER=8 python bench.py $quick > $out/bench_mlp_c3_cluster8.json 2> $out/bench_mlp_c3_cluster8.err
 python - <<PY
 import json, glob, os
 for f in sorted(glob.glob('$out/bench_*.json')):
@@ -30,11 +32,7 @@ for f in sorted(glob.glob('$out/bench_*.json')):
 PY
 python tools/gemm_sweep.py > $out/gemm_sweep.log 2>&1
 MC_GEMM_RASTER=0 python tools/gemm_sweep.py sq4096 sq4096_nt sq8192 > $out/gemm_sweep_noraster.log 2>&1
-MC_GEMM_PERSISTENT=1 python tools/gemm_sweep.py sq2048 sq4096 sq4096_nt sq4096_tn sq8192 c5_vocab > $out/gemm_sweep_persistent.log 2>&1
-MC_PDL=0 python tools/gemm_sweep.py c3_fwd1 c3_dw1 c3_fwd2 c3_dx2 c3_dw2 sq4096 > $out/gemm_sweep_nopdl.log 2>&1
-MC_GEMM_SPLIT_FROM_KB=16 MC_GEMM_CLUSTER=2 python tools/gemm_sweep.py c3_fwd1 c3_dw1 c3_fwd2 c3_dx2 c3_dw2 > $out/gemm_sweep_split16_cluster2.log 2>&1
-MC_GEMM_SPLIT_FROM_KB=16 python tools/gemm_sweep.py c3_fwd2 c3_dx2 c3_dw2 > $out/gemm_sweep_split16.log 2>&1
-MC_GEMM_SPLIT_FROM_KB=16 MC_GEMM_CLUSTER=2 python bench.py $quick > $out/bench_mlp_c3_split16_cluster2.json 2> $out/bench_mlp_c3_split16_cluster2.err
+MC_GEMM_PERSISTENT=0 python tools/gemm_sweep.py sq2048 sq4096 sq4096_nt sq4096_tn sq8192 c5_vocab > $out/gemm_sweep_nonpersistent.log 2>&1
 tail -30 $out/gemm_sweep.log
 python bench.py > $out/bench_default.json 2> $out/bench_default.err; echo "default bench rc=$?"
 python bench.py --impl reference --steps 20 --warmup 5 > $out/bench_reference.json 2> $out/bench_reference.err; echo "reference rc=$?"
