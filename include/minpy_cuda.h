@@ -44,6 +44,16 @@ const char* mc_last_error(void);
 /* Number of kernels this library has launched since load (bench.py's gpu_launches). */
 int mc_launch_count(uint64_t* count);
 
+/* Side stream: library calls between mc_side_begin and mc_side_end run on a second stream forked from the
+ * compute stream (and, inside mc_graph_begin..end, become a parallel branch of the graph); mc_side_join makes
+ * the compute stream wait for them (mc_sync and mc_graph_end join implicitly).  Used for the weight-gradient
+ * contractions of the backward pass, which only the update rule reads (nn/solver.py:190-195) while the
+ * data-gradient chain continues (minpy/tape.py:223-234 replays VJPs strictly in sequence).  The caller keeps
+ * the operands of side work alive until the join. */
+int mc_side_begin(void);
+int mc_side_end(void);
+int mc_side_join(void);
+
 /* Stream-ordered device allocator (cudaMallocAsync pool): replaces NDArray allocation
  * inside mxnet.ndarray.array / mx.nd.* results (minpy/array.py:388-389). */
 int mc_alloc(void** ptr, size_t nbytes);

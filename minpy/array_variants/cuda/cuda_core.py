@@ -512,14 +512,25 @@ def _affine_vjps():
         return lambda g: ops.gemm(concrete(g, ans.shape), w, trans_b=True)
 
     def dw(ans, x, w, b):  # pylint: disable=unused-argument
-        return lambda g: ops.gemm(ops.as_f32(x), concrete(g, ans.shape), trans_a=True)
+        def vjp(g):
+            # x^T . g is read only by the update rule: on the side stream, beside the dX chain (ops.side_stream)
+            xf, gc = ops.as_f32(x), concrete(g, ans.shape)
+            with ops.side_stream(xf, gc):
+                out = ops.gemm(xf, gc, trans_a=True)
+            ops.side_keep(out)
+            return out
+        return vjp
 
     def db(ans, x, w, b):  # pylint: disable=unused-argument
         def vjp(g):
             tag = g._tag if isinstance(g, CudaArray) else None  # pylint: disable=protected-access
             if tag is not None and tag[0] == 'relu_done':
                 return tag[2].reshape(b.shape)          # column sums computed by batchnorm's fused VJP
-            return ops.reduce(E['MC_RED_SUM'], concrete(g, ans.shape), 0).reshape(b.shape)
+            gc = concrete(g, ans.shape)
+            with ops.side_stream(gc):                   # read only by the update rule: beside the dX chain
+                out = ops.reduce(E['MC_RED_SUM'], gc, 0)
+            ops.side_keep(out)
+            return out.reshape(b.shape)
         return vjp
     return dx, dw, db
 
@@ -853,9 +864,11 @@ def _lstm_temporal_vjp(ans, x, h0, Wx, Wh, b):
         dA = CudaArray.empty((T * N, 4 * H))
         lib.mc_lstm_seq_bwd(gates.ptr, cbuf.ptr, Wh.ptr, dH.ptr, dA.ptr, T, N, H, prec)
         h_prev = _view(hbuf, 0, (T * N, H))
-        dWx = ops.gemm(x_tm, dA, trans_a=True)
-        dWh = ops.gemm(h_prev, dA, trans_a=True)
-        db = ops.reduce(E['MC_RED_SUM'], dA, 0).reshape(b.shape)
+        with ops.side_stream(x_tm, dA, hbuf, h_prev):       # the three parameter gradients: beside dx and its transpose
+            dWx = ops.gemm(x_tm, dA, trans_a=True)
+            dWh = ops.gemm(h_prev, dA, trans_a=True)
+            db = ops.reduce(E['MC_RED_SUM'], dA, 0).reshape(b.shape)
+        ops.side_keep(dWx, dWh, db)
         dh0 = CudaArray.empty((N, H))
         lib.mc_memcpy_d2d(dh0.ptr, dH.ptr, sH)
         dx = ops.transpose(ops.gemm(dA, Wx, trans_b=True).reshape((T, N, D)), (1, 0, 2))

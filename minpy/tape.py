@@ -33,6 +33,12 @@ from minpy_b200.lazy import ChainGrad
 
 _logger = log.get_logger(__name__)
 
+
+def _side_join():
+    from minpy_b200 import ops
+    ops.side_join()
+
+
 GradRecord = collections.namedtuple('GradRecord', ['grad_func', 'result', 'owner'])
 
 
@@ -112,6 +118,8 @@ class Tape(object):
             if isinstance(grad, array.Value):
                 grad = grad._get_latest_data() if isinstance(grad, array.Array) else grad.val  # pylint: disable=protected-access
             have = self._grads.get(owner.id)
+            if have is not None:
+                _side_join()          # an earlier contribution may still be in flight on the side stream
             self._grads[owner.id] = grad if have is None else _add(have, grad)
         elif owner is not None:
             if len(owner) != len(grad):
@@ -156,6 +164,7 @@ class Tape(object):
                 for rid in ids:
                     if rid not in keep:
                         self._grads.pop(rid, None)
+        _side_join()                  # weight gradients computed beside the chain are complete from here on
         out = []
         for arr in origin:
             g = self._grads.get(arr.id)

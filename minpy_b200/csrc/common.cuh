@@ -14,6 +14,7 @@ void set_error(const char* fmt, ...);
 cudaStream_t stream();
 int sm_count();
 int device();
+int side_index();        // 1 while library calls are routed to the side stream (mc_side_begin .. mc_side_end), else 0
 // true exactly once per (mask, current device): per-device one-time set-up such as
 // cudaFuncSetAttribute, which applies to the current device only
 bool first_use_on_device(uint32_t* mask);

@@ -1002,9 +1002,9 @@ static int* splitk_counters() {
 // reuse in program order is safe; a cudaMallocAsync / cudaFreeAsync pair per call put two memory nodes
 // per GEMM into the captured step graph (suspected part of the per-node cost).
 static float* splitk_workspace(size_t bytes) {
-  static float* ws[16] = {};
-  static size_t cap[16] = {};
-  const int d = device() & 15;
+  static float* ws[32] = {};            // [device][main / side stream]
+  static size_t cap[32] = {};
+  const int d = ((device() & 15) << 1) | side_index();
   if (cap[d] < bytes) {
     size_t want = bytes < ((size_t)32 << 20) ? ((size_t)32 << 20) : bytes * 2;
     float* fresh = nullptr;

@@ -44,12 +44,18 @@ bool first_use_on_device(uint32_t* mask) {
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 const unsigned long long* graph_epoch() { return g_capturing ? g_epoch : nullptr; }
 
+// ---- side stream (weight-gradient contractions beside the main backward chain) ------------------------
+static cudaStream_t g_side_streams[MC_MAX_DEVICES] = {};
+static cudaEvent_t g_fork_ev[MC_MAX_DEVICES] = {}, g_join_ev[MC_MAX_DEVICES] = {};
+static bool g_in_side = false, g_side_pending = false;
+int side_index() { return g_in_side ? 1 : 0; }
+
 struct Arena { char* base; size_t cap, top; };
-static Arena g_arena[MC_MAX_DEVICES] = {};
-size_t scratch_mark() { return g_arena[g_device < 0 ? 0 : g_device].top; }
-void scratch_release(size_t mark) { g_arena[g_device < 0 ? 0 : g_device].top = mark; }
+static Arena g_arena[MC_MAX_DEVICES][2] = {};       // [device][main / side stream]: the two run concurrently
+size_t scratch_mark() { return g_arena[g_device < 0 ? 0 : g_device][side_index()].top; }
+void scratch_release(size_t mark) { g_arena[g_device < 0 ? 0 : g_device][side_index()].top = mark; }
 void* scratch_push(size_t bytes) {
-  Arena& a = g_arena[g_device < 0 ? 0 : g_device];
+  Arena& a = g_arena[g_device < 0 ? 0 : g_device][side_index()];
   bytes = (bytes + 255) & ~(size_t)255;
   if (a.top + bytes > a.cap) {
     size_t want = a.cap ? a.cap * 2 : ((size_t)64 << 20);
@@ -131,7 +137,45 @@ int mc_get_stream(void** s) {
   *s = (void*)g_stream;
   return 0;
 }
+/* Side stream: work that nothing on the main chain waits for until the end of the backward pass -- the
+ * weight-gradient GEMMs / convolutions (dW = x^T . g is read only by the update rule, while dX = g . W^T feeds
+ * the next VJP) -- runs on a second stream, forked from and joined back into the compute stream with events,
+ * inside a captured step graph too (parallel branches).  Between mc_side_begin and mc_side_end every library
+ * call is enqueued on the side stream; mc_side_join makes the compute stream wait for all of it.  The caller
+ * keeps the operands of side work alive until the join (the host-side free lists assume one stream). */
+int mc_side_begin(void) {
+  MC_REQUIRE(!g_in_side, "mc_side_begin: already on the side stream");
+  MC_REQUIRE(g_device >= 0 && g_stream != nullptr, "mc_init first");
+  const int d = g_device;
+  if (g_side_streams[d] == nullptr) {
+    MC_CHECK(cudaStreamCreateWithFlags(&g_side_streams[d], cudaStreamNonBlocking));
+    MC_CHECK(cudaEventCreateWithFlags(&g_fork_ev[d], cudaEventDisableTiming));
+    MC_CHECK(cudaEventCreateWithFlags(&g_join_ev[d], cudaEventDisableTiming));
+  }
+  MC_CHECK(cudaEventRecord(g_fork_ev[d], g_streams[d]));
+  MC_CHECK(cudaStreamWaitEvent(g_side_streams[d], g_fork_ev[d], 0));
+  g_stream = g_side_streams[d];
+  g_in_side = true;
+  return 0;
+}
+int mc_side_end(void) {
+  MC_REQUIRE(g_in_side, "mc_side_end without mc_side_begin");
+  const int d = g_device;
+  MC_CHECK(cudaEventRecord(g_join_ev[d], g_side_streams[d]));
+  g_stream = g_streams[d];
+  g_in_side = false;
+  g_side_pending = true;
+  return 0;
+}
+int mc_side_join(void) {
+  if (g_in_side) { if (mc_side_end()) return 1; }
+  if (!g_side_pending) return 0;
+  MC_CHECK(cudaStreamWaitEvent(g_streams[g_device], g_join_ev[g_device], 0));
+  g_side_pending = false;
+  return 0;
+}
 int mc_sync(void) {
+  if (g_side_pending || g_in_side) { if (mc_side_join()) return 1; }
   MC_CHECK(cudaStreamSynchronize(g_stream));
   return 0;
 }
@@ -323,6 +367,7 @@ int mc_graph_begin(void) {
 }
 int mc_graph_end(void** graph_exec) {
   MC_REQUIRE(g_capturing, "no capture in progress");
+  if (g_side_pending || g_in_side) { if (mc_side_join()) return 1; }     // every forked branch rejoins the capture
   g_capturing = false;
   cudaGraph_t graph = nullptr;
   MC_CHECK(cudaStreamEndCapture(g_stream, &graph));
@@ -336,6 +381,8 @@ int mc_graph_end(void** graph_exec) {
 /* Give up a capture after an error inside it: ends the capture, discards the partial graph and
  * clears the sticky capture error so that eager work can continue. */
 int mc_graph_abort(void) {
+  if (g_in_side) { g_stream = g_streams[g_device]; g_in_side = false; }
+  g_side_pending = false;
   if (!g_capturing) return 0;
   g_capturing = false;
   cudaGraph_t graph = nullptr;

@@ -816,8 +816,10 @@ def conv2d_nhwc_bwd(a, w, dy, pad=0, need_dx=True, need_db=True):
         dx = Nhwc(d, a.N, C, a.H, a.W, a.Cp)
     dw = CudaArray.empty(w.shape)
     db = CudaArray.empty((F,)) if need_db else None
-    lib.mc_conv2d_nhwc_wgrad(a.data.ptr, dy.data.ptr, dw.ptr, db.ptr if db is not None else None, a.N, C, a.H, a.W, a.Cp,
-                             a.wpad, F, dy.Cp, KH, KW, pad)
+    # the weight gradient is read only by the update rule: beside the data-gradient chain, on the side stream
+    with side_stream(a.data, dy.data, dw, db):
+        lib.mc_conv2d_nhwc_wgrad(a.data.ptr, dy.data.ptr, dw.ptr, db.ptr if db is not None else None, a.N, C, a.H, a.W,
+                                 a.Cp, a.wpad, F, dy.Cp, KH, KW, pad)
     return dx, dw, db
 
 
@@ -841,6 +843,48 @@ def maxpool2d_nhwc_bwd(dy, idx, like, k, relu_y=None):
         L().mc_maxpool2d_nhwc_bwd(dy.data.ptr, idx.ptr, relu_y.data.ptr if relu_y is not None else None, dx.ptr,
                                   like.N, like.H, like.W, like.Cp, k, dy.H, dy.W)
     return Nhwc(dx, like.N, like.C, like.H, like.W, like.Cp)
+
+
+# ------------------------------------------------------------------ side stream ----
+import contextlib as _contextlib
+import os as _os
+
+SIDE_STREAM = _os.environ.get('MINPY_SIDE_STREAM', '1') != '0'
+_side = {'keep': [], 'pending': False, 'active': False}
+
+
+@_contextlib.contextmanager
+def side_stream(*operands):
+    """Library calls inside the block run on the side stream (mc_side_begin / mc_side_end): for work whose
+    result nothing reads before the end of the backward pass (weight gradients).  `operands` -- everything the
+    block reads -- and whatever is passed to `side_keep` stay referenced until `side_join`, because the
+    host-side free lists hand a dropped buffer to the next MAIN-stream kernel at once."""
+    if not SIDE_STREAM or _side['active']:
+        yield False
+        return
+    lib = L()
+    _side['keep'].extend(operands)
+    lib.mc_side_begin()
+    _side['active'] = True
+    try:
+        yield True
+    finally:
+        _side['active'] = False
+        _side['pending'] = True
+        lib.mc_side_end()
+
+
+def side_keep(*arrays):
+    if _side['pending'] or _side['active']:
+        _side['keep'].extend(arrays)
+
+
+def side_join():
+    """The compute stream waits for all side work issued so far; its operands may be released."""
+    if _side['pending']:
+        L().mc_side_join()
+        _side['pending'] = False
+        del _side['keep'][:]
 
 
 # ------------------------------------------------------- operators of the raw array type ----

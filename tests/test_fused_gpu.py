@@ -92,7 +92,8 @@ def test_bn_dropout_fwd_equals_the_two_kernels(cuda, N, D):
     for a, b in ((y1, y2), (nrm1, nrm2), (nrv1, nrv2), (sm1, sm2), (si1, si2)):
         assert np.array_equal(a.asnumpy(), b.asnumpy())
     keep = y2.asnumpy() != 0
-    assert abs(keep.mean() - (1 - p)) < 0.02
+    if N * D >= 10000:
+        assert abs(keep.mean() - (1 - p)) < 0.02
     # oracle: batchnorm (layers.py:93-110) times the device's own mask
     ones = empty((N, D))
     lib.mc_dropout(cuda.full((N, D), 1.0).ptr, ones.ptr, N * D, p, seed, offset)

@@ -50,7 +50,9 @@ def fake(monkeypatch):
     monkeypatch.setitem(_state, 'device', 0)
     monkeypatch.setitem(_state, 'home', 0)
     monkeypatch.setattr(cuda_array, 'get_lib', lambda: lib)
-    return lib
+    ops._side.update(keep=[], pending=False, active=False)      # pylint: disable=protected-access
+    yield lib
+    ops._side.update(keep=[], pending=False, active=False)      # pylint: disable=protected-access
 
 
 def _arr(shape):
@@ -95,7 +97,12 @@ def test_hidden_block_forward_and_backward_call_sequence(fake):
     assert db.ptr == dh._tag[2].ptr and len(fake.calls) == 1                   # pylint: disable=protected-access
     dw_fn(a, x, w, b)(g_a)
     dx_fn(a, x, w, b)(g_a)
-    assert fake.names() == ['mc_bn_dropout_relu_bwd', 'mc_gemm', 'mc_gemm']
+    # the weight gradient runs on the side stream, the data gradient stays on the compute stream
+    assert fake.names() == ['mc_bn_dropout_relu_bwd', 'mc_side_begin', 'mc_gemm', 'mc_side_end', 'mc_gemm']
+    from minpy_b200 import ops
+    assert ops._side['pending'] and any(k is x for k in ops._side['keep'])     # pylint: disable=protected-access
+    ops.side_join()
+    assert fake.names()[-1] == 'mc_side_join' and not ops._side['keep']        # pylint: disable=protected-access
     assert a.pending() and out.pending()                                       # never evaluated
 
 
@@ -188,7 +195,15 @@ def test_mlp_c3_step_launch_sequence(fake, monkeypatch):
         del fake.calls[:]
         solver._step(DataBatch([xb], [yb], pad=0, index=1))          # pylint: disable=protected-access
         names = [n for n in fake.names() if n not in ('mc_readback_begin',)]
-        kernels = [n for n in names if n not in ('mc_memset', 'mc_memcpy_d2d')]
+        # every layer's weight-gradient GEMM (4 hidden + the head) is bracketed onto the side stream; ONE join before the update
+        # (5 weight gradients + the head's bias-gradient reduction; the hidden layers' bias gradients come out of
+        # the fused batchnorm VJP)
+        assert names.count('mc_side_begin') == 6 and names.count('mc_side_end') == 6 and names.count('mc_side_join') == 1
+        for i, n in enumerate(names):
+            if n == 'mc_side_begin':
+                assert names[i + 1] in ('mc_gemm', 'mc_reduce') and names[i + 2] == 'mc_side_end'
+        assert names.index('mc_side_join') == len(names) - 2 and names[-1] == 'mc_multi_update'
+        kernels = [n for n in names if n not in ('mc_memset', 'mc_memcpy_d2d', 'mc_side_begin', 'mc_side_end', 'mc_side_join')]
         fwd_block = ['mc_gemm', 'mc_bn_dropout_fwd']
         bwd_block = ['mc_bn_dropout_relu_bwd', 'mc_gemm', 'mc_gemm']
         want = fwd_block * 4 + ['mc_gemm', 'mc_softmax_ce_fused'] + \

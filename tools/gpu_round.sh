@@ -17,6 +17,9 @@ for m in 0 2; do
   done
 done
 MINPY_FUSE_FORWARD=0 python bench.py $quick > $out/bench_mlp_c3_nofuse.json 2> $out/bench_mlp_c3_nofuse.err
+for w in mlp_c3 mlp_c1 cnn_c4 lstm_c5; do
+  MINPY_SIDE_STREAM=0 python bench.py $quick --no-family-replay --workload $w > $out/bench_${w}_noside.json 2> $out/bench_${w}_noside.err
+done
 MC_GEMM_CLUSTER=4 python bench.py $quick > $out/bench_mlp_c3_cluster4.json 2> $out/bench_mlp_c3_cluster4.err
 python - <<PY
 import json, glob, os
