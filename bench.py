@@ -121,7 +121,7 @@ class CallTimer(object):
         lib = self.lib
         self.saved = {}
         skip = ('mc_event', 'mc_alloc', 'mc_free', 'mc_sync', 'mc_launch_count', 'mc_last_error', 'mc_get', 'mc_set',
-                'mc_init', 'mc_host', 'mc_mem_info', 'mc_device_count', 'mc_sm_count', 'mc_graph', 'mc_gemm_last_path')
+                'mc_init', 'mc_host', 'mc_mem_info', 'mc_device_count', 'mc_sm_count', 'mc_graph', 'mc_gemm_last_path', 'mc_side_')
         for name in lib.decls:
             if name.startswith(skip):
                 continue

@@ -322,6 +322,27 @@ constexpr int BM = 128;         // UMMA M (cta_group::1): accumulator row i <-> 
 constexpr int BK = 32;          // fp32 per stage along K = 128 B = one SWIZZLE_128B row
 constexpr int THREADS = 128;    // warp 0: TMA producer, warp 1: MMA issuer; all 4: epilogue
 
+// The LSTM time step as the epilogue of its recurrent GEMM (cluster split-K path only; see lstm.cu).
+//   mode 1 (forward):  the GEMM is h_{t-1} . Wh' with Wh' = Wh's columns reordered unit-major (column 4u+g =
+//          gate g of hidden unit u), so every float4 of the reduced tile holds the four recurrent
+//          pre-activations of ONE unit; the epilogue adds the input projection ax[row, g*H + u], applies the
+//          gate non-linearities and writes h_t, c_t and the gates (all gate-major, as the un-fused kernels).
+//   mode 2 (backward): the GEMM is dA_t . Wh^T = the recurrent part of dh_{t-1}; every float4 holds it for four
+//          consecutive units; the epilogue adds dH[t], and runs the gate backward of step t-1: dA_{t-1}, dc_{t-1}.
+struct LstmEpilogue {
+  const float* ax;        // fwd: (N, 4H) input projection of this step
+  const float* c_prev;    // fwd: c_{t-1};            bwd: c_{t-1} of the step being differentiated
+  const float* c_next;    //                           bwd: c_t of that step
+  float* h_out;           // fwd: h_t
+  float* c_out;           // fwd: c_t
+  float* gates;           // fwd: out (N, 4H);         bwd: in, the gates of that step
+  const float* dh_in;     // bwd: upstream dH of that step's h
+  const float* dc_next;   // bwd: dc flowing in from the step after it (may be null)
+  float* da;              // bwd: out (N, 4H)
+  float* dc_out;          // bwd: out (N, H)
+  int H;
+};
+
 struct GemmParams {
   float* C;
   int64_t ldc;
@@ -334,6 +355,8 @@ struct GemmParams {
   int kb_per_split;    // k-blocks (of BK) per grid.z slice
   int cluster;         // > 1: the grid.z slices of a tile are one thread-block cluster; partials meet in DSMEM
   int group_m;         // tile raster: CTAs walk `group_m` M-tiles for each N-tile before moving on (0 = x-major)
+  int lstm_mode;       // cluster epilogue: 0 plain, 1 LSTM gate forward, 2 LSTM gate backward (lstm.cu)
+  LstmEpilogue lstm;
 };
 
 // CTA q of an S-CTA cluster sums rows [q*BM/S, (q+1)*BM/S) of the parked partial tiles of all S peers
@@ -360,6 +383,57 @@ __device__ __forceinline__ void cluster_reduce(const GemmParams& p, uint32_t sme
 #pragma unroll
     for (int z = 1; z < S; ++z) { o.x += t[z].x; o.y += t[z].y; o.z += t[z].z; o.w += t[z].w; }
     const int grow = m0 + r, col = n0 + 4 * j;
+    if (p.lstm_mode == 1) {
+      if (grow < p.M && col < p.N) {
+        const LstmEpilogue& L = p.lstm;
+        const int H = L.H, u = col >> 2;
+        const int64_t gbase = (int64_t)grow * 4 * H + u, cell = (int64_t)grow * H + u;
+        const float p0 = o.x + L.ax[gbase], p1 = o.y + L.ax[gbase + H], p2 = o.z + L.ax[gbase + 2 * H],
+                    p3 = o.w + L.ax[gbase + 3 * H];
+        const float gi = 1.0f / (1.0f + expf(-p0)), gf = 1.0f / (1.0f + expf(-p1)), go = 1.0f / (1.0f + expf(-p2)),
+                    gg = tanhf(p3);
+        const float c = gf * L.c_prev[cell] + gi * gg;
+        L.c_out[cell] = c;
+        L.h_out[cell] = go * tanhf(c);
+        L.gates[gbase] = gi; L.gates[gbase + H] = gf; L.gates[gbase + 2 * H] = go; L.gates[gbase + 3 * H] = gg;
+      }
+      continue;
+    }
+    if (p.lstm_mode == 2) {
+      if (grow < p.M && col < p.N) {
+        const LstmEpilogue& L = p.lstm;
+        const int H = L.H;
+        const int64_t gbase = (int64_t)grow * 4 * H + col, cell = (int64_t)grow * H + col;
+        const float4 gi = *reinterpret_cast<const float4*>(L.gates + gbase), gf = *reinterpret_cast<const float4*>(L.gates + gbase + H),
+                     go = *reinterpret_cast<const float4*>(L.gates + gbase + 2 * H),
+                     gg = *reinterpret_cast<const float4*>(L.gates + gbase + 3 * H);
+        const float4 cn = *reinterpret_cast<const float4*>(L.c_next + cell), cp = *reinterpret_cast<const float4*>(L.c_prev + cell);
+        float4 dh = *reinterpret_cast<const float4*>(L.dh_in + cell);
+        dh.x += o.x; dh.y += o.y; dh.z += o.z; dh.w += o.w;
+        float4 dcn = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (L.dc_next) dcn = *reinterpret_cast<const float4*>(L.dc_next + cell);
+        float4 d0, d1, d2, d3, dpc;
+#define MC_LSTM_BWD(m)                                                \
+        {                                                             \
+          const float tc = tanhf(cn.m);                               \
+          float dc = dh.m * go.m * (1.f - tc * tc);                   \
+          if (L.dc_next) dc += dcn.m;                                 \
+          d0.m = dc * gg.m * gi.m * (1.f - gi.m);                     \
+          d1.m = dc * cp.m * gf.m * (1.f - gf.m);                     \
+          d2.m = dh.m * tc * go.m * (1.f - go.m);                     \
+          d3.m = dc * gi.m * (1.f - gg.m * gg.m);                     \
+          dpc.m = dc * gf.m;                                          \
+        }
+        MC_LSTM_BWD(x) MC_LSTM_BWD(y) MC_LSTM_BWD(z) MC_LSTM_BWD(w)
+#undef MC_LSTM_BWD
+        *reinterpret_cast<float4*>(L.da + gbase) = d0;
+        *reinterpret_cast<float4*>(L.da + gbase + H) = d1;
+        *reinterpret_cast<float4*>(L.da + gbase + 2 * H) = d2;
+        *reinterpret_cast<float4*>(L.da + gbase + 3 * H) = d3;
+        *reinterpret_cast<float4*>(L.dc_out + cell) = dpc;
+      }
+      continue;
+    }
     if (grow < p.M && col < p.N) {
       float* dst = p.C + (int64_t)grow * p.ldc + col;
       if (vec_ok && col + 4 <= p.N) {
@@ -922,10 +996,12 @@ static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
       MC_CHECK(cudaFuncSetAttribute(gemm_tf32_kernel<BN, STAGES>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = SMEM; cfg.stream = stream();
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)p.cluster;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl_mode() != 0 ? 2 : 1;
     MC_CHECK(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<BN, STAGES>, tmA, tmB, p));
     count_launch();
     return 0;
@@ -1072,6 +1148,8 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   p.kb_per_split = kb_per;
   p.counters = nullptr;
   p.cluster = 0;
+  p.lstm_mode = 0;
+  p.lstm = LstmEpilogue();
   // raster only when the grid is larger than one wave: keep <= ~48 MB of A panels resident in the 126 MB L2
   p.group_m = 0;
   {
@@ -1132,6 +1210,50 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     else count_launch();
   }
   return rc;
+}
+
+// One LSTM time step as ONE launch: the recurrent GEMM (cluster split-K, partials reduced through distributed
+// shared memory) with the gate arithmetic as its epilogue (LstmEpilogue above).  *taken = 0 when the shape does
+// not fit (the caller then runs the GEMM and the gate kernel separately).
+//   mode 1: op(A) = h_{t-1} (M = batch, K = H), B = Wh' (K, N = 4H) unit-major columns
+//   mode 2: op(A) = dA_t (M = batch, K = 4H), B = Wh (N = H rows of K = 4H): trans_b
+int gemm_tf32_lstm(int mode, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B, int64_t ldb,
+                   const tc::LstmEpilogue& epi, int* taken) {
+  using namespace tc;
+  *taken = 0;
+  const int tb = (mode == 2) ? 1 : 0;
+  if (M <= 0 || N < 64 || K < 64 || (N & 3) || (epi.H & 3) || !tma_ok(A, lda) || !tma_ok(B, ldb)) return 0;
+  static int enabled = -1;
+  if (enabled < 0) { const char* e = getenv("MC_LSTM_FUSED"); enabled = (e && e[0] == '0') ? 0 : 1; }
+  if (!enabled) return 0;
+  const int BN = 64;                                      // 4H / 64 (or H / 64) tiles x S slices ~ one CTA per SM
+  const int64_t tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int num_kb = (int)((K + BK - 1) / BK);
+  int S = 16;
+  while (S > 1 && (tiles * S > sm_count() || num_kb / S < 4)) S >>= 1;
+  int kb_per = 0;
+  for (; S > 1; S >>= 1) {
+    kb_per = (num_kb + S - 1) / S;
+    if ((S - 1) * kb_per < num_kb) break;                 // every slice non-empty
+  }
+  if (S < 2) return 0;
+  CUtensorMap tmA, tmB;
+  if (make_tmap_2d(&tmA, A, K, M, lda, BK, BM, false)) return 1;
+  if (!tb) { if (make_tmap_2d(&tmB, B, N, K, ldb, 32, BK, true)) return 1; }
+  else     { if (make_tmap_2d(&tmB, B, K, N, ldb, BK, BN, false)) return 1; }
+  GemmParams p;
+  p.C = nullptr; p.ldc = N; p.bias = nullptr; p.ws = nullptr; p.counters = nullptr;
+  p.M = (int)M; p.N = (int)N; p.K = (int)K;
+  p.relu = 0; p.accumulate = 0;
+  p.a_mn = 0;
+  p.b_mn = tb ? 0 : 1;
+  p.kb_per_split = kb_per;
+  p.cluster = S;
+  p.group_m = 0;
+  p.lstm_mode = mode;
+  p.lstm = epi;
+  *taken = 1;
+  return launch_tf32<64, 8>(tmA, tmB, p, S);
 }
 
 // The split-K GEMM without its combine pass, for consumers that add the slices themselves (the LSTM gate

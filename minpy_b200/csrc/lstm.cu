@@ -17,7 +17,29 @@ namespace mc {
 int gemm_tf32_partials(int ta, int tb, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B,
                        int64_t ldb, float* ws, int max_splits, int* splits);   // gemm.cu
 
+namespace tc {
+struct LstmEpilogue {        // must match gemm.cu
+  const float* ax; const float* c_prev; const float* c_next; float* h_out; float* c_out; float* gates;
+  const float* dh_in; const float* dc_next; float* da; float* dc_out; int H;
+};
+}
+int gemm_tf32_lstm(int mode, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B, int64_t ldb,
+                   const tc::LstmEpilogue& epi, int* taken);                    // gemm.cu
+
 constexpr int LS_THREADS = 256;
+
+// Wh (H, 4H) gate-major columns [i | f | o | g]  ->  unit-major columns: out[k, 4u + g] = in[k, g*H + u]
+__global__ void __launch_bounds__(LS_THREADS) lstm_permute_wh_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t H) {
+  mc::pdl_sync();
+  const int64_t n = H * H;                                 // one thread per (k, u): four loads, one float4 store
+  const int64_t stride = (int64_t)gridDim.x * LS_THREADS;
+  for (int64_t t = (int64_t)blockIdx.x * LS_THREADS + threadIdx.x; t < n; t += stride) {
+    const int64_t k = t / H, u = t - k * H;
+    const float* __restrict__ r = in + k * 4 * H + u;
+    *reinterpret_cast<float4*>(out + k * 4 * H + 4 * u) = make_float4(r[0], r[H], r[2 * H], r[3 * H]);
+  }
+}
+
 constexpr int LS_MAX_SPLITS = 16;
 
 __device__ __forceinline__ float ls_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }  // layers.py:243
@@ -172,8 +194,27 @@ int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* 
   if (try_partials) { ws = scratch.floats((size_t)(LS_MAX_SPLITS * sA)); if (!ws) return 1; }
   int rc = 0;
   const bool vec = ls_vec_ok(H, {A, ws, hbuf, cbuf, gates});
+  // Fused step: ONE launch = recurrent GEMM against the unit-major copy of Wh + gate arithmetic in its epilogue
+  float* whp = nullptr;
+  bool fused = try_partials && vec && aligned16(Wh) && T > 0;
+  if (fused) {
+    whp = scratch.floats((size_t)(H * 4 * H));
+    if (!whp) return 1;
+    mc::launch(lstm_permute_wh_kernel, grid_for(H * H, LS_THREADS), LS_THREADS, 0, Wh, whp, H);
+    MC_LAUNCHED();
+  }
   for (int64_t t = 0; t < T && rc == 0; ++t) {
     float* a_t = A + t * sA;
+    if (fused) {
+      tc::LstmEpilogue e = {};
+      e.ax = a_t; e.c_prev = cbuf + t * sH; e.h_out = hbuf + (t + 1) * sH; e.c_out = cbuf + (t + 1) * sH;
+      e.gates = gates + t * sA; e.H = (int)H;
+      int taken = 0;
+      rc = gemm_tf32_lstm(1, N, 4 * H, H, hbuf + t * sH, H, whp, 4 * H, e, &taken);
+      if (rc) break;
+      if (taken) continue;
+      fused = false;             // shape not taken: the two-launch path for the whole sequence
+    }
     int splits = 0;
     if (try_partials) rc = gemm_tf32_partials(0, 0, N, 4 * H, H, hbuf + t * sH, H, Wh, 4 * H, ws, LS_MAX_SPLITS, &splits);
     if (rc) break;
@@ -206,8 +247,42 @@ int mc_lstm_seq_bwd(const float* gates, const float* cbuf, const float* Wh, floa
   if (!dc) return 1;
   int rc = 0, pending = 0;
   const bool vec = ls_vec_ok(H, {gates, cbuf, dH, dA, ws, dc});
+  bool fused = try_partials && vec && aligned16(Wh);
+  bool done_by_epilogue = false;      // the gate backward of step t was computed by the epilogue of GEMM(t + 1)
   for (int64_t t = T - 1; t >= 0 && rc == 0; --t) {
     const float* dnext_c = (t < T - 1) ? dc + ((t + 1) & 1) * sH : nullptr;
+    if (fused) {
+      if (!done_by_epilogue) {          // only the last time step: nothing flows in from a later one
+        mc::launch(lstm_bwd_part4_kernel, grid_for(sH / 4, LS4_THREADS), LS4_THREADS, 0, gates + t * sA, cbuf + t * sH,
+                   cbuf + (t + 1) * sH, dH + (t + 1) * sH, (const float*)nullptr, 0, dnext_c, dA + t * sA, dc + (t & 1) * sH,
+                   N, H);
+        MC_LAUNCHED();
+      }
+      done_by_epilogue = false;
+      if (t > 0) {
+        // dA_t . Wh^T (the recurrent part of dh_{t-1}) with the gate backward of step t-1 as its epilogue
+        tc::LstmEpilogue e = {};
+        e.gates = const_cast<float*>(gates) + (t - 1) * sA; e.c_prev = cbuf + (t - 1) * sH; e.c_next = cbuf + t * sH;
+        e.dh_in = dH + t * sH; e.dc_next = dc + (t & 1) * sH; e.da = dA + (t - 1) * sA; e.dc_out = dc + ((t - 1) & 1) * sH;
+        e.H = (int)H;
+        int taken = 0;
+        rc = gemm_tf32_lstm(2, N, H, 4 * H, dA + t * sA, 4 * H, Wh, 4 * H, e, &taken);
+        if (rc) break;
+        if (taken) { done_by_epilogue = true; continue; }
+        fused = false;                // not taken: fall through to the two-launch path from this step on
+        pending = 0;
+      } else {
+        rc = mc_gemm(0, 1, N, H, 4 * H, dA, 4 * H, Wh, 4 * H, dH, H, nullptr, 0, 1, precision);   // dh0 += dA_0 . Wh^T
+        continue;
+      }
+      // (fall-through only when the fused GEMM was not taken at this t: dA[t] is computed, run its plain GEMM)
+      if (try_partials) {
+        rc = gemm_tf32_partials(0, 1, N, H, 4 * H, dA + t * sA, 4 * H, Wh, 4 * H, ws, LS_MAX_SPLITS, &pending);
+        if (rc) break;
+      }
+      if (pending == 0) rc = mc_gemm(0, 1, N, H, 4 * H, dA + t * sA, 4 * H, Wh, 4 * H, dH + t * sH, H, nullptr, 0, 1, precision);
+      continue;
+    }
     if (vec)
       mc::launch(lstm_bwd_part4_kernel, grid_for(sH / 4, LS4_THREADS), LS4_THREADS, 0, 
           gates + t * sA, cbuf + t * sH, cbuf + (t + 1) * sH, dH + (t + 1) * sH, ws, pending, dnext_c, dA + t * sA,
