@@ -1224,7 +1224,11 @@ int gemm_tf32_lstm(int mode, int64_t M, int64_t N, int64_t K, const float* A, in
   const int tb = (mode == 2) ? 1 : 0;
   if (M <= 0 || N < 64 || K < 64 || (N & 3) || (epi.H & 3) || !tma_ok(A, lda) || !tma_ok(B, ldb)) return 0;
   static int enabled = -1;
-  if (enabled < 0) { const char* e = getenv("MC_LSTM_FUSED"); enabled = (e && e[0] == '0') ? 0 : 1; }
+  // MEASURED (gpurun r2g, C5): correct (golden / full-size / step-graph LSTM tests pass) but SLOWER than GEMM +
+  // gate kernel -- 18 vs 10.5 us per time step: the 128 epilogue threads of a CTA each walk 2-8 items one after
+  // the other, every item a DSMEM round trip, then dependent global loads, then exp/tanh, while the separate gate
+  // kernel spreads the same items over 32 k threads.  Kept behind MC_LSTM_FUSED=1 (tests run both paths).
+  if (enabled < 0) { const char* e = getenv("MC_LSTM_FUSED"); enabled = (e && e[0] == '1') ? 1 : 0; }
   if (!enabled) return 0;
   const int BN = 64;                                      // 4H / 64 (or H / 64) tiles x S slices ~ one CTA per SM
   const int64_t tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);

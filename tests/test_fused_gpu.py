@@ -321,3 +321,37 @@ def test_temporal_softmax_loss_matches_the_oracle(N, T, V):
         assert np.all(g.asnumpy()[mask == 0] == 0)
     finally:
         minpy.set_global_policy('prefer_cuda')
+
+
+def test_lstm_fused_step_opt_in_matches_default():
+    """MC_LSTM_FUSED=1 (recurrent GEMM with the gate arithmetic as its cluster epilogue) gives the same
+    lstm_temporal value and gradients as the default GEMM + gate-kernel path."""
+    import os, subprocess, sys
+    code = r"""
+import numpy as np, minpy
+minpy.set_global_policy('only_cuda')
+import minpy.numpy as mnp
+from minpy import core
+from minpy.nn import layers
+rng = np.random.RandomState(0)
+N, T, D, H = 128, 6, 64, 256
+x = rng.randn(N, T, D).astype(np.float32); h0 = rng.randn(N, H).astype(np.float32) * 0.1
+Wx = (rng.randn(D, 4 * H) * 0.1).astype(np.float32); Wh = (rng.randn(H, 4 * H) * 0.1).astype(np.float32); b = rng.randn(4 * H).astype(np.float32) * 0.1
+f = lambda x_, h_, wx, wh, b_: mnp.sum(layers.lstm_temporal(x_, h_, wx, wh, b_) ** 2)
+g, v = core.grad_and_loss(f, argnum=range(5))(*[mnp.array(a) for a in (x, h0, Wx, Wh, b)])
+np.savez(__import__('sys').argv[1], v=float(v), **dict(('g%d' % i, a.asnumpy()) for i, a in enumerate(g)))
+"""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for flag in ('0', '1'):
+        path = os.path.join(root, 'gpurun_out', 'lstm_fused_%s.npz' % flag)
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        res = subprocess.run([sys.executable, '-c', code, path], env=dict(os.environ, PYTHONPATH=root, MC_LSTM_FUSED=flag),
+                             cwd=root, capture_output=True, text=True, timeout=300)
+        assert res.returncode == 0, res.stderr[-3000:]
+        outs.append(dict(np.load(path)))
+    a, b = outs
+    assert abs(a['v'] - b['v']) <= 2e-3 * abs(a['v'])
+    for k in a:
+        if k != 'v':
+            assert rel(b[k], a[k]) <= 5e-3, k
