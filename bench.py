@@ -229,6 +229,9 @@ def _work_of(name, a):
         if name == 'mc_bn_dropout_relu_bwd':
             N, D = _i(a[9]), _i(a[10])
             return 0.0, 4.0 * (3 * N * D + 5 * D)            # x, dy in; dx out; dgamma, dbeta, dbias
+        if name == 'mc_head_softmax_loss':
+            r, K, C = _i(a[-3]), _i(a[-2]), _i(a[-1])
+            return 4.0 * r * K * C, 4.0 * (2 * r * K + K * C + 3 * r * C)
         if name == 'mc_softmax_ce_fused':
             r, c = _i(a[-2]), _i(a[-1])
             return 0.0, 8.0 * r * c

@@ -216,6 +216,11 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels_i32, const float* on
  * loss[0].  A classifier head (integer labels, cols <= 32) is ONE launch (warp per row, last block sums). */
 int mc_softmax_ce_fused(const float* x, const int32_t* labels_i32, const float* onehot,
                         float* probs, float* dx, float* loss, int64_t rows, int64_t cols);
+/* The classifier head as one launch: logits = h (rows, K) . W (K, C) + bias, C <= 16; loss[0] = softmax_loss(logits,
+ * labels) (nn/layers.py:27, 201-221); dlogits = (softmax - onehot) / rows (numpy_core.py:170-175); dh = dlogits . W^T
+ * (the VJP of the affine with respect to its input; dh / logits may be NULL).  FP32 arithmetic. */
+int mc_head_softmax_loss(const float* h, const float* W, const float* bias, const int32_t* labels_i32, float* logits,
+                         float* dlogits, float* dh, float* loss, int64_t rows, int64_t K, int64_t C);
 /* temporal_softmax_loss of nn/layers.py:444-480 over rows = N*T score vectors of `cols` classes:
  * loss[0] = -sum_r mask[r] * log softmax(x[r])[y[r]] / batch   and   dx = mask * (softmax(x) - onehot(y)) / batch
  * (the derivative of that loss; the VJP multiplies it by the upstream scalar).  mask may be NULL (all ones). */

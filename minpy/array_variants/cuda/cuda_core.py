@@ -509,7 +509,12 @@ def fused_affine(x, w, b):
 def _affine_vjps():
     # (`ans` may be a LazyArray that was never evaluated: only its shape is used)
     def dx(ans, x, w, b):  # pylint: disable=unused-argument
-        return lambda g: ops.gemm(concrete(g, ans.shape), w, trans_b=True)
+        def vjp(g):
+            tag = g._tag if isinstance(g, CudaArray) else None  # pylint: disable=protected-access
+            if tag is not None and tag[0] == 'head_done' and tag[1] is ans:
+                return tag[2]                           # computed by the classifier-head kernel (fused_softmax_loss)
+            return ops.gemm(concrete(g, ans.shape), w, trans_b=True)
+        return vjp
 
     def dw(ans, x, w, b):  # pylint: disable=unused-argument
         def vjp(g):
@@ -575,7 +580,13 @@ class _BnPending(object):
         lib = ops.L()
         x = self.x
         N, D = x.shape
-        new_rm, new_rv = CudaArray.empty(self.rm.shape), CudaArray.empty(self.rv.shape)
+        from minpy_b200.cuda_array import _Buffer
+        if _Buffer._active_pool is not None and not self.stats_done:  # pylint: disable=protected-access
+            # step-graph capture: the running statistics are updated in place (each column is read and written by
+            # one thread), so the graph needs no copy-back node per statistic (step_graph.py)
+            new_rm, new_rv = self.rm, self.rv
+        else:
+            new_rm, new_rv = CudaArray.empty(self.rm.shape), CudaArray.empty(self.rv.shape)
         save_mean, save_invstd = CudaArray.empty((D,)), CudaArray.empty((D,))
         if drop is None:
             lib.mc_batchnorm_train_fwd(x.ptr, self.gamma.ptr, self.beta.ptr, self.rm.ptr, self.rv.ptr, out.ptr,
@@ -731,6 +742,19 @@ def fused_softmax_loss(x, label):
     lib = ops.L()
     rows, cols = x.shape
     loss = CudaArray.empty(())
+    if _FUSE_FORWARD and type(x) is LazyArray and x.pending() and type(x._saved) is tuple and x._saved[0] == 'affine' \
+            and label.ndim == 1 and cols <= 16 and x._saved[1].shape[1] * cols * 4 <= 200 * 1024:  # pylint: disable=protected-access,unidiomatic-typecheck
+        # the classifier head in one launch: the pending affine's GEMM, the loss, its gradient AND the gradient with
+        # respect to the affine's input (mc_head_softmax_loss) -- three launches on the chain otherwise
+        _, hh, w, b1 = x._saved  # pylint: disable=protected-access
+        K = hh.shape[1]
+        logits, dl, dh = CudaArray.empty((rows, cols)), CudaArray.empty((rows, cols)), CudaArray.empty((rows, K))
+        lib.mc_head_softmax_loss(hh.ptr, ops.as_f32(w).ptr, b1.ptr, ops.as_i32(label).ptr, logits.ptr, dl.ptr, dh.ptr, loss.ptr,
+                                 rows, K, cols)
+        x.bind(logits)                                  # the affine's value, should anything else ask for it
+        dl._tag = ('head_done', x, dh)  # pylint: disable=protected-access
+        loss._saved = dl  # pylint: disable=protected-access
+        return loss
     # the VJP ignores its upstream gradient (numpy_core.py:170-175), so dx = (p - y) / N is known now: the
     # forward kernel writes it instead of the probabilities and the backward pass launches nothing
     dx = CudaArray.empty((rows, cols))

@@ -156,13 +156,24 @@ def multi_update(rule, params, grads, configs):
         sig = tuple(float(cfg[k]) for k in hyper_keys) + ((int(cfg['t']) + 1,) if code == 3 else ())
         groups.setdefault(sig, []).append(i)
     lib = ops.L()
+    from minpy_b200.cuda_array import _Buffer
+    capturing = _Buffer._active_pool is not None  # pylint: disable=protected-access
     outs = [None] * len(ws)
     new_states = [None] * len(ws)
     for sig, idxs in groups.items():
         k = len(idxs)
         vp = ctypes.c_void_p * k
-        w_out = [CudaArray.empty(ws[i].shape) for i in idxs]
-        s_out = [[CudaArray.empty(ws[i].shape) for i in idxs] for _ in state_keys]
+        if capturing:
+            # inside a step-graph capture the replays overwrite parameters and optimizer state IN PLACE anyway
+            # (minpy_b200/step_graph.py copies new -> old at the end of the graph): let the kernel do it -- every
+            # element is read and written by the same thread -- and the graph carries no copy node per tensor
+            # (mlp_c3: 36 device-to-device copies per step)
+            w_out = [ws[i] for i in idxs]
+            s_out = [[states[i][q] if states[i][q] is not None else CudaArray.empty(ws[i].shape) for i in idxs]
+                     for q in range(len(state_keys))]
+        else:
+            w_out = [CudaArray.empty(ws[i].shape) for i in idxs]
+            s_out = [[CudaArray.empty(ws[i].shape) for i in idxs] for _ in state_keys]
         hyper = (ctypes.c_float * 4)(*(list(sig[:len(hyper_keys)]) + [0.0] * (4 - len(hyper_keys))))
 
         def arr(items):

@@ -281,6 +281,93 @@ __global__ void __launch_bounds__(CE_THREADS) softmax_ce_small_kernel(const floa
   if (threadIdx.x == 0) *loss = acc * inv_rows;
 }
 
+// The classifier head in ONE launch: logits = h . W + b (nn/layers.py:27), softmax_loss and its gradient
+// dlogits = (p - onehot) / rows (layers.py:201-221; numpy_core.py:170-175), and the gradient with respect to the
+// head's input, dh = dlogits . W^T -- what affine + softmax_loss + the two VJPs compute in three launches on the
+// chain (skinny GEMM, loss kernel, skinny GEMM).  One warp per row; W (K x C, C <= 16) lives in shared memory;
+// FP32 throughout, like the skinny kernels it replaces.  The block that finishes last sums the row losses.
+constexpr int HEAD_THREADS = 256;
+constexpr int HEAD_MAXC = 16;
+__global__ void __launch_bounds__(HEAD_THREADS) head_softmax_kernel(const float* __restrict__ h, const float* __restrict__ W,
+                                                                    const float* __restrict__ bias, const int32_t* __restrict__ labels,
+                                                                    float* __restrict__ logits, float* __restrict__ dlogits,
+                                                                    float* __restrict__ dh, float* __restrict__ loss,
+                                                                    float* __restrict__ rowloss, int* __restrict__ counter, int rows,
+                                                                    int K, int C, float inv_rows) {
+  extern __shared__ float w_s[];            // K * C
+  mc::pdl_sync();
+  __shared__ float red[32];
+  __shared__ int s_last;
+  for (int i = threadIdx.x; i < K * C; i += HEAD_THREADS) w_s[i] = W[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int row = blockIdx.x * (HEAD_THREADS / 32) + warp;
+  if (row < rows) {
+    const float* __restrict__ hr = h + (int64_t)row * K;
+    float acc[HEAD_MAXC];
+#pragma unroll
+    for (int c = 0; c < HEAD_MAXC; ++c) acc[c] = 0.f;
+    for (int f = lane; f < K; f += 32) {
+      const float hv = hr[f];
+      const float* __restrict__ wr = w_s + f * C;
+#pragma unroll
+      for (int c = 0; c < HEAD_MAXC; ++c) if (c < C) acc[c] = fmaf(hv, wr[c], acc[c]);
+    }
+    float m = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < HEAD_MAXC; ++c) {
+      if (c < C) {
+        acc[c] = warp_sum(acc[c]) + (bias ? bias[c] : 0.f);
+        m = fmaxf(m, acc[c]);
+      }
+    }
+    float ssum = 0.f;
+#pragma unroll
+    for (int c = 0; c < HEAD_MAXC; ++c) if (c < C) ssum += expf(acc[c] - m);
+    const int lab = labels[row];
+    float dl[HEAD_MAXC];
+    float lab_logit = 0.f;
+#pragma unroll
+    for (int c = 0; c < HEAD_MAXC; ++c) {
+      dl[c] = 0.f;
+      if (c < C) {
+        const float pr = expf(acc[c] - m) / ssum;
+        dl[c] = (pr - (c == lab ? 1.f : 0.f)) * inv_rows;
+        if (c == lab) lab_logit = acc[c];
+        if (lane == 0) {
+          if (logits) logits[(int64_t)row * C + c] = acc[c];
+          dlogits[(int64_t)row * C + c] = dl[c];
+        }
+      }
+    }
+    if (lane == 0) rowloss[row] = -(lab_logit - m - logf(ssum));
+    if (dh) {
+      float* __restrict__ dr = dh + (int64_t)row * K;
+      for (int f = lane; f < K; f += 32) {
+        const float* __restrict__ wr = w_s + f * C;
+        float v = 0.f;
+#pragma unroll
+        for (int c = 0; c < HEAD_MAXC; ++c) if (c < C) v = fmaf(dl[c], wr[c], v);
+        dr[f] = v;
+      }
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int ticket = atomicAdd(counter, 1);
+    s_last = (ticket == (int)gridDim.x - 1) ? 1 : 0;
+    if (s_last) *counter = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  float a = 0.f;
+  for (int r = threadIdx.x; r < rows; r += HEAD_THREADS) a += __ldcg(rowloss + r);
+  a = block_reduce(a, SumOp(), red);
+  if (threadIdx.x == 0) *loss = a * inv_rows;
+}
+
 // temporal_softmax_loss (nn/layers.py:444-480) over rows = N*T score vectors: one warp per row computes the
 // softmax, the masked cross-entropy term  -mask * log p[y] / N  and the gradient  mask * (p - onehot) / N.
 // The reference composes it from ~12 primitives (30 launches forward + backward on the device).
@@ -354,18 +441,24 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels, const float* onehot
   return rc;
 }
 
+static int* ticket_counter() {
+  static int* counters[16] = {};             // one ticket counter per device, zero between calls
+  int*& counter = counters[device() & 15];
+  if (!counter) {
+    if (cudaMalloc((void**)&counter, sizeof(int)) != cudaSuccess) { counter = nullptr; return nullptr; }
+    cudaMemsetAsync(counter, 0, sizeof(int), stream());
+  }
+  return counter;
+}
+
 int mc_softmax_ce_fused(const float* x, const int32_t* labels, const float* onehot, float* probs, float* dx, float* loss,
                         int64_t rows, int64_t cols) {
   MC_REQUIRE((labels != nullptr) != (onehot != nullptr), "exactly one of labels / onehot");
   MC_REQUIRE(rows > 0 && cols > 0, "empty input");
   MC_REQUIRE(probs != nullptr || dx != nullptr, "nothing to write");
   if (labels && cols <= 32 && rows <= (1 << 20)) {
-    static int* counters[16] = {};             // one ticket counter per device, zero between calls
-    int*& counter = counters[device() & 15];
-    if (!counter) {
-      MC_CHECK(cudaMalloc((void**)&counter, sizeof(int)));
-      MC_CHECK(cudaMemsetAsync(counter, 0, sizeof(int), stream()));     // stream-ordered (legal inside a capture)
-    }
+    int* counter = ticket_counter();
+    MC_REQUIRE(counter != nullptr, "ticket counter allocation failed");
     ScratchFrame scratch;
     float* rowloss = scratch.floats((size_t)rows);
     if (!rowloss) return 1;
@@ -392,6 +485,26 @@ int mc_temporal_softmax_loss(const float* x, const int32_t* y, const float* mask
              1.f / (float)batch);
   MC_LAUNCHED();
   return reduce_sum_internal(rowloss, loss, 1, rows, 1);
+}
+
+int mc_head_softmax_loss(const float* h, const float* W, const float* bias, const int32_t* labels, float* logits,
+                         float* dlogits, float* dh, float* loss, int64_t rows, int64_t K, int64_t C) {
+  MC_REQUIRE(rows > 0 && K > 0 && C > 0 && C <= HEAD_MAXC, "classifier head: 1 <= classes <= 16");
+  const size_t smem = sizeof(float) * (size_t)K * C;
+  MC_REQUIRE(smem <= 200 * 1024, "classifier head: weight matrix beyond 200 KB of shared memory");
+  static uint32_t configured = 0;
+  if (first_use_on_device(&configured))
+    MC_CHECK(cudaFuncSetAttribute(head_softmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  int* counter = ticket_counter();
+  MC_REQUIRE(counter != nullptr, "ticket counter allocation failed");
+  ScratchFrame scratch;
+  float* rowloss = scratch.floats((size_t)rows);
+  if (!rowloss) return 1;
+  const unsigned blocks = (unsigned)((rows + HEAD_THREADS / 32 - 1) / (HEAD_THREADS / 32));
+  mc::launch(head_softmax_kernel, blocks, HEAD_THREADS, smem, h, W, bias, labels, logits, dlogits, dh, loss, rowloss, counter,
+             (int)rows, (int)K, (int)C, 1.f / (float)rows);
+  MC_LAUNCHED();
+  return 0;
 }
 
 int mc_softmax_ce_bwd(const float* probs, const int32_t* labels, const float* onehot, float* dx, int64_t rows,

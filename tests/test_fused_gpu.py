@@ -355,3 +355,49 @@ np.savez(__import__('sys').argv[1], v=float(v), **dict(('g%d' % i, a.asnumpy()) 
     for k in a:
         if k != 'v':
             assert rel(b[k], a[k]) <= 5e-3, k
+
+
+@pytest.mark.parametrize('rows,K,C', [(1024, 512, 10), (256, 512, 10), (512, 2048, 10), (37, 50, 3), (128, 96, 16)])
+def test_classifier_head_kernel_matches_oracle_and_composition(cuda, rows, K, C):
+    """mc_head_softmax_loss: logits, loss, dlogits and dh against float64 (affine + softmax_loss differentiated by
+    the oracle's tape) and, through the front end, against the separate kernels (MINPY_FUSE_FORWARD off)."""
+    lib = cuda.L()
+    rng = np.random.RandomState(rows + K)
+    h = rng.randn(rows, K).astype(np.float32)
+    W = (rng.randn(K, C) * 0.1).astype(np.float32)
+    b = rng.randn(C).astype(np.float32)
+    lab = rng.randint(0, C, rows).astype(np.int32)
+    H, Wd, B, L = up(h), up(W), up(b), up(lab)
+    logits, dl, dh, loss = empty((rows, C)), empty((rows, C)), empty((rows, K)), empty(())
+    n0 = launches(lib)
+    lib.mc_head_softmax_loss(H.ptr, Wd.ptr, B.ptr, L.ptr, logits.ptr, dl.ptr, dh.ptr, loss.ptr, rows, K, C)
+    assert launches(lib) - n0 == 1
+    f = lambda hv, wv, bv: orc.softmax_loss(orc.affine(hv, wv, bv), lab)
+    (gh, gw, gb), want = orc.grad_and_loss(f, argnum=range(3))(h.astype(np.float64), W.astype(np.float64), b.astype(np.float64))
+    assert rel(logits.asnumpy(), h.astype(np.float64).dot(W) + b) <= 1e-5
+    assert abs(float(loss.asnumpy()) - float(orc.raw(want))) <= 1e-5 * abs(float(orc.raw(want)))
+    assert rel(dh.asnumpy(), orc.raw(gh)) <= 2e-5
+    assert rel(dl.asnumpy().sum(axis=0), orc.raw(gb)) <= 2e-5
+    assert rel(h.T.astype(np.float64).dot(dl.asnumpy()), orc.raw(gw)) <= 2e-5
+    # front end: the same head through layers.affine + layers.softmax_loss, fused and un-fused
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    try:
+        import minpy.numpy as mnp
+        from minpy import core
+        from minpy.nn import layers
+        from minpy.array_variants.cuda import cuda_core
+        res = []
+        for fuse in (True, False):
+            saved, cuda_core._FUSE_FORWARD = cuda_core._FUSE_FORWARD, fuse          # pylint: disable=protected-access
+            try:
+                g, v = core.grad_and_loss(lambda hv, wv, bv: layers.softmax_loss(layers.affine(hv, wv, bv), mnp.array(lab)),
+                                          argnum=range(3))(mnp.array(h), mnp.array(W), mnp.array(b))
+                res.append((float(v), [a.asnumpy() for a in g]))
+            finally:
+                cuda_core._FUSE_FORWARD = saved                                     # pylint: disable=protected-access
+        assert abs(res[0][0] - res[1][0]) <= 1e-5 * abs(res[1][0])
+        for a, b2, o in zip(res[0][1], res[1][1], (gh, gw, gb)):
+            assert rel(a, orc.raw(o)) <= 2e-5 and rel(b2, orc.raw(o)) <= 2e-5
+    finally:
+        minpy.set_global_policy('prefer_cuda')

@@ -162,6 +162,32 @@ def test_dropout_marker_materialises_through_mc_dropout(fake):
     assert fake.names() == ['mc_dropout'] and fake.calls[0][1][0] == g.ptr
 
 
+def test_classifier_head_is_one_call(fake):
+    """affine (<= 16 classes) -> softmax_loss: one mc_head_softmax_loss; the affine's data-gradient VJP returns the
+    dh that kernel produced, its weight-gradient VJP still runs a GEMM on dlogits."""
+    from minpy.array_variants.cuda import cuda_core as cc
+    from minpy_b200.cuda_array import CudaArray, _I32
+    from minpy_b200 import ops
+    h, w, b = _arr((64, 32)), _arr((32, 10)), _arr((10,))
+    lab = CudaArray.empty((64,), _I32)
+    a = cc.fused_affine(h, w, b)
+    loss = cc.fused_softmax_loss(a, lab)
+    assert fake.names() == ['mc_head_softmax_loss'] and not a.pending()
+    args = fake.calls[0][1]
+    assert args[0] == h.ptr and args[1] == w.ptr and args[4] == a.ptr and args[-3:] == (64, 32, 10)
+    dl = cc._softmax_loss_vjp(loss, a, lab)(1.0)                                # pylint: disable=protected-access
+    dx_fn, dw_fn, _ = cc._affine_vjps()                                          # pylint: disable=protected-access
+    dh = dx_fn(a, h, w, b)(dl)
+    assert dh.ptr == args[6] and len(fake.calls) == 1
+    dw_fn(a, h, w, b)(dl)
+    ops.side_join()
+    assert [n for n in fake.names() if not n.startswith('mc_side')] == ['mc_head_softmax_loss', 'mc_gemm']
+    # more than 16 classes, or a concrete input: the plain loss kernel
+    del fake.calls[:]
+    cc.fused_softmax_loss(cc.fused_affine(h, _arr((32, 40)), _arr((40,))), lab)
+    assert fake.names() == ['mc_gemm', 'mc_softmax_ce_fused']
+
+
 def test_softmax_loss_gradient_comes_from_the_forward_kernel(fake):
     from minpy.array_variants.cuda import cuda_core as cc
     from minpy_b200.cuda_array import CudaArray, _I32
@@ -176,7 +202,7 @@ def test_softmax_loss_gradient_comes_from_the_forward_kernel(fake):
 def test_mlp_c3_step_launch_sequence(fake, monkeypatch):
     """One full `Solver._step` of BASELINE config 3 (5-layer MLP, batchnorm + dropout, batch 1024) against the
     recorder: the library calls it issues, through the real front end (layers, tape, optim).  Round 1 issued
-    55 kernel launches per step; the fused step issues the 25 library calls below (a split-K GEMM is two launches)."""
+    55 kernel launches per step; the fused step issues the 23 library calls below (a split-K GEMM is two launches)."""
     import minpy
     from minpy import array as marray
     from minpy.nn.io import DataBatch
@@ -206,13 +232,15 @@ def test_mlp_c3_step_launch_sequence(fake, monkeypatch):
         kernels = [n for n in names if n not in ('mc_memset', 'mc_memcpy_d2d', 'mc_side_begin', 'mc_side_end', 'mc_side_join')]
         fwd_block = ['mc_gemm', 'mc_bn_dropout_fwd']
         bwd_block = ['mc_bn_dropout_relu_bwd', 'mc_gemm', 'mc_gemm']
-        want = fwd_block * 4 + ['mc_gemm', 'mc_softmax_ce_fused'] + \
-            ['mc_gemm', 'mc_gemm', 'mc_reduce'] + bwd_block * 3 + ['mc_bn_dropout_relu_bwd', 'mc_gemm'] + ['mc_multi_update']
+        # (the head -- affine 512 -> 10, softmax_loss, both their chain VJPs -- is ONE call; its weight and bias
+        # gradients are the 'mc_gemm', 'mc_reduce' pair on the side stream)
+        want = fwd_block * 4 + ['mc_head_softmax_loss'] + \
+            ['mc_gemm', 'mc_reduce'] + bwd_block * 3 + ['mc_bn_dropout_relu_bwd', 'mc_gemm'] + ['mc_multi_update']
         assert sorted(kernels) == sorted(want), kernels
-        assert kernels[:10] == want[:10]                              # the forward order
-        assert kernels.count('mc_gemm') == 14 and len(kernels) == 25
-        relu_modes = [c[1][12] for c in fake.calls if c[0] == 'mc_gemm'][:5]
-        assert relu_modes == [2, 2, 2, 2, 0]
+        assert kernels[:9] == want[:9]                                # the forward order
+        assert kernels.count('mc_gemm') == 12 and len(kernels) == 23
+        relu_modes = [c[1][12] for c in fake.calls if c[0] == 'mc_gemm'][:4]
+        assert relu_modes == [2, 2, 2, 2]
         bwd = [c[1] for c in fake.calls if c[0] == 'mc_bn_dropout_relu_bwd']
         assert all(a[11] == 1 and a[15] == 1 and a[8] is not None for a in bwd)     # dropout + relu + bias gradient fused
     finally:
