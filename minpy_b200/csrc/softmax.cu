@@ -298,7 +298,13 @@ __global__ void __launch_bounds__(HEAD_THREADS) head_softmax_kernel(const float*
   mc::pdl_sync();
   __shared__ float red[32];
   __shared__ int s_last;
-  for (int i = threadIdx.x; i < K * C; i += HEAD_THREADS) w_s[i] = W[i];
+  // (unrolled: an un-unrolled copy loop is one dependent global-load round trip per iteration -- the first
+  // version of this kernel took 14.5 us for 1024 x 512 x 10, profiles/r2i)
+  {
+    const int n = K * C;
+#pragma unroll 8
+    for (int i = threadIdx.x; i < n; i += HEAD_THREADS) w_s[i] = __ldg(W + i);
+  }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int row = blockIdx.x * (HEAD_THREADS / 32) + warp;
@@ -307,11 +313,18 @@ __global__ void __launch_bounds__(HEAD_THREADS) head_softmax_kernel(const float*
     float acc[HEAD_MAXC];
 #pragma unroll
     for (int c = 0; c < HEAD_MAXC; ++c) acc[c] = 0.f;
-    for (int f = lane; f < K; f += 32) {
-      const float hv = hr[f];
-      const float* __restrict__ wr = w_s + f * C;
+    for (int f0 = lane; f0 < K; f0 += 32 * 8) {          // eight row elements in flight per lane
+      float hv[8];
 #pragma unroll
-      for (int c = 0; c < HEAD_MAXC; ++c) if (c < C) acc[c] = fmaf(hv, wr[c], acc[c]);
+      for (int q = 0; q < 8; ++q) hv[q] = (f0 + 32 * q < K) ? __ldg(hr + f0 + 32 * q) : 0.f;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if (f0 + 32 * q < K) {
+          const float* __restrict__ wr = w_s + (f0 + 32 * q) * C;
+#pragma unroll
+          for (int c = 0; c < HEAD_MAXC; ++c) if (c < C) acc[c] = fmaf(hv[q], wr[c], acc[c]);
+        }
+      }
     }
     float m = -INFINITY;
 #pragma unroll
