@@ -189,6 +189,60 @@ __global__ void __launch_bounds__(P2P_THREADS) p2p_allreduce_kernel(P2PParams p,
   p2p_block_barrier(p);
 }
 
+// PUSH version (default; MINPY_P2P_PUSH=0 selects the pull kernel above).  NVLink stores are posted -- they cost
+// bandwidth, not a round trip -- while every peer LOAD of the pull version is a 2-3 us round trip, and the pull
+// version needs three barriers (data ready / slices reduced / everybody done reading).  Here:
+//   reduce-scatter   rank r WRITES slice q of its gradients into rank q's receive area (slot r)
+//   barrier          (flag after a system fence: the pushed data is visible before the flag)
+//   reduce + gather  rank r sums its slice over the W slots in rank order (own slot = its own buffer), scales,
+//                    and WRITES the result into its own window and into every peer's window
+//   barrier
+// Two barriers, no peer loads.  No trailing barrier is needed: a peer can only start pushing step k+1 after it has
+// seen this rank's second flag of step k, which is sent after this rank finished reading its receive area.
+// The receive area is the second half of the IPC allocation (mc_p2p_create allocates 2 x bytes).
+__global__ void __launch_bounds__(P2P_THREADS) p2p_allreduce_push_kernel(P2PParams p, int64_t off4, int64_t n4, int64_t recv4,
+                                                                         float scale) {
+  const int W = p.world, R = p.rank;
+  const int64_t chunk = (n4 + W - 1) / W;
+  const int64_t lane = (int64_t)blockIdx.x * P2P_THREADS + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * P2P_THREADS;
+  float4* mine = reinterpret_cast<float4*>(p.bufs[R]) + off4;
+  constexpr int U = 4;
+  for (int d = 1; d < W; ++d) {
+    const int q = (R + d) % W;                 // start at a different peer on every rank
+    const int64_t lo = (int64_t)q * chunk, hi = min(n4, lo + chunk);
+    float4* dst = reinterpret_cast<float4*>(p.bufs[q]) + recv4 + off4 + (int64_t)R * chunk - lo;
+    int64_t i = lo + lane;
+    for (; i + (U - 1) * stride < hi; i += U * stride) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) v[u] = mine[i + u * stride];
+#pragma unroll
+      for (int u = 0; u < U; ++u) dst[i + u * stride] = v[u];
+    }
+    for (; i < hi; i += stride) dst[i] = mine[i];
+  }
+  p2p_block_barrier(p);
+  {
+    const int64_t lo = (int64_t)R * chunk, hi = min(n4, lo + chunk);
+    const float4* recv = reinterpret_cast<const float4*>(p.bufs[R]) + recv4 + off4 - lo;
+    for (int64_t i = lo + lane; i < hi; i += stride) {
+      float4 acc = (R == 0) ? mine[i] : __ldcv(recv + i);
+      for (int s = 1; s < W; ++s) {
+        const float4 v = (s == R) ? mine[i] : __ldcv(recv + (int64_t)s * chunk + i);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+      mine[i] = acc;
+      for (int d = 1; d < W; ++d) {
+        const int q = (R + d) % W;
+        (reinterpret_cast<float4*>(p.bufs[q]) + off4)[i] = acc;
+      }
+    }
+  }
+  p2p_block_barrier(p);
+}
+
 struct P2PState {
   bool active = false;
   int rank = 0, world = 1;
@@ -197,6 +251,7 @@ struct P2PState {
   uint32_t* flags = nullptr;
   void* peer_data[P2P_MAX_WORLD] = {};
   void* peer_flags[P2P_MAX_WORLD] = {};
+  size_t recv_offset = 0;            // bytes from the window base to the receive area of the push kernel
   P2PParams params;
   int* err_host = nullptr;
 } g_p2p;
@@ -209,7 +264,11 @@ int p2p_allreduce(float* buf, int64_t n, float scale) {
   if (blocks < 1) blocks = 1;
   const int64_t cap = sm_count() < P2P_MAX_BLOCKS ? sm_count() : P2P_MAX_BLOCKS;
   if (blocks > cap) blocks = cap;
-  p2p_allreduce_kernel<<<(unsigned)blocks, P2P_THREADS, 0, stream()>>>(g_p2p.params, off4, n4, scale);
+  static int push = -1;
+  if (push < 0) { const char* e = getenv("MINPY_P2P_PUSH"); push = (e && e[0] == '0') ? 0 : 1; }
+  if (push) p2p_allreduce_push_kernel<<<(unsigned)blocks, P2P_THREADS, 0, stream()>>>(g_p2p.params, off4, n4,
+                                                                                  (int64_t)(g_p2p.recv_offset / 16), scale);
+  else p2p_allreduce_kernel<<<(unsigned)blocks, P2P_THREADS, 0, stream()>>>(g_p2p.params, off4, n4, scale);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_error("p2p_allreduce_kernel launch failed: %s", cudaGetErrorString(e)); return 1; }
   count_launch();
@@ -285,8 +344,10 @@ int mc_p2p_create(int rank, int world, size_t bytes, void* handles128) {
   MC_REQUIRE(!g_p2p.base, "mc_p2p_create called twice");
   MC_REQUIRE(sizeof(cudaIpcMemHandle_t) == 64, "unexpected IPC handle size");
   bytes = (bytes + 4095) & ~(size_t)4095;
-  MC_CHECK(cudaMalloc((void**)&g_p2p.base, bytes));
-  MC_CHECK(cudaMemset(g_p2p.base, 0, bytes));
+  // [window: bytes][receive area of the push kernel: bytes + slack for the rounded-up slices]
+  g_p2p.recv_offset = bytes;
+  MC_CHECK(cudaMalloc((void**)&g_p2p.base, 2 * bytes + 4096));
+  MC_CHECK(cudaMemset(g_p2p.base, 0, 2 * bytes + 4096));
   const size_t flag_bytes = sizeof(uint32_t) * P2P_MAX_BLOCKS * (P2P_MAX_WORLD + 1);   // flags + local counters
   MC_CHECK(cudaMalloc((void**)&g_p2p.flags, flag_bytes));
   MC_CHECK(cudaMemset(g_p2p.flags, 0, flag_bytes));
