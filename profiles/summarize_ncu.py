@@ -58,6 +58,39 @@ def full(path):
                 print('    %-66s %16s %s' % (m, row[i], units[i]))
 
 
+def fullcsv(path, limit=40):
+    """Compact table from the raw CSV page of an `ncu --set full` report (written on the GPU box:
+    `ncu -i x.ncu-rep --page raw --csv`): one line per launch."""
+    rows = list(csv.reader(open(path)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    ki = hdr.index('Kernel Name')
+
+    def col(name):
+        return hdr.index(name) if name in hdr else None
+    cols = [('us', 'gpu__time_duration.sum'), ('grid', 'launch__grid_size'), ('block', 'launch__block_size'),
+            ('regs', 'launch__registers_per_thread'), ('tensor%', 'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active'),
+            ('dramR_MB', 'dram__bytes_read.sum'), ('dramW_MB', 'dram__bytes_write.sum'),
+            ('dram%', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed'),
+            ('l2%', 'lts__throughput.avg.pct_of_peak_sustained_elapsed'), ('sm%', 'sm__throughput.avg.pct_of_peak_sustained_elapsed'),
+            ('warps%', 'sm__warps_active.avg.pct_of_peak_sustained_active')]
+    scale = {'byte': 1e-6, 'Kbyte': 1e-3, 'Mbyte': 1.0, 'Gbyte': 1e3, 'ns': 1e-3, 'us': 1.0, 'ms': 1e3, 'usecond': 1.0, 'nsecond': 1e-3, 'msecond': 1e3}
+    print('# ncu --set full --clock-control none (raw page): %s' % path)
+    print('%-46s' % 'kernel' + ''.join('%10s' % c[0] for c in cols))
+    for row in data[:limit]:
+        name = re.sub(r'<.*', '', re.sub(r'\(.*', '', row[ki])).replace('void ', '')[-46:]
+        out = '%-46s' % name
+        for label, metric in cols:
+            i = col(metric)
+            if i is None or row[i] == '':
+                out += '%10s' % '-'
+                continue
+            v = float(row[i].replace(',', ''))
+            if label in ('us', 'dramR_MB', 'dramW_MB'):
+                v *= scale.get(units[i], 1.0)
+            out += '%10.2f' % v if label not in ('grid', 'block', 'regs') else '%10d' % v
+        print(out)
+
+
 def traffic(path, workload, family, calls):
     """dram bytes (read + write) of every launch in an `ncu --set full` capture that covers `calls`
     library calls of `family`, averaged per call -> profiles/traffic.json (read by bench.py)."""
@@ -92,4 +125,4 @@ if __name__ == '__main__':
     if sys.argv[1] == 'traffic':
         traffic(sys.argv[2], sys.argv[3], sys.argv[4], sys.argv[5])
     else:
-        {'launches': launches, 'full': full}[sys.argv[1]](sys.argv[2])
+        {'launches': launches, 'full': full, 'fullcsv': fullcsv}[sys.argv[1]](sys.argv[2])
