@@ -80,14 +80,14 @@ def _init_native_comm(rank, world):
 def _init_p2p_window(rank, world):
     """Peer-memory window for the gradient bucket (csrc/comm.cu, two-shot all-reduce over NVLink peer
     loads): every rank allocates it, the IPC handles travel through torch.distributed, and the window
-    is used only if EVERY rank could map every peer.  MINPY_P2P_ALLREDUCE: 'auto' (default) uses the
-    window at world size 2, where it is the faster exchange inside the step (mlp_c3 0.400 -> 0.384 ms,
-    profiles/r1z/n2); at 4 ranks it ties with NCCL in the step and loses alone (73 vs 52 us for 9.5 MB,
-    profiles/r1z/n4), so 3..8 ranks need an explicit '1'; '0' always keeps NCCL.
+    is used only if EVERY rank could map every peer.  MINPY_P2P_ALLREDUCE: 'auto' (default) and '1' use the
+    window at every world size 2..8 -- with the push kernel (round 2) it beats NCCL alone and inside the step
+    (9.5 MB: 32 vs 48 us at 2 ranks, 44 vs 52 us at 4; mlp_c3 step 0.2195 vs 0.2467 ms at 2 ranks, 0.2303 vs
+    0.2518 at 4: profiles/r2n2b, r2n4; the round-1 pull kernel only paid off at 2 ranks); '0' keeps NCCL.
     MINPY_P2P_MB sizes the window (default 64 MB, buckets beyond it go to NCCL)."""
     _state['p2p'] = None
     mode = os.environ.get('MINPY_P2P_ALLREDUCE', 'auto')
-    if world < 2 or world > 8 or mode == '0' or (mode != '1' and world != 2):
+    if world < 2 or world > 8 or mode == '0':
         return
     from .ops import L
     lib = L()

@@ -114,9 +114,9 @@ def test_two_rank_data_parallel_matches_full_batch(tmp_path):
         minpy.set_global_policy('prefer_cuda')
 
 
-def test_peer_memory_window_is_opt_in_beyond_two_ranks(monkeypatch):
-    """_init_p2p_window: 'auto' uses the window only at world size 2 (where it was measured faster inside
-    the step), '0' never, and outside 2..8 ranks never -- decided before the library is touched."""
+def test_peer_memory_window_gating(monkeypatch):
+    """_init_p2p_window: '0' never uses the window, and outside 2..8 ranks it is never used -- decided before
+    the library is touched ('auto' uses it at every world size 2..8 since the push kernel, profiles/r2n4)."""
     from minpy_b200 import parallel
 
     class Boom(object):
@@ -126,7 +126,7 @@ def test_peer_memory_window_is_opt_in_beyond_two_ranks(monkeypatch):
     import minpy_b200.ops as ops
     monkeypatch.setattr(ops, 'L', lambda: Boom())
     monkeypatch.setattr(parallel, '_dist', lambda: Boom())
-    for world, mode in ((4, 'auto'), (8, 'auto'), (2, '0'), (9, '1'), (1, '1')):
+    for world, mode in ((4, '0'), (9, 'auto'), (2, '0'), (9, '1'), (1, '1'), (1, 'auto')):
         if mode == 'auto':
             monkeypatch.delenv('MINPY_P2P_ALLREDUCE', raising=False)
         else:
