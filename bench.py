@@ -248,6 +248,11 @@ def _work_of(name, a):
             return 0.0, 28.0 * _i(a[12])
         if name in ('mc_memcpy_d2d', 'mc_memset'):
             return 0.0, (2.0 if name == 'mc_memcpy_d2d' else 1.0) * _i(a[2])
+        if name == 'mc_conv2d_nhwc_fwd_pool':
+            N, C, H, W, Cp, wpad, F, Fp, KH, KW, pad = [_i(v) for v in a[5:16]]
+            OH, OW = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+            return (2.0 * N * OH * OW * F * C * KH * KW,
+                    4.0 * (N * H * W * Cp + F * C * KH * KW) + 5.0 * N * (OH // 2) * (OW // 2) * Fp)
         if name in ('mc_conv2d_nhwc_fwd', 'mc_conv2d_nhwc_wgrad'):
             N, C, H, W, Cp, wpad, F, Fp, KH, KW, pad = [_i(v) for v in a[4:15]]
             OH, OW = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1

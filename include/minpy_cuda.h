@@ -390,6 +390,15 @@ int mc_conv2d_dgrad(const float* dy, const float* w, float* dx,
 int mc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* dbias,
                     int64_t N, int64_t C, int64_t H, int64_t W, int64_t F, int64_t KH, int64_t KW,
                     int64_t stride, int64_t pad, int precision);
+/* Convolution + bias (+ relu) + 2x2 / stride-2 max pooling in one kernel (examples/nn/cnn.py:32-40: Convolution ->
+ * Activation('relu') -> Pooling(max, 2x2 / 2)): only the pooled tensor y_pooled (N, OH/2, OW/2, Fp) and the window
+ * index (idx_u8, same shape, 0..3 = kh*2 + kw of the first maximum; may be NULL) are written -- the format
+ * mc_maxpool2d_nhwc_fwd produces, so mc_maxpool2d_nhwc_bwd is its VJP.  Shapes: OH, OW even, OW <= 32, F % 32 == 0,
+ * Fp == F (mc_conv2d_nhwc_pool_supported). */
+int mc_conv2d_nhwc_pool_supported(int64_t OH, int64_t OW, int64_t F, int64_t Fp, int* ok);
+int mc_conv2d_nhwc_fwd_pool(const float* x, const float* w, const float* bias, float* y_pooled, uint8_t* idx_u8,
+                            int64_t N, int64_t C, int64_t H, int64_t W, int64_t Cp, int64_t wpad,
+                            int64_t F, int64_t Fp, int64_t KH, int64_t KW, int64_t pad, int relu);
 /* Channels-last (NHWC) convolution path -- what the tensor-core kernels natively consume.  TMA needs
  * the innermost box coordinate 16-byte aligned, so the filter-tap shifts must fall on outer
  * dimensions: activations are (N, H, W, Cp) with Cp = channel pitch, a multiple of 4.  The symbol

@@ -71,6 +71,12 @@ struct ConvFwdParams {
   long long* dbg;        // MC_CONV_DBG: clock64 stamps of CTA 0 [role][tile][slot] (nullptr = off)
   int halo;              // stage = one channel block of a whole tile WITH its filter halo (see below)
   uint32_t copy_bytes;   // halo mode: bytes of one column-shifted copy, (box_h + TH - 1) * bw * 128
+  // pool != 0: the epilogue applies bias (+ relu) and a 2x2 / stride-2 max pooling and stores ONLY the pooled
+  // tensor y (N, OH/2, OW/2, ldy) and the window index (0..3 = kh*2 + kw of the first maximum, the format of
+  // maxpool_nhwc_fwd) -- the full-resolution activation never goes to memory.
+  int pool;
+  uint8_t* pidx;         // (N, OH/2, OW/2, ldy) bytes, or nullptr (inference)
+  uint32_t pool_smem;    // byte offset (from the 1024-aligned base) of the cross-warp exchange area (OWv == 32 only)
 };
 
 // Persistent: grid = min(#tiles, #SMs); a CTA walks tiles t = blockIdx.x, += gridDim.x, where a
@@ -322,6 +328,83 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
       for (int c0 = 0; c0 < p.BN; c0 += 32) {
         float v[32];
         tmem_ld32(tacc + (uint32_t)c0, v);
+        if (p.pool) {
+          // ---- bias, relu, 2x2 max pooling: candidates in window order (0,0) (0,1) (1,0) (1,1), first maximum wins
+          const int f0 = n0 + c0;
+          uint32_t kk[8];                      // window index of the winner so far, one byte per channel
+#pragma unroll
+          for (int j = 0; j < 8; ++j) kk[j] = 0u;
+          const bool odd_col = (ow & 1) != 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float a = v[j];
+            if (p.bias) a += __ldg(p.bias + f0 + j);
+            if (p.relu) a = (a != a) ? a : fmaxf(a, 0.f);
+            if (!live) a = -INFINITY;
+            const float b = __shfl_xor_sync(0xffffffffu, a, 1);           // the horizontal neighbour
+            // even column: (a = kw 0, b = kw 1); the odd lane computes the same pair mirrored and is not used
+            const float left = odd_col ? b : a, right = odd_col ? a : b;
+            const bool take_right = (right > left) || (right != right && left == left);
+            v[j] = take_right ? right : left;
+            kk[j >> 2] |= (take_right ? 1u : 0u) << (8 * (j & 3));
+          }
+          const bool within_warp = p.g.OWv < 32;
+          bool top;                             // this lane holds the TOP row of its window
+          if (within_warp) {
+            const int rowbit = 1 << p.g.owv_shift;
+            top = (lane & rowbit) == 0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float other = __shfl_xor_sync(0xffffffffu, v[j], rowbit);
+              const uint32_t ko = __shfl_xor_sync(0xffffffffu, (kk[j >> 2] >> (8 * (j & 3))) & 0xffu, rowbit);
+              const float tv = top ? v[j] : other, bv = top ? other : v[j];
+              const uint32_t tk = top ? ((kk[j >> 2] >> (8 * (j & 3))) & 0xffu) : ko;
+              const uint32_t bk = (top ? ko : ((kk[j >> 2] >> (8 * (j & 3))) & 0xffu)) + 2u;
+              const bool take_bottom = (bv > tv) || (bv != bv && tv == tv);
+              v[j] = take_bottom ? bv : tv;
+              kk[j >> 2] = (kk[j >> 2] & ~(0xffu << (8 * (j & 3)))) | ((take_bottom ? bk : tk) << (8 * (j & 3)));
+            }
+          } else {
+            // rows of a window live in two warps (quarter q and q ^ 1): the bottom warp parks its horizontal
+            // winners in shared memory, the top warp finishes.  Two named barriers per chunk (data ready / buffer free).
+            top = (quarter & 1) == 0;
+            const int pair = grp * 2 + (quarter >> 1);
+            float* xm = reinterpret_cast<float*>(smem_raw + ((smem_base - smem_u32(smem_raw)) + p.pool_smem)) + pair * (16 * 33 + 16 * 9);
+            uint32_t* xk = reinterpret_cast<uint32_t*>(xm + 16 * 33);
+            if (!top && !odd_col) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) xm[(lane >> 1) * 33 + j] = v[j];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) xk[(lane >> 1) * 9 + j] = kk[j];
+            }
+            asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
+            if (top && !odd_col) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const float bv = xm[(lane >> 1) * 33 + j];
+                const uint32_t bk = ((xk[(lane >> 1) * 9 + (j >> 2)] >> (8 * (j & 3))) & 0xffu) + 2u;
+                const uint32_t tk = (kk[j >> 2] >> (8 * (j & 3))) & 0xffu;
+                const bool take_bottom = (bv > v[j]) || (bv != bv && v[j] == v[j]);
+                v[j] = take_bottom ? bv : v[j];
+                kk[j >> 2] = (kk[j >> 2] & ~(0xffu << (8 * (j & 3)))) | ((take_bottom ? bk : tk) << (8 * (j & 3)));
+              }
+            }
+            asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
+          }
+          if (live && top && !odd_col) {
+            const int POH = p.g.OH >> 1, POW = p.g.OW >> 1;
+            const int64_t at = (((int64_t)n * POH + (oh >> 1)) * POW + (ow >> 1)) * p.ldy + f0;
+            float* __restrict__ dst = p.y + at;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            if (p.pidx) {
+              uint4* __restrict__ di = reinterpret_cast<uint4*>(p.pidx + at);
+              di[0] = make_uint4(kk[0], kk[1], kk[2], kk[3]);
+              di[1] = make_uint4(kk[4], kk[5], kk[6], kk[7]);
+            }
+          }
+          continue;
+        }
         if (live) {
           const int f0 = n0 + c0;
           if (vec_ok && f0 + 32 <= p.Nout) {
@@ -1000,10 +1083,21 @@ static int set_max_smem(const void* fn, const char* what) {
 // y (N, OH, OW, ldy) = conv over x (N, H, Wt, Cp) with `Kreal` contraction channels per pixel.
 // mode 0 forward, 1 forward merged (x physically W-padded by `pad`), 2 dgrad (x := dy, w flipped,
 // `pad` already K-1-pad).  Nout = output channels (F for forward, C for dgrad).
+// 2x2 / stride-2 max pooling in the epilogue is possible when a pooling window never straddles two tiles
+// and the channel pitch is a whole number of 32-channel epilogue chunks
+static bool conv_pool_ok(int OH, int OW, int Nout, int ldy) {
+  if ((OH & 1) || (OW & 1) || OW > 32 || (Nout & 31) || ldy != Nout) return false;
+  const ConvGeom g = make_geom(1, OH, OW, true);
+  return g.OWv < 32 ? (g.bh % 2 == 0) : (g.OWv == 32 && g.cpi % 4 == 0);
+}
+
 int conv_igemm(const float* x, const float* w, const float* bias, float* y, int N, int H, int Wt, int Cp, int Kreal,
-               int Nout, int ldy, int F, int C, int KH, int KW, int pad, int OH, int OW, int relu, int mode) {
+               int Nout, int ldy, int F, int C, int KH, int KW, int pad, int OH, int OW, int relu, int mode,
+               int pool = 0, uint8_t* pidx = nullptr) {
   ConvFwdParams p;
   p.g = make_geom(N, OH, OW, true);
+  p.pool = pool; p.pidx = pidx; p.pool_smem = 0;
+  if (pool && !conv_pool_ok(OH, OW, Nout, ldy)) { set_error("conv_igemm: shape outside the pooled epilogue"); return 2; }
   int K, Wdim;                     // contraction length per tap; number of start pixels along W
   if (mode == 1) { p.g.TH = KH; p.g.TW = 1; p.g.dh0 = -pad; p.g.dw0 = 0; K = KW * Cp; Wdim = Wt - KW + 1; }
   else { p.g.TH = KH; p.g.TW = KW; p.g.dh0 = -pad; p.g.dw0 = -pad; K = Kreal; Wdim = Wt; }
@@ -1041,7 +1135,12 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   if (stages > 8) stages = 8;
   if (stages < 1) stages = 1;
   p.stages = stages;
-  const size_t smem = (p.wres ? w_bytes : 0) + stages * stage_bytes + (2 * stages + 2 * nacc + 1) * 8 + 16 + 1024;
+  size_t smem = (p.wres ? w_bytes : 0) + stages * stage_bytes + (2 * stages + 2 * nacc + 1) * 8 + 16 + 1024;
+  if (pool && p.g.OWv >= 32) {          // cross-warp exchange area of the pooled epilogue: 4 warp pairs
+    const size_t used = (p.wres ? w_bytes : 0) + stages * stage_bytes + (2 * stages + 2 * nacc + 1) * 8 + 16;
+    p.pool_smem = (uint32_t)((used + 15) & ~(size_t)15);
+    smem = p.pool_smem + 4 * (16 * 33 + 16 * 9) * 4 + 1024;
+  }
 
   CUtensorMap tmX, tmW;
   int rc = make_act_tmap(&tmX, x, N, H, Wt, Cp, K, Wdim, p.g.bw,
@@ -1294,6 +1393,26 @@ int mc_nhwc_to_nchw(const float* x, float* y, int64_t N, int64_t C, int64_t H, i
   if (N * H * W * C == 0) return 0;
   MC_REQUIRE(N * H <= 2147483647LL, "N*H exceeds the grid limit");
   return tc::nhwc_to_nchw(x, y, (int)N, (int)C, (int)H, (int)W, (int)Cp);
+}
+
+int mc_conv2d_nhwc_pool_supported(int64_t OH, int64_t OW, int64_t F, int64_t Fp, int* ok) {
+  *ok = tc::conv_pool_ok((int)OH, (int)OW, (int)F, (int)Fp) ? 1 : 0;
+  return 0;
+}
+
+int mc_conv2d_nhwc_fwd_pool(const float* x, const float* w, const float* bias, float* y_pooled, uint8_t* idx_u8, int64_t N,
+                            int64_t C, int64_t H, int64_t W, int64_t Cp, int64_t wpad, int64_t F, int64_t Fp, int64_t KH,
+                            int64_t KW, int64_t pad, int relu) {
+  if (int rc = check_nhwc(x, y_pooled, y_pooled, Cp, Fp, "mc_conv2d_nhwc_fwd_pool")) return rc;
+  const int64_t OH = H + 2 * pad - KH + 1, OW = W + 2 * pad - KW + 1;
+  MC_REQUIRE(OH > 0 && OW > 0, "kernel larger than padded input");
+  MC_REQUIRE(wpad == 0 || merged_mode(KW, Cp, wpad, pad), "a W-padded input needs wpad == pad and KW*Cp <= 32");
+  MC_REQUIRE(tc::conv_pool_ok((int)OH, (int)OW, (int)F, (int)Fp), "shape outside the pooled epilogue (mc_conv2d_nhwc_pool_supported)");
+  MC_REQUIRE(idx_u8 == nullptr || aligned16(idx_u8), "idx must be 16-byte aligned");
+  if (N == 0) return 0;
+  const int mode = merged_mode(KW, Cp, wpad, pad) ? 1 : 0;
+  return tc::conv_igemm(x, w, bias, y_pooled, (int)N, (int)H, (int)(W + 2 * wpad), (int)Cp, (int)C, (int)F, (int)Fp, (int)F,
+                        (int)C, (int)KH, (int)KW, (int)pad, (int)OH, (int)OW, relu, mode, 1, idx_u8);
 }
 
 int mc_conv2d_nhwc_fwd(const float* x, const float* w, const float* bias, float* y, int64_t N, int64_t C, int64_t H,

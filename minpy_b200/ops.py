@@ -803,6 +803,31 @@ def conv2d_nhwc_fwd(a, w, b=None, pad=0, relu=False):
     return Nhwc(y, a.N, F, OH, OW, Fp)
 
 
+def conv_pool_fusable(a, w, pad):
+    """mc_conv2d_nhwc_pool_supported, restated: conv output even-sized, at most 32 wide, F a multiple of 32."""
+    F, C, KH, KW = w.shape
+    OH, OW = a.H + 2 * pad - KH + 1, a.W + 2 * pad - KW + 1
+    return OH > 0 and OW > 0 and OH % 2 == 0 and OW % 2 == 0 and OW <= 32 and F % 32 == 0
+
+
+def conv2d_nhwc_fwd_pool(a, w, b=None, pad=0, relu=True, want_idx=True):
+    """conv -> (relu) -> 2x2 / 2 max pooling in ONE kernel: returns (pooled Nhwc, uint8 window index or None,
+    `like` = an Nhwc describing the un-pooled convolution output, which is never stored)."""
+    lib = L()
+    w = as_f32(w)
+    F, C, KH, KW = w.shape
+    if C != a.C:
+        raise ValueError('conv2d: input has %d channels, filter expects %d' % (a.C, C))
+    OH, OW = a.H + 2 * pad - KH + 1, a.W + 2 * pad - KW + 1
+    y = CudaArray.empty((a.N, OH // 2, OW // 2, F))
+    idx = CudaArray.empty((a.N, OH // 2, OW // 2, F), np.dtype('uint8')) if want_idx else None
+    if y.size:
+        lib.mc_conv2d_nhwc_fwd_pool(a.data.ptr, w.ptr, as_f32(b).ptr if b is not None else None, y.ptr,
+                                    idx.ptr if idx is not None else None, a.N, C, a.H, a.W, a.Cp, a.wpad, F, F, KH, KW, pad,
+                                    1 if relu else 0)
+    return Nhwc(y, a.N, F, OH // 2, OW // 2, F), idx, Nhwc(None, a.N, F, OH, OW, F)
+
+
 def conv2d_nhwc_bwd(a, w, dy, pad=0, need_dx=True, need_db=True):
     """(dx Nhwc or None, dw, db) for y = conv(a, w); dy is the Nhwc gradient of y."""
     lib = L()

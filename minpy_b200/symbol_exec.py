@@ -22,6 +22,17 @@ from .cuda_array import CudaArray, _F32, _I32
 from .lazy import concrete
 
 _GT0 = 'MC_VJP_GT0_A'
+import os as _os
+_POOL_FUSE = _os.environ.get('MINPY_CONV_POOL_FUSE', '1') != '0'
+
+
+class _Pooled(object):
+    """Value of a Convolution (+ fused relu) node whose 2x2 max pooling ran in the convolution's epilogue:
+    the un-pooled activation does not exist; the Pooling node downstream takes `y` / `idx` as its own."""
+    __slots__ = ('y', 'idx', 'like')
+
+    def __init__(self, y, idx, like):
+        self.y, self.idx, self.like = y, idx, like
 
 # test hook: when a list, `Plan.forward` appends the (NCHW, host) output of every Convolution node
 # (post-relu when the activation is fused) -- the full-size parity tests read the device's relu /
@@ -85,6 +96,15 @@ class Plan(object):
                 if src.op == 'Activation' and consumers.get(id(src), 0) == 1 and \
                         any(act is src for act in self.fused_relu.values()):
                     self.pool_masks_relu[id(node)] = src.inputs[0]
+        # Convolution -> relu -> max pooling 2x2 / 2 (every link with a single consumer): the pooling runs in the
+        # convolution's epilogue when the shapes allow (decided per forward call)
+        self.fused_pool = {}
+        for node in self.order:
+            if id(node) in self.pool_masks_relu:
+                a = node.attrs
+                if a['pool_type'] == 'max' and tuple(a['kernel']) == (2, 2) and tuple(a['stride']) == (2, 2) and \
+                        tuple(a['pad']) == (0, 0) and not a['global_pool']:
+                    self.fused_pool[id(self.pool_masks_relu[id(node)])] = node
         # which nodes need a gradient: anything downstream of a non-input argument
         self.needs_grad = {}
         for node in self.order:
@@ -128,12 +148,15 @@ class Plan(object):
                     # consecutive conv / relu / pool nodes)
                     if not isinstance(x, ops.Nhwc):
                         x = ops.to_nhwc(x, pad if ops.conv_merged_ok(w.shape[1], w.shape[3]) else 0)
-                    values[key] = ops.conv2d_nhwc_fwd(x, w, b, pad, relu=relu)
+                    if _POOL_FUSE and trace is None and key in self.fused_pool and ops.conv_pool_fusable(x, w, pad):
+                        values[key] = _Pooled(*ops.conv2d_nhwc_fwd_pool(x, w, b, pad, relu=True, want_idx=train))
+                    else:
+                        values[key] = ops.conv2d_nhwc_fwd(x, w, b, pad, relu=relu)
                 else:
                     x = _nchw(x)
                     values[key] = ops.conv2d_fwd(x, w, b, stride, pad, relu=relu)
                 saved[key] = (x, w)
-                if trace is not None:
+                if trace is not None:       # (the pooled epilogue is off while tracing: the test wants the un-pooled output)
                     trace.append(_nchw(values[key]).asnumpy())
             elif node.op == 'Activation':
                 if key in skip_relu:
@@ -150,7 +173,10 @@ class Plan(object):
                 k, stride = a['kernel'], _sq(a['stride'], 'stride')
                 if a['global_pool']:
                     k, stride = tuple(_nchw(x).shape[2:]), 1
-                if a['pool_type'] == 'avg':
+                if isinstance(x, _Pooled):              # already pooled by the producing convolution
+                    values[key] = x.y
+                    saved[key] = (x.idx, x.like)
+                elif a['pool_type'] == 'avg':
                     x = _nchw(x)
                     values[key] = ops.avgpool2d_fwd(x, k, stride)
                     saved[key] = ('avg', x.shape, k, stride)
@@ -246,6 +272,8 @@ class Plan(object):
             if g is None or not want(node):
                 return
             like = values.get(id(node))
+            if isinstance(like, _Pooled):
+                like = like.like                      # layout / shape of the un-pooled activation
             if isinstance(like, ops.Nhwc) and not isinstance(g, ops.Nhwc):
                 g = ops.to_nhwc(g.reshape(like.shape))
             elif isinstance(g, ops.Nhwc) and not isinstance(like, ops.Nhwc):

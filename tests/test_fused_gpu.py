@@ -401,3 +401,66 @@ def test_classifier_head_kernel_matches_oracle_and_composition(cuda, rows, K, C)
             assert rel(a, orc.raw(o)) <= 2e-5 and rel(b2, orc.raw(o)) <= 2e-5
     finally:
         minpy.set_global_policy('prefer_cuda')
+
+
+@pytest.mark.parametrize('N,C,H,F,K,pad', [(8, 3, 32, 32, 3, 1), (4, 32, 16, 64, 3, 1), (4, 64, 8, 128, 3, 1), (6, 3, 32, 32, 7, 0),
+                                           (3, 16, 12, 32, 3, 1), (2, 8, 20, 64, 5, 2), (5, 4, 6, 32, 3, 1)])
+def test_conv_relu_pool_epilogue_equals_conv_then_pool(cuda, N, C, H, F, K, pad):
+    """mc_conv2d_nhwc_fwd_pool against mc_conv2d_nhwc_fwd (+relu) followed by mc_maxpool2d_nhwc_fwd: the same MMAs,
+    so pooled values AND window indices must be bit-identical; and the symbol path with / without the fusion gives
+    the same loss-side gradients (the pooling VJP consumes the index either way)."""
+    rng = np.random.RandomState(N * 100 + H)
+    x = rng.randn(N, C, H, H).astype(np.float32)
+    w = (rng.randn(F, C, K, K) * 0.2).astype(np.float32)
+    b = rng.randn(F).astype(np.float32) * 0.1
+    x[0, :, :2, :2] = 0.0                       # a window of exact ties
+    a = cuda.to_nhwc(up(x), pad if cuda.conv_merged_ok(C, K) else 0)
+    W, B = up(w), up(b)
+    assert cuda.conv_pool_fusable(a, W, pad)
+    full = cuda.conv2d_nhwc_fwd(a, W, B, pad, relu=True)
+    y1, i1 = cuda.maxpool2d_nhwc_fwd(full, 2, want_idx=True)
+    y2, i2, like = cuda.conv2d_nhwc_fwd_pool(a, W, B, pad, relu=True, want_idx=True)
+    assert (like.N, like.C, like.H, like.W) == (full.N, full.C, full.H, full.W)
+    assert np.array_equal(y1.data.asnumpy(), y2.data.asnumpy())
+    assert np.array_equal(i1.asnumpy(), i2.asnumpy())
+    y3, i3, _ = cuda.conv2d_nhwc_fwd_pool(a, W, B, pad, relu=True, want_idx=False)
+    assert i3 is None and np.array_equal(y3.data.asnumpy(), y1.data.asnumpy())
+    # against the float64 oracle (TF32 contraction: 1e-2 of the largest entry)
+    want = orc.raw(orc.maxpool2d(orc.relu_mx(orc.conv2d(x.astype(np.float64), w.astype(np.float64), b.astype(np.float64), 1, pad)), 2, 2))
+    assert rel(cuda.to_nchw(y2).asnumpy(), want) <= 1e-2
+
+
+def test_conv_pool_fusion_in_the_symbol_path_matches_unfused():
+    """ConvNet C4 in miniature through core.Function: gradients with MINPY_CONV_POOL_FUSE on and off are equal."""
+    import minpy
+    minpy.set_global_policy('only_cuda')
+    try:
+        import minpy.numpy as mnp
+        from minpy import core
+        from minpy_b200 import workloads, symbol_exec
+        rng = np.random.RandomState(5)
+        X = rng.randn(16, 3, 32, 32).astype(np.float32)
+        Y = rng.randint(0, 10, 16)
+        res = []
+        for fuse in (True, False):
+            saved, symbol_exec._POOL_FUSE = symbol_exec._POOL_FUSE, fuse       # pylint: disable=protected-access
+            try:
+                model = workloads.ConvNet(batch=16)
+                init = workloads.init_params(model, 3, scale=0.1)
+                names = sorted(init)
+                for k in names:
+                    model.params[k] = mnp.array(init[k])
+
+                def loss(*ps):
+                    for k, pv in zip(names, ps):
+                        model.params[k] = pv
+                    return model.loss(model.forward(mnp.array(X), 'train'), mnp.array(Y))
+                g, v = core.grad_and_loss(loss, argnum=range(len(names)))(*[model.params[k] for k in names])
+                res.append((float(v), [a.asnumpy() for a in g]))
+            finally:
+                symbol_exec._POOL_FUSE = saved                                  # pylint: disable=protected-access
+        assert res[0][0] == res[1][0]
+        for a, b in zip(res[0][1], res[1][1]):
+            assert np.array_equal(a, b)
+    finally:
+        minpy.set_global_policy('prefer_cuda')
