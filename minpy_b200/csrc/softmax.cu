@@ -287,114 +287,251 @@ __global__ void __launch_bounds__(CE_THREADS) softmax_ce_small_kernel(const floa
 // head's input, dh = dlogits . W^T -- what affine + softmax_loss + the two VJPs compute in three launches on the
 // chain (skinny GEMM, loss kernel, skinny GEMM).  One warp per row; W (K x C, C <= 16) lives in shared memory;
 // FP32 throughout, like the skinny kernels it replaces.  The block that finishes last sums the row losses.
-constexpr int HEAD_THREADS = 256;
+constexpr int HEAD_ROWS = 8;      // rows per block
+constexpr int HEAD_RPW = 4;       // rows a warp carries through its chunks of K
+constexpr int HEAD_RG = HEAD_ROWS / HEAD_RPW;
+constexpr int HEAD_SLOTS = 8;     // warps that split K
+constexpr int HEAD_THREADS = 32 * HEAD_RG * HEAD_SLOTS;
 constexpr int HEAD_MAXC = 16;
+// tools/head_probe.sh builds a second library with -DMC_HEAD_PROBE: thread 0 of every block stamps %globaltimer
+// at the phase boundaries below.  Compiled out of libminpy_cuda.so.
+#ifdef MC_HEAD_PROBE
+__device__ unsigned long long g_head_probe[1024 * 8];
+#define HEAD_STAMP(i)                                                                   \
+  do {                                                                                  \
+    if (threadIdx.x == 0 && blockIdx.x < 1024) {                                        \
+      unsigned long long t_;                                                            \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                            \
+      g_head_probe[blockIdx.x * 8 + (i)] = t_;                                          \
+    }                                                                                   \
+  } while (0)
+extern "C" int mc_head_probe_read(unsigned long long* out) {
+  return cudaMemcpyFromSymbol(out, g_head_probe, sizeof(g_head_probe)) == cudaSuccess ? 0 : 1;
+}
+#else
+#define HEAD_STAMP(i)
+#endif
+// One row of W (C floats at w_s + f * C) into registers with the widest shared-memory loads its alignment allows.
+template <int C>
+__device__ __forceinline__ void head_load_w(const float* __restrict__ wr, float (&w)[C]) {
+  if constexpr (C % 4 == 0) {
+#pragma unroll
+    for (int c = 0; c < C; c += 4) {
+      const float4 v = *reinterpret_cast<const float4*>(wr + c);
+      w[c] = v.x, w[c + 1] = v.y, w[c + 2] = v.z, w[c + 3] = v.w;
+    }
+  } else if constexpr (C % 2 == 0) {
+#pragma unroll
+    for (int c = 0; c < C; c += 2) {
+      const float2 v = *reinterpret_cast<const float2*>(wr + c);
+      w[c] = v.x, w[c + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < C; ++c) w[c] = wr[c];
+  }
+}
+
+// Sum v[0..N) over the 32 lanes by halving: at each step a lane keeps one half of its values and trades the other
+// half with its partner, so N values cost about N shuffles instead of 5 N.  Afterwards the lane holds, in v[0..R),
+// the totals of the original indices base + i, for those below `limit` (R = N halved five times, rounding up).
+template <int N, int MASK>
+__device__ __forceinline__ void head_fold(float* v, int lane, int& base, int& limit) {
+  if constexpr (MASK >= 1) {
+    constexpr int H = (N + 1) / 2;
+    const bool upper = (lane & MASK) != 0;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const float lo = v[i];
+      const float hi = (i + H < N) ? v[i + H] : 0.f;
+      const float send = upper ? lo : hi;
+      const float keep = upper ? hi : lo;
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, MASK);
+    }
+    if (upper) base += H;
+    else limit = min(limit, base + H);
+    head_fold<H, MASK / 2>(v, lane, base, limit);
+  }
+}
+constexpr int head_fold_left(int n) {
+  for (int s = 0; s < 5; ++s) n = (n + 1) / 2;
+  return n;
+}
+
+// Layout of the work (profiles/r2l has the in-kernel phase timings that led here).  The first version gave each
+// row one warp and a run-time class count: every W element was a predicated scalar LDS feeding one FMA, and each
+// row re-read all of W from shared memory, twice (logits, then dh) -- 12.5 us at 1024 x 512 x 10, 27 us at K = 2048,
+// bound by LDS latency and then by shared-memory bandwidth.  Now: C is a template parameter (LDS.64 / LDS.128 rows
+// of W, no predicates); a warp owns 32-element chunks of K for FOUR rows at a time, so a W row read from shared
+// memory feeds 4 x C FMAs; the per-lane partial logits are folded across lanes by halving (head_fold), the eight
+// K-slots are summed in a fixed order by the warp that owns the row, which also does the softmax with one class
+// per lane; thread 0 takes the ticket while the other warps write dh.
+template <int C>
 __global__ void __launch_bounds__(HEAD_THREADS) head_softmax_kernel(const float* __restrict__ h, const float* __restrict__ W,
                                                                     const float* __restrict__ bias, const int32_t* __restrict__ labels,
                                                                     float* __restrict__ logits, float* __restrict__ dlogits,
                                                                     float* __restrict__ dh, float* __restrict__ loss,
-                                                                    float* __restrict__ rowloss, int* __restrict__ counter, int rows,
-                                                                    int K, int C, float inv_rows) {
-  extern __shared__ float w_s[];            // K * C
-  mc::pdl_sync();
-  __shared__ float red[32];
+                                                                    float* __restrict__ blockloss, int* __restrict__ counter, int rows,
+                                                                    int K, float inv_rows) {
+  extern __shared__ __align__(16) float w_s[];            // K * C
+  __shared__ __align__(16) float part[HEAD_SLOTS][HEAD_ROWS * HEAD_MAXC];
+  __shared__ __align__(16) float dls[HEAD_ROWS][HEAD_MAXC];
+  __shared__ float rl[HEAD_ROWS];
   __shared__ int s_last;
-  // Every global load of the kernel's first phase is issued before anything waits: the row of h this warp owns
-  // (16 elements per lane at a time, in registers) and the block's copy of W (float4, eight in flight per thread).
-  // The first two versions looped "load, use" and paid one L2 round trip per iteration: 14.5 us and 16.8 us for
-  // 1024 x 512 x 10 (profiles/r2i, r2j).
+  HEAD_STAMP(0);
+  mc::pdl_sync();
+  HEAD_STAMP(1);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int row = blockIdx.x * (HEAD_THREADS / 32) + warp;
-  const float* __restrict__ hr = h + (int64_t)(row < rows ? row : 0) * K;
-  float hv[16];
+  const int rg = warp % HEAD_RG, slot = warp / HEAD_RG;   // group of four rows, K-slot
+  const int row0 = blockIdx.x * HEAD_ROWS + rg * HEAD_RPW;
+  constexpr int PASS_CHUNKS = 4;                          // chunks of 32 a warp handles per pass
+  // what the softmax warps need later, fetched now
+  const int my_row = blockIdx.x * HEAD_ROWS + warp;
+  const bool owner = warp < HEAD_ROWS && my_row < rows;
+  const int lab = owner ? labels[my_row] : 0;
+  const float my_bias = (owner && bias && lane < C) ? __ldg(bias + lane) : 0.f;
+
+  auto load_h = [&](int pass, float (&hv)[HEAD_RPW * PASS_CHUNKS]) {
 #pragma unroll
-  for (int q = 0; q < 16; ++q) hv[q] = (lane + 32 * q < K) ? __ldg(hr + lane + 32 * q) : 0.f;
+    for (int j = 0; j < HEAD_RPW; ++j) {
+#pragma unroll
+      for (int i = 0; i < PASS_CHUNKS; ++i) {
+        const int f = ((pass * PASS_CHUNKS + i) * HEAD_SLOTS + slot) * 32 + lane;
+        hv[j * PASS_CHUNKS + i] = (row0 + j < rows && f < K) ? __ldg(h + (int64_t)(row0 + j) * K + f) : 0.f;
+      }
+    }
+  };
+  float hv[HEAD_RPW * PASS_CHUNKS];
+  load_h(0, hv);
   {
     const int n = K * C;
     if ((n & 3) == 0 && ((reinterpret_cast<uintptr_t>(W) & 15u) == 0)) {
       const float4* __restrict__ W4 = reinterpret_cast<const float4*>(W);
       float4* w4 = reinterpret_cast<float4*>(w_s);
-#pragma unroll 8
+#pragma unroll 4
       for (int i = threadIdx.x; i < (n >> 2); i += HEAD_THREADS) w4[i] = __ldg(W4 + i);
     } else {
-#pragma unroll 8
+#pragma unroll 4
       for (int i = threadIdx.x; i < n; i += HEAD_THREADS) w_s[i] = __ldg(W + i);
     }
   }
   __syncthreads();
-  if (row < rows) {
-    float acc[HEAD_MAXC];
+  HEAD_STAMP(2);
+  float acc[HEAD_RPW * C];
 #pragma unroll
-    for (int c = 0; c < HEAD_MAXC; ++c) acc[c] = 0.f;
-    for (int f0 = 0; f0 < K; f0 += 32 * 16) {            // 512 row elements per pass
-      if (f0 > 0) {
+  for (int i = 0; i < HEAD_RPW * C; ++i) acc[i] = 0.f;
+  const int npass = (K + 32 * HEAD_SLOTS * PASS_CHUNKS - 1) / (32 * HEAD_SLOTS * PASS_CHUNKS);
+  for (int pass = 0; pass < npass; ++pass) {
+    float hn[HEAD_RPW * PASS_CHUNKS];
+    if (pass + 1 < npass) load_h(pass + 1, hn);          // the next pass's slice of h is in flight during this one
 #pragma unroll
-        for (int q = 0; q < 16; ++q) hv[q] = (f0 + lane + 32 * q < K) ? __ldg(hr + f0 + lane + 32 * q) : 0.f;
+    for (int i = 0; i < PASS_CHUNKS; ++i) {
+      const int f = ((pass * PASS_CHUNKS + i) * HEAD_SLOTS + slot) * 32 + lane;
+      if (f - lane >= K) break;
+      float w[C];
+      if (f - lane + 32 <= K) {
+        head_load_w<C>(w_s + f * C, w);
+      } else {
+#pragma unroll
+        for (int c = 0; c < C; ++c) w[c] = (f < K) ? w_s[f * C + c] : 0.f;
       }
 #pragma unroll
-      for (int q = 0; q < 16; ++q) {
-        const int f = f0 + lane + 32 * q;
-        if (f < K) {
-          const float* __restrict__ wr = w_s + f * C;
+      for (int j = 0; j < HEAD_RPW; ++j) {
 #pragma unroll
-          for (int c = 0; c < HEAD_MAXC; ++c) if (c < C) acc[c] = fmaf(hv[q], wr[c], acc[c]);
-        }
-      }
-    }
-    float m = -INFINITY;
-#pragma unroll
-    for (int c = 0; c < HEAD_MAXC; ++c) {
-      if (c < C) {
-        acc[c] = warp_sum(acc[c]) + (bias ? bias[c] : 0.f);
-        m = fmaxf(m, acc[c]);
+        for (int c = 0; c < C; ++c) acc[j * C + c] = fmaf(hv[j * PASS_CHUNKS + i], w[c], acc[j * C + c]);
       }
     }
-    float ssum = 0.f;
+    if (pass + 1 < npass) {
 #pragma unroll
-    for (int c = 0; c < HEAD_MAXC; ++c) if (c < C) ssum += expf(acc[c] - m);
-    const int lab = labels[row];
-    float dl[HEAD_MAXC];
-    float lab_logit = 0.f;
-#pragma unroll
-    for (int c = 0; c < HEAD_MAXC; ++c) {
-      dl[c] = 0.f;
-      if (c < C) {
-        const float pr = expf(acc[c] - m) / ssum;
-        dl[c] = (pr - (c == lab ? 1.f : 0.f)) * inv_rows;
-        if (c == lab) lab_logit = acc[c];
-        if (lane == 0) {
-          if (logits) logits[(int64_t)row * C + c] = acc[c];
-          dlogits[(int64_t)row * C + c] = dl[c];
-        }
-      }
-    }
-    if (lane == 0) rowloss[row] = -(lab_logit - m - logf(ssum));
-    if (dh) {
-      float* __restrict__ dr = dh + (int64_t)row * K;
-      for (int f = lane; f < K; f += 32) {
-        const float* __restrict__ wr = w_s + f * C;
-        float v = 0.f;
-#pragma unroll
-        for (int c = 0; c < HEAD_MAXC; ++c) if (c < C) v = fmaf(dl[c], wr[c], v);
-        dr[f] = v;
-      }
+      for (int q = 0; q < HEAD_RPW * PASS_CHUNKS; ++q) hv[q] = hn[q];
     }
   }
-  __threadfence();
+  {
+    int base = 0, limit = HEAD_RPW * C;
+    head_fold<HEAD_RPW * C, 16>(acc, lane, base, limit);
+#pragma unroll
+    for (int i = 0; i < head_fold_left(HEAD_RPW * C); ++i) {
+      const int idx = base + i;                           // (row in group) * C + class
+      if (idx < limit) part[slot][(rg * HEAD_RPW + idx / C) * HEAD_MAXC + idx % C] = acc[i];
+    }
+  }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (warp < HEAD_ROWS) {                                 // warp r finishes row r of the block: one class per lane
+    if (owner) {
+      float t = -INFINITY;
+      if (lane < C) {
+        t = part[0][warp * HEAD_MAXC + lane];
+#pragma unroll
+        for (int sl = 1; sl < HEAD_SLOTS; ++sl) t += part[sl][warp * HEAD_MAXC + lane];
+        t += my_bias;
+      }
+      const float m = warp_max(t);
+      const float ex = (lane < C) ? expf(t - m) : 0.f;
+      const float ssum = warp_sum(ex);
+      const float pr = ex / ssum;
+      const float d = (pr - (lane == lab ? 1.f : 0.f)) * inv_rows;
+      const float tl = __shfl_sync(0xffffffffu, t, lab & 31);
+      const float lab_logit = (lab >= 0 && lab < C) ? tl : 0.f;
+      if (lane < C) {
+        if (logits) logits[(int64_t)my_row * C + lane] = t;
+        dlogits[(int64_t)my_row * C + lane] = d;
+        dls[warp][lane] = d;
+      }
+      if (lane == 0) rl[warp] = -(lab_logit - m - logf(ssum));
+    } else if (lane == 0) {
+      rl[warp] = 0.f;
+    }
+  }
+  __syncthreads();
+  HEAD_STAMP(3);
+  if (threadIdx.x == 0) {                                // the block's loss and the ticket, while the others write dh
+    float t = 0.f;
+#pragma unroll
+    for (int r = 0; r < HEAD_ROWS; ++r) t += rl[r];
+    blockloss[blockIdx.x] = t;
+    __threadfence();
     const int ticket = atomicAdd(counter, 1);
     s_last = (ticket == (int)gridDim.x - 1) ? 1 : 0;
     if (s_last) *counter = 0;
   }
+  if (dh && row0 < rows) {
+    float dl[HEAD_RPW][C];
+#pragma unroll
+    for (int j = 0; j < HEAD_RPW; ++j) {
+      if (row0 + j < rows) {
+        head_load_w<C>(&dls[rg * HEAD_RPW + j][0], dl[j]);
+      } else {
+#pragma unroll
+        for (int c = 0; c < C; ++c) dl[j][c] = 0.f;
+      }
+    }
+#pragma unroll 2
+    for (int f = slot * 32 + lane; f < K; f += 32 * HEAD_SLOTS) {
+      float w[C];
+      head_load_w<C>(w_s + f * C, w);
+#pragma unroll
+      for (int j = 0; j < HEAD_RPW; ++j) {
+        float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          if (c & 1) v1 = fmaf(dl[j][c], w[c], v1);
+          else v0 = fmaf(dl[j][c], w[c], v0);
+        }
+        if (row0 + j < rows) dh[(int64_t)(row0 + j) * K + f] = v0 + v1;
+      }
+    }
+  }
+  HEAD_STAMP(4);
   __syncthreads();
-  if (!s_last) return;
+  HEAD_STAMP(5);
+  HEAD_STAMP(6);
+  if (!s_last || warp != 0) return;
   __threadfence();
   float a = 0.f;
-#pragma unroll 8
-  for (int r = threadIdx.x; r < rows; r += HEAD_THREADS) a += __ldcg(rowloss + r);
-  a = block_reduce(a, SumOp(), red);
-  if (threadIdx.x == 0) *loss = a * inv_rows;
+  for (int b = lane; b < (int)gridDim.x; b += 32) a += __ldcg(blockloss + b);
+  a = warp_sum(a);
+  if (lane == 0) *loss = a * inv_rows;
+  HEAD_STAMP(7);
 }
 
 // temporal_softmax_loss (nn/layers.py:444-480) over rows = N*T score vectors: one warp per row computes the
@@ -521,17 +658,27 @@ int mc_head_softmax_loss(const float* h, const float* W, const float* bias, cons
   MC_REQUIRE(rows > 0 && K > 0 && C > 0 && C <= HEAD_MAXC, "classifier head: 1 <= classes <= 16");
   const size_t smem = sizeof(float) * (size_t)K * C;
   MC_REQUIRE(smem <= 200 * 1024, "classifier head: weight matrix beyond 200 KB of shared memory");
-  static uint32_t configured = 0;
-  if (first_use_on_device(&configured))
-    MC_CHECK(cudaFuncSetAttribute(head_softmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  static uint32_t configured[HEAD_MAXC + 1] = {};
   int* counter = ticket_counter();
   MC_REQUIRE(counter != nullptr, "ticket counter allocation failed");
   ScratchFrame scratch;
-  float* rowloss = scratch.floats((size_t)rows);
+  const unsigned blocks = (unsigned)((rows + HEAD_ROWS - 1) / HEAD_ROWS);
+  float* rowloss = scratch.floats((size_t)blocks);      // one partial loss per block
   if (!rowloss) return 1;
-  const unsigned blocks = (unsigned)((rows + HEAD_THREADS / 32 - 1) / (HEAD_THREADS / 32));
-  mc::launch(head_softmax_kernel, blocks, HEAD_THREADS, smem, h, W, bias, labels, logits, dlogits, dh, loss, rowloss, counter,
-             (int)rows, (int)K, (int)C, 1.f / (float)rows);
+  const float inv_rows = 1.f / (float)rows;
+  switch ((int)C) {
+#define HEAD_CASE(CC)                                                                                                  \
+  case CC:                                                                                                             \
+    if (first_use_on_device(&configured[CC]))                                                                          \
+      MC_CHECK(cudaFuncSetAttribute(head_softmax_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+    mc::launch(head_softmax_kernel<CC>, blocks, HEAD_THREADS, smem, h, W, bias, labels, logits, dlogits, dh, loss,     \
+               rowloss, counter, (int)rows, (int)K, inv_rows);                                                         \
+    break;
+    HEAD_CASE(1) HEAD_CASE(2) HEAD_CASE(3) HEAD_CASE(4) HEAD_CASE(5) HEAD_CASE(6) HEAD_CASE(7) HEAD_CASE(8)
+    HEAD_CASE(9) HEAD_CASE(10) HEAD_CASE(11) HEAD_CASE(12) HEAD_CASE(13) HEAD_CASE(14) HEAD_CASE(15) HEAD_CASE(16)
+#undef HEAD_CASE
+    default: MC_REQUIRE(false, "classifier head: 1 <= classes <= 16");
+  }
   MC_LAUNCHED();
   return 0;
 }

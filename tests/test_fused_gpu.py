@@ -357,7 +357,8 @@ np.savez(__import__('sys').argv[1], v=float(v), **dict(('g%d' % i, a.asnumpy()) 
             assert rel(b[k], a[k]) <= 5e-3, k
 
 
-@pytest.mark.parametrize('rows,K,C', [(1024, 512, 10), (256, 512, 10), (512, 2048, 10), (37, 50, 3), (128, 96, 16)])
+@pytest.mark.parametrize('rows,K,C', [(1024, 512, 10), (256, 512, 10), (512, 2048, 10), (37, 50, 3), (128, 96, 16),
+                                      (9, 2600, 7), (64, 3072, 16), (5, 1, 1), (100, 513, 5), (33, 1000, 12)])
 def test_classifier_head_kernel_matches_oracle_and_composition(cuda, rows, K, C):
     """mc_head_softmax_loss: logits, loss, dlogits and dh against float64 (affine + softmax_loss differentiated by
     the oracle's tape) and, through the front end, against the separate kernels (MINPY_FUSE_FORWARD off)."""
@@ -397,8 +398,9 @@ def test_classifier_head_kernel_matches_oracle_and_composition(cuda, rows, K, C)
             finally:
                 cuda_core._FUSE_FORWARD = saved                                     # pylint: disable=protected-access
         assert abs(res[0][0] - res[1][0]) <= 1e-5 * abs(res[1][0])
-        for a, b2, o in zip(res[0][1], res[1][1], (gh, gw, gb)):
-            assert rel(a, orc.raw(o)) <= 2e-5 and rel(b2, orc.raw(o)) <= 2e-5
+        # dW = h^T . dlogits is a tcgen05 TF32 GEMM on the chain when the shape is large enough (mc_gemm routing)
+        for a, b2, o, tol in zip(res[0][1], res[1][1], (gh, gw, gb), (2e-5, 2e-3, 2e-5)):
+            assert rel(a, orc.raw(o)) <= tol and rel(b2, orc.raw(o)) <= tol
     finally:
         minpy.set_global_policy('prefer_cuda')
 
