@@ -293,19 +293,47 @@ __global__ void __launch_bounds__(L_THREADS) bn_bwd_apply_kernel(const float* __
 
 // ---- small batches: statistics + apply in ONE kernel ("slab" kernels) ----------------------
 // (1024, 512) is 2 MB: the two-kernel path above costs two launches (~4-6 us each inside a step
-// graph) for ~1 us of memory time.  Here a block owns 8 columns (one 32-byte sector of every row)
-// and keeps its whole N x 8 slab in registers: thread = (row lane 0..127, column half), up to
-// SLAB_RPT rows each.  Sums: per thread, then 16 row lanes by shuffle, then 8 warps through shared
+// graph) for ~1 us of memory time.  Here a block owns 4 * HALVES columns of every row and keeps its
+// whole slab in registers: thread = (row lane, column half), up to N / lanes rows each.  HALVES = 2
+// (8 columns = one 32-byte sector per row, 128 row lanes x 8 rows) when that still fills the machine,
+// HALVES = 1 (4 columns, 256 row lanes x 4 rows) otherwise: twice the blocks, half the serial work in
+// each.  Sums: per thread, then the row lanes of a warp by shuffle, then 8 warps through shared
 // memory -- a fixed order, so results are deterministic.
-constexpr int SLAB_RPT = 8;                    // rows per thread: N <= 128 * SLAB_RPT
+// The kernels are latency chains, not bandwidth: the phase probe (tools/probe.py, profiles/r2l) showed
+// 1.25 us of the forward kernel's 4.4 us between the barrier and the first store -- gamma / beta / running
+// statistics were loaded only then -- and 1.5 us of Philox serialised behind the loads in both kernels.
+// Every parameter is now fetched at entry and the keep-mask is computed while the slab loads are in flight.
+constexpr int SLAB_MAXN = 1024;                // rows a slab kernel can hold
+MC_PROBE_DEFINE(bnf)
+MC_PROBE_DEFINE(bnb)
+// Loads the optimiser may not sink towards their first use (it moved the parameter loads behind ~500 instructions
+// of Philox, exposing their latency after the barrier): volatile asm keeps them where they are written.
+__device__ __forceinline__ float4 ldg4_here(const float* p) {
+  float4 v;
+  asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float ldg_here(const float* p) {
+  float v;
+  asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+// 1 / sqrt(v) to within an ulp without the IEEE sqrt + divide sequences (two dependent ~40-instruction chains in
+// every thread of the block, on the critical path between the barrier and the first store).
+__device__ __forceinline__ float rsqrt_nr(float v) {
+  const float y = rsqrtf(v);
+  return y * fmaf(-0.5f * v * y, y, 1.5f);
+}
+
+template <int HALVES>
 __device__ __forceinline__ void slab_block_sums(float (&a)[4], float (&b)[4], float (&ta)[4], float (&tb)[4]) {
   __shared__ float red[8][2][8];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, half = threadIdx.x & 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, half = (HALVES == 2) ? (threadIdx.x & 1) : 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
 #pragma unroll
-    for (int o = 2; o < 32; o <<= 1) { a[k] += __shfl_xor_sync(0xffffffffu, a[k], o); b[k] += __shfl_xor_sync(0xffffffffu, b[k], o); }
-    if (lane < 2) { red[warp][half][k] = a[k]; red[warp][half][4 + k] = b[k]; }
+    for (int o = HALVES; o < 32; o <<= 1) { a[k] += __shfl_xor_sync(0xffffffffu, a[k], o); b[k] += __shfl_xor_sync(0xffffffffu, b[k], o); }
+    if (lane < HALVES) { red[warp][half][k] = a[k]; red[warp][half][4 + k] = b[k]; }
   }
   __syncthreads();
 #pragma unroll
@@ -317,10 +345,26 @@ __device__ __forceinline__ void slab_block_sums(float (&a)[4], float (&b)[4], fl
   }
 }
 
+// Keep-mask of the thread's slab: bit 4 * i + k is set when element (row i of this thread, column k) survives the
+// dropout -- lane (e & 3) of Philox(seed)(offset + e / 4) for flat element index e, exactly dropout_kernel's.
+template <int RPT, int LANES>
+__device__ __forceinline__ uint32_t slab_keep_mask(const Philox& rng, uint64_t offset, int rl, int N, int64_t D, int64_t col,
+                                                   float p) {
+  uint32_t keep = 0;
+#pragma unroll
+  for (int i = 0; i < RPT; ++i) {
+    const int r = rl + LANES * i;
+    if (r < N) {
+      const uint4 q = rng(offset + (uint64_t)(((int64_t)r * D + col) >> 2));
+      keep |= ((u01(q.x) > p ? 1u : 0u) | (u01(q.y) > p ? 2u : 0u) | (u01(q.z) > p ? 4u : 0u) | (u01(q.w) > p ? 8u : 0u)) << (4 * i);
+    }
+  }
+  return keep;
+}
+
 // DROP: the dropout that follows batchnorm in the reference's block (mlp_bn_dropout.py:41-54) is applied
-// at the store -- out = bn(x) * (u > p), the mask of element i being lane (i & 3) of Philox(seed)(offset + i/4),
-// exactly dropout_kernel's -- so the normalised activations are never written unmasked.
-template <bool DROP>
+// at the store -- out = bn(x) * (u > p) -- so the normalised activations are never written unmasked.
+template <bool DROP, int HALVES>
 __global__ void __launch_bounds__(L_THREADS) bn_slab_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                                 const float* __restrict__ beta, const float* __restrict__ rmean,
                                                                 const float* __restrict__ rvar, float* __restrict__ out,
@@ -328,57 +372,77 @@ __global__ void __launch_bounds__(L_THREADS) bn_slab_fwd_kernel(const float* __r
                                                                 float* __restrict__ save_mean, float* __restrict__ save_invstd,
                                                                 int N, int64_t D, float eps, float momentum, float p,
                                                                 uint64_t seed, uint64_t offset, const unsigned long long* epoch) {
+  constexpr int LANES = L_THREADS / HALVES, RPT = SLAB_MAXN / LANES;
+  MC_STAMP(bnf, 0);
   mc::pdl_sync();
+  MC_STAMP(bnf, 1);
   if (DROP && epoch) offset += (uint64_t)(*epoch) << 40;
-  const int half = threadIdx.x & 1, rl = threadIdx.x >> 1;
-  const int64_t col = (int64_t)blockIdx.x * 8 + 4 * half;
-  float4 v[SLAB_RPT];
+  const int half = (HALVES == 2) ? (threadIdx.x & 1) : 0, rl = threadIdx.x / HALVES;
+  const int64_t col = (int64_t)blockIdx.x * (4 * HALVES) + 4 * half;
+  float4 v[RPT];
 #pragma unroll
-  for (int i = 0; i < SLAB_RPT; ++i) {
-    const int r = rl + 128 * i;
+  for (int i = 0; i < RPT; ++i) {
+    const int r = rl + LANES * i;
     if (r < N) v[i] = *reinterpret_cast<const float4*>(x + (int64_t)r * D + col);
   }
-  const float4 x0 = *reinterpret_cast<const float4*>(x + col);       // shift: no cancellation blow-up
+  const float4 x0 = ldg4_here(x + col);                              // shift: no cancellation blow-up
+  float gm[4], bt[4], rm[4] = {0.f, 0.f, 0.f, 0.f}, rv[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    gm[k] = ldg_here(gamma + col + k);
+    bt[k] = ldg_here(beta + col + k);
+    if (rl == 0) { rm[k] = ldg_here(rmean + col + k); rv[k] = ldg_here(rvar + col + k); }
+  }
+  const float inv_n = 1.0f / (float)N;
+  uint32_t keep = 0xffffffffu;
+  if (DROP) keep = slab_keep_mask<RPT, LANES>(Philox(seed), offset, rl, N, D, col, p);
   float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f}, s1[4], s2[4];
 #pragma unroll
-  for (int i = 0; i < SLAB_RPT; ++i) {
-    if (rl + 128 * i < N) {
+  for (int i = 0; i < RPT; ++i) {
+    if (rl + LANES * i < N) {
       const float d0 = v[i].x - x0.x, d1 = v[i].y - x0.y, d2 = v[i].z - x0.z, d3 = v[i].w - x0.w;
       a[0] += d0; a[1] += d1; a[2] += d2; a[3] += d3;
       b[0] += d0 * d0; b[1] += d1 * d1; b[2] += d2 * d2; b[3] += d3 * d3;
     }
   }
-  slab_block_sums(a, b, s1, s2);
+  MC_STAMP(bnf, 2);
+  slab_block_sums<HALVES>(a, b, s1, s2);
+  MC_STAMP(bnf, 3);
   const float x0v[4] = {x0.x, x0.y, x0.z, x0.w};
-  float sc[4], sh[4];
+  float sc[4], sh[4], mean[4], inv[4], var[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const float dm = s1[k] / (float)N;
-    float var = fmaxf(s2[k] / (float)N - dm * dm, 0.f);               // biased variance (layers.py:103)
-    const float mean = x0v[k] + dm, inv = 1.0f / sqrtf(var + eps);
-    sc[k] = gamma[col + k] * inv;
-    sh[k] = beta[col + k] - mean * sc[k];
-    if (rl == 0) {
-      save_mean[col + k] = mean;
-      save_invstd[col + k] = inv;
-      new_rmean[col + k] = momentum * rmean[col + k] + (1.0f - momentum) * mean;
-      new_rvar[col + k] = momentum * rvar[col + k] + (1.0f - momentum) * var;
+    const float dm = s1[k] * inv_n;
+    var[k] = fmaxf(s2[k] * inv_n - dm * dm, 0.f);                     // biased variance (layers.py:103)
+    mean[k] = x0v[k] + dm;
+    inv[k] = rsqrt_nr(var[k] + eps);
+    sc[k] = gm[k] * inv[k];
+    sh[k] = bt[k] - mean[k] * sc[k];
+  }
+  if (rl == 0) {                                                      // one divergent region, after the arithmetic
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      save_mean[col + k] = mean[k];
+      save_invstd[col + k] = inv[k];
+      new_rmean[col + k] = momentum * rm[k] + (1.0f - momentum) * mean[k];
+      new_rvar[col + k] = momentum * rv[k] + (1.0f - momentum) * var[k];
     }
   }
-  const Philox rng(seed);
+  MC_STAMP(bnf, 4);
 #pragma unroll
-  for (int i = 0; i < SLAB_RPT; ++i) {
-    const int r = rl + 128 * i;
+  for (int i = 0; i < RPT; ++i) {
+    const int r = rl + LANES * i;
     if (r < N) {
       float4 o = make_float4(fmaf(v[i].x, sc[0], sh[0]), fmaf(v[i].y, sc[1], sh[1]), fmaf(v[i].z, sc[2], sh[2]), fmaf(v[i].w, sc[3], sh[3]));
       if (DROP) {
-        const uint4 q = rng(offset + (uint64_t)(((int64_t)r * D + col) >> 2));
-        o.x = (u01(q.x) > p) ? o.x : 0.f; o.y = (u01(q.y) > p) ? o.y : 0.f;
-        o.z = (u01(q.z) > p) ? o.z : 0.f; o.w = (u01(q.w) > p) ? o.w : 0.f;
+        const uint32_t m = keep >> (4 * i);
+        o.x = (m & 1u) ? o.x : 0.f; o.y = (m & 2u) ? o.y : 0.f;
+        o.z = (m & 4u) ? o.z : 0.f; o.w = (m & 8u) ? o.w : 0.f;
       }
       *reinterpret_cast<float4*>(out + (int64_t)r * D + col) = o;
     }
   }
+  MC_STAMP(bnf, 5);
 }
 
 // DROP: dy is the gradient of the dropout that followed this batchnorm; its keep-mask is regenerated from
@@ -386,60 +450,73 @@ __global__ void __launch_bounds__(L_THREADS) bn_slab_fwd_kernel(const float* __r
 // relu_apply): dx is zeroed where x's sign bit is set, i.e. the result is already the gradient of the affine
 // PRE-activation, and its column sums (the bias gradient of that affine layer) are written to `dbias`.
 // One launch instead of dropout-bwd + batchnorm-bwd + relu-bwd + a column reduction.
-template <bool DROP, bool RELU>
+template <bool DROP, bool RELU, int HALVES>
 __global__ void __launch_bounds__(L_THREADS) bn_slab_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy,
                                                                 const float* __restrict__ gamma, const float* __restrict__ mean,
                                                                 const float* __restrict__ invstd, float* __restrict__ dx,
                                                                 float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                                 float* __restrict__ dbias, int N, int64_t D, float p,
                                                                 uint64_t seed, uint64_t offset, const unsigned long long* epoch) {
+  constexpr int LANES = L_THREADS / HALVES, RPT = SLAB_MAXN / LANES;
+  MC_STAMP(bnb, 0);
   mc::pdl_sync();
+  MC_STAMP(bnb, 1);
   if (DROP && epoch) offset += (uint64_t)(*epoch) << 40;
-  const Philox rng(seed);
   uint32_t neg = 0;            // RELU: bit 4*i+k set when x[row i of this thread][column k] has its sign bit set
-  const int half = threadIdx.x & 1, rl = threadIdx.x >> 1;
-  const int64_t col = (int64_t)blockIdx.x * 8 + 4 * half;
-  float4 xh[SLAB_RPT], g[SLAB_RPT];
-  const float4 mu = *reinterpret_cast<const float4*>(mean + col), iv = *reinterpret_cast<const float4*>(invstd + col);
+  const int half = (HALVES == 2) ? (threadIdx.x & 1) : 0, rl = threadIdx.x / HALVES;
+  const int64_t col = (int64_t)blockIdx.x * (4 * HALVES) + 4 * half;
+  float4 xh[RPT], g[RPT];
 #pragma unroll
-  for (int i = 0; i < SLAB_RPT; ++i) {
-    const int r = rl + 128 * i;
+  for (int i = 0; i < RPT; ++i) {
+    const int r = rl + LANES * i;
     if (r < N) {
       xh[i] = *reinterpret_cast<const float4*>(x + (int64_t)r * D + col);
       g[i] = *reinterpret_cast<const float4*>(dy + (int64_t)r * D + col);
+    }
+  }
+  const float4 mu = ldg4_here(mean + col), iv = ldg4_here(invstd + col);
+  float gm[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) gm[k] = ldg_here(gamma + col + k);
+  const float inv_n = 1.0f / (float)N;
+  uint32_t keep = 0xffffffffu;
+  if (DROP) keep = slab_keep_mask<RPT, LANES>(Philox(seed), offset, rl, N, D, col, p);
+  float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f}, s1[4], s2[4];
+#pragma unroll
+  for (int i = 0; i < RPT; ++i) {
+    if (rl + LANES * i < N) {
       if (DROP) {
-        const uint4 q = rng(offset + (uint64_t)(((int64_t)r * D + col) >> 2));
-        g[i].x = (u01(q.x) > p) ? g[i].x : 0.f; g[i].y = (u01(q.y) > p) ? g[i].y : 0.f;
-        g[i].z = (u01(q.z) > p) ? g[i].z : 0.f; g[i].w = (u01(q.w) > p) ? g[i].w : 0.f;
+        const uint32_t m = keep >> (4 * i);
+        g[i].x = (m & 1u) ? g[i].x : 0.f; g[i].y = (m & 2u) ? g[i].y : 0.f;
+        g[i].z = (m & 4u) ? g[i].z : 0.f; g[i].w = (m & 8u) ? g[i].w : 0.f;
       }
       if (RELU)
         neg |= ((__float_as_uint(xh[i].x) >> 31) | ((__float_as_uint(xh[i].y) >> 31) << 1) |
                 ((__float_as_uint(xh[i].z) >> 31) << 2) | ((__float_as_uint(xh[i].w) >> 31) << 3)) << (4 * i);
-    }
-  }
-  float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f}, s1[4], s2[4];
-#pragma unroll
-  for (int i = 0; i < SLAB_RPT; ++i) {
-    if (rl + 128 * i < N) {
       xh[i] = make_float4((xh[i].x - mu.x) * iv.x, (xh[i].y - mu.y) * iv.y, (xh[i].z - mu.z) * iv.z, (xh[i].w - mu.w) * iv.w);
       a[0] += g[i].x; a[1] += g[i].y; a[2] += g[i].z; a[3] += g[i].w;
       b[0] += g[i].x * xh[i].x; b[1] += g[i].y * xh[i].y; b[2] += g[i].z * xh[i].z; b[3] += g[i].w * xh[i].w;
     }
   }
-  slab_block_sums(a, b, s1, s2);
+  MC_STAMP(bnb, 2);
+  slab_block_sums<HALVES>(a, b, s1, s2);
+  MC_STAMP(bnb, 3);
   const float ivv[4] = {iv.x, iv.y, iv.z, iv.w};
   float k1[4], k2[4], k3[4];                       // dx = k1 * (dy - k2 - xhat * k3)
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    if (rl == 0) { dbeta[col + k] = s1[k]; dgamma[col + k] = s2[k]; }
-    k1[k] = gamma[col + k] * ivv[k];
-    k2[k] = s1[k] / (float)N;
-    k3[k] = s2[k] / (float)N;
+    k1[k] = gm[k] * ivv[k];
+    k2[k] = s1[k] * inv_n;
+    k3[k] = s2[k] * inv_n;
+  }
+  if (rl == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { dbeta[col + k] = s1[k]; dgamma[col + k] = s2[k]; }
   }
   float c[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-  for (int i = 0; i < SLAB_RPT; ++i) {
-    const int r = rl + 128 * i;
+  for (int i = 0; i < RPT; ++i) {
+    const int r = rl + LANES * i;
     if (r < N) {
       float4 o = make_float4(k1[0] * (g[i].x - k2[0] - xh[i].x * k3[0]), k1[1] * (g[i].y - k2[1] - xh[i].y * k3[1]),
                              k1[2] * (g[i].z - k2[2] - xh[i].z * k3[2]), k1[3] * (g[i].w - k2[3] - xh[i].w * k3[3]));
@@ -454,18 +531,22 @@ __global__ void __launch_bounds__(L_THREADS) bn_slab_bwd_kernel(const float* __r
       *reinterpret_cast<float4*>(dx + (int64_t)r * D + col) = o;
     }
   }
+  MC_STAMP(bnb, 4);
   if (RELU) {
     float z[4] = {0.f, 0.f, 0.f, 0.f}, t1[4], t2[4];
     __syncthreads();                  // slab_block_sums reuses its shared buffer
-    slab_block_sums(c, z, t1, t2);
+    slab_block_sums<HALVES>(c, z, t1, t2);
     if (rl == 0) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) dbias[col + k] = t1[k];
     }
   }
+  MC_STAMP(bnb, 5);
 }
+// 8 columns a block while that gives every SM a block, 4 columns otherwise.
+static int bn_slab_halves(int64_t D) { return (D / 8 >= sm_count()) ? 2 : 1; }
 static bool bn_slab_ok(int64_t N, int64_t D, bool aligned) {
-  return aligned && N <= 128 * SLAB_RPT && (D % 8) == 0 && N * D <= (1 << 20);
+  return aligned && N <= SLAB_MAXN && (D % 8) == 0 && N * D <= (1 << 20);
 }
 
 template <int VEC>
@@ -636,9 +717,14 @@ int mc_batchnorm_train_fwd(const float* x, const float* gamma, const float* beta
                            float* save_mean, float* save_invstd, int64_t N, int64_t D, float eps, float momentum) {
   MC_REQUIRE(N > 0 && D > 0, "empty batch");
   if (bn_slab_ok(N, D, aligned16(x) && aligned16(out))) {
-    mc::launch(bn_slab_fwd_kernel<false>, (unsigned)(D / 8), L_THREADS, 0, x, gamma, beta, running_mean, running_var, out,
-               new_running_mean, new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum, 0.f, (uint64_t)0,
-               (uint64_t)0, (const unsigned long long*)nullptr);
+    if (bn_slab_halves(D) == 2)
+      mc::launch(bn_slab_fwd_kernel<false, 2>, (unsigned)(D / 8), L_THREADS, 0, x, gamma, beta, running_mean, running_var, out,
+                 new_running_mean, new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum, 0.f, (uint64_t)0,
+                 (uint64_t)0, (const unsigned long long*)nullptr);
+    else
+      mc::launch(bn_slab_fwd_kernel<false, 1>, (unsigned)(D / 4), L_THREADS, 0, x, gamma, beta, running_mean, running_var, out,
+                 new_running_mean, new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum, 0.f, (uint64_t)0,
+                 (uint64_t)0, (const unsigned long long*)nullptr);
     MC_LAUNCHED();
     return 0;
   }
@@ -675,9 +761,14 @@ int mc_bn_dropout_fwd(const float* x, const float* gamma, const float* beta, con
                       uint64_t seed, uint64_t offset) {
   MC_REQUIRE(N > 0 && D > 0, "empty batch");
   MC_REQUIRE(bn_slab_ok(N, D, aligned16(x) && aligned16(out)), "shape outside the fused kernel (mc_bn_fused_supported)");
-  mc::launch(bn_slab_fwd_kernel<true>, (unsigned)(D / 8), L_THREADS, 0, x, gamma, beta, running_mean, running_var, out,
-             new_running_mean, new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum, p, seed, offset,
-             (const unsigned long long*)graph_epoch());
+  if (bn_slab_halves(D) == 2)
+    mc::launch(bn_slab_fwd_kernel<true, 2>, (unsigned)(D / 8), L_THREADS, 0, x, gamma, beta, running_mean, running_var, out,
+               new_running_mean, new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum, p, seed, offset,
+               (const unsigned long long*)graph_epoch());
+  else
+    mc::launch(bn_slab_fwd_kernel<true, 1>, (unsigned)(D / 4), L_THREADS, 0, x, gamma, beta, running_mean, running_var, out,
+               new_running_mean, new_running_var, save_mean, save_invstd, (int)N, D, eps, momentum, p, seed, offset,
+               (const unsigned long long*)graph_epoch());
   MC_LAUNCHED();
   return 0;
 }
@@ -690,14 +781,19 @@ int mc_bn_dropout_relu_bwd(const float* x, const float* dy, const float* gamma, 
              "shape outside the fused kernel (mc_bn_fused_supported)");
   MC_REQUIRE(!relu_signed || dbias != nullptr, "relu_signed needs dbias");
   const unsigned long long* ep = (const unsigned long long*)graph_epoch();
-  const unsigned grid = (unsigned)(D / 8);
+  const int halves = bn_slab_halves(D);
+  const unsigned grid = (unsigned)(D / (4 * halves));
 #define MC_BN_BWD(DR, RE)                                                                                            \
-  mc::launch(bn_slab_bwd_kernel<DR, RE>, grid, L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, dx, dgamma, dbeta, dbias, \
-             (int)N, D, p, seed, offset, ep)
-  if (dropout && relu_signed) MC_BN_BWD(true, true);
-  else if (dropout) MC_BN_BWD(true, false);
-  else if (relu_signed) MC_BN_BWD(false, true);
-  else MC_BN_BWD(false, false);
+  if (halves == 2)                                                                                                   \
+    mc::launch(bn_slab_bwd_kernel<DR, RE, 2>, grid, L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, dx, dgamma, dbeta, \
+               dbias, (int)N, D, p, seed, offset, ep);                                                               \
+  else                                                                                                               \
+    mc::launch(bn_slab_bwd_kernel<DR, RE, 1>, grid, L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, dx, dgamma, dbeta, \
+               dbias, (int)N, D, p, seed, offset, ep)
+  if (dropout && relu_signed) { MC_BN_BWD(true, true); }
+  else if (dropout) { MC_BN_BWD(true, false); }
+  else if (relu_signed) { MC_BN_BWD(false, true); }
+  else { MC_BN_BWD(false, false); }
 #undef MC_BN_BWD
   MC_LAUNCHED();
   return 0;
@@ -707,8 +803,12 @@ int mc_batchnorm_train_bwd(const float* x, const float* dy, const float* gamma, 
                            const float* save_invstd, float* dx, float* dgamma, float* dbeta, int64_t N, int64_t D) {
   MC_REQUIRE(N > 0 && D > 0, "empty batch");
   if (bn_slab_ok(N, D, aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(save_mean) && aligned16(save_invstd))) {
-    mc::launch(bn_slab_bwd_kernel<false, false>, (unsigned)(D / 8), L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, dx, dgamma,
-               dbeta, (float*)nullptr, (int)N, D, 0.f, (uint64_t)0, (uint64_t)0, (const unsigned long long*)nullptr);
+    if (bn_slab_halves(D) == 2)
+      mc::launch(bn_slab_bwd_kernel<false, false, 2>, (unsigned)(D / 8), L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, dx,
+                 dgamma, dbeta, (float*)nullptr, (int)N, D, 0.f, (uint64_t)0, (uint64_t)0, (const unsigned long long*)nullptr);
+    else
+      mc::launch(bn_slab_bwd_kernel<false, false, 1>, (unsigned)(D / 4), L_THREADS, 0, x, dy, gamma, save_mean, save_invstd, dx,
+                 dgamma, dbeta, (float*)nullptr, (int)N, D, 0.f, (uint64_t)0, (uint64_t)0, (const unsigned long long*)nullptr);
     MC_LAUNCHED();
     return 0;
   }

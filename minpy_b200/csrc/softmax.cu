@@ -293,24 +293,8 @@ constexpr int HEAD_RG = HEAD_ROWS / HEAD_RPW;
 constexpr int HEAD_SLOTS = 8;     // warps that split K
 constexpr int HEAD_THREADS = 32 * HEAD_RG * HEAD_SLOTS;
 constexpr int HEAD_MAXC = 16;
-// tools/head_probe.sh builds a second library with -DMC_HEAD_PROBE: thread 0 of every block stamps %globaltimer
-// at the phase boundaries below.  Compiled out of libminpy_cuda.so.
-#ifdef MC_HEAD_PROBE
-__device__ unsigned long long g_head_probe[1024 * 8];
-#define HEAD_STAMP(i)                                                                   \
-  do {                                                                                  \
-    if (threadIdx.x == 0 && blockIdx.x < 1024) {                                        \
-      unsigned long long t_;                                                            \
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                            \
-      g_head_probe[blockIdx.x * 8 + (i)] = t_;                                          \
-    }                                                                                   \
-  } while (0)
-extern "C" int mc_head_probe_read(unsigned long long* out) {
-  return cudaMemcpyFromSymbol(out, g_head_probe, sizeof(g_head_probe)) == cudaSuccess ? 0 : 1;
-}
-#else
-#define HEAD_STAMP(i)
-#endif
+MC_PROBE_DEFINE(head)   // tools/probe.sh: %globaltimer stamps at the phase boundaries of head_softmax_kernel
+#define HEAD_STAMP(i) MC_STAMP(head, i)
 // One row of W (C floats at w_s + f * C) into registers with the widest shared-memory loads its alignment allows.
 template <int C>
 __device__ __forceinline__ void head_load_w(const float* __restrict__ wr, float (&w)[C]) {

@@ -1,0 +1,84 @@
+"""Phase timing from inside a kernel (library built by tools/probe.sh with -DMC_PROBE).
+
+    MINPY_CUDA_LIB=$PWD/tools/_probe/libminpy_cuda_probe.so python tools/probe.py head 1024 512 10
+    ... python tools/probe.py bnf 1024 512        (mc_bn_dropout_fwd,       batchnorm + dropout forward)
+    ... python tools/probe.py bnb 1024 512        (mc_bn_dropout_relu_bwd,  dropout + batchnorm + relu backward)
+
+Thread 0 of every block stores %globaltimer (ns) at the kernel's MC_STAMP points; the output is, per iteration,
+the spread of block start times, the time at which the last block passed each stamp, and the per-phase median /
+maximum over blocks.  Stamps cost a few hundred ns in total: compare phases, not absolute times.
+"""
+import ctypes
+import sys
+
+import numpy as np
+
+from minpy_b200 import ops
+from minpy_b200._lib import get_lib
+from minpy_b200.cuda_array import CudaArray
+
+
+def dev(a):
+    return CudaArray.from_numpy(np.ascontiguousarray(a))
+
+
+def case_head(lib, rows=1024, K=512, C=10):
+    rng = np.random.RandomState(0)
+    h, W = dev(rng.randn(rows, K).astype(np.float32)), dev((rng.randn(K, C) * 0.05).astype(np.float32))
+    b, y = dev(np.zeros(C, np.float32)), dev(rng.randint(0, C, rows).astype(np.int32))
+    logits, dl, dh, loss = ops.empty((rows, C)), ops.empty((rows, C)), ops.empty((rows, K)), ops.empty(())
+    keep = (h, W, b, y, logits, dl, dh, loss)
+    return (lambda: lib.mc_head_softmax_loss(h.ptr, W.ptr, b.ptr, y.ptr, logits.ptr, dl.ptr, dh.ptr, loss.ptr, rows, K, C),
+            (rows + 7) // 8, keep)
+
+
+def case_bnf(lib, N=1024, D=512):
+    rng = np.random.RandomState(0)
+    x = dev(rng.randn(N, D).astype(np.float32))
+    g, b, rm, rv = dev(np.ones(D, np.float32)), dev(np.zeros(D, np.float32)), dev(np.zeros(D, np.float32)), dev(np.ones(D, np.float32))
+    out, nm, nv, sm, si = ops.empty((N, D)), ops.empty((D,)), ops.empty((D,)), ops.empty((D,)), ops.empty((D,))
+    keep = (x, g, b, rm, rv, out, nm, nv, sm, si)
+    return (lambda: lib.mc_bn_dropout_fwd(x.ptr, g.ptr, b.ptr, rm.ptr, rv.ptr, out.ptr, nm.ptr, nv.ptr, sm.ptr, si.ptr,
+                                          N, D, 1e-5, 0.9, 0.5, 1234, 0), D // 8, keep)
+
+
+def case_bnb(lib, N=1024, D=512):
+    rng = np.random.RandomState(0)
+    x, dy = dev(rng.randn(N, D).astype(np.float32)), dev(rng.randn(N, D).astype(np.float32))
+    g, sm, si = dev(np.ones(D, np.float32)), dev(np.zeros(D, np.float32)), dev(np.ones(D, np.float32))
+    dx, dg, db, dbias = ops.empty((N, D)), ops.empty((D,)), ops.empty((D,)), ops.empty((D,))
+    keep = (x, dy, g, sm, si, dx, dg, db, dbias)
+    return (lambda: lib.mc_bn_dropout_relu_bwd(x.ptr, dy.ptr, g.ptr, sm.ptr, si.ptr, dx.ptr, dg.ptr, db.ptr, dbias.ptr,
+                                               N, D, 1, 0.5, 1234, 0, 1), D // 8, keep)
+
+
+CASES = {'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
+
+
+def main():
+    tag = sys.argv[1]
+    lib = get_lib()
+    call, blocks, _keep = CASES[tag](lib, *(int(v) for v in sys.argv[2:]))
+    blocks = min(1024, blocks)
+    read = getattr(lib.cdll, 'mc_probe_read_' + tag)
+    read.argtypes = [ctypes.c_void_p]
+    buf = np.zeros(1024 * 8, np.uint64)
+    for it in range(6):
+        call()
+        lib.mc_sync()
+        assert read(buf.ctypes.data) == 0
+        t = buf.reshape(1024, 8)[:blocks].astype(np.int64)
+        used = [i for i in range(8) if t[:, i].max() > 0]
+        t0 = t[:, 0].min()
+        if it < 3:
+            continue
+        print('%s it %d: %d blocks, entry spread %d ns; last block past stamp i at (ns): %s'
+              % (tag, it, blocks, t[:, 0].max() - t0, [int(t[:, i].max() - t0) for i in used]))
+        full = [i for i in used if (t[:, i] >= t0).all()]
+        ph = np.diff(t[:, full], axis=1)
+        print('   phases between stamps %s: median %s  max %s'
+              % (full, np.median(ph, axis=0).astype(int).tolist(), ph.max(axis=0).tolist()))
+
+
+if __name__ == '__main__':
+    main()
