@@ -208,20 +208,21 @@ struct MinOp {
 
 // In-kernel phase timing (tools/probe.sh builds a second library with -DMC_PROBE; nothing of this is compiled into
 // libminpy_cuda.so).  MC_PROBE_DEFINE(tag) at file scope declares the stamp buffer of a kernel and the entry point
-// mc_probe_read_<tag>(out[1024 * 8]); MC_STAMP(tag, i), i < 8, makes thread 0 of every block (the first 1024) store
+// mc_probe_read_<tag>(out[1024 * 16]); MC_STAMP(tag, i), i < 16, makes thread 0 of every block (the first 1024) store
 // %globaltimer (ns).  tools/probe.py prints per-phase medians over blocks.
 #ifdef MC_PROBE
 #define MC_PROBE_DEFINE(tag)                                                                           \
-  __device__ unsigned long long g_probe_##tag[1024 * 8];                                               \
+  __device__ unsigned long long g_probe_##tag[1024 * 16];                                               \
   extern "C" int mc_probe_read_##tag(unsigned long long* out) {                                        \
     return cudaMemcpyFromSymbol(out, g_probe_##tag, sizeof(g_probe_##tag)) == cudaSuccess ? 0 : 1;     \
   }
 #define MC_STAMP(tag, i)                                                                               \
   do {                                                                                                 \
-    if (threadIdx.x == 0 && blockIdx.x < 1024 && blockIdx.y == 0) {                                    \
+    const unsigned lin_ = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);              \
+    if (threadIdx.x == 0 && lin_ < 1024) {                                                             \
       unsigned long long t_;                                                                           \
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                           \
-      g_probe_##tag[blockIdx.x * 8 + (i)] = t_;                                                        \
+      g_probe_##tag[lin_ * 16 + (i)] = t_;                                                              \
     }                                                                                                  \
   } while (0)
 #else

@@ -320,7 +320,7 @@ namespace tc {
 
 constexpr int BM = 128;         // UMMA M (cta_group::1): accumulator row i <-> TMEM lane i
 constexpr int BK = 32;          // fp32 per stage along K = 128 B = one SWIZZLE_128B row
-constexpr int THREADS = 128;    // warp 0: TMA producer, warp 1: MMA issuer; all 4: epilogue
+constexpr int THREADS = 256;    // warp 0: TMA producer, warp 1: MMA issuer; all 8: epilogue (two per TMEM lane quadrant)
 
 // The LSTM time step as the epilogue of its recurrent GEMM (cluster split-K path only; see lstm.cu).
 //   mode 1 (forward):  the GEMM is h_{t-1} . Wh' with Wh' = Wh's columns reordered unit-major (column 4u+g =
@@ -473,6 +473,7 @@ __device__ __forceinline__ void cluster_reduce(const GemmParams& p, uint32_t sme
 //   MN-major tile: R/32 blocks of [BK k-rows x 128 B] (4096 B each, LBO), written by TMA with
 //            SWIZZLE_128B_ATOM_32B (pattern repeats every 4 k-rows = 512 B, SBO); one MMA
 //            (K = 8) covers two such groups: start + 1024k.
+MC_PROBE_DEFINE(gemm)
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                const __grid_constant__ CUtensorMap tmB,
@@ -488,6 +489,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
 
+  MC_STAMP(gemm, 0);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // Tile raster.  CTAs are scheduled in linear block order; with the plain x-major order one wave of 148
   // CTAs of a 4096^3 problem touches ~5 A panels and ALL 32 B panels, so B (64 MB) is streamed from HBM
@@ -528,7 +530,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  MC_STAMP(gemm, 1);
   mc::pdl_sync();      // prologue done (on-chip state only); global memory from here on
+  MC_STAMP(gemm, 2);
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
@@ -557,6 +561,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
       }
       if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
+    MC_STAMP(gemm, 3);
   } else if (warp == 1 && elect_one()) {
     // ------------------------------ MMA issuer --------------------------------------
     // Instruction descriptor (cute UMMA::InstrDescriptor): c_format F32 (1<<4), a/b TF32
@@ -587,11 +592,27 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   __syncwarp();
 
   // ---------------------------------- epilogue ----------------------------------------
+  // Eight warps: warp w drains TMEM lanes 32 (w & 3) .. +31 (the quadrant a warp may read), columns
+  // [(w >> 2) BN / 2, +BN / 2).  With four warps -- one per scheduler -- every dependent-issue stall of the
+  // epilogue's instruction stream was exposed: 1.0 us per 32-column pass, 2.5 us of a 7.2 us (1024,512,512) GEMM
+  // (tools/probe.py gemm, profiles/r2l), whatever the store pattern.
+  const int quad = warp & 3, chalf = warp >> 2;
+  const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+  const int j4 = (lane & 7) * 4, rsub = lane >> 3;
+  // interior tile, aligned output: no bounds checks, no per-element branches
+  const bool ws_mode = p.ws != nullptr;
+  const bool fast = (m0 + BM <= p.M) && (n0 + BN <= p.N) && p.cluster <= 1 &&
+                    (ws_mode ? ((p.N & 3) == 0) : (vec_ok && (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0)));
+  float4 bq[BN / 64];                                   // this lane's bias columns, fetched under the main loop
+#pragma unroll
+  for (int c = 0; c < BN / 64; ++c) {
+    bq[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (fast && !ws_mode && p.bias) bq[c] = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + chalf * (BN / 2) + c * 32 + j4));
+  }
   mbar_wait_warp(tmem_full_bar, 0);
   tcgen05_fence_after();
   __syncwarp();
-  const int row = m0 + warp * 32 + lane;
-  const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+  MC_STAMP(gemm, 4);
   if (p.cluster > 1) {
     // Split-K inside a thread-block cluster: the S = gridDim.z CTAs of one output tile each hold a
     // partial accumulator.  Every CTA parks its partial in its own shared memory (the operand ring is
@@ -599,11 +620,11 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
     // through distributed shared memory, in slice order 0..S-1 (deterministic), and applies the
     // epilogue.  No workspace in HBM, no second kernel (splitk_reduce_kernel + its launch gap were
     // 12% of the C3 step).  Parked layout: row r at r*BN*4, its 16-byte chunk j at slot j ^ (r & 7).
-    const int r_local = warp * 32 + lane;
+    const int r_local = quad * 32 + lane;
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
+    for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
       float v[32];
-      tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+      tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
       const uint32_t rbase = smem_base + (uint32_t)r_local * (BN * 4u);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -628,61 +649,132 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
     }
     return;
   }
-#pragma unroll 1
-  for (int c0 = 0; c0 < BN; c0 += 32) {
-    float v[32];
-    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
-    if (row < p.M && num_kb > 0) {
-      const int col0 = n0 + c0;
-      if (p.ws) {
-        float* dst = p.ws + ((int64_t)blockIdx.z * p.M + row) * p.N + col0;
-        if ((p.N & 3) == 0 && col0 + 32 <= p.N) {
+  // A thread reads one ROW of the accumulator (32 columns a pass).  The warp's 32 x 32 block is turned through
+  // shared memory (the operand ring is idle once tmem_full has fired; 4 KB a warp, 16-byte chunks XOR-swizzled by
+  // row) so that eight lanes write one 128-byte row segment and a warp store covers four whole lines.
+  const uint32_t stage = smem_base + (uint32_t)warp * 4096u;
+  const uint32_t st_addr = stage + (uint32_t)lane * 128u, st_x = (uint32_t)(lane & 7);
+  const int row0 = m0 + quad * 32;
+  if (fast) {
+    float* base;
+    int64_t ld;
+    if (ws_mode) { base = p.ws + ((int64_t)blockIdx.z * p.M + row0 + rsub) * p.N + n0 + j4; ld = p.N; }
+    else { base = p.C + (int64_t)(row0 + rsub) * p.ldc + n0 + j4; ld = p.ldc; }
+    const int mode = ws_mode ? 0 : (p.accumulate ? 2 : (p.relu ? 1 : 0));
+    const int relu = ws_mode ? 0 : p.relu;
+    const float negv = (relu == 2) ? -0.0f : 0.f;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-        } else {
+    for (int c = 0; c < BN / 64; ++c) {
+      const int c0 = chalf * (BN / 2) + c * 32;
+      float v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+      if (num_kb <= 0) continue;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) if (col0 + j < p.N) dst[j] = v[j];
+      for (int j = 0; j < 8; ++j)
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(st_addr + (((uint32_t)j ^ st_x) * 16u)), "f"(v[4 * j]),
+                     "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+      __syncwarp();
+      const float4 b4 = bq[c];
+      float* d = base + c0;
+      float4 o[8];
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int rr = it * 4 + rsub;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o[it].x), "=f"(o[it].y), "=f"(o[it].z), "=f"(o[it].w)
+                     : "r"(stage + (uint32_t)rr * 128u + (uint32_t)(((lane & 7) ^ (rr & 7)) * 16)) : "memory");
+      }
+      float4 cv[8];
+      if (mode == 2) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it) cv[it] = *reinterpret_cast<const float4*>(d + (int64_t)(it * 4) * ld);
+      }
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        float4 t = make_float4(o[it].x + b4.x, o[it].y + b4.y, o[it].z + b4.z, o[it].w + b4.w);
+        if (mode == 2) { t.x += cv[it].x; t.y += cv[it].y; t.z += cv[it].z; t.w += cv[it].w; }
+        if (relu) {                                     // relu_apply without branches: NaN passes, -x -> negv, +-0 -> +0
+          t.x = (t.x < 0.f) ? negv : ((t.x == 0.f) ? 0.f : t.x); t.y = (t.y < 0.f) ? negv : ((t.y == 0.f) ? 0.f : t.y);
+          t.z = (t.z < 0.f) ? negv : ((t.z == 0.f) ? 0.f : t.z); t.w = (t.w < 0.f) ? negv : ((t.w == 0.f) ? 0.f : t.w);
         }
-      } else {
-        float* dst = p.C + (int64_t)row * p.ldc + col0;
-        if (vec_ok && col0 + 32 <= p.N) {
+        *reinterpret_cast<float4*>(d + (int64_t)(it * 4) * ld) = t;
+      }
+      __syncwarp();                                     // the block is reused by the next pass
+    }
+  } else {
+    const bool ws_vec = (p.N & 3) == 0;
+#pragma unroll 1
+    for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
+      float v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+      if (num_kb <= 0) continue;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            if (p.bias) {
-              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-              o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-            }
+      for (int j = 0; j < 8; ++j)
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(st_addr + (((uint32_t)j ^ st_x) * 16u)), "f"(v[4 * j]),
+                     "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+      __syncwarp();
+      const int col = n0 + c0 + j4;                     // this lane's four columns, the same in every row
+      const bool full4 = col + 4 <= p.N;
+      float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!p.ws && p.bias) {
+        if (col < p.N) b4.x = __ldg(p.bias + col);
+        if (col + 1 < p.N) b4.y = __ldg(p.bias + col + 1);
+        if (col + 2 < p.N) b4.z = __ldg(p.bias + col + 2);
+        if (col + 3 < p.N) b4.w = __ldg(p.bias + col + 3);
+      }
+#pragma unroll 1
+      for (int it = 0; it < 8; ++it) {
+        const int rr = it * 4 + rsub;
+        float4 o;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
+                     : "r"(stage + (uint32_t)rr * 128u + (uint32_t)(((lane & 7) ^ (rr & 7)) * 16)) : "memory");
+        const int orow = row0 + rr;
+        if (orow >= p.M || col >= p.N) continue;
+        if (p.ws) {
+          float* dst = p.ws + ((int64_t)blockIdx.z * p.M + orow) * p.N + col;
+          if (ws_vec && full4) *reinterpret_cast<float4*>(dst) = o;
+          else {
+            dst[0] = o.x;
+            if (col + 1 < p.N) dst[1] = o.y;
+            if (col + 2 < p.N) dst[2] = o.z;
+            if (col + 3 < p.N) dst[3] = o.w;
+          }
+        } else {
+          float* dst = p.C + (int64_t)orow * p.ldc + col;
+          o.x += b4.x; o.y += b4.y; o.z += b4.z; o.w += b4.w;
+          if (vec_ok && full4) {
             if (p.accumulate) {
-              const float4 c = *reinterpret_cast<const float4*>(dst + j);
-              o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
+              const float4 cv = *reinterpret_cast<const float4*>(dst);
+              o.x += cv.x; o.y += cv.y; o.z += cv.z; o.w += cv.w;
             }
             if (p.relu) {
               o.x = relu_apply(o.x, p.relu); o.y = relu_apply(o.y, p.relu);
               o.z = relu_apply(o.z, p.relu); o.w = relu_apply(o.w, p.relu);
             }
-            *reinterpret_cast<float4*>(dst + j) = o;
-          }
-        } else {
+            *reinterpret_cast<float4*>(dst) = o;
+          } else {
+            const float ov[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (col0 + j < p.N) {
-              float o = v[j];
-              if (p.bias) o += __ldg(p.bias + col0 + j);
-              if (p.accumulate) o += dst[j];
-              if (p.relu) o = relu_apply(o, p.relu);
-              dst[j] = o;
+            for (int e2 = 0; e2 < 4; ++e2) {
+              if (col + e2 < p.N) {
+                float t = ov[e2];
+                if (p.accumulate) t += dst[e2];
+                if (p.relu) t = relu_apply(t, p.relu);
+                dst[e2] = t;
+              }
             }
           }
         }
       }
+      __syncwarp();                                     // the block is reused by the next pass
     }
   }
+  MC_STAMP(gemm, 5);
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
   }
+  MC_STAMP(gemm, 6);
   if (p.ws && p.counters) {
     // Split-K without a second kernel: the LAST slice CTA of a tile to arrive adds the partials in
     // slice order 0..S-1 (the same order whichever CTA happens to be last: deterministic) and

@@ -52,7 +52,20 @@ def case_bnb(lib, N=1024, D=512):
                                                N, D, 1, 0.5, 1234, 0, 1), D // 8, keep)
 
 
-CASES = {'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
+def case_gemm(lib, M=1024, N=512, K=512, ta=0, tb=0, bias=1, relu=0):
+    """Stamps: 0 entry, 1 barriers + TMEM ready, 2 after the PDL wait, 3 producer issued its last TMA load,
+    4 accumulator complete, 5 tile stored, 6 TMEM released."""
+    rng = np.random.RandomState(0)
+    A = dev(rng.randn(*((K, M) if ta else (M, K))).astype(np.float32))
+    B = dev(rng.randn(*((N, K) if tb else (K, N))).astype(np.float32))
+    bv = dev(rng.randn(N).astype(np.float32))
+    C = ops.empty((M, N))
+    keep = (A, B, bv, C)
+    return (lambda: lib.mc_gemm(ta, tb, M, N, K, A.ptr, M if ta else K, B.ptr, K if tb else N, C.ptr, N,
+                                bv.ptr if bias else None, relu, 0, 1), 1024, keep)
+
+
+CASES = {'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
 
 
 def main():
@@ -62,18 +75,23 @@ def main():
     blocks = min(1024, blocks)
     read = getattr(lib.cdll, 'mc_probe_read_' + tag)
     read.argtypes = [ctypes.c_void_p]
-    buf = np.zeros(1024 * 8, np.uint64)
+    buf = np.zeros(1024 * 16, np.uint64)
     for it in range(6):
         call()
         lib.mc_sync()
         assert read(buf.ctypes.data) == 0
-        t = buf.reshape(1024, 8)[:blocks].astype(np.int64)
-        used = [i for i in range(8) if t[:, i].max() > 0]
+        t = buf.reshape(1024, 16)[:blocks].astype(np.int64)
+        if it == 0:
+            first = t.copy()
+            continue
+        live = (t != first).any(axis=1) if tag == 'gemm' else np.ones(len(t), bool)   # blocks this launch has
+        t = t[live]
+        used = [i for i in range(16) if t[:, i].max() > 0]
         t0 = t[:, 0].min()
         if it < 3:
             continue
         print('%s it %d: %d blocks, entry spread %d ns; last block past stamp i at (ns): %s'
-              % (tag, it, blocks, t[:, 0].max() - t0, [int(t[:, i].max() - t0) for i in used]))
+              % (tag, it, len(t), t[:, 0].max() - t0, [int(t[:, i].max() - t0) for i in used]))
         full = [i for i in used if (t[:, i] >= t0).all()]
         ph = np.diff(t[:, full], axis=1)
         print('   phases between stamps %s: median %s  max %s'
