@@ -495,6 +495,38 @@ struct ConvWgradParams {
 // Per 32-pixel chunk a CTA loads dy ONCE (only the 32-filter blocks that exist) and one shifted
 // window of x per tap; tap t accumulates into TMEM columns [t*BNc, (t+1)*BNc).  The CTA of tap
 // group 0 also multiplies dy by a block of ones: that is the bias gradient, for free.
+// A warp's 32 (rows = filters, one per lane) x 32 (columns) block of partial sums to  dst_row0 + r * ld + c :
+// turned through shared memory (4 KB at `stage`, 16-byte chunks XOR-swizzled by row) so that eight lanes write one
+// 128-byte row segment.  Storing straight from the row-per-lane TMEM layout was 32 scalar stores per lane and tap,
+// every warp store touching 32 lines: 13 of the 31 us of the weight-gradient kernel (tools/probe.py wgh, r2l).
+__device__ __forceinline__ void store_block_staged(uint32_t stage, const float (&v)[32], float* __restrict__ dst_row0, int64_t ld,
+                                                    int rows_left, int cols_left, bool vec) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stage + (uint32_t)lane * 128u + (uint32_t)((j ^ (lane & 7)) * 16)),
+                 "f"(v[4 * j]), "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+  __syncwarp();
+  const int j4 = (lane & 7) * 4, rsub = lane >> 3;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int rr = it * 4 + rsub;
+    float4 o;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
+                 : "r"(stage + (uint32_t)rr * 128u + (uint32_t)(((lane & 7) ^ (rr & 7)) * 16)) : "memory");
+    if (rr >= rows_left || j4 >= cols_left) continue;
+    float* d = dst_row0 + (int64_t)rr * ld + j4;
+    if (vec && j4 + 4 <= cols_left) *reinterpret_cast<float4*>(d) = o;
+    else {
+      d[0] = o.x;
+      if (j4 + 1 < cols_left) d[1] = o.y;
+      if (j4 + 2 < cols_left) d[2] = o.z;
+      if (j4 + 3 < cols_left) d[3] = o.w;
+    }
+  }
+  __syncwarp();
+}
+
 __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy,
                                                                       const __grid_constant__ CUtensorMap tmX,
                                                                       const ConvWgradParams p) {
@@ -616,17 +648,20 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_kernel(const __gri
   __syncwarp();
   const int f = f0 + warp * 32 + lane;
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint32_t stage = smem_base + (uint32_t)warp * 4096u;      // the operand ring is idle now
+  const bool ws_vec = (p.Nn & 3) == 0 && (reinterpret_cast<uintptr_t>(p.ws) & 15u) == 0;
   for (int t = 0; t < ntap; ++t) {
-    float* __restrict__ dst = p.ws + (((int64_t)blockIdx.y * taps + tap0 + t) * p.F + f) * p.Nn;
+    float* __restrict__ dst0 = p.ws + (((int64_t)blockIdx.y * taps + tap0 + t) * p.F + f0 + warp * 32) * p.Nn;
 #pragma unroll 1
     for (int c0 = 0; c0 < p.BNc; c0 += 32) {
       float v[32];
       tmem_ld32(lane_addr + (uint32_t)(t * p.BNc + c0), v);
-      if (f < p.F) {
+      if (num_it <= 0) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (c0 + j < p.Nn) dst[c0 + j] = (num_it > 0) ? v[j] : 0.f;
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
       }
+      if (f0 + warp * 32 < p.F && c0 < p.Nn)
+        store_block_staged(stage, v, dst0 + c0, p.Nn, p.F - (f0 + warp * 32), p.Nn - c0, ws_vec);
     }
   }
   if (do_bias) {
@@ -665,11 +700,13 @@ struct ConvWgradHaloParams {
   uint32_t ring_bytes;   // stages * stage_bytes, padded so that the 4-block A descriptor of the last stage stays inside
 };
 
+MC_PROBE_DEFINE(wgh)
 template <int TWC>   // column shifts known at compile time (1 = merged rows, 3 = 3x3 filter), 0 = run time
 __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const __grid_constant__ CUtensorMap tmDy,
                                                                            const __grid_constant__ CUtensorMap tmX,
                                                                            const ConvWgradHaloParams p) {
   extern __shared__ uint8_t smem_raw[];
+  MC_STAMP(wgh, 0);
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   constexpr uint32_t fblk = 128u * 128u;                        // [128 pixels][32 f]
   const int TH = p.g.TH, TW = TWC ? TWC : p.g.TW, taps = TH * TW;
@@ -711,7 +748,9 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  MC_STAMP(wgh, 1);
   mc::pdl_sync();      // prologue done (on-chip state only); global memory from here on
+  MC_STAMP(wgh, 2);
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
@@ -785,18 +824,23 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
   mbar_wait_warp(tmem_full_bar, 0);
   tcgen05_fence_after();
   __syncwarp();
+  MC_STAMP(wgh, 3);
   if (p.dbg && blockIdx.x + blockIdx.y + blockIdx.z == 0 && threadIdx.x == 64) p.dbg[(2 * 32 + 0) * 4 + 1] = clock64();
   const int f = f0 + warp * 32 + lane;
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint32_t stage = smem_base + (uint32_t)warp * 4096u;      // the operand ring is idle now
+  const bool ws_vec = (p.Nn & 3) == 0 && (reinterpret_cast<uintptr_t>(p.ws) & 15u) == 0;
   for (int tw = 0; tw < TW; ++tw) {
     for (int th = 0; th < TH; ++th) {
       float v[32];
       tmem_ld32(lane_addr + (uint32_t)((tw * TH + th) * 32), v);
-      if (f < p.F && warp < fblocks) {
-        float* __restrict__ dst = p.ws + (((int64_t)blockIdx.y * taps + th * TW + tw) * p.F + f) * p.Nn + c0;
+      if (num_it <= 0) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (c0 + j < p.Nn) dst[j] = (num_it > 0) ? v[j] : 0.f;
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+      }
+      if (warp < fblocks && f0 + warp * 32 < p.F && c0 < p.Nn) {
+        float* __restrict__ dst0 = p.ws + (((int64_t)blockIdx.y * taps + th * TW + tw) * p.F + f0 + warp * 32) * p.Nn + c0;
+        store_block_staged(stage, v, dst0, p.Nn, p.F - (f0 + warp * 32), p.Nn - c0, ws_vec);
       }
     }
   }
@@ -806,11 +850,13 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_wgrad_halo_kernel(const 
     if (f < p.F && warp < fblocks) p.ws_bias[(int64_t)blockIdx.y * p.F + f] = (num_it > 0) ? v[0] : 0.f;
   }
   if (p.dbg && blockIdx.x + blockIdx.y + blockIdx.z == 0 && threadIdx.x == 64) p.dbg[(2 * 32 + 0) * 4 + 2] = clock64();
+  MC_STAMP(wgh, 4);
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tcols) : "memory");
   }
+  MC_STAMP(wgh, 5);
 }
 
 // dw (F, C, KH, KW) = sum_z ws[z][tap][f][n] (merged: tap = kh, n = kw*Cp + c; else tap = kh*KW+kw, n = c)

@@ -65,7 +65,21 @@ def case_gemm(lib, M=1024, N=512, K=512, ta=0, tb=0, bias=1, relu=0):
                                 bv.ptr if bias else None, relu, 0, 1), 1024, keep)
 
 
-CASES = {'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
+def case_wgh(lib, layer=1, B=512):
+    """conv_wgrad_halo_kernel on C4 layer 0 / 1 / 2.  Stamps: 0 entry, 1 set-up done, 2 after the PDL wait,
+    3 accumulators complete, 4 partials stored, 5 TMEM released."""
+    C, F, HW = ((3, 32, 32), (32, 64, 16), (64, 128, 8))[layer]
+    rng = np.random.RandomState(0)
+    wpad = 1 if layer == 0 else 0
+    Cp = (C + 3) // 4 * 4
+    x = dev(rng.randn(B, HW, HW + 2 * wpad, Cp).astype(np.float32))
+    dy = dev(rng.randn(B, HW, HW, F).astype(np.float32))
+    dw, db = ops.empty((F, C, 3, 3)), ops.empty((F,))
+    keep = (x, dy, dw, db)
+    return (lambda: lib.mc_conv2d_nhwc_wgrad(x.ptr, dy.ptr, dw.ptr, db.ptr, B, C, HW, HW, Cp, wpad, F, F, 3, 3, 1), 1024, keep)
+
+
+CASES = {'wgh': case_wgh, 'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
 
 
 def main():
@@ -84,7 +98,7 @@ def main():
         if it == 0:
             first = t.copy()
             continue
-        live = (t != first).any(axis=1) if tag == 'gemm' else np.ones(len(t), bool)   # blocks this launch has
+        live = (t != first).any(axis=1) if tag in ('gemm', 'wgh') else np.ones(len(t), bool)   # blocks this launch has
         t = t[live]
         used = [i for i in range(16) if t[:, i].max() > 0]
         t0 = t[:, 0].min()
