@@ -301,7 +301,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
     const bool vec_ok = ((p.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15u) == 0);
     const int grp = warp >> 2, quarter = warp & 3;
     int acc = grp % NACC;
-    uint32_t aph = 0;
+    uint32_t aph = 0, xpar = 0;                       // xpar: which half of the pooled epilogue's exchange buffer
     const int first = blockIdx.x + grp * gridDim.x, stride = 2 * gridDim.x;
     int pt = first % ptiles, nt = first / ptiles;
     const int dpt = stride % ptiles, dnt = stride / ptiles;
@@ -329,79 +329,93 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) conv_igemm_kernel(const __gr
         float v[32];
         tmem_ld32(tacc + (uint32_t)c0, v);
         if (p.pool) {
-          // ---- bias, relu, 2x2 max pooling: candidates in window order (0,0) (0,1) (1,0) (1,1), first maximum wins
+          // ---- bias, relu, 2x2 max pooling.  Candidates in window order (0,0) (0,1) (1,0) (1,1), the first maximum
+          // wins, a NaN beats numbers (maxpool_nhwc_fwd's rule).  The four lanes of a window split the 32 channels:
+          // a lane trades the half it does not keep with its horizontal neighbour, then the quarter it does not
+          // keep with its vertical neighbour, and finishes 8 channels -- 24 shuffles, all lanes storing.  (The first
+          // version shuffled every channel three times and left the result in one lane of four: ~1100 instructions
+          // and ~5000 cycles per 32 channels, which made all three C4 layers epilogue-bound: profiles/r2l.)
+          // relu commutes with the maximum; where it flattens the whole window to zero the first candidate wins.
           const int f0 = n0 + c0;
-          uint32_t kk[8];                      // window index of the winner so far, one byte per channel
+          if (p.bias) {
+            if ((reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) kk[j] = 0u;
-          const bool odd_col = (ow & 1) != 0;
+              for (int j = 0; j < 32; j += 4) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + f0 + j));
+                v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+              }
+            } else {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float a = v[j];
-            if (p.bias) a += __ldg(p.bias + f0 + j);
-            if (p.relu) a = (a != a) ? a : fmaxf(a, 0.f);
-            if (!live) a = -INFINITY;
-            const float b = __shfl_xor_sync(0xffffffffu, a, 1);           // the horizontal neighbour
-            // even column: (a = kw 0, b = kw 1); the odd lane computes the same pair mirrored and is not used
-            const float left = odd_col ? b : a, right = odd_col ? a : b;
-            const bool take_right = (right > left) || (right != right && left == left);
-            v[j] = take_right ? right : left;
-            kk[j >> 2] |= (take_right ? 1u : 0u) << (8 * (j & 3));
+              for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + f0 + j);
+            }
+          }
+          const bool hp = (lane & 1) != 0;      // odd column of the window
+          float m1[16];
+          uint32_t kb = 0;                      // bit s: the right-hand candidate won channel s of the kept half
+#pragma unroll
+          for (int s2 = 0; s2 < 16; ++s2) {
+            const float mine = hp ? v[16 + s2] : v[s2];
+            const float send = hp ? v[s2] : v[16 + s2];
+            const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+            const float left = hp ? recv : mine, right = hp ? mine : recv;
+            const bool tr = !(left >= right) && (left == left);
+            m1[s2] = tr ? right : left;
+            kb |= (tr ? 1u : 0u) << s2;
           }
           const bool within_warp = p.g.OWv < 32;
-          bool top;                             // this lane holds the TOP row of its window
+          const bool vp = within_warp ? (((lane >> p.g.owv_shift) & 1) != 0) : ((quarter & 1) != 0);   // bottom row
+          float own[8], rcv[8];
+          uint32_t okb;
           if (within_warp) {
             const int rowbit = 1 << p.g.owv_shift;
-            top = (lane & rowbit) == 0;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float other = __shfl_xor_sync(0xffffffffu, v[j], rowbit);
-              const uint32_t ko = __shfl_xor_sync(0xffffffffu, (kk[j >> 2] >> (8 * (j & 3))) & 0xffu, rowbit);
-              const float tv = top ? v[j] : other, bv = top ? other : v[j];
-              const uint32_t tk = top ? ((kk[j >> 2] >> (8 * (j & 3))) & 0xffu) : ko;
-              const uint32_t bk = (top ? ko : ((kk[j >> 2] >> (8 * (j & 3))) & 0xffu)) + 2u;
-              const bool take_bottom = (bv > tv) || (bv != bv && tv == tv);
-              v[j] = take_bottom ? bv : tv;
-              kk[j >> 2] = (kk[j >> 2] & ~(0xffu << (8 * (j & 3)))) | ((take_bottom ? bk : tk) << (8 * (j & 3)));
+            for (int s2 = 0; s2 < 8; ++s2) {
+              own[s2] = vp ? m1[8 + s2] : m1[s2];
+              rcv[s2] = __shfl_xor_sync(0xffffffffu, vp ? m1[s2] : m1[8 + s2], rowbit);
             }
+            okb = __shfl_xor_sync(0xffffffffu, kb, rowbit);
           } else {
-            // rows of a window live in two warps (quarter q and q ^ 1): the bottom warp parks its horizontal
-            // winners in shared memory, the top warp finishes.  Two named barriers per chunk (data ready / buffer free).
-            top = (quarter & 1) == 0;
+            // the rows of a window live in two warps (quarter q and q ^ 1): 48 bytes per lane through shared memory,
+            // double-buffered by pass so that one named barrier per pass is enough
             const int pair = grp * 2 + (quarter >> 1);
-            float* xm = reinterpret_cast<float*>(smem_raw + ((smem_base - smem_u32(smem_raw)) + p.pool_smem)) + pair * (16 * 33 + 16 * 9);
-            uint32_t* xk = reinterpret_cast<uint32_t*>(xm + 16 * 33);
-            if (!top && !odd_col) {
+            const uint32_t xbase = smem_base + p.pool_smem + (uint32_t)((pair * 2 + (int)xpar) * 3072);
+            const uint32_t mine_at = xbase + (uint32_t)(((quarter & 1) * 32 + lane) * 48);
+            const uint32_t peer_at = xbase + (uint32_t)((((quarter & 1) ^ 1) * 32 + lane) * 48);
+            xpar ^= 1u;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) xm[(lane >> 1) * 33 + j] = v[j];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) xk[(lane >> 1) * 9 + j] = kk[j];
-            }
+            for (int s2 = 0; s2 < 8; ++s2) own[s2] = vp ? m1[8 + s2] : m1[s2];
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(mine_at), "f"(vp ? m1[0] : m1[8]), "f"(vp ? m1[1] : m1[9]),
+                         "f"(vp ? m1[2] : m1[10]), "f"(vp ? m1[3] : m1[11]) : "memory");
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(mine_at + 16u), "f"(vp ? m1[4] : m1[12]), "f"(vp ? m1[5] : m1[13]),
+                         "f"(vp ? m1[6] : m1[14]), "f"(vp ? m1[7] : m1[15]) : "memory");
+            asm volatile("st.shared.b32 [%0], %1;" ::"r"(mine_at + 32u), "r"(kb) : "memory");
             asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
-            if (top && !odd_col) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const float bv = xm[(lane >> 1) * 33 + j];
-                const uint32_t bk = ((xk[(lane >> 1) * 9 + (j >> 2)] >> (8 * (j & 3))) & 0xffu) + 2u;
-                const uint32_t tk = (kk[j >> 2] >> (8 * (j & 3))) & 0xffu;
-                const bool take_bottom = (bv > v[j]) || (bv != bv && v[j] == v[j]);
-                v[j] = take_bottom ? bv : v[j];
-                kk[j >> 2] = (kk[j >> 2] & ~(0xffu << (8 * (j & 3)))) | ((take_bottom ? bk : tk) << (8 * (j & 3)));
-              }
-            }
-            asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(rcv[0]), "=f"(rcv[1]), "=f"(rcv[2]), "=f"(rcv[3]) : "r"(peer_at) : "memory");
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(rcv[4]), "=f"(rcv[5]), "=f"(rcv[6]), "=f"(rcv[7]) : "r"(peer_at + 16u) : "memory");
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(okb) : "r"(peer_at + 32u) : "memory");
           }
-          if (live && top && !odd_col) {
-            const int POH = p.g.OH >> 1, POW = p.g.OW >> 1;
-            const int64_t at = (((int64_t)n * POH + (oh >> 1)) * POW + (ow >> 1)) * p.ldy + f0;
-            float* __restrict__ dst = p.y + at;
+          const uint32_t mybits = (vp ? (kb >> 8) : kb) & 0xffu, otherbits = (vp ? (okb >> 8) : okb) & 0xffu;
+          const uint32_t topbits = vp ? otherbits : mybits, botbits = vp ? mybits : otherbits;
+          float outv[8];
+          uint32_t kk0 = 0, kk1 = 0;
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            if (p.pidx) {
-              uint4* __restrict__ di = reinterpret_cast<uint4*>(p.pidx + at);
-              di[0] = make_uint4(kk[0], kk[1], kk[2], kk[3]);
-              di[1] = make_uint4(kk[4], kk[5], kk[6], kk[7]);
-            }
+          for (int s2 = 0; s2 < 8; ++s2) {
+            const float top = vp ? rcv[s2] : own[s2], bot = vp ? own[s2] : rcv[s2];
+            const bool tb = !(top >= bot) && (top == top);
+            float val = tb ? bot : top;
+            uint32_t idx = tb ? (2u + ((botbits >> s2) & 1u)) : ((topbits >> s2) & 1u);
+            if (p.relu && !(val > 0.f) && val == val) { val = 0.f; idx = 0u; }
+            outv[s2] = val;
+            if (s2 < 4) kk0 |= idx << (8 * s2);
+            else kk1 |= idx << (8 * (s2 - 4));
+          }
+          if (live) {
+            const int POH = p.g.OH >> 1, POW = p.g.OW >> 1;
+            const int64_t at = (((int64_t)n * POH + (oh >> 1)) * POW + (ow >> 1)) * p.ldy + f0 + (hp ? 16 : 0) + (vp ? 8 : 0);
+            float* __restrict__ dst = p.y + at;
+            *reinterpret_cast<float4*>(dst) = make_float4(outv[0], outv[1], outv[2], outv[3]);
+            *reinterpret_cast<float4*>(dst + 4) = make_float4(outv[4], outv[5], outv[6], outv[7]);
+            if (p.pidx) *reinterpret_cast<uint2*>(p.pidx + at) = make_uint2(kk0, kk1);
           }
           continue;
         }
@@ -1185,7 +1199,7 @@ int conv_igemm(const float* x, const float* w, const float* bias, float* y, int 
   if (pool && p.g.OWv >= 32) {          // cross-warp exchange area of the pooled epilogue: 4 warp pairs
     const size_t used = (p.wres ? w_bytes : 0) + stages * stage_bytes + (2 * stages + 2 * nacc + 1) * 8 + 16;
     p.pool_smem = (uint32_t)((used + 15) & ~(size_t)15);
-    smem = p.pool_smem + 4 * (16 * 33 + 16 * 9) * 4 + 1024;
+    smem = p.pool_smem + 4 * 2 * 3072 + 1024;        // 4 warp pairs x 2 buffers x (64 lanes x 48 bytes)
   }
 
   CUtensorMap tmX, tmW;
