@@ -216,6 +216,17 @@ int mc_softmax_ce_fwd(const float* x, const int32_t* labels_i32, const float* on
  * loss[0].  A classifier head (integer labels, cols <= 32) is ONE launch (warp per row, last block sums). */
 int mc_softmax_ce_fused(const float* x, const int32_t* labels_i32, const float* onehot,
                         float* probs, float* dx, float* loss, int64_t rows, int64_t cols);
+/* mc_softmax_ce_fused for callers that cannot allocate.  NO counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * Same results as mc_softmax_ce_fused with integer labels (probs or dx may be NULL, not both), but the row losses and
+ * the ticket counter live in a file-scope `static __device__` array of the library (257 KB per GPU, held until
+ * exit) instead of the scratch arena: the call makes no cudaMalloc / cudaFree / allocating library call.
+ * Limits: cols <= 32, rows <= MC_SOFTMAX_CE_STATIC_MAX_ROWS; anything larger is rejected (status 2, mc_last_error
+ * says which limit).  All calls share the one array: calls that overlap on the GPU (different streams, devices are
+ * separate) race; calls on the library's stream are ordered and safe. */
+#define MC_SOFTMAX_CE_STATIC_MAX_ROWS 65536
+int mc_softmax_ce_fused_static(const float* x, const int32_t* labels_i32, float* probs, float* dx, float* loss,
+                               int64_t rows, int64_t cols);
 /* The classifier head as one launch: logits = h (rows, K) . W (K, C) + bias, C <= 16; loss[0] = softmax_loss(logits,
  * labels) (nn/layers.py:27, 201-221); dlogits = (softmax - onehot) / rows (numpy_core.py:170-175); dh = dlogits . W^T
  * (the VJP of the affine with respect to its input; dh / logits may be NULL).  FP32 arithmetic. */

@@ -625,6 +625,57 @@ int mc_softmax_ce_fused(const float* x, const int32_t* labels, const float* oneh
   return 0;
 }
 
+// ---- softmax_loss with no allocation at all -------------------------------------------------------------
+// The row losses and the ticket counter of softmax_ce_small_kernel live in a file-scope device array instead of
+// the scratch arena / a cudaMalloc'd counter, for callers that cannot allocate (graph capture, serving loops).
+// Every GPU that loads the library holds these 257 KB until exit.  Layout: [0, MAX_ROWS) row losses, then one
+// 256-byte line whose first word is the ticket counter.
+static __device__ __align__(256) float g_ce_static_scratch[MC_SOFTMAX_CE_STATIC_MAX_ROWS + 64];
+
+// The array's name is a host-side stand-in in host code; the device address comes from cudaGetSymbolAddress,
+// asked once per device with that device current.
+static float* ce_static_scratch_ptr() {
+  static float* ptrs[16] = {};
+  const int dev = device();
+  if (dev < 0 || dev >= 16) { mc::set_error("mc_init has not selected a device"); return nullptr; }
+  if (!ptrs[dev]) {
+    int current = -1;
+    cudaError_t e = cudaGetDevice(&current);
+    if (e == cudaSuccess && current != dev) e = cudaSetDevice(dev);
+    void* p = nullptr;
+    if (e == cudaSuccess) e = cudaGetSymbolAddress(&p, g_ce_static_scratch);
+    if (e != cudaSuccess || !p) {
+      mc::set_error("cudaGetSymbolAddress(g_ce_static_scratch) on device %d: %s", dev, cudaGetErrorString(e));
+      cudaGetLastError();
+      return nullptr;
+    }
+    ptrs[dev] = static_cast<float*>(p);
+  }
+  return ptrs[dev];
+}
+
+int mc_softmax_ce_fused_static(const float* x, const int32_t* labels, float* probs, float* dx, float* loss, int64_t rows,
+                               int64_t cols) {
+  MC_REQUIRE(x != nullptr && labels != nullptr && loss != nullptr, "x, labels and loss are required");
+  MC_REQUIRE(probs != nullptr || dx != nullptr, "nothing to write");
+  MC_REQUIRE(rows > 0 && cols > 0, "empty input");
+  MC_REQUIRE(cols <= 32, "more than 32 classes: beyond the static-scratch variant (use mc_softmax_ce_fused)");
+  MC_REQUIRE(rows <= MC_SOFTMAX_CE_STATIC_MAX_ROWS,
+             "rows beyond MC_SOFTMAX_CE_STATIC_MAX_ROWS (65536): the static scratch cannot hold them (use mc_softmax_ce_fused)");
+  float* scratch = ce_static_scratch_ptr();
+  if (!scratch) return 1;
+  float* rowloss = scratch;
+  int* counter = reinterpret_cast<int*>(scratch + MC_SOFTMAX_CE_STATIC_MAX_ROWS);
+  // the array keeps the last call's contents: the ticket counter must start at zero (a memset node, no allocation);
+  // every row loss the last block reads is rewritten by this call
+  MC_CHECK(cudaMemsetAsync(counter, 0, sizeof(int), stream()));
+  const unsigned blocks = (unsigned)((rows + CE_THREADS / 32 - 1) / (CE_THREADS / 32));
+  mc::launch(softmax_ce_small_kernel, blocks, CE_THREADS, 0, x, labels, probs, dx, loss, rowloss, counter, (int)rows, (int)cols,
+             1.f / (float)rows);
+  MC_LAUNCHED();
+  return 0;
+}
+
 int mc_temporal_softmax_loss(const float* x, const int32_t* y, const float* mask, float* dx, float* loss, int64_t rows,
                              int64_t cols, int64_t batch) {
   MC_REQUIRE(rows > 0 && cols > 0 && batch > 0, "empty input");
