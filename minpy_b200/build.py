@@ -18,7 +18,7 @@ BUILD_DIR = os.path.join(HERE, '_build')
 LIB_PATH = os.path.join(HERE, 'libminpy_cuda.so')
 HEADER = os.path.join(os.path.dirname(HERE), 'include', 'minpy_cuda.h')
 
-SOURCES = ['runtime.cu', 'elementwise.cu', 'reduce.cu', 'softmax.cu', 'index.cu', 'gemm.cu', 'layers.cu', 'lstm.cu', 'conv.cu', 'conv_tc.cu', 'comm.cu']
+SOURCES = ['runtime.cu', 'elementwise.cu', 'reduce.cu', 'softmax.cu', 'index.cu', 'gemm.cu', 'layers.cu', 'lstm.cu', 'lstm_persist.cu', 'conv.cu', 'conv_tc.cu', 'comm.cu']
 
 NVCC_FLAGS = [
     '-gencode', 'arch=compute_100a,code=sm_100a',

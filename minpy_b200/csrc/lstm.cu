@@ -26,6 +26,9 @@ struct LstmEpilogue {        // must match gemm.cu
 int gemm_tf32_lstm(int mode, int64_t M, int64_t N, int64_t K, const float* A, int64_t lda, const float* B, int64_t ldb,
                    const tc::LstmEpilogue& epi, int* taken);                    // gemm.cu
 
+int lstm_persist_fwd(const float* A, const float* Wh, float* hbuf, float* cbuf, float* gates, int64_t T, int64_t N, int64_t H,
+                     int* taken);                                               // lstm_persist.cu
+
 constexpr int LS_THREADS = 256;
 
 // Wh (H, 4H) gate-major columns [i | f | o | g]  ->  unit-major columns: out[k, 4u + g] = in[k, g*H + u]
@@ -190,6 +193,11 @@ int mc_lstm_seq_fwd(float* A, const float* Wh, float* hbuf, float* cbuf, float* 
   const int64_t sH = N * H, sA = N * 4 * H;
   float* ws = nullptr;
   const bool try_partials = (precision == MC_GEMM_TF32);
+  if (try_partials) {          // all T steps as ONE persistent launch with Wh resident in shared memory
+    int taken = 0;
+    if (lstm_persist_fwd(A, Wh, hbuf, cbuf, gates, T, N, H, &taken)) return 1;
+    if (taken) return 0;
+  }
   ScratchFrame scratch;
   if (try_partials) { ws = scratch.floats((size_t)(LS_MAX_SPLITS * sA)); if (!ws) return 1; }
   int rc = 0;

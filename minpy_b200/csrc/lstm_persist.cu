@@ -1,0 +1,361 @@
+// lstm_temporal (nn/layers.py:383-420) forward as ONE persistent launch for all T time steps.
+//
+// The launch-per-step path of lstm.cu streams Wh (H x 4H, 16.8 MB at H = 1024) from L2 for every step and pays
+// two launches per step (10.5 us per step on C5: 7 us GEMM + 3.5 us gate kernel, profiles/r2m).  Here Wh never
+// moves after the first microsecond: H/8 CTAs (128 at H = 1024, one per SM) form H/32 clusters of four; cluster c
+// owns hidden units [32c, 32c+32) = 128 gate columns, CTA q of the cluster owns the K slice [q H/4, (q+1) H/4) of
+// those columns, H/4 x 128 floats = 128 KB of shared memory at H = 1024, loaded once.  Per time step a CTA
+//   1. waits for the H/32 CTAs that produce its K slice of h_{t-1} (one flag word each, release / acquire),
+//   2. streams that slice (128 rows x H/4, 128 KB) through a four-stage TMA ring into tcgen05 MMAs
+//      (M = 128 batch rows, N = 128 gate columns, accumulator in TMEM),
+//   3. parks the partial tile in its own shared memory (the ring is idle by then), and after a cluster barrier
+//      sums rows [32q, 32q+32) of the four partials through distributed shared memory in slice order 0..3,
+//   4. adds the input projection a_t = x_t . Wx + b (fetched under the MMAs), applies the gate arithmetic of
+//      lstm_step (layers.py:353-380: i, f, o sigmoid, g tanh, c' = f c + i g, h' = o tanh(c')), keeps c in
+//      registers, writes h_t / c_t / gates for the backward pass and publishes its flag.
+// Per step and CTA: 128 KB from L2 instead of 256 KB, no partial tile in HBM, no launch.
+#include <initializer_list>
+#include <stdlib.h>
+#include "tc_common.cuh"
+
+namespace mc {
+namespace tc {
+
+constexpr int LP_THREADS = 256;
+constexpr int LP_S = 4;                       // CTAs per cluster = K slices
+constexpr int LP_STAGES = 6;
+constexpr uint32_t LP_TILE = 128 * 32 * 4;    // one k-block of an operand: 128 rows x 128 B
+constexpr uint32_t LP_RING = LP_STAGES * LP_TILE;   // 96 KB operand ring; its first 64 KB later hold the parked partial (128 x 128 fp32)
+constexpr int LP_MAX_KB = 8;                  // k-blocks per CTA and step (H / 128)
+
+struct LstmPersistParams {
+  const float* ax;     // (T, N, 4H) input projections, gate-major columns [i | f | o | g]
+  float* hbuf;         // (T + 1, N, H), slot 0 = h0
+  float* cbuf;         // (T + 1, N, H), slot 0 = c0
+  float* gates;        // (T, N, 4H)
+  int* flags;          // one word per CTA: number of hidden states it has published (zero at launch)
+  int T, N, H;
+};
+
+// Wp[(32c.. packed column) , k] = Wh[k, g H + 32 c + ul], packed column = 128 c + 32 g + ul: the 128 gate columns of
+// cluster c side by side, K-major (k contiguous) so that one TMA box (32 k x 128 columns) is an UMMA B tile.
+__global__ void __launch_bounds__(256) lstm_pack_wh_kernel(const float* __restrict__ Wh, float* __restrict__ Wp, int H) {
+  mc::pdl_sync();
+  __shared__ float tile[32][33];
+  const int k0 = blockIdx.x * 32;             // 32 k's
+  const int strip = blockIdx.y;               // 32 packed columns: strip = 4 c + g
+  const int c = strip >> 2, g = strip & 3;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;     // 8 rows a pass
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int k = k0 + ty + 8 * i;
+    tile[ty + 8 * i][tx] = Wh[(int64_t)k * 4 * H + (int64_t)g * H + 32 * c + tx];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int ul = ty + 8 * i;
+    Wp[(int64_t)(128 * c + 32 * g + ul) * H + k0 + tx] = tile[tx][ul];
+  }
+}
+
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Gate non-linearities on the special-function unit: 16 of them per thread sit on the critical path of every time
+// step (the accurate expf / tanhf / IEEE division versions cost 1.0 us per step).  Absolute error ~1e-7, three orders
+// below the TF32 rounding of the recurrent product they are applied to.
+__device__ __forceinline__ float lp_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }   // layers.py:243
+__device__ __forceinline__ float lp_tanh(float x) {
+  const float e = __expf(-2.0f * fabsf(x));                  // in (0, 1]: no overflow
+  return copysignf(__fdividef(1.0f - e, 1.0f + e), x);
+}
+
+MC_PROBE_DEFINE(lstmp)   // tools/probe.sh: %globaltimer stamps of the second-to-last time step
+#define LP_STAMP(i) do { if (t == p.T - 2) { MC_STAMP(lstmp, i); } } while (0)
+__global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_fwd_kernel(const __grid_constant__ CUtensorMap tmH,
+                                                                         const __grid_constant__ CUtensorMap tmW,
+                                                                         const LstmPersistParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t ring = smem_base;                                   // [0, 64 KB)
+  const uint32_t wres = smem_base + LP_RING;                         // resident Wh slice: kb_per tiles
+  const int kb_per = p.H >> 7;                                       // (H / 4) / 32
+  const uint32_t bar_base = wres + (uint32_t)kb_per * LP_TILE;       // full[4], empty[4], tmem_full, w_full
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (LP_STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * LP_STAGES);
+  const uint32_t w_full_bar = tmem_full_bar + 8u;
+  const uint32_t tmem_slot = w_full_bar + 8u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int cluster = blockIdx.x / LP_S;
+  const int k_base = (int)rank * (p.H >> 2);
+  const int nprod = p.H >> 5;                                        // CTAs that produce this K slice of h
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmH)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW)) : "memory");
+    for (int s = 0; s < LP_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    mbar_init(w_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  mc::pdl_sync();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  // the resident Wh slice: kb_per boxes of 32 k x 128 packed columns
+  if (warp == 0 && elect_one()) {
+    mbar_expect_tx(w_full_bar, (uint32_t)kb_per * LP_TILE);
+    for (int kb = 0; kb < kb_per; ++kb) tma_load_2d(wres + (uint32_t)kb * LP_TILE, &tmW, w_full_bar, k_base + 32 * kb, 128 * cluster);
+  }
+  __syncwarp();
+
+  // this thread's cells: batch row 32 rank + r, hidden units unit0 .. unit0 + 3
+  const int r = threadIdx.x >> 3, j = threadIdx.x & 7;
+  const int trow = (int)rank * 32 + r;                  // row inside the 128-row tile = batch row
+  const bool live = trow < p.N;
+  const int unit0 = 32 * cluster + 4 * j;
+  const int64_t H = p.H, sH = (int64_t)p.N * H, sA = 4 * sH;
+  const int64_t cell = (int64_t)trow * H + unit0, gcell = (int64_t)trow * 4 * H + unit0;
+  float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (live) c = *reinterpret_cast<const float4*>(p.cbuf + cell);
+  // peers in the order rank, rank + 1, ...: at any moment the four CTAs of a cluster read four DIFFERENT shared
+  // memories (distributed shared memory is served by the owner's port at ~20 B/clk); the order is fixed per CTA, so
+  // the sums stay deterministic
+  uint32_t peer[LP_S];
+#pragma unroll
+  for (int z = 0; z < LP_S; ++z)
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(peer[z]) : "r"(ring), "r"((rank + (uint32_t)z) & (LP_S - 1)));
+
+  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  const uint64_t desc0 = make_desc(0, 16, 1024, 2);
+  int s = 0;                 // ring position and phase: the producer thread and the MMA thread each carry their own copy
+  uint32_t ph = 0;
+  const int quad = warp & 3, chalf = warp >> 2;
+  const int prow = quad * 32 + lane;                    // accumulator row this thread parks
+  const bool leader = elect_one();                      // the same lane of each warp for the whole sequence
+
+  for (int t = 0; t < p.T; ++t) {
+    LP_STAMP(0);
+    // input projection of this step: in flight while the recurrent product is computed
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0, a3 = a0;
+    if (live) {
+      const float* ap = p.ax + (int64_t)t * sA + gcell;
+      a0 = __ldcs(reinterpret_cast<const float4*>(ap));
+      a1 = __ldcs(reinterpret_cast<const float4*>(ap + H));
+      a2 = __ldcs(reinterpret_cast<const float4*>(ap + 2 * H));
+      a3 = __ldcs(reinterpret_cast<const float4*>(ap + 3 * H));
+    }
+    if (warp == 0) {
+      // k-block kb of this CTA's K slice = the 32 hidden units of cluster (rank H/128 + kb): complete once that
+      // cluster's four CTAs (flags 4 kb .. 4 kb + 3 of the slice) have published t states.  Every lane polls its own
+      // producer (one L2 round trip per poll, all in parallel); the loads go out in order as their four flags arrive.
+      // (The proxy fence between the producers' generic-proxy stores and these async-proxy reads is on the WRITER's
+      //  side, before its flag: it costs ~0.6 us, and a fence per acquire here put 8 of them on the critical path.)
+      bool seen = (t == 0) || (lane >= nprod);
+      const int* f = p.flags + (int)rank * nprod + (lane < nprod ? lane : 0);
+      int issued = 0;
+      long long t0 = 0;
+      while (issued < kb_per) {
+        if (!seen) seen = ld_acquire_gpu(f) >= t;
+        const uint32_t ready = __ballot_sync(0xffffffffu, seen);
+        if (issued == 0) LP_STAMP(1);
+        while (issued < kb_per && ((ready >> (4 * issued)) & 0xFu) == 0xFu) {
+          if (leader) {
+            mbar_wait(empty_bar(s), ph ^ 1u);
+            mbar_expect_tx(full_bar(s), LP_TILE);
+            tma_load_2d(ring + (uint32_t)s * LP_TILE, &tmH, full_bar(s), k_base + 32 * issued, t * p.N);
+            if (++s == LP_STAGES) { s = 0; ph ^= 1u; }
+          }
+          ++issued;
+        }
+        if (ready != 0xffffffffu) {            // a missing CTA must be an error, never a hung GPU
+          if (t0 == 0) t0 = clock64();
+          else if (clock64() - t0 > 2000000000LL) __trap();
+        }
+      }
+      __syncwarp();
+      LP_STAMP(2);
+    } else if (warp == 1 && leader) {
+      if (t == 0) mbar_wait(w_full_bar, 0);
+      for (int kb = 0; kb < kb_per; ++kb) {
+        mbar_wait(full_bar(s), ph);
+        tcgen05_fence_after();
+        const uint64_t adesc = desc0 + (uint64_t)(((ring + (uint32_t)s * LP_TILE) & 0x3FFFFu) >> 4);
+        const uint64_t bdesc = desc0 + (uint64_t)(((wres + (uint32_t)kb * LP_TILE) & 0x3FFFFu) >> 4);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_tf32(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        umma_commit(empty_bar(s));
+        if (++s == LP_STAGES) { s = 0; ph ^= 1u; }
+      }
+      umma_commit(tmem_full_bar);
+    }
+    __syncwarp();
+    mbar_wait_warp(tmem_full_bar, (uint32_t)(t & 1));
+    tcgen05_fence_after();
+    __syncwarp();
+    LP_STAMP(3);
+    // park the partial tile: row r at r * 512 B, its 16-byte chunk j at slot j ^ (r & 7)
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      const int c0 = chalf * 64 + cc * 32;
+      float v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+      const uint32_t rbase = ring + (uint32_t)prow * 512u;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const uint32_t slot = (uint32_t)((c0 >> 2) + q) ^ (uint32_t)(prow & 7);
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(rbase + slot * 16u), "f"(v[4 * q]), "f"(v[4 * q + 1]),
+                     "f"(v[4 * q + 2]), "f"(v[4 * q + 3]) : "memory");
+      }
+    }
+    tcgen05_fence_before();
+    LP_STAMP(4);
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    LP_STAMP(5);
+    // recurrent pre-activations of this thread's four units: gate g sits in packed columns 32 g + 4 j .. + 3
+    float4 part[4][LP_S];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const uint32_t off = (uint32_t)trow * 512u + (uint32_t)((8 * g + j) ^ (trow & 7)) * 16u;
+#pragma unroll
+      for (int z = 1; z < LP_S; ++z)
+        asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(part[g][z].x), "=f"(part[g][z].y), "=f"(part[g][z].z), "=f"(part[g][z].w) : "r"(peer[z] + off) : "memory");
+    }
+    // this CTA's own partial through the local port: a quarter of the bytes off the ~20 B/clk cluster path
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const uint32_t off = (uint32_t)trow * 512u + (uint32_t)((8 * g + j) ^ (trow & 7)) * 16u;
+      asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(part[g][0].x), "=f"(part[g][0].y), "=f"(part[g][0].z), "=f"(part[g][0].w) : "r"(ring + off) : "memory");
+    }
+    float4 pre[4] = {a0, a1, a2, a3};
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+#pragma unroll
+      for (int z = 0; z < LP_S; ++z) { pre[g].x += part[g][z].x; pre[g].y += part[g][z].y; pre[g].z += part[g][z].z; pre[g].w += part[g][z].w; }
+    }
+    // peers may overwrite their ring (= the parked tiles) only after every CTA of the cluster has read them: the loads
+    // above have returned (their values were just added), so the arrival needs no release fence (it cost 1.4 us)
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+    LP_STAMP(6);
+    float4 gi, gf, go, gg, h;
+#define LP_CELL(m)                                                                                             \
+    gi.m = lp_sigmoid(pre[0].m); gf.m = lp_sigmoid(pre[1].m); go.m = lp_sigmoid(pre[2].m); gg.m = lp_tanh(pre[3].m); \
+    c.m = gf.m * c.m + gi.m * gg.m; h.m = go.m * lp_tanh(c.m);
+    LP_CELL(x) LP_CELL(y) LP_CELL(z) LP_CELL(w)
+#undef LP_CELL
+    // h first: it is what the other CTAs wait for; c and the gates (read by the backward pass) follow the flag
+    if (live) *reinterpret_cast<float4*>(p.hbuf + (int64_t)(t + 1) * sH + cell) = h;
+    LP_STAMP(7);
+    __syncthreads();
+    LP_STAMP(8);
+    if (threadIdx.x == 0) {
+      // the block barrier ordered every thread's h stores before this point; the proxy fence orders them against the
+      // consumers' TMA (async-proxy) reads; st.release carries the gpu-scope fence (a separate __threadfence cost 0.5 us)
+      asm volatile("fence.proxy.async.global;" ::: "memory");
+      LP_STAMP(9);
+      st_release_gpu(p.flags + blockIdx.x, t + 1);
+    }
+    LP_STAMP(10);
+    if (live) {
+      *reinterpret_cast<float4*>(p.cbuf + (int64_t)(t + 1) * sH + cell) = c;
+      float* gp = p.gates + (int64_t)t * sA + gcell;
+      __stcs(reinterpret_cast<float4*>(gp), gi);
+      __stcs(reinterpret_cast<float4*>(gp + H), gf);
+      __stcs(reinterpret_cast<float4*>(gp + 2 * H), go);
+      __stcs(reinterpret_cast<float4*>(gp + 3 * H), gg);
+    }
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    LP_STAMP(11);
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+}
+
+}  // namespace tc
+
+// The whole forward recurrence as one launch.  *taken = 0 (nothing launched) when the shape is outside the
+// kernel's range (N <= 128, H a multiple of 128 up to 1024, 16-byte aligned buffers), when the device cannot
+// hold all H/32 clusters at once (the CTAs wait for each other), or with MC_LSTM_PERSIST=0.
+int lstm_persist_fwd(const float* A, const float* Wh, float* hbuf, float* cbuf, float* gates, int64_t T, int64_t N, int64_t H,
+                     int* taken) {
+  using namespace tc;
+  *taken = 0;
+  static int enabled = -1;
+  if (enabled < 0) { const char* e = getenv("MC_LSTM_PERSIST"); enabled = (e && e[0] == '0') ? 0 : 1; }
+  if (!enabled || T <= 0 || N <= 0 || N > 128 || H < 128 || H > 1024 || (H & 127)) return 0;
+  if (T * N >= (int64_t)1 << 30) return 0;
+  for (const void* q : {(const void*)A, (const void*)Wh, (const void*)hbuf, (const void*)cbuf, (const void*)gates})
+    if (!aligned16(q)) return 0;
+  const int kb_per = (int)(H >> 7), ctas = (int)(H >> 3);
+  const size_t smem = (size_t)LP_RING + (size_t)kb_per * LP_TILE + 128 + 1024;
+  static uint32_t configured = 0;
+  if (first_use_on_device(&configured))
+    MC_CHECK(cudaFuncSetAttribute(lstm_persist_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(LP_RING + LP_MAX_KB * LP_TILE + 128 + 1024)));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(LP_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream();
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = LP_S; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  // every CTA waits for others: all clusters must be resident at once
+  static int fits[16][LP_MAX_KB + 1] = {};          // [device][kb_per]: 0 unknown, 1 yes, -1 no
+  int& fit = fits[device() & 15][kb_per];
+  if (fit == 0) {
+    int nclusters = 0;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&nclusters, lstm_persist_fwd_kernel, &cfg);
+    if (e != cudaSuccess) { cudaGetLastError(); nclusters = 0; }
+    fit = (nclusters >= ctas / LP_S) ? 1 : -1;
+  }
+  if (fit < 0) return 0;
+
+  ScratchFrame scratch;
+  float* wp = scratch.floats((size_t)(4 * H * H));
+  int* flags = reinterpret_cast<int*>(scratch.floats((size_t)ctas));
+  if (!wp || !flags) return 1;
+  mc::launch(lstm_pack_wh_kernel, dim3((unsigned)(H / 32), (unsigned)(4 * H / 32)), 256, 0, Wh, wp, (int)H);
+  MC_LAUNCHED();
+  MC_CHECK(cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)ctas, stream()));
+  CUtensorMap tmH, tmW;
+  {
+    const uint64_t dims[2] = {(uint64_t)H, (uint64_t)((T + 1) * N)};
+    const uint64_t strides[1] = {(uint64_t)H * 4};
+    const uint32_t box[2] = {32, 128};
+    if (make_tmap(&tmH, hbuf, 2, dims, strides, box, false)) return 1;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)H, (uint64_t)(4 * H)};
+    const uint64_t strides[1] = {(uint64_t)H * 4};
+    const uint32_t box[2] = {32, 128};
+    if (make_tmap(&tmW, wp, 2, dims, strides, box, false)) return 1;
+  }
+  LstmPersistParams p;
+  p.ax = A; p.hbuf = hbuf; p.cbuf = cbuf; p.gates = gates; p.flags = flags; p.T = (int)T; p.N = (int)N; p.H = (int)H;
+  MC_CHECK(cudaLaunchKernelEx(&cfg, lstm_persist_fwd_kernel, tmH, tmW, p));
+  count_launch();
+  *taken = 1;
+  return 0;
+}
+
+}  // namespace mc

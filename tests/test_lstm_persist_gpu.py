@@ -1,0 +1,112 @@
+"""mc_lstm_seq_fwd / mc_lstm_seq_bwd as ONE persistent launch per direction (csrc/lstm_persist.cu) through the C ABI,
+against a float64 restatement of lstm_step / lstm_temporal (nn/layers.py:353-420: gates i, f, o sigmoid, g tanh,
+c' = f c + i g, h' = o tanh(c')) and its hand-derived BPTT, on shapes inside the kernel's range (N <= 128,
+H a multiple of 128 up to 1024) -- the launch count proves which path ran -- and one outside (falls back)."""
+import ctypes
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TF32_TOL = 3e-3      # measured 7e-4 per contraction (profiles/r2m/gemm_sweep.log); errors feed back through T steps
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    return float(np.max(np.abs(a - b)) / max(1e-30, np.max(np.abs(b))))
+
+
+def up(a):
+    from minpy_b200.cuda_array import CudaArray
+    return CudaArray.from_numpy(a)
+
+
+def launches(lib):
+    n = ctypes.c_uint64()
+    lib.mc_launch_count(ctypes.byref(n))
+    return n.value
+
+
+def sig(x):
+    return 1.0 / (1.0 + np.exp(-x))
+
+
+def forward64(A, Wh, h0, c0):
+    """(T, N, 4H) input projections -> hbuf (T+1, N, H), cbuf, gates (T, N, 4H) in float64."""
+    T, N, H4 = A.shape
+    H = H4 // 4
+    hb, cb, gt = np.zeros((T + 1, N, H)), np.zeros((T + 1, N, H)), np.zeros((T, N, H4))
+    hb[0], cb[0] = h0, c0
+    for t in range(T):
+        a = A[t] + hb[t].dot(Wh)
+        i, f, o, g = sig(a[:, :H]), sig(a[:, H:2 * H]), sig(a[:, 2 * H:3 * H]), np.tanh(a[:, 3 * H:])
+        cb[t + 1] = f * cb[t] + i * g
+        hb[t + 1] = o * np.tanh(cb[t + 1])
+        gt[t] = np.concatenate([i, f, o, g], axis=1)
+    return hb, cb, gt
+
+
+def backward64(gt, cb, Wh, dH):
+    """dH (T+1, N, H): slot t+1 holds the upstream gradient of h_t; returns dA (T, N, 4H) and dh0."""
+    T, N, H4 = gt.shape
+    H = H4 // 4
+    dA = np.zeros((T, N, H4))
+    dh = dH[T].copy()
+    dc = np.zeros((N, H))
+    for t in range(T - 1, -1, -1):
+        i, f, o, g = gt[t, :, :H], gt[t, :, H:2 * H], gt[t, :, 2 * H:3 * H], gt[t, :, 3 * H:]
+        tc = np.tanh(cb[t + 1])
+        dcc = dh * o * (1 - tc * tc) + dc
+        dA[t] = np.concatenate([dcc * g * i * (1 - i), dcc * cb[t] * f * (1 - f), dh * tc * o * (1 - o), dcc * i * (1 - g * g)], axis=1)
+        dc = dcc * f
+        dh = dH[t] + dA[t].dot(Wh.T)
+    return dA, dh
+
+
+SHAPES = [(5, 128, 128), (7, 100, 256), (4, 128, 512), (6, 128, 1024), (3, 17, 128), (12, 64, 384)]
+
+
+def make(T, N, H, seed):
+    rng = np.random.RandomState(seed)
+    A = rng.randn(T, N, 4 * H).astype(np.float32)
+    Wh = (rng.randn(H, 4 * H) / np.sqrt(H)).astype(np.float32)
+    h0 = (rng.randn(N, H) * 0.5).astype(np.float32)
+    c0 = (rng.randn(N, H) * 0.5).astype(np.float32)
+    return A, Wh, h0, c0
+
+
+def run_fwd(lib, A, Wh, h0, c0):
+    T, N, H4 = A.shape
+    H = H4 // 4
+    hb = np.zeros((T + 1, N, H), np.float32)
+    cb = np.zeros((T + 1, N, H), np.float32)
+    hb[0], cb[0] = h0, c0
+    dA, dW, dh, dc, dg = up(A), up(Wh), up(hb), up(cb), up(np.zeros((T, N, H4), np.float32))
+    n0 = launches(lib)
+    lib.mc_lstm_seq_fwd(dA.ptr, dW.ptr, dh.ptr, dc.ptr, dg.ptr, T, N, H, lib.MC_GEMM_TF32)
+    return dh, dc, dg, dW, launches(lib) - n0
+
+
+@pytest.mark.parametrize('T,N,H', SHAPES)
+def test_persistent_forward_matches_float64(cuda, T, N, H):
+    lib = cuda.L()
+    A, Wh, h0, c0 = make(T, N, H, seed=T + H)
+    for _ in range(2):                       # twice: the flags and the parked tiles start from the last call's state
+        dh, dc, dg, _, n = run_fwd(lib, A, Wh, h0, c0)
+        assert n == 2, 'expected the packing kernel + ONE persistent launch, saw %d launches' % n
+        hb, cb, gt = forward64(A.astype(np.float64), Wh.astype(np.float64), h0, c0)
+        assert rel(dh.asnumpy(), hb) <= TF32_TOL
+        assert rel(dc.asnumpy(), cb) <= TF32_TOL
+        assert rel(dg.asnumpy(), gt) <= TF32_TOL
+
+
+def test_shape_outside_the_range_falls_back(cuda):
+    lib = cuda.L()
+    T, N, H = 3, 40, 96
+    A, Wh, h0, c0 = make(T, N, H, seed=9)
+    dh, dc, dg, _, n = run_fwd(lib, A, Wh, h0, c0)
+    assert n >= 2 * T
+    hb, cb, gt = forward64(A.astype(np.float64), Wh.astype(np.float64), h0, c0)
+    assert rel(dh.asnumpy(), hb) <= TF32_TOL and rel(dg.asnumpy(), gt) <= TF32_TOL

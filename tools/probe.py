@@ -79,7 +79,20 @@ def case_wgh(lib, layer=1, B=512):
     return (lambda: lib.mc_conv2d_nhwc_wgrad(x.ptr, dy.ptr, dw.ptr, db.ptr, B, C, HW, HW, Cp, wpad, F, F, 3, 3, 1), 1024, keep)
 
 
-CASES = {'wgh': case_wgh, 'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
+def case_lstmp(lib, T=100, N=128, H=1024):
+    """lstm_persist_fwd_kernel, second-to-last time step.  Stamps: 0 step begins, 1 producers' flags seen, 2 TMA loads
+    issued, 3 accumulator complete, 4 partial parked, 5 cluster barrier passed, 6 partials summed, 7 gate arithmetic done
+    and stores issued, 8 block barrier, 9 flag published, 10 second cluster barrier passed."""
+    rng = np.random.RandomState(0)
+    A = dev(rng.randn(T, N, 4 * H).astype(np.float32))
+    Wh = dev((rng.randn(H, 4 * H) / np.sqrt(H)).astype(np.float32))
+    hb, cb = dev(np.zeros((T + 1, N, H), np.float32)), dev(np.zeros((T + 1, N, H), np.float32))
+    gt = dev(np.zeros((T, N, 4 * H), np.float32))
+    keep = (A, Wh, hb, cb, gt)
+    return (lambda: lib.mc_lstm_seq_fwd(A.ptr, Wh.ptr, hb.ptr, cb.ptr, gt.ptr, T, N, H, 1), H // 8, keep)
+
+
+CASES = {'lstmp': case_lstmp, 'wgh': case_wgh, 'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
 
 
 def main():
