@@ -28,6 +28,8 @@ int gemm_tf32_lstm(int mode, int64_t M, int64_t N, int64_t K, const float* A, in
 
 int lstm_persist_fwd(const float* A, const float* Wh, float* hbuf, float* cbuf, float* gates, int64_t T, int64_t N, int64_t H,
                      int* taken);                                               // lstm_persist.cu
+int lstm_persist_bwd(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA, int64_t T, int64_t N, int64_t H,
+                     int* taken);
 
 constexpr int LS_THREADS = 256;
 
@@ -249,6 +251,11 @@ int mc_lstm_seq_bwd(const float* gates, const float* cbuf, const float* Wh, floa
   const int64_t sH = N * H, sA = N * 4 * H;
   float *ws = nullptr, *dc = nullptr;
   const bool try_partials = (precision == MC_GEMM_TF32);
+  if (try_partials) {          // all T steps as ONE persistent launch with Wh resident in shared memory
+    int taken = 0;
+    if (lstm_persist_bwd(gates, cbuf, Wh, dH, dA, T, N, H, &taken)) return 1;
+    if (taken) return 0;
+  }
   ScratchFrame scratch;
   if (try_partials) { ws = scratch.floats((size_t)(LS_MAX_SPLITS * sH)); if (!ws) return 1; }
   dc = scratch.floats((size_t)(2 * sH));

@@ -292,6 +292,243 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_fwd_kernel(const _
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Backward (BPTT of lstm_step, numpy_core VJPs of layers.py:353-380) as one persistent launch.
+// The recurrent product of the backward pass, dA_t . Wh^T, has K = 4H and only H output columns: four times the
+// broadcast volume of the forward pass for a quarter of the output.  H/64 clusters of EIGHT CTAs: cluster c owns
+// the 64 hidden units [64c, 64c+64) (rows of Wh, which as stored IS the K-major B operand -- no packing), CTA q
+// owns the K slice [q H/2, (q+1) H/2) of the 4H gate columns (gate q / 2, one half of its units): H/2 x 64
+// floats = 128 KB resident at H = 1024.  Per step: wait for the CTAs that produced this slice of dA_{t+1}, stream
+// it (128 rows x H/2) into M = 128 / N = 64 MMAs, park the partial (32 KB), cluster barrier, sum rows
+// [16q, 16q+16) of the eight partials through distributed shared memory, add the upstream gradient dH[t+1], run
+// the gate backward for those 16 rows x 64 units (dc stays in registers), write dA_t, publish.
+constexpr int LB_S = 8;
+constexpr uint32_t LB_BTILE = 64 * 32 * 4;    // 8 KB: 64 units x 32 k
+constexpr int LB_MAX_KB = 16;
+
+struct LstmPersistBwdParams {
+  const float* gates;  // (T, N, 4H)
+  const float* cbuf;   // (T + 1, N, H)
+  float* dH;           // (T + 1, N, H): slot t + 1 = upstream gradient of h_t; slot 0 receives dL/dh0
+  float* dA;           // (T, N, 4H) out
+  int* flags;
+  int T, N, H;
+};
+
+MC_PROBE_DEFINE(lstmb)
+#define LB_STAMP(i) do { if (it == p.T - 2) { MC_STAMP(lstmb, i); } } while (0)
+__global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const __grid_constant__ CUtensorMap tmD,
+                                                                         const __grid_constant__ CUtensorMap tmW,
+                                                                         const LstmPersistBwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t ring = smem_base;
+  const uint32_t wres = smem_base + LP_RING;
+  const int kb_per = p.H >> 6;                                       // (H / 2) / 32
+  const uint32_t bar_base = wres + (uint32_t)kb_per * LB_BTILE;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (LP_STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * LP_STAGES);
+  const uint32_t w_full_bar = tmem_full_bar + 8u;
+  const uint32_t tmem_slot = w_full_bar + 8u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int cluster = blockIdx.x / LB_S;
+  const int k_base = (int)rank * (p.H >> 1);
+  const int nflags = p.H >> 4;                                       // CTAs that produce this K slice of dA
+  const int flag_base = (int)(rank & 1u) * nflags;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmD)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW)) : "memory");
+    for (int s = 0; s < LP_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    mbar_init(w_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(64u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  mc::pdl_sync();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0 && elect_one()) {      // the resident slice of Wh: kb_per boxes of 32 k x 64 units
+    mbar_expect_tx(w_full_bar, (uint32_t)kb_per * LB_BTILE);
+    for (int kb = 0; kb < kb_per; ++kb) tma_load_2d(wres + (uint32_t)kb * LB_BTILE, &tmW, w_full_bar, k_base + 32 * kb, 64 * cluster);
+  }
+  __syncwarp();
+
+  // this thread's cells: batch row 16 rank + r, hidden units unit0 .. unit0 + 3
+  const int r = threadIdx.x >> 4, j = threadIdx.x & 15;
+  const int trow = (int)rank * 16 + r;
+  const bool live = trow < p.N;
+  const int unit0 = 64 * cluster + 4 * j;
+  const int64_t H = p.H, sH = (int64_t)p.N * H, sA = 4 * sH;
+  const int64_t cell = (int64_t)trow * H + unit0, gcell = (int64_t)trow * 4 * H + unit0;
+  float4 dcn = make_float4(0.f, 0.f, 0.f, 0.f);          // dc flowing in from the later time step
+  uint32_t peer[LB_S];
+#pragma unroll
+  for (int z = 0; z < LB_S; ++z)
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(peer[z]) : "r"(ring), "r"((rank + (uint32_t)z) & (LB_S - 1)));
+
+  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  const uint64_t desc0 = make_desc(0, 16, 1024, 2);
+  int s = 0;
+  uint32_t ph = 0;
+  const int quad = warp & 3, chalf = warp >> 2;
+  const int prow = quad * 32 + lane;
+  const bool leader = elect_one();
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  // iteration `it` runs the recurrent product of the step after t = T - 1 - it (none at it = 0) and the gate
+  // backward of step t; the last iteration (it = T) only has the product: dH[0] += dA_0 . Wh^T
+  for (int it = 0; it <= p.T; ++it) {
+    const int t = p.T - 1 - it;
+    LB_STAMP(0);
+    float4 gi = zero4, gf = zero4, go = zero4, gg = zero4, cn = zero4, cp = zero4, dh = zero4;
+    if (live) {
+      if (it < p.T) {
+        const float* gp = p.gates + (int64_t)t * sA + gcell;
+        gi = __ldcs(reinterpret_cast<const float4*>(gp));
+        gf = __ldcs(reinterpret_cast<const float4*>(gp + H));
+        go = __ldcs(reinterpret_cast<const float4*>(gp + 2 * H));
+        gg = __ldcs(reinterpret_cast<const float4*>(gp + 3 * H));
+        cn = __ldcs(reinterpret_cast<const float4*>(p.cbuf + (int64_t)(t + 1) * sH + cell));
+        cp = __ldcs(reinterpret_cast<const float4*>(p.cbuf + (int64_t)t * sH + cell));
+        dh = __ldcs(reinterpret_cast<const float4*>(p.dH + (int64_t)(t + 1) * sH + cell));
+      } else {
+        dh = *reinterpret_cast<const float4*>(p.dH + cell);
+      }
+    }
+    if (it > 0) {
+      if (warp == 0) {
+        // k-blocks 2 pr, 2 pr + 1 of this K slice = the 64 units of one cluster: ready once its eight CTAs have
+        // published `it` gradients.  Lane l polls producers l and l + 32 of the slice.
+        bool seen0 = lane >= nflags, seen1 = lane + 32 >= nflags;
+        const int* f0 = p.flags + flag_base + (lane < nflags ? lane : 0);
+        const int* f1 = p.flags + flag_base + (lane + 32 < nflags ? lane + 32 : 0);
+        int issued = 0;
+        long long t0 = 0;
+        while (issued < kb_per) {
+          if (!seen0) seen0 = ld_acquire_gpu(f0) >= it;
+          if (!seen1) seen1 = ld_acquire_gpu(f1) >= it;
+          const uint32_t r0 = __ballot_sync(0xffffffffu, seen0), r1 = __ballot_sync(0xffffffffu, seen1);
+          if (issued == 0) LB_STAMP(1);
+          while (issued < kb_per) {
+            const int pr = issued >> 1;
+            const uint32_t m = pr < 4 ? (r0 >> (8 * pr)) : (r1 >> (8 * (pr - 4)));
+            if ((m & 0xFFu) != 0xFFu) break;
+            if (leader) {
+              mbar_wait(empty_bar(s), ph ^ 1u);
+              mbar_expect_tx(full_bar(s), LP_TILE);
+              tma_load_2d(ring + (uint32_t)s * LP_TILE, &tmD, full_bar(s), k_base + 32 * issued, (t + 1) * p.N);
+              if (++s == LP_STAGES) { s = 0; ph ^= 1u; }
+            }
+            ++issued;
+          }
+          if ((r0 & r1) != 0xffffffffu) {          // a missing CTA must be an error, never a hung GPU
+            if (t0 == 0) t0 = clock64();
+            else if (clock64() - t0 > 2000000000LL) __trap();
+          }
+        }
+        __syncwarp();
+        LB_STAMP(2);
+      } else if (warp == 1 && leader) {
+        if (it == 1) mbar_wait(w_full_bar, 0);
+        for (int kb = 0; kb < kb_per; ++kb) {
+          mbar_wait(full_bar(s), ph);
+          tcgen05_fence_after();
+          const uint64_t adesc = desc0 + (uint64_t)(((ring + (uint32_t)s * LP_TILE) & 0x3FFFFu) >> 4);
+          const uint64_t bdesc = desc0 + (uint64_t)(((wres + (uint32_t)kb * LB_BTILE) & 0x3FFFFu) >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_tf32(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar(s));
+          if (++s == LP_STAGES) { s = 0; ph ^= 1u; }
+        }
+        umma_commit(tmem_full_bar);
+      }
+      __syncwarp();
+      mbar_wait_warp(tmem_full_bar, (uint32_t)((it - 1) & 1));
+      tcgen05_fence_after();
+      __syncwarp();
+      LB_STAMP(3);
+      {   // park the partial tile (128 x 64): row r at r * 256 B, its 16-byte chunk j at slot j ^ (r & 7)
+        const int c0 = chalf * 32;
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+        const uint32_t rbase = ring + (uint32_t)prow * 256u;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const uint32_t slot = (uint32_t)((c0 >> 2) + q) ^ (uint32_t)(prow & 7);
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(rbase + slot * 16u), "f"(v[4 * q]), "f"(v[4 * q + 1]),
+                       "f"(v[4 * q + 2]), "f"(v[4 * q + 3]) : "memory");
+        }
+      }
+      tcgen05_fence_before();
+      LB_STAMP(4);
+      asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+      LB_STAMP(5);
+      const uint32_t off = (uint32_t)trow * 256u + (uint32_t)(j ^ (trow & 7)) * 16u;
+      float4 part[LB_S];
+#pragma unroll
+      for (int z = 1; z < LB_S; ++z)
+        asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(part[z].x), "=f"(part[z].y), "=f"(part[z].z), "=f"(part[z].w) : "r"(peer[z] + off) : "memory");
+      asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(part[0].x), "=f"(part[0].y), "=f"(part[0].z), "=f"(part[0].w) : "r"(ring + off) : "memory");
+#pragma unroll
+      for (int z = 0; z < LB_S; ++z) { dh.x += part[z].x; dh.y += part[z].y; dh.z += part[z].z; dh.w += part[z].w; }
+      asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+      LB_STAMP(6);
+    }
+    if (it < p.T) {
+      float4 d0, d1, d2, d3;
+#define LB_CELL(m)                                                          \
+      {                                                                     \
+        const float tc = lp_tanh(cn.m);                                     \
+        const float dc = dh.m * go.m * (1.f - tc * tc) + dcn.m;             \
+        d0.m = dc * gg.m * gi.m * (1.f - gi.m);                             \
+        d1.m = dc * cp.m * gf.m * (1.f - gf.m);                             \
+        d2.m = dh.m * tc * go.m * (1.f - go.m);                             \
+        d3.m = dc * gi.m * (1.f - gg.m * gg.m);                             \
+        dcn.m = dc * gf.m;                                                  \
+      }
+      LB_CELL(x) LB_CELL(y) LB_CELL(z) LB_CELL(w)
+#undef LB_CELL
+      if (live) {
+        float* dp = p.dA + (int64_t)t * sA + gcell;
+        *reinterpret_cast<float4*>(dp) = d0;
+        *reinterpret_cast<float4*>(dp + H) = d1;
+        *reinterpret_cast<float4*>(dp + 2 * H) = d2;
+        *reinterpret_cast<float4*>(dp + 3 * H) = d3;
+      }
+      LB_STAMP(7);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        asm volatile("fence.proxy.async.global;" ::: "memory");
+        st_release_gpu(p.flags + blockIdx.x, it + 1);
+      }
+      LB_STAMP(8);
+    } else if (live) {
+      *reinterpret_cast<float4*>(p.dH + cell) = dh;          // dL/dh0
+    }
+    if (it > 0) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    LB_STAMP(9);
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(64u) : "memory");
+}
+
 }  // namespace tc
 
 // The whole forward recurrence as one launch.  *taken = 0 (nothing launched) when the shape is outside the
@@ -325,6 +562,7 @@ int lstm_persist_fwd(const float* A, const float* Wh, float* hbuf, float* cbuf, 
   if (fit == 0) {
     int nclusters = 0;
     cudaError_t e = cudaOccupancyMaxActiveClusters(&nclusters, lstm_persist_fwd_kernel, &cfg);
+    if (getenv("MC_LSTM_DEBUG")) fprintf(stderr, "lstm_persist_fwd: H=%d needs %d clusters of %d, device holds %d (%s)\n", (int)H, ctas / LP_S, LP_S, nclusters, cudaGetErrorString(e));
     if (e != cudaSuccess) { cudaGetLastError(); nclusters = 0; }
     fit = (nclusters >= ctas / LP_S) ? 1 : -1;
   }
@@ -353,6 +591,69 @@ int lstm_persist_fwd(const float* A, const float* Wh, float* hbuf, float* cbuf, 
   LstmPersistParams p;
   p.ax = A; p.hbuf = hbuf; p.cbuf = cbuf; p.gates = gates; p.flags = flags; p.T = (int)T; p.N = (int)N; p.H = (int)H;
   MC_CHECK(cudaLaunchKernelEx(&cfg, lstm_persist_fwd_kernel, tmH, tmW, p));
+  count_launch();
+  *taken = 1;
+  return 0;
+}
+
+// The whole backward recurrence as one launch (same range and conditions as lstm_persist_fwd).
+int lstm_persist_bwd(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA, int64_t T, int64_t N, int64_t H,
+                     int* taken) {
+  using namespace tc;
+  *taken = 0;
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("MC_LSTM_PERSIST");
+    const char* b = getenv("MC_LSTM_PERSIST_BWD");
+    enabled = ((e && e[0] == '0') || (b && b[0] == '0')) ? 0 : 1;
+  }
+  if (!enabled || T <= 0 || N <= 0 || N > 128 || H < 128 || H > 1024 || (H & 127)) return 0;
+  if (T * N >= (int64_t)1 << 30) return 0;
+  for (const void* q : {(const void*)gates, (const void*)cbuf, (const void*)Wh, (const void*)dH, (const void*)dA})
+    if (!aligned16(q)) return 0;
+  const int kb_per = (int)(H >> 6), ctas = (int)(H >> 3);
+  const size_t smem = (size_t)LP_RING + (size_t)kb_per * LB_BTILE + 128 + 1024;
+  static uint32_t configured = 0;
+  if (first_use_on_device(&configured))
+    MC_CHECK(cudaFuncSetAttribute(lstm_persist_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(LP_RING + LB_MAX_KB * LB_BTILE + 128 + 1024)));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(LP_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream();
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = LB_S; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  static int fits[16][LB_MAX_KB + 1] = {};
+  int& fit = fits[device() & 15][kb_per];
+  if (fit == 0) {
+    int nclusters = 0;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&nclusters, lstm_persist_bwd_kernel, &cfg);
+    if (getenv("MC_LSTM_DEBUG")) fprintf(stderr, "lstm_persist_bwd: H=%d needs %d clusters of %d, device holds %d (%s)\n", (int)H, ctas / LB_S, LB_S, nclusters, cudaGetErrorString(e));
+    if (e != cudaSuccess) { cudaGetLastError(); nclusters = 0; }
+    fit = (nclusters >= ctas / LB_S) ? 1 : -1;
+  }
+  if (fit < 0) return 0;
+
+  ScratchFrame scratch;
+  int* flags = reinterpret_cast<int*>(scratch.floats((size_t)ctas));
+  if (!flags) return 1;
+  MC_CHECK(cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)ctas, stream()));
+  CUtensorMap tmD, tmW;
+  {
+    const uint64_t dims[2] = {(uint64_t)(4 * H), (uint64_t)(T * N)};
+    const uint64_t strides[1] = {(uint64_t)(4 * H) * 4};
+    const uint32_t box[2] = {32, 128};
+    if (make_tmap(&tmD, dA, 2, dims, strides, box, false)) return 1;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)(4 * H), (uint64_t)H};
+    const uint64_t strides[1] = {(uint64_t)(4 * H) * 4};
+    const uint32_t box[2] = {32, 64};
+    if (make_tmap(&tmW, Wh, 2, dims, strides, box, false)) return 1;
+  }
+  LstmPersistBwdParams p;
+  p.gates = gates; p.cbuf = cbuf; p.dH = dH; p.dA = dA; p.flags = flags; p.T = (int)T; p.N = (int)N; p.H = (int)H;
+  MC_CHECK(cudaLaunchKernelEx(&cfg, lstm_persist_bwd_kernel, tmD, tmW, p));
   count_launch();
   *taken = 1;
   return 0;

@@ -92,7 +92,21 @@ def case_lstmp(lib, T=100, N=128, H=1024):
     return (lambda: lib.mc_lstm_seq_fwd(A.ptr, Wh.ptr, hb.ptr, cb.ptr, gt.ptr, T, N, H, 1), H // 8, keep)
 
 
-CASES = {'lstmp': case_lstmp, 'wgh': case_wgh, 'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
+def case_lstmb(lib, T=100, N=128, H=1024):
+    """lstm_persist_bwd_kernel, second-to-last iteration.  Stamps: 0 iteration begins, 1 first producers' flags seen,
+    2 TMA loads issued, 3 accumulator complete, 4 partial parked, 5 cluster barrier passed, 6 partials summed,
+    7 gate backward done and dA stores issued, 8 flag published, 9 second cluster barrier passed."""
+    rng = np.random.RandomState(0)
+    gt = dev(rng.rand(T, N, 4 * H).astype(np.float32))
+    cb = dev((rng.randn(T + 1, N, H) * 0.5).astype(np.float32))
+    Wh = dev((rng.randn(H, 4 * H) / np.sqrt(H)).astype(np.float32))
+    dH = dev((rng.randn(T + 1, N, H) * 0.1).astype(np.float32))
+    dA = dev(np.zeros((T, N, 4 * H), np.float32))
+    keep = (gt, cb, Wh, dH, dA)
+    return (lambda: lib.mc_lstm_seq_bwd(gt.ptr, cb.ptr, Wh.ptr, dH.ptr, dA.ptr, T, N, H, 1), H // 8, keep)
+
+
+CASES = {'lstmb': case_lstmb, 'lstmp': case_lstmp, 'wgh': case_wgh, 'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
 
 
 def main():
