@@ -296,15 +296,19 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_fwd_kernel(const _
 // ---------------------------------------------------------------------------------------------------------
 // Backward (BPTT of lstm_step, numpy_core VJPs of layers.py:353-380) as one persistent launch.
 // The recurrent product of the backward pass, dA_t . Wh^T, has K = 4H and only H output columns: four times the
-// broadcast volume of the forward pass for a quarter of the output.  H/64 clusters of EIGHT CTAs: cluster c owns
-// the 64 hidden units [64c, 64c+64) (rows of Wh, which as stored IS the K-major B operand -- no packing), CTA q
-// owns the K slice [q H/2, (q+1) H/2) of the 4H gate columns (gate q / 2, one half of its units): H/2 x 64
-// floats = 128 KB resident at H = 1024.  Per step: wait for the CTAs that produced this slice of dA_{t+1}, stream
-// it (128 rows x H/2) into M = 128 / N = 64 MMAs, park the partial (32 KB), cluster barrier, sum rows
-// [16q, 16q+16) of the eight partials through distributed shared memory, add the upstream gradient dH[t+1], run
-// the gate backward for those 16 rows x 64 units (dc stays in registers), write dA_t, publish.
+// broadcast volume of the forward pass for a quarter of the output.  Clusters of EIGHT CTAs: cluster c owns the BN
+// hidden units [BN c, BN c + BN) (rows of Wh, which as stored IS the K-major B operand -- no packing), CTA q owns
+// the K slice [q H/2, (q+1) H/2) of the 4H gate columns (gate q / 2, one half of its units).  Per step: wait for
+// the CTAs that produced this slice of dA_{t+1}, stream it (128 rows x H/2) into M = 128 / N = BN MMAs, park the
+// partial, cluster barrier, sum rows [16q, 16q+16) of the eight partials through distributed shared memory, add
+// the upstream gradient dH[t+1], run the gate backward for those 16 rows x BN units (dc stays in registers),
+// write dA_t, publish.  One float4 of units per thread: 4 BN threads.
+//   BN = 64: H/64 clusters, 128 KB of Wh resident at H = 1024, six-stage ring.  This pool's B200 holds 15 clusters
+//            of eight (cudaOccupancyMaxActiveClusters), so H = 1024 (16 clusters) does not fit.
+//   BN = 80: ceil(H/80) clusters (13 at H = 1024; the last one owns 64 live units, the rest of its tile is TMA
+//            zero fill), 160 KB resident, four-stage ring, 320 threads.  A k-block of dA may then straddle the
+//            units of two clusters: it is loaded once both have published.
 constexpr int LB_S = 8;
-constexpr uint32_t LB_BTILE = 64 * 32 * 4;    // 8 KB: 64 units x 32 k
 constexpr int LB_MAX_KB = 16;
 
 struct LstmPersistBwdParams {
@@ -316,20 +320,39 @@ struct LstmPersistBwdParams {
   int T, N, H;
 };
 
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
 MC_PROBE_DEFINE(lstmb)
 #define LB_STAMP(i) do { if (it == p.T - 2) { MC_STAMP(lstmb, i); } } while (0)
-__global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const __grid_constant__ CUtensorMap tmD,
-                                                                         const __grid_constant__ CUtensorMap tmW,
-                                                                         const LstmPersistBwdParams p) {
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(4 * BN, 1) lstm_persist_bwd_kernel(const __grid_constant__ CUtensorMap tmD,
+                                                                     const __grid_constant__ CUtensorMap tmW,
+                                                                     const LstmPersistBwdParams p) {
+  constexpr uint32_t BTILE = BN * 32 * 4;            // one k-block of the resident operand: BN units x 128 B
+  constexpr uint32_t RING = STAGES * LP_TILE;
+  constexpr int CH = BN / 4;                         // 16-byte chunks per parked row
+  constexpr uint32_t ROWB = BN * 4;                  // bytes per parked row
+  constexpr uint32_t TMEM_COLS = BN <= 64 ? 64 : 128;
+  static_assert(128 * ROWB <= RING, "the parked partial lives in the idle ring");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ring = smem_base;
-  const uint32_t wres = smem_base + LP_RING;
+  const uint32_t wres = smem_base + RING;
   const int kb_per = p.H >> 6;                                       // (H / 2) / 32
-  const uint32_t bar_base = wres + (uint32_t)kb_per * LB_BTILE;
+  const uint32_t bar_base = wres + (uint32_t)kb_per * BTILE;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (LP_STAGES + s); };
-  const uint32_t tmem_full_bar = bar_base + 8u * (2 * LP_STAGES);
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
   const uint32_t w_full_bar = tmem_full_bar + 8u;
   const uint32_t tmem_slot = w_full_bar + 8u;
 
@@ -338,20 +361,21 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const _
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
   const int cluster = blockIdx.x / LB_S;
   const int k_base = (int)rank * (p.H >> 1);
-  const int nflags = p.H >> 4;                                       // CTAs that produce this K slice of dA
-  const int flag_base = (int)(rank & 1u) * nflags;
+  const int slice_u0 = (int)(rank & 1u) * (p.H >> 1);                // first hidden unit of this K slice
+  // producers of the slice: clusters c_first .. c_last, flag words 8 c .. 8 c + 7 (= blockIdx.x of their CTAs)
+  const int c_first = slice_u0 / BN, c_last = (slice_u0 + (p.H >> 1) - 1) / BN;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmD)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW)) : "memory");
-    for (int s = 0; s < LP_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     mbar_init(tmem_full_bar, 1);
     mbar_init(w_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(64u) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tcgen05_fence_before();
@@ -361,17 +385,17 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const _
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-  if (warp == 0 && elect_one()) {      // the resident slice of Wh: kb_per boxes of 32 k x 64 units
-    mbar_expect_tx(w_full_bar, (uint32_t)kb_per * LB_BTILE);
-    for (int kb = 0; kb < kb_per; ++kb) tma_load_2d(wres + (uint32_t)kb * LB_BTILE, &tmW, w_full_bar, k_base + 32 * kb, 64 * cluster);
+  if (warp == 0 && elect_one()) {      // the resident slice of Wh: kb_per boxes of 32 k x BN units (rows >= H: zero fill)
+    mbar_expect_tx(w_full_bar, (uint32_t)kb_per * BTILE);
+    for (int kb = 0; kb < kb_per; ++kb) tma_load_2d(wres + (uint32_t)kb * BTILE, &tmW, w_full_bar, k_base + 32 * kb, BN * cluster);
   }
   __syncwarp();
 
   // this thread's cells: batch row 16 rank + r, hidden units unit0 .. unit0 + 3
-  const int r = threadIdx.x >> 4, j = threadIdx.x & 15;
+  const int r = threadIdx.x / CH, j = threadIdx.x % CH;
   const int trow = (int)rank * 16 + r;
-  const bool live = trow < p.N;
-  const int unit0 = 64 * cluster + 4 * j;
+  const int unit0 = BN * cluster + 4 * j;
+  const bool live = trow < p.N && unit0 < p.H;
   const int64_t H = p.H, sH = (int64_t)p.N * H, sA = 4 * sH;
   const int64_t cell = (int64_t)trow * H + unit0, gcell = (int64_t)trow * 4 * H + unit0;
   float4 dcn = make_float4(0.f, 0.f, 0.f, 0.f);          // dc flowing in from the later time step
@@ -380,7 +404,7 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const _
   for (int z = 0; z < LB_S; ++z)
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(peer[z]) : "r"(ring), "r"((rank + (uint32_t)z) & (LB_S - 1)));
 
-  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
   const uint64_t desc0 = make_desc(0, 16, 1024, 2);
   int s = 0;
   uint32_t ph = 0;
@@ -411,31 +435,46 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const _
     }
     if (it > 0) {
       if (warp == 0) {
-        // k-blocks 2 pr, 2 pr + 1 of this K slice = the 64 units of one cluster: ready once its eight CTAs have
-        // published `it` gradients.  Lane l polls producers l and l + 32 of the slice.
-        bool seen0 = lane >= nflags, seen1 = lane + 32 >= nflags;
-        const int* f0 = p.flags + flag_base + (lane < nflags ? lane : 0);
-        const int* f1 = p.flags + flag_base + (lane + 32 < nflags ? lane + 32 : 0);
+        // Lane l polls the flags l, l + 32, l + 64, l + 96 that belong to this slice's producers; a k-block goes
+        // out once the one or two clusters whose units it covers have published `it` gradients (all eight CTAs).
+        bool seen[4];
+        const int* fp[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          const int f = 32 * w + lane;
+          const bool relevant = f >= 8 * c_first && f < 8 * (c_last + 1);
+          seen[w] = !relevant;
+          fp[w] = p.flags + (relevant ? f : 0);
+        }
         int issued = 0;
         long long t0 = 0;
         while (issued < kb_per) {
-          if (!seen0) seen0 = ld_acquire_gpu(f0) >= it;
-          if (!seen1) seen1 = ld_acquire_gpu(f1) >= it;
-          const uint32_t r0 = __ballot_sync(0xffffffffu, seen0), r1 = __ballot_sync(0xffffffffu, seen1);
+          uint32_t rd[4];
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            if (!seen[w]) seen[w] = ld_acquire_gpu(fp[w]) >= it;
+            rd[w] = __ballot_sync(0xffffffffu, seen[w]);
+          }
           if (issued == 0) LB_STAMP(1);
           while (issued < kb_per) {
-            const int pr = issued >> 1;
-            const uint32_t m = pr < 4 ? (r0 >> (8 * pr)) : (r1 >> (8 * (pr - 4)));
-            if ((m & 0xFFu) != 0xFFu) break;
+            const int u_lo = slice_u0 + 32 * issued;
+            const int c_lo = u_lo / BN, c_hi = (u_lo + 31) / BN;
+            bool ok = true;
+            for (int c = c_lo; c <= c_hi; ++c) {
+              const int w = c >> 2;
+              const uint32_t word = w == 0 ? rd[0] : (w == 1 ? rd[1] : (w == 2 ? rd[2] : rd[3]));
+              ok = ok && (((word >> (8 * (c & 3))) & 0xFFu) == 0xFFu);
+            }
+            if (!ok) break;
             if (leader) {
               mbar_wait(empty_bar(s), ph ^ 1u);
               mbar_expect_tx(full_bar(s), LP_TILE);
               tma_load_2d(ring + (uint32_t)s * LP_TILE, &tmD, full_bar(s), k_base + 32 * issued, (t + 1) * p.N);
-              if (++s == LP_STAGES) { s = 0; ph ^= 1u; }
+              if (++s == STAGES) { s = 0; ph ^= 1u; }
             }
             ++issued;
           }
-          if ((r0 & r1) != 0xffffffffu) {          // a missing CTA must be an error, never a hung GPU
+          if ((rd[0] & rd[1] & rd[2] & rd[3]) != 0xffffffffu) {          // a missing CTA must be an error, never a hung GPU
             if (t0 == 0) t0 = clock64();
             else if (clock64() - t0 > 2000000000LL) __trap();
           }
@@ -448,11 +487,11 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const _
           mbar_wait(full_bar(s), ph);
           tcgen05_fence_after();
           const uint64_t adesc = desc0 + (uint64_t)(((ring + (uint32_t)s * LP_TILE) & 0x3FFFFu) >> 4);
-          const uint64_t bdesc = desc0 + (uint64_t)(((wres + (uint32_t)kb * LB_BTILE) & 0x3FFFFu) >> 4);
+          const uint64_t bdesc = desc0 + (uint64_t)(((wres + (uint32_t)kb * BTILE) & 0x3FFFFu) >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k) umma_tf32(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
           umma_commit(empty_bar(s));
-          if (++s == LP_STAGES) { s = 0; ph ^= 1u; }
+          if (++s == STAGES) { s = 0; ph ^= 1u; }
         }
         umma_commit(tmem_full_bar);
       }
@@ -461,23 +500,35 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const _
       tcgen05_fence_after();
       __syncwarp();
       LB_STAMP(3);
-      {   // park the partial tile (128 x 64): row r at r * 256 B, its 16-byte chunk j at slot j ^ (r & 7)
-        const int c0 = chalf * 32;
-        float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
-        const uint32_t rbase = ring + (uint32_t)prow * 256u;
+      if (warp < 8) {   // park the partial tile (128 x BN): row r at r * ROWB, its 16-byte chunk j at slot (j + r) % CH
+        const uint32_t rbase = ring + (uint32_t)prow * ROWB;
+        {
+          const int c0 = chalf * 32;
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const uint32_t slot = (uint32_t)((c0 >> 2) + q) ^ (uint32_t)(prow & 7);
-          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(rbase + slot * 16u), "f"(v[4 * q]), "f"(v[4 * q + 1]),
-                       "f"(v[4 * q + 2]), "f"(v[4 * q + 3]) : "memory");
+          for (int q = 0; q < 8; ++q) {
+            const uint32_t slot = (uint32_t)((c0 >> 2) + q + prow) % (uint32_t)CH;
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(rbase + slot * 16u), "f"(v[4 * q]), "f"(v[4 * q + 1]),
+                         "f"(v[4 * q + 2]), "f"(v[4 * q + 3]) : "memory");
+          }
+        }
+        if (BN > 64 && chalf == 0) {       // columns 64 .. BN - 1
+          float v[16];
+          tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + 64u, v);
+#pragma unroll
+          for (int q = 0; q < (BN - 64) / 4; ++q) {
+            const uint32_t slot = (uint32_t)(16 + q + prow) % (uint32_t)CH;
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(rbase + slot * 16u), "f"(v[4 * q]), "f"(v[4 * q + 1]),
+                         "f"(v[4 * q + 2]), "f"(v[4 * q + 3]) : "memory");
+          }
         }
       }
       tcgen05_fence_before();
       LB_STAMP(4);
       asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
       LB_STAMP(5);
-      const uint32_t off = (uint32_t)trow * 256u + (uint32_t)(j ^ (trow & 7)) * 16u;
+      const uint32_t off = (uint32_t)trow * ROWB + ((uint32_t)(j + trow) % (uint32_t)CH) * 16u;
       float4 part[LB_S];
 #pragma unroll
       for (int z = 1; z < LB_S; ++z)
@@ -526,7 +577,7 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lstm_persist_bwd_kernel(const _
   }
   tcgen05_fence_before();
   __syncthreads();
-  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(64u) : "memory");
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
 }  // namespace tc
@@ -596,41 +647,35 @@ int lstm_persist_fwd(const float* A, const float* Wh, float* hbuf, float* cbuf, 
   return 0;
 }
 
-// The whole backward recurrence as one launch (same range and conditions as lstm_persist_fwd).
-int lstm_persist_bwd(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA, int64_t T, int64_t N, int64_t H,
-                     int* taken) {
+// One configuration of the backward kernel: *taken = 1 when it was launched, 0 when the device cannot hold its
+// clusters at once (or its shared memory does not fit).
+template <int BN, int STAGES>
+static int lstm_persist_bwd_launch(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA, int64_t T,
+                                   int64_t N, int64_t H, int* taken) {
   using namespace tc;
   *taken = 0;
-  static int enabled = -1;
-  if (enabled < 0) {
-    const char* e = getenv("MC_LSTM_PERSIST");
-    const char* b = getenv("MC_LSTM_PERSIST_BWD");
-    enabled = ((e && e[0] == '0') || (b && b[0] == '0')) ? 0 : 1;
-  }
-  if (!enabled || T <= 0 || N <= 0 || N > 128 || H < 128 || H > 1024 || (H & 127)) return 0;
-  if (T * N >= (int64_t)1 << 30) return 0;
-  for (const void* q : {(const void*)gates, (const void*)cbuf, (const void*)Wh, (const void*)dH, (const void*)dA})
-    if (!aligned16(q)) return 0;
-  const int kb_per = (int)(H >> 6), ctas = (int)(H >> 3);
-  const size_t smem = (size_t)LP_RING + (size_t)kb_per * LB_BTILE + 128 + 1024;
+  const int kb_per = (int)(H >> 6), clusters = (int)((H + BN - 1) / BN), ctas = clusters * LB_S;
+  const size_t smem = (size_t)STAGES * LP_TILE + (size_t)kb_per * (BN * 128) + 128 + 1024;
+  if (smem > 227 * 1024 || ctas > 128) return 0;
   static uint32_t configured = 0;
   if (first_use_on_device(&configured))
-    MC_CHECK(cudaFuncSetAttribute(lstm_persist_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)(LP_RING + LB_MAX_KB * LB_BTILE + 128 + 1024)));
+    MC_CHECK(cudaFuncSetAttribute(lstm_persist_bwd_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(LP_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream();
+  cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(4 * BN); cfg.dynamicSmemBytes = smem; cfg.stream = stream();
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = LB_S; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  static int fits[16][LB_MAX_KB + 1] = {};
+  static int fits[16][LB_MAX_KB + 1] = {};          // [device][kb_per]: 0 unknown, 1 yes, -1 no
   int& fit = fits[device() & 15][kb_per];
   if (fit == 0) {
     int nclusters = 0;
-    cudaError_t e = cudaOccupancyMaxActiveClusters(&nclusters, lstm_persist_bwd_kernel, &cfg);
-    if (getenv("MC_LSTM_DEBUG")) fprintf(stderr, "lstm_persist_bwd: H=%d needs %d clusters of %d, device holds %d (%s)\n", (int)H, ctas / LB_S, LB_S, nclusters, cudaGetErrorString(e));
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&nclusters, lstm_persist_bwd_kernel<BN, STAGES>, &cfg);
+    if (getenv("MC_LSTM_DEBUG"))
+      fprintf(stderr, "lstm_persist_bwd<%d>: H=%d needs %d clusters of %d, device holds %d (%s)\n", BN, (int)H, clusters, LB_S,
+              nclusters, cudaGetErrorString(e));
     if (e != cudaSuccess) { cudaGetLastError(); nclusters = 0; }
-    fit = (nclusters >= ctas / LB_S) ? 1 : -1;
+    fit = (nclusters >= clusters) ? 1 : -1;
   }
   if (fit < 0) return 0;
 
@@ -648,15 +693,40 @@ int lstm_persist_bwd(const float* gates, const float* cbuf, const float* Wh, flo
   {
     const uint64_t dims[2] = {(uint64_t)(4 * H), (uint64_t)H};
     const uint64_t strides[1] = {(uint64_t)(4 * H) * 4};
-    const uint32_t box[2] = {32, 64};
+    const uint32_t box[2] = {32, (uint32_t)BN};
     if (make_tmap(&tmW, Wh, 2, dims, strides, box, false)) return 1;
   }
   LstmPersistBwdParams p;
   p.gates = gates; p.cbuf = cbuf; p.dH = dH; p.dA = dA; p.flags = flags; p.T = (int)T; p.N = (int)N; p.H = (int)H;
-  MC_CHECK(cudaLaunchKernelEx(&cfg, lstm_persist_bwd_kernel, tmD, tmW, p));
+  MC_CHECK(cudaLaunchKernelEx(&cfg, lstm_persist_bwd_kernel<BN, STAGES>, tmD, tmW, p));
   count_launch();
   *taken = 1;
   return 0;
+}
+
+// The whole backward recurrence as one launch (same range and conditions as lstm_persist_fwd): 64-unit clusters
+// when the device holds H/64 of them (H <= 896 on this pool's B200), else nothing is launched.
+int lstm_persist_bwd(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA, int64_t T, int64_t N, int64_t H,
+                     int* taken) {
+  *taken = 0;
+  static int enabled = -1, force80 = 0;
+  if (enabled < 0) {
+    const char* e = getenv("MC_LSTM_PERSIST");
+    const char* b = getenv("MC_LSTM_PERSIST_BWD");
+    enabled = ((e && e[0] == '0') || (b && b[0] == '0')) ? 0 : 1;
+    force80 = (b && b[0] == '8') ? 1 : 0;           // MC_LSTM_PERSIST_BWD=80: the 80-unit configuration everywhere (tests)
+  }
+  if (!enabled || T <= 0 || N <= 0 || N > 128 || H < 128 || H > 1024 || (H & 127)) return 0;
+  if (T * N >= (int64_t)1 << 30) return 0;
+  for (const void* q : {(const void*)gates, (const void*)cbuf, (const void*)Wh, (const void*)dH, (const void*)dA})
+    if (!aligned16(q)) return 0;
+  // MEASURED (profiles/r2r, C5: T = 100, N = 128, H = 1024): the 80-unit configuration is correct but takes 13.4 us per
+  // step against 10.0 us for the launch-per-step path: 160 KB of resident Wh leave room for four 16 KB stages only, and
+  // 64 KB in flight against ~1.2 us of TMA latency is 53 GB/s per SM -- 4.9 us for the 256 KB of dA a CTA needs per
+  // step.  It therefore runs only on request (MC_LSTM_PERSIST_BWD=80); the 64-unit configuration (six stages,
+  // 8.7 us per step at H = 896) is the default wherever its clusters fit.
+  if (force80) return lstm_persist_bwd_launch<80, 4>(gates, cbuf, Wh, dH, dA, T, N, H, taken);
+  return lstm_persist_bwd_launch<64, 6>(gates, cbuf, Wh, dH, dA, T, N, H, taken);
 }
 
 }  // namespace mc

@@ -146,3 +146,15 @@ def test_backward_outside_the_range_falls_back(cuda):
     lib.mc_lstm_seq_bwd(up(gt.astype(np.float32)).ptr, up(cb.astype(np.float32)).ptr, up(Wh).ptr, ddH.ptr, ddA.ptr, T, N, H,
                         lib.MC_GEMM_TF32)
     assert rel(ddA.asnumpy(), want_dA) <= TF32_TOL and rel(ddH.asnumpy()[0], want_dh0) <= TF32_TOL
+
+
+def test_backward_80_unit_configuration_opt_in():
+    """MC_LSTM_PERSIST_BWD=80 selects the 80-unit clusters (13 clusters at H = 1024, a k-block of dA may straddle two
+    producers' units): same float64 parity, in a process of its own because the switch is read once."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, '-m', 'pytest', os.path.join(root, 'tests', 'test_lstm_persist_gpu.py'), '-q', '-x',
+                          '-m', 'gpu', '-k', 'persistent_backward_matches', '-p', 'no:cacheprovider'],
+                         env=dict(os.environ, PYTHONPATH=root, MC_LSTM_PERSIST_BWD='80'), cwd=root, capture_output=True,
+                         text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-2000:]
