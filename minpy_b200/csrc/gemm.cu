@@ -1292,8 +1292,25 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   // TF/s, 8192^3 560 -> 585; MC_GEMM_PERSISTENT=0 selects the one-tile-per-CTA kernel)
   static int persistent = -1;
   if (persistent < 0) { const char* e = getenv("MC_GEMM_PERSISTENT"); persistent = (e && e[0] == '0') ? 0 : 1; }
-  if (persistent && splits == 1 && BN == 128 && tiles > sm_count())
+  if (persistent && splits == 1 && BN == 128 && tiles > sm_count()) {
+    // 256-column tiles: one tcgen05.mma of M128 x N256 x K8 reads 4 KB of A + 8 KB of B from shared memory for 138
+    // clocks of tensor work (87 B/clk) where the 128 x 128 tile reads 8 KB per 69 clocks (118 B/clk of the 128 B/clk an
+    // SM has), and A panels are re-read half as often.  Both accumulators fill TMEM (2 x 256 columns).
+    // MEASURED (profiles/r2t): 4096^3 562 -> 629 TF/s, 8192^3 573 -> 707 TF/s.  Taken when its waves are not worse:
+    // a 256-wide tile costs ~1.6 of a 128-wide one (MC_GEMM_BN256=0 keeps 128 everywhere).
+    static int bn256 = -1;
+    if (bn256 < 0) { const char* e = getenv("MC_GEMM_BN256"); bn256 = e ? atoi(e) : 1; }
+    const int64_t tiles256 = ((M + BM - 1) / BM) * ((N + 255) / 256);
+    const int64_t sms = sm_count();
+    const double t128 = (double)((tiles + sms - 1) / sms), t256 = 1.6 * (double)((tiles256 + sms - 1) / sms);
+    if (bn256 && N % 256 == 0 && t256 <= t128) {
+      CUtensorMap tmB2;
+      if (!tb) { if (make_tmap_2d(&tmB2, B, N, K, ldb, 32, BK, true)) return 1; }
+      else     { if (make_tmap_2d(&tmB2, B, K, N, ldb, BK, 256, false)) return 1; }
+      return launch_tf32_persistent<256, 4>(tmA, tmB2, p, tiles256);
+    }
     return launch_tf32_persistent<128, 6>(tmA, tmB, p, tiles);
+  }
   int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
   if (rc == 0 && splits > 1 && !p.counters && !p.cluster) {
     mc::launch(splitk_reduce_kernel, grid_for(M * N / 4 + 1, 256), 256, 0, p.ws, splits, M, N, C, ldc, bias, relu, accumulate);
