@@ -355,6 +355,7 @@ struct GemmParams {
   int kb_per_split;    // k-blocks (of BK) per grid.z slice
   int cluster;         // > 1: the grid.z slices of a tile are one thread-block cluster; partials meet in DSMEM
   int group_m;         // tile raster: CTAs walk `group_m` M-tiles for each N-tile before moving on (0 = x-major)
+  int half_from;       // persistent kernel: work items >= half_from are HALF-width tiles (two per tile), -1 = none
   int lstm_mode;       // cluster epilogue: 0 plain, 1 LSTM gate forward, 2 LSTM gate backward (lstm.cu)
   LstmEpilogue lstm;
 };
@@ -911,6 +912,7 @@ __device__ __forceinline__ void tile_of(const GemmParams& p, int lin, int tiles_
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                            const __grid_constant__ CUtensorMap tmB,
+                                                                           const __grid_constant__ CUtensorMap tmBh,
                                                                            const GemmParams p) {
   constexpr uint32_t A_BYTES = BM * BK * 4;
   constexpr uint32_t B_BYTES = BN * BK * 4;
@@ -918,6 +920,14 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;   // full[S], empty[S], tfull[2], tempty[2]
+  // Work list: items below `half_from` are whole tiles; from there on item i is half (i - half_from) & 1 of tile
+  // half_from + (i - half_from) / 2, BN / 2 columns wide (tmBh: the K-major B box of that width).  The host splits
+  // the tiles of the last, less-than-half-full wave so that it costs half a tile time (4096^3: 3 waves + 68 tiles).
+  const int half_from = p.half_from;
+  auto item_of = [&](int lin, int& tile_lin, int& half) {
+    if (half_from < 0 || lin < half_from) { tile_lin = lin; half = -1; }
+    else { tile_lin = half_from + ((lin - half_from) >> 1); half = (lin - half_from) & 1; }
+  };
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
@@ -926,7 +936,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m = (p.M + BM - 1) / BM, tiles_n = (p.N + BN - 1) / BN;
-  const int total = tiles_m * tiles_n;
+  const int total = half_from < 0 ? tiles_m * tiles_n : half_from + 2 * (tiles_m * tiles_n - half_from);
   const int num_kb = (p.K + BK - 1) / BK;
 
   if (warp == 4 && lane == 0) {
@@ -956,14 +966,17 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
       int s = 0;
       uint32_t ph = 0;
       for (int lin = blockIdx.x; lin < total; lin += gridDim.x) {
-        int tile_m, tile_n;
-        tile_of(p, lin, tiles_m, tiles_n, tile_m, tile_n);
-        const int m0 = tile_m * BM, n0 = tile_n * BN;
+        int tile_m, tile_n, tile_lin, half;
+        item_of(lin, tile_lin, half);
+        tile_of(p, tile_lin, tiles_m, tiles_n, tile_m, tile_n);
+        const int m0 = tile_m * BM, n0 = tile_n * BN + (half > 0 ? BN / 2 : 0);
+        const int nbox = half < 0 ? BN / 32 : BN / 64;
+        const uint32_t stage_tx = half < 0 ? STAGE_BYTES : A_BYTES + B_BYTES / 2;
         int k0 = 0;
         for (int i = 0; i < num_kb; ++i, k0 += BK) {
           mbar_wait(empty_bar(s), ph ^ 1u);
           const uint32_t fb = full_bar(s);
-          mbar_expect_tx(fb, STAGE_BYTES);
+          mbar_expect_tx(fb, stage_tx);
           const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
           if (!a_mn) {
             tma_load_2d(sa, &tmA, fb, k0, m0);
@@ -972,10 +985,9 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
             for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, fb, m0 + 32 * j, k0);
           }
           if (!b_mn) {
-            tma_load_2d(sb, &tmB, fb, k0, n0);
+            tma_load_2d(sb, half < 0 ? &tmB : &tmBh, fb, k0, n0);
           } else {
-#pragma unroll
-            for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, fb, n0 + 32 * j, k0);
+            for (int j = 0; j < nbox; ++j) tma_load_2d(sb + j * 4096, &tmB, fb, n0 + 32 * j, k0);
           }
           if (++s == STAGES) { s = 0; ph ^= 1u; }
         }
@@ -991,7 +1003,9 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
       const uint32_t astep = p.a_mn ? 64u : 2u, bstep = p.b_mn ? 64u : 2u;
       int s = 0, acc = 0;
       uint32_t ph = 0, aph = 0;
+      const uint32_t idesc_half = (idesc & ~(0x3Fu << 17)) | ((uint32_t)(BN >> 4) << 17);
       for (int lin = blockIdx.x; lin < total; lin += gridDim.x) {
+        const uint32_t idesc_t = (half_from >= 0 && lin >= half_from) ? idesc_half : idesc;
         mbar_wait(tempty_bar(acc), aph ^ 1u);          // the epilogue has drained this accumulator
         tcgen05_fence_after();
         const uint32_t dacc = tmem_base + (uint32_t)(acc * BN);
@@ -1003,7 +1017,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
           const uint64_t bdesc = bdesc0 + (uint64_t)((sb & 0x3FFFFu) >> 4);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
-            umma_tf32(dacc, adesc + (uint64_t)(astep * k), bdesc + (uint64_t)(bstep * k), idesc, (i > 0 || k > 0) ? 1u : 0u);
+            umma_tf32(dacc, adesc + (uint64_t)(astep * k), bdesc + (uint64_t)(bstep * k), idesc_t, (i > 0 || k > 0) ? 1u : 0u);
           umma_commit(empty_bar(s));
           if (++s == STAGES) { s = 0; ph ^= 1u; }
         }
@@ -1017,14 +1031,16 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
     int acc = 0;
     uint32_t aph = 0;
     for (int lin = blockIdx.x; lin < total; lin += gridDim.x) {
-      int tile_m, tile_n;
-      tile_of(p, lin, tiles_m, tiles_n, tile_m, tile_n);
-      const int row = tile_m * BM + warp * 32 + lane, n0 = tile_n * BN;
+      int tile_m, tile_n, tile_lin, half;
+      item_of(lin, tile_lin, half);
+      tile_of(p, tile_lin, tiles_m, tiles_n, tile_m, tile_n);
+      const int row = tile_m * BM + warp * 32 + lane, n0 = tile_n * BN + (half > 0 ? BN / 2 : 0);
+      const int width = half < 0 ? BN : BN / 2;
       mbar_wait_warp(tfull_bar(acc), aph);
       tcgen05_fence_after();
       const uint32_t tacc = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = 0; c0 < width; c0 += 32) {
         float v[32];
         tmem_ld32(tacc + (uint32_t)c0, v);
         const int col0 = n0 + c0;
@@ -1142,14 +1158,20 @@ static int gemm_fp32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
 }
 
 template <int BN, int STAGES>
-static int launch_tf32_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const tc::GemmParams& p, int64_t tiles) {
+static int launch_tf32_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmBh, tc::GemmParams p,
+                                  int64_t tiles, bool split_tail) {
   using namespace tc;
   constexpr size_t SMEM = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) + (2 * STAGES + 4) * 8 + 16 + 1024;
   static uint32_t configured = 0;
   if (first_use_on_device(&configured))
     MC_CHECK(cudaFuncSetAttribute(gemm_tf32_persistent_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
   const unsigned grid = (unsigned)(tiles < sm_count() ? tiles : sm_count());
-  mc::launch_pdl(gemm_tf32_persistent_kernel<BN, STAGES>, grid, PTHREADS, SMEM, tmA, tmB, p);
+  p.half_from = -1;
+  if (split_tail && tiles > grid) {
+    const int64_t tail = tiles % grid;
+    if (tail > 0 && 2 * tail <= grid) p.half_from = (int)(tiles - tail);
+  }
+  mc::launch_pdl(gemm_tf32_persistent_kernel<BN, STAGES>, grid, PTHREADS, SMEM, tmA, tmB, tmBh, p);
   MC_LAUNCHED();
   return 0;
 }
@@ -1240,6 +1262,7 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   p.kb_per_split = kb_per;
   p.counters = nullptr;
   p.cluster = 0;
+  p.half_from = -1;
   p.lstm_mode = 0;
   p.lstm = LstmEpilogue();
   // raster only when the grid is larger than one wave: keep <= ~48 MB of A panels resident in the 126 MB L2
@@ -1302,14 +1325,19 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     if (bn256 < 0) { const char* e = getenv("MC_GEMM_BN256"); bn256 = e ? atoi(e) : 1; }
     const int64_t tiles256 = ((M + BM - 1) / BM) * ((N + 255) / 256);
     const int64_t sms = sm_count();
-    const double t128 = (double)((tiles + sms - 1) / sms), t256 = 1.6 * (double)((tiles256 + sms - 1) / sms);
+    const int64_t tail256 = tiles256 > sms ? tiles256 % sms : 0;      // a last wave at most half full runs as half tiles
+    const double t128 = (double)((tiles + sms - 1) / sms);
+    const double t256 = 1.6 * ((double)(tiles256 / sms) + (tiles256 % sms == 0 ? 0.0 : ((tail256 > 0 && 2 * tail256 <= sms) ? 0.5 : 1.0)));
     if (bn256 && N % 256 == 0 && t256 <= t128) {
       CUtensorMap tmB2;
       if (!tb) { if (make_tmap_2d(&tmB2, B, N, K, ldb, 32, BK, true)) return 1; }
       else     { if (make_tmap_2d(&tmB2, B, K, N, ldb, BK, 256, false)) return 1; }
-      return launch_tf32_persistent<256, 4>(tmA, tmB2, p, tiles256);
+      // (tmB = the 128-wide box of the same matrix: the half tiles of a split last wave)
+      static int tail = -1;
+      if (tail < 0) { const char* e = getenv("MC_GEMM_TAIL_SPLIT"); tail = (e && e[0] == '0') ? 0 : 1; }
+      return launch_tf32_persistent<256, 4>(tmA, tmB2, tmB, p, tiles256, tail != 0);
     }
-    return launch_tf32_persistent<128, 6>(tmA, tmB, p, tiles);
+    return launch_tf32_persistent<128, 6>(tmA, tmB, tmB, p, tiles, false);
   }
   int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
   if (rc == 0 && splits > 1 && !p.counters && !p.cluster) {

@@ -193,7 +193,8 @@ cuda.set_gemm_precision('tf32')
 rng = np.random.RandomState(0)
 # grids of more than 148 tiles (more than one wave): the rastered tile order / the persistent kernel
 for M, N, K, ta, tb in [(2048, 2048, 256, 0, 0), (2000, 1900, 136, 0, 1), (4096, 1024, 96, 1, 0), (1500, 2100, 64, 1, 1),
-                        (8192, 384, 40, 0, 0), (2304, 2048, 72, 0, 1), (2200, 2048, 64, 1, 1)]:   # the last two (and the first, third): 256-column tiles
+                        (8192, 384, 40, 0, 0), (2304, 2048, 72, 0, 1), (2200, 2048, 64, 1, 1),      # (and the first, third): 256-column tiles
+                        (2688, 2048, 72, 0, 0), (2688, 2048, 40, 0, 1), (2600, 2048, 64, 1, 0)]:   # 168 tiles: 148 whole + 20 split in halves
     a = rng.randn(*((K, M) if ta else (M, K))).astype(np.float32)
     b = rng.randn(*((N, K) if tb else (K, N))).astype(np.float32)
     bias = rng.randn(N).astype(np.float32)
@@ -211,7 +212,7 @@ print('multiwave ok')
 """
 
 
-@pytest.mark.parametrize('env', [{}, {'MC_GEMM_BN256': '0'}, {'MC_GEMM_PERSISTENT': '0'}, {'MC_GEMM_PERSISTENT': '0', 'MC_GEMM_RASTER': '0'}, {'MC_PDL': '0'}, {'MC_PDL': '2'}])
+@pytest.mark.parametrize('env', [{}, {'MC_GEMM_BN256': '0'}, {'MC_GEMM_TAIL_SPLIT': '0'}, {'MC_GEMM_PERSISTENT': '0'}, {'MC_GEMM_PERSISTENT': '0', 'MC_GEMM_RASTER': '0'}, {'MC_PDL': '0'}, {'MC_PDL': '2'}])
 def test_gemm_grids_beyond_one_wave(env):
     """Default (persistent TMEM-double-buffered kernel, rastered tile order), the one-tile-per-CTA kernel with and
     without the raster, and the three programmatic-launch modes all give the float64 product within the TF32 bound, with bias / signed-zero relu / accumulate epilogues and
