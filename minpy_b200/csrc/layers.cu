@@ -955,6 +955,42 @@ __global__ void __launch_bounds__(L_THREADS) multi_update_kernel(const __grid_co
     }
     return;
   }
+  // rmsprop / adam, whole aligned tile: the same two-float4 pattern, the same per-element expressions as the scalar
+  // loop below (the scalar loop ran the C5 adam update, 4.85 M parameters, at 2.4 TB/s: 58 us)
+  if (hi - lo == MU_TILE && (align_bits & 15u) == 0) {
+    const int64_t idx[2] = {lo + 4 * threadIdx.x, lo + 4 * threadIdx.x + 4 * L_THREADS};
+    float4 g4[2], w4[2], a4[2], b4[2];
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      g4[u] = *reinterpret_cast<const float4*>(dw + idx[u]);
+      w4[u] = *reinterpret_cast<const float4*>(w + idx[u]);
+      a4[u] = s1 ? *reinterpret_cast<const float4*>(s1 + idx[u]) : z4;
+      b4[u] = (d.rule == 3 && s2) ? *reinterpret_cast<const float4*>(s2 + idx[u]) : z4;
+    }
+    const float h1 = d.h[1], h2 = d.h[2], h3 = d.h[3];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      float4 wn, an, bn = z4;
+#define MU_CELL(m)                                                                      \
+      if (d.rule == 2) {                                                                \
+        const float c = a4[u].m * h1 + g4[u].m * g4[u].m * (1.f - h1);                  \
+        an.m = c;                                                                       \
+        wn.m = w4[u].m - lr * g4[u].m / (sqrtf(c) + h2);                                \
+      } else {                                                                          \
+        const float nm = h1 * a4[u].m + (1.f - h1) * g4[u].m;                           \
+        const float nv = h2 * b4[u].m + (1.f - h2) * (g4[u].m * g4[u].m);               \
+        an.m = nm; bn.m = nv;                                                           \
+        wn.m = w4[u].m - lr * (nm / bc1) / (sqrtf(nv / bc2) + h3);                      \
+      }
+      MU_CELL(x) MU_CELL(y) MU_CELL(z) MU_CELL(w)
+#undef MU_CELL
+      *reinterpret_cast<float4*>(s1o + idx[u]) = an;
+      if (d.rule == 3) *reinterpret_cast<float4*>(s2o + idx[u]) = bn;
+      *reinterpret_cast<float4*>(wo + idx[u]) = wn;
+    }
+    return;
+  }
   for (int64_t i = lo + threadIdx.x; i < hi; i += L_THREADS) {
     const float g = dw[i];
     if (d.rule == 0) {

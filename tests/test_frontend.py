@@ -470,7 +470,7 @@ def test_multi_tensor_update_equals_per_parameter_loop(rule):
     import minpy.numpy as mnp
     from minpy.nn import optim
     rng = np.random.RandomState(12)
-    shapes = [(33, 17), (5,), (128, 64), (1,), (7, 3, 3, 3)] * 8          # 40 tensors: more than one launch group
+    shapes = [(33, 17), (5,), (128, 64), (1,), (7, 3, 3, 3), (300, 70)] * 7   # 42 tensors: more than one launch group; whole (float4 path) and ragged tiles
     w0 = [rng.randn(*s).astype(np.float32) for s in shapes]
     fn = getattr(optim, rule)
     base = {'learning_rate': 0.05}
