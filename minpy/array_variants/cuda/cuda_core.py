@@ -882,9 +882,7 @@ def _lstm_temporal_vjp(ans, x, h0, Wx, Wh, b):
         sH, sA = 4 * N * H, 4 * N * 4 * H
         dH = CudaArray.empty((T + 1, N, H))
         lib.mc_memset(dH.ptr, 0, sH)
-        g_tm = ops.transpose(g, (1, 0, 2))
-        lib.mc_memcpy_d2d(dH.ptr + sH, g_tm.ptr, T * sH)
-        del g_tm
+        ops.transpose(g, (1, 0, 2), out=_view(dH, sH, (T, N, H)))      # time-major, straight into slots 1..T
         dA = CudaArray.empty((T * N, 4 * H))
         lib.mc_lstm_seq_bwd(gates.ptr, cbuf.ptr, Wh.ptr, dH.ptr, dA.ptr, T, N, H, prec)
         h_prev = _view(hbuf, 0, (T * N, H))

@@ -358,21 +358,27 @@ def reshape(x, shape):
     return as_cuda(x).reshape(shape)
 
 
-def transpose(x, axes=None):
+def transpose(x, axes=None, out=None):
+    """np.transpose as one strided copy; `out` (a float32 CudaArray or view of the result's shape) receives it in place
+    of a fresh array."""
     lib = L()
     x = as_cuda(x)
     nd = x.ndim
     if axes is None:
         axes = tuple(reversed(range(nd)))
     axes = tuple(a + nd if a < 0 else a for a in axes)
-    if nd <= 1 or axes == tuple(range(nd)):
-        return x
-    if x.dtype != _F32:
-        return CudaArray.from_numpy(np.transpose(x.asnumpy(), axes))
+    if out is None:
+        if nd <= 1 or axes == tuple(range(nd)):
+            return x
+        if x.dtype != _F32:
+            return CudaArray.from_numpy(np.transpose(x.asnumpy(), axes))
     st = _contig_strides(x.shape)
     oshape = tuple(x.shape[a] for a in axes)
     ostr = tuple(st[a] for a in axes)
-    out = CudaArray.empty(oshape)
+    if out is None:
+        out = CudaArray.empty(oshape)
+    elif tuple(out.shape) != oshape or out.dtype != _F32 or x.dtype != _F32:
+        raise ValueError('transpose: out must be a float32 array of shape %r' % (oshape,))
     if out.size:
         if nd > 6:
             raise ValueError('transpose of more than 6 dims is not supported')
