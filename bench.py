@@ -666,6 +666,50 @@ def run_ufunc_sweep(sizes=(10 ** 4, 10 ** 5, 10 ** 6, 10 ** 7, 10 ** 8, 10 ** 9)
     return res
 
 
+def run_gemm_sweep(sizes=(2048, 4096, 8192)):
+    """np.dot (mc_gemm, tcgen05 kind::tf32) at square sizes where the tensor pipe is reachable: TFLOP/s per size and the
+    fraction of the kind::tf32 ceiling (half the measured bf16 cuBLAS rate).  Each size alone in a CUDA graph, events;
+    operands (>= 50 MB) are re-read from L2 / HBM as the tile raster dictates -- nothing is cached between sizes."""
+    from minpy_b200._lib import get_lib
+    from minpy_b200.cuda_array import CudaArray
+    lib = get_lib()
+    peaks = measured_peaks()
+    ceiling = peaks['bf16_tflops_sustained'] / 2.0
+    e0, e1 = ctypes.c_void_p(), ctypes.c_void_p()
+    lib.mc_event_create(ctypes.byref(e0))
+    lib.mc_event_create(ctypes.byref(e1))
+    rng = np.random.RandomState(0)
+    res = {}
+    for n in sizes:
+        a = rng.randn(n, n).astype(np.float32)
+        A, B, C = CudaArray.from_numpy(a), CudaArray.from_numpy(a.T.copy()), CudaArray.empty((n, n))
+
+        def run():
+            lib.mc_gemm(0, 0, n, n, n, A.ptr, n, B.ptr, n, C.ptr, n, None, 0, 0, 1)
+        for _ in range(3):
+            run()
+        lib.mc_sync()
+        reps = 20 if n <= 4096 else 5
+        lib.mc_event_record(e0)
+        for _ in range(reps):
+            run()
+        lib.mc_event_record(e1)
+        lib.mc_sync()
+        ms = ctypes.c_float()
+        lib.mc_event_elapsed_ms(e0, e1, ctypes.byref(ms))
+        us = ms.value / reps * 1e3
+        rows = rng.randint(0, n, 4)
+        ref = a[rows].astype(np.float64) @ a.T.astype(np.float64)
+        err = float(np.max(np.abs(C.asnumpy()[rows] - ref)) / np.max(np.abs(ref)))
+        tf = 2.0 * n ** 3 / us / 1e6
+        res['%d^3' % n] = {'us': round(us, 2), 'tflops': round(tf, 1), 'frac_of_tf32_ceiling': round(tf / ceiling, 3),
+                           'relerr_vs_float64': err, 'l2_resident': bool(12.0 * n * n <= L2_BYTES)}
+        del A, B, C
+    res['tf32_ceiling_tflops'] = round(ceiling, 1)
+    res['ceiling_source'] = 'half the %s bf16 cuBLAS sustained rate (MEASURED_PEAKS.json)' % peaks['source']
+    return res
+
+
 # ------------------------------------------------------------- CPU arm (oracle port) -------
 def oracle_step_fn(workload, mask_fn=None, with_grads=False, decisions=None):
     """One training step of `workload` on the NumPy oracle (float64, as the reference's NumPy
@@ -989,6 +1033,7 @@ def main():
     if rank == 0:
         if world == 1 and not args.no_ufunc:
             out['ufunc'] = run_ufunc_sweep()
+            out['gemm_tf32'] = run_gemm_sweep()
         if world == 1 and not args.no_cpu_baseline:
             out['cpu_baseline'] = time_cpu(args.workload)
         print(json.dumps(out), flush=True)
