@@ -893,7 +893,7 @@ int make_tmap_2d(CUtensorMap* map, const float* ptr, int64_t inner, int64_t oute
 // ring never stops at a tile boundary -- the non-persistent kernel above pays TMEM allocation, barrier
 // set-up, a pipeline fill and an un-overlapped epilogue per 128 x BN tile (profiles/r1z/prof_gemm_4096.txt:
 // 54.7 % tensor-pipe active at 4096^3).
-constexpr int PTHREADS = 192;
+constexpr int PTHREADS = 320;   // warps 0-7: epilogue (two per TMEM lane quadrant, half the columns each), 8: TMA producer, 9: MMA issuer
 
 __device__ __forceinline__ void tile_of(const GemmParams& p, int lin, int tiles_m, int tiles_n, int& tile_m, int& tile_n) {
   if (p.group_m > 0) {
@@ -933,21 +933,22 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+  const uint32_t turn_base = (tmem_slot + 16u + 127u) & ~127u;  // 8 x 4 KB: one 32 x 32 block per epilogue warp
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m = (p.M + BM - 1) / BM, tiles_n = (p.N + BN - 1) / BN;
   const int total = half_from < 0 ? tiles_m * tiles_n : half_from + 2 * (tiles_m * tiles_n - half_from);
   const int num_kb = (p.K + BK - 1) / BK;
 
-  if (warp == 4 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  if (warp == 5) {
+  if (warp == 9) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)(2 * BN))
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -959,7 +960,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (elect_one()) {
       // ------------------------------ TMA producer ------------------------------------
       const bool a_mn = p.a_mn != 0, b_mn = p.b_mn != 0;
@@ -993,7 +994,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     if (elect_one()) {
       // ------------------------------ MMA issuer --------------------------------------
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
@@ -1026,53 +1027,108 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
       }
     }
   } else {
-    // ---------------------------------- epilogue (warps 0-3) ----------------------------
-    const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+    // ---------------------------------- epilogue (warps 0-7) ----------------------------
+    // Warp w drains TMEM lanes 32 (w & 3) .. +31, columns [(w >> 2) width / 2, + width / 2).  Interior tiles: every
+    // 32 x 32 block is turned through 4 KB of shared memory (16-byte chunks XOR-swizzled by row) so that eight lanes
+    // write one 128-byte row segment and a warp store covers four whole lines -- the pattern of gemm_tf32_kernel.
+    // (Four warps storing one ROW per thread took ~1 us per 32-column pass: (12800, 4096, 128), whose tiles have four
+    //  k-blocks of mainloop, ran at 110 us against 33 us of output traffic.)
+    const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0) &&
+                        (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0);
+    const int quad = warp & 3, chalf = warp >> 2;
+    const uint32_t turn = turn_base + (uint32_t)warp * 4096u;
+    const uint32_t st_addr = turn + (uint32_t)lane * 128u, st_x = (uint32_t)(lane & 7);
+    const int j4 = (lane & 7) * 4, rsub = lane >> 3;
+    const float negv = (p.relu == 2) ? -0.0f : 0.f;
     int acc = 0;
     uint32_t aph = 0;
     for (int lin = blockIdx.x; lin < total; lin += gridDim.x) {
       int tile_m, tile_n, tile_lin, half;
       item_of(lin, tile_lin, half);
       tile_of(p, tile_lin, tiles_m, tiles_n, tile_m, tile_n);
-      const int row = tile_m * BM + warp * 32 + lane, n0 = tile_n * BN + (half > 0 ? BN / 2 : 0);
+      const int m0 = tile_m * BM, n0 = tile_n * BN + (half > 0 ? BN / 2 : 0);
       const int width = half < 0 ? BN : BN / 2;
+      const int cbeg = chalf * (width / 2), cend = cbeg + width / 2;
       mbar_wait_warp(tfull_bar(acc), aph);
       tcgen05_fence_after();
-      const uint32_t tacc = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * BN);
+      const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
+      if (vec_ok && m0 + BM <= p.M && n0 + width <= p.N) {
+        float* base = p.C + (int64_t)(m0 + quad * 32 + rsub) * p.ldc + n0 + j4;
 #pragma unroll 1
-      for (int c0 = 0; c0 < width; c0 += 32) {
-        float v[32];
-        tmem_ld32(tacc + (uint32_t)c0, v);
-        const int col0 = n0 + c0;
-        if (row < p.M && col0 < p.N) {
-          float* dst = p.C + (int64_t)row * p.ldc + col0;
-          if (vec_ok && col0 + 32 <= p.N) {
+        for (int c0 = cbeg; c0 < cend; c0 += 32) {
+          float v[32];
+          tmem_ld32(tacc + (uint32_t)c0, v);
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-              if (p.bias) {
-                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-                o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-              }
-              if (p.accumulate) {
-                const float4 c = *reinterpret_cast<const float4*>(dst + j);
-                o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
-              }
-              if (p.relu) {
-                o.x = relu_apply(o.x, p.relu); o.y = relu_apply(o.y, p.relu);
-                o.z = relu_apply(o.z, p.relu); o.w = relu_apply(o.w, p.relu);
-              }
-              *reinterpret_cast<float4*>(dst + j) = o;
+          for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(st_addr + (((uint32_t)j ^ st_x) * 16u)), "f"(v[4 * j]),
+                         "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+          __syncwarp();
+          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (p.bias) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c0 + j4));
+          float* d = base + c0;
+          float4 o[8];
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rsub;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o[it].x), "=f"(o[it].y), "=f"(o[it].z), "=f"(o[it].w)
+                         : "r"(turn + (uint32_t)rr * 128u + (uint32_t)(((lane & 7) ^ (rr & 7)) * 16)) : "memory");
+          }
+          float4 cv[8];
+          if (p.accumulate) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) cv[it] = *reinterpret_cast<const float4*>(d + (int64_t)(it * 4) * p.ldc);
+          }
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            float4 t = make_float4(o[it].x + b4.x, o[it].y + b4.y, o[it].z + b4.z, o[it].w + b4.w);
+            if (p.accumulate) { t.x += cv[it].x; t.y += cv[it].y; t.z += cv[it].z; t.w += cv[it].w; }
+            if (p.relu) {                                   // relu_apply without branches: NaN passes, -x -> negv, +-0 -> +0
+              t.x = (t.x < 0.f) ? negv : ((t.x == 0.f) ? 0.f : t.x); t.y = (t.y < 0.f) ? negv : ((t.y == 0.f) ? 0.f : t.y);
+              t.z = (t.z < 0.f) ? negv : ((t.z == 0.f) ? 0.f : t.z); t.w = (t.w < 0.f) ? negv : ((t.w == 0.f) ? 0.f : t.w);
             }
-          } else {
+            *reinterpret_cast<float4*>(d + (int64_t)(it * 4) * p.ldc) = t;
+          }
+          __syncwarp();                                     // the block is reused by the next pass
+        }
+      } else {
+        // edge tiles / unaligned output: one row per thread, bounds checked per element
+        const int row = m0 + quad * 32 + lane;
+        const bool vec_c = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+#pragma unroll 1
+        for (int c0 = cbeg; c0 < cend; c0 += 32) {
+          float v[32];
+          tmem_ld32(tacc + (uint32_t)c0, v);
+          const int col0 = n0 + c0;
+          if (row < p.M && col0 < p.N) {
+            float* dst = p.C + (int64_t)row * p.ldc + col0;
+            if (vec_c && col0 + 32 <= p.N && (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0)) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (col0 + j < p.N) {
-                float o = v[j];
-                if (p.bias) o += __ldg(p.bias + col0 + j);
-                if (p.accumulate) o += dst[j];
-                if (p.relu) o = relu_apply(o, p.relu);
-                dst[j] = o;
+              for (int j = 0; j < 32; j += 4) {
+                float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                if (p.bias) {
+                  const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+                  o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+                }
+                if (p.accumulate) {
+                  const float4 c = *reinterpret_cast<const float4*>(dst + j);
+                  o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
+                }
+                if (p.relu) {
+                  o.x = relu_apply(o.x, p.relu); o.y = relu_apply(o.y, p.relu);
+                  o.z = relu_apply(o.z, p.relu); o.w = relu_apply(o.w, p.relu);
+                }
+                *reinterpret_cast<float4*>(dst + j) = o;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (col0 + j < p.N) {
+                  float o = v[j];
+                  if (p.bias) o += __ldg(p.bias + col0 + j);
+                  if (p.accumulate) o += dst[j];
+                  if (p.relu) o = relu_apply(o, p.relu);
+                  dst[j] = o;
+                }
               }
             }
           }
@@ -1086,7 +1142,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
   }
   tcgen05_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == 9) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)(2 * BN)) : "memory");
   }
 }
@@ -1161,7 +1217,7 @@ template <int BN, int STAGES>
 static int launch_tf32_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmBh, tc::GemmParams p,
                                   int64_t tiles, bool split_tail) {
   using namespace tc;
-  constexpr size_t SMEM = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) + (2 * STAGES + 4) * 8 + 16 + 1024;
+  constexpr size_t SMEM = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) + (2 * STAGES + 4) * 8 + 16 + 128 + 8 * 4096 + 1024;
   static uint32_t configured = 0;
   if (first_use_on_device(&configured))
     MC_CHECK(cudaFuncSetAttribute(gemm_tf32_persistent_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));

@@ -18,6 +18,8 @@ SHAPES = [
     ('c3_fwd2', 0, 0, 1024, 512, 512), ('c3_dx2', 0, 1, 1024, 512, 512), ('c3_dw2', 1, 0, 512, 512, 1024),
     ('c5_hWh', 0, 0, 128, 4096, 1024), ('c5_dh', 0, 1, 128, 1024, 4096), ('c5_dWh', 1, 0, 1024, 4096, 128),
     ('c5_vocab', 0, 0, 12800, 128, 1024),
+    ('c5_xWx', 0, 0, 12800, 4096, 128), ('c5_dhs', 0, 1, 12800, 1024, 128), ('c5_dWh_all', 1, 0, 1024, 4096, 12800),
+    ('c5_dWx', 1, 0, 128, 4096, 12800), ('c5_dx', 0, 1, 12800, 128, 4096), ('c5_dWa', 1, 0, 1024, 128, 12800),
     ('c3_out', 0, 0, 1024, 10, 512), ('c3_dwo', 1, 0, 512, 10, 1024), ('c3_dho', 0, 1, 1024, 512, 10),
     ('c4_out', 0, 0, 512, 10, 2048), ('c4_dwo', 1, 0, 2048, 10, 512), ('c4_dho', 0, 1, 512, 2048, 10),
     ('sq1024', 0, 0, 1024, 1024, 1024), ('sq2048', 0, 0, 2048, 2048, 2048),
