@@ -12,6 +12,6 @@ for o in minpy_b200/_build/*.o; do
 done
 echo
 echo "# per tcgen05 kernel"
-for o in minpy_b200/_build/gemm.o minpy_b200/_build/conv_tc.o; do
+for o in minpy_b200/_build/gemm.o minpy_b200/_build/conv_tc.o minpy_b200/_build/lstm_persist.o; do
   cuobjdump -sass $o 2>/dev/null | awk '/Function :/{name=$3} /UTCHMMA/{m[name]++} /UTMALDG/{t[name]++} / LDTM/{l[name]++} END{for(k in m) printf "%-110s UTCHMMA %3d UTMALDG %3d LDTM %3d\n", k, m[k], t[k], l[k]}' | sort
 done
