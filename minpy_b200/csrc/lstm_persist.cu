@@ -580,6 +580,233 @@ __global__ void __launch_bounds__(4 * BN, 1) lstm_persist_bwd_kernel(const __gri
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Backward recurrence without clusters (H = 1024, where 16 eight-CTA clusters do not fit the device): one persistent
+// launch of H/8 independent CTAs that STREAM Wh from L2 (16.8 MB, resident there) instead of keeping it in shared
+// memory -- what is saved against the launch-per-step path is the two launches per step, the launch ramps and the
+// round trip of the split-K partials through a separate gate kernel.
+//   CTA (j, s): output units [128 j, 128 j + 128), K slice s of 16 = gate columns [s H/4, (s+1) H/4).
+//   per step   wait for the CTAs that produced this slice of dA_{t+1} (flags, as above) -> TMA ring of
+//              {dA tile, Wh tile} pairs (32 KB a stage, six stages) -> M128 x N128 MMAs -> the partial tile (64 KB)
+//              goes to a workspace in L2, flag -> wait for the 16 partials of unit tile j -> sum rows [8 s, 8 s + 8)
+//              in slice order -> + dH[t + 1], gate backward (dc in registers) -> dA_t, flag.
+// The workspace is double-buffered by step parity: a partial of step i is overwritten at step i + 2, and no CTA can
+// reach step i + 2 before every CTA has published dA of step i, i.e. finished reading the partials of step i.
+constexpr int LS2_S = 16;
+constexpr int LS2_STAGES = 6;
+constexpr uint32_t LS2_STAGE = 2 * LP_TILE;        // dA tile + Wh tile
+
+struct LstmStreamBwdParams {
+  const float* gates;
+  const float* cbuf;
+  float* dH;
+  float* dA;
+  float* ws;           // [2][CTAs][128][128]
+  int* flag_da;        // per CTA: number of dA steps published
+  int* flag_part;      // per CTA: number of partial tiles published
+  int T, N, H;
+};
+
+MC_PROBE_DEFINE(lstms)
+#define LS2_STAMP(i) do { if (it == p.T - 2) { MC_STAMP(lstms, i); } } while (0)
+__global__ void __launch_bounds__(LP_THREADS, 1) lstm_stream_bwd_kernel(const __grid_constant__ CUtensorMap tmD,
+                                                                        const __grid_constant__ CUtensorMap tmW,
+                                                                        const LstmStreamBwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t ring = smem_base;
+  const uint32_t bar_base = ring + LS2_STAGES * LS2_STAGE;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (LS2_STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (2 * LS2_STAGES);
+  const uint32_t tmem_slot = tmem_full_bar + 8u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int jt = blockIdx.x / LS2_S, sl = blockIdx.x % LS2_S;      // unit tile, K slice
+  const int kb_per = p.H >> 7;                                       // (H / 4) / 32
+  const int k_base = sl * (p.H >> 2);
+  const int slice_u0 = (sl & 3) * (p.H >> 2);                        // first hidden unit of the slice
+  const int jt_first = slice_u0 >> 7, jt_last = (slice_u0 + (p.H >> 2) - 1) >> 7;   // producer unit tiles (<= 2)
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmD)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW)) : "memory");
+    for (int s = 0; s < LS2_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  mc::pdl_sync();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  // this thread's cells: batch row 8 sl + r, hidden units unit0 .. unit0 + 3
+  const int r = threadIdx.x >> 5;
+  const int trow = sl * 8 + r;
+  const int unit0 = 128 * jt + 4 * lane;
+  const bool live = trow < p.N;
+  const int64_t H = p.H, sH = (int64_t)p.N * H, sA = 4 * sH;
+  const int64_t cell = (int64_t)trow * H + unit0, gcell = (int64_t)trow * 4 * H + unit0;
+  float4 dcn = make_float4(0.f, 0.f, 0.f, 0.f);
+  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  const uint64_t desc0 = make_desc(0, 16, 1024, 2);
+  int s = 0;
+  uint32_t ph = 0;
+  const int quad = warp & 3, chalf = warp >> 2;
+  const int prow = quad * 32 + lane;
+  const bool leader = elect_one();
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int64_t tile_elems = 128 * 128;
+  const int ctas = gridDim.x;
+
+  for (int it = 0; it <= p.T; ++it) {
+    const int t = p.T - 1 - it;
+    LS2_STAMP(0);
+    float4 gi = zero4, gf = zero4, go = zero4, gg = zero4, cn = zero4, cp = zero4, dh = zero4;
+    if (live) {
+      if (it < p.T) {
+        const float* gp = p.gates + (int64_t)t * sA + gcell;
+        gi = __ldcs(reinterpret_cast<const float4*>(gp));
+        gf = __ldcs(reinterpret_cast<const float4*>(gp + H));
+        go = __ldcs(reinterpret_cast<const float4*>(gp + 2 * H));
+        gg = __ldcs(reinterpret_cast<const float4*>(gp + 3 * H));
+        cn = __ldcs(reinterpret_cast<const float4*>(p.cbuf + (int64_t)(t + 1) * sH + cell));
+        cp = __ldcs(reinterpret_cast<const float4*>(p.cbuf + (int64_t)t * sH + cell));
+        dh = __ldcs(reinterpret_cast<const float4*>(p.dH + (int64_t)(t + 1) * sH + cell));
+      } else {
+        dh = *reinterpret_cast<const float4*>(p.dH + cell);
+      }
+    }
+    if (it > 0) {
+      float* wsp = p.ws + ((int64_t)((it & 1) * ctas) + blockIdx.x) * tile_elems;
+      if (warp == 0) {
+        // lane l polls CTA (jt_first + l / 16, slice l % 16): the producers of this K slice of dA
+        const int pj = jt_first + (lane >> 4);
+        bool seen = pj > jt_last;
+        const int* f = p.flag_da + (pj <= jt_last ? pj * LS2_S + (lane & 15) : 0);
+        int issued = 0;
+        long long t0 = 0;
+        while (issued < kb_per) {
+          if (!seen) seen = ld_acquire_gpu(f) >= it;
+          const uint32_t ready = __ballot_sync(0xffffffffu, seen);
+          if (issued == 0) LS2_STAMP(1);
+          while (issued < kb_per) {
+            const int pt = ((slice_u0 + 32 * issued) >> 7) - jt_first;          // producer tile of this k-block: 0 or 1
+            if (((ready >> (16 * pt)) & 0xFFFFu) != 0xFFFFu) break;
+            if (leader) {
+              mbar_wait(empty_bar(s), ph ^ 1u);
+              mbar_expect_tx(full_bar(s), LS2_STAGE);
+              const uint32_t st = ring + (uint32_t)s * LS2_STAGE;
+              tma_load_2d(st, &tmD, full_bar(s), k_base + 32 * issued, (t + 1) * p.N);
+              tma_load_2d(st + LP_TILE, &tmW, full_bar(s), k_base + 32 * issued, 128 * jt);
+              if (++s == LS2_STAGES) { s = 0; ph ^= 1u; }
+            }
+            ++issued;
+          }
+          if (ready != 0xffffffffu) {
+            if (t0 == 0) t0 = clock64();
+            else if (clock64() - t0 > 2000000000LL) __trap();
+          }
+        }
+        __syncwarp();
+        LS2_STAMP(2);
+      } else if (warp == 1 && leader) {
+        for (int kb = 0; kb < kb_per; ++kb) {
+          mbar_wait(full_bar(s), ph);
+          tcgen05_fence_after();
+          const uint32_t st = ring + (uint32_t)s * LS2_STAGE;
+          const uint64_t adesc = desc0 + (uint64_t)((st & 0x3FFFFu) >> 4);
+          const uint64_t bdesc = desc0 + (uint64_t)(((st + LP_TILE) & 0x3FFFFu) >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_tf32(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar(s));
+          if (++s == LS2_STAGES) { s = 0; ph ^= 1u; }
+        }
+        umma_commit(tmem_full_bar);
+      }
+      __syncwarp();
+      mbar_wait_warp(tmem_full_bar, (uint32_t)((it - 1) & 1));
+      tcgen05_fence_after();
+      __syncwarp();
+      LS2_STAMP(3);
+      // the partial tile to the workspace: this thread's row, 64 columns
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c0 = chalf * 64 + cc * 32;
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+        float4* dst = reinterpret_cast<float4*>(wsp + (int64_t)prow * 128 + c0);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) __stcg(dst + q, make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+      }
+      tcgen05_fence_before();
+      __syncthreads();
+      if (threadIdx.x == 0) st_release_gpu(p.flag_part + blockIdx.x, it);
+      LS2_STAMP(4);
+      // the 16 partials of unit tile jt: lanes 0..15 of every warp poll one each (every warp reads them)
+      {
+        const int* f = p.flag_part + jt * LS2_S + (lane & 15);
+        long long t0 = 0;
+        while (true) {
+          const bool ok = ld_acquire_gpu(f) >= it;
+          if (__all_sync(0xffffffffu, ok)) break;
+          if (t0 == 0) t0 = clock64();
+          else if (clock64() - t0 > 2000000000LL) __trap();
+        }
+      }
+      LS2_STAMP(5);
+      const float* src = p.ws + ((int64_t)((it & 1) * ctas) + jt * LS2_S) * tile_elems + (int64_t)trow * 128 + 4 * lane;
+      float4 part[LS2_S];
+#pragma unroll
+      for (int z = 0; z < LS2_S; ++z) part[z] = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)z * tile_elems));
+#pragma unroll
+      for (int z = 0; z < LS2_S; ++z) { dh.x += part[z].x; dh.y += part[z].y; dh.z += part[z].z; dh.w += part[z].w; }
+      LS2_STAMP(6);
+    }
+    if (it < p.T) {
+      float4 d0, d1, d2, d3;
+#define LS2_CELL(m)                                                         \
+      {                                                                     \
+        const float tc = lp_tanh(cn.m);                                     \
+        const float dc = dh.m * go.m * (1.f - tc * tc) + dcn.m;             \
+        d0.m = dc * gg.m * gi.m * (1.f - gi.m);                             \
+        d1.m = dc * cp.m * gf.m * (1.f - gf.m);                             \
+        d2.m = dh.m * tc * go.m * (1.f - go.m);                             \
+        d3.m = dc * gi.m * (1.f - gg.m * gg.m);                             \
+        dcn.m = dc * gf.m;                                                  \
+      }
+      LS2_CELL(x) LS2_CELL(y) LS2_CELL(z) LS2_CELL(w)
+#undef LS2_CELL
+      if (live) {
+        float* dp = p.dA + (int64_t)t * sA + gcell;
+        *reinterpret_cast<float4*>(dp) = d0;
+        *reinterpret_cast<float4*>(dp + H) = d1;
+        *reinterpret_cast<float4*>(dp + 2 * H) = d2;
+        *reinterpret_cast<float4*>(dp + 3 * H) = d3;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        asm volatile("fence.proxy.async.global;" ::: "memory");
+        st_release_gpu(p.flag_da + blockIdx.x, it + 1);
+      }
+      LS2_STAMP(7);
+    } else if (live) {
+      *reinterpret_cast<float4*>(p.dH + cell) = dh;          // dL/dh0
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+}
+
 }  // namespace tc
 
 // The whole forward recurrence as one launch.  *taken = 0 (nothing launched) when the shape is outside the
@@ -704,6 +931,56 @@ static int lstm_persist_bwd_launch(const float* gates, const float* cbuf, const 
   return 0;
 }
 
+// The cluster-free backward kernel (lstm_stream_bwd_kernel): *taken = 1 when launched.
+static int lstm_stream_bwd_launch(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA, int64_t T,
+                                  int64_t N, int64_t H, int* taken) {
+  using namespace tc;
+  *taken = 0;
+  const int ctas = (int)(H >> 3), slice = (int)(H >> 2);
+  for (int s = 0; s < 4; ++s)                        // a K slice's units must come from at most two 128-unit tiles
+    if (((s * slice + slice - 1) >> 7) - ((s * slice) >> 7) > 1) return 0;
+  const size_t smem = (size_t)LS2_STAGES * LS2_STAGE + 128 + 1024;
+  static uint32_t configured = 0;
+  if (first_use_on_device(&configured))
+    MC_CHECK(cudaFuncSetAttribute(lstm_stream_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static int per_sm[16] = {};
+  int& fit = per_sm[device() & 15];
+  if (fit == 0) {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, lstm_stream_bwd_kernel, LP_THREADS, smem) != cudaSuccess) { cudaGetLastError(); nb = 0; }
+    fit = nb > 0 ? nb : -1;
+  }
+  if (fit < 0 || (int64_t)fit * sm_count() < ctas) return 0;     // every CTA waits for others: all must be resident
+
+  ScratchFrame scratch;
+  float* ws = scratch.floats((size_t)2 * ctas * 128 * 128);
+  int* flags = reinterpret_cast<int*>(scratch.floats((size_t)2 * ctas));
+  if (!ws || !flags) return 1;
+  MC_CHECK(cudaMemsetAsync(flags, 0, sizeof(int) * 2 * (size_t)ctas, stream()));
+  CUtensorMap tmD, tmW;
+  {
+    const uint64_t dims[2] = {(uint64_t)(4 * H), (uint64_t)(T * N)};
+    const uint64_t strides[1] = {(uint64_t)(4 * H) * 4};
+    const uint32_t box[2] = {32, 128};
+    if (make_tmap(&tmD, dA, 2, dims, strides, box, false)) return 1;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)(4 * H), (uint64_t)H};
+    const uint64_t strides[1] = {(uint64_t)(4 * H) * 4};
+    const uint32_t box[2] = {32, 128};
+    if (make_tmap(&tmW, Wh, 2, dims, strides, box, false)) return 1;
+  }
+  LstmStreamBwdParams p;
+  p.gates = gates; p.cbuf = cbuf; p.dH = dH; p.dA = dA; p.ws = ws; p.flag_da = flags; p.flag_part = flags + ctas;
+  p.T = (int)T; p.N = (int)N; p.H = (int)H;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(LP_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream();
+  MC_CHECK(cudaLaunchKernelEx(&cfg, lstm_stream_bwd_kernel, tmD, tmW, p));
+  count_launch();
+  *taken = 1;
+  return 0;
+}
+
 // The whole backward recurrence as one launch (same range and conditions as lstm_persist_fwd): 64-unit clusters
 // when the device holds H/64 of them (H <= 896 on this pool's B200), else nothing is launched.
 int lstm_persist_bwd(const float* gates, const float* cbuf, const float* Wh, float* dH, float* dA, int64_t T, int64_t N, int64_t H,
@@ -714,7 +991,7 @@ int lstm_persist_bwd(const float* gates, const float* cbuf, const float* Wh, flo
     const char* e = getenv("MC_LSTM_PERSIST");
     const char* b = getenv("MC_LSTM_PERSIST_BWD");
     enabled = ((e && e[0] == '0') || (b && b[0] == '0')) ? 0 : 1;
-    force80 = (b && b[0] == '8') ? 1 : 0;           // MC_LSTM_PERSIST_BWD=80: the 80-unit configuration everywhere (tests)
+    force80 = (b && b[0] == '8') ? 1 : ((b && b[0] == 's') ? 2 : 0);   // =80: the 80-unit clusters; =stream: the cluster-free kernel (tests)
   }
   if (!enabled || T <= 0 || N <= 0 || N > 128 || H < 128 || H > 1024 || (H & 127)) return 0;
   if (T * N >= (int64_t)1 << 30) return 0;
@@ -725,7 +1002,12 @@ int lstm_persist_bwd(const float* gates, const float* cbuf, const float* Wh, flo
   // 64 KB in flight against ~1.2 us of TMA latency is 53 GB/s per SM -- 4.9 us for the 256 KB of dA a CTA needs per
   // step.  It therefore runs only on request (MC_LSTM_PERSIST_BWD=80); the 64-unit configuration (six stages,
   // 8.7 us per step at H = 896) is the default wherever its clusters fit.
-  if (force80) return lstm_persist_bwd_launch<80, 4>(gates, cbuf, Wh, dH, dA, T, N, H, taken);
+  if (force80 == 1) return lstm_persist_bwd_launch<80, 4>(gates, cbuf, Wh, dH, dA, T, N, H, taken);
+  if (force80 == 2) return lstm_stream_bwd_launch(gates, cbuf, Wh, dH, dA, T, N, H, taken);
+  // (lstm_stream_bwd_kernel, the cluster-free variant for H = 1024, is correct but MEASURED at 16.9 us per step against
+  //  10.0 us for the launch-per-step path (profiles/r2w): its two flag hops per step -- partial tiles through L2, then
+  //  dA -- cost 3.1 + 4.2 us with the skew of 128 CTAs, more than the two kernel boundaries they replace.  On request
+  //  only: MC_LSTM_PERSIST_BWD=stream.)
   return lstm_persist_bwd_launch<64, 6>(gates, cbuf, Wh, dH, dA, T, N, H, taken);
 }
 

@@ -148,6 +148,18 @@ def test_backward_outside_the_range_falls_back(cuda):
     assert rel(ddA.asnumpy(), want_dA) <= TF32_TOL and rel(ddH.asnumpy()[0], want_dh0) <= TF32_TOL
 
 
+def test_backward_cluster_free_kernel_on_every_shape():
+    """MC_LSTM_PERSIST_BWD=stream runs lstm_stream_bwd_kernel (no clusters, Wh streamed from L2, partials through an L2
+    workspace; opt-in: measured slower than the launch-per-step path at H = 1024) on all the shapes of this file."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, '-m', 'pytest', os.path.join(root, 'tests', 'test_lstm_persist_gpu.py'), '-q', '-x',
+                          '-m', 'gpu', '-k', 'persistent_backward_matches', '-p', 'no:cacheprovider'],
+                         env=dict(os.environ, PYTHONPATH=root, MC_LSTM_PERSIST_BWD='stream'), cwd=root, capture_output=True,
+                         text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-2000:]
+
+
 def test_backward_80_unit_configuration_opt_in():
     """MC_LSTM_PERSIST_BWD=80 selects the 80-unit clusters (13 clusters at H = 1024, a k-block of dA may straddle two
     producers' units): same float64 parity, in a process of its own because the switch is read once."""

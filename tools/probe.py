@@ -106,7 +106,7 @@ def case_lstmb(lib, T=100, N=128, H=1024):
     return (lambda: lib.mc_lstm_seq_bwd(gt.ptr, cb.ptr, Wh.ptr, dH.ptr, dA.ptr, T, N, H, 1), H // 8, keep)
 
 
-CASES = {'lstmb': case_lstmb, 'lstmp': case_lstmp, 'wgh': case_wgh, 'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
+CASES = {'lstms': case_lstmb, 'lstmb': case_lstmb, 'lstmp': case_lstmp, 'wgh': case_wgh, 'gemm': case_gemm, 'head': case_head, 'bnf': case_bnf, 'bnb': case_bnb}
 
 
 def main():
