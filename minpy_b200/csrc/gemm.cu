@@ -356,8 +356,6 @@ struct GemmParams {
   int cluster;         // > 1: the grid.z slices of a tile are one thread-block cluster; partials meet in DSMEM
   int group_m;         // tile raster: CTAs walk `group_m` M-tiles for each N-tile before moving on (0 = x-major)
   int half_from;       // persistent kernel: work items >= half_from are HALF-width tiles (two per tile), -1 = none
-  int mc_x, mc_y;      // one-tile kernel: 2 = the A tile is shared with the x-neighbour (next N tile) / the B tile with the
-                       // y-neighbour (next M tile) of a (mc_x, mc_y, 1) cluster: each CTA loads half of it and TMA multicasts
   int lstm_mode;       // cluster epilogue: 0 plain, 1 LSTM gate forward, 2 LSTM gate backward (lstm.cu)
   LstmEpilogue lstm;
 };
@@ -476,23 +474,10 @@ __device__ __forceinline__ void cluster_reduce(const GemmParams& p, uint32_t sme
 //   MN-major tile: R/32 blocks of [BK k-rows x 128 B] (4096 B each, LBO), written by TMA with
 //            SWIZZLE_128B_ATOM_32B (pattern repeats every 4 k-rows = 512 B, SBO); one MMA
 //            (K = 8) covers two such groups: start + 1024k.
-__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "h"(mask)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask)
-               : "memory");
-}
-
 MC_PROBE_DEFINE(gemm)
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                const __grid_constant__ CUtensorMap tmB,
-                                                               const __grid_constant__ CUtensorMap tmAh,
-                                                               const __grid_constant__ CUtensorMap tmBh,
                                                                const GemmParams p) {
   constexpr uint32_t A_BYTES = BM * BK * 4;
   constexpr uint32_t B_BYTES = BN * BK * 4;
@@ -533,10 +518,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
     // descriptor fetch overlaps the previous kernel's tail (the maps are kernel parameters: legal before pdl_sync)
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
-    // multicast: a stage is refilled by this CTA and by the neighbours it shares a tile with, so its `empty` barrier
-    // collects the MMA commits of all of them
-    const uint32_t empties = 1u + (p.mc_x > 1 ? 1u : 0u) + (p.mc_y > 1 ? 1u : 0u);
-    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), empties); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -549,13 +531,6 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
-  const bool mcast = p.mc_x > 1 || p.mc_y > 1;
-  // a neighbour's TMA writes into this CTA's shared memory and signals its barriers: they must exist first
-  if (mcast) asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-  const int cpx = mcast ? (int)(blockIdx.x & (unsigned)(p.mc_x - 1)) : 0, cpy = mcast ? (int)(blockIdx.y & (unsigned)(p.mc_y - 1)) : 0;
-  const uint16_t bit_self = (uint16_t)(1u << (cpx + p.mc_x * cpy));
-  const uint16_t mask_x = (uint16_t)(bit_self | (p.mc_x > 1 ? (1u << ((cpx ^ 1) + p.mc_x * cpy)) : 0u));   // shares my A tile
-  const uint16_t mask_y = (uint16_t)(bit_self | (p.mc_y > 1 ? (1u << (cpx + p.mc_x * (cpy ^ 1))) : 0u));   // shares my B tile
   MC_STAMP(gemm, 1);
   mc::pdl_sync();      // prologue done (on-chip state only); global memory from here on
   MC_STAMP(gemm, 2);
@@ -573,25 +548,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
       const uint32_t fb = full_bar(s);
       mbar_expect_tx(fb, STAGE_BYTES);
       const uint32_t sa = smem_base + s * STAGE_BYTES, sb = sa + A_BYTES;
-      if (p.mc_x > 1) {              // my half of the A tile, to me and to the x-neighbour
-        if (!a_mn) tma_load_2d_mc(sa + (uint32_t)cpx * (BM / 2 * 128u), &tmAh, fb, k0, m0 + cpx * (BM / 2), mask_x);
-        else {
-#pragma unroll
-          for (int j = 0; j < BM / 64; ++j) { const int jj = cpx * (BM / 64) + j; tma_load_2d_mc(sa + jj * 4096, &tmA, fb, m0 + 32 * jj, k0, mask_x); }
-        }
-      } else if (!a_mn) {
+      if (!a_mn) {
         tma_load_2d(sa, &tmA, fb, k0, m0);
       } else {
 #pragma unroll
         for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, fb, m0 + 32 * j, k0);
       }
-      if (p.mc_y > 1) {              // my half of the B tile, to me and to the y-neighbour
-        if (!b_mn) tma_load_2d_mc(sb + (uint32_t)cpy * (BN / 2 * 128u), &tmBh, fb, k0, n0 + cpy * (BN / 2), mask_y);
-        else {
-#pragma unroll
-          for (int j = 0; j < BN / 64; ++j) { const int jj = cpy * (BN / 64) + j; tma_load_2d_mc(sb + jj * 4096, &tmB, fb, n0 + 32 * jj, k0, mask_y); }
-        }
-      } else if (!b_mn) {
+      if (!b_mn) {
         tma_load_2d(sb, &tmB, fb, k0, n0);
       } else {
 #pragma unroll
@@ -622,8 +585,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
 #pragma unroll
       for (int k = 0; k < BK / UMMA_K; ++k)
         umma_tf32(tmem_base, adesc + (uint64_t)(astep * k), bdesc + (uint64_t)(bstep * k), idesc, (i > 0 || k > 0) ? 1u : 0u);
-      // frees the smem stage once these MMAs have read it (multicast: also in the neighbours that write into it)
-      if (mcast) umma_commit_mc(empty_bar(s), (uint16_t)(mask_x | mask_y)); else umma_commit(empty_bar(s));
+      umma_commit(empty_bar(s));  // frees the smem stage once these MMAs have read it
       if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
     umma_commit(tmem_full_bar);   // accumulator complete
@@ -810,8 +772,6 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_tf32_kernel(const __grid_cons
   MC_STAMP(gemm, 5);
   tcgen05_fence_before();
   __syncthreads();
-  // multicast: my MMA commits arrive on the neighbours' barriers too -- nobody leaves before everybody's have landed
-  if (mcast) asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
   }
@@ -1188,10 +1148,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) gemm_tf32_persistent_kernel(const
 }
 
 template <int BN, int STAGES>
-static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits,
-                       const CUtensorMap* tmAh_p = nullptr, const CUtensorMap* tmBh_p = nullptr) {
-  const CUtensorMap& tmAh = tmAh_p ? *tmAh_p : tmA;
-  const CUtensorMap& tmBh = tmBh_p ? *tmBh_p : tmB;
+static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits) {
   constexpr size_t SMEM = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) + (2 * STAGES + 1) * 8 + 16 + 1024;
   static uint32_t configured = 0;      // function attributes are per device
   if (first_use_on_device(&configured))
@@ -1209,24 +1166,11 @@ static int launch_tf32(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl_mode() != 0 ? 2 : 1;
-    MC_CHECK(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<BN, STAGES>, tmA, tmB, tmAh, tmBh, p));
+    MC_CHECK(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<BN, STAGES>, tmA, tmB, p));
     count_launch();
     return 0;
   }
-  if (p.mc_x > 1 || p.mc_y > 1) {        // tile neighbours as a (mc_x, mc_y, 1) cluster: shared operand tiles by TMA multicast
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid; cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = SMEM; cfg.stream = stream();
-    cudaLaunchAttribute attr[2];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)p.mc_x; attr[0].val.clusterDim.y = (unsigned)p.mc_y; attr[0].val.clusterDim.z = 1;
-    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[1].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = pdl_mode() != 0 ? 2 : 1;
-    MC_CHECK(cudaLaunchKernelEx(&cfg, gemm_tf32_kernel<BN, STAGES>, tmA, tmB, tmAh, tmBh, p));
-    count_launch();
-    return 0;
-  }
-  mc::launch_pdl(gemm_tf32_kernel<BN, STAGES>, grid, THREADS, SMEM, tmA, tmB, tmAh, tmBh, p);
+  mc::launch_pdl(gemm_tf32_kernel<BN, STAGES>, grid, THREADS, SMEM, tmA, tmB, p);
   MC_LAUNCHED();
   return 0;
 }
@@ -1375,7 +1319,6 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   p.counters = nullptr;
   p.cluster = 0;
   p.half_from = -1;
-  p.mc_x = 1; p.mc_y = 1;
   p.lstm_mode = 0;
   p.lstm = LstmEpilogue();
   // raster only when the grid is larger than one wave: keep <= ~48 MB of A panels resident in the 126 MB L2
@@ -1397,40 +1340,15 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   // -1..+1 us per call in isolation, but whole steps got slower (C3 0.341 -> 0.348 ms, C5 3.83 -> 4.06 ms,
   // profiles/r1z: S co-scheduled SMs per tile delay the next kernel's start).  MC_GEMM_CLUSTER=<max S>
   // enables it for experiments.
-  // TMA multicast between tile neighbours (one-tile kernel only): with 128 x BN tiles the A panel of an M tile is read by
-  // every N tile and the B panel by every M tile -- the K = 3072 / M = 3072 GEMMs of the MLP's first layer move 100 MB
-  // through L2 for 19 MB of operands.  In a (2, 2, 1) cluster each CTA loads half of its A tile for itself and its
-  // x-neighbour and half of its B tile for itself and its y-neighbour: half the L2 reads.  MC_GEMM_MULTICAST=0: off.
-  static int mcast = -1;
-  if (mcast < 0) { const char* e = getenv("MC_GEMM_MULTICAST"); mcast = e ? atoi(e) : 0; }
-  CUtensorMap tmAh, tmBh;
-  bool use_mc = false;
-  {
-    const int64_t gx = (N + BN - 1) / BN, gy = (M + BM - 1) / BM;
-    const bool one_tile_kernel = !(splits == 1 && BN == 128 && tiles > sm_count());      // (else: the persistent kernel)
-    if (mcast && one_tile_kernel && p.group_m == 0 && kb_per >= 4) {
-      p.mc_x = (gx % 2 == 0) ? 2 : 1;
-      p.mc_y = (gy % 2 == 0) ? 2 : 1;
-      if (mcast == 2) p.mc_y = 1;            // experiments: A only / B only
-      if (mcast == 3) p.mc_x = 1;
-      use_mc = p.mc_x > 1 || p.mc_y > 1;
-      if (use_mc) {
-        if (!ta) { if (make_tmap_2d(&tmAh, A, K, M, lda, BK, BM / 2, false)) return 1; } else tmAh = tmA;
-        if (tb)  { if (make_tmap_2d(&tmBh, B, K, N, ldb, BK, BN / 2, false)) return 1; } else tmBh = tmB;
-      }
-    }
-  }
   static int use_cluster = -1;
   if (use_cluster < 0) { const char* e = getenv("MC_GEMM_CLUSTER"); use_cluster = e ? atoi(e) : 0; }
   if (ext_ws) {
     if (splits > 1) p.ws = ext_ws;
     else { p.C = ext_ws; p.ldc = N; p.bias = nullptr; p.relu = 0; p.accumulate = 0; }
     *splits_out = splits;
-    return (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits, use_mc ? &tmAh : nullptr, use_mc ? &tmBh : nullptr)
-                       : launch_tf32<64, 8>(tmA, tmB, p, splits, use_mc ? &tmAh : nullptr, use_mc ? &tmBh : nullptr);
+    return (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
   }
   if (splits > 1 && use_cluster > 1) {
-    p.mc_x = p.mc_y = 1; use_mc = false;
     int S = 2;
     while (S * 2 <= splits && S * 2 <= use_cluster && S * 2 <= 16) S *= 2;
     for (; S > 1; S /= 2) {
@@ -1477,8 +1395,7 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
     }
     return launch_tf32_persistent<128, 6>(tmA, tmB, tmB, p, tiles, false);
   }
-  int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits, use_mc ? &tmAh : nullptr, use_mc ? &tmBh : nullptr)
-                       : launch_tf32<64, 8>(tmA, tmB, p, splits, use_mc ? &tmAh : nullptr, use_mc ? &tmBh : nullptr);
+  int rc = (BN == 128) ? launch_tf32<128, 6>(tmA, tmB, p, splits) : launch_tf32<64, 8>(tmA, tmB, p, splits);
   if (rc == 0 && splits > 1 && !p.counters && !p.cluster) {
     mc::launch(splitk_reduce_kernel, grid_for(M * N / 4 + 1, 256), 256, 0, p.ws, splits, M, N, C, ldc, bias, relu, accumulate);
     cudaError_t e = cudaGetLastError();

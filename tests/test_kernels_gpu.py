@@ -212,7 +212,7 @@ print('multiwave ok')
 """
 
 
-@pytest.mark.parametrize('env', [{}, {'MC_GEMM_BN256': '0'}, {'MC_GEMM_TAIL_SPLIT': '0'}, {'MC_GEMM_MULTICAST': '1', 'MC_GEMM_PERSISTENT': '0'}, {'MC_GEMM_PERSISTENT': '0'}, {'MC_GEMM_PERSISTENT': '0', 'MC_GEMM_RASTER': '0'}, {'MC_PDL': '0'}, {'MC_PDL': '2'}])
+@pytest.mark.parametrize('env', [{}, {'MC_GEMM_BN256': '0'}, {'MC_GEMM_TAIL_SPLIT': '0'}, {'MC_GEMM_PERSISTENT': '0'}, {'MC_GEMM_PERSISTENT': '0', 'MC_GEMM_RASTER': '0'}, {'MC_PDL': '0'}, {'MC_PDL': '2'}])
 def test_gemm_grids_beyond_one_wave(env):
     """Default (persistent TMEM-double-buffered kernel, rastered tile order), the one-tile-per-CTA kernel with and
     without the raster, and the three programmatic-launch modes all give the float64 product within the TF32 bound, with bias / signed-zero relu / accumulate epilogues and
