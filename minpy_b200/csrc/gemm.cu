@@ -1299,7 +1299,10 @@ static int gemm_tf32(int ta, int tb, int64_t M, int64_t N, int64_t K, const floa
   int splits = 1;
   // K >= 1024 only: with 16..31 k-blocks the combine launch costs more than the second slice saves
   // (profiles/r1za: (1024,512,512) 8.2 us split in two, 7.6 us whole)
-  if (tiles < sm_count() && num_kb >= split_from_kb) {
+  // On the side stream (weight gradients beside the backward chain) a GEMM has slack and its CTAs compete with the
+  // critical chain for SMs: K is split there only from 64 k-blocks on (mlp_c3: 28 -> 25 launches, 0.1465 -> 0.1458 ms).
+  const int split_from = (side_index() && split_from_kb < 64) ? 64 : split_from_kb;
+  if (tiles < sm_count() && num_kb >= split_from) {
     splits = (int)(sm_count() / tiles);
     const int maxs = num_kb / min_kb;  // at least 8 k-blocks (K = 256) per slice
     if (splits > maxs) splits = maxs;
