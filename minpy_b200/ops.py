@@ -848,7 +848,7 @@ def conv2d_nhwc_bwd(a, w, dy, pad=0, need_dx=True, need_db=True):
     dw = CudaArray.empty(w.shape)
     db = CudaArray.empty((F,)) if need_db else None
     # the weight gradient is read only by the update rule: beside the data-gradient chain, on the side stream
-    with side_stream(a.data, dy.data, dw, db):
+    with side_stream(a.data, dy.data, dw, db, any_size=True):     # measured: cnn_c4 0.2937 beside the chain, 0.295 in sequence
         lib.mc_conv2d_nhwc_wgrad(a.data.ptr, dy.data.ptr, dw.ptr, db.ptr if db is not None else None, a.N, C, a.H, a.W,
                                  a.Cp, a.wpad, F, dy.Cp, KH, KW, pad)
     return dx, dw, db
@@ -881,16 +881,20 @@ import contextlib as _contextlib
 import os as _os
 
 SIDE_STREAM = _os.environ.get('MINPY_SIDE_STREAM', '1') != '0'
+SIDE_MAX_BYTES = 32 << 20      # operands of one side-stream section beyond this run on the compute stream
 _side = {'keep': [], 'pending': False, 'active': False}
 
 
 @_contextlib.contextmanager
-def side_stream(*operands):
+def side_stream(*operands, any_size=False):
     """Library calls inside the block run on the side stream (mc_side_begin / mc_side_end): for work whose
     result nothing reads before the end of the backward pass (weight gradients).  `operands` -- everything the
     block reads -- and whatever is passed to `side_keep` stay referenced until `side_join`, because the
     host-side free lists hand a dropped buffer to the next MAIN-stream kernel at once."""
-    if not SIDE_STREAM or _side['active']:
+    # only for work that leaves room beside it: a contraction over tens of MB fills every SM and the memory system by
+    # itself (lstm_c5: its weight-gradient GEMMs beside the data-gradient chain measured 1.7 % SLOWER than in sequence)
+    big = (not any_size) and sum(getattr(a, 'nbytes', 0) for a in operands) > SIDE_MAX_BYTES
+    if not SIDE_STREAM or _side['active'] or big:
         yield False
         return
     lib = L()
