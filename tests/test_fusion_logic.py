@@ -245,3 +245,36 @@ def test_mlp_c3_step_launch_sequence(fake, monkeypatch):
         assert all(a[11] == 1 and a[15] == 1 and a[8] is not None for a in bwd)     # dropout + relu + bias gradient fused
     finally:
         minpy.set_global_policy('prefer_cuda')
+
+
+def test_side_stream_only_for_sections_that_leave_room(fake):
+    """ops.side_stream: operands beyond SIDE_MAX_BYTES (a contraction that fills the GPU by itself, e.g. the LSTM's
+    weight gradients over 210 MB of dA) run on the compute stream; small sections and sections marked any_size (the
+    convolution weight gradients, measured) go to the side stream."""
+    from minpy_b200 import ops
+    small, big = _arr((1024, 512)), _arr((12800, 4096))
+    assert big.nbytes > ops.SIDE_MAX_BYTES > small.nbytes
+    with ops.side_stream(small) as on_side:
+        assert on_side
+    assert fake.names() == ['mc_side_begin', 'mc_side_end']
+    ops.side_join()
+    del fake.calls[:]
+    with ops.side_stream(small, big) as on_side:
+        assert not on_side
+    assert fake.names() == []
+    with ops.side_stream(small, big, any_size=True) as on_side:
+        assert on_side
+    assert fake.names() == ['mc_side_begin', 'mc_side_end']
+    ops.side_join()
+    assert fake.names()[-1] == 'mc_side_join'
+
+
+def test_transpose_into_a_given_buffer(fake):
+    """ops.transpose(out=): one strided copy into the caller's array (the LSTM VJP writes the time-major gradient
+    straight into dH's slots 1..T); the shape is checked."""
+    from minpy_b200 import ops
+    x, out = _arr((4, 6, 8)), _arr((6, 4, 8))
+    assert ops.transpose(x, (1, 0, 2), out=out) is out
+    assert fake.names() == ['mc_strided_copy'] and fake.calls[0][1][1] == out.ptr
+    with pytest.raises(ValueError):
+        ops.transpose(x, (1, 0, 2), out=_arr((4, 6, 8)))
